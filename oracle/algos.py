@@ -1,0 +1,235 @@
+"""oracle/algos.py -- TEST INFRASTRUCTURE ONLY (CPU oracle).
+
+Restatement of the reference's host-side algorithms (the op sequences the hot path executes),
+written against an OpenFHE-like `cc` (oracle.ckks_ops.OracleCC).  Every function cites the
+reference lines it follows (/root/reference/src/...).  Used to (1) pin the oracle on the reference's
+known-answer vectors and level budgets, (2) produce expected outputs / op traces for the CUDA path.
+"""
+import math
+
+import numpy as np
+
+from .cheby import truncated_doubled_sinc_coeffs
+
+G4_COEFFS = [
+    0.0, 1.077117252745569, 0.0, -0.36166113998402755, 0.0, 0.2137420717859748, 0.0, -0.15635204788780485,
+    0.0, 0.11749645501187332, 0.0, -0.10074154666447852, 0.0, 0.08002086947825496, 0.0, -0.07533558758484624,
+    0.0, 0.059514472116534836, 0.0, -0.06146663712787884, 0.0, 0.04570084927999001, 0.0, -0.05403683682999072,
+    0.0, 0.03364293851188723, 0.0, -0.054459493266273494]  # src/sign.cpp:68-75
+G3 = [4589.0 / 1024.0, -16577.0 / 1024.0, 25614.0 / 1024.0, -12860.0 / 1024.0]  # sign.cpp:18-21
+F3 = [35.0 / 16.0, -35.0 / 16.0, 21.0 / 16.0, -5.0 / 16.0]  # sign.cpp:41-44
+F4 = [3.14208984375, -7.33154296875, 13.19677734375, -15.71044921875, 12.21923828125, -5.99853515625,
+      1.69189453125, -0.20947265625]  # sign.cpp:81-88
+
+
+def _odd7(cc, x, c):
+    """CompositeSign<3>::g_n / f_n evaluation order (sign.cpp:23-36, 46-59)"""
+    x2 = cc.EvalSquare(x)
+    x4 = cc.EvalSquare(x2)
+    y = cc.EvalMult(x, c[0])
+    y = cc.EvalAdd(y, cc.EvalMultAndRelinearize(cc.EvalMult(x, c[1]), x2))
+    c5x = cc.EvalMult(x, c[2])
+    c7x = cc.EvalMult(x, c[3])
+    c7x3 = cc.EvalMultAndRelinearize(c7x, x2)
+    return cc.EvalAdd(y, cc.EvalMultAndRelinearize(cc.EvalAdd(c5x, c7x3), x4))
+
+
+def _f4(cc, x):
+    """CompositeSign<4>::f_n (sign.cpp:79-157)"""
+    c = F4
+    x2 = cc.EvalSquare(x)
+    cx = [cc.EvalMult(x, v) for v in c]
+    x4 = cc.EvalSquare(x2)
+    c3x3 = cc.EvalMultAndRelinearize(cx[1], x2)
+    c7x3 = cc.EvalMultAndRelinearize(cx[3], x2)
+    c11x3 = cc.EvalMultAndRelinearize(cx[5], x2)
+    c15x3 = cc.EvalMultAndRelinearize(cx[7], x2)
+    x8 = cc.EvalSquare(x4)
+    y = cc.EvalAdd(cx[0], c3x3)
+    y = cc.EvalAdd(y, cc.EvalMultAndRelinearize(cc.EvalAdd(cx[2], c7x3), x4))
+    tmp1 = cc.EvalAdd(cx[4], c11x3)
+    tmp2 = cc.EvalAdd(cx[6], c15x3)
+    tmp1 = cc.EvalAdd(tmp1, cc.EvalMultAndRelinearize(tmp2, x4))
+    return cc.EvalAdd(y, cc.EvalMultAndRelinearize(tmp1, x8))
+
+
+def composite_sign(cc, x, n, dg, df):
+    """compositeSign<n> (sign.cpp:160-185): g_n applied max(dg,1) times, then f_n df times
+    (the first g_n call is unconditional, :174).  No bootstrap (multDepth sentinel 100)."""
+    if n == 3:
+        g = lambda v: _odd7(cc, v, G3)
+        f = lambda v: _odd7(cc, v, F3)
+    elif n == 4:
+        g = lambda v: cc.EvalChebyshevSeriesPS(v, G4_COEFFS, -1, 1)
+        f = lambda v: _f4(cc, v)
+    else:
+        raise ValueError("composite sign n must be 3 or 4")
+    y = g(x)
+    for _ in range(1, dg):
+        y = g(y)
+    for _ in range(df):
+        y = f(y)
+    return y
+
+
+def compare(cc, a, b, n, dg, df):
+    """Comparison::compare (comparison.cpp:4-22): (sign(a-b)+1)*0.5"""
+    s = composite_sign(cc, cc.EvalSub(a, b), n, dg, df)
+    return cc.EvalMult(cc.EvalAdd(s, 1.0), 0.5)
+
+
+class Rotator:
+    """RotationComposer<N>::rotate (rotation.h:215-233) with BINARY decomposition (:105-114)"""
+
+    def __init__(self, cc, N, indices):
+        self.cc, self.N, self.avail = cc, N, sorted(set(indices))
+
+    def rotate(self, ct, r):
+        if r % ct.slots == 0:
+            return ct.clone()
+        if r in self.avail:
+            return self.cc.EvalRotate(ct, r)
+        out = ct.clone()
+        for s in decompose_binary(r, self.avail, self.N, ct.slots):
+            out = self.cc.EvalRotate(out, s)
+        return out
+
+
+def decompose_binary(rotation, rot_indices, N, wrap):
+    """Decomposer<N>::decompose(..., BINARY) (rotation.h:53-114): returns step sizes"""
+    idx = sorted(rot_indices)
+    max_dec, step = 0, 1
+    for i in idx:  # calculateMax (:36-45)
+        if step == i // 2:
+            max_dec += i
+        step = i
+    steps = []
+    largest = idx[-1]
+    while rotation >= largest:
+        steps.append(largest)
+        rotation -= largest
+    if rotation:
+        while rotation > max_dec:
+            import bisect
+            legal = idx[bisect.bisect_left(idx, rotation) - 1]
+            steps.append(legal)
+            rotation -= legal
+        if rotation:
+            for i in range(31, -1, -1):
+                s = 1 << i
+                if s < N and rotation & s:
+                    steps.append(s)
+    return [s for s in steps if s % wrap != 0]
+
+
+DIRECT_SORT_PARAMS = {  # DirectSort<N>::getSizeParameters (sort_algo.h:87-201): multDepth, rotations
+    4: (23, [1, 2, 4, 8, 16]),
+    8: (24, [1, 2, 4, 6, 8, 16, 32, 64]),
+    16: (25, [1, 2, 3, 4, 8, 12, 16, 32, 64, 128, 256]),
+    32: (28, [1, 2, 3, 4, 8, 12, 16, 20, 24, 28, 32, 64, 128, 256, 512, 1024]),
+    64: (29, [1, 2, 3, 4, 5, 6, 7, 8, 16, 24, 32, 40, 48, 56, 64, 128, 256, 512, 1024, 2048, 4096]),
+    128: (30, [1, 2, 3, 4, 5, 6, 7, 8, 16, 24, 32, 40, 48, 56, 64, 72, 80, 88, 96, 104, 112, 120, 128, 256,
+               512, 1024, 2048, 4096, 8192, 16384]),
+}
+RANK_NP = {4: 2, 8: 2, 16: 4, 32: 4, 64: 8, 128: 8, 256: 16, 512: 16, 1024: 32, 2048: 32}  # sort_algo.h:383-416
+INDEX_NP = {4: 2, 8: 2, 16: 4, 32: 4, 64: 8, 128: 8, 256: 16, 512: 8, 1024: 8}  # sort_algo.h:670-703
+
+
+class DirectSort:
+    """DirectSort<N> (sort_algo.h:61-774): constructRank + rotationIndexCheckN"""
+
+    def __init__(self, cc, N, rot_indices, sinc_coeffs=None):
+        self.cc, self.N = cc, N
+        self.rot = Rotator(cc, N, rot_indices)
+        self.max_batch = cc.ctx.n // 2
+        self.zero = cc.encrypt(cc.encode([0.0] * N, slots=N))  # SortBase::createZeroCache (:42-45)
+        self.sinc = truncated_doubled_sinc_coeffs(N) if sinc_coeffs is None else sinc_coeffs
+
+    def mask(self, num_slots, k):  # generateMaskVector (:206-214)
+        v = np.zeros(num_slots)
+        v[k * self.N:(k + 1) * self.N] = 1.0
+        return v
+
+    def vec_rots_opt(self, baby, num_partition, num_slots, np_, is_):
+        """vecRotsOpt (:326-366)"""
+        cc = self.cc
+        outer = []
+        for j in range(num_partition // np_):
+            T = self.zero.clone()
+            T.slots = num_slots
+            for i in range(np_):
+                msk = np.roll(self.mask(num_slots, np_ * j + i), is_ * num_partition + j * np_)  # vectorRotate(-r)
+                pm = cc.MakeCKKSPackedPlaintext(msk, 1, 0, None, num_slots)
+                T = cc.EvalAdd(T, cc.EvalMult(baby[i], pm))
+            outer.append(self.rot.rotate(T, is_ * num_partition + j * np_))
+        return cc.EvalAddMany(outer)
+
+    def construct_rank(self, ct_in, sign_cfg):
+        """constructRank (:368-506)"""
+        cc, N = self.cc, self.N
+        num_partition = min(N, self.max_batch // N)
+        num_batch = N // num_partition
+        num_slots = N * num_partition
+        np_ = min(RANK_NP[N], num_partition)
+        baby = []
+        for i in range(np_):
+            t = self.rot.rotate(ct_in, i)
+            t.slots = num_slots
+            baby.append(t)
+        rank = self.zero.clone()
+        rank.slots = num_slots
+        for i in range(num_batch):
+            shifted = self.vec_rots_opt(baby, num_partition, num_slots, np_, i)
+            dup = ct_in.clone()
+            dup.slots = num_slots
+            rank = cc.EvalAdd(rank, compare(cc, dup, shifted, *sign_cfg))
+        for i in range(1, int(math.log2(num_partition)) + 1):
+            rank = cc.EvalAdd(rank, self.rot.rotate(rank, num_slots // (1 << i)))
+        rank.slots = N
+        return cc.EvalSub(rank, 0.5)
+
+    def blind_rotation_opt_n(self, masked, num_slots, np_, ib, num_partition):
+        """blindRotationOptN (:561-584)"""
+        cc = self.cc
+        result = self.zero.clone()
+        for i in range((num_slots // self.N) // np_):
+            tmp = self.zero.clone()
+            for j in range(np_):
+                msk = np.roll(self.mask(num_slots, np_ * i + j), -j)  # vectorRotate(msk, j): left by j
+                pm = cc.MakeCKKSPackedPlaintext(msk, 1, masked[j].level, None, num_slots)
+                tmp = cc.EvalAdd(tmp, cc.EvalMult(masked[j], pm))
+            tmp = self.rot.rotate(tmp, ib * num_partition + i * np_)
+            result = cc.EvalAdd(result, tmp)
+        return result
+
+    def rotation_index_check_n(self, rank, ct_in):
+        """rotationIndexCheckN (:658-750)"""
+        cc, N = self.cc, self.N
+        out = self.zero.clone()
+        num_partition = min(N, self.max_batch // N)
+        num_batch = N // num_partition
+        num_slots = num_partition * N
+        np_ = INDEX_NP.get(N, 4)
+        idx_pt = cc.MakeCKKSPackedPlaintext(np.arange(N, dtype=np.float64), 1, rank.level, None, N)
+        d = cc.EvalSub(idx_pt, rank)
+        d.slots = num_slots
+        ct_in = ct_in.clone()
+        ct_in.slots = num_slots
+        for b in range(num_batch):
+            chk = np.array([(b * num_partition + (i // N)) % N for i in range(num_slots)], dtype=np.float64)  # :272-286
+            pchk = cc.MakeCKKSPackedPlaintext(chk, 1, d.level, None, num_slots)
+            r = cc.EvalSub(d, pchk)
+            r = cc.EvalMult(r, 1.0 / N / 2)
+            r = cc.EvalChebyshevSeriesPS(r, self.sinc, -1, 1)
+            masked_input = cc.EvalMult(r, ct_in)
+            masked = [self.rot.rotate(masked_input, i) for i in range(np_)]
+            out = cc.EvalAdd(out, self.blind_rotation_opt_n(masked, num_slots, np_, b, num_partition))
+        for i in range(1, int(math.log2(num_partition)) + 1):
+            out = cc.EvalAdd(out, self.rot.rotate(out, num_slots // (1 << i)))
+        out.slots = N
+        return out
+
+    def sort(self, ct_in, sign_cfg):
+        """DirectSort::sort (:752-774)"""
+        rank = self.construct_rank(ct_in, sign_cfg)
+        return self.rotation_index_check_n(rank, ct_in)
