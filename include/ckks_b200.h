@@ -1,0 +1,113 @@
+/* ckks_b200.h -- C-ABI of the B200-native RNS-CKKS evaluation engine (libckks_b200.so).
+ *
+ * Drop-in boundary for oksuman/sorting-fhe.  The reference has no FFI: its seam is the set of
+ * lbcrypto::CryptoContextImpl<DCRTPoly> member functions its headers call after
+ * `#include "openfhe.h"` (src/sort_algo.h:3-12, src/comparison.h:3-9, src/sign.h:3-4,
+ * src/rotation.h:1-10, src/sort.h:1-13).  Every entry point below replaces one of those member
+ * functions (cited per function); sorting-fhe_b200/host/openfhe_shim.h re-creates the lbcrypto
+ * value types on top of this ABI so the sorter headers compile unchanged in spirit.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success, non-zero on
+ * failure with the message available from ckks_last_error() (thread-local) -- OpenFHE's
+ * OpenFHEException becomes a status code, the C++ shim rethrows std::runtime_error.
+ * Ciphertexts/plaintexts are opaque handles owning device memory, limb-major uint64
+ * [part][limb][ring_dim], EVALUATION (bit-reversed NTT) format; results are fresh handles,
+ * inputs are never mutated except by the *_set_* metadata calls (SetSlots semantics,
+ * src/sort_algo.h:429,434,447,501,710-711).  There is no CPU fallback: without a CUDA device
+ * every compute call fails, except on a context created with dry_run=1 (metadata only).
+ */
+#ifndef CKKS_B200_H
+#define CKKS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ckks_ctx ckks_ctx_t; /* CryptoContext<DCRTPoly> */
+typedef struct ckks_ct ckks_ct_t;   /* Ciphertext<DCRTPoly> (2 polys) or Plaintext (1 poly) */
+
+const char* ckks_last_error(void);
+
+/* GenCryptoContext(CCParams<CryptoContextCKKSRNS>) -- tests/DirectSortTest.cpp:29-44,
+ * src/sort_algo.h:87-201 (SetMultiplicativeDepth, SetScalingModSize, SetRingDim),
+ * src/kway_adapter.h:45-46 (SetFirstModSize).  scaling_technique: 1 = FLEXIBLEAUTOEXT (OpenFHE
+ * default), 0 = FLEXIBLEAUTO.  num_large_digits 0 = OpenFHE default.  seed drives the
+ * counter-based sampler for keys and encryption randomness. */
+int ckks_ctx_create(ckks_ctx_t** out, int log_ring_dim, int mult_depth, int scaling_mod_size, int first_mod_size,
+                    int num_large_digits, int scaling_technique, uint64_t seed, int dry_run);
+int ckks_ctx_destroy(ckks_ctx_t* ctx); /* ClearEvalMultKeys/ClearEvalAutomorphismKeys/ReleaseAllContexts */
+int ckks_ctx_set_stream(ckks_ctx_t* ctx, void* cuda_stream);
+int ckks_ctx_sync(ckks_ctx_t* ctx);
+/* what: 0 ring dim (GetRingDimension, sort_algo.h:80), 1 #Q limbs, 2 #P limbs, 3 digit size alpha, 4 #digits,
+ * 5 cyclotomic order (rotation.h:267), 6 kernel launches so far, 7 device bytes of keys */
+int ckks_ctx_info(ckks_ctx_t* ctx, int what, int64_t* out);
+int ckks_ctx_get_moduli(ckks_ctx_t* ctx, uint64_t* moduli, uint64_t* roots, int cap);   /* Q then P */
+int ckks_ctx_get_scaling_factors(ckks_ctx_t* ctx, double* sf_real, double* sf_big, int cap);
+
+/* KeyGen / EvalMultKeyGen / EvalRotateKeyGen -- tests/DirectSortTest.cpp:40-57 */
+int ckks_keygen(ckks_ctx_t* ctx);
+int ckks_eval_mult_keygen(ckks_ctx_t* ctx);
+int ckks_eval_rotate_keygen(ckks_ctx_t* ctx, const int32_t* indices, int count);
+/* raw key material (host buffers), normal form: secret [Q+P][n]; pk [2][Q][n] (b,a);
+ * evk (kind 0 = relin, else signed rotation index via is_rotation) [digit][2 (b,a)][Q+P][n].
+ * This is the hook the OpenFHE BINARY importer (sort.h:31-74) feeds. */
+int ckks_export_secret(ckks_ctx_t* ctx, uint64_t* host, size_t cap_words);
+int ckks_export_public_key(ckks_ctx_t* ctx, uint64_t* host, size_t cap_words);
+int ckks_export_eval_key(ckks_ctx_t* ctx, int is_rotation, int32_t index, uint64_t* host, size_t cap_words);
+int ckks_import_eval_key(ckks_ctx_t* ctx, int is_rotation, int32_t index, const uint64_t* host, size_t words);
+
+/* MakeCKKSPackedPlaintext(vec, scaleDeg, level, nullptr, slots) -- sort_algo.h:341,356,573,706,715.
+ * slots = 0 -> next power of two >= count. */
+int ckks_make_packed_plaintext(ckks_ctx_t* ctx, const double* values, int count, int scale_deg, int level, int slots,
+                               ckks_ct_t** out);
+int ckks_encrypt(ckks_ctx_t* ctx, const ckks_ct_t* plaintext, ckks_ct_t** out);            /* encryption.cpp:10 */
+int ckks_decrypt(ckks_ctx_t* ctx, const ckks_ct_t* ct, double* values, int count);        /* encryption.cpp:18,31 */
+
+/* handle management + metadata (Clone, SetSlots/GetSlots, GetLevel, GetNoiseScaleDeg, GetScalingFactor) */
+int ckks_ct_free(ckks_ct_t* ct);
+int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out);
+int ckks_ct_set_slots(ckks_ct_t* ct, int slots);
+/* what: 0 slots, 1 level, 2 noiseScaleDeg, 3 #limbs, 4 #polys */
+int ckks_ct_get(const ckks_ct_t* ct, int what, int64_t* out);
+int ckks_ct_get_scaling_factor(const ckks_ct_t* ct, double* out);
+/* host <-> device transfer of the raw limbs (the e2e path of bench.py; OpenFHE import format hook) */
+int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap_words);
+int ckks_ct_import(ckks_ctx_t* ctx, const uint64_t* host, int polys, int limbs, int level, int noise_scale_deg,
+                   double scaling_factor, int slots, ckks_ct_t** out);
+
+/* EvalAdd / EvalSub over (ct,ct) (ct,pt) (pt,ct) -- ~130 call sites, e.g. sort_algo.h:358,454,708,720 */
+int ckks_eval_add(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out);
+int ckks_eval_sub(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out);
+int ckks_eval_add_const(ckks_ctx_t* ctx, const ckks_ct_t* a, double c, ckks_ct_t** out);   /* comparison.cpp:19 */
+int ckks_eval_sub_const(ckks_ctx_t* ctx, const ckks_ct_t* a, double c, ckks_ct_t** out);   /* sort_algo.h:504 */
+int ckks_eval_const_sub(ckks_ctx_t* ctx, double c, const ckks_ct_t* a, ckks_ct_t** out);   /* comparison.cpp:38 */
+int ckks_eval_negate(ckks_ctx_t* ctx, const ckks_ct_t* a, ckks_ct_t** out);
+int ckks_eval_add_many(ckks_ctx_t* ctx, const ckks_ct_t* const* cts, int count, ckks_ct_t** out); /* sort_algo.h:364 */
+/* EvalMult(ct,ct) == EvalMultAndRelinearize, EvalMult(ct,pt), EvalMult(ct,double), EvalSquare -- sign.cpp:23-56 */
+int ckks_eval_mult(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out);
+int ckks_eval_mult_const(ckks_ctx_t* ctx, const ckks_ct_t* a, double c, ckks_ct_t** out);
+int ckks_eval_square(ckks_ctx_t* ctx, const ckks_ct_t* a, ckks_ct_t** out);
+/* EvalRotate(ct, index) -- rotation.h:224,231; fails if no key for index (OpenFHE throws) */
+int ckks_eval_rotate(ckks_ctx_t* ctx, const ckks_ct_t* a, int32_t index, ckks_ct_t** out);
+int ckks_has_rotation_key(ckks_ctx_t* ctx, int32_t index);
+/* EvalChebyshevSeriesPS(ct, coeffs, a, b) -- sort_algo.h:727-728, sign.cpp:76 */
+int ckks_eval_chebyshev_series_ps(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, double a, double b,
+                                  ckks_ct_t** out);
+/* EvalPolyLinear(ct, coeffs) -- mehp24_utils.cpp:256-259 */
+int ckks_eval_poly_linear(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, ckks_ct_t** out);
+
+/* op statistics (JSON) for roofline accounting; reset clears counters */
+int ckks_stats_json(ckks_ctx_t* ctx, char* buf, size_t cap);
+int ckks_stats_reset(ckks_ctx_t* ctx);
+
+/* kernel-level entry points on raw buffers, for parity tests and kernel benchmarks.
+ * *_host variants stage through host memory; *_dev variants take device pointers. */
+int ckks_ntt_host(ckks_ctx_t* ctx, uint64_t* data, int rows, const int32_t* modulus_ids, int inverse);
+int ckks_ntt_dev(ckks_ctx_t* ctx, void* dev_data, int rows, int first_modulus, int inverse);
+int ckks_key_switch_dev(ckks_ctx_t* ctx, const void* dev_src, int limbs, int is_rotation, int32_t index, void* dev_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,301 @@
+"""sorting-fhe_b200 -- B200-native RNS-CKKS engine behind the oksuman/sorting-fhe sorter API.
+
+This module is only the ctypes binding of the C-ABI in include/ckks_b200.h (libckks_b200.so,
+hand-written sm_100a CUDA) plus the binding of the host-side sorter library
+(libsortfhe_host.so: the C++ re-creation of the reference's sort_algo.h / comparison.h / sign.h /
+rotation.h).  There is no Python or CPU compute path: if the shared library is missing the import
+fails loudly, and every compute call fails without a CUDA device (dry_run contexts carry metadata only).
+
+The package directory name contains a hyphen, so import it with
+    importlib.import_module("sorting-fhe_b200")
+"""
+import ctypes
+import json
+import os
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_DIR, "libckks_b200.so")
+if not os.path.exists(LIB_PATH):
+    raise ImportError("libckks_b200.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                      "(the CUDA extension is mandatory; there is no fallback path)")
+_L = ctypes.CDLL(LIB_PATH)
+_L.ckks_last_error.restype = ctypes.c_char_p
+_vp, _i, _d, _u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_uint64
+_pp = ctypes.POINTER(ctypes.c_void_p)
+
+
+class CkksError(RuntimeError):
+    pass
+
+
+def _chk(rc):
+    if rc != 0:
+        raise CkksError(_L.ckks_last_error().decode())
+
+
+def _u64p(a):
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))
+
+
+def _f64p(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+class Ciphertext:
+    """Ciphertext<DCRTPoly> / Plaintext handle (value semantics of the shared_ptr are the caller's)"""
+
+    def __init__(self, eng, h):
+        self.eng, self.h = eng, h
+
+    def __del__(self):
+        try:
+            if self.h:
+                _L.ckks_ct_free(ctypes.c_void_p(self.h))
+                self.h = None
+        except Exception:
+            pass
+
+    def _get(self, what):
+        o = ctypes.c_int64()
+        _chk(_L.ckks_ct_get(_vp(self.h), what, ctypes.byref(o)))
+        return o.value
+
+    slots = property(lambda s: s._get(0), lambda s, v: _chk(_L.ckks_ct_set_slots(_vp(s.h), int(v))))
+    level = property(lambda s: s._get(1))
+    deg = property(lambda s: s._get(2))
+    nlimbs = property(lambda s: s._get(3))
+    parts = property(lambda s: s._get(4))
+
+    @property
+    def sf(self):
+        o = ctypes.c_double()
+        _chk(_L.ckks_ct_get_scaling_factor(_vp(self.h), ctypes.byref(o)))
+        return o.value
+
+    def clone(self):
+        o = ctypes.c_void_p()
+        _chk(_L.ckks_ct_clone(_vp(self.h), ctypes.byref(o)))
+        return Ciphertext(self.eng, o.value)
+
+    def export(self):
+        """raw limbs [parts][nlimbs][n] (device -> host)"""
+        a = np.empty((self.parts, self.nlimbs, self.eng.n), dtype=np.uint64)
+        _chk(_L.ckks_ct_export(_vp(self.h), _u64p(a), a.size))
+        return a
+
+    # OpenFHE spellings used by the reference code
+    def Clone(self):
+        return self.clone()
+
+    def SetSlots(self, s):
+        self.slots = s
+
+    def GetSlots(self):
+        return self.slots
+
+    def GetLevel(self):
+        return self.level
+
+
+class Engine:
+    """CryptoContext<DCRTPoly> over the C-ABI"""
+
+    def __init__(self, log_n, mult_depth, scaling_mod_size=40, first_mod_size=60, num_large_digits=0, ext=True,
+                 seed=1, dry_run=False, stream=None):
+        h = ctypes.c_void_p()
+        _chk(_L.ckks_ctx_create(ctypes.byref(h), log_n, mult_depth, scaling_mod_size, first_mod_size, num_large_digits,
+                                1 if ext else 0, _u64(seed), 1 if dry_run else 0))
+        self.h = h.value
+        self.log_n, self.n, self.dry = log_n, 1 << log_n, dry_run
+        if stream is not None:
+            _chk(_L.ckks_ctx_set_stream(_vp(self.h), _vp(stream)))
+        self.size_q, self.size_p = self.info(1), self.info(2)
+        self.alpha, self.num_part_q = self.info(3), self.info(4)
+
+    ctx = property(lambda s: s)  # so algorithm code written against oracle.OracleCC (cc.ctx.n) also drives the engine
+
+    def close(self):
+        if self.h:
+            _L.ckks_ctx_destroy(_vp(self.h))
+            self.h = None
+
+    def info(self, what):
+        o = ctypes.c_int64()
+        _chk(_L.ckks_ctx_info(_vp(self.h), what, ctypes.byref(o)))
+        return o.value
+
+    def sync(self):
+        _chk(_L.ckks_ctx_sync(_vp(self.h)))
+
+    def moduli(self):
+        m = np.zeros(self.size_q + self.size_p, dtype=np.uint64)
+        r = np.zeros_like(m)
+        _chk(_L.ckks_ctx_get_moduli(_vp(self.h), _u64p(m), _u64p(r), m.size))
+        return [int(x) for x in m], [int(x) for x in r]
+
+    def scaling_factors(self):
+        a = np.zeros(self.size_q, dtype=np.float64)
+        b = np.zeros(self.size_q, dtype=np.float64)
+        _chk(_L.ckks_ctx_get_scaling_factors(_vp(self.h), _f64p(a), _f64p(b), a.size))
+        return a, b[:max(self.size_q - 1, 0)]
+
+    def stats(self, reset=False):
+        buf = ctypes.create_string_buffer(1 << 20)
+        _chk(_L.ckks_stats_json(_vp(self.h), buf, len(buf)))
+        if reset:
+            _chk(_L.ckks_stats_reset(_vp(self.h)))
+        return json.loads(buf.value.decode())
+
+    # ---- keys
+    def KeyGen(self):
+        _chk(_L.ckks_keygen(_vp(self.h)))
+
+    def EvalMultKeyGen(self):
+        _chk(_L.ckks_eval_mult_keygen(_vp(self.h)))
+
+    def EvalRotateKeyGen(self, indices):
+        a = (ctypes.c_int32 * len(indices))(*indices)
+        _chk(_L.ckks_eval_rotate_keygen(_vp(self.h), a, len(indices)))
+
+    def export_secret(self):
+        a = np.empty((self.size_q + self.size_p, self.n), dtype=np.uint64)
+        _chk(_L.ckks_export_secret(_vp(self.h), _u64p(a), a.size))
+        return a
+
+    def export_public_key(self):
+        a = np.empty((2, self.size_q, self.n), dtype=np.uint64)
+        _chk(_L.ckks_export_public_key(_vp(self.h), _u64p(a), a.size))
+        return a
+
+    def export_eval_key(self, rotation=None):
+        a = np.empty((self.num_part_q, 2, self.size_q + self.size_p, self.n), dtype=np.uint64)
+        _chk(_L.ckks_export_eval_key(_vp(self.h), 0 if rotation is None else 1, 0 if rotation is None else rotation,
+                                     _u64p(a), a.size))
+        return a
+
+    def import_eval_key(self, a, rotation=None):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        _chk(_L.ckks_import_eval_key(_vp(self.h), 0 if rotation is None else 1, 0 if rotation is None else rotation,
+                                     _u64p(a), a.size))
+
+    # ---- encode / encrypt / decrypt
+    def _out(self, rc, o):
+        _chk(rc)
+        return Ciphertext(self, o.value)
+
+    def MakeCKKSPackedPlaintext(self, values, scale_deg=1, level=0, params=None, slots=None):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_make_packed_plaintext(_vp(self.h), _f64p(v), v.size, scale_deg, level, slots or 0,
+                                                       ctypes.byref(o)), o)
+
+    encode = lambda self, values, scale_deg=1, level=0, slots=None: self.MakeCKKSPackedPlaintext(values, scale_deg, level, None, slots)
+
+    def encrypt(self, pt):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_encrypt(_vp(self.h), _vp(pt.h), ctypes.byref(o)), o)
+
+    def decrypt(self, ct, length=None):
+        n = ct.slots if length is None else length
+        out = np.zeros(n, dtype=np.float64)
+        _chk(_L.ckks_decrypt(_vp(self.h), _vp(ct.h), _f64p(out), n))
+        return out
+
+    decode = decrypt
+
+    def import_ct(self, arr, level, deg, sf, slots):
+        arr = np.ascontiguousarray(arr, dtype=np.uint64)
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_ct_import(_vp(self.h), _u64p(arr), arr.shape[0], arr.shape[1], level, deg, _d(sf), slots,
+                                           ctypes.byref(o)), o)
+
+    # ---- evaluation (OpenFHE names)
+    def _bin(self, f, a, b):
+        o = ctypes.c_void_p()
+        return self._out(f(_vp(self.h), _vp(a.h), _vp(b.h), ctypes.byref(o)), o)
+
+    def _cst(self, f, a, x):
+        o = ctypes.c_void_p()
+        return self._out(f(_vp(self.h), _vp(a.h), _d(float(x)), ctypes.byref(o)), o)
+
+    def EvalAdd(self, a, b):
+        if isinstance(b, (int, float)):
+            return self._cst(_L.ckks_eval_add_const, a, b)
+        return self._bin(_L.ckks_eval_add, a, b)
+
+    def EvalSub(self, a, b):
+        if isinstance(a, (int, float)):
+            o = ctypes.c_void_p()
+            return self._out(_L.ckks_eval_const_sub(_vp(self.h), _d(float(a)), _vp(b.h), ctypes.byref(o)), o)
+        if isinstance(b, (int, float)):
+            return self._cst(_L.ckks_eval_sub_const, a, b)
+        return self._bin(_L.ckks_eval_sub, a, b)
+
+    def EvalNegate(self, a):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_negate(_vp(self.h), _vp(a.h), ctypes.byref(o)), o)
+
+    def EvalAddMany(self, cts):
+        arr = (ctypes.c_void_p * len(cts))(*[c.h for c in cts])
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_add_many(_vp(self.h), arr, len(cts), ctypes.byref(o)), o)
+
+    def EvalMult(self, a, b):
+        if isinstance(b, (int, float)):
+            return self._cst(_L.ckks_eval_mult_const, a, b)
+        return self._bin(_L.ckks_eval_mult, a, b)
+
+    EvalMultAndRelinearize = EvalMult
+
+    def EvalSquare(self, a):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_square(_vp(self.h), _vp(a.h), ctypes.byref(o)), o)
+
+    def EvalRotate(self, a, r):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_rotate(_vp(self.h), _vp(a.h), int(r), ctypes.byref(o)), o)
+
+    def EvalChebyshevSeriesPS(self, x, coeffs, a=-1.0, b=1.0):
+        v = np.ascontiguousarray(coeffs, dtype=np.float64)
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_chebyshev_series_ps(_vp(self.h), _vp(x.h), _f64p(v), v.size, _d(a), _d(b),
+                                                          ctypes.byref(o)), o)
+
+    def EvalPolyLinear(self, x, coeffs):
+        v = np.ascontiguousarray(coeffs, dtype=np.float64)
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_poly_linear(_vp(self.h), _vp(x.h), _f64p(v), v.size, ctypes.byref(o)), o)
+
+    # ---- raw kernels
+    def ntt_host(self, data, mod_ids, inverse=False):
+        data = np.ascontiguousarray(data, dtype=np.uint64)
+        ids = (ctypes.c_int32 * len(mod_ids))(*mod_ids)
+        _chk(_L.ckks_ntt_host(_vp(self.h), _u64p(data), data.shape[0], ids, 1 if inverse else 0))
+        return data
+
+    def ntt_dev(self, dev_ptr, rows, first_mod=0, inverse=False):
+        _chk(_L.ckks_ntt_dev(_vp(self.h), _vp(dev_ptr), rows, first_mod, 1 if inverse else 0))
+
+    def key_switch_dev(self, src_ptr, limbs, out_ptr, rotation=None):
+        _chk(_L.ckks_key_switch_dev(_vp(self.h), _vp(src_ptr), limbs, 0 if rotation is None else 1,
+                                    0 if rotation is None else rotation, _vp(out_ptr)))
+
+
+_L.ckks_ctx_create.argtypes = [_pp, _i, _i, _i, _i, _i, _i, _u64, _i]
+_L.ckks_ct_import.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), _i, _i, _i, _i, _d, _i, _pp]
+_L.ckks_eval_add_const.argtypes = [_vp, _vp, _d, _pp]
+_L.ckks_eval_sub_const.argtypes = [_vp, _vp, _d, _pp]
+_L.ckks_eval_mult_const.argtypes = [_vp, _vp, _d, _pp]
+_L.ckks_eval_const_sub.argtypes = [_vp, _d, _vp, _pp]
+_L.ckks_eval_chebyshev_series_ps.argtypes = [_vp, _vp, ctypes.POINTER(ctypes.c_double), _i, _d, _d, _pp]
+_L.ckks_make_packed_plaintext.argtypes = [_vp, ctypes.POINTER(ctypes.c_double), _i, _i, _i, _i, _pp]
+_L.ckks_ct_export.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_export_secret.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_export_public_key.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_export_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_import_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_stats_json.argtypes = [_vp, ctypes.c_char_p, ctypes.c_size_t]

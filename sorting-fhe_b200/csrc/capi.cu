@@ -1,0 +1,322 @@
+// capi.cu -- extern "C" boundary (include/ckks_b200.h) over the evaluator.
+#include "../../include/ckks_b200.h"
+#include "evaluator.h"
+#include <cstring>
+#include <sstream>
+#include <stdexcept>
+
+struct ckks_ctx { Context c; };
+struct ckks_ct { Ct* p; };
+
+static thread_local std::string g_err;
+extern "C" const char* ckks_last_error(void) { return g_err.c_str(); }
+
+#define API_BEGIN try {
+#define API_END                                                             \
+    return 0; }                                                             \
+    catch (const std::exception& e) { g_err = e.what(); return 1; }         \
+    catch (...) { g_err = "unknown error"; return 2; }
+
+static void check_cuda(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e));
+}
+static void require_device(bool dry) {
+    if (dry) return;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        throw std::runtime_error("no CUDA device: the CKKS engine has no CPU fallback (use dry_run=1 for metadata only)");
+    }
+}
+static ckks_ct* box(Ct* p) { return new ckks_ct{p}; }
+static Context* C(ckks_ctx_t* x) { if (!x) throw std::runtime_error("null context"); return &x->c; }
+static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_error("null ciphertext handle"); return x->p; }
+
+extern "C" {
+
+int ckks_ctx_create(ckks_ctx_t** out, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits,
+                    int scaling_technique, uint64_t seed, int dry_run) {
+    API_BEGIN
+    require_device(dry_run != 0);
+    ckks_ctx* x = new ckks_ctx();
+    try { context_generate(&x->c, log_n, mult_depth, scaling_bits, first_bits, num_large_digits, scaling_technique, seed, dry_run); }
+    catch (...) { delete x; throw; }
+    if (!dry_run) check_cuda("context tables");
+    *out = x;
+    API_END
+}
+
+int ckks_ctx_destroy(ckks_ctx_t* x) {
+    API_BEGIN
+    if (!x) return 0;
+    Context* c = &x->c;
+    if (!c->dry) {
+        cudaStreamSynchronize(c->stream);
+        cudaFree(c->d_mod); cudaFree(c->d_psi); cudaFree(c->d_psi_sh); cudaFree(c->d_ipsi); cudaFree(c->d_ipsi_sh);
+        cudaFree(c->d_ksi); cudaFree(c->d_rot);
+        for (auto& kv : c->ks) {
+            for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); }
+            cudaFree(kv.second.moddown.d_hatinv); cudaFree(kv.second.moddown.d_hatinv_sh); cudaFree(kv.second.moddown.d_hatmod);
+            cudaFree(kv.second.d_pinv); cudaFree(kv.second.d_pinv_sh);
+        }
+        dev_free(c, c->d_secret); dev_free(c, c->d_pk); dev_free(c, c->relin.d);
+        for (auto& kv : c->rot) dev_free(c, kv.second.d);
+        cudaStreamSynchronize(c->stream);
+        if (c->own_stream) cudaStreamDestroy(c->stream);
+    }
+    delete x;
+    API_END
+}
+
+int ckks_ctx_set_stream(ckks_ctx_t* x, void* s) {
+    API_BEGIN
+    Context* c = C(x);
+    if (c->dry) return 0;
+    cudaStreamSynchronize(c->stream);
+    if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+    c->stream = (cudaStream_t)s;
+    API_END
+}
+int ckks_ctx_sync(ckks_ctx_t* x) {
+    API_BEGIN
+    Context* c = C(x);
+    if (!c->dry) { cudaError_t e = cudaStreamSynchronize(c->stream); if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); check_cuda("sync"); }
+    API_END
+}
+int ckks_ctx_info(ckks_ctx_t* x, int what, int64_t* out) {
+    API_BEGIN
+    Context* c = C(x);
+    switch (what) {
+        case 0: *out = c->n; break;
+        case 1: *out = c->size_q; break;
+        case 2: *out = c->size_p; break;
+        case 3: *out = c->alpha; break;
+        case 4: *out = c->num_part_q; break;
+        case 5: *out = 2 * (int64_t)c->n; break;
+        case 6: *out = c->stats.kernel_launches; break;
+        case 7: *out = (int64_t)((c->relin.d ? 1 : 0) + (int64_t)c->rot.size()) * c->num_part_q * 2 * c->M() * c->n * 8; break;
+        default: throw std::runtime_error("ckks_ctx_info: unknown selector");
+    }
+    API_END
+}
+int ckks_ctx_get_moduli(ckks_ctx_t* x, uint64_t* moduli, uint64_t* roots, int cap) {
+    API_BEGIN
+    Context* c = C(x);
+    if (cap < c->M()) throw std::runtime_error("ckks_ctx_get_moduli: buffer too small");
+    for (int i = 0; i < c->M(); i++) { moduli[i] = c->moduli[i]; if (roots) roots[i] = c->psi[i]; }
+    API_END
+}
+int ckks_ctx_get_scaling_factors(ckks_ctx_t* x, double* sf_real, double* sf_big, int cap) {
+    API_BEGIN
+    Context* c = C(x);
+    if (cap < c->size_q) throw std::runtime_error("ckks_ctx_get_scaling_factors: buffer too small");
+    for (int i = 0; i < c->size_q; i++) sf_real[i] = c->sf_real[i];
+    if (sf_big) for (size_t i = 0; i < c->sf_big.size(); i++) sf_big[i] = c->sf_big[i];
+    API_END
+}
+
+int ckks_keygen(ckks_ctx_t* x) { API_BEGIN keygen(C(x)); API_END }
+int ckks_eval_mult_keygen(ckks_ctx_t* x) { API_BEGIN relin_keygen(C(x)); API_END }
+int ckks_eval_rotate_keygen(ckks_ctx_t* x, const int32_t* idx, int count) { API_BEGIN rot_keygen(C(x), idx, count); API_END }
+
+static void d2h(Context* c, uint64_t* host, const u64* dev, size_t words) {
+    if (c->dry) { memset(host, 0, words * 8); return; }
+    cudaMemcpyAsync(host, dev, words * 8, cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("device->host copy: ") + cudaGetErrorString(e));
+}
+static void h2d(Context* c, u64* dev, const uint64_t* host, size_t words) {
+    if (c->dry) return;
+    cudaMemcpyAsync(dev, host, words * 8, cudaMemcpyHostToDevice, c->stream);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("host->device copy: ") + cudaGetErrorString(e));
+}
+
+int ckks_export_secret(ckks_ctx_t* x, uint64_t* host, size_t cap) {
+    API_BEGIN
+    Context* c = C(x); size_t w = (size_t)c->M() * c->n;
+    if (cap < w) throw std::runtime_error("export_secret: buffer too small");
+    if (!c->d_secret && !c->dry) throw std::runtime_error("export_secret: no secret key");
+    d2h(c, host, c->d_secret, w);
+    API_END
+}
+int ckks_export_public_key(ckks_ctx_t* x, uint64_t* host, size_t cap) {
+    API_BEGIN
+    Context* c = C(x); size_t w = (size_t)2 * c->size_q * c->n;
+    if (cap < w) throw std::runtime_error("export_public_key: buffer too small");
+    if (!c->d_pk && !c->dry) throw std::runtime_error("export_public_key: no public key");
+    d2h(c, host, c->d_pk, w);
+    API_END
+}
+static EvalKey* find_key(Context* c, int is_rot, int32_t index, bool create) {
+    if (!is_rot) return &c->relin;
+    uint32_t k = auto_index(c, index);
+    auto it = c->rot.find(k);
+    if (it == c->rot.end()) { if (!create) return nullptr; return &c->rot[k]; }
+    return &it->second;
+}
+int ckks_export_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, uint64_t* host, size_t cap) {
+    API_BEGIN
+    Context* c = C(x);
+    EvalKey* k = find_key(c, is_rot, index, false);
+    if (!k || (!k->d && !c->dry)) throw std::runtime_error("export_eval_key: key not present");
+    int rows = c->num_part_q * 2 * c->M(); size_t w = (size_t)rows * c->n;
+    if (cap < w) throw std::runtime_error("export_eval_key: buffer too small");
+    u64* tmp = dev_alloc(c, w);
+    launch_copy_rows(c, tmp, k->d, w);
+    launch_from_mont(c, tmp, rows, mods_range(0, c->M()));
+    d2h(c, host, tmp, w);
+    dev_free(c, tmp);
+    API_END
+}
+int ckks_import_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, const uint64_t* host, size_t words_) {
+    API_BEGIN
+    Context* c = C(x);
+    int rows = c->num_part_q * 2 * c->M(); size_t w = (size_t)rows * c->n;
+    if (words_ != w) throw std::runtime_error("import_eval_key: size mismatch");
+    EvalKey* k = find_key(c, is_rot, index, true);
+    k->nparts = c->num_part_q;
+    if (!k->d) k->d = dev_alloc(c, w);
+    h2d(c, k->d, host, w);
+    launch_to_mont(c, k->d, rows, mods_range(0, c->M()));
+    API_END
+}
+
+int ckks_make_packed_plaintext(ckks_ctx_t* x, const double* v, int count, int scale_deg, int level, int slots, ckks_ct_t** out) {
+    API_BEGIN *out = box(encode(C(x), v, count, scale_deg, level, slots)); API_END
+}
+int ckks_encrypt(ckks_ctx_t* x, const ckks_ct_t* pt, ckks_ct_t** out) { API_BEGIN *out = box(encrypt(C(x), G(pt))); API_END }
+int ckks_decrypt(ckks_ctx_t* x, const ckks_ct_t* ct, double* v, int count) { API_BEGIN (void)C(x); decrypt(G(ct), v, count); check_cuda("decrypt"); API_END }
+
+int ckks_ct_free(ckks_ct_t* ct) { API_BEGIN if (ct) { ct_free(ct->p); delete ct; } API_END }
+int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out) { API_BEGIN *out = box(ct_clone(G(ct))); API_END }
+int ckks_ct_set_slots(ckks_ct_t* ct, int slots) {
+    API_BEGIN
+    Ct* p = const_cast<Ct*>(G(ct));
+    if (slots <= 0 || (slots & (slots - 1)) || slots > p->ctx->n / 2) throw std::runtime_error("SetSlots: bad slot count");
+    p->slots = slots;
+    API_END
+}
+int ckks_ct_get(const ckks_ct_t* ct, int what, int64_t* out) {
+    API_BEGIN
+    const Ct* p = G(ct);
+    switch (what) {
+        case 0: *out = p->slots; break; case 1: *out = p->level; break; case 2: *out = p->deg; break;
+        case 3: *out = p->nl; break; case 4: *out = p->parts; break;
+        default: throw std::runtime_error("ckks_ct_get: unknown selector");
+    }
+    API_END
+}
+int ckks_ct_get_scaling_factor(const ckks_ct_t* ct, double* out) { API_BEGIN *out = G(ct)->sf; API_END }
+int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
+    API_BEGIN
+    const Ct* p = G(ct); size_t w = (size_t)p->parts * p->nl * p->ctx->n;
+    if (cap < w) throw std::runtime_error("ct_export: buffer too small");
+    d2h(p->ctx, host, p->d, w);
+    API_END
+}
+int ckks_ct_import(ckks_ctx_t* x, const uint64_t* host, int polys, int limbs, int level, int deg, double sf, int slots, ckks_ct_t** out) {
+    API_BEGIN
+    Context* c = C(x);
+    if (polys < 1 || polys > 3 || limbs < 1 || limbs + level != c->size_q) throw std::runtime_error("ct_import: shape does not match context");
+    Ct* p = ct_new(c, polys, limbs, level, deg, sf, slots);
+    try { h2d(c, p->d, host, (size_t)polys * limbs * c->n); } catch (...) { ct_free(p); throw; }
+    *out = box(p);
+    API_END
+}
+
+int ckks_eval_add(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add(G(a), G(b), 1)); API_END }
+int ckks_eval_sub(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add(G(a), G(b), -1)); API_END }
+int ckks_eval_add_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add_const(G(a), v)); API_END }
+int ckks_eval_sub_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add_const(G(a), -v)); API_END }
+int ckks_eval_const_sub(ckks_ctx_t* x, double v, const ckks_ct_t* a, ckks_ct_t** out) {
+    API_BEGIN (void)C(x);
+    Ct* n = eval_negate(G(a));
+    Ct* r = eval_add_const(n, v);
+    ct_free(n);
+    *out = box(r);
+    API_END
+}
+int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_negate(G(a))); API_END }
+int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
+    API_BEGIN (void)C(x);
+    if (count < 1) throw std::runtime_error("EvalAddMany: empty list");
+    std::vector<Ct*> cur; std::vector<bool> owned;
+    for (int i = 0; i < count; i++) { cur.push_back(const_cast<Ct*>(G(cts[i]))); owned.push_back(false); }
+    while (cur.size() > 1) {   // binary tree, same association as oracle EvalAddMany
+        std::vector<Ct*> nxt; std::vector<bool> no;
+        for (size_t i = 0; i + 1 < cur.size(); i += 2) {
+            nxt.push_back(eval_add(cur[i], cur[i + 1], 1)); no.push_back(true);
+            if (owned[i]) ct_free(cur[i]);
+            if (owned[i + 1]) ct_free(cur[i + 1]);
+        }
+        if (cur.size() % 2) { nxt.push_back(cur.back()); no.push_back(owned.back()); }
+        cur.swap(nxt); owned.swap(no);
+    }
+    *out = box(owned[0] ? cur[0] : ct_clone(cur[0]));
+    API_END
+}
+int ckks_eval_mult(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult(G(a), G(b))); API_END }
+int ckks_eval_mult_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult_const(G(a), v)); API_END }
+int ckks_eval_square(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult(G(a), G(a))); API_END }
+int ckks_eval_rotate(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_rotate(G(a), index)); API_END }
+int ckks_has_rotation_key(ckks_ctx_t* x, int32_t index) {
+    try { Context* c = C(x); return c->rot.count(auto_index(c, index)) ? 1 : 0; } catch (...) { return 0; }
+}
+int ckks_eval_chebyshev_series_ps(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, double a, double b, ckks_ct_t** out) {
+    API_BEGIN (void)C(x);
+    if (count < 2) throw std::runtime_error("EvalChebyshevSeriesPS: need at least 2 coefficients");
+    *out = box(eval_chebyshev_series_ps(G(ct), std::vector<double>(coeffs, coeffs + count), a, b));
+    API_END
+}
+int ckks_eval_poly_linear(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, ckks_ct_t** out) {
+    API_BEGIN (void)C(x); *out = box(eval_poly_linear(G(ct), std::vector<double>(coeffs, coeffs + count))); API_END
+}
+
+int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
+    API_BEGIN
+    Context* c = C(x);
+    std::ostringstream os;
+    os << "{\"kernel_launches\": " << c->stats.kernel_launches << ", \"ops\": [";
+    bool first = true;
+    for (auto& kv : c->stats.ops) { os << (first ? "" : ", ") << "[\"" << kv.first.first << "\", " << kv.first.second << ", " << kv.second << "]"; first = false; }
+    os << "]}";
+    std::string s = os.str();
+    if (s.size() + 1 > cap) throw std::runtime_error("stats_json: buffer too small");
+    memcpy(buf, s.c_str(), s.size() + 1);
+    API_END
+}
+int ckks_stats_reset(ckks_ctx_t* x) { API_BEGIN C(x)->stats = Stats(); API_END }
+
+int ckks_ntt_host(ckks_ctx_t* x, uint64_t* data, int rows, const int32_t* mod_ids, int inverse) {
+    API_BEGIN
+    Context* c = C(x);
+    if (rows < 1 || rows > MAX_LIMBS) throw std::runtime_error("ntt_host: bad row count");
+    LimbMods m; m.n = rows;
+    for (int i = 0; i < rows; i++) { if (mod_ids[i] < 0 || mod_ids[i] >= c->M()) throw std::runtime_error("ntt_host: bad modulus id"); m.m[i] = (short)mod_ids[i]; }
+    size_t w = (size_t)rows * c->n;
+    u64* d = dev_alloc(c, w);
+    h2d(c, d, data, w);
+    launch_ntt(c, d, rows, m, inverse != 0);
+    d2h(c, data, d, w);
+    dev_free(c, d);
+    if (!c->dry) check_cuda("ntt");
+    API_END
+}
+int ckks_ntt_dev(ckks_ctx_t* x, void* dev, int rows, int first_mod, int inverse) {
+    API_BEGIN
+    Context* c = C(x);
+    if (rows < 1 || first_mod < 0 || first_mod + rows > c->M()) throw std::runtime_error("ntt_dev: bad limb range");
+    launch_ntt(c, (u64*)dev, rows, mods_range(first_mod, first_mod + rows), inverse != 0);
+    API_END
+}
+int ckks_key_switch_dev(ckks_ctx_t* x, const void* src, int limbs, int is_rot, int32_t index, void* out) {
+    API_BEGIN
+    Context* c = C(x);
+    EvalKey* k = find_key(c, is_rot, index, false);
+    if (!k) throw std::runtime_error("key_switch_dev: key not present");
+    key_switch(c, (const u64*)src, limbs, *k, (u64*)out, nullptr, nullptr);
+    API_END
+}
+}  // extern "C"

@@ -1,0 +1,135 @@
+// encode.cu -- CKKS canonical-embedding encode / decode on the GPU (kernel K9).
+//
+// Replaces OpenFHE MakeCKKSPackedPlaintext -> CKKSPackedEncoding::Encode (DiscreteFourierTransform::
+// FFTSpecialInv, scale, round, RNS expand, NTT) and Decode; the reference executes 258 encodes per
+// DirectSort N=128 (src/sort_algo.h:341,356,573,706,715).  Floating-point operation order is the
+// oracle's (oracle/ckks_prims.c orc_fft_special{,_inv}); every product/sum uses the explicit
+// round-to-nearest intrinsics (no FMA contraction) so coefficients are bit-identical to the oracle.
+#include "engine.h"
+
+#define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
+
+__global__ void k_fft_inv_stage(double2* v, int size, int len, const double2* ksi, const uint32_t* rot, int M) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= size / 2) return;
+    int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
+    int i = (t / lenh) * len, j = t % lenh;
+    int idx = (lenq - (int)(rot[j] % (uint32_t)lenq)) * gap;
+    double2 a = v[i + j], b = v[i + j + lenh], w = ksi[idx];
+    double ur = __dadd_rn(a.x, b.x), ui = __dadd_rn(a.y, b.y), vr = __dsub_rn(a.x, b.x), vi = __dsub_rn(a.y, b.y);
+    double p1 = __dmul_rn(vr, w.x), p2 = __dmul_rn(vi, w.y), p3 = __dmul_rn(vr, w.y), p4 = __dmul_rn(vi, w.x);
+    v[i + j] = make_double2(ur, ui);
+    v[i + j + lenh] = make_double2(__dsub_rn(p1, p2), __dadd_rn(p3, p4));
+}
+__global__ void k_fft_fwd_stage(double2* v, int size, int len, const double2* ksi, const uint32_t* rot, int M) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= size / 2) return;
+    int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
+    int i = (t / lenh) * len, j = t % lenh;
+    int idx = (int)(rot[j] % (uint32_t)lenq) * gap;
+    double2 u = v[i + j], b = v[i + j + lenh], w = ksi[idx];
+    double p1 = __dmul_rn(b.x, w.x), p2 = __dmul_rn(b.y, w.y), p3 = __dmul_rn(b.x, w.y), p4 = __dmul_rn(b.y, w.x);
+    double vr = __dsub_rn(p1, p2), vi = __dadd_rn(p3, p4);
+    v[i + j] = make_double2(__dadd_rn(u.x, vr), __dadd_rn(u.y, vi));
+    v[i + j + lenh] = make_double2(__dsub_rn(u.x, vr), __dsub_rn(u.y, vi));
+}
+// out[i] = in[bitrev(i)] * scale
+__global__ void k_bitrev_scale(double2* out, const double2* in, int size, int bits, double scale, int do_scale) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= size) return;
+    int j = bits ? (int)(__brev((u32)i) >> (32 - bits)) : 0;
+    double2 a = in[j];
+    if (do_scale) { a.x = __dmul_rn(a.x, scale); a.y = __dmul_rn(a.y, scale); }
+    out[i] = a;
+}
+// coefficient x of limb row l: slot k = x / gap (x < nh: real part, else imaginary part)
+__global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, int n, int slots, double sf) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= n) return;
+    int l = blockIdx.y, nh = n >> 1, gap = nh / slots;
+    u64 q = mi[l].q, r = 0;
+    int xx = x < nh ? x : x - nh;
+    if (xx % gap == 0) {
+        double2 z = v[xx / gap];
+        double val = rint(__dmul_rn(x < nh ? z.x : z.y, sf));
+        long long iv = (long long)val;
+        if (iv >= 0) r = (u64)iv % q; else { u64 m = ((u64)(-iv)) % q; r = m ? q - m : 0; }
+    }
+    out[(size_t)l * n + x] = r;
+}
+
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl) {
+    int bits = 0; while ((1 << bits) < slots) bits++;
+    c->stats.kernel_launches += bits + 2;
+    if (c->dry) return;
+    double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
+    double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
+    std::vector<double> h(2 * (size_t)slots, 0.0);
+    for (int i = 0; i < nvals; i++) h[2 * i] = h_values[i];
+    cudaMemcpyAsync(a, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+    cudaStreamSynchronize(c->stream);  // h is a stack-lifetime staging buffer
+    const int M = 2 * c->n;
+    for (int len = slots; len >= 2; len >>= 1)
+        k_fft_inv_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(a, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
+    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0 / (double)slots, 1);
+    dim3 grid((c->n + 255) / 256, nl);
+    k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, sf);
+    dev_free(c, a);
+    dev_free(c, b);
+    launch_ntt(c, out, nl, mods_q(nl), false);
+}
+
+// centred CRT of limbs (0,1) (or limb 0 alone) -> double, then gather slots with 1/sf
+__global__ void k_crt_gather(double2* v, const u64* m, int nlimbs, const ModInfo* mi, int n, int slots, double sf, u64 q0inv_q1) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= slots) return;
+    int nh = n >> 1, gap = nh / slots;
+    double o[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        int x = k * gap + h * nh;
+        u64 a0 = m[x], q0 = mi[0].q;
+        double d;
+        if (nlimbs >= 2) {
+            const ModInfo m1 = mi[1];
+            u64 q1 = m1.q, a1 = m[(size_t)n + x];
+            u64 dd = sub_mod(a1 % q1, a0 % q1, q1);
+            u64 kk = barrett_mul(dd, q0inv_q1, m1);
+            unsigned __int128 val = (unsigned __int128)a0 + (unsigned __int128)q0 * kk;
+            unsigned __int128 Q = (unsigned __int128)q0 * q1, half = Q >> 1;
+            if (val > half) { unsigned __int128 neg = Q - val;
+                d = -__dadd_rn(__dmul_rn(__ull2double_rn((u64)(neg >> 64)), 18446744073709551616.0), __ull2double_rn((u64)neg)); }
+            else d = __dadd_rn(__dmul_rn(__ull2double_rn((u64)(val >> 64)), 18446744073709551616.0), __ull2double_rn((u64)val));
+        } else {
+            d = a0 > (q0 >> 1) ? -__ull2double_rn(q0 - a0) : __ull2double_rn(a0);
+        }
+        o[h] = __ddiv_rn(d, sf);
+    }
+    v[k] = make_double2(o[0], o[1]);
+}
+
+void launch_decode(Context* c, double* h_out, const u64* m, int nlimbs, double sf, int slots) {
+    int bits = 0; while ((1 << bits) < slots) bits++;
+    c->stats.kernel_launches += bits + 2;
+    if (c->dry) { for (int i = 0; i < slots; i++) h_out[i] = 0.0; return; }
+    double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
+    double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
+    u64 q0inv = 0;
+    if (nlimbs >= 2) {
+        u64 q0 = c->moduli[0], q1 = c->moduli[1];
+        unsigned __int128 r = 1, bb = q0 % q1; u64 e = q1 - 2;
+        while (e) { if (e & 1) r = r * bb % q1; bb = bb * bb % q1; e >>= 1; }
+        q0inv = (u64)r;
+    }
+    k_crt_gather<<<(slots + 255) / 256, 256, 0, c->stream>>>(a, m, nlimbs, c->d_mod, c->n, slots, sf, q0inv);
+    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0, 0);
+    const int M = 2 * c->n;
+    for (int len = 2; len <= slots; len <<= 1)
+        k_fft_fwd_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(b, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
+    std::vector<double> h(2 * (size_t)slots);
+    cudaMemcpyAsync(h.data(), b, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+    cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < slots; i++) h_out[i] = h[2 * i];
+    dev_free(c, a);
+    dev_free(c, b);
+}

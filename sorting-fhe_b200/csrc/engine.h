@@ -1,0 +1,119 @@
+// engine.h -- internal types of the B200 CKKS engine (behind include/ckks_b200.h).
+//
+// Data layout in HBM: every polynomial bundle is limb-major uint64 [part][limb][n]; ciphertexts
+// and keys stay in EVALUATION (bit-reversed negacyclic NTT) format, like OpenFHE's DCRTPoly.
+// Modulus index space: 0..sizeQ-1 = Q chain, sizeQ..sizeQ+sizeP-1 = special primes P.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <map>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "modarith.cuh"
+
+#define MAX_LIMBS 96
+
+struct LimbMods {          // passed by value to kernels: row r of a bundle uses modulus m[r % n]
+    int n;
+    short m[MAX_LIMBS];
+};
+
+struct ConvTables {        // ApproxSwitchCRTBasis tables for one (source basis -> target basis)
+    int nin, nout;
+    short in_ids[MAX_LIMBS], out_ids[MAX_LIMBS];
+    u64* d_hatinv;         // [nin]   (Qhat_i^-1 mod q_i)
+    u64* d_hatinv_sh;      // [nin]   Shoup companions
+    u64* d_hatmod;         // [nin][nout]  (Qhat_i mod t_j) * 2^64 mod t_j  (Montgomery form)
+};
+
+struct KsTables {          // per number-of-Q-limbs tables of the hybrid key switch
+    int nl, nparts;
+    std::vector<ConvTables> modup;   // one per digit
+    std::vector<int> dig_lo, dig_hi; // digit limb ranges [lo, hi)
+    ConvTables moddown;              // P -> Q_l
+    u64* d_pinv;                     // [nl] P^-1 mod q_i
+    u64* d_pinv_sh;
+};
+
+struct EvalKey {           // hybrid evk: [part][2 (b, a)][sizeQ+sizeP][n], Montgomery form
+    u64* d = nullptr;
+    int nparts = 0;
+};
+
+struct Stats { std::map<std::pair<std::string, int>, long> ops; long kernel_launches = 0; };
+
+struct Context {
+    // parameters
+    int log_n = 0, n = 0, mult_depth = 0, scaling_bits = 0, first_bits = 0, ext = 1;
+    int size_q = 0, size_p = 0, alpha = 0, num_part_q = 0;
+    uint64_t seed = 1;
+    bool dry = false;      // metadata-only mode: no device allocations, no kernel launches
+    std::vector<u64> moduli, psi;           // Q then P
+    std::vector<double> sf_real, sf_big;
+    // device tables
+    ModInfo* d_mod = nullptr;               // [M]
+    std::vector<ModInfo> h_mod;
+    u64 *d_psi = nullptr, *d_psi_sh = nullptr, *d_ipsi = nullptr, *d_ipsi_sh = nullptr;  // [M][n]
+    double* d_ksi = nullptr;                // [2n+1] complex roots for the special FFT
+    uint32_t* d_rot = nullptr;              // [n/2] 5^j mod 2n
+    std::map<int, KsTables> ks;             // keyed by nl
+    // keys (device)
+    u64* d_secret = nullptr;                // [M][n] EVALUATION
+    u64* d_pk = nullptr;                    // [2][sizeQ][n]  (b, a)
+    EvalKey relin;
+    std::map<uint32_t, EvalKey> rot;        // automorphism index -> key
+    uint64_t enc_counter = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    Stats stats;
+    std::string last_error;
+    int M() const { return size_q + size_p; }
+};
+
+struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
+    Context* ctx;
+    u64* d;
+    int parts, nl;
+    int level, deg;
+    double sf;
+    int slots;
+};
+
+// ---- device memory helpers (stream-ordered pool) ----
+u64* dev_alloc(Context* c, size_t words);
+void dev_free(Context* c, void* p);
+
+// ---- kernel launchers (ntt.cu / kernels.cu / keyswitch.cu / encode.cu) ----
+LimbMods mods_q(int nl);                          // Q limbs 0..nl-1
+LimbMods mods_qp(const Context* c, int nl);       // Q limbs 0..nl-1 then all P limbs
+LimbMods mods_range(int lo, int hi);              // moduli lo..hi-1
+void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse);
+
+void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op /*0 add 1 sub*/);
+void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m);
+void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m);
+void launch_mul_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/);
+void launch_add_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* h_scalars);
+void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
+void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
+void launch_base_conv(Context* c, u64* out, const u64* in, const ConvTables& t);
+void launch_ks_inner2(Context* c, u64* acc /*[2][nl+K][n]*/, const u64* src, const u64* conv, const EvalKey& k,
+                      const KsTables& t);
+void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* addend, int nl,
+                          int acc_stride_limbs, const KsTables& t);
+void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod);
+void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in);
+void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words);
+void launch_to_mont(Context* c, u64* data, int rows, const LimbMods& m);
+void launch_from_mont(Context* c, u64* data, int rows, const LimbMods& m);
+void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream, int kind);
+void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream);
+void launch_evk_combine(Context* c, u64* b, const u64* a, const u64* e, const u64* s_new, const u64* s_old,
+                        int lo, int hi);
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl);
+void launch_decode(Context* c, double* h_out, const u64* m /*[<=2][n] coeff*/, int nlimbs, double sf, int slots);
+void launch_decrypt_combine(Context* c, u64* out, const Ct* ct, int use);
+void launch_encrypt_combine(Context* c, u64* out, const u64* pt, const u64* v, const u64* e0, const u64* e1, int nl);
+
+const KsTables& get_ks_tables(Context* c, int nl);

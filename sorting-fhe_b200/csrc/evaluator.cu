@@ -1,0 +1,367 @@
+// evaluator.cu -- host-side schedule of the CKKS evaluator over the CUDA kernels.
+//
+// This is the layer that sits where OpenFHE's LeveledSHECKKSRNS / KeySwitchHYBRID / PKERNS sit
+// under the reference's `cc->` calls: FLEXIBLEAUTO(EXT)
+// level/scale bookkeeping (AdjustLevelsAndDepthInPlace), lazy rescale, hybrid key switching for
+// relinearisation and rotations, key generation, encode/encrypt/decrypt.  All polynomial
+// arithmetic is launched on the GPU; the host only moves metadata.  With Context::dry set the
+// same code runs metadata-only (no allocations or launches) so that level budgets and op traces
+// can be checked on a machine without a GPU.  Bit-level behaviour is pinned by oracle/ckks_ops.py.
+#include "engine.h"
+#include "evaluator.h"
+#include <cmath>
+#include <stdexcept>
+#include <algorithm>
+
+typedef __int128 i128;
+
+static inline size_t words(const Context* c, int rows) { return (size_t)rows * c->n; }
+static void count(Context* c, const char* name, int nl) { c->stats.ops[{name, nl}]++; }
+
+Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots) {
+    Ct* t = new Ct{c, nullptr, parts, nl, level, deg, sf, slots};
+    t->d = dev_alloc(c, words(c, parts * nl));
+    return t;
+}
+Ct* ct_clone(const Ct* a) {
+    Ct* t = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl));
+    return t;
+}
+void ct_free(Ct* a) { if (!a) return; dev_free(a->ctx, a->d); delete a; }
+static void ct_swap_buffer(Ct* a, u64* nd, int nl) { dev_free(a->ctx, a->d); a->d = nd; a->nl = nl; }
+
+static void int_residues(const Context* c, i128 v, int nl, u64* out) {
+    for (int i = 0; i < nl; i++) { i128 q = (i128)c->moduli[i]; i128 r = v % q; if (r < 0) r += q; out[i] = (u64)r; }
+}
+
+// EvalMultCoreInPlace(ct, double)
+void mult_core_const(Ct* a, double x) {
+    Context* c = a->ctx;
+    double sf = c->sf_real[a->level];
+    i128 v = (i128)(x * sf + 0.5);
+    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    launch_mul_scalar(c, a->d, a->parts * a->nl, mods_q(a->nl), s);
+    a->deg += 1; a->sf *= sf;
+}
+
+// ModReduceInternalInPlace -> DropLastElementAndScale
+void rescale(Ct* a) {
+    Context* c = a->ctx; int nl = a->nl, parts = a->parts;
+    if (nl < 2) throw std::runtime_error("rescale: no limb left to drop (multiplicative depth exhausted)");
+    count(c, "rescale", nl);
+    u64* last = dev_alloc(c, words(c, parts));
+    for (int p = 0; p < parts; p++) launch_copy_rows(c, c->dry ? nullptr : last + words(c, p), c->dry ? nullptr : a->d + words(c, p * nl + nl - 1), c->n);
+    launch_ntt(c, last, parts, mods_range(nl - 1, nl), true);
+    u64* t = dev_alloc(c, words(c, parts * (nl - 1)));
+    launch_rescale_prep(c, t, last, parts, nl - 1, nl - 1);
+    launch_ntt(c, t, parts * (nl - 1), mods_q(nl - 1), false);
+    u64* out = dev_alloc(c, words(c, parts * (nl - 1)));
+    launch_rescale_final(c, out, a->d, t, parts, nl);
+    dev_free(c, last); dev_free(c, t);
+    double ql = (double)c->moduli[nl - 1];
+    ct_swap_buffer(a, out, nl - 1);
+    a->level += 1; a->deg -= 1; a->sf /= ql;
+}
+
+// LevelReduceInternalInPlace
+void level_reduce(Ct* a, int levels) {
+    if (levels <= 0) return;
+    Context* c = a->ctx; int nl2 = a->nl - levels;
+    if (nl2 < 1) throw std::runtime_error("level_reduce: not enough limbs");
+    u64* out = dev_alloc(c, words(c, a->parts * nl2));
+    for (int p = 0; p < a->parts; p++)
+        launch_copy_rows(c, c->dry ? nullptr : out + words(c, p * nl2), c->dry ? nullptr : a->d + words(c, p * a->nl), words(c, nl2));
+    ct_swap_buffer(a, out, nl2);
+    a->level += levels;
+}
+
+// LeveledSHECKKSRNS::AdjustLevelsAndDepthInPlace
+void adjust_levels_and_depth(Ct* a, Ct* b) {
+    Context* c = a->ctx;
+    if (a->level == b->level) {
+        if (a->deg < b->deg) mult_core_const(a, 1.0);
+        else if (b->deg < a->deg) mult_core_const(b, 1.0);
+        return;
+    }
+    if (a->level > b->level) std::swap(a, b);
+    const int l1 = a->level, l2 = b->level;
+    const double scf = c->sf_real[l1];
+    if (a->deg == 2) {
+        if (b->deg == 2) {
+            double q1 = (double)c->moduli[a->nl - 1];
+            mult_core_const(a, b->sf / a->sf * q1 / scf);
+            rescale(a);
+            if (l1 + 1 < l2) level_reduce(a, l2 - l1 - 1);
+            a->sf = b->sf;
+        } else if (l1 + 1 == l2) {
+            rescale(a);
+        } else {
+            double q1 = (double)c->moduli[a->nl - 1];
+            mult_core_const(a, c->sf_big[l2 - 1] / a->sf * q1 / scf);
+            rescale(a);
+            if (l1 + 2 < l2) level_reduce(a, l2 - l1 - 2);
+            rescale(a);
+            a->sf = b->sf;
+        }
+    } else {
+        if (b->deg == 2) {
+            mult_core_const(a, b->sf / a->sf / scf);
+            level_reduce(a, l2 - l1);
+            a->sf = b->sf;
+        } else {
+            mult_core_const(a, c->sf_big[l2 - 1] / a->sf / scf);
+            if (l1 + 1 < l2) level_reduce(a, l2 - l1 - 1);
+            rescale(a);
+            a->sf = b->sf;
+        }
+    }
+}
+void adjust_to_one(Ct* a, Ct* b) {
+    adjust_levels_and_depth(a, b);
+    if (a->deg == 2) { rescale(a); if (b != a) rescale(b); }
+}
+
+// KeySwitchHYBRID::KeySwitchCore (+ optional addends): out[h] = add_h + ModDown(sum_j d_j * evk_j[h])
+void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1) {
+    count(c, "keyswitch", nl);
+    if (!c->dry && !key.d) throw std::runtime_error("key switch: evaluation key not generated");
+    const KsTables& t = get_ks_tables(c, nl);
+    const int K = c->size_p, next = nl + K;
+    u64* coef = dev_alloc(c, words(c, nl));
+    launch_copy_rows(c, coef, src, words(c, nl));
+    launch_ntt(c, coef, nl, mods_q(nl), true);
+    u64* conv = dev_alloc(c, words(c, t.nparts * next));
+    for (int j = 0; j < t.nparts; j++) {
+        u64* cj = c->dry ? nullptr : conv + words(c, j * next);
+        launch_base_conv(c, cj, c->dry ? nullptr : coef + words(c, t.dig_lo[j]), t.modup[j]);
+        LimbMods m; m.n = t.modup[j].nout;
+        for (int i = 0; i < m.n; i++) m.m[i] = t.modup[j].out_ids[i];
+        launch_ntt(c, cj, m.n, m, false);
+    }
+    u64* acc = dev_alloc(c, words(c, 2 * next));
+    launch_ks_inner2(c, acc, src, conv, key, t);
+    dev_free(c, coef); dev_free(c, conv);
+    u64* conv2 = dev_alloc(c, words(c, nl));
+    for (int h = 0; h < 2; h++) {
+        u64* acch = c->dry ? nullptr : acc + words(c, h * next);
+        u64* pp = c->dry ? nullptr : acch + words(c, nl);
+        launch_ntt(c, pp, K, mods_range(c->size_q, c->size_q + K), true);
+        launch_base_conv(c, conv2, pp, t.moddown);
+        launch_ntt(c, conv2, nl, mods_q(nl), false);
+        launch_moddown_final(c, c->dry ? nullptr : out + words(c, h * nl), acch, conv2, h == 0 ? add0 : add1, nl, next, t);
+    }
+    dev_free(c, conv2); dev_free(c, acc);
+}
+
+// ------------------------------------------------------------------ public evaluator ops
+static void add_const_inplace(Ct* a, double x) {
+    Context* c = a->ctx;
+    i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
+    if (x < 0) v = -v;
+    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    launch_add_scalar(c, a->d, a->nl, mods_q(a->nl), s);   // c0 only: rows 0..nl-1
+}
+Ct* eval_add_const(const Ct* a, double x) { Ct* r = ct_clone(a); add_const_inplace(r, x); return r; }
+
+Ct* eval_negate(const Ct* a) {
+    Ct* r = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_neg(a->ctx, r->d, a->d, a->parts * a->nl, mods_q(a->nl));
+    return r;
+}
+
+// EvalAdd / EvalSub over (ct,ct) (ct,pt) (pt,ct): sign=+1 add, -1 sub (a - b)
+Ct* eval_add(const Ct* a, const Ct* b, int sign) {
+    Context* c = a->ctx;
+    Ct *x = ct_clone(a), *y = ct_clone(b);
+    adjust_levels_and_depth(x, y);
+    Ct *ct = x, *pt = y; bool swapped = false;
+    if (x->parts < y->parts) { ct = y; pt = x; swapped = true; }
+    const int nl = ct->nl;
+    count(c, "add", nl);
+    if (swapped && sign < 0) {   // pt - ct
+        launch_neg(c, ct->d, ct->d, ct->parts * nl, mods_q(nl));
+        launch_add(c, ct->d, ct->d, pt->d, nl, mods_q(nl), 0);
+    } else {
+        launch_add(c, ct->d, ct->d, pt->d, pt->parts * nl, mods_q(nl), sign > 0 ? 0 : 1);
+    }
+    ct->slots = std::max(a->slots, b->slots);
+    ct_free(pt);
+    return ct;
+}
+
+Ct* eval_mult_const(const Ct* a, double x) {
+    Ct* r = ct_clone(a);
+    if (r->deg == 2) rescale(r);
+    mult_core_const(r, x);
+    return r;
+}
+
+// EvalMult(ct,ct) with relinearisation / EvalMult(ct,pt)
+Ct* eval_mult(const Ct* a, const Ct* b) {
+    Context* c = a->ctx;
+    Ct* x = ct_clone(a);
+    Ct* y = ct_clone(b);
+    adjust_to_one(x, y);
+    const int nl = x->nl;
+    Ct* r;
+    if (x->parts == 2 && y->parts == 2) {
+        count(c, "mult", nl);
+        u64* d3 = dev_alloc(c, words(c, 3 * nl));
+        launch_tensor(c, d3, x->d, y->d, nl);
+        r = ct_new(c, 2, nl, x->level, x->deg + y->deg, x->sf * y->sf, std::max(a->slots, b->slots));
+        key_switch(c, c->dry ? nullptr : d3 + words(c, 2 * nl), nl, c->relin, r->d, d3, c->dry ? nullptr : d3 + words(c, nl));
+        dev_free(c, d3);
+    } else {
+        Ct *ct = x->parts == 2 ? x : y, *pt = x->parts == 2 ? y : x;
+        if (ct->parts != 2 || pt->parts != 1) throw std::runtime_error("eval_mult: unsupported operand shapes");
+        count(c, "mult_pt", nl);
+        r = ct_new(c, 2, nl, x->level, x->deg + y->deg, x->sf * y->sf, ct->slots);
+        launch_mul(c, r->d, ct->d, pt->d, 2 * nl, nl, mods_q(nl));
+    }
+    ct_free(x); ct_free(y);
+    return r;
+}
+
+uint32_t auto_index(const Context* c, int r) {
+    const u64 m = 2ull * c->n;
+    if (r == 0) return 1;
+    u64 g = 5;
+    if (r < 0) {  // 5^-1 mod m by exponentiation in (Z/m)^*: order divides m/2
+        u64 e = m / 2 - 1, b = 5, acc = 1;   // 5^(ord-1); ord of 5 is m/4, and m/2-1 = 2*(m/4)-1 == -1 mod ord
+        while (e) { if (e & 1) acc = acc * b % m; b = b * b % m; e >>= 1; }
+        g = acc;
+    }
+    u64 res = 1, base = g; unsigned e = (unsigned)std::abs(r);
+    while (e) { if (e & 1) res = res * base % m; base = base * base % m; e >>= 1; }
+    return (uint32_t)res;
+}
+
+// EvalRotate -> EvalAutomorphism: key switch c1, then permute both polynomials
+Ct* eval_rotate(const Ct* a, int r) {
+    Context* c = a->ctx;
+    if (a->parts != 2) throw std::runtime_error("EvalRotate: ciphertext must have 2 components");
+    uint32_t k = auto_index(c, r);
+    auto it = c->rot.find(k);
+    if (it == c->rot.end()) throw std::runtime_error("EvalRotate: no rotation key for index " + std::to_string(r));
+    count(c, "rotate", a->nl);
+    const int nl = a->nl;
+    u64* tmp = dev_alloc(c, words(c, 2 * nl));
+    key_switch(c, c->dry ? nullptr : a->d + words(c, nl), nl, it->second, tmp, a->d, nullptr);
+    Ct* out = ct_new(c, 2, nl, a->level, a->deg, a->sf, a->slots);
+    launch_automorph(c, out->d, tmp, 2 * nl, k);
+    dev_free(c, tmp);
+    return out;
+}
+
+// ------------------------------------------------------------------ keys / encrypt / decrypt
+enum { STREAM_SECRET = 1, STREAM_PK_A = 2, STREAM_PK_E = 3 };
+static uint64_t stream_evk(uint64_t tag, int part, int which) { return (1ull << 32) + tag * 64 + part * 2 + which; }
+static uint64_t stream_enc(uint64_t cnt, int which) { return (2ull << 32) + 3 * cnt + which; }
+
+static void sample_small_ntt(Context* c, u64* out, const LimbMods& m, uint64_t stream, int kind) {
+    launch_sample_small(c, out, m.n, m, stream, kind);
+    launch_ntt(c, out, m.n, m, false);
+}
+
+void keygen(Context* c) {
+    const int M = c->M(), sq = c->size_q;
+    if (!c->d_secret) c->d_secret = dev_alloc(c, words(c, M));
+    sample_small_ntt(c, c->d_secret, mods_range(0, M), STREAM_SECRET, 0);
+    if (!c->d_pk) c->d_pk = dev_alloc(c, words(c, 2 * sq));
+    u64* a = c->dry ? nullptr : c->d_pk + words(c, sq);
+    launch_sample_uniform(c, a, sq, mods_q(sq), STREAM_PK_A);
+    u64* e = dev_alloc(c, words(c, sq));
+    sample_small_ntt(c, e, mods_q(sq), STREAM_PK_E, 1);
+    launch_mul(c, c->d_pk, a, c->d_secret, sq, sq, mods_q(sq));      // a*s
+    launch_add(c, c->d_pk, e, c->d_pk, sq, mods_q(sq), 1);           // e - a*s
+    dev_free(c, e);
+}
+
+static void switch_key_gen(Context* c, EvalKey& key, const u64* s_old, const u64* s_new, uint64_t tag) {
+    const int M = c->M();
+    key.nparts = c->num_part_q;
+    if (!key.d) key.d = dev_alloc(c, words(c, key.nparts * 2 * M));
+    u64* e = dev_alloc(c, words(c, M));
+    for (int part = 0; part < key.nparts; part++) {
+        u64* b = c->dry ? nullptr : key.d + words(c, (part * 2 + 0) * M);
+        u64* a = c->dry ? nullptr : key.d + words(c, (part * 2 + 1) * M);
+        launch_sample_uniform(c, a, M, mods_range(0, M), stream_evk(tag, part, 0));
+        sample_small_ntt(c, e, mods_range(0, M), stream_evk(tag, part, 1), 1);
+        int lo = c->alpha * part, hi = std::min(c->alpha * (part + 1), c->size_q);
+        launch_evk_combine(c, b, a, e, s_new, s_old, lo, hi);
+        launch_to_mont(c, b, 2 * M, mods_range(0, M));   // b and a rows are adjacent
+    }
+    dev_free(c, e);
+}
+
+void relin_keygen(Context* c) {
+    if (!c->d_secret && !c->dry) throw std::runtime_error("EvalMultKeyGen: no secret key");
+    const int M = c->M();
+    u64* s2 = dev_alloc(c, words(c, M));
+    launch_mul(c, s2, c->d_secret, c->d_secret, M, M, mods_range(0, M));
+    switch_key_gen(c, c->relin, s2, c->d_secret, 0);
+    dev_free(c, s2);
+}
+
+void rot_keygen(Context* c, const int* indices, int count_) {
+    if (!c->d_secret && !c->dry) throw std::runtime_error("EvalRotateKeyGen: no secret key");
+    const int M = c->M(); const u64 m = 2ull * c->n;
+    u64* sp = dev_alloc(c, words(c, M));
+    for (int t = 0; t < count_; t++) {
+        uint32_t k = auto_index(c, indices[t]);
+        if (c->rot.count(k)) continue;
+        uint32_t kinv = auto_index(c, -indices[t]);
+        if ((u64)k * kinv % m != 1) throw std::runtime_error("internal: automorphism inverse");
+        launch_automorph(c, sp, c->d_secret, M, kinv);
+        EvalKey key;
+        switch_key_gen(c, key, c->d_secret, sp, k);
+        c->rot[k] = key;
+    }
+    dev_free(c, sp);
+}
+
+Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots) {
+    if (slots <= 0) { slots = 1; while (slots < nvals) slots <<= 1; }
+    if (nvals > slots || slots > c->n / 2 || (slots & (slots - 1))) throw std::runtime_error("MakeCKKSPackedPlaintext: bad slot count");
+    if (level < 0 || level >= c->size_q) throw std::runtime_error("MakeCKKSPackedPlaintext: bad level");
+    double sf; int deg;
+    if (c->ext && level == 0) { sf = c->sf_big[0]; deg = 2; }
+    else { sf = std::pow(c->sf_real[level], (double)scale_deg); deg = scale_deg; }
+    const int nl = c->size_q - level;
+    Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots);
+    count(c, "encode", nl);
+    launch_encode(c, pt->d, values, nvals, slots, sf, nl);
+    return pt;
+}
+
+Ct* encrypt(Context* c, const Ct* pt) {
+    if (pt->parts != 1) throw std::runtime_error("Encrypt: operand is not a plaintext");
+    if (!c->d_pk && !c->dry) throw std::runtime_error("Encrypt: no public key");
+    const int nl = pt->nl; uint64_t cnt = c->enc_counter++;
+    u64* t = dev_alloc(c, words(c, 3 * nl));
+    u64 *v = t, *e0 = c->dry ? nullptr : t + words(c, nl), *e1 = c->dry ? nullptr : t + words(c, 2 * nl);
+    sample_small_ntt(c, v, mods_q(nl), stream_enc(cnt, 0), 0);
+    sample_small_ntt(c, e0, mods_q(nl), stream_enc(cnt, 1), 1);
+    sample_small_ntt(c, e1, mods_q(nl), stream_enc(cnt, 2), 1);
+    Ct* ct = ct_new(c, 2, nl, pt->level, pt->deg, pt->sf, pt->slots);
+    launch_encrypt_combine(c, ct->d, pt->d, v, e0, e1, nl);
+    dev_free(c, t);
+    return ct;
+}
+
+void decrypt(const Ct* ct, double* out, int out_len) {
+    Context* c = ct->ctx;
+    const int use = std::min(2, ct->nl);
+    u64* m = dev_alloc(c, words(c, use));
+    if (ct->parts == 1) launch_copy_rows(c, m, ct->d, words(c, use));
+    else {
+        if (!c->d_secret && !c->dry) throw std::runtime_error("Decrypt: no secret key");
+        launch_decrypt_combine(c, m, ct, use);
+    }
+    launch_ntt(c, m, use, mods_q(use), true);
+    std::vector<double> tmp(ct->slots);
+    launch_decode(c, tmp.data(), m, use, ct->sf, ct->slots);
+    dev_free(c, m);
+    for (int i = 0; i < out_len; i++) out[i] = i < ct->slots ? tmp[i] : 0.0;
+}

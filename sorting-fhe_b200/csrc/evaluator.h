@@ -1,0 +1,41 @@
+// evaluator.h -- internal C++ interface of the evaluator layer (see evaluator.cu, cheby.cu)
+#pragma once
+#include "engine.h"
+#include <vector>
+
+void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits, int ext,
+                      uint64_t seed, int dry);
+
+Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots);
+Ct* ct_clone(const Ct* a);
+void ct_free(Ct* a);
+
+void mult_core_const(Ct* a, double x);
+void rescale(Ct* a);
+void level_reduce(Ct* a, int levels);
+void adjust_levels_and_depth(Ct* a, Ct* b);
+void adjust_to_one(Ct* a, Ct* b);
+void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1);
+
+Ct* eval_add(const Ct* a, const Ct* b, int sign);
+Ct* eval_add_const(const Ct* a, double x);
+Ct* eval_negate(const Ct* a);
+Ct* eval_mult(const Ct* a, const Ct* b);
+Ct* eval_mult_const(const Ct* a, double x);
+Ct* eval_rotate(const Ct* a, int r);
+uint32_t auto_index(const Context* c, int r);
+
+void keygen(Context* c);
+void relin_keygen(Context* c);
+void rot_keygen(Context* c, const int* indices, int count);
+Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots);
+Ct* encrypt(Context* c, const Ct* pt);
+void decrypt(const Ct* ct, double* out, int out_len);
+
+// cheby.cu
+Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& weights);
+Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coeffs, double a, double b);
+Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs);
+void long_division_chebyshev(const std::vector<double>& f, const std::vector<double>& g, std::vector<double>& q,
+                             std::vector<double>& r);
+void compute_degrees_ps(int n, int& k, int& m);

@@ -1,0 +1,228 @@
+// kernels.cu -- limb-wise pointwise kernels (K5-K8 of SURVEY.md 2.2), rescale, sampling.
+//
+// All are HBM-streaming integer kernels: one thread per coefficient, rows = parts x limbs on
+// grid.y, coalesced 8-byte accesses, per-limb modulus looked up from a by-value LimbMods.
+// They replace the DCRTPoly operator+ / operator* / AutomorphismTransform /
+// DropLastElementAndScale calls OpenFHE executes under the reference's cc->EvalAdd / EvalMult /
+// EvalRotate / implicit rescale; semantics pinned by
+// oracle/ckks_prims.c (orc_v*, orc_automorph_eval, orc_switch_modulus).
+#include "engine.h"
+
+struct LimbScalars { u64 v[MAX_LIMBS]; u64 sh[MAX_LIMBS]; };
+
+static inline dim3 grid_for(const Context* c, int rows) { return dim3((c->n + 255) / 256, rows); }
+#define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
+
+LimbMods mods_q(int nl) { LimbMods m; m.n = nl; for (int i = 0; i < nl; i++) m.m[i] = (short)i; return m; }
+LimbMods mods_qp(const Context* c, int nl) {
+    LimbMods m; m.n = nl + c->size_p;
+    for (int i = 0; i < nl; i++) m.m[i] = (short)i;
+    for (int k = 0; k < c->size_p; k++) m.m[nl + k] = (short)(c->size_q + k);
+    return m;
+}
+LimbMods mods_range(int lo, int hi) { LimbMods m; m.n = hi - lo; for (int i = lo; i < hi; i++) m.m[i - lo] = (short)i; return m; }
+
+static u64 host_shoup(u64 w, u64 q) { return (u64)((((unsigned __int128)w) << 64) / q); }
+
+__global__ void k_addsub(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int op) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
+    size_t o = (size_t)row * n + x;
+    out[o] = op == 0 ? add_mod(a[o], b[o], q) : sub_mod(a[o], b[o], q);
+}
+void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op) {
+    KL(c); k_addsub<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, op);
+}
+
+__global__ void k_neg(u64* out, const u64* a, LimbMods mods, const ModInfo* mi, int n) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
+    size_t o = (size_t)row * n + x; out[o] = neg_mod(a[o], q);
+}
+void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m) {
+    KL(c); k_neg<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, m, c->d_mod, c->n);
+}
+
+__global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
+    size_t o = (size_t)row * n + x, ob = (size_t)(row % rows_b) * n + x;
+    out[o] = barrett_mul(a[o], b[ob], m);
+}
+void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m) {
+    KL(c); k_mul<<<grid_for(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
+}
+
+__global__ void k_mul_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
+    size_t o = (size_t)row * n + x; d[o] = shoup_mul(d[o], s.v[l], s.sh[l], q);
+}
+void launch_mul_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
+    KL(c);
+    LimbScalars s;
+    for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
+    k_mul_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
+}
+
+__global__ void k_add_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
+    size_t o = (size_t)row * n + x; d[o] = add_mod(d[o], s.v[l], q);
+}
+void launch_add_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
+    KL(c);
+    LimbScalars s;
+    for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
+    k_add_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
+}
+
+// (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
+__global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi, int n, int nl) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int l = blockIdx.y; const ModInfo m = mi[l];
+    size_t o = (size_t)l * n + x, P = (size_t)nl * n;
+    u64 a0 = a[o], a1 = a[o + P], b0 = b[o], b1 = b[o + P];
+    d3[o] = barrett_mul(a0, b0, m);
+    d3[o + P] = add_mod(barrett_mul(a0, b1, m), barrett_mul(a1, b0, m), m.q);
+    d3[o + 2 * P] = barrett_mul(a1, b1, m);
+}
+void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl) {
+    KL(c); k_tensor<<<grid_for(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
+}
+
+// out[p] = in[brev(idx)], j = brev(p), idx = ((2j+1)k mod 2n) >> 1  (PrecomputeAutoMap)
+__global__ void k_automorph(u64* out, const u64* in, int n, int logn, u32 k) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x; if (p >= n) return;
+    size_t ro = (size_t)blockIdx.y * n;
+    u32 j = __brev((u32)p) >> (32 - logn);
+    u64 jt = 2ull * j + 1;
+    u32 idx = (u32)(((jt * k) & (2ull * n - 1)) >> 1);
+    u32 src = __brev(idx) >> (32 - logn);
+    out[ro + p] = in[ro + src];
+}
+void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k) {
+    KL(c); k_automorph<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, c->log_n, k);
+}
+
+// rescale: t[p][i] = centred switch of last[p] (coefficient format, mod q_last) to q_i
+__global__ void k_rescale_prep(u64* t, const u64* last, const ModInfo* mi, int n, int nl_out, int last_mod) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, p = row / nl_out, i = row % nl_out;
+    u64 ql = mi[last_mod].q, qi = mi[i].q, half = ql >> 1;
+    u64 v = last[(size_t)p * n + x], r;
+    if (v > half) { u64 neg = (ql - v) % qi; r = neg ? qi - neg : 0; } else r = v % qi;
+    t[(size_t)row * n + x] = r;
+}
+void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod) {
+    KL(c); k_rescale_prep<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(t, last, c->d_mod, c->n, nl_out, last_mod);
+}
+// out[p][i] = (in[p][i] - t[p][i]) * q_last^-1 mod q_i ; in has nl_in = nl_out + 1 limbs per part
+__global__ void k_rescale_final(u64* out, const u64* in, const u64* t, const ModInfo* mi, int n, int nl_out, LimbScalars s) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, p = row / nl_out, i = row % nl_out;
+    u64 q = mi[i].q;
+    u64 a = in[((size_t)p * (nl_out + 1) + i) * n + x], b = t[(size_t)row * n + x];
+    out[(size_t)row * n + x] = shoup_mul(sub_mod(a, b, q), s.v[i], s.sh[i], q);
+}
+static u64 host_powmod(u64 a, u64 e, u64 q) {
+    unsigned __int128 r = 1, b = a % q;
+    while (e) { if (e & 1) r = r * b % q; b = b * b % q; e >>= 1; }
+    return (u64)r;
+}
+void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in) {
+    KL(c);
+    LimbScalars s; int nl_out = nl_in - 1; u64 ql = c->moduli[nl_in - 1];
+    for (int i = 0; i < nl_out; i++) { u64 q = c->moduli[i]; s.v[i] = host_powmod(ql % q, q - 2, q); s.sh[i] = host_shoup(s.v[i], q); }
+    k_rescale_final<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(out, in, t, c->d_mod, c->n, nl_out, s);
+}
+
+void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words) {
+    KL(c); cudaMemcpyAsync(dst, src, words * sizeof(u64), cudaMemcpyDeviceToDevice, c->stream);
+}
+
+__global__ void k_mont(u64* d, LimbMods mods, const ModInfo* mi, int n, int to) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
+    size_t o = (size_t)row * n + x;
+    if (to) { u64 v = d[o]; u64 lo = v * m.r2, hi = __umul64hi(v, m.r2); d[o] = mont_reduce(lo, hi, m.q, m.qinv); }
+    else d[o] = mont_reduce(d[o], 0, m.q, m.qinv);
+}
+void launch_to_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); k_mont<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, 1); }
+void launch_from_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); k_mont<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, 0); }
+
+// ---- counter-based sampling (spec shared with oracle/ckks_prims.c orc_hash / orc_sample) ----
+__device__ __forceinline__ u64 mix64(u64 x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ULL; x ^= x >> 27; x *= 0x94d049bb133111ebULL; x ^= x >> 31; return x;
+}
+__device__ __forceinline__ u64 hash3(u64 seed, u64 stream, u64 idx) {
+    return mix64(mix64(seed + 0x9E3779B97F4A7C15ULL * (stream + 1)) ^ mix64(idx + 0xD1B54A32D192ED03ULL));
+}
+__global__ void k_sample_small(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream, int kind) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
+    u64 h = hash3(seed, stream, (u64)x), r;
+    if (kind == 0) { u64 t = h % 3; r = t == 0 ? 0 : (t == 1 ? 1 : q - 1); }
+    else { int e = __popcll(h & 0xFFFFF) - __popcll((h >> 20) & 0xFFFFF); r = e >= 0 ? (u64)e : q - (u64)(-e); }
+    out[(size_t)row * n + x] = r;
+}
+void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream, int kind) {
+    KL(c); k_sample_small<<<grid_for(c, rows), 256, 0, c->stream>>>(out, m, c->d_mod, c->n, c->seed, stream, kind);
+}
+__global__ void k_sample_uniform(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, mid = mods.m[row % mods.n]; u64 q = mi[mid].q;
+    out[(size_t)row * n + x] = hash3(seed, stream, (((u64)mid + 1) << 32) + (u64)x) % q;
+}
+void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream) {
+    KL(c); k_sample_uniform<<<grid_for(c, rows), 256, 0, c->stream>>>(out, m, c->d_mod, c->n, c->seed, stream);
+}
+
+// evk part: b = -a*s_new + e (+ P*s_old on the digit's own limbs [lo,hi)); all [M][n] EVALUATION
+__global__ void k_evk_combine(u64* b, const u64* a, const u64* e, const u64* sn, const u64* so, const ModInfo* mi, int n,
+                              int lo, int hi, LimbScalars pm) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y; const ModInfo m = mi[row];
+    size_t o = (size_t)row * n + x;
+    u64 r = sub_mod(e[o], barrett_mul(a[o], sn[o], m), m.q);
+    if (row >= lo && row < hi) r = add_mod(r, shoup_mul(so[o], pm.v[row], pm.sh[row], m.q), m.q);
+    b[o] = r;
+}
+void launch_evk_combine(Context* c, u64* b, const u64* a, const u64* e, const u64* s_new, const u64* s_old, int lo, int hi) {
+    KL(c);
+    LimbScalars pm;
+    for (int i = 0; i < c->M(); i++) {
+        unsigned __int128 p = 1; u64 q = c->moduli[i];
+        for (int k = 0; k < c->size_p; k++) p = p * (c->moduli[c->size_q + k] % q) % q;
+        pm.v[i] = (u64)p; pm.sh[i] = host_shoup((u64)p, q);
+    }
+    k_evk_combine<<<grid_for(c, c->M()), 256, 0, c->stream>>>(b, a, e, s_new, s_old, c->d_mod, c->n, lo, hi, pm);
+}
+
+// Encrypt: c0 = b*v + e0 + m, c1 = a*v + e1 ; pk = [2][sizeQ][n]
+__global__ void k_encrypt(u64* out, const u64* pt, const u64* pk, const u64* v, const u64* e0, const u64* e1,
+                          const ModInfo* mi, int n, int nl, int size_q) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int l = blockIdx.y; const ModInfo m = mi[l];
+    size_t o = (size_t)l * n + x;
+    u64 vv = v[o];
+    out[o] = add_mod(add_mod(barrett_mul(pk[o], vv, m), e0[o], m.q), pt[o], m.q);
+    out[(size_t)nl * n + o] = add_mod(barrett_mul(pk[(size_t)size_q * n + o], vv, m), e1[o], m.q);
+}
+void launch_encrypt_combine(Context* c, u64* out, const u64* pt, const u64* v, const u64* e0, const u64* e1, int nl) {
+    KL(c); k_encrypt<<<grid_for(c, nl), 256, 0, c->stream>>>(out, pt, c->d_pk, v, e0, e1, c->d_mod, c->n, nl, c->size_q);
+}
+
+// Decrypt core on the first `use` limbs: out = c0 + c1*s (+ c2*s^2)
+__global__ void k_decrypt(u64* out, const u64* d, const u64* s, const ModInfo* mi, int n, int nl, int parts) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int l = blockIdx.y; const ModInfo m = mi[l];
+    size_t o = (size_t)l * n + x, P = (size_t)nl * n;
+    u64 sv = s[o];
+    u64 r = add_mod(d[o], barrett_mul(d[o + P], sv, m), m.q);
+    if (parts == 3) r = add_mod(r, barrett_mul(barrett_mul(d[o + 2 * P], sv, m), sv, m), m.q);
+    out[o] = r;
+}
+void launch_decrypt_combine(Context* c, u64* out, const Ct* ct, int use) {
+    KL(c); k_decrypt<<<grid_for(c, use), 256, 0, c->stream>>>(out, ct->d, c->d_secret, c->d_mod, c->n, ct->nl, ct->parts);
+}

@@ -1,0 +1,126 @@
+"""GPU parity tests proper: every CUDA primitive, called through the C-ABI, bit-exact against the
+CPU oracle on the same seeded inputs (north_star level 1)."""
+import numpy as np
+import pytest
+
+from oracle.ckks_oracle import P, lib
+from tests.common import make_pair, same
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pair12():
+    eng, orc = make_pair(12, 8, rots=(1, -1, 2, 5, 64))
+    yield eng, orc
+    eng.close()
+
+
+@pytest.mark.parametrize("log_n", [8, 10, 11, 12, 13, 14, 16, 17])
+def test_ntt_bit_exact(log_n):
+    eng, orc = None, None
+    sf = __import__("importlib").import_module("sorting-fhe_b200")
+    eng = sf.Engine(log_n, 3, 40)
+    from oracle.ckks_oracle import Context, Params
+    ctx = Context(Params(log_n, 3, 40))
+    M = ctx.size_q + ctx.size_p
+    rng = np.random.default_rng(log_n)
+    ids = list(range(M))
+    data = np.stack([rng.integers(0, ctx.moduli[i], ctx.n, dtype=np.uint64) for i in ids])
+    ref = data.copy()
+    for r, i in enumerate(ids):
+        ctx.ntt(ref[r], i)
+    got = eng.ntt_host(data.copy(), ids, inverse=False)
+    bad = np.argwhere(got != ref)
+    assert bad.size == 0, "forward NTT mismatches at %s" % bad[:5].tolist()
+    back = eng.ntt_host(got.copy(), ids, inverse=True)
+    assert np.array_equal(back, data), "inverse NTT does not round-trip"
+    ref2 = ref.copy()
+    for r, i in enumerate(ids):
+        ctx.intt(ref2[r], i)
+    assert np.array_equal(ref2, data)
+    eng.close()
+
+
+def test_keys_bit_exact(pair12):
+    eng, orc = pair12
+    assert np.array_equal(eng.export_secret(), orc.secret)
+    pk = eng.export_public_key()
+    assert np.array_equal(pk[0], orc.pk[0]) and np.array_equal(pk[1], orc.pk[1])
+    rk = eng.export_eval_key()
+    for j in range(eng.num_part_q):
+        assert np.array_equal(rk[j, 0], orc.relin[1][j]), "relin b digit %d" % j
+        assert np.array_equal(rk[j, 1], orc.relin[0][j]), "relin a digit %d" % j
+    for r in (1, -1, 5):
+        k = eng.export_eval_key(rotation=r)
+        av, bv = orc.rot[orc.auto_index(r)]
+        for j in range(eng.num_part_q):
+            assert np.array_equal(k[j, 0], bv[j]) and np.array_equal(k[j, 1], av[j])
+
+
+def test_encode_encrypt_decrypt(pair12):
+    eng, orc = pair12
+    x = np.linspace(-1, 1, 16)
+    for level, slots in [(0, 16), (0, 2048), (3, 64), (5, 16)]:
+        pe, po = eng.encode(x, 1, level, slots), orc.encode(x, 1, level, slots)
+        same(pe, po)
+        assert np.allclose(eng.decrypt(pe, 16), x, atol=1e-8)
+    orc.ctx.enc_counter = 0
+    ce, co = eng.encrypt(eng.encode(x, slots=16)), orc.encrypt(orc.encode(x, slots=16))
+    same(ce, co)
+    de, do = eng.decrypt(ce, 16), orc.decrypt(co, 16)
+    assert np.array_equal(de, do), "decrypt/decode must be bit-identical to the oracle"
+    assert np.allclose(de, x, atol=1e-7)
+
+
+def test_eval_ops_bit_exact(pair12):
+    eng, orc = pair12
+    x = np.array([0.1, 0.2, -0.3, 0.4, 0.5, -0.6, 0.7, 0.8])
+    orc.ctx.enc_counter = 100
+    # engine counter: encrypt consumed 1 in the previous test at most; import the oracle ct instead
+    co = orc.encrypt(orc.encode(x, slots=8))
+    ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+    same(ce, co)
+    # EvalMult + relinearisation (+ implicit rescale of both fresh operands)
+    me, mo = eng.EvalMult(ce, ce), orc.EvalMult(co, co)
+    same(me, mo)
+    # second multiplication: lazy rescale then tensor + relin
+    m2e, m2o = eng.EvalMult(me, ce), orc.EvalMult(mo, co)
+    same(m2e, m2o)
+    assert np.allclose(eng.decrypt(m2e, 8), x ** 3, atol=1e-6)
+    # rotations (key switch + automorphism), positive / negative / composite index
+    for r in (1, -1, 5, 64):
+        same(eng.EvalRotate(m2e, r), orc.EvalRotate(m2o, r))
+    assert np.allclose(eng.decrypt(eng.EvalRotate(ce, 1), 8), np.roll(x, -1), atol=1e-7)
+    # level/scale alignment paths of EvalAdd/EvalSub
+    same(eng.EvalAdd(m2e, ce), orc.EvalAdd(m2o, co))
+    same(eng.EvalSub(ce, m2e), orc.EvalSub(co, m2o))
+    same(eng.EvalAdd(m2e, 0.5), orc.EvalAdd(m2o, 0.5))
+    same(eng.EvalSub(m2e, 0.25), orc.EvalSub(m2o, 0.25))
+    same(eng.EvalSub(1.0, m2e), orc.EvalSub(1.0, m2o))
+    same(eng.EvalMult(m2e, -0.25), orc.EvalMult(m2o, -0.25))
+    same(eng.EvalNegate(m2e), orc.EvalNegate(m2o))
+    # ct x pt and ct - pt with plaintexts at a different level
+    pe, po = eng.encode(x, 1, 0, 8), orc.encode(x, 1, 0, 8)
+    same(eng.EvalMult(m2e, pe), orc.EvalMult(m2o, po))
+    same(eng.EvalSub(pe, m2e), orc.EvalSub(po, m2o))
+    same(eng.EvalAddMany([ce, me, m2e]), orc.EvalAddMany([co, mo, m2o]))
+
+
+def test_chebyshev_ps_bit_exact(pair12):
+    eng, orc = pair12
+    from oracle.algos import G4_COEFFS
+    x = np.linspace(-0.9, 0.9, 16)
+    co = orc.encrypt(orc.encode(x, slots=16))
+    ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+    re, ro = eng.EvalChebyshevSeriesPS(ce, G4_COEFFS, -1, 1), orc.EvalChebyshevSeriesPS(co, G4_COEFFS, -1, 1)
+    same(re, ro)
+    assert re.level == 5
+
+
+def test_missing_rotation_key_fails(pair12):
+    eng, _ = pair12
+    sf = __import__("importlib").import_module("sorting-fhe_b200")
+    ct = eng.encrypt(eng.encode([1.0, 2.0], slots=2))
+    with pytest.raises(sf.CkksError):
+        eng.EvalRotate(ct, 3)
