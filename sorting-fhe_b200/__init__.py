@@ -299,3 +299,104 @@ _L.ckks_export_public_key.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctyp
 _L.ckks_export_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
 _L.ckks_import_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
 _L.ckks_stats_json.argtypes = [_vp, ctypes.c_char_p, ctypes.c_size_t]
+
+
+# ------------------------------------------------------------------------------------------------
+# sorter layer (libsortfhe_host.so, include/sortfhe_host.h): the reference's sort_algo.h / comparison.h /
+# sign.h / rotation.h API, re-created in host C++ on top of the engine's C-ABI
+HOST_LIB_PATH = os.path.join(_DIR, "libsortfhe_host.so")
+if not os.path.exists(HOST_LIB_PATH):
+    raise ImportError("libsortfhe_host.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+_H = ctypes.CDLL(HOST_LIB_PATH)
+_H.sortfhe_last_error.restype = ctypes.c_char_p
+_i32p = ctypes.POINTER(ctypes.c_int32)
+_ip = ctypes.POINTER(ctypes.c_int)
+_H.sortfhe_direct_sort_params.argtypes = [_i, _i, _ip, _i32p, _i, _ip]
+_H.sortfhe_direct_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _pp]
+_H.sortfhe_construct_rank.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _pp]
+_H.sortfhe_rotation_index_check.argtypes = [_vp, _vp, _vp, _i, _i32p, _i, _pp]
+_H.sortfhe_compare.argtypes = [_vp, _vp, _vp, _i, _i, _i, _pp]
+_H.sortfhe_sign.argtypes = [_vp, _vp, _i, _i, _i, _pp]
+_H.sortfhe_indicator.argtypes = [_vp, _vp, _d, _i, _i, _i, _pp]
+_H.sortfhe_rotate.argtypes = [_vp, _vp, _i, _i, _i32p, _i, _pp]
+_H.sortfhe_decompose.argtypes = [_i, _i, _i, _i, _i32p, _i, _i32p, _i, _ip]
+_H.sortfhe_sinc_coefficients.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_double), _i, _ip]
+
+
+def _hchk(rc):
+    if rc != 0:
+        raise CkksError(_H.sortfhe_last_error().decode())
+
+
+def _idx(indices):
+    return (ctypes.c_int32 * len(indices))(*indices), len(indices)
+
+
+def direct_sort_params(n, ring_dim=1 << 17):
+    """DirectSort<N>::getSizeParameters -> (multDepth, rotation key indices)"""
+    depth, cnt = ctypes.c_int(), ctypes.c_int()
+    buf = (ctypes.c_int32 * 4096)()
+    _hchk(_H.sortfhe_direct_sort_params(n, ring_dim, ctypes.byref(depth), buf, 4096, ctypes.byref(cnt)))
+    return depth.value, list(buf[:cnt.value])
+
+
+class DirectSort:
+    """DirectSort<N> over an Engine (reference src/sort_algo.h:61-774)"""
+
+    def __init__(self, eng, n, rot_indices):
+        self.eng, self.n, self.rots = eng, n, list(rot_indices)
+
+    def _run(self, f, *args):
+        a, c = _idx(self.rots)
+        o = ctypes.c_void_p()
+        _hchk(f(_vp(self.eng.h), *args, a, c, ctypes.byref(o)))
+        return Ciphertext(self.eng, o.value)
+
+    def sort(self, ct, sign_cfg=(3, 3, 2)):
+        return self._run(_H.sortfhe_direct_sort, _vp(ct.h), self.n, *sign_cfg)
+
+    def construct_rank(self, ct, sign_cfg=(3, 3, 2)):
+        return self._run(_H.sortfhe_construct_rank, _vp(ct.h), self.n, *sign_cfg)
+
+    def rotation_index_check(self, rank, ct):
+        return self._run(_H.sortfhe_rotation_index_check, _vp(rank.h), _vp(ct.h), self.n)
+
+
+def compare(eng, a, b, sign_cfg=(4, 3, 3)):
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_compare(_vp(eng.h), _vp(a.h), _vp(b.h), *sign_cfg, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def sign(eng, x, sign_cfg=(3, 0, 1)):
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_sign(_vp(eng.h), _vp(x.h), *sign_cfg, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def indicator(eng, x, c, sign_cfg=(3, 3, 2)):
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_indicator(_vp(eng.h), _vp(x.h), _d(c), *sign_cfg, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def rotate(eng, x, n, rotation, rot_indices):
+    a, c = _idx(rot_indices)
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_rotate(_vp(eng.h), _vp(x.h), n, rotation, a, c, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def decompose(n, rotation, wrap, rot_indices, algo="BINARY"):
+    a, c = _idx(rot_indices)
+    steps, cnt = (ctypes.c_int32 * 256)(), ctypes.c_int()
+    _hchk(_H.sortfhe_decompose(n, rotation, wrap, {"NAF": 0, "BNAF": 1, "BINARY": 2}[algo], a, c, steps, 256,
+                               ctypes.byref(cnt)))
+    return list(steps[:cnt.value])
+
+
+def sinc_coefficients(n, doubled=True):
+    cnt = ctypes.c_int()
+    buf = np.zeros(16384, dtype=np.float64)
+    _hchk(_H.sortfhe_sinc_coefficients(n, 1 if doubled else 0, _f64p(buf), buf.size, ctypes.byref(cnt)))
+    return buf[:cnt.value].copy()

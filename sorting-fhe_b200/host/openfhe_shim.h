@@ -1,0 +1,257 @@
+// openfhe_shim.h -- the lbcrypto value types the reference's sorter headers use, re-created on top of
+// the C-ABI of the B200 engine (include/ckks_b200.h).
+//
+// The reference has no FFI seam: its headers call lbcrypto::CryptoContextImpl<DCRTPoly> members after
+// `#include "openfhe.h"` (reference src/sort_algo.h:3-12, src/comparison.h:3-9, src/sign.h:3-4,
+// src/rotation.h:1-10, src/sort.h:1-13).  This header provides exactly those names -- CryptoContext<DCRTPoly>,
+// Ciphertext<DCRTPoly>, Plaintext, KeyPair/PublicKey/PrivateKey, CCParams<CryptoContextCKKSRNS>,
+// GenCryptoContext -- with the same call signatures and shared_ptr value semantics, each member forwarding
+// to one extern "C" entry point.  OpenFHE exceptions become std::runtime_error carrying ckks_last_error().
+// No arithmetic happens on the host: every member ends in a CUDA kernel launch inside libckks_b200.so.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <functional>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/ckks_b200.h"
+
+namespace lbcrypto {
+
+struct DCRTPoly {};               // element tag (all polynomials live on the device)
+struct CryptoContextCKKSRNS {};   // scheme tag for CCParams
+enum PKESchemeFeature { PKE = 1, KEYSWITCH = 2, LEVELEDSHE = 4, ADVANCEDSHE = 8, FHE = 16 };
+enum SecurityLevel { HEStd_128_classic, HEStd_192_classic, HEStd_256_classic, HEStd_NotSet };
+enum ScalingTechnique { FIXEDMANUAL, FIXEDAUTO, FLEXIBLEAUTO, FLEXIBLEAUTOEXT };
+enum KeySwitchTechnique { BV, HYBRID };
+enum SecretKeyDist { GAUSSIAN, UNIFORM_TERNARY, SPARSE_TERNARY };
+
+inline void ckks_check(int rc, const char* what) {
+    if (rc != 0) throw std::runtime_error(std::string(what) + ": " + ckks_last_error());
+}
+
+template <class Scheme> class CCParams;
+template <> class CCParams<CryptoContextCKKSRNS> {
+  public:
+    uint32_t multDepth = 1, scalingModSize = 50, firstModSize = 60, batchSize = 0, ringDim = 0, numLargeDigits = 0;
+    SecurityLevel security = HEStd_128_classic;
+    ScalingTechnique scalTech = FLEXIBLEAUTOEXT;
+    uint64_t seed = 1;   // engine extension: seed of the counter-based sampler
+    void SetMultiplicativeDepth(uint32_t d) { multDepth = d; }
+    void SetScalingModSize(uint32_t b) { scalingModSize = b; }
+    void SetFirstModSize(uint32_t b) { firstModSize = b; }
+    void SetBatchSize(uint32_t b) { batchSize = b; }
+    void SetRingDim(uint32_t r) { ringDim = r; }
+    void SetSecurityLevel(SecurityLevel s) { security = s; }
+    void SetScalingTechnique(ScalingTechnique t) { scalTech = t; }
+    void SetNumLargeDigits(uint32_t n) { numLargeDigits = n; }
+    void SetKeySwitchTechnique(KeySwitchTechnique) {}
+    void SetSecretKeyDist(SecretKeyDist) {}
+    uint32_t GetMultiplicativeDepth() const { return multDepth; }
+    uint32_t GetRingDim() const { return ringDim; }
+    uint32_t GetBatchSize() const { return batchSize; }
+};
+
+class CryptoContextImpl;
+
+// Ciphertext<DCRTPoly> / encoded Plaintext: owns (or borrows) one ckks_ct_t handle.
+class CiphertextImpl {
+  public:
+    ckks_ct_t* h = nullptr;
+    bool owned = true;
+    CiphertextImpl(ckks_ct_t* handle, bool own = true) : h(handle), owned(own) {}
+    CiphertextImpl(const CiphertextImpl&) = delete;
+    ~CiphertextImpl() { if (h && owned) ckks_ct_free(h); }
+    int64_t get(int what) const { int64_t v = 0; ckks_check(ckks_ct_get(h, what, &v), "ct_get"); return v; }
+    size_t GetSlots() const { return (size_t)get(0); }
+    size_t GetLevel() const { return (size_t)get(1); }
+    size_t GetNoiseScaleDeg() const { return (size_t)get(2); }
+    double GetScalingFactor() const { double s = 0; ckks_check(ckks_ct_get_scaling_factor(h, &s), "ct_sf"); return s; }
+    // SetSlots mutates metadata through const references exactly like the reference relies on
+    // (reference src/sort_algo.h:429,434,447,501,614,711)
+    void SetSlots(size_t s) const { ckks_check(ckks_ct_set_slots(h, (int)s), "SetSlots"); }
+    std::shared_ptr<CiphertextImpl> Clone() const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_ct_clone(h, &o), "Clone");
+        return std::make_shared<CiphertextImpl>(o);
+    }
+};
+template <class E> using Ciphertext = std::shared_ptr<CiphertextImpl>;
+template <class E> using ConstCiphertext = std::shared_ptr<const CiphertextImpl>;
+
+// Plaintext: either an encoded device polynomial (MakeCKKSPackedPlaintext) or a decrypted value vector.
+class PlaintextImpl {
+  public:
+    std::shared_ptr<CiphertextImpl> enc;   // encoded form (1 polynomial)
+    std::vector<double> values;            // decoded form (Decrypt)
+    double logPrecision = 0;
+    void SetLength(size_t n) { values.resize(n); }
+    const std::vector<double>& GetRealPackedValue() const { return values; }
+    std::vector<double> GetCKKSPackedValueReal() const { return values; }
+    double GetLogPrecision() const { return logPrecision; }
+    size_t GetLevel() const { return enc ? enc->GetLevel() : 0; }
+    size_t GetSlots() const { return enc ? enc->GetSlots() : values.size(); }
+};
+typedef std::shared_ptr<PlaintextImpl> Plaintext;
+typedef std::shared_ptr<const PlaintextImpl> ConstPlaintext;
+
+struct KeyImpl { CryptoContextImpl* cc; };
+template <class E> using PublicKey = std::shared_ptr<KeyImpl>;
+template <class E> using PrivateKey = std::shared_ptr<KeyImpl>;
+template <class E> struct KeyPair {
+    PublicKey<E> publicKey; PrivateKey<E> secretKey;
+    bool good() const { return publicKey && secretKey; }
+};
+
+struct EncodingParamsImpl { uint32_t batch; uint32_t GetBatchSize() const { return batch; } };
+
+// CryptoContext<DCRTPoly>: one engine context (owned when created by GenCryptoContext, borrowed when
+// wrapped around a handle that arrived through the C entry points of sortfhe_host.h).
+class CryptoContextImpl {
+    typedef std::shared_ptr<CiphertextImpl> CT;
+    static CT wrap(ckks_ct_t* o) { return std::make_shared<CiphertextImpl>(o); }
+    typedef int (*BinFn)(ckks_ctx_t*, const ckks_ct_t*, const ckks_ct_t*, ckks_ct_t**);
+    typedef int (*CstFn)(ckks_ctx_t*, const ckks_ct_t*, double, ckks_ct_t**);
+    CT bin(BinFn f, const CT& a, const CT& b, const char* name) const {
+        if (!a || !b) throw std::runtime_error(std::string(name) + ": null ciphertext");
+        ckks_ct_t* o = nullptr; ckks_check(f(ctx, a->h, b->h, &o), name); return wrap(o);
+    }
+    CT cst(CstFn f, const CT& a, double c, const char* name) const {
+        if (!a) throw std::runtime_error(std::string(name) + ": null ciphertext");
+        ckks_ct_t* o = nullptr; ckks_check(f(ctx, a->h, c, &o), name); return wrap(o);
+    }
+    static const CT& enc_of(const Plaintext& p) {
+        if (!p || !p->enc) throw std::runtime_error("plaintext is not encoded");
+        return p->enc;
+    }
+
+  public:
+    ckks_ctx_t* ctx = nullptr;
+    bool owned = false;
+    uint32_t batchSize = 0;
+    CryptoContextImpl(ckks_ctx_t* c, bool own, uint32_t batch) : ctx(c), owned(own), batchSize(batch) {}
+    CryptoContextImpl(const CryptoContextImpl&) = delete;
+    ~CryptoContextImpl() { if (ctx && owned) ckks_ctx_destroy(ctx); }
+
+    int64_t info(int what) const { int64_t v = 0; ckks_check(ckks_ctx_info(ctx, what, &v), "ctx_info"); return v; }
+    void Enable(PKESchemeFeature) {}
+    uint32_t GetRingDimension() const { return (uint32_t)info(0); }
+    uint32_t GetCyclotomicOrder() const { return (uint32_t)info(5); }
+    std::shared_ptr<EncodingParamsImpl> GetEncodingParams() const {
+        return std::make_shared<EncodingParamsImpl>(EncodingParamsImpl{batchSize ? batchSize : GetRingDimension() / 2});
+    }
+
+    // ---- keys (tests/DirectSortTest.cpp:40-57)
+    KeyPair<DCRTPoly> KeyGen() {
+        ckks_check(ckks_keygen(ctx), "KeyGen");
+        auto k = std::make_shared<KeyImpl>(KeyImpl{this});
+        return KeyPair<DCRTPoly>{k, k};
+    }
+    void EvalMultKeyGen(const PrivateKey<DCRTPoly>&) { ckks_check(ckks_eval_mult_keygen(ctx), "EvalMultKeyGen"); }
+    void EvalRotateKeyGen(const PrivateKey<DCRTPoly>&, const std::vector<int>& idx) {
+        std::vector<int32_t> v(idx.begin(), idx.end());
+        ckks_check(ckks_eval_rotate_keygen(ctx, v.data(), (int)v.size()), "EvalRotateKeyGen");
+    }
+    void ClearEvalMultKeys() {}
+    void ClearEvalAutomorphismKeys() {}
+
+    // ---- encode / encrypt / decrypt
+    Plaintext MakeCKKSPackedPlaintext(const std::vector<double>& v, size_t scaleDeg = 1, uint32_t level = 0,
+                                      const void* params = nullptr, uint32_t slots = 0) const {
+        (void)params;
+        uint32_t s = slots ? slots : (batchSize ? batchSize : GetRingDimension() / 2);
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_make_packed_plaintext(ctx, v.data(), (int)v.size(), (int)scaleDeg, (int)level, (int)s, &o),
+                   "MakeCKKSPackedPlaintext");
+        auto p = std::make_shared<PlaintextImpl>();
+        p->enc = wrap(o);
+        return p;
+    }
+    CT Encrypt(const PublicKey<DCRTPoly>&, const Plaintext& pt) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_encrypt(ctx, enc_of(pt)->h, &o), "Encrypt"); return wrap(o);
+    }
+    void Decrypt(const PrivateKey<DCRTPoly>&, const CT& ct, Plaintext* out) const {
+        auto p = std::make_shared<PlaintextImpl>();
+        p->values.assign(ct->GetSlots(), 0.0);
+        ckks_check(ckks_decrypt(ctx, ct->h, p->values.data(), (int)p->values.size()), "Decrypt");
+        *out = p;
+    }
+
+    // ---- additions (reference: ~160 call sites, e.g. sort_algo.h:358,454,708,720; comparison.cpp:13,19)
+    CT EvalAdd(const CT& a, const CT& b) const { return bin(ckks_eval_add, a, b, "EvalAdd"); }
+    CT EvalAdd(const CT& a, const Plaintext& p) const { return bin(ckks_eval_add, a, enc_of(p), "EvalAdd"); }
+    CT EvalAdd(const Plaintext& p, const CT& a) const { return bin(ckks_eval_add, a, enc_of(p), "EvalAdd"); }
+    CT EvalAdd(const CT& a, double c) const { return cst(ckks_eval_add_const, a, c, "EvalAdd"); }
+    CT EvalAdd(double c, const CT& a) const { return cst(ckks_eval_add_const, a, c, "EvalAdd"); }
+    CT EvalSub(const CT& a, const CT& b) const { return bin(ckks_eval_sub, a, b, "EvalSub"); }
+    CT EvalSub(const CT& a, const Plaintext& p) const { return bin(ckks_eval_sub, a, enc_of(p), "EvalSub"); }
+    CT EvalSub(const Plaintext& p, const CT& a) const { return bin(ckks_eval_sub, enc_of(p), a, "EvalSub"); }
+    CT EvalSub(const CT& a, double c) const { return cst(ckks_eval_sub_const, a, c, "EvalSub"); }
+    CT EvalSub(double c, const CT& a) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_const_sub(ctx, c, a->h, &o), "EvalSub"); return wrap(o);
+    }
+    template <class B> void EvalAddInPlace(CT& a, const B& b) const { a = EvalAdd(a, b); }
+    template <class B> void EvalSubInPlace(CT& a, const B& b) const { a = EvalSub(a, b); }
+    CT EvalNegate(const CT& a) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_negate(ctx, a->h, &o), "EvalNegate"); return wrap(o);
+    }
+    void EvalNegateInPlace(CT& a) const { a = EvalNegate(a); }
+    CT EvalAddMany(const std::vector<CT>& v) const {
+        std::vector<const ckks_ct_t*> hs; for (auto& c : v) hs.push_back(c->h);
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_add_many(ctx, hs.data(), (int)hs.size(), &o), "EvalAddMany");
+        return wrap(o);
+    }
+    // ---- multiplications (sign.cpp:23-56,100-156; comparison.cpp:19,35-38; sort_algo.h:358,576,723,730)
+    CT EvalMult(const CT& a, const CT& b) const { return bin(ckks_eval_mult, a, b, "EvalMult"); }
+    CT EvalMult(const CT& a, const Plaintext& p) const { return bin(ckks_eval_mult, a, enc_of(p), "EvalMult"); }
+    CT EvalMult(const Plaintext& p, const CT& a) const { return bin(ckks_eval_mult, a, enc_of(p), "EvalMult"); }
+    CT EvalMult(const CT& a, double c) const { return cst(ckks_eval_mult_const, a, c, "EvalMult"); }
+    CT EvalMult(double c, const CT& a) const { return cst(ckks_eval_mult_const, a, c, "EvalMult"); }
+    void EvalMultInPlace(CT& a, double c) const { a = EvalMult(a, c); }
+    CT EvalMultAndRelinearize(const CT& a, const CT& b) const { return bin(ckks_eval_mult, a, b, "EvalMultAndRelinearize"); }
+    CT EvalSquare(const CT& a) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_square(ctx, a->h, &o), "EvalSquare"); return wrap(o);
+    }
+    // ---- rotations (rotation.h:224,231; mehp24_utils.h:32-40)
+    CT EvalRotate(const CT& a, int32_t index) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_rotate(ctx, a->h, index, &o), "EvalRotate"); return wrap(o);
+    }
+    bool HasRotationKey(int32_t index) const { return ckks_has_rotation_key(ctx, index) != 0; }
+    // ---- polynomial evaluators (sort_algo.h:727-728, sign.cpp:76, mehp24_utils.cpp:256-259)
+    CT EvalChebyshevSeriesPS(const CT& x, const std::vector<double>& coeffs, double a, double b) const {
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_eval_chebyshev_series_ps(ctx, x->h, coeffs.data(), (int)coeffs.size(), a, b, &o), "EvalChebyshevSeriesPS");
+        return wrap(o);
+    }
+    CT EvalChebyshevSeries(const CT& x, const std::vector<double>& coeffs, double a, double b) const {
+        return EvalChebyshevSeriesPS(x, coeffs, a, b);
+    }
+    CT EvalPolyLinear(const CT& x, const std::vector<double>& coeffs) const {
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_eval_poly_linear(ctx, x->h, coeffs.data(), (int)coeffs.size(), &o), "EvalPolyLinear");
+        return wrap(o);
+    }
+    // EvalBootstrap (EvalUtils.cpp:76, sign.cpp:168): not part of this round's hot-path scope
+    CT EvalBootstrap(const CT&, uint32_t = 1, uint32_t = 0) const {
+        throw std::runtime_error("EvalBootstrap: CKKS bootstrapping is not implemented by the B200 engine yet");
+    }
+};
+template <class E> using CryptoContext = std::shared_ptr<CryptoContextImpl>;
+
+// GenCryptoContext(CCParams<CryptoContextCKKSRNS>) -- tests/DirectSortTest.cpp:29-44
+inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKSRNS>& p) {
+    if (p.ringDim == 0 || (p.ringDim & (p.ringDim - 1))) throw std::runtime_error("GenCryptoContext: SetRingDim(2^k) is required");
+    int logn = 0; while ((1u << logn) < p.ringDim) logn++;
+    int tech = p.scalTech == FLEXIBLEAUTOEXT ? 1 : 0;
+    if (p.scalTech != FLEXIBLEAUTOEXT && p.scalTech != FLEXIBLEAUTO)
+        throw std::runtime_error("GenCryptoContext: only FLEXIBLEAUTO / FLEXIBLEAUTOEXT are implemented");
+    ckks_ctx_t* c = nullptr;
+    ckks_check(ckks_ctx_create(&c, logn, (int)p.multDepth, (int)p.scalingModSize, (int)p.firstModSize, (int)p.numLargeDigits,
+                               tech, p.seed, 0), "GenCryptoContext");
+    return std::make_shared<CryptoContextImpl>(c, true, p.batchSize);
+}
+
+}  // namespace lbcrypto

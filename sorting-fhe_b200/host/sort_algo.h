@@ -1,0 +1,192 @@
+// sort_algo.h -- SortBase<N> and DirectSort<N> (Optimized Rank Sort) with the reference's interface
+// (reference src/sort_algo.h:36-59, 61-774).  Orchestration only: every cc-> call below is a CUDA kernel
+// schedule inside libckks_b200.so.  The reference's OpenMP loops (sort_algo.h:334,349,425,713) are plain loops
+// here: all work is queued on the engine's CUDA stream, where the limb dimension provides the parallelism.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <set>
+#include <vector>
+#include "cheb_coeffs.h"
+#include "comparison.h"
+#include "rotation.h"
+
+enum class SortAlgo { DirectSort, BitonicSort };
+
+template <int N> class SortBase {
+  protected:
+    std::shared_ptr<Encryption> m_enc;
+    const Ciphertext<DCRTPoly> m_zeroCache;   // encryption of N zeros, cloned as accumulator seed (:42-45)
+    virtual Ciphertext<DCRTPoly> createZeroCache() { return m_enc->encryptInput(std::vector<double>(N, 0.0)); }
+  public:
+    SortBase(std::shared_ptr<Encryption> enc) : m_enc(enc), m_zeroCache(createZeroCache()) {}
+    virtual ~SortBase() = default;
+    virtual Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly>& input_array, SignFunc SignFunc, SignConfig& Cfg) = 0;
+    virtual const Ciphertext<DCRTPoly>& getZero() const { return m_zeroCache; }
+    constexpr size_t getArraySize() const { return N; }
+};
+
+namespace directsort_detail {
+inline int log2i(int v) { int l = 0; while ((1 << (l + 1)) <= v) l++; return l; }
+// np of constructRank (:383-416) and of rotationIndexCheckN (:670-703)
+inline int rankBabySteps(int n) { return n <= 8 ? 2 : n <= 32 ? 4 : n <= 128 ? 8 : n <= 512 ? 16 : 32; }
+inline int indexBabySteps(int n) { return n <= 8 ? 2 : n <= 32 ? 4 : n <= 128 ? 8 : n == 256 ? 16 : n <= 1024 ? 8 : 4; }
+}  // namespace directsort_detail
+
+template <int N> class DirectSort : public SortBase<N> {
+    CryptoContext<DCRTPoly> m_cc;
+    PublicKey<DCRTPoly> m_PublicKey;
+    Comparison comp;
+    RotationComposer<N> rot;
+    int max_batch;   // ringDim / 2
+    typedef Ciphertext<DCRTPoly> CT;
+
+  public:
+    std::shared_ptr<Encryption> m_enc;
+
+    DirectSort(CryptoContext<DCRTPoly> cc, PublicKey<DCRTPoly> publicKey, std::vector<int> rotIndices,
+               std::shared_ptr<Encryption> enc)
+        : SortBase<N>(enc), m_cc(cc), m_PublicKey(publicKey), comp(enc), rot(cc, enc, rotIndices), m_enc(enc) {
+        max_batch = (int)m_cc->GetRingDimension() / 2;
+    }
+    const std::set<int>& getRotationCalls() const { return rot.getRotationCalls(); }
+
+    // every rotation amount sort() asks RotationComposer for at a given ring dimension; equals the reference's
+    // literal key tables (:94-198) for the ring 2^17 fixtures
+    static std::vector<int> requiredRotations(int ringDim) {
+        using namespace directsort_detail;
+        const int P = std::min(N, ringDim / 2 / N), B = N / P, S = N * P;
+        std::set<int> r;
+        const int np = std::min(rankBabySteps(N), P), npi = indexBabySteps(N);
+        for (int i = 1; i < np; i++) r.insert(i);
+        for (int b = 0; b < B; b++) for (int j = 0; j < P / np; j++) r.insert(b * P + j * np);
+        for (int i = 1; i <= log2i(P); i++) r.insert(S >> i);
+        if (S < ringDim / 2) r.insert(S);   // the reference also keys the full-wrap amount (:95,99,104,...)
+        for (int i = 1; i < npi; i++) r.insert(i);
+        for (int b = 0; b < B; b++) for (int i = 0; i < (S / N) / npi; i++) r.insert(b * P + i * npi);
+        r.erase(0);
+        return std::vector<int>(r.begin(), r.end());
+    }
+
+    // DirectSort<N>::getSizeParameters (:87-201): batch N, 40-bit scaling, depth table, rotation key set
+    static void getSizeParameters(CCParams<CryptoContextCKKSRNS>& parameters, std::vector<int>& rotations) {
+        static const int depth[][2] = {{4, 23}, {8, 24}, {16, 25}, {32, 28}, {64, 29}, {128, 30},
+                                       {256, 34}, {512, 35}, {1024, 39}, {2048, 52}};
+        parameters.SetBatchSize(N);
+        parameters.SetScalingModSize(40);
+        int d = 0;
+        for (auto& e : depth) if (e[0] == N) d = e[1];
+        if (!d) throw std::runtime_error("DirectSort: unsupported array size");
+        parameters.SetMultiplicativeDepth(d);
+        rotations = requiredRotations(parameters.GetRingDim() ? (int)parameters.GetRingDim() : (1 << 17));
+    }
+
+    // ---- plaintext pattern generators (:206-306)
+    std::vector<double> generateMaskVector(int num_slots, int k) {    // block k of length N set to 1
+        std::vector<double> v(num_slots, 0.0);
+        std::fill(v.begin() + (size_t)k * N, v.begin() + (size_t)(k + 1) * N, 1.0);
+        return v;
+    }
+    std::vector<double> generateMaskVectorN(int num_slots, int k) { return generateMaskVector(num_slots, k); }
+    std::vector<double> generateIndexVector() {
+        std::vector<double> v(N);
+        for (int i = 0; i < N; i++) v[i] = (double)i;
+        return v;
+    }
+    std::vector<double> generateCheckingVectorN(int num_slots, int k) {   // block j holds (k + j) mod N
+        std::vector<double> v(num_slots);
+        for (int i = 0; i < num_slots; i++) v[i] = (double)((k + i / N) % N);
+        return v;
+    }
+    std::vector<double> vectorRotate(const std::vector<double>& vec, int rotateIndex) {   // >0 left, <0 right
+        std::vector<double> r = vec;
+        if (r.empty()) return r;
+        int n = (int)r.size(), k = ((rotateIndex % n) + n) % n;
+        std::rotate(r.begin(), r.begin() + k, r.end());
+        return r;
+    }
+
+    // vecRotsOpt (:326-366): sum_j Rot_{is*P + j*np}( sum_i mask_{np*j+i} (shifted right) * babyStep_i )
+    CT vecRotsOpt(const std::vector<CT>& preRotatedArrays, int num_partition, int num_slots, int np, int is) {
+        std::vector<CT> outer(num_partition / np);
+        for (int j = 0; j < num_partition / np; j++) {
+            CT T = this->getZero()->Clone();
+            T->SetSlots(num_slots);
+            for (int i = 0; i < np; i++) {
+                auto msk = vectorRotate(generateMaskVector(num_slots, np * j + i), -is * num_partition - j * np);
+                auto pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, 0, nullptr, num_slots);
+                T = m_cc->EvalAdd(T, m_cc->EvalMult(preRotatedArrays[i], pmsk));
+            }
+            outer[j] = rot.rotate(T, is * num_partition + j * np);
+        }
+        return m_cc->EvalAddMany(outer);
+    }
+
+    // constructRank (:368-506): rank_i = #{j : a_j < a_i}
+    CT constructRank(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) {
+        const int num_partition = std::min(N, max_batch / N), num_batch = N / num_partition;
+        const int num_slots = N * num_partition;
+        const int np = std::min(directsort_detail::rankBabySteps(N), num_partition);
+        std::vector<CT> babySteps(np);
+        for (int i = 0; i < np; i++) { babySteps[i] = rot.rotate(input_array, i); babySteps[i]->SetSlots(num_slots); }
+        CT rank = this->getZero()->Clone();
+        rank->SetSlots(num_slots);
+        for (int i = 0; i < num_batch; i++) {
+            CT shifted = vecRotsOpt(babySteps, num_partition, num_slots, np, i);
+            CT dup = input_array->Clone();
+            dup->SetSlots(num_slots);
+            m_cc->EvalAddInPlace(rank, comp.compare(m_cc, dup, shifted, SignFunc, Cfg));
+        }
+        for (int i = 1; i < std::log2(num_partition) + 1; i++)
+            m_cc->EvalAddInPlace(rank, rot.rotate(rank, num_slots / (1 << i)));
+        rank->SetSlots(N);
+        return m_cc->EvalSub(rank, 0.5);   // self comparison contributes 1/2
+    }
+
+    // blindRotationOptN (:561-584)
+    CT blindRotationOptN(const std::vector<CT>& masked_inputs, int num_slots, int np, int ib, int num_partition) {
+        CT result = this->getZero()->Clone();
+        for (int i = 0; i < (num_slots / N) / np; i++) {
+            CT tmp = this->getZero()->Clone();
+            for (int j = 0; j < np; j++) {
+                auto msk = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j);
+                Plaintext pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)masked_inputs[j]->GetLevel(), nullptr, num_slots);
+                m_cc->EvalAddInPlace(tmp, m_cc->EvalMult(masked_inputs[j], pmsk));
+            }
+            tmp = rot.rotate(tmp, ib * num_partition + i * np);
+            m_cc->EvalAddInPlace(result, tmp);
+        }
+        return result;
+    }
+
+    // rotationIndexCheckN (:658-750): out_j = sum_i a_i [rank_i = j] through the doubled-sinc indicator
+    CT rotationIndexCheckN(const CT& ctx_Rank, const CT& input_array) {
+        CT output = this->getZero()->Clone();
+        const int num_partition = std::min(N, max_batch / N), num_batch = N / num_partition;
+        const int num_slots = num_partition * N, np = directsort_detail::indexBabySteps(N);
+        Plaintext index_vector = m_cc->MakeCKKSPackedPlaintext(generateIndexVector(), 1, (uint32_t)ctx_Rank->GetLevel(), nullptr, N);
+        CT index_minus_rank = m_cc->EvalSub(index_vector, ctx_Rank);
+        index_minus_rank->SetSlots(num_slots);
+        input_array->SetSlots(num_slots);   // mutates the caller's ciphertext metadata, as the reference does (:711)
+        for (int b = 0; b < num_batch; b++) {
+            Plaintext chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(num_slots, b * num_partition), 1,
+                                                          (uint32_t)index_minus_rank->GetLevel(), nullptr, num_slots);
+            CT rotIndex = m_cc->EvalSub(index_minus_rank, chk);
+            m_cc->EvalMultInPlace(rotIndex, 1.0 / N / 2);   // (-2N, N) -> (-1, 1/2)
+            rotIndex = m_cc->EvalChebyshevSeriesPS(rotIndex, selectDoubledSincCoefficients<N>(), -1, 1);
+            CT masked_input = m_cc->EvalMult(rotIndex, input_array);
+            std::vector<CT> masked_inputs(np);
+            for (int i = 0; i < np; i++) masked_inputs[i] = rot.rotate(masked_input, i);
+            m_cc->EvalAddInPlace(output, blindRotationOptN(masked_inputs, num_slots, np, b, num_partition));
+        }
+        for (int i = 1; i < std::log2(num_partition) + 1; i++)
+            m_cc->EvalAddInPlace(output, rot.rotate(output, num_slots / (1 << i)));
+        output->SetSlots(N);
+        return output;
+    }
+
+    CT sort(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) override {   // (:752-774)
+        CT rank = constructRank(input_array, SignFunc, Cfg);
+        return rotationIndexCheckN(rank, input_array);
+    }
+};
