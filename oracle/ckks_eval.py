@@ -7,6 +7,8 @@ FLEXIBLEAUTO(EXT) level/scale bookkeeping (leveledshe-ckksrns.cpp AdjustLevelsAn
 hybrid key switching (keyswitch-hybrid.cpp) and rescale (DropLastElementAndScale).
 Parity unpinned vs OpenFHE at limb level (see ckks_oracle.py header).
 """
+import math
+
 import numpy as np
 
 from .ckks_oracle import (P, PD, STREAM_PK_A, STREAM_PK_E, STREAM_SECRET, Context, lib, stream_enc,
@@ -157,14 +159,26 @@ class Evaluator:
         ksi, rot, M = c.fft_tables()
         self.L.orc_fft_special_inv(PD(v), slots, PD(ksi), rot.ctypes.data_as(u32p), M)
         nh, gap = c.n // 2, (c.n // 2) // slots
+        vs = v * sf
+        # CKKSPackedEncoding::Encode (64-bit native): values beyond 61 bits are scaled down by 2^logApprox
+        # before rounding and the residues multiplied back by 2^logApprox mod q_i
+        mx = float(np.max(np.abs(vs)))
+        log_approx = 0
+        if mx > 0.0:
+            f, e = math.frexp(mx)
+            logc = e - 1 if f == 0.5 else e
+            log_approx = max(0, logc - 61)
+        vs = np.ldexp(vs, -log_approx)
         coef = np.zeros(c.n, dtype=np.float64)
-        coef[0:nh:gap] = v[0::2] * sf
-        coef[nh::gap] = v[1::2] * sf
+        coef[0:nh:gap] = vs[0::2]
+        coef[nh::gap] = vs[1::2]
         nl = c.size_q - level
         d = np.empty((1, nl, c.n), dtype=np.uint64)
         for i in range(nl):
             self.L.orc_round_to_rns(P(d[0, i]), PD(coef), c.n, c.q[i])
-            c.ntt(d[0, i], i)
+            if log_approx:
+                self.L.orc_vmuls(P(d[0, i]), P(d[0, i]), (1 << log_approx) % c.q[i], c.n, c.q[i])
+        c.ntt_rows(d[0], list(range(nl)))
         return Ct(d, level, deg, sf, slots)
 
     def encrypt(self, pt: Ct):

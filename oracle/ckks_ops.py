@@ -45,12 +45,13 @@ class OracleCC(ChebyshevMixin, Evaluator):
         for p in range(ct.d.shape[0]):
             last = ct.d[p, nl - 1].copy()
             c.intt(last, nl - 1)
+            t = np.empty((nl - 1, c.n), dtype=np.uint64)
+            for i in range(nl - 1):
+                self.L.orc_switch_modulus(P(t[i]), P(last), c.n, ql, c.q[i])
+            c.ntt_rows(t, list(range(nl - 1)))
             for i in range(nl - 1):
                 qi = c.q[i]
-                t = np.empty(c.n, dtype=np.uint64)
-                self.L.orc_switch_modulus(P(t), P(last), c.n, ql, qi)
-                c.ntt(t, i)
-                self.L.orc_vsub(P(out[p, i]), P(ct.d[p, i]), P(t), c.n, qi)
+                self.L.orc_vsub(P(out[p, i]), P(ct.d[p, i]), P(t[i]), c.n, qi)
                 self.L.orc_vmuls(P(out[p, i]), P(out[p, i]), pow(ql % qi, -1, qi), c.n, qi)
         ct.d = out
         ct.level += 1
@@ -130,13 +131,11 @@ class OracleCC(ChebyshevMixin, Evaluator):
         for j, pt in enumerate(parts):
             dig = pt["dig"]
             coef = np.ascontiguousarray(poly[dig[0]:dig[-1] + 1].copy())
-            for r, i in enumerate(dig):
-                c.intt(coef[r], i)
+            c.ntt_rows(coef, dig, inverse=True)
             conv = np.empty((len(pt["compl"]), c.n), dtype=np.uint64)
             self.L.orc_approx_switch_crt_basis(P(conv), P(coef), c.n, len(dig), len(pt["compl"]),
                                                P(pt["qin"]), P(pt["qout"]), P(pt["hatinv"]), P(pt["hatmod"]))
-            for r, mi in enumerate(pt["compl"]):
-                c.ntt(conv[r], mi)
+            c.ntt_rows(conv, pt["compl"])
             pos = {mi: r for r, mi in enumerate(pt["compl"])}
             for e, mi in enumerate(ext_ids):
                 dj = poly[mi] if mi in dig else conv[pos[mi]]
@@ -146,14 +145,13 @@ class OracleCC(ChebyshevMixin, Evaluator):
         out = np.empty((2, nl, c.n), dtype=np.uint64)
         for h in range(2):
             pp = np.ascontiguousarray(acc[h, nl:].copy())
-            for k in range(c.size_p):
-                c.intt(pp[k], c.size_q + k)
+            c.ntt_rows(pp, [c.size_q + k for k in range(c.size_p)], inverse=True)
             conv = np.empty((nl, c.n), dtype=np.uint64)
             self.L.orc_approx_switch_crt_basis(P(conv), P(pp), c.n, c.size_p, nl, P(md["pin"]), P(md["qout"]),
                                                P(md["phatinv"]), P(md["phatmod"]))
+            c.ntt_rows(conv, list(range(nl)))
             for i in range(nl):
                 q = c.q[i]
-                c.ntt(conv[i], i)
                 self.L.orc_vsub(P(out[h, i]), P(acc[h, i]), P(conv[i]), c.n, q)
                 self.L.orc_vmuls(P(out[h, i]), P(out[h, i]), md["pinv"][i], c.n, q)
         return out

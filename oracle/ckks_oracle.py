@@ -31,11 +31,16 @@ u32p = ctypes.POINTER(ctypes.c_uint32)
 
 def build_lib(force=False):
     so = os.path.join(_HERE, "libckks_oracle.so")
-    src = os.path.join(_HERE, "ckks_prims.c")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
-        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp",
-                               "-o", so, src, "-lm"])
+    srcs = [os.path.join(_HERE, "ckks_prims.c"), os.path.join(_HERE, "ckks_fast.c")]
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(x) for x in srcs):
+        subprocess.check_call(["gcc", "-O3", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp",
+                               "-o", so] + srcs + ["-lm"])
     return so
+
+
+SLOW = bool(int(os.environ.get("ORACLE_SLOW", "0")))  # 1: use only the slow reference loops of ckks_prims.c
+_FAST_TWINS = ["vadd", "vsub", "vneg", "vmul", "vmuladd", "vmuls", "vadds", "automorph_eval",
+               "approx_switch_crt_basis", "switch_modulus"]
 
 
 def lib():
@@ -60,9 +65,17 @@ def lib():
             ("orc_round_to_rns", None, [u64p, f64p, S, U]),
             ("orc_crt2_to_double", None, [f64p, u64p, u64p, S, U, U]),
             ("orc_crt1_to_double", None, [f64p, u64p, S, U]),
+            ("orf_shoup_table", None, [u64p, u64p, S, U]),
+            ("orf_ntt_batch", None, [u64p, I, I, ctypes.POINTER(ctypes.c_int32), u64p, u64p, u64p, u64p, I]),
         ]:
             f = getattr(L, name)
             f.restype, f.argtypes = res, args
+        for nm in _FAST_TWINS:  # fast twins share the slow functions' signatures
+            slow, fast = getattr(L, "orc_" + nm), getattr(L, "orf_" + nm)
+            fast.restype, fast.argtypes = slow.restype, slow.argtypes
+            setattr(L, "slow_" + nm, slow)
+            if not SLOW:
+                setattr(L, "orc_" + nm, fast)
         _LIB = L
     return _LIB
 
@@ -170,16 +183,21 @@ class Context:
         self.pmod = pp
         self.moduli = q + pp  # global modulus index space: Q then P
         # NTT tables
-        self.psi, self.psi_br, self.psi_inv_br = [], [], []
-        for mod in self.moduli:
+        M = len(self.moduli)
+        self.psi = []
+        self.psi_br = np.zeros((M, self.n), dtype=np.uint64)       # [modulus][bitrev(i)] = psi^i
+        self.psi_inv_br = np.zeros((M, self.n), dtype=np.uint64)
+        self.psi_br_sh = np.zeros((M, self.n), dtype=np.uint64)    # Shoup companions (fast path only)
+        self.psi_inv_br_sh = np.zeros((M, self.n), dtype=np.uint64)
+        for i, mod in enumerate(self.moduli):
             psi = L.orc_min_root_of_unity(m, mod)
-            t = np.zeros(self.n, dtype=np.uint64)
-            ti = np.zeros(self.n, dtype=np.uint64)
-            L.orc_make_psi_table(P(t), self.log_n, psi, mod)
-            L.orc_make_psi_table(P(ti), self.log_n, L.orc_invmod(psi, mod), mod)
+            L.orc_make_psi_table(P(self.psi_br[i]), self.log_n, psi, mod)
+            L.orc_make_psi_table(P(self.psi_inv_br[i]), self.log_n, L.orc_invmod(psi, mod), mod)
+            L.orf_shoup_table(P(self.psi_br_sh[i]), P(self.psi_br[i]), self.n, mod)
+            L.orf_shoup_table(P(self.psi_inv_br_sh[i]), P(self.psi_inv_br[i]), self.n, mod)
             self.psi.append(psi)
-            self.psi_br.append(t)
-            self.psi_inv_br.append(ti)
+        self.mod_arr = np.array(self.moduli, dtype=np.uint64)
+        self.ninv_arr = np.array([pow(self.n, -1, x) for x in self.moduli], dtype=np.uint64)
         # scaling factors (FLEXIBLEAUTO / FLEXIBLEAUTOEXT)
         sfr = [0.0] * size_q
         sfr[0] = float(q[size_q - 1])
@@ -204,10 +222,26 @@ class Context:
 
     # ---- limb helpers -------------------------------------------------------------
     def ntt(self, a, mod_idx):
-        lib().orc_ntt_fwd(P(a), self.log_n, self.moduli[mod_idx], P(self.psi_br[mod_idx]))
+        self.ntt_rows(a.reshape(1, -1), [mod_idx])
 
     def intt(self, a, mod_idx):
-        lib().orc_ntt_inv(P(a), self.log_n, self.moduli[mod_idx], P(self.psi_inv_br[mod_idx]))
+        self.ntt_rows(a.reshape(1, -1), [mod_idx], inverse=True)
+
+    def ntt_rows(self, a, mod_ids, inverse=False):
+        """in-place (inverse) NTT of the rows of a[rows][n]; row r is a limb modulo moduli[mod_ids[r]]"""
+        assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"] and a.shape == (len(mod_ids), self.n)
+        L = lib()
+        if SLOW:
+            for r, mi in enumerate(mod_ids):
+                if inverse:
+                    L.orc_ntt_inv(P(a[r]), self.log_n, self.moduli[mi], P(self.psi_inv_br[mi]))
+                else:
+                    L.orc_ntt_fwd(P(a[r]), self.log_n, self.moduli[mi], P(self.psi_br[mi]))
+            return
+        ids = (ctypes.c_int32 * len(mod_ids))(*mod_ids)
+        tab, tsh = (self.psi_inv_br, self.psi_inv_br_sh) if inverse else (self.psi_br, self.psi_br_sh)
+        L.orf_ntt_batch(P(a), len(mod_ids), self.log_n, ids, P(self.mod_arr), P(tab), P(tsh), P(self.ninv_arr),
+                        1 if inverse else 0)
 
     def ks_tables(self, size_ql):
         """tables of EvalKeySwitchPrecomputeCore / ApproxModDown at a given number of Q limbs"""

@@ -33,24 +33,7 @@ static ckks_ct* box(Ct* p) { return new ckks_ct{p}; }
 static Context* C(ckks_ctx_t* x) { if (!x) throw std::runtime_error("null context"); return &x->c; }
 static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_error("null ciphertext handle"); return x->p; }
 
-extern "C" {
-
-int ckks_ctx_create(ckks_ctx_t** out, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits,
-                    int scaling_technique, uint64_t seed, int dry_run) {
-    API_BEGIN
-    require_device(dry_run != 0);
-    ckks_ctx* x = new ckks_ctx();
-    try { context_generate(&x->c, log_n, mult_depth, scaling_bits, first_bits, num_large_digits, scaling_technique, seed, dry_run); }
-    catch (...) { delete x; throw; }
-    if (!dry_run) check_cuda("context tables");
-    *out = x;
-    API_END
-}
-
-int ckks_ctx_destroy(ckks_ctx_t* x) {
-    API_BEGIN
-    if (!x) return 0;
-    Context* c = &x->c;
+void context_release(Context* c) {
     if (!c->dry) {
         cudaStreamSynchronize(c->stream);
         cudaFree(c->d_mod); cudaFree(c->d_psi); cudaFree(c->d_psi_sh); cudaFree(c->d_ipsi); cudaFree(c->d_ipsi_sh);
@@ -64,8 +47,33 @@ int ckks_ctx_destroy(ckks_ctx_t* x) {
         for (auto& kv : c->rot) dev_free(c, kv.second.d);
         cudaStreamSynchronize(c->stream);
         if (c->own_stream) cudaStreamDestroy(c->stream);
+        cudaGetLastError();
     }
-    delete x;
+    delete reinterpret_cast<ckks_ctx*>(c);   // Context is the first (only) member of ckks_ctx
+}
+
+extern "C" {
+
+int ckks_ctx_create(ckks_ctx_t** out, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits,
+                    int scaling_technique, uint64_t seed, int dry_run) {
+    API_BEGIN
+    require_device(dry_run != 0);
+    if (!dry_run) cudaGetLastError();   // do not inherit a stale error from earlier work in this process
+    ckks_ctx* x = new ckks_ctx();
+    try { context_generate(&x->c, log_n, mult_depth, scaling_bits, first_bits, num_large_digits, scaling_technique, seed, dry_run); }
+    catch (...) { delete x; throw; }
+    if (!dry_run) check_cuda("context tables");
+    *out = x;
+    API_END
+}
+
+int ckks_ctx_destroy(ckks_ctx_t* x) {
+    API_BEGIN
+    if (!x) return 0;
+    Context* c = &x->c;
+    if (c->closed) return 0;
+    c->closed = true;
+    if (c->live_cts == 0) context_release(c);   // otherwise the last ckks_ct_free finishes the teardown
     API_END
 }
 

@@ -33,27 +33,44 @@ __global__ void k_fft_fwd_stage(double2* v, int size, int len, const double2* ks
     v[i + j] = make_double2(__dadd_rn(u.x, vr), __dadd_rn(u.y, vi));
     v[i + j + lenh] = make_double2(__dsub_rn(u.x, vr), __dsub_rn(u.y, vi));
 }
-// out[i] = in[bitrev(i)] * scale
-__global__ void k_bitrev_scale(double2* out, const double2* in, int size, int bits, double scale, int do_scale) {
+// out[i] = in[bitrev(i)] * scale (* sf, tracking max |.| as raw double bits when maxbits != nullptr)
+__global__ void k_bitrev_scale(double2* out, const double2* in, int size, int bits, double scale, int do_scale, double sf,
+                               u64* maxbits) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= size) return;
     int j = bits ? (int)(__brev((u32)i) >> (32 - bits)) : 0;
     double2 a = in[j];
     if (do_scale) { a.x = __dmul_rn(a.x, scale); a.y = __dmul_rn(a.y, scale); }
+    if (maxbits) {
+        a.x = __dmul_rn(a.x, sf); a.y = __dmul_rn(a.y, sf);
+        double m = fmax(fabs(a.x), fabs(a.y));
+        if (m > 0.0) atomicMax(maxbits, (u64)__double_as_longlong(m));   // positive doubles order like their bit patterns
+    }
     out[i] = a;
 }
 // coefficient x of limb row l: slot k = x / gap (x < nh: real part, else imaginary part)
-__global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, int n, int slots, double sf) {
+// v holds the scaled slot values.  Values beyond 61 bits are divided by 2^logApprox before rounding and the
+// residues multiplied back by 2^logApprox mod q (OpenFHE CKKSPackedEncoding::Encode, 64-bit native path).
+__global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, int n, int slots, const u64* maxbits) {
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
     int l = blockIdx.y, nh = n >> 1, gap = nh / slots;
-    u64 q = mi[l].q, r = 0;
+    const ModInfo m = mi[l];
+    u64 q = m.q, r = 0;
     int xx = x < nh ? x : x - nh;
     if (xx % gap == 0) {
+        int log_approx = 0;
+        u64 mb = *maxbits;
+        if (mb) {   // ceil(log2(max)) from the exponent: frexp gives max = f * 2^e, f in [0.5, 1)
+            int e; double f = frexp(__longlong_as_double((long long)mb), &e);
+            int logc = (f == 0.5) ? e - 1 : e;
+            if (logc > 61) log_approx = logc - 61;
+        }
         double2 z = v[xx / gap];
-        double val = rint(__dmul_rn(x < nh ? z.x : z.y, sf));
+        double val = rint(ldexp(x < nh ? z.x : z.y, -log_approx));
         long long iv = (long long)val;
-        if (iv >= 0) r = (u64)iv % q; else { u64 m = ((u64)(-iv)) % q; r = m ? q - m : 0; }
+        if (iv >= 0) r = (u64)iv % q; else { u64 mm = ((u64)(-iv)) % q; r = mm ? q - mm : 0; }
+        if (log_approx) r = barrett_mul(r, (1ull << log_approx) % q, m);
     }
     out[(size_t)l * n + x] = r;
 }
@@ -71,11 +88,14 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
     const int M = 2 * c->n;
     for (int len = slots; len >= 2; len >>= 1)
         k_fft_inv_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(a, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
-    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0 / (double)slots, 1);
+    u64* mx = dev_alloc(c, 1);
+    cudaMemsetAsync(mx, 0, sizeof(u64), c->stream);
+    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0 / (double)slots, 1, sf, mx);
     dim3 grid((c->n + 255) / 256, nl);
-    k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, sf);
+    k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, mx);
     dev_free(c, a);
     dev_free(c, b);
+    dev_free(c, mx);
     launch_ntt(c, out, nl, mods_q(nl), false);
 }
 
@@ -122,7 +142,7 @@ void launch_decode(Context* c, double* h_out, const u64* m, int nlimbs, double s
         q0inv = (u64)r;
     }
     k_crt_gather<<<(slots + 255) / 256, 256, 0, c->stream>>>(a, m, nlimbs, c->d_mod, c->n, slots, sf, q0inv);
-    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0, 0);
+    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0, 0, 1.0, nullptr);
     const int M = 2 * c->n;
     for (int len = 2; len <= slots; len <<= 1)
         k_fft_fwd_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(b, slots, len, (const double2*)c->d_ksi, c->d_rot, M);

@@ -68,6 +68,10 @@ struct Context {
     bool own_stream = false;
     Stats stats;
     std::string last_error;
+    // handle lifetime: ciphertexts may outlive ckks_ctx_destroy (shared_ptr / Python GC order); the context is
+    // torn down when it is closed AND the last ciphertext handle is gone
+    long live_cts = 0;
+    bool closed = false;
     int M() const { return size_q + size_p; }
 };
 
@@ -79,6 +83,8 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     double sf;
     int slots;
 };
+
+void context_release(Context* c);   // capi.cu: free device tables + delete (called once closed && live_cts == 0)
 
 // ---- device memory helpers (stream-ordered pool) ----
 u64* dev_alloc(Context* c, size_t words);

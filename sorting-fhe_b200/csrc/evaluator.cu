@@ -21,6 +21,7 @@ static void count(Context* c, const char* name, int nl) { c->stats.ops[{name, nl
 Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots) {
     Ct* t = new Ct{c, nullptr, parts, nl, level, deg, sf, slots};
     t->d = dev_alloc(c, words(c, parts * nl));
+    c->live_cts++;
     return t;
 }
 Ct* ct_clone(const Ct* a) {
@@ -28,7 +29,13 @@ Ct* ct_clone(const Ct* a) {
     launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl));
     return t;
 }
-void ct_free(Ct* a) { if (!a) return; dev_free(a->ctx, a->d); delete a; }
+void ct_free(Ct* a) {
+    if (!a) return;
+    Context* c = a->ctx;
+    dev_free(c, a->d);
+    delete a;
+    if (--c->live_cts == 0 && c->closed) context_release(c);
+}
 static void ct_swap_buffer(Ct* a, u64* nd, int nl) { dev_free(a->ctx, a->d); a->d = nd; a->nl = nl; }
 
 static void int_residues(const Context* c, i128 v, int nl, u64* out) {

@@ -27,7 +27,13 @@ def test_sign_kat_and_parity():
     re, ro = sf.sign(eng, ce, (3, 0, 1)), algos.composite_sign(orc, co, 3, 0, 1)
     same(re, ro)
     got = eng.decrypt(re, 8)
-    assert np.all(np.abs(got - np.sign(x)) < 0.1), got
+    # the reference EXPECT_NEARs +-1 within 0.1 (SignTest.cpp:64-66); f_3(g_3(0.1)) = 0.788 in exact arithmetic, so
+    # that soft expectation cannot hold for the 0.1 entry -- the gate here is the plaintext polynomial + sign checks
+    odd7 = lambda v, c: c[0] * v + c[1] * v ** 3 + c[2] * v ** 5 + c[3] * v ** 7
+    want = odd7(odd7(x, algos.G3), algos.F3)
+    assert np.max(np.abs(got - want)) < 1e-6, got
+    assert np.all(np.sign(got[x != 0]) == np.sign(x[x != 0])) and abs(got[4]) < 0.1
+    assert np.all(np.abs(got - np.sign(x))[np.abs(x) >= 0.2] < 0.1)
     eng.close()
 
 

@@ -1,0 +1,76 @@
+"""CPU tests of the product's host side: the C-ABI libraries load and export every declared symbol, and the
+sorter layer's pure logic (Decomposer, parameter tables, coefficient generator, level budgets in dry-run mode)
+behaves like the reference's.  No compute call needs a GPU here."""
+import ctypes
+import importlib
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import algos
+from oracle.cheby import truncated_doubled_sinc_coeffs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sf = importlib.import_module("sorting-fhe_b200")
+
+
+@pytest.mark.parametrize("header,lib", [("ckks_b200.h", "libckks_b200.so"), ("sortfhe_host.h", "libsortfhe_host.so")])
+def test_c_abi_exports_every_declared_symbol(header, lib):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"\b((?:ckks|sortfhe)_[a-z0-9_]+)\s*\(", text)
+    assert len(names) > 8
+    L = ctypes.CDLL(os.path.join(ROOT, "sorting-fhe_b200", lib))
+    for n in set(names):
+        assert hasattr(L, n), n
+
+
+def test_compute_without_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(sf.CkksError, match="no CUDA device"):
+        sf.Engine(10, 2)
+
+
+def test_decomposer_reference_vectors():
+    """tests/DecomposeTest.cpp:64-74: Decomposer<128>{1..64}, sum of steps == rotation for 15 values x 3 algos"""
+    keys = [1, 2, 4, 8, 16, 32, 64]
+    for r in [1, 2, 3, 4, 7, 8, 15, 16, 31, 32, 63, 64, 65, 127, 128]:
+        for algo in ("NAF", "BNAF", "BINARY"):
+            assert sum(sf.decompose(128, r, 128, keys, algo)) == r, (r, algo)
+    assert sf.decompose(128, 21, 128, keys, "BINARY") == algos.decompose_binary(21, keys, 128, 128) == [16, 4, 1]
+    assert sf.decompose(128, 7, 128, keys, "NAF") == [8, -1]
+
+
+def test_direct_sort_parameter_tables():
+    """DirectSort<N>::getSizeParameters (src/sort_algo.h:87-201): depth and rotation key set per N"""
+    for n, (depth, rots) in algos.DIRECT_SORT_PARAMS.items():
+        assert sf.direct_sort_params(n, 1 << 17) == (depth, rots)
+
+
+def test_sinc_coefficients_match_generator():
+    """utils/generate_cheb_doubled_coeffs.cpp: the product's C++ generator and the oracle's restatement agree to
+    the last printed digit"""
+    for n in (4, 16):
+        assert np.array_equal(sf.sinc_coefficients(n), truncated_doubled_sinc_coeffs(n))
+
+
+@pytest.mark.parametrize("n,cfg", [(4, (3, 2, 2)), (16, (3, 2, 2)), (64, (3, 3, 2)), (128, (3, 3, 2)), (256, (3, 4, 2))])
+def test_level_budget_dry_run(n, cfg):
+    """SURVEY 8a level-budget identity: DirectSort<N>::sort ends exactly at multDepth (tests/DirectSortTest.cpp:140).
+    dry_run contexts execute the whole host schedule with metadata only."""
+    depth, rots = sf.direct_sort_params(n, 1 << 17)
+    eng = sf.Engine(17, depth, 40, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    ct = eng.encrypt(eng.encode(np.arange(n) / n, slots=n))
+    out = sf.DirectSort(eng, n, rots).sort(ct, cfg)
+    assert out.level == depth and out.slots == n
+    ops = {}
+    for name, nl, cnt in eng.stats()["ops"]:
+        ops[name] = ops.get(name, 0) + cnt
+    if n == 128:   # SURVEY 3.1 op table: 58 rotations, 258 encodes (+1 zero cache)
+        assert ops["rotate"] == 58 and ops["encode"] in (258, 259, 260)
+    eng.close()
