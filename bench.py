@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- DirectSort N=128 end-to-end sort latency on B200 (BASELINE.json metric), one process per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n 128] [--log-n 17]
+
+A "step" is one DirectSort<N>::sort of one encrypted array (reference src/sort_algo.h:752-774) at the
+reference's parameter card: ring 2^17, multDepth 30, 40-bit scaling, Sign(3,3,2), 30 rotation keys
+(src/sort_algo.h:117-123, tests/DirectSortTest.cpp:29-44,116-117).  `value` times K steps with the input
+ciphertexts already resident in HBM; `e2e` times the same K steps through the C-ABI with HOST buffers
+(ckks_ct_import from pinned memory -> sortfhe_direct_sort -> ckks_ct_export).  With N GPUs every rank sorts its
+own arrays (replicas, no data-path collective: SURVEY 8e) and `value` is seconds per sort over the whole job.
+`--impl reference` times the CPU arm (the oracle port of the same op sequence, OpenMP on the host cores).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "DirectSort N=128 end-to-end sort latency (s)"
+SIGN_CFG = {4: (3, 2, 2), 8: (3, 2, 2), 16: (3, 2, 2), 32: (3, 3, 2), 64: (3, 3, 2), 128: (3, 3, 2), 256: (3, 4, 2)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--n", type=int, default=128)
+    ap.add_argument("--log-n", type=int, default=17)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_op_times(log_n, depth, nls, reps=1, slots=16384):
+    """Time the ORACLE's ops (the CPU restatement: oracle/ckks_ops.py over oracle/ckks_fast.c, OpenMP) at the
+    bench parameters for a few limb counts.  Returns {op: {nl: seconds}} and the thread count used."""
+    from oracle.ckks_eval import Ct
+    from oracle.ckks_oracle import Context, Params
+    from oracle.ckks_ops import OracleCC
+    cc = OracleCC(Context(Params(log_n, depth, 40)))
+    cc.keygen(); cc.relin_keygen(); cc.rot_keygen([1])
+    c = cc.ctx
+    rng = np.random.default_rng(0)
+    out = {k: {} for k in ("mult", "rotate", "rescale", "mult_pt", "add", "encode")}
+
+    def best(fn):
+        ts = []
+        for _ in range(reps):
+            t = time.perf_counter(); fn(); ts.append(time.perf_counter() - t)
+        return min(ts)
+
+    for nl in nls:
+        lvl = c.size_q - nl
+        mk = lambda parts: Ct(np.stack([np.stack([rng.integers(0, c.q[i], c.n, dtype=np.uint64) for i in range(nl)])
+                                        for _ in range(parts)]), lvl, 1, c.sf_real[lvl], slots)
+        a, b, p = mk(2), mk(2), mk(1)
+        out["mult"][nl] = best(lambda: cc.EvalMult(a, b))          # tensor + hybrid key switch (no rescale: deg 1)
+        out["rotate"][nl] = best(lambda: cc.EvalRotate(a, 1))      # hybrid key switch + automorphism
+        out["mult_pt"][nl] = best(lambda: cc.EvalMult(a, p))
+        out["add"][nl] = best(lambda: cc.EvalAdd(a, b))
+        if nl >= 2:
+            out["rescale"][nl] = best(lambda: cc.rescale(a.clone()))
+        vals = rng.random(slots)
+        out["encode"][nl] = best(lambda: cc.encode(vals, 1, lvl, slots))
+    return out, (os.cpu_count() if "OMP_NUM_THREADS" not in os.environ else int(os.environ["OMP_NUM_THREADS"]))
+
+
+def cpu_estimate(trace, times):
+    """seconds of CPU work for an op trace [(name, nl, count)], piecewise-linear in nl between the sampled points"""
+    total, used = 0.0, 0
+    for name, nl, cnt in trace:
+        if name not in times or not times[name]:
+            continue   # 'keyswitch' is contained in mult / rotate
+        xs = sorted(times[name]); ys = [times[name][x] for x in xs]
+        total += cnt * float(np.interp(nl, xs, ys))
+        used += cnt
+    return total, used
+
+
+def dry_trace(n, log_n, cfg):
+    """op trace of one sort from a metadata-only (dry_run) engine context: no GPU needed"""
+    sf = importlib.import_module("sorting-fhe_b200")
+    depth, rots = sf.direct_sort_params(n, 1 << log_n)
+    eng = sf.Engine(log_n, depth, 40, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    ct = eng.encrypt(eng.encode(np.arange(n) / n, slots=n))
+    eng.stats(reset=True)
+    sf.DirectSort(eng, n, rots).sort(ct, cfg)
+    tr = [tuple(x) for x in eng.stats()["ops"]]
+    eng.close()
+    return depth, tr
+
+
+def cpu_baseline(n, log_n, cfg, trace=None, reps=1):
+    depth = None
+    if trace is None:
+        depth, trace = dry_trace(n, log_n, cfg)
+    sf = importlib.import_module("sorting-fhe_b200")
+    depth = depth or sf.direct_sort_params(n, 1 << log_n)[0]
+    size_q = depth + 2
+    nls = sorted({size_q, max(2, (size_q * 2) // 3), max(2, size_q // 3), 2})
+    t0 = time.perf_counter()
+    times, cores = cpu_op_times(log_n, depth, nls, reps=reps, slots=min(n * n, (1 << log_n) // 2))
+    est, used = cpu_estimate(trace, times)
+    return {"value": est, "unit": "s", "cores": cores, "kind": "port",
+            "sample": "oracle (CPU restatement, OpenMP) ops mult+relin / rotate / rescale / ct*pt / add / encode timed at "
+                      "limb counts %s on the bench parameters (%.1f s of CPU work), piecewise-linear in the limb count, "
+                      "summed over the %d ops of one sort's op trace" % (nls, time.perf_counter() - t0, round(used))}
+
+
+def run_reference(args):
+    """--impl reference: the CPU arm.  OpenFHE 1.1.4 (the reference's arithmetic) is an un-vendored dependency that
+    cannot be built here, so the arm is the oracle port on all host threads; each step is the bounded
+    op sample of cpu_baseline()."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = SIGN_CFG[args.n]
+    depth, trace = dry_trace(args.n, args.log_n, cfg)
+    vals = []
+    for _ in range(max(1, min(args.steps, 3))):
+        vals.append(cpu_baseline(args.n, args.log_n, cfg, trace))
+    cb = min(vals, key=lambda d: d["value"])
+    v = cb["value"]
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "DirectSort N=%d, ring 2^%d, depth %d, Sign%s" % (args.n, args.log_n, depth, str(cfg)),
+                   "arm": "CPU oracle port (OpenFHE 1.1.4 unavailable offline)"},
+        "cpu_baseline": cb, "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    sf = importlib.import_module("sorting-fhe_b200")   # fails loudly if the CUDA extension is not built
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the engine has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n, log_n, cfg = args.n, args.log_n, SIGN_CFG[args.n]
+    K, W = args.steps, args.warmup
+    depth, rots = sf.direct_sort_params(n, 1 << log_n)
+    stream = torch.cuda.Stream()
+    eng = sf.Engine(log_n, depth, 40, seed=1 + rank, stream=stream.cuda_stream)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    sorter = sf.DirectSort(eng, n, rots)
+    rng = np.random.default_rng(100 + rank)
+    arrays = [rng.permutation(n) / n for _ in range(max(K, 1))]      # tests/utils.h:28-50 with (N, 0, 1, 1/N)
+    cts = [eng.encrypt(eng.encode(a, slots=n)) for a in arrays]
+    meta = (cts[0].parts, cts[0].nlimbs, cts[0].level, cts[0].deg, cts[0].sf, n)
+    words_in = cts[0].parts * cts[0].nlimbs * eng.n
+    host_in = [torch.empty(words_in, dtype=torch.int64).pin_memory() for _ in cts]
+    for h, c in zip(host_in, cts):
+        eng.export_ct_ptr(c, h.data_ptr(), words_in)
+    key_bytes = eng.info(7)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):                                   # warm-up (also fills the stream-ordered memory pool)
+        out = sorter.sort(cts[i % len(cts)], cfg)
+    eng.sync()
+
+    # ---- timed region 1: inputs resident in HBM
+    eng.stats(reset=True)
+    eng.profile_enable(["ntt"])
+    eng.profile()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    outs = []
+    for i in range(K):
+        cts[i].slots = n                                 # sort() widens the caller's metadata (sort_algo.h:711)
+        outs.append(sorter.sort(cts[i], cfg))
+    e1.record(stream)
+    barrier()
+    t_dev = e0.elapsed_time(e1) / 1e3
+    clocks = sampler.stop()
+    prof_ntt = eng.profile()["ntt"]
+    eng.profile_enable([])
+    st = eng.stats(reset=True)
+    launches = st["kernel_launches"]
+    trace = [(nm, nl, cnt / K) for nm, nl, cnt in st["ops"]]          # ops of ONE sort
+
+    # ---- correctness of what was timed
+    errs = [float(np.max(np.abs(eng.decrypt(o, n) - np.sort(a)))) for o, a in zip(outs, arrays)]
+    out_words = outs[0].parts * outs[0].nlimbs * eng.n
+    host_out = torch.empty(out_words, dtype=torch.int64).pin_memory()
+    del outs
+
+    # ---- timed region 2: end to end through the C-ABI with host buffers
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        c = eng.import_ct_ptr(host_in[i].data_ptr(), *meta)           # H2D inside the timed region
+        o = sorter.sort(c, cfg)
+        eng.export_ct_ptr(o, host_out.data_ptr(), out_words)          # D2H + stream sync
+    barrier()
+    t_e2e = time.perf_counter() - t0
+
+    # ---- one extra (untimed) step with every kernel class timed: the step's breakdown
+    eng.profile_enable(None); eng.profile()
+    cts[0].slots = n
+    sorter.sort(cts[0], cfg)
+    breakdown = eng.profile()
+    eng.profile_enable([])
+
+    tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_dev, t_e2e = float(tt[0]), float(tt[1])
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        dom = max(breakdown, key=lambda k: breakdown[k]["ms"])
+        ach = prof_ntt["bytes"] / max(prof_ntt["ms"], 1e-9) / 1e6     # GB/s over the timed region's NTT launches
+        total_ms = sum(v["ms"] for v in breakdown.values())
+        line = {
+            "metric": METRIC, "value": t_dev / (K * world), "unit": "s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": t_dev / K * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "DirectSort N=%d (Optimized Rank Sort), ring 2^%d, multDepth %d, scaling 40 bit, "
+                                   "Sign%s, %d rotation keys" % (n, log_n, depth, str(cfg), len(rots)),
+                       "parallelism": "replicas: one independent sort per GPU per step" if world > 1 else "single GPU",
+                       "l2": "working set (%.1f GB of evaluation keys streamed per sort) exceeds the 126 MB L2" % (key_bytes / 1e9),
+                       "max_abs_err": max(errs), "size_q": eng.size_q, "size_p": eng.size_p, "dnum": eng.num_part_q},
+            "e2e": {"value": t_e2e / (K * world), "unit": "s", "h2d_bytes_per_step": words_in * 8,
+                    "d2h_bytes_per_step": out_words * 8},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "ntt_kernel (all NTT/INTT launches of the timed region)",
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "peak_source": peak_src, "launches": prof_ntt["launches"],
+                         "avg_launch_us": prof_ntt["ms"] * 1e3 / max(prof_ntt["launches"], 1),
+                         "share_of_step": breakdown["ntt"]["ms"] / max(total_ms, 1e-9), "dominant_class": dom},
+            "breakdown_ms": {k: round(v["ms"], 3) for k, v in breakdown.items()},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(n, log_n, cfg, trace)
+        print(json.dumps(line))
+    del cts, sorter
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -101,6 +101,13 @@ int ckks_eval_poly_linear(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coe
 int ckks_stats_json(ckks_ctx_t* ctx, char* buf, size_t cap);
 int ckks_stats_reset(ckks_ctx_t* ctx);
 
+/* per-kernel-class device timing (CUDA events on the engine stream around every launch of the selected
+ * classes).  class bits: 0 ntt, 1 base conversion, 2 evk inner product, 3 mod-down epilogue, 4 pointwise,
+ * 5 rescale, 6 automorphism, 7 encode, 8 copies.  ckks_profile_json synchronises, returns the totals
+ * {"class": [ms, launches, algorithmic_bytes], ...} accumulated since the last call, and clears them. */
+int ckks_profile_enable(ckks_ctx_t* ctx, unsigned class_mask);
+int ckks_profile_json(ckks_ctx_t* ctx, char* buf, size_t cap);
+
 /* kernel-level entry points on raw buffers, for parity tests and kernel benchmarks.
  * *_host variants stage through host memory; *_dev variants take device pointers. */
 int ckks_ntt_host(ckks_ctx_t* ctx, uint64_t* data, int rows, const int32_t* modulus_ids, int inverse);

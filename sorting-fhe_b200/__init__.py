@@ -150,6 +150,19 @@ class Engine:
             _chk(_L.ckks_stats_reset(_vp(self.h)))
         return json.loads(buf.value.decode())
 
+    KCLASSES = ["ntt", "baseconv", "ks_inner", "moddown", "pointwise", "rescale", "automorph", "encode", "copy"]
+
+    def profile_enable(self, classes=None):
+        """CUDA-event timing of kernel classes (None = all, [] = off)"""
+        mask = sum(1 << self.KCLASSES.index(k) for k in (self.KCLASSES if classes is None else classes))
+        _chk(_L.ckks_profile_enable(_vp(self.h), ctypes.c_uint(mask)))
+
+    def profile(self):
+        """{class: {"ms", "launches", "bytes"}} since the last call"""
+        buf = ctypes.create_string_buffer(1 << 16)
+        _chk(_L.ckks_profile_json(_vp(self.h), buf, len(buf)))
+        return {k: {"ms": v[0], "launches": int(v[1]), "bytes": v[2]} for k, v in json.loads(buf.value.decode()).items()}
+
     # ---- keys
     def KeyGen(self):
         _chk(_L.ckks_keygen(_vp(self.h)))
@@ -212,6 +225,15 @@ class Engine:
         o = ctypes.c_void_p()
         return self._out(_L.ckks_ct_import(_vp(self.h), _u64p(arr), arr.shape[0], arr.shape[1], level, deg, _d(sf), slots,
                                            ctypes.byref(o)), o)
+
+    def import_ct_ptr(self, host_ptr, polys, limbs, level, deg, sf, slots):
+        """ckks_ct_import from a raw host pointer (e.g. a pinned torch tensor's data_ptr())"""
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_ct_import(_vp(self.h), ctypes.cast(host_ptr, ctypes.POINTER(ctypes.c_uint64)), polys, limbs,
+                                           level, deg, _d(sf), slots, ctypes.byref(o)), o)
+
+    def export_ct_ptr(self, ct, host_ptr, cap_words):
+        _chk(_L.ckks_ct_export(_vp(ct.h), ctypes.cast(host_ptr, ctypes.POINTER(ctypes.c_uint64)), cap_words))
 
     # ---- evaluation (OpenFHE names)
     def _bin(self, f, a, b):
@@ -298,6 +320,8 @@ _L.ckks_export_secret.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c
 _L.ckks_export_public_key.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
 _L.ckks_export_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
 _L.ckks_import_eval_key.argtypes = [_vp, _i, ctypes.c_int32, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
+_L.ckks_profile_json.argtypes = [_vp, ctypes.c_char_p, ctypes.c_size_t]
+_L.ckks_profile_enable.argtypes = [_vp, ctypes.c_uint]
 _L.ckks_stats_json.argtypes = [_vp, ctypes.c_char_p, ctypes.c_size_t]
 
 

@@ -297,6 +297,34 @@ int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
 }
 int ckks_stats_reset(ckks_ctx_t* x) { API_BEGIN C(x)->stats = Stats(); API_END }
 
+int ckks_profile_enable(ckks_ctx_t* x, unsigned mask) {
+    API_BEGIN
+    Context* c = C(x);
+    prof_collect(c);
+    c->prof.mask = mask;
+    API_END
+}
+int ckks_profile_json(ckks_ctx_t* x, char* buf, size_t cap) {
+    API_BEGIN
+    Context* c = C(x);
+    prof_collect(c);
+    static const char* names[KC_COUNT] = {"ntt", "baseconv", "ks_inner", "moddown", "pointwise", "rescale", "automorph",
+                                          "encode", "copy"};
+    std::ostringstream os;
+    os.precision(17);
+    os << "{";
+    for (int i = 0; i < KC_COUNT; i++) {
+        os << (i ? ", " : "") << "\"" << names[i] << "\": [" << c->prof.ms[i] << ", " << c->prof.launches[i] << ", "
+           << c->prof.bytes[i] << "]";
+        c->prof.ms[i] = 0; c->prof.launches[i] = 0; c->prof.bytes[i] = 0;
+    }
+    os << "}";
+    std::string s = os.str();
+    if (s.size() + 1 > cap) throw std::runtime_error("profile_json: buffer too small");
+    memcpy(buf, s.c_str(), s.size() + 1);
+    API_END
+}
+
 int ckks_ntt_host(ckks_ctx_t* x, uint64_t* data, int rows, const int32_t* mod_ids, int inverse) {
     API_BEGIN
     Context* c = C(x);

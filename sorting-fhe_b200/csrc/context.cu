@@ -212,3 +212,28 @@ const KsTables& get_ks_tables(Context* c, int nl) {
     t.d_pinv = upload(c, pinv); t.d_pinv_sh = upload(c, pinv_sh);
     return c->ks.emplace(nl, std::move(t)).first->second;
 }
+
+// ---- per-class kernel timing ----
+static cudaEvent_t prof_event(Context* c) {
+    if (!c->prof.pool.empty()) { cudaEvent_t e = c->prof.pool.back(); c->prof.pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+ProfScope::ProfScope(Context* c_, int cls, double alg_bytes, int nlaunch) : c(c_) {
+    if (c->dry || !(c->prof.mask & (1u << cls))) return;
+    c->prof.bytes[cls] += alg_bytes; c->prof.launches[cls] += nlaunch;
+    ProfRec r{cls, prof_event(c), prof_event(c)};
+    cudaEventRecord(r.e0, c->stream);
+    idx = (int)c->prof.pending.size();
+    c->prof.pending.push_back(r);
+}
+ProfScope::~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof.pending[idx].e1, c->stream); }
+void prof_collect(Context* c) {
+    if (c->dry) return;
+    cudaStreamSynchronize(c->stream);
+    for (auto& r : c->prof.pending) {
+        float ms = 0; cudaEventElapsedTime(&ms, r.e0, r.e1);
+        c->prof.ms[r.cls] += ms;
+        c->prof.pool.push_back(r.e0); c->prof.pool.push_back(r.e1);
+    }
+    c->prof.pending.clear();
+}

@@ -82,6 +82,7 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
     double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
     double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
     std::vector<double> h(2 * (size_t)slots, 0.0);
+    ProfScope ps(c, KC_ENCODE, 8.0 * c->n * nl, bits + 2);
     for (int i = 0; i < nvals; i++) h[2 * i] = h_values[i];
     cudaMemcpyAsync(a, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream);
     cudaStreamSynchronize(c->stream);  // h is a stack-lifetime staging buffer

@@ -41,6 +41,18 @@ struct EvalKey {           // hybrid evk: [part][2 (b, a)][sizeQ+sizeP][n], Mont
     int nparts = 0;
 };
 
+// kernel classes for the per-class device timing bench.py reports (roofline object)
+enum KClass { KC_NTT = 0, KC_BASECONV, KC_KSINNER, KC_MODDOWN, KC_POINTWISE, KC_RESCALE, KC_AUTOMORPH, KC_ENCODE, KC_COPY,
+              KC_COUNT };
+struct ProfRec { int cls; cudaEvent_t e0, e1; };
+struct Prof {
+    unsigned mask = 0;                       // bit per KClass; 0 = profiling off
+    std::vector<ProfRec> pending;
+    std::vector<cudaEvent_t> pool;
+    double ms[KC_COUNT] = {0}, bytes[KC_COUNT] = {0};
+    long launches[KC_COUNT] = {0};
+};
+
 struct Stats { std::map<std::pair<std::string, int>, long> ops; long kernel_launches = 0; };
 
 struct Context {
@@ -67,6 +79,7 @@ struct Context {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     Stats stats;
+    Prof prof;
     std::string last_error;
     // handle lifetime: ciphertexts may outlive ckks_ctx_destroy (shared_ptr / Python GC order); the context is
     // torn down when it is closed AND the last ciphertext handle is gone
@@ -84,7 +97,14 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     int slots;
 };
 
-void context_release(Context* c);   // capi.cu: free device tables + delete (called once closed && live_cts == 0)
+void context_release(Context* c);
+// RAII scope around the launches of one kernel class: CUDA events on the engine stream when that class is profiled
+struct ProfScope {
+    Context* c; int idx = -1;
+    ProfScope(Context* c, int cls, double alg_bytes, int nlaunch = 1);
+    ~ProfScope();
+};
+void prof_collect(Context* c);   // synchronises and folds pending event pairs into Prof::ms   // capi.cu: free device tables + delete (called once closed && live_cts == 0)
 
 // ---- device memory helpers (stream-ordered pool) ----
 u64* dev_alloc(Context* c, size_t words);

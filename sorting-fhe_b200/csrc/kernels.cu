@@ -31,7 +31,7 @@ __global__ void k_addsub(u64* out, const u64* a, const u64* b, LimbMods mods, co
     out[o] = op == 0 ? add_mod(a[o], b[o], q) : sub_mod(a[o], b[o], q);
 }
 void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op) {
-    KL(c); k_addsub<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, op);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows * c->n); k_addsub<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, op);
 }
 
 __global__ void k_neg(u64* out, const u64* a, LimbMods mods, const ModInfo* mi, int n) {
@@ -40,7 +40,7 @@ __global__ void k_neg(u64* out, const u64* a, LimbMods mods, const ModInfo* mi, 
     size_t o = (size_t)row * n + x; out[o] = neg_mod(a[o], q);
 }
 void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m) {
-    KL(c); k_neg<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, m, c->d_mod, c->n);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n); k_neg<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, m, c->d_mod, c->n);
 }
 
 __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b) {
@@ -50,7 +50,7 @@ __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const
     out[o] = barrett_mul(a[o], b[ob], m);
 }
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m) {
-    KL(c); k_mul<<<grid_for(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows_out * c->n); k_mul<<<grid_for(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
 }
 
 __global__ void k_mul_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
@@ -59,7 +59,7 @@ __global__ void k_mul_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, Li
     size_t o = (size_t)row * n + x; d[o] = shoup_mul(d[o], s.v[l], s.sh[l], q);
 }
 void launch_mul_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
-    KL(c);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
     k_mul_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
@@ -71,7 +71,7 @@ __global__ void k_add_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, Li
     size_t o = (size_t)row * n + x; d[o] = add_mod(d[o], s.v[l], q);
 }
 void launch_add_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
-    KL(c);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
     k_add_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
@@ -88,7 +88,7 @@ __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi,
     d3[o + 2 * P] = barrett_mul(a1, b1, m);
 }
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl) {
-    KL(c); k_tensor<<<grid_for(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 56.0 * nl * c->n); k_tensor<<<grid_for(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
 }
 
 // out[p] = in[brev(idx)], j = brev(p), idx = ((2j+1)k mod 2n) >> 1  (PrecomputeAutoMap)
@@ -102,7 +102,7 @@ __global__ void k_automorph(u64* out, const u64* in, int n, int logn, u32 k) {
     out[ro + p] = in[ro + src];
 }
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k) {
-    KL(c); k_automorph<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, c->log_n, k);
+    KL(c); ProfScope ps(c, KC_AUTOMORPH, 16.0 * rows * c->n); k_automorph<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, c->log_n, k);
 }
 
 // rescale: t[p][i] = centred switch of last[p] (coefficient format, mod q_last) to q_i
@@ -115,7 +115,7 @@ __global__ void k_rescale_prep(u64* t, const u64* last, const ModInfo* mi, int n
     t[(size_t)row * n + x] = r;
 }
 void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod) {
-    KL(c); k_rescale_prep<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(t, last, c->d_mod, c->n, nl_out, last_mod);
+    KL(c); ProfScope ps(c, KC_RESCALE, 8.0 * c->n * parts * (nl_out + 1)); k_rescale_prep<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(t, last, c->d_mod, c->n, nl_out, last_mod);
 }
 // out[p][i] = (in[p][i] - t[p][i]) * q_last^-1 mod q_i ; in has nl_in = nl_out + 1 limbs per part
 __global__ void k_rescale_final(u64* out, const u64* in, const u64* t, const ModInfo* mi, int n, int nl_out, LimbScalars s) {
@@ -131,14 +131,14 @@ static u64 host_powmod(u64 a, u64 e, u64 q) {
     return (u64)r;
 }
 void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in) {
-    KL(c);
+    KL(c); ProfScope ps(c, KC_RESCALE, 8.0 * c->n * parts * (3.0 * nl_in - 3));
     LimbScalars s; int nl_out = nl_in - 1; u64 ql = c->moduli[nl_in - 1];
     for (int i = 0; i < nl_out; i++) { u64 q = c->moduli[i]; s.v[i] = host_powmod(ql % q, q - 2, q); s.sh[i] = host_shoup(s.v[i], q); }
     k_rescale_final<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(out, in, t, c->d_mod, c->n, nl_out, s);
 }
 
 void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words) {
-    KL(c); cudaMemcpyAsync(dst, src, words * sizeof(u64), cudaMemcpyDeviceToDevice, c->stream);
+    KL(c); ProfScope ps(c, KC_COPY, 16.0 * words); cudaMemcpyAsync(dst, src, words * sizeof(u64), cudaMemcpyDeviceToDevice, c->stream);
 }
 
 __global__ void k_mont(u64* d, LimbMods mods, const ModInfo* mi, int n, int to) {

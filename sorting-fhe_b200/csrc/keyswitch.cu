@@ -38,6 +38,7 @@ k_base_conv(u64* __restrict__ out, const u64* __restrict__ in, ConvIds ids, int 
 }
 void launch_base_conv(Context* c, u64* out, const u64* in, const ConvTables& t) {
     KL(c);
+    ProfScope ps(c, KC_BASECONV, 8.0 * c->n * (t.nin + t.nout));
     ConvIds ids;
     for (int i = 0; i < t.nin; i++) ids.in_ids[i] = t.in_ids[i];
     for (int j = 0; j < t.nout; j++) ids.out_ids[j] = t.out_ids[j];
@@ -74,6 +75,7 @@ k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __rest
 }
 void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, const EvalKey& k, const KsTables& t) {
     KL(c);
+    ProfScope ps(c, KC_KSINNER, 8.0 * c->n * (t.nl + c->size_p) * (3.0 * t.nparts + 2));
     DigitMap dm;
     for (int j = 0; j < 4; j++) { dm.lo[j] = j < t.nparts ? t.dig_lo[j] : 0; dm.hi[j] = j < t.nparts ? t.dig_hi[j] : 0; }
     dim3 grid((c->n + 255) / 256, t.nl + c->size_p);
@@ -95,6 +97,7 @@ void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv,
                           int acc_stride_limbs, const KsTables& t) {
     (void)acc_stride_limbs;
     KL(c);
+    ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (addend ? 4 : 3));
     dim3 grid((c->n + 255) / 256, nl);
     k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, addend, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n);
 }

@@ -133,6 +133,7 @@ ntt_kernel(u64* __restrict__ data, LimbMods mods, const ModInfo* __restrict__ mo
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse) {
     c->stats.kernel_launches += (c->log_n > TB_MAX) ? 2 : 1;
     if (c->dry || rows == 0) return;
+    ProfScope ps(c, KC_NTT, 16.0 * rows * c->n, (c->log_n > TB_MAX) ? 2 : 1);
     const int logn = c->log_n, tb = logn < TB_MAX ? logn : TB_MAX, s1 = logn - tb;
     const int threads = (1 << tb) / 8;
     const size_t smem = (size_t)((1 << tb) + ((1 << tb) >> 3) + 8) * sizeof(u64);
