@@ -36,7 +36,7 @@ static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_err
 void context_release(Context* c) {
     if (!c->dry) {
         cudaStreamSynchronize(c->stream);
-        cudaFree(c->d_mod); cudaFree(c->d_psi); cudaFree(c->d_psi_sh); cudaFree(c->d_ipsi); cudaFree(c->d_ipsi_sh);
+        cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
         for (auto& kv : c->ks) {
             for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); }
@@ -240,10 +240,7 @@ int ckks_eval_add_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t**
 int ckks_eval_sub_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add_const(G(a), -v)); API_END }
 int ckks_eval_const_sub(ckks_ctx_t* x, double v, const ckks_ct_t* a, ckks_ct_t** out) {
     API_BEGIN (void)C(x);
-    Ct* n = eval_negate(G(a));
-    Ct* r = eval_add_const(n, v);
-    ct_free(n);
-    *out = box(r);
+    *out = box(eval_const_sub(v, G(a)));
     API_END
 }
 int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_negate(G(a))); API_END }
@@ -352,7 +349,7 @@ int ckks_key_switch_dev(ckks_ctx_t* x, const void* src, int limbs, int is_rot, i
     Context* c = C(x);
     EvalKey* k = find_key(c, is_rot, index, false);
     if (!k) throw std::runtime_error("key_switch_dev: key not present");
-    key_switch(c, (const u64*)src, limbs, *k, (u64*)out, nullptr, nullptr);
+    key_switch(c, (const u64*)src, limbs, *k, (u64*)out, nullptr, nullptr, 0);
     API_END
 }
 }  // extern "C"

@@ -132,21 +132,24 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
     // per-modulus info + twiddles
     const int M = c->M(), n = c->n;
     c->h_mod.resize(M); c->psi.resize(M);
-    std::vector<u64> tw((size_t)M * n), tws((size_t)M * n), itw((size_t)M * n), itws((size_t)M * n);
+    std::vector<u64> tw((size_t)2 * M * n), itw((size_t)2 * M * n), ninvp((size_t)2 * M);
     for (int i = 0; i < M; i++) {
         u64 qi = c->moduli[i]; ModInfo& mi = c->h_mod[i];
         mi.q = qi; mi.bits = bitlen(qi); mi.pad = 0;
+        mi.qrecip = (u64)((((u128)1) << 64) / qi);
         mi.mu = (u64)((((u128)1) << (2 * mi.bits)) / qi);
         u64 inv = 1; for (int k = 0; k < 6; k++) inv *= 2 - qi * inv;   // Newton: q^-1 mod 2^64
         mi.qinv = inv;
         u64 r = (u64)((((u128)1) << 64) % qi); mi.r2 = mulmod(r, r, qi);
         mi.ninv = invmod(n % qi, qi); mi.ninv_sh = shoup(mi.ninv, qi);
+        ninvp[2 * i] = mi.ninv; ninvp[2 * i + 1] = mi.ninv_sh;
         u64 psi = min_root(m, qi), ipsi = invmod(psi, qi); c->psi[i] = psi;
         u64 x = 1, y = 1;
         for (int k = 0; k < n; k++) {
             uint32_t b = brev(k, log_n);
-            tw[(size_t)i * n + b] = x; tws[(size_t)i * n + b] = shoup(x, qi);
-            itw[(size_t)i * n + b] = y; itws[(size_t)i * n + b] = shoup(y, qi);
+            const size_t o = 2 * ((size_t)i * n + b);
+            tw[o] = x; tw[o + 1] = shoup(x, qi);
+            itw[o] = y; itw[o + 1] = shoup(y, qi);
             x = mulmod(x, psi, qi); y = mulmod(y, ipsi, qi);
         }
     }
@@ -156,7 +159,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) { uint64_t thr = UINT64_MAX; cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr); }
     }
     c->d_mod = upload(c, c->h_mod);
-    c->d_psi = upload(c, tw); c->d_psi_sh = upload(c, tws); c->d_ipsi = upload(c, itw); c->d_ipsi_sh = upload(c, itws);
+    c->d_tw = upload(c, tw); c->d_itw = upload(c, itw); c->d_ninv_pairs = upload(c, ninvp);
     // special FFT tables (same expressions as oracle Context.fft_tables)
     const int Mc = 2 * n;
     std::vector<double> ksi(2 * (size_t)(Mc + 1));

@@ -66,7 +66,8 @@ struct Context {
     // device tables
     ModInfo* d_mod = nullptr;               // [M]
     std::vector<ModInfo> h_mod;
-    u64 *d_psi = nullptr, *d_psi_sh = nullptr, *d_ipsi = nullptr, *d_ipsi_sh = nullptr;  // [M][n]
+    u64 *d_tw = nullptr, *d_itw = nullptr;   // [M][n] (w, Shoup companion) pairs: psi / psi^-1 powers, bit-reversed
+    u64* d_ninv_pairs = nullptr;             // [M] (n^-1, Shoup companion): default final factor of the inverse NTT
     double* d_ksi = nullptr;                // [2n+1] complex roots for the special FFT
     uint32_t* d_rot = nullptr;              // [n/2] 5^j mod 2n
     std::map<int, KsTables> ks;             // keyed by nl
@@ -95,6 +96,7 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     int level, deg;
     double sf;
     int slots;
+    mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
 };
 
 void context_release(Context* c);
@@ -115,19 +117,26 @@ LimbMods mods_q(int nl);                          // Q limbs 0..nl-1
 LimbMods mods_qp(const Context* c, int nl);       // Q limbs 0..nl-1 then all P limbs
 LimbMods mods_range(int lo, int hi);              // moduli lo..hi-1
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse);
+// out-of-place capable form; scale_pairs (inverse only): [M] (factor, Shoup) pairs indexed by modulus id that
+// replace the n^-1 factor (nullptr = n^-1)
+void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs);
 
 void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op /*0 add 1 sub*/);
 void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m);
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m);
-void launch_mul_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/);
-void launch_add_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* h_scalars);
+void launch_mul_scalar(Context* c, u64* out, const u64* in, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/);
+// out[0] = (negate ? -in[0] : in[0]) + s ; out[p>0] = (negate ? -in[p] : in[p])
+void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* h_scalars, bool negate);
+// out[p] = (p < xparts ? x[p] : 0) +- (p < yparts ? y[p] : 0), p < max(xparts, yparts)
+void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub);
+void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in);
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
 void launch_base_conv(Context* c, u64* out, const u64* in, const ConvTables& t);
 void launch_ks_inner2(Context* c, u64* acc /*[2][nl+K][n]*/, const u64* src, const u64* conv, const EvalKey& k,
                       const KsTables& t);
 void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* addend, int nl,
-                          int acc_stride_limbs, const KsTables& t);
+                          uint32_t auto_k, const KsTables& t);
 void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod);
 void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in);
 void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words);

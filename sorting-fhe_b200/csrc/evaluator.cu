@@ -29,108 +29,153 @@ Ct* ct_clone(const Ct* a) {
     launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl));
     return t;
 }
+static void drop_twin(const Ct* a) { if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); } }
 void ct_free(Ct* a) {
     if (!a) return;
     Context* c = a->ctx;
+    drop_twin(a);
     dev_free(c, a->d);
     delete a;
     if (--c->live_cts == 0 && c->closed) context_release(c);
 }
-static void ct_swap_buffer(Ct* a, u64* nd, int nl) { dev_free(a->ctx, a->d); a->d = nd; a->nl = nl; }
+// a takes over t's buffer and metadata (t is consumed)
+static void ct_steal(Ct* a, Ct* t) {
+    drop_twin(a);
+    dev_free(a->ctx, a->d);
+    a->d = t->d; a->parts = t->parts; a->nl = t->nl; a->level = t->level; a->deg = t->deg; a->sf = t->sf;
+    a->resc = t->resc; t->resc = nullptr;
+    t->d = nullptr;
+    ct_free(t);
+}
 
 static void int_residues(const Context* c, i128 v, int nl, u64* out) {
     for (int i = 0; i < nl; i++) { i128 q = (i128)c->moduli[i]; i128 r = v % q; if (r < 0) r += q; out[i] = (u64)r; }
 }
 
-// EvalMultCoreInPlace(ct, double)
-void mult_core_const(Ct* a, double x) {
-    Context* c = a->ctx;
-    double sf = c->sf_real[a->level];
-    i128 v = (i128)(x * sf + 0.5);
-    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
-    launch_mul_scalar(c, a->d, a->parts * a->nl, mods_q(a->nl), s);
-    a->deg += 1; a->sf *= sf;
-}
-
-// ModReduceInternalInPlace -> DropLastElementAndScale
-void rescale(Ct* a) {
-    Context* c = a->ctx; int nl = a->nl, parts = a->parts;
+// ModReduceInternal -> DropLastElementAndScale, out of place
+static Ct* rescale_new(const Ct* a) {
+    Context* c = a->ctx; const int nl = a->nl, parts = a->parts;
     if (nl < 2) throw std::runtime_error("rescale: no limb left to drop (multiplicative depth exhausted)");
     count(c, "rescale", nl);
-    u64* last = dev_alloc(c, words(c, parts));
-    for (int p = 0; p < parts; p++) launch_copy_rows(c, c->dry ? nullptr : last + words(c, p), c->dry ? nullptr : a->d + words(c, p * nl + nl - 1), c->n);
-    launch_ntt(c, last, parts, mods_range(nl - 1, nl), true);
-    u64* t = dev_alloc(c, words(c, parts * (nl - 1)));
-    launch_rescale_prep(c, t, last, parts, nl - 1, nl - 1);
-    launch_ntt(c, t, parts * (nl - 1), mods_q(nl - 1), false);
-    u64* out = dev_alloc(c, words(c, parts * (nl - 1)));
-    launch_rescale_final(c, out, a->d, t, parts, nl);
-    dev_free(c, last); dev_free(c, t);
-    double ql = (double)c->moduli[nl - 1];
-    ct_swap_buffer(a, out, nl - 1);
-    a->level += 1; a->deg -= 1; a->sf /= ql;
+    Ct* out = ct_new(c, parts, nl - 1, a->level + 1, a->deg - 1, a->sf / (double)c->moduli[nl - 1], a->slots);
+    launch_rescale(c, out->d, a->d, parts, nl);
+    return out;
+}
+// the rescaled twin of a pristine ciphertext is computed once and cached on it: under FLEXIBLEAUTO the same
+// operand is (lazily) rescaled again by every multiplication that consumes it
+static const Ct* rescaled_twin(const Ct* a) {
+    if (!a->resc) { a->resc = rescale_new(a); a->ctx->stats.ops[{"rescale_unique", a->nl}]++; }
+    else count(a->ctx, "rescale_cached", a->nl);
+    return a->resc;
 }
 
-// LevelReduceInternalInPlace
-void level_reduce(Ct* a, int levels) {
-    if (levels <= 0) return;
-    Context* c = a->ctx; int nl2 = a->nl - levels;
-    if (nl2 < 1) throw std::runtime_error("level_reduce: not enough limbs");
-    u64* out = dev_alloc(c, words(c, a->parts * nl2));
-    for (int p = 0; p < a->parts; p++)
-        launch_copy_rows(c, c->dry ? nullptr : out + words(c, p * nl2), c->dry ? nullptr : a->d + words(c, p * a->nl), words(c, nl2));
-    ct_swap_buffer(a, out, nl2);
-    a->level += levels;
-}
+// Operand of an evaluator op: a read-only view of a caller's ciphertext (or of its cached twin) until an
+// adjustment has to change the data, at which point it owns a private temporary.
+struct Opnd {
+    const Ct* v;        // current value
+    Ct* own = nullptr;  // == v when the value is a private temporary
+    explicit Opnd(const Ct* src) : v(src) {}
+    ~Opnd() { if (own) ct_free(own); }
+    Opnd(const Opnd&) = delete;
+    void set_own(Ct* t) { if (own) ct_free(own); own = t; v = t; }
+    Ct* release() { Ct* t = own; own = nullptr; return t; }   // caller takes the temporary (or nullptr)
+};
 
-// LeveledSHECKKSRNS::AdjustLevelsAndDepthInPlace
-void adjust_levels_and_depth(Ct* a, Ct* b) {
+static Ct* mult_const_new(const Ct* a, double x) {   // EvalMultCore(ct, double), out of place
     Context* c = a->ctx;
-    if (a->level == b->level) {
-        if (a->deg < b->deg) mult_core_const(a, 1.0);
-        else if (b->deg < a->deg) mult_core_const(b, 1.0);
+    const double sf = c->sf_real[a->level];
+    i128 v = (i128)(x * sf + 0.5);
+    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg + 1, a->sf * sf, a->slots);
+    launch_mul_scalar(c, r->d, a->d, a->parts * a->nl, mods_q(a->nl), s);
+    return r;
+}
+static Ct* level_reduce_new(const Ct* a, int levels) {
+    Context* c = a->ctx; const int nl2 = a->nl - levels;
+    if (nl2 < 1) throw std::runtime_error("level_reduce: not enough limbs");
+    Ct* r = ct_new(c, a->parts, nl2, a->level + levels, a->deg, a->sf, a->slots);
+    for (int p = 0; p < a->parts; p++)
+        launch_copy_rows(c, c->dry ? nullptr : r->d + words(c, p * nl2), c->dry ? nullptr : a->d + words(c, p * a->nl), words(c, nl2));
+    return r;
+}
+static void op_mult_const(Opnd& o, double x) { o.set_own(mult_const_new(o.v, x)); }
+static void op_rescale(Opnd& o) { if (o.own) o.set_own(rescale_new(o.v)); else o.v = rescaled_twin(o.v); }
+static void op_level_reduce(Opnd& o, int levels) { if (levels > 0) o.set_own(level_reduce_new(o.v, levels)); }
+static void op_set_sf(Opnd& o, double sf) {
+    if (o.v->sf == sf) return;
+    if (!o.own) o.set_own(ct_clone(o.v));
+    o.own->sf = sf;
+}
+
+// LeveledSHECKKSRNS::AdjustLevelsAndDepthInPlace on operand views
+static void adjust_levels_and_depth(Opnd& A, Opnd& B) {
+    Context* c = A.v->ctx;
+    if (A.v->level == B.v->level) {
+        if (A.v->deg < B.v->deg) op_mult_const(A, 1.0);
+        else if (B.v->deg < A.v->deg) op_mult_const(B, 1.0);
         return;
     }
-    if (a->level > b->level) std::swap(a, b);
-    const int l1 = a->level, l2 = b->level;
-    const double scf = c->sf_real[l1];
-    if (a->deg == 2) {
-        if (b->deg == 2) {
-            double q1 = (double)c->moduli[a->nl - 1];
-            mult_core_const(a, b->sf / a->sf * q1 / scf);
-            rescale(a);
-            if (l1 + 1 < l2) level_reduce(a, l2 - l1 - 1);
-            a->sf = b->sf;
+    Opnd& a = A.v->level < B.v->level ? A : B;     // a: lower level (more limbs), brought to b
+    Opnd& b = A.v->level < B.v->level ? B : A;
+    const int l1 = a.v->level, l2 = b.v->level;
+    const double scf = c->sf_real[l1], bsf = b.v->sf;
+    if (a.v->deg == 2) {
+        if (b.v->deg == 2) {
+            double q1 = (double)c->moduli[a.v->nl - 1];
+            op_mult_const(a, bsf / a.v->sf * q1 / scf);
+            op_rescale(a);
+            op_level_reduce(a, l2 - l1 - 1);
+            op_set_sf(a, bsf);
         } else if (l1 + 1 == l2) {
-            rescale(a);
+            op_rescale(a);
         } else {
-            double q1 = (double)c->moduli[a->nl - 1];
-            mult_core_const(a, c->sf_big[l2 - 1] / a->sf * q1 / scf);
-            rescale(a);
-            if (l1 + 2 < l2) level_reduce(a, l2 - l1 - 2);
-            rescale(a);
-            a->sf = b->sf;
+            double q1 = (double)c->moduli[a.v->nl - 1];
+            op_mult_const(a, c->sf_big[l2 - 1] / a.v->sf * q1 / scf);
+            op_rescale(a);
+            op_level_reduce(a, l2 - l1 - 2);
+            op_rescale(a);
+            op_set_sf(a, bsf);
         }
     } else {
-        if (b->deg == 2) {
-            mult_core_const(a, b->sf / a->sf / scf);
-            level_reduce(a, l2 - l1);
-            a->sf = b->sf;
+        if (b.v->deg == 2) {
+            op_mult_const(a, bsf / a.v->sf / scf);
+            op_level_reduce(a, l2 - l1);
+            op_set_sf(a, bsf);
         } else {
-            mult_core_const(a, c->sf_big[l2 - 1] / a->sf / scf);
-            if (l1 + 1 < l2) level_reduce(a, l2 - l1 - 1);
-            rescale(a);
-            a->sf = b->sf;
+            op_mult_const(a, c->sf_big[l2 - 1] / a.v->sf / scf);
+            op_level_reduce(a, l2 - l1 - 1);
+            op_rescale(a);
+            op_set_sf(a, bsf);
         }
     }
 }
-void adjust_to_one(Ct* a, Ct* b) {
+static void adjust_to_one(Opnd& a, Opnd& b) {
     adjust_levels_and_depth(a, b);
-    if (a->deg == 2) { rescale(a); if (b != a) rescale(b); }
+    if (a.v->deg == 2) { op_rescale(a); op_rescale(b); }
 }
 
-// KeySwitchHYBRID::KeySwitchCore (+ optional addends): out[h] = add_h + ModDown(sum_j d_j * evk_j[h])
-void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1) {
+// ---- in-place forms (EvalLinearWSumMutable and the Chebyshev evaluator mutate their operands)
+static void commit(Ct* a, Opnd& o) {
+    if (o.v == a) return;
+    if (o.own) { ct_steal(a, o.release()); return; }
+    // o.v is a's cached twin: a becomes its twin
+    Ct* t = a->resc; a->resc = nullptr;
+    ct_steal(a, t);
+}
+void mult_core_const(Ct* a, double x) { Opnd o(a); op_mult_const(o, x); commit(a, o); }
+void rescale(Ct* a) { Opnd o(a); op_rescale(o); commit(a, o); }
+void level_reduce(Ct* a, int levels) { Opnd o(a); op_level_reduce(o, levels); commit(a, o); }
+void adjust_levels_and_depth(Ct* a, Ct* b) {
+    if (a == b) return;
+    Opnd x(a), y(b);
+    adjust_levels_and_depth(x, y);
+    commit(a, x); commit(b, y);
+}
+
+// KeySwitchHYBRID::KeySwitchCore (+ optional addends): out[h] = add_h + ModDown(sum_j d_j * evk_j[h]);
+// auto_k != 0 additionally applies the automorphism X -> X^k to both outputs while writing them
+void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1,
+                uint32_t auto_k) {
     count(c, "keyswitch", nl);
     if (!c->dry && !key.d) throw std::runtime_error("key switch: evaluation key not generated");
     const KsTables& t = get_ks_tables(c, nl);
@@ -156,20 +201,32 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
         launch_ntt(c, pp, K, mods_range(c->size_q, c->size_q + K), true);
         launch_base_conv(c, conv2, pp, t.moddown);
         launch_ntt(c, conv2, nl, mods_q(nl), false);
-        launch_moddown_final(c, c->dry ? nullptr : out + words(c, h * nl), acch, conv2, h == 0 ? add0 : add1, nl, next, t);
+        launch_moddown_final(c, c->dry ? nullptr : out + words(c, h * nl), acch, conv2, h == 0 ? add0 : add1, nl, auto_k, t);
     }
     dev_free(c, conv2); dev_free(c, acc);
 }
 
 // ------------------------------------------------------------------ public evaluator ops
-static void add_const_inplace(Ct* a, double x) {
+// EvalAdd(ct, double): add round(|x| * scalingFactor) (signed) to c0
+Ct* eval_add_const(const Ct* a, double x) {
     Context* c = a->ctx;
     i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
     if (x < 0) v = -v;
     u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
-    launch_add_scalar(c, a->d, a->nl, mods_q(a->nl), s);   // c0 only: rows 0..nl-1
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, false);
+    return r;
 }
-Ct* eval_add_const(const Ct* a, double x) { Ct* r = ct_clone(a); add_const_inplace(r, x); return r; }
+// EvalSub(double, ct) = -ct + x in one pass
+Ct* eval_const_sub(double x, const Ct* a) {
+    Context* c = a->ctx;
+    i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
+    if (x < 0) v = -v;
+    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, true);
+    return r;
+}
 
 Ct* eval_negate(const Ct* a) {
     Ct* r = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
@@ -180,53 +237,46 @@ Ct* eval_negate(const Ct* a) {
 // EvalAdd / EvalSub over (ct,ct) (ct,pt) (pt,ct): sign=+1 add, -1 sub (a - b)
 Ct* eval_add(const Ct* a, const Ct* b, int sign) {
     Context* c = a->ctx;
-    Ct *x = ct_clone(a), *y = ct_clone(b);
+    Opnd x(a), y(b);
     adjust_levels_and_depth(x, y);
-    Ct *ct = x, *pt = y; bool swapped = false;
-    if (x->parts < y->parts) { ct = y; pt = x; swapped = true; }
-    const int nl = ct->nl;
+    const Ct *X = x.v, *Y = y.v;
+    const int nl = X->nl, parts = std::max(X->parts, Y->parts);
     count(c, "add", nl);
-    if (swapped && sign < 0) {   // pt - ct
-        launch_neg(c, ct->d, ct->d, ct->parts * nl, mods_q(nl));
-        launch_add(c, ct->d, ct->d, pt->d, nl, mods_q(nl), 0);
-    } else {
-        launch_add(c, ct->d, ct->d, pt->d, pt->parts * nl, mods_q(nl), sign > 0 ? 0 : 1);
-    }
-    ct->slots = std::max(a->slots, b->slots);
-    ct_free(pt);
-    return ct;
+    Ct* r = ct_new(c, parts, nl, X->level, X->deg, X->sf, std::max(a->slots, b->slots));
+    // out[p] = (p < X.parts ? X[p] : 0) +- (p < Y.parts ? Y[p] : 0)
+    launch_addsub_parts(c, r->d, X->d, X->parts, Y->d, Y->parts, nl, sign < 0);
+    return r;
 }
 
 Ct* eval_mult_const(const Ct* a, double x) {
-    Ct* r = ct_clone(a);
-    if (r->deg == 2) rescale(r);
-    mult_core_const(r, x);
-    return r;
+    Opnd o(a);
+    if (o.v->deg == 2) op_rescale(o);
+    return mult_const_new(o.v, x);
 }
 
 // EvalMult(ct,ct) with relinearisation / EvalMult(ct,pt)
 Ct* eval_mult(const Ct* a, const Ct* b) {
     Context* c = a->ctx;
-    Ct* x = ct_clone(a);
-    Ct* y = ct_clone(b);
-    adjust_to_one(x, y);
-    const int nl = x->nl;
+    Opnd x(a), y(b);
+    if (a == b) { if (x.v->deg == 2) op_rescale(x); y.v = x.v; }   // EvalSquare: one operand, rescaled once
+    else adjust_to_one(x, y);
+    const Ct *X = x.v, *Y = y.v;
+    const int nl = X->nl;
     Ct* r;
-    if (x->parts == 2 && y->parts == 2) {
+    if (X->parts == 2 && Y->parts == 2) {
         count(c, "mult", nl);
         u64* d3 = dev_alloc(c, words(c, 3 * nl));
-        launch_tensor(c, d3, x->d, y->d, nl);
-        r = ct_new(c, 2, nl, x->level, x->deg + y->deg, x->sf * y->sf, std::max(a->slots, b->slots));
-        key_switch(c, c->dry ? nullptr : d3 + words(c, 2 * nl), nl, c->relin, r->d, d3, c->dry ? nullptr : d3 + words(c, nl));
+        launch_tensor(c, d3, X->d, Y->d, nl);
+        r = ct_new(c, 2, nl, X->level, X->deg + Y->deg, X->sf * Y->sf, std::max(a->slots, b->slots));
+        key_switch(c, c->dry ? nullptr : d3 + words(c, 2 * nl), nl, c->relin, r->d, d3, c->dry ? nullptr : d3 + words(c, nl), 0);
         dev_free(c, d3);
     } else {
-        Ct *ct = x->parts == 2 ? x : y, *pt = x->parts == 2 ? y : x;
+        const Ct *ct = X->parts == 2 ? X : Y, *pt = X->parts == 2 ? Y : X;
         if (ct->parts != 2 || pt->parts != 1) throw std::runtime_error("eval_mult: unsupported operand shapes");
         count(c, "mult_pt", nl);
-        r = ct_new(c, 2, nl, x->level, x->deg + y->deg, x->sf * y->sf, ct->slots);
+        r = ct_new(c, 2, nl, X->level, X->deg + Y->deg, X->sf * Y->sf, ct->slots);
         launch_mul(c, r->d, ct->d, pt->d, 2 * nl, nl, mods_q(nl));
     }
-    ct_free(x); ct_free(y);
     return r;
 }
 
@@ -244,7 +294,8 @@ uint32_t auto_index(const Context* c, int r) {
     return (uint32_t)res;
 }
 
-// EvalRotate -> EvalAutomorphism: key switch c1, then permute both polynomials
+// EvalRotate -> EvalAutomorphism: key switch c1, then permute both polynomials (the permutation is applied by
+// the mod-down epilogue while it writes the result)
 Ct* eval_rotate(const Ct* a, int r) {
     Context* c = a->ctx;
     if (a->parts != 2) throw std::runtime_error("EvalRotate: ciphertext must have 2 components");
@@ -253,11 +304,8 @@ Ct* eval_rotate(const Ct* a, int r) {
     if (it == c->rot.end()) throw std::runtime_error("EvalRotate: no rotation key for index " + std::to_string(r));
     count(c, "rotate", a->nl);
     const int nl = a->nl;
-    u64* tmp = dev_alloc(c, words(c, 2 * nl));
-    key_switch(c, c->dry ? nullptr : a->d + words(c, nl), nl, it->second, tmp, a->d, nullptr);
     Ct* out = ct_new(c, 2, nl, a->level, a->deg, a->sf, a->slots);
-    launch_automorph(c, out->d, tmp, 2 * nl, k);
-    dev_free(c, tmp);
+    key_switch(c, c->dry ? nullptr : a->d + words(c, nl), nl, it->second, out->d, a->d, nullptr, k);
     return out;
 }
 

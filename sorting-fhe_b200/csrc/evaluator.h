@@ -14,11 +14,12 @@ void mult_core_const(Ct* a, double x);
 void rescale(Ct* a);
 void level_reduce(Ct* a, int levels);
 void adjust_levels_and_depth(Ct* a, Ct* b);
-void adjust_to_one(Ct* a, Ct* b);
-void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1);
+void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1,
+                uint32_t auto_k);
 
 Ct* eval_add(const Ct* a, const Ct* b, int sign);
 Ct* eval_add_const(const Ct* a, double x);
+Ct* eval_const_sub(double x, const Ct* a);
 Ct* eval_negate(const Ct* a);
 Ct* eval_mult(const Ct* a, const Ct* b);
 Ct* eval_mult_const(const Ct* a, double x);

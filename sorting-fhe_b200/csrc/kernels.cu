@@ -53,28 +53,46 @@ void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, 
     KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows_out * c->n); k_mul<<<grid_for(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
 }
 
-__global__ void k_mul_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
+__global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
-    size_t o = (size_t)row * n + x; d[o] = shoup_mul(d[o], s.v[l], s.sh[l], q);
+    size_t o = (size_t)row * n + x; out[o] = shoup_mul(d[o], s.v[l], s.sh[l], q);
 }
-void launch_mul_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
+void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const LimbMods& m, const u64* hs) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
-    k_mul_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
+    k_mul_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, c->n, s);
 }
 
-__global__ void k_add_scalar(u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
+__global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, int nl, LimbScalars s, int negate) {
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
-    int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
-    size_t o = (size_t)row * n + x; d[o] = add_mod(d[o], s.v[l], q);
+    int row = blockIdx.y, l = row % nl; u64 q = mi[l].q;
+    size_t o = (size_t)row * n + x;
+    u64 v = d[o];
+    if (negate) v = neg_mod(v, q);
+    if (row < nl) v = add_mod(v, s.v[l], q);
+    out[o] = v;
 }
-void launch_add_scalar(Context* c, u64* data, int rows, const LimbMods& m, const u64* hs) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
+void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* hs, bool negate) {
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * parts * nl * c->n);
     LimbScalars s;
-    for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
-    k_add_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, s);
+    for (int i = 0; i < nl; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
+    k_add_scalar<<<grid_for(c, parts * nl), 256, 0, c->stream>>>(out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
+}
+
+__global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
+                               int sub) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    int row = blockIdx.y, p = row / nl; u64 q = mi[row % nl].q;
+    size_t o = (size_t)row * n + x;
+    u64 a = p < xparts ? xs[o] : 0, b = p < yparts ? ys[o] : 0;
+    out[o] = sub ? sub_mod(a, b, q) : add_mod(a, b, q);
+}
+void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub) {
+    int parts = xparts > yparts ? xparts : yparts;
+    KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * (xparts + yparts + parts));
+    k_addsub_parts<<<grid_for(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0);
 }
 
 // (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
@@ -135,6 +153,21 @@ void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int
     LimbScalars s; int nl_out = nl_in - 1; u64 ql = c->moduli[nl_in - 1];
     for (int i = 0; i < nl_out; i++) { u64 q = c->moduli[i]; s.v[i] = host_powmod(ql % q, q - 2, q); s.sh[i] = host_shoup(s.v[i], q); }
     k_rescale_final<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(out, in, t, c->d_mod, c->n, nl_out, s);
+}
+
+// DropLastElementAndScale of `parts` polynomials with nl_in limbs each -> out [parts][nl_in-1][n]
+void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in) {
+    const int nl = nl_in;
+    const size_t n = c->n;
+    u64* last = dev_alloc(c, (size_t)parts * n);
+    for (int p = 0; p < parts; p++)
+        launch_copy_rows(c, c->dry ? nullptr : last + p * n, c->dry ? nullptr : in + ((size_t)p * nl + nl - 1) * n, n);
+    launch_ntt(c, last, parts, mods_range(nl - 1, nl), true);
+    u64* t = dev_alloc(c, (size_t)parts * (nl - 1) * n);
+    launch_rescale_prep(c, t, last, parts, nl - 1, nl - 1);
+    launch_ntt(c, t, parts * (nl - 1), mods_q(nl - 1), false);
+    launch_rescale_final(c, out, in, t, parts, nl);
+    dev_free(c, last); dev_free(c, t);
 }
 
 void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words) {

@@ -82,22 +82,29 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
     k_ks_inner<<<grid, 256, 0, c->stream>>>(acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
 }
 
-// out[i] = addend[i] + (acc[i] - conv[i]) * P^-1 mod q_i   (ApproxModDown epilogue; addend optional)
+// out[i] = addend[i] + (acc[i] - conv[i]) * P^-1 mod q_i   (ApproxModDown epilogue; addend optional).
+// With auto_k != 0 the result is written through the automorphism X -> X^k (EVALUATION-format index
+// permutation of OpenFHE's PrecomputeAutoMap): out[p] = value[src(p)].
 __global__ void k_moddown_final(u64* out, const u64* acc, const u64* conv, const u64* addend, const u64* pinv,
-                                const u64* pinv_sh, const ModInfo* mi, int n) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    if (x >= n) return;
+                                const u64* pinv_sh, const ModInfo* mi, int n, int logn, u32 auto_k) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
     int i = blockIdx.y; u64 q = mi[i].q;
+    int x = p;
+    if (auto_k) {
+        u32 j = __brev((u32)p) >> (32 - logn);
+        u32 idx = (u32)((((2ull * j + 1) * auto_k) & (2ull * n - 1)) >> 1);
+        x = (int)(__brev(idx) >> (32 - logn));
+    }
     size_t o = (size_t)i * n + x;
     u64 r = shoup_mul(sub_mod(acc[o], conv[o], q), pinv[i], pinv_sh[i], q);
     if (addend) r = add_mod(r, addend[o], q);
-    out[o] = r;
+    out[(size_t)i * n + p] = r;
 }
 void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* addend, int nl,
-                          int acc_stride_limbs, const KsTables& t) {
-    (void)acc_stride_limbs;
+                          uint32_t auto_k, const KsTables& t) {
     KL(c);
     ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (addend ? 4 : 3));
     dim3 grid((c->n + 255) / 256, nl);
-    k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, addend, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n);
+    k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, addend, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, auto_k);
 }

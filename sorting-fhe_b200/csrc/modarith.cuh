@@ -21,6 +21,7 @@ struct ModInfo {   // one entry per modulus (Q primes then P primes), lives in g
     u64 r2;        // 2^128 mod q (to enter Montgomery form)
     u64 ninv;      // n^-1 mod q
     u64 ninv_sh;   // Shoup companion of ninv
+    u64 qrecip;    // floor(2^64 / q): x - mulhi(x, qrecip) * q lies in [0, 2q) for any x < 2^64
     int bits;
     int pad;
 };

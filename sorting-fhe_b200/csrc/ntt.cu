@@ -6,146 +6,245 @@
 // Semantics (pinned by oracle/ckks_prims.c orc_ntt_fwd/orc_ntt_inv): Cooley-Tukey, natural in ->
 // bit-reversed out with table W[m+i] = psi^bitrev(m+i); inverse Gentleman-Sande with n^-1.
 //
-// Design: a limb of n = 2^logn words is processed in <= 2 HBM passes.  A CTA stages a tile of
-// 2^tb (tb = min(11, logn)) words in shared memory; every thread owns 8 words in registers and
-// performs up to 3 butterfly stages per shared-memory round trip (radix-8), Harvey lazy
-// butterflies with Shoup twiddles on the integer pipes.  The "strided" phase handles the first
-// s1 = logn - tb stages on tiles of 2^s1 rows x 2^(tb-s1) contiguous columns (coalesced 256 B+
-// runs); the "local" phase handles the last tb stages on contiguous 2^tb-word chunks.
-// Index math was validated against the oracle by tools/emulate_ntt_indexing.py.
+// Design (B200): the transform is bound by instruction issue on the 32-bit integer pipes (a 64-bit Shoup
+// butterfly is ~25 SASS instructions), not by HBM, so the kernel is organised to spend instructions on
+// butterflies only:
+//   * a limb of n = 2^logn words is processed in <= 2 passes; a CTA owns a tile of 2^T words (T = min(11,
+//     logn)); pass "A" (first logn-T stages) works on tiles of 2^a rows x 2^(T-a) contiguous columns, pass "B"
+//     (last T stages) on contiguous chunks;
+//   * every thread keeps 8 words in registers and runs up to 3 stages per round; the first round of a pass
+//     loads straight from global memory (coalesced 256 B runs), the last one stores straight back, only the
+//     rounds in between exchange through (padded, conflict-free) shared memory;
+//   * butterflies are lazy (Harvey): no per-butterfly correction for moduli < 2^58 forward / < 2^46 inverse
+//     (values may grow to (2s+1)q resp. 2^s q < 2^64); larger moduli use one conditional subtraction;
+//   * twiddles are (w, floor(w 2^64 / q)) pairs fetched with one 16-byte load; rounds touch 1, 2 and 4
+//     consecutive pairs per thread.
+// Results are canonical residues, bit-identical to the oracle.
 #include "engine.h"
+#include <utility>
 
 static constexpr int TB_MAX = 11;
+typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
 
 __device__ __forceinline__ int padi(int e) { return e + (e >> 3); }
 
-template <bool INV, int S>
-__device__ __forceinline__ void ntt_pass(u64* sm, int tb, int sl_lo, int s0, u32 pre, const u64* __restrict__ W,
-                                         const u64* __restrict__ Wsh, u64 q) {
-    constexpr int G = 8 >> S;
-    constexpr int E = 1 << S;
-    const int lowbits = tb - sl_lo - S;
+// element index (tile-local) of register k of thread u in a round whose 3-bit window sits at bit p
+__device__ __forceinline__ int local_index(int u, int k, int p) {
+    return ((u >> p) << (p + 3)) | (k << p) | (u & ((1 << p) - 1));
+}
+
+template <bool FIX>
+__device__ __forceinline__ void bf_fwd(u64& X, u64& Y, const tw_t w, const u64 q, const u64 q2) {
+    const u64 T = shoup_lazy(Y, w.x, w.y, q);   // [0, 2q)
+    const u64 x = X;
+    X = x + T;
+    Y = x - T + q2;
+    (void)FIX;
+}
+template <bool FIX>
+__device__ __forceinline__ void bf_inv(u64& X, u64& Y, const tw_t w, const u64 q, const u64 q2, const u64 cq) {
+    const u64 x = X, y = Y;
+    if (FIX) {                       // operands < 2q
+        u64 s = x + y;
+        if (s >= q2) s -= q2;
+        X = s;
+        Y = shoup_lazy(x - y + q2, w.x, w.y, q);
+    } else {                         // operands < cq = 2^t q (t = stages done so far), no correction
+        X = x + y;
+        Y = shoup_lazy(x - y + cq, w.x, w.y, q);
+    }
+}
+
+// One round on the 8 registers of a thread: butterfly stages j in [J0, J1) of the 3-bit window.
+// s0 = global stage number of j = 0; ehi = all element-index bits above the window.
+template <bool INV, bool FIX, int J0, int J1>
+__device__ __forceinline__ void round8(u64 (&r)[8], const tw_t* __restrict__ W, const u32 ehi, const int s0, const u64 q,
+                                       int t_done) {
     const u64 q2 = q << 1;
+    if (!INV) {
+        if (FIX) {
+            const u64 q8 = q << 3;
 #pragma unroll
-    for (int g = 0; g < G; g++) {
-        const int u = threadIdx.x * G + g;
-        const int e0 = ((u >> lowbits) << (lowbits + S)) | (u & ((1 << lowbits) - 1));
-        const u32 top = (u32)e0 >> (tb - sl_lo);
-        u64 r[E];
-#pragma unroll
-        for (int k = 0; k < E; k++) r[k] = sm[padi(e0 + (k << lowbits))];
-        if (!INV) {
-#pragma unroll
-            for (int j = 0; j < S; j++) {
-                const int sl = sl_lo + j, s = s0 + sl, bit = 1 << (S - 1 - j);
-#pragma unroll
-                for (int k = 0; k < E; k++) {
-                    if (k & bit) continue;
-                    const u32 ti = (1u << s) + ((pre << sl) | (top << j) | (u32)(k >> (S - j)));
-                    const u64 w = W[ti], wsh = Wsh[ti];
-                    u64 X = r[k];
-                    if (X >= q2) X -= q2;
-                    const u64 T = shoup_lazy(r[k | bit], w, wsh, q);
-                    r[k] = X + T;
-                    r[k | bit] = X - T + q2;
-                }
-            }
-        } else {
-#pragma unroll
-            for (int j = S - 1; j >= 0; j--) {
-                const int sl = sl_lo + j, s = s0 + sl, bit = 1 << (S - 1 - j);
-#pragma unroll
-                for (int k = 0; k < E; k++) {
-                    if (k & bit) continue;
-                    const u32 ti = (1u << s) + ((pre << sl) | (top << j) | (u32)(k >> (S - j)));
-                    const u64 w = W[ti], wsh = Wsh[ti];
-                    const u64 X = r[k], Y = r[k | bit];
-                    u64 sum = X + Y;
-                    if (sum >= q2) sum -= q2;
-                    r[k] = sum;
-                    r[k | bit] = shoup_lazy(X - Y + q2, w, wsh, q);
-                }
-            }
+            for (int k = 0; k < 8; k++) if (r[k] >= q8) r[k] -= q8;
         }
 #pragma unroll
-        for (int k = 0; k < E; k++) sm[padi(e0 + (k << lowbits))] = r[k];
+        for (int j = J0; j < J1; j++) {
+            const int bit = 4 >> j;
+            const tw_t* Ws = W + ((1u << (s0 + j)) + (ehi << j));
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                bf_fwd<FIX>(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), q, q2);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = J1 - 1; j >= J0; j--) {
+            const int bit = 4 >> j;
+            const tw_t* Ws = W + ((1u << (s0 + j)) + (ehi << j));
+            const u64 cq = q << t_done;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                bf_inv<FIX>(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), q, q2, cq);
+            }
+            t_done++;
+        }
+    }
+}
+
+struct NttArgs {
+    u64* dst;                // [rows][n]
+    const u64* src;          // [rows][n] (== dst for in-place)
+    const ModInfo* mi;
+    const tw_t* tw;          // [M][n] forward or inverse twiddle pairs
+    const tw_t* scale;       // INV only: final factor (n^-1 [* extra]) as Shoup pair, indexed by modulus id
+    int logn, T, a;          // T = tile bits, a = logn - T stages in pass A
+    int pass;                // 0 = pass A (strided), 1 = pass B (contiguous)
+    int final_pass;          // this pass produces the final output (canonicalise / scale)
+};
+
+// rounds of one pass: window position p and stage range [J0,J1) per round (host fills, <= 4 rounds)
+struct Sched { int nr; int p[4]; int j0[4]; int j1[4]; };
+
+template <bool INV, bool FIX>
+__device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, int s0, u64 q, int t_done, int j0, int j1) {
+    if (j0 == 0 && j1 == 3) round8<INV, FIX, 0, 3>(r, W, ehi, s0, q, t_done);
+    else if (j0 == 1 && j1 == 3) round8<INV, FIX, 1, 3>(r, W, ehi, s0, q, t_done);
+    else if (j0 == 2 && j1 == 3) round8<INV, FIX, 2, 3>(r, W, ehi, s0, q, t_done);
+    else if (j0 == 0 && j1 == 2) round8<INV, FIX, 0, 2>(r, W, ehi, s0, q, t_done);
+    else round8<INV, FIX, 0, 1>(r, W, ehi, s0, q, t_done);
+}
+
+template <bool INV, bool FIX>
+__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& S, const int row, const int mid, const ModInfo& mi,
+                                         u64* sm) {
+    const u64 q = mi.q;
+    const int logn = A.logn, T = A.T, cb = T - A.a;       // cb: column bits of a pass-A tile
+    const tw_t* W = A.tw + ((size_t)mid << logn);
+    const u64* src = A.src + ((size_t)row << logn);
+    u64* dst = A.dst + ((size_t)row << logn);
+    const int tile = blockIdx.x, u = threadIdx.x;
+    const bool strided = A.pass == 0;
+    // global word offset of tile-local index L
+    auto gaddr = [&](int L) -> size_t {
+        return strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
+    };
+    // position of tile-local bit 0 in the element index, and the index bits above the tile
+    // pass B: E = tile << T | L.   pass A: E = (row bits = L >> cb) << T | (tile << cb | col): stages only touch
+    // the row bits, whose position in E is T + (bit - cb).
+    u64 r[8];
+    int t_done = 0;   // inverse: number of GS stages already applied to the data (for the lazy offset)
+    if (INV) t_done = strided ? T : 0;
+    for (int ri = 0; ri < S.nr; ri++) {
+        const int p = S.p[ri];
+        if (ri == 0) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) r[k] = src[gaddr(local_index(u, k, p))];
+        } else {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; k++) r[k] = sm[padi(local_index(u, k, p))];
+        }
+        // element-index bits above the window, and the global stage of window bit 2 (j = 0)
+        const int L0 = local_index(u, 0, p);
+        u32 ehi; int s0;
+        if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = A.a - 1 - (p + 2 - cb); }
+        else { ehi = (u32)(((size_t)tile << T | (size_t)L0) >> (p + 3)); s0 = logn - 1 - (p + 2); }
+        do_round<INV, FIX>(r, W, ehi, s0, q, t_done, S.j0[ri], S.j1[ri]);
+        if (INV) t_done += S.j1[ri] - S.j0[ri];
+        if (ri + 1 < S.nr) {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; k++) sm[padi(local_index(u, k, p))] = r[k];
+        } else {
+            if (A.final_pass) {
+                if (!INV) {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {   // any value < 2^64 -> [0, q)
+                        u64 v = r[k] - __umul64hi(r[k], mi.qrecip) * q;
+                        r[k] = v >= q ? v - q : v;
+                    }
+                } else {
+                    const tw_t sc = A.scale[mid];
+#pragma unroll
+                    for (int k = 0; k < 8; k++) { u64 v = shoup_lazy(r[k], sc.x, sc.y, q); r[k] = v >= q ? v - q : v; }
+                }
+            } else if (INV && FIX) {
+                // between inverse passes the FIX path keeps values < 2q already
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = r[k];
+        }
     }
 }
 
 template <bool INV>
 __global__ void __launch_bounds__(256)
-ntt_kernel(u64* __restrict__ data, LimbMods mods, const ModInfo* __restrict__ modinfo, const u64* __restrict__ tw,
-           const u64* __restrict__ tw_sh, int logn, int tb, int s0, int ns, int strided, int s1, int final_phase) {
+ntt_kernel(NttArgs A, Sched S, LimbMods mods) {
     extern __shared__ u64 sm[];
     const int row = blockIdx.y;
     const int mid = mods.m[row % mods.n];
-    const ModInfo mi = modinfo[mid];
-    const u64 q = mi.q;
-    const u64* W = tw + ((size_t)mid << logn);
-    const u64* Wsh = tw_sh + ((size_t)mid << logn);
-    u64* base = data + ((size_t)row << logn);
-    const int tile = blockIdx.x, tsize = 1 << tb, cb = tb - s1;
-    const u32 pre = strided ? 0u : (u32)tile;
+    const ModInfo mi = A.mi[mid];
+    const bool fix = INV ? (mi.bits > 46) : (mi.bits > 58);
+    if (fix) ntt_tile<INV, true>(A, S, row, mid, mi, sm);
+    else ntt_tile<INV, false>(A, S, row, mid, mi, sm);
+}
 
-    for (int e = threadIdx.x; e < tsize; e += blockDim.x) {
-        const size_t g = strided ? (((size_t)(e >> cb) << (logn - s1)) | (size_t)((tile << cb) + (e & ((1 << cb) - 1))))
-                                 : (((size_t)tile << tb) + e);
-        sm[padi(e)] = base[g];
+// rounds of a pass that butterflies `ns` consecutive bits whose top one is tile-local bit `top` (T-1 for both
+// passes: the row bits of pass A are the top a bits of the tile index)
+static Sched make_sched(int T, int ns, bool inverse) {
+    Sched s; s.nr = 0;
+    int ct = T - 1, rem = ns;
+    bool first = true;
+    while (rem > 0) {
+        const int S = rem < 3 ? rem : 3;
+        int p, j0, j1;
+        if (S == 3) { p = ct - 2; j0 = 0; j1 = 3; }
+        else if (first) { p = ct - 2; j0 = 0; j1 = S; }          // short first round: top S bits of the window
+        else { p = ct - S + 1; j0 = 3 - S; j1 = 3; }             // short later round: low S bits of the window
+        s.p[s.nr] = p; s.j0[s.nr] = j0; s.j1[s.nr] = j1; s.nr++;
+        ct -= S; rem -= S; first = false;
     }
-    __syncthreads();
-    if (!INV) {
-        for (int sl = 0; sl < ns;) {
-            const int S = min(3, ns - sl);
-            if (S == 3) ntt_pass<false, 3>(sm, tb, sl, s0, pre, W, Wsh, q);
-            else if (S == 2) ntt_pass<false, 2>(sm, tb, sl, s0, pre, W, Wsh, q);
-            else ntt_pass<false, 1>(sm, tb, sl, s0, pre, W, Wsh, q);
-            sl += S;
-            __syncthreads();
+    if (inverse) {
+        for (int i = 0; i < s.nr / 2; i++) {
+            std::swap(s.p[i], s.p[s.nr - 1 - i]); std::swap(s.j0[i], s.j0[s.nr - 1 - i]); std::swap(s.j1[i], s.j1[s.nr - 1 - i]);
         }
+    }
+    return s;
+}
+
+void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs) {
+    c->stats.kernel_launches += (c->log_n > TB_MAX) ? 2 : 1;
+    if (c->dry || rows == 0) return;
+    ProfScope ps(c, KC_NTT, 16.0 * rows * c->n, (c->log_n > TB_MAX) ? 2 : 1);
+    const int logn = c->log_n, T = logn < TB_MAX ? logn : TB_MAX, a = logn - T;
+    const int threads = (1 << T) / 8;
+    const size_t smem = (size_t)((1 << T) + ((1 << T) >> 3) + 8) * sizeof(u64);
+    dim3 grid(c->n >> T, rows);
+    NttArgs A;
+    A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a;
+    A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
+    A.scale = (const tw_t*)(scale_pairs ? scale_pairs : c->d_ninv_pairs);
+    if (!inverse) {
+        A.src = src;
+        if (a > 0) {
+            A.pass = 0; A.final_pass = 0;
+            ntt_kernel<false><<<grid, threads, smem, c->stream>>>(A, make_sched(T, a, false), m);
+            A.src = dst;
+        }
+        A.pass = 1; A.final_pass = 1;
+        ntt_kernel<false><<<grid, threads, smem, c->stream>>>(A, make_sched(T, T, false), m);
     } else {
-        // groups are the forward groups taken in reverse order
-        const int rem = ns % 3;  // forward grouping: 3,3,...,rem  -> last group has size rem (if rem != 0)
-        int sl_hi = ns;
-        bool first = true;
-        while (sl_hi > 0) {
-            const int S = (first && rem) ? rem : 3;
-            first = false;
-            const int sl = sl_hi - S;
-            if (S == 3) ntt_pass<true, 3>(sm, tb, sl, s0, pre, W, Wsh, q);
-            else if (S == 2) ntt_pass<true, 2>(sm, tb, sl, s0, pre, W, Wsh, q);
-            else ntt_pass<true, 1>(sm, tb, sl, s0, pre, W, Wsh, q);
-            sl_hi = sl;
-            __syncthreads();
+        A.src = src; A.pass = 1; A.final_pass = a == 0;
+        ntt_kernel<true><<<grid, threads, smem, c->stream>>>(A, make_sched(T, T, true), m);
+        if (a > 0) {
+            A.src = dst; A.pass = 0; A.final_pass = 1;
+            ntt_kernel<true><<<grid, threads, smem, c->stream>>>(A, make_sched(T, a, true), m);
         }
-    }
-    const u64 q2 = q << 1;
-    for (int e = threadIdx.x; e < tsize; e += blockDim.x) {
-        const size_t g = strided ? (((size_t)(e >> cb) << (logn - s1)) | (size_t)((tile << cb) + (e & ((1 << cb) - 1))))
-                                 : (((size_t)tile << tb) + e);
-        u64 v = sm[padi(e)];
-        if (!INV) { if (v >= q2) v -= q2; }
-        else if (final_phase) v = shoup_lazy(v, mi.ninv, mi.ninv_sh, q);
-        if (v >= q) v -= q;
-        base[g] = v;
     }
 }
 
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse) {
-    c->stats.kernel_launches += (c->log_n > TB_MAX) ? 2 : 1;
-    if (c->dry || rows == 0) return;
-    ProfScope ps(c, KC_NTT, 16.0 * rows * c->n, (c->log_n > TB_MAX) ? 2 : 1);
-    const int logn = c->log_n, tb = logn < TB_MAX ? logn : TB_MAX, s1 = logn - tb;
-    const int threads = (1 << tb) / 8;
-    const size_t smem = (size_t)((1 << tb) + ((1 << tb) >> 3) + 8) * sizeof(u64);
-    dim3 grid(c->n >> tb, rows);
-    if (!inverse) {
-        if (s1 > 0)
-            ntt_kernel<false><<<grid, threads, smem, c->stream>>>(data, m, c->d_mod, c->d_psi, c->d_psi_sh, logn, tb, 0, s1, 1, s1, 0);
-        ntt_kernel<false><<<grid, threads, smem, c->stream>>>(data, m, c->d_mod, c->d_psi, c->d_psi_sh, logn, tb, s1, tb, 0, s1, 1);
-    } else {
-        ntt_kernel<true><<<grid, threads, smem, c->stream>>>(data, m, c->d_mod, c->d_ipsi, c->d_ipsi_sh, logn, tb, s1, tb, 0, s1,
-                                                             s1 == 0);
-        if (s1 > 0)
-            ntt_kernel<true><<<grid, threads, smem, c->stream>>>(data, m, c->d_mod, c->d_ipsi, c->d_ipsi_sh, logn, tb, 0, s1, 1, s1, 1);
-    }
+    launch_ntt_ex(c, data, data, rows, m, inverse, nullptr);
 }
