@@ -107,6 +107,32 @@ struct NttArgs {
 // rounds of one pass: window position p and stage range [J0,J1) per round (host fills, <= 4 rounds)
 struct Sched { int nr; int p[4]; int j0[4]; int j1[4]; };
 
+// rounds of a pass that butterflies `ns` consecutive tile-local bits starting at bit T-1 (the row bits of pass A are
+// the top a bits of the tile index)
+__host__ __device__ constexpr Sched make_sched(int T, int ns, bool inverse) {
+    Sched s{};
+    int ct = T - 1, rem = ns;
+    bool first = true;
+    while (rem > 0) {
+        const int S = rem < 3 ? rem : 3;
+        int p = 0, j0 = 0, j1 = 0;
+        if (S == 3) { p = ct - 2; j0 = 0; j1 = 3; }
+        else if (first) { p = ct - 2; j0 = 0; j1 = S; }          // short first round: top S bits of the window
+        else { p = ct - S + 1; j0 = 3 - S; j1 = 3; }             // short later round: low S bits of the window
+        s.p[s.nr] = p; s.j0[s.nr] = j0; s.j1[s.nr] = j1; s.nr++;
+        ct -= S; rem -= S; first = false;
+    }
+    if (inverse) {
+        for (int i = 0; i < s.nr / 2; i++) {
+            const int k = s.nr - 1 - i;
+            int t = s.p[i]; s.p[i] = s.p[k]; s.p[k] = t;
+            t = s.j0[i]; s.j0[i] = s.j0[k]; s.j0[k] = t;
+            t = s.j1[i]; s.j1[i] = s.j1[k]; s.j1[k] = t;
+        }
+    }
+    return s;
+}
+
 template <bool INV, bool FIX>
 __device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, int s0, u64 q, int t_done, int j0, int j1) {
     if (j0 == 0 && j1 == 3) round8<INV, FIX, 0, 3>(r, W, ehi, s0, q, t_done);
@@ -116,16 +142,22 @@ __device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, in
     else round8<INV, FIX, 0, 1>(r, W, ehi, s0, q, t_done);
 }
 
-template <bool INV, bool FIX>
-__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& S, const int row, const int mid, const ModInfo& mi,
+// LOGN_C != 0: ring size, pass and round schedule are compile-time constants (all index arithmetic folds);
+// LOGN_C == 0: generic runtime form.
+template <bool INV, bool FIX, int LOGN_C, int PASS_C>
+__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const int row, const int mid, const ModInfo& mi,
                                          u64* sm) {
+    constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
+    constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
+    const Sched& S = LOGN_C ? SC : SR;
     const u64 q = mi.q;
-    const int logn = A.logn, T = A.T, cb = T - A.a;       // cb: column bits of a pass-A tile
+    const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
+    const int cb = T - a_;                                // cb: column bits of a pass-A tile
     const tw_t* W = A.tw + ((size_t)mid << logn);
     const u64* src = A.src + ((size_t)row << logn);
     u64* dst = A.dst + ((size_t)row << logn);
     const int tile = blockIdx.x, u = threadIdx.x;
-    const bool strided = A.pass == 0;
+    const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     // global word offset of tile-local index L
     auto gaddr = [&](int L) -> size_t {
         return strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
@@ -136,7 +168,8 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& S, const
     u64 r[8];
     int t_done = 0;   // inverse: number of GS stages already applied to the data (for the lazy offset)
     if (INV) t_done = strided ? T : 0;
-    for (int ri = 0; ri < S.nr; ri++) {
+#pragma unroll
+    for (int ri = 0; ri < (LOGN_C ? SC.nr : SR.nr); ri++) {
         const int p = S.p[ri];
         if (ri == 0) {
 #pragma unroll
@@ -149,11 +182,11 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& S, const
         // element-index bits above the window, and the global stage of window bit 2 (j = 0)
         const int L0 = local_index(u, 0, p);
         u32 ehi; int s0;
-        if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = A.a - 1 - (p + 2 - cb); }
+        if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = a_ - 1 - (p + 2 - cb); }
         else { ehi = (u32)(((size_t)tile << T | (size_t)L0) >> (p + 3)); s0 = logn - 1 - (p + 2); }
         do_round<INV, FIX>(r, W, ehi, s0, q, t_done, S.j0[ri], S.j1[ri]);
         if (INV) t_done += S.j1[ri] - S.j0[ri];
-        if (ri + 1 < S.nr) {
+        if (ri + 1 < (LOGN_C ? SC.nr : SR.nr)) {
             __syncthreads();
 #pragma unroll
             for (int k = 0; k < 8; k++) sm[padi(local_index(u, k, p))] = r[k];
@@ -179,7 +212,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& S, const
     }
 }
 
-template <bool INV>
+template <bool INV, int LOGN_C, int PASS_C>
 __global__ void __launch_bounds__(256)
 ntt_kernel(NttArgs A, Sched S, LimbMods mods) {
     extern __shared__ u64 sm[];
@@ -187,31 +220,19 @@ ntt_kernel(NttArgs A, Sched S, LimbMods mods) {
     const int mid = mods.m[row % mods.n];
     const ModInfo mi = A.mi[mid];
     const bool fix = INV ? (mi.bits > 46) : (mi.bits > 58);
-    if (fix) ntt_tile<INV, true>(A, S, row, mid, mi, sm);
-    else ntt_tile<INV, false>(A, S, row, mid, mi, sm);
+    if (fix) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, row, mid, mi, sm);
+    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, row, mid, mi, sm);
 }
 
-// rounds of a pass that butterflies `ns` consecutive bits whose top one is tile-local bit `top` (T-1 for both
-// passes: the row bits of pass A are the top a bits of the tile index)
-static Sched make_sched(int T, int ns, bool inverse) {
-    Sched s; s.nr = 0;
-    int ct = T - 1, rem = ns;
-    bool first = true;
-    while (rem > 0) {
-        const int S = rem < 3 ? rem : 3;
-        int p, j0, j1;
-        if (S == 3) { p = ct - 2; j0 = 0; j1 = 3; }
-        else if (first) { p = ct - 2; j0 = 0; j1 = S; }          // short first round: top S bits of the window
-        else { p = ct - S + 1; j0 = 3 - S; j1 = 3; }             // short later round: low S bits of the window
-        s.p[s.nr] = p; s.j0[s.nr] = j0; s.j1[s.nr] = j1; s.nr++;
-        ct -= S; rem -= S; first = false;
+template <bool INV, int PASS_C>
+static void launch_pass(Context* c, dim3 grid, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
+    switch (c->log_n) {   // compile-time schedules for the ring sizes of the reference's fixtures
+        case 17: ntt_kernel<INV, 17, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        case 16: ntt_kernel<INV, 16, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        case 13: ntt_kernel<INV, 13, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        case 12: ntt_kernel<INV, 12, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        default: ntt_kernel<INV, 0, 0><<<grid, threads, smem, c->stream>>>(A, S, m); break;
     }
-    if (inverse) {
-        for (int i = 0; i < s.nr / 2; i++) {
-            std::swap(s.p[i], s.p[s.nr - 1 - i]); std::swap(s.j0[i], s.j0[s.nr - 1 - i]); std::swap(s.j1[i], s.j1[s.nr - 1 - i]);
-        }
-    }
-    return s;
 }
 
 void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs) {
@@ -230,17 +251,17 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
         A.src = src;
         if (a > 0) {
             A.pass = 0; A.final_pass = 0;
-            ntt_kernel<false><<<grid, threads, smem, c->stream>>>(A, make_sched(T, a, false), m);
+            launch_pass<false, 0>(c, grid, threads, smem, A, make_sched(T, a, false), m);
             A.src = dst;
         }
         A.pass = 1; A.final_pass = 1;
-        ntt_kernel<false><<<grid, threads, smem, c->stream>>>(A, make_sched(T, T, false), m);
+        launch_pass<false, 1>(c, grid, threads, smem, A, make_sched(T, T, false), m);
     } else {
         A.src = src; A.pass = 1; A.final_pass = a == 0;
-        ntt_kernel<true><<<grid, threads, smem, c->stream>>>(A, make_sched(T, T, true), m);
+        launch_pass<true, 1>(c, grid, threads, smem, A, make_sched(T, T, true), m);
         if (a > 0) {
             A.src = dst; A.pass = 0; A.final_pass = 1;
-            ntt_kernel<true><<<grid, threads, smem, c->stream>>>(A, make_sched(T, a, true), m);
+            launch_pass<true, 0>(c, grid, threads, smem, A, make_sched(T, a, true), m);
         }
     }
 }
