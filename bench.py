@@ -301,6 +301,8 @@ def run_b200(args):
                          "avg_launch_us": prof_ntt["ms"] * 1e3 / max(prof_ntt["launches"], 1),
                          "share_of_step": breakdown["ntt"]["ms"] / max(total_ms, 1e-9), "dominant_class": dom},
             "breakdown_ms": {k: round(v["ms"], 3) for k, v in breakdown.items()},
+            "breakdown_GBs": {k: round(v["bytes"] / v["ms"] / 1e6, 1) for k, v in breakdown.items() if v["ms"] > 0},
+            "breakdown_launches": {k: v["launches"] for k, v in breakdown.items()},
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(n, log_n, cfg, trace)

@@ -38,11 +38,16 @@ void context_release(Context* c) {
         cudaStreamSynchronize(c->stream);
         cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
+        if (c->enc_pinned) cudaFreeHost(c->enc_pinned);
+        for (auto e : c->enc_events) if (e) cudaEventDestroy(e);
+        for (auto e : c->prof.pool) cudaEventDestroy(e);
         for (auto& kv : c->ks) {
             for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); }
             cudaFree(kv.second.moddown.d_hatinv); cudaFree(kv.second.moddown.d_hatinv_sh); cudaFree(kv.second.moddown.d_hatmod);
             cudaFree(kv.second.d_pinv); cudaFree(kv.second.d_pinv_sh);
+            cudaFree(kv.second.d_modup_scale); cudaFree(kv.second.d_moddown_scale);
         }
+        for (auto& kv : c->rescale_pairs) cudaFree(kv.second);
         dev_free(c, c->d_secret); dev_free(c, c->d_pk); dev_free(c, c->relin.d);
         for (auto& kv : c->rot) dev_free(c, kv.second.d);
         cudaStreamSynchronize(c->stream);

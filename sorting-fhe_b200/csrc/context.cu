@@ -213,6 +213,23 @@ const KsTables& get_ks_tables(Context* c, int nl) {
         pinv[i] = invmod(pm, qi); pinv_sh[i] = shoup(pinv[i], qi);
     }
     t.d_pinv = upload(c, pinv); t.d_pinv_sh = upload(c, pinv_sh);
+    // fused final factors of the inverse NTTs that feed the basis conversions
+    std::vector<u64> ms(2 * (size_t)c->M(), 0), ds(2 * (size_t)c->M(), 0);
+    for (int j = 0; j < t.nparts; j++) {
+        for (int i = t.dig_lo[j]; i < t.dig_hi[j]; i++) {
+            u64 qi = c->moduli[i], h = 1;
+            for (int k = t.dig_lo[j]; k < t.dig_hi[j]; k++) if (k != i) h = mulmod(h, c->moduli[k] % qi, qi);
+            u64 f = mulmod(c->h_mod[i].ninv, invmod(h, qi), qi);
+            ms[2 * i] = f; ms[2 * i + 1] = shoup(f, qi);
+        }
+    }
+    for (int k = 0; k < c->size_p; k++) {
+        int id = c->size_q + k; u64 pk = c->moduli[id], h = 1;
+        for (int k2 = 0; k2 < c->size_p; k2++) if (k2 != k) h = mulmod(h, c->moduli[c->size_q + k2] % pk, pk);
+        u64 f = mulmod(c->h_mod[id].ninv, invmod(h, pk), pk);
+        ds[2 * id] = f; ds[2 * id + 1] = shoup(f, pk);
+    }
+    t.d_modup_scale = upload(c, ms); t.d_moddown_scale = upload(c, ds);
     return c->ks.emplace(nl, std::move(t)).first->second;
 }
 

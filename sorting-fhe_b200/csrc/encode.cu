@@ -6,6 +6,7 @@
 // oracle's (oracle/ckks_prims.c orc_fft_special{,_inv}); every product/sum uses the explicit
 // round-to-nearest intrinsics (no FMA contraction) so coefficients are bit-identical to the oracle.
 #include "engine.h"
+#include <cstring>
 
 #define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
 
@@ -75,28 +76,108 @@ __global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, i
     out[(size_t)l * n + x] = r;
 }
 
+// stages of FFTSpecialInv with len <= 2048 on one contiguous block of min(size, 2048) points held in shared memory,
+// followed by the bit-reversal permutation, the 1/size and scaling-factor multiplications and the max-|.| reduction.
+// from_real: the block is built from the real input vector (imaginary parts and entries >= nvals are zero).
+__global__ void __launch_bounds__(1024)
+k_fft_inv_tail(double2* __restrict__ out, const double2* __restrict__ v, const double* __restrict__ real_in, int nvals, int from_real,
+               int size, int bits, const double2* __restrict__ ksi, const uint32_t* __restrict__ rot, int M, double inv_size,
+               double sf, u64* maxbits) {
+    extern __shared__ double2 blk[];
+    const int bsz = size < 2048 ? size : 2048, base = blockIdx.x * bsz;
+    for (int i = threadIdx.x; i < bsz; i += blockDim.x) {
+        const int g = base + i;
+        blk[i] = from_real ? make_double2(g < nvals ? real_in[g] : 0.0, 0.0) : v[g];
+    }
+    __syncthreads();
+    for (int len = bsz; len >= 2; len >>= 1) {
+        const int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
+        for (int t = threadIdx.x; t < bsz / 2; t += blockDim.x) {
+            const int i = (t / lenh) * len, j = t % lenh;
+            const int idx = (lenq - (int)(rot[j] % (uint32_t)lenq)) * gap;
+            const double2 a = blk[i + j], b = blk[i + j + lenh], w = ksi[idx];
+            const double ur = __dadd_rn(a.x, b.x), ui = __dadd_rn(a.y, b.y), vr = __dsub_rn(a.x, b.x), vi = __dsub_rn(a.y, b.y);
+            const double p1 = __dmul_rn(vr, w.x), p2 = __dmul_rn(vi, w.y), p3 = __dmul_rn(vr, w.y), p4 = __dmul_rn(vi, w.x);
+            blk[i + j] = make_double2(ur, ui);
+            blk[i + j + lenh] = make_double2(__dsub_rn(p1, p2), __dadd_rn(p3, p4));
+        }
+        __syncthreads();
+    }
+    double mx = 0.0;
+    for (int i = threadIdx.x; i < bsz; i += blockDim.x) {
+        const int g = base + i;
+        const int o = bits ? (int)(__brev((u32)g) >> (32 - bits)) : 0;
+        double2 a = blk[i];
+        a.x = __dmul_rn(__dmul_rn(a.x, inv_size), sf); a.y = __dmul_rn(__dmul_rn(a.y, inv_size), sf);
+        mx = fmax(mx, fmax(fabs(a.x), fabs(a.y)));
+        out[o] = a;
+    }
+    if (mx > 0.0) atomicMax(maxbits, (u64)__double_as_longlong(mx));
+}
+// one stage with len > 2048 (pairs further apart than a block); from_real as above
+__global__ void k_fft_inv_stage_big(double2* v, const double* __restrict__ real_in, int nvals, int from_real, int size, int len,
+                                    const double2* ksi, const uint32_t* rot, int M) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= size / 2) return;
+    int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
+    int i = (t / lenh) * len, j = t % lenh;
+    int idx = (lenq - (int)(rot[j] % (uint32_t)lenq)) * gap;
+    double2 a, b;
+    if (from_real) {
+        a = make_double2(i + j < nvals ? real_in[i + j] : 0.0, 0.0);
+        b = make_double2(i + j + lenh < nvals ? real_in[i + j + lenh] : 0.0, 0.0);
+    } else { a = v[i + j]; b = v[i + j + lenh]; }
+    const double2 w = ksi[idx];
+    double ur = __dadd_rn(a.x, b.x), ui = __dadd_rn(a.y, b.y), vr = __dsub_rn(a.x, b.x), vi = __dsub_rn(a.y, b.y);
+    double p1 = __dmul_rn(vr, w.x), p2 = __dmul_rn(vi, w.y), p3 = __dmul_rn(vr, w.y), p4 = __dmul_rn(vi, w.x);
+    v[i + j] = make_double2(ur, ui);
+    v[i + j + lenh] = make_double2(__dsub_rn(p1, p2), __dadd_rn(p3, p4));
+}
+
+// host staging: a ring of pinned chunks so that MakeCKKSPackedPlaintext never synchronises the stream
+static double* stage_values(Context* c, const double* h_values, int nvals) {
+    constexpr int RING = 32;
+    if (!c->enc_pinned) {
+        cudaHostAlloc((void**)&c->enc_pinned, (size_t)RING * (c->n / 2) * sizeof(double), cudaHostAllocDefault);
+        c->enc_events.resize(RING, nullptr);
+    }
+    const int slot = (int)(c->enc_ring_pos++ % RING);
+    if (c->enc_events[slot]) cudaEventSynchronize(c->enc_events[slot]);
+    else cudaEventCreateWithFlags(&c->enc_events[slot], cudaEventDisableTiming);
+    double* p = c->enc_pinned + (size_t)slot * (c->n / 2);
+    memcpy(p, h_values, (size_t)nvals * sizeof(double));
+    return p;
+}
+
 void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl) {
     int bits = 0; while ((1 << bits) < slots) bits++;
-    c->stats.kernel_launches += bits + 2;
+    const int big_stages = bits > 11 ? bits - 11 : 0;
+    c->stats.kernel_launches += big_stages + 2;
     if (c->dry) return;
-    double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
-    double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
-    std::vector<double> h(2 * (size_t)slots, 0.0);
-    ProfScope ps(c, KC_ENCODE, 8.0 * c->n * nl, bits + 2);
-    for (int i = 0; i < nvals; i++) h[2 * i] = h_values[i];
-    cudaMemcpyAsync(a, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream);
-    cudaStreamSynchronize(c->stream);  // h is a stack-lifetime staging buffer
-    const int M = 2 * c->n;
-    for (int len = slots; len >= 2; len >>= 1)
-        k_fft_inv_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(a, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
-    u64* mx = dev_alloc(c, 1);
-    cudaMemsetAsync(mx, 0, sizeof(u64), c->stream);
-    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0 / (double)slots, 1, sf, mx);
-    dim3 grid((c->n + 255) / 256, nl);
-    k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, mx);
-    dev_free(c, a);
-    dev_free(c, b);
-    dev_free(c, mx);
+    {
+        ProfScope ps(c, KC_ENCODE, 8.0 * c->n * nl, big_stages + 2);
+        double* d_in = (double*)dev_alloc(c, (size_t)(nvals > 0 ? nvals : 1));
+        double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
+        double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
+        u64* mx = dev_alloc(c, 1);
+        double* staged = stage_values(c, h_values, nvals);
+        cudaMemcpyAsync(d_in, staged, (size_t)nvals * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+        cudaEventRecord(c->enc_events[(c->enc_ring_pos - 1) % c->enc_events.size()], c->stream);
+        cudaMemsetAsync(mx, 0, sizeof(u64), c->stream);
+        const int M = 2 * c->n;
+        int from_real = 1;
+        for (int len = slots; len > 2048; len >>= 1) {
+            k_fft_inv_stage_big<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(a, d_in, nvals, from_real, slots, len,
+                                                                                  (const double2*)c->d_ksi, c->d_rot, M);
+            from_real = 0;
+        }
+        const int bsz = slots < 2048 ? slots : 2048, threads = bsz / 2 < 32 ? 32 : (bsz / 2 > 1024 ? 1024 : bsz / 2);
+        k_fft_inv_tail<<<slots / bsz, threads, (size_t)bsz * sizeof(double2), c->stream>>>(
+            b, a, d_in, nvals, from_real, slots, bits, (const double2*)c->d_ksi, c->d_rot, M, 1.0 / (double)slots, sf, mx);
+        dim3 grid((c->n + 255) / 256, nl);
+        k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, mx);
+        dev_free(c, d_in); dev_free(c, a); dev_free(c, b); dev_free(c, mx);
+    }
     launch_ntt(c, out, nl, mods_q(nl), false);
 }
 

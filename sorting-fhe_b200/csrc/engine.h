@@ -19,6 +19,22 @@ struct LimbMods {          // passed by value to kernels: row r of a bundle uses
     short m[MAX_LIMBS];
 };
 
+// logical row r of a batched launch -> physical limb row: (r / grp) * stride + off + r % grp
+struct RowMap { int grp = 1 << 30, stride = 0, off = 0, mul = 1; };
+__host__ __device__ inline int row_of(const RowMap& m, int r) { return (r / m.grp) * m.stride + m.off + (r % m.grp) * m.mul; }
+
+// work fused into an NTT launch: a prologue applied to the words as they are first loaded, an epilogue applied to
+// the canonical results as they are stored
+enum { PRO_NONE = 0, PRO_SWITCHMOD = 1 };
+enum { EPI_NONE = 0, EPI_RESCALE = 1 };
+struct NttFuse {
+    int pro = PRO_NONE, pro_mod = 0;      // PRO_SWITCHMOD: modulus id the source limb is reduced by
+    int epi = EPI_NONE;
+    const u64* epi_in = nullptr;          // EPI_RESCALE: minuend limbs, addressed through emap
+    RowMap emap;
+    const u64* epi_pairs = nullptr;       // EPI_RESCALE: [M] (q_last^-1 mod q_i, Shoup) pairs
+};
+
 struct ConvTables {        // ApproxSwitchCRTBasis tables for one (source basis -> target basis)
     int nin, nout;
     short in_ids[MAX_LIMBS], out_ids[MAX_LIMBS];
@@ -34,6 +50,8 @@ struct KsTables {          // per number-of-Q-limbs tables of the hybrid key swi
     ConvTables moddown;              // P -> Q_l
     u64* d_pinv;                     // [nl] P^-1 mod q_i
     u64* d_pinv_sh;
+    u64* d_modup_scale;              // [M] pairs: n^-1 * Qhat_i^-1 (digit of limb i) -- final factor of the ModUp INTT
+    u64* d_moddown_scale;            // [M] pairs: n^-1 * Phat_k^-1 -- final factor of the ModDown INTT
 };
 
 struct EvalKey {           // hybrid evk: [part][2 (b, a)][sizeQ+sizeP][n], Montgomery form
@@ -71,12 +89,16 @@ struct Context {
     double* d_ksi = nullptr;                // [2n+1] complex roots for the special FFT
     uint32_t* d_rot = nullptr;              // [n/2] 5^j mod 2n
     std::map<int, KsTables> ks;             // keyed by nl
+    std::map<int, u64*> rescale_pairs;      // keyed by nl_in: device [M] (q_last^-1 mod q_i, Shoup) pairs
     // keys (device)
     u64* d_secret = nullptr;                // [M][n] EVALUATION
     u64* d_pk = nullptr;                    // [2][sizeQ][n]  (b, a)
     EvalKey relin;
     std::map<uint32_t, EvalKey> rot;        // automorphism index -> key
     uint64_t enc_counter = 0;
+    double* enc_pinned = nullptr;           // pinned staging ring for MakeCKKSPackedPlaintext inputs
+    std::vector<cudaEvent_t> enc_events;
+    uint64_t enc_ring_pos = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     Stats stats;
@@ -119,7 +141,8 @@ LimbMods mods_range(int lo, int hi);              // moduli lo..hi-1
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse);
 // out-of-place capable form; scale_pairs (inverse only): [M] (factor, Shoup) pairs indexed by modulus id that
 // replace the n^-1 factor (nullptr = n^-1)
-void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs);
+void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs,
+                   RowMap smap, RowMap dmap, const NttFuse* fuse = nullptr);
 
 void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op /*0 add 1 sub*/);
 void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m);
@@ -132,13 +155,16 @@ void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u
 void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in);
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
-void launch_base_conv(Context* c, u64* out, const u64* in, const ConvTables& t);
+#define MAX_CONV_IN 24
+#define MAX_CONV_OUT 88
+struct ConvGroup { int in_row0, nin, out_row0, nout; const u64* hatmod; /* [nin][nout] Montgomery form */ };
+struct ConvBatch { int ng; ConvGroup g[4]; short out_ids[4][MAX_CONV_OUT]; };
+
+void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B);
 void launch_ks_inner2(Context* c, u64* acc /*[2][nl+K][n]*/, const u64* src, const u64* conv, const EvalKey& k,
                       const KsTables& t);
-void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* addend, int nl,
+void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, int nl,
                           uint32_t auto_k, const KsTables& t);
-void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod);
-void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in);
 void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words);
 void launch_to_mont(Context* c, u64* data, int rows, const LimbMods& m);
 void launch_from_mont(Context* c, u64* data, int rows, const LimbMods& m);

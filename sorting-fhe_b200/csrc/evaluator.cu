@@ -180,30 +180,56 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
     if (!c->dry && !key.d) throw std::runtime_error("key switch: evaluation key not generated");
     const KsTables& t = get_ks_tables(c, nl);
     const int K = c->size_p, next = nl + K;
+    if (K > MAX_CONV_IN || c->alpha > MAX_CONV_IN || next > MAX_CONV_OUT) throw std::runtime_error("key switch: parameter set too large");
+    // ---- ModUp: INTT (x n^-1 Qhat^-1 fused) -> basis conversion of every digit -> NTT of all converted limbs
     u64* coef = dev_alloc(c, words(c, nl));
-    launch_copy_rows(c, coef, src, words(c, nl));
-    launch_ntt(c, coef, nl, mods_q(nl), true);
-    u64* conv = dev_alloc(c, words(c, t.nparts * next));
-    for (int j = 0; j < t.nparts; j++) {
-        u64* cj = c->dry ? nullptr : conv + words(c, j * next);
-        launch_base_conv(c, cj, c->dry ? nullptr : coef + words(c, t.dig_lo[j]), t.modup[j]);
-        LimbMods m; m.n = t.modup[j].nout;
-        for (int i = 0; i < m.n; i++) m.m[i] = t.modup[j].out_ids[i];
-        launch_ntt(c, cj, m.n, m, false);
+    launch_ntt_ex(c, coef, src, nl, mods_q(nl), true, t.d_modup_scale, RowMap{}, RowMap{});
+    int conv_rows = 0;
+    for (int j = 0; j < t.nparts; j++) conv_rows += t.modup[j].nout;
+    u64* conv = dev_alloc(c, words(c, conv_rows));
+    {
+        ConvBatch B; B.ng = t.nparts;
+        LimbMods m; m.n = 0;
+        int row0 = 0;
+        for (int j = 0; j < t.nparts; j++) {
+            const ConvTables& ct = t.modup[j];
+            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod};
+            for (int i = 0; i < ct.nout; i++) { B.out_ids[j][i] = ct.out_ids[i]; if (m.n < MAX_LIMBS) m.m[m.n++] = ct.out_ids[i]; }
+            row0 += ct.nout;
+        }
+        launch_conv_batch(c, conv, coef, B);
+        if (conv_rows <= MAX_LIMBS) launch_ntt(c, conv, conv_rows, m, false);
+        else {
+            for (int j = 0, r0 = 0; j < t.nparts; r0 += t.modup[j].nout, j++) {
+                LimbMods mj; mj.n = t.modup[j].nout;
+                for (int i = 0; i < mj.n; i++) mj.m[i] = t.modup[j].out_ids[i];
+                launch_ntt(c, c->dry ? nullptr : conv + words(c, r0), mj.n, mj, false);
+            }
+        }
     }
+    // ---- inner product with the evaluation key over Q_l u P
     u64* acc = dev_alloc(c, words(c, 2 * next));
     launch_ks_inner2(c, acc, src, conv, key, t);
     dev_free(c, coef); dev_free(c, conv);
-    u64* conv2 = dev_alloc(c, words(c, nl));
-    for (int h = 0; h < 2; h++) {
-        u64* acch = c->dry ? nullptr : acc + words(c, h * next);
-        u64* pp = c->dry ? nullptr : acch + words(c, nl);
-        launch_ntt(c, pp, K, mods_range(c->size_q, c->size_q + K), true);
-        launch_base_conv(c, conv2, pp, t.moddown);
-        launch_ntt(c, conv2, nl, mods_q(nl), false);
-        launch_moddown_final(c, c->dry ? nullptr : out + words(c, h * nl), acch, conv2, h == 0 ? add0 : add1, nl, auto_k, t);
+    // ---- ModDown of both polynomials: INTT of the P limbs (x n^-1 Phat^-1) -> conversion to Q_l -> NTT -> epilogue
+    u64* pp = dev_alloc(c, words(c, 2 * K));
+    {
+        LimbMods mp; mp.n = K;
+        for (int k = 0; k < K; k++) mp.m[k] = (short)(c->size_q + k);
+        launch_ntt_ex(c, pp, acc, 2 * K, mp, true, t.d_moddown_scale, RowMap{K, next, nl}, RowMap{});
     }
-    dev_free(c, conv2); dev_free(c, acc);
+    u64* conv2 = dev_alloc(c, words(c, 2 * nl));
+    {
+        ConvBatch B; B.ng = 2;
+        for (int h = 0; h < 2; h++) {
+            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod};
+            for (int i = 0; i < nl; i++) B.out_ids[h][i] = (short)i;
+        }
+        launch_conv_batch(c, conv2, pp, B);
+    }
+    launch_ntt(c, conv2, 2 * nl, mods_q(nl), false);
+    launch_moddown_final(c, out, acc, conv2, add0, add1, nl, auto_k, t);
+    dev_free(c, pp); dev_free(c, conv2); dev_free(c, acc);
 }
 
 // ------------------------------------------------------------------ public evaluator ops

@@ -7,10 +7,17 @@
 // EvalRotate / implicit rescale; semantics pinned by
 // oracle/ckks_prims.c (orc_v*, orc_automorph_eval, orc_switch_modulus).
 #include "engine.h"
+#include <map>
 
 struct LimbScalars { u64 v[MAX_LIMBS]; u64 sh[MAX_LIMBS]; };
 
 static inline dim3 grid_for(const Context* c, int rows) { return dim3((c->n + 255) / 256, rows); }
+// streaming kernels below move two coefficients (16 bytes) per thread per operand
+static inline dim3 grid_for2(const Context* c, int rows) { return dim3((c->n / 2 + 255) / 256, rows); }
+typedef ulonglong2 u64x2;
+__device__ __forceinline__ u64x2 ld2(const u64* p, size_t o) { return *reinterpret_cast<const u64x2*>(p + o); }
+__device__ __forceinline__ void st2(u64* p, size_t o, u64 a, u64 b) { *reinterpret_cast<u64x2*>(p + o) = make_ulonglong2(a, b); }
+#define X2_PROLOGUE int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x); if (x >= n) return
 #define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
 
 LimbMods mods_q(int nl) { LimbMods m; m.n = nl; for (int i = 0; i < nl; i++) m.m[i] = (short)i; return m; }
@@ -44,69 +51,75 @@ void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m)
 }
 
 __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    X2_PROLOGUE;
     int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
     size_t o = (size_t)row * n + x, ob = (size_t)(row % rows_b) * n + x;
-    out[o] = barrett_mul(a[o], b[ob], m);
+    const u64x2 va = ld2(a, o), vb = ld2(b, ob);
+    st2(out, o, barrett_mul(va.x, vb.x, m), barrett_mul(va.y, vb.y, m));
 }
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows_out * c->n); k_mul<<<grid_for(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows_out * c->n); k_mul<<<grid_for2(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
 }
 
 __global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    X2_PROLOGUE;
     int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
-    size_t o = (size_t)row * n + x; out[o] = shoup_mul(d[o], s.v[l], s.sh[l], q);
+    size_t o = (size_t)row * n + x;
+    const u64x2 v = ld2(d, o);
+    st2(out, o, shoup_mul(v.x, s.v[l], s.sh[l], q), shoup_mul(v.y, s.v[l], s.sh[l], q));
 }
 void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const LimbMods& m, const u64* hs) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
-    k_mul_scalar<<<grid_for(c, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, c->n, s);
+    k_mul_scalar<<<grid_for2(c, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, c->n, s);
 }
 
 __global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, int nl, LimbScalars s, int negate) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    X2_PROLOGUE;
     int row = blockIdx.y, l = row % nl; u64 q = mi[l].q;
     size_t o = (size_t)row * n + x;
-    u64 v = d[o];
-    if (negate) v = neg_mod(v, q);
-    if (row < nl) v = add_mod(v, s.v[l], q);
-    out[o] = v;
+    u64x2 v = ld2(d, o);
+    if (negate) { v.x = neg_mod(v.x, q); v.y = neg_mod(v.y, q); }
+    if (row < nl) { v.x = add_mod(v.x, s.v[l], q); v.y = add_mod(v.y, s.v[l], q); }
+    st2(out, o, v.x, v.y);
 }
 void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* hs, bool negate) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * parts * nl * c->n);
     LimbScalars s;
     for (int i = 0; i < nl; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
-    k_add_scalar<<<grid_for(c, parts * nl), 256, 0, c->stream>>>(out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
+    k_add_scalar<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
 }
 
 __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
                                int sub) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    X2_PROLOGUE;
     int row = blockIdx.y, p = row / nl; u64 q = mi[row % nl].q;
     size_t o = (size_t)row * n + x;
-    u64 a = p < xparts ? xs[o] : 0, b = p < yparts ? ys[o] : 0;
-    out[o] = sub ? sub_mod(a, b, q) : add_mod(a, b, q);
+    const u64x2 z = make_ulonglong2(0, 0);
+    const u64x2 a = p < xparts ? ld2(xs, o) : z, b = p < yparts ? ld2(ys, o) : z;
+    if (sub) st2(out, o, sub_mod(a.x, b.x, q), sub_mod(a.y, b.y, q));
+    else st2(out, o, add_mod(a.x, b.x, q), add_mod(a.y, b.y, q));
 }
 void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub) {
     int parts = xparts > yparts ? xparts : yparts;
     KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * (xparts + yparts + parts));
-    k_addsub_parts<<<grid_for(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0);
+    k_addsub_parts<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0);
 }
 
 // (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
 __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi, int n, int nl) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    X2_PROLOGUE;
     int l = blockIdx.y; const ModInfo m = mi[l];
     size_t o = (size_t)l * n + x, P = (size_t)nl * n;
-    u64 a0 = a[o], a1 = a[o + P], b0 = b[o], b1 = b[o + P];
-    d3[o] = barrett_mul(a0, b0, m);
-    d3[o + P] = add_mod(barrett_mul(a0, b1, m), barrett_mul(a1, b0, m), m.q);
-    d3[o + 2 * P] = barrett_mul(a1, b1, m);
+    const u64x2 a0 = ld2(a, o), a1 = ld2(a, o + P), b0 = ld2(b, o), b1 = ld2(b, o + P);
+    st2(d3, o, barrett_mul(a0.x, b0.x, m), barrett_mul(a0.y, b0.y, m));
+    st2(d3, o + P, add_mod(barrett_mul(a0.x, b1.x, m), barrett_mul(a1.x, b0.x, m), m.q),
+        add_mod(barrett_mul(a0.y, b1.y, m), barrett_mul(a1.y, b0.y, m), m.q));
+    st2(d3, o + 2 * P, barrett_mul(a1.x, b1.x, m), barrett_mul(a1.y, b1.y, m));
 }
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 56.0 * nl * c->n); k_tensor<<<grid_for(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 56.0 * nl * c->n); k_tensor<<<grid_for2(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
 }
 
 // out[p] = in[brev(idx)], j = brev(p), idx = ((2j+1)k mod 2n) >> 1  (PrecomputeAutoMap)
@@ -123,51 +136,36 @@ void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k)
     KL(c); ProfScope ps(c, KC_AUTOMORPH, 16.0 * rows * c->n); k_automorph<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, c->log_n, k);
 }
 
-// rescale: t[p][i] = centred switch of last[p] (coefficient format, mod q_last) to q_i
-__global__ void k_rescale_prep(u64* t, const u64* last, const ModInfo* mi, int n, int nl_out, int last_mod) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
-    int row = blockIdx.y, p = row / nl_out, i = row % nl_out;
-    u64 ql = mi[last_mod].q, qi = mi[i].q, half = ql >> 1;
-    u64 v = last[(size_t)p * n + x], r;
-    if (v > half) { u64 neg = (ql - v) % qi; r = neg ? qi - neg : 0; } else r = v % qi;
-    t[(size_t)row * n + x] = r;
-}
-void launch_rescale_prep(Context* c, u64* t, const u64* last, int parts, int nl_out, int last_mod) {
-    KL(c); ProfScope ps(c, KC_RESCALE, 8.0 * c->n * parts * (nl_out + 1)); k_rescale_prep<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(t, last, c->d_mod, c->n, nl_out, last_mod);
-}
-// out[p][i] = (in[p][i] - t[p][i]) * q_last^-1 mod q_i ; in has nl_in = nl_out + 1 limbs per part
-__global__ void k_rescale_final(u64* out, const u64* in, const u64* t, const ModInfo* mi, int n, int nl_out, LimbScalars s) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
-    int row = blockIdx.y, p = row / nl_out, i = row % nl_out;
-    u64 q = mi[i].q;
-    u64 a = in[((size_t)p * (nl_out + 1) + i) * n + x], b = t[(size_t)row * n + x];
-    out[(size_t)row * n + x] = shoup_mul(sub_mod(a, b, q), s.v[i], s.sh[i], q);
-}
 static u64 host_powmod(u64 a, u64 e, u64 q) {
     unsigned __int128 r = 1, b = a % q;
     while (e) { if (e & 1) r = r * b % q; b = b * b % q; e >>= 1; }
     return (u64)r;
 }
-void launch_rescale_final(Context* c, u64* out, const u64* in, const u64* t, int parts, int nl_in) {
-    KL(c); ProfScope ps(c, KC_RESCALE, 8.0 * c->n * parts * (3.0 * nl_in - 3));
-    LimbScalars s; int nl_out = nl_in - 1; u64 ql = c->moduli[nl_in - 1];
-    for (int i = 0; i < nl_out; i++) { u64 q = c->moduli[i]; s.v[i] = host_powmod(ql % q, q - 2, q); s.sh[i] = host_shoup(s.v[i], q); }
-    k_rescale_final<<<grid_for(c, parts * nl_out), 256, 0, c->stream>>>(out, in, t, c->d_mod, c->n, nl_out, s);
-}
-
-// DropLastElementAndScale of `parts` polynomials with nl_in limbs each -> out [parts][nl_in-1][n]
+// DropLastElementAndScale of `parts` polynomials with nl_in limbs each -> out [parts][nl_in-1][n]:
+// INTT of the last limbs, then ONE forward NTT launch over all remaining limbs whose prologue switches the last
+// limb's coefficients to the row modulus and whose epilogue forms (c_i - that) * q_last^-1.
 void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in) {
-    const int nl = nl_in;
+    const int nl = nl_in, nlo = nl_in - 1;
     const size_t n = c->n;
     u64* last = dev_alloc(c, (size_t)parts * n);
-    for (int p = 0; p < parts; p++)
-        launch_copy_rows(c, c->dry ? nullptr : last + p * n, c->dry ? nullptr : in + ((size_t)p * nl + nl - 1) * n, n);
-    launch_ntt(c, last, parts, mods_range(nl - 1, nl), true);
-    u64* t = dev_alloc(c, (size_t)parts * (nl - 1) * n);
-    launch_rescale_prep(c, t, last, parts, nl - 1, nl - 1);
-    launch_ntt(c, t, parts * (nl - 1), mods_q(nl - 1), false);
-    launch_rescale_final(c, out, in, t, parts, nl);
-    dev_free(c, last); dev_free(c, t);
+    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, nullptr, RowMap{1, nl, nl - 1, 1}, RowMap{});
+    auto it = c->rescale_pairs.find(nl);
+    if (it == c->rescale_pairs.end()) {
+        std::vector<u64> v(2 * (size_t)c->M(), 0); u64 ql = c->moduli[nl - 1];
+        for (int i = 0; i < nlo; i++) { u64 q = c->moduli[i]; v[2 * i] = host_powmod(ql % q, q - 2, q); v[2 * i + 1] = host_shoup(v[2 * i], q); }
+        u64* d = nullptr;
+        if (!c->dry) { cudaMalloc(&d, v.size() * sizeof(u64)); cudaMemcpy(d, v.data(), v.size() * sizeof(u64), cudaMemcpyHostToDevice); }
+        it = c->rescale_pairs.emplace(nl, d).first;
+    }
+    NttFuse f;
+    f.pro = PRO_SWITCHMOD; f.pro_mod = nl - 1;
+    f.epi = EPI_RESCALE; f.epi_in = in; f.emap = RowMap{nlo, nl, 0, 1}; f.epi_pairs = it->second;
+    c->stats.kernel_launches += 0;
+    {
+        ProfScope ps(c, KC_RESCALE, 0.0, 0);   // the fused launch is accounted to the NTT class
+    }
+    launch_ntt_ex(c, out, last, parts * nlo, mods_q(nlo), false, nullptr, RowMap{nlo, 1, 0, 0}, RowMap{}, &f);
+    dev_free(c, last);
 }
 
 void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words) {

@@ -11,45 +11,40 @@
 #include "engine.h"
 
 #define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
-#define MAX_CONV_IN 24
 
-struct ConvIds { short in_ids[MAX_CONV_IN]; short out_ids[MAX_LIMBS]; };
-
-// out[j][x] = sum_i ([in[i][x] * hatinv_i]_{q_i}) * hatmod[i][j]  mod t_j     (no correction term)
+// Batched ApproxSwitchCRTBasis on PRE-SCALED inputs: the inverse NTT that produced `in` already multiplied limb i by
+// n^-1 * Qhat_i^-1 (one fused Shoup factor), so y_i = in_i and
+//   out[j][x] = sum_i y_i[x] * (Qhat_i mod t_j)   mod t_j            (no correction term, 128-bit accumulate)
+// Up to 4 groups per launch: the digits of a ModUp, or the two polynomials of a ModDown.
 __global__ void __launch_bounds__(256)
-k_base_conv(u64* __restrict__ out, const u64* __restrict__ in, ConvIds ids, int nin, int nout,
-            const u64* __restrict__ hatinv, const u64* __restrict__ hatinv_sh, const u64* __restrict__ hatmod,
-            const ModInfo* __restrict__ mi, int n) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
+k_conv_batch(u64* __restrict__ out, const u64* __restrict__ in, const ConvBatch B, const ModInfo* __restrict__ mi, int n, int ysplit) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
+    const int gi = blockIdx.y / ysplit, part = blockIdx.y % ysplit;
+    const ConvGroup g = B.g[gi];
     u64 y[MAX_CONV_IN];
 #pragma unroll 4
-    for (int i = 0; i < nin; i++) {
-        u64 q = mi[ids.in_ids[i]].q;
-        y[i] = shoup_mul(in[(size_t)i * n + x], hatinv[i], hatinv_sh[i], q);
-    }
-    // targets are split over grid.y to expose more parallelism
-    for (int j = blockIdx.y; j < nout; j += gridDim.y) {
-        const ModInfo m = mi[ids.out_ids[j]];
+    for (int i = 0; i < g.nin; i++) y[i] = in[(size_t)(g.in_row0 + i) * n + x];
+    for (int j = part; j < g.nout; j += ysplit) {
+        const ModInfo m = mi[B.out_ids[gi][j]];
         u64 lo = 0, hi = 0;
-        for (int i = 0; i < nin; i++) mac128(lo, hi, y[i], hatmod[(size_t)i * nout + j]);
-        out[(size_t)j * n + x] = mont_reduce(lo, hi, m.q, m.qinv);
+        for (int i = 0; i < g.nin; i++) mac128(lo, hi, y[i], __ldg(g.hatmod + (size_t)i * g.nout + j));
+        out[(size_t)(g.out_row0 + j) * n + x] = mont_reduce(lo, hi, m.q, m.qinv);
     }
 }
-void launch_base_conv(Context* c, u64* out, const u64* in, const ConvTables& t) {
+void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) {
     KL(c);
-    ProfScope ps(c, KC_BASECONV, 8.0 * c->n * (t.nin + t.nout));
-    ConvIds ids;
-    for (int i = 0; i < t.nin; i++) ids.in_ids[i] = t.in_ids[i];
-    for (int j = 0; j < t.nout; j++) ids.out_ids[j] = t.out_ids[j];
-    int ysplit = t.nout < 4 ? t.nout : 4;
-    dim3 grid((c->n + 255) / 256, ysplit);
-    k_base_conv<<<grid, 256, 0, c->stream>>>(out, in, ids, t.nin, t.nout, t.d_hatinv, t.d_hatinv_sh, t.d_hatmod, c->d_mod, c->n);
+    double rows = 0;
+    for (int i = 0; i < B.ng; i++) rows += B.g[i].nin + B.g[i].nout;
+    ProfScope ps(c, KC_BASECONV, 8.0 * c->n * rows);
+    const int ysplit = 4;
+    dim3 grid((c->n + 255) / 256, B.ng * ysplit);
+    k_conv_batch<<<grid, 256, 0, c->stream>>>(out, in, B, c->d_mod, c->n, ysplit);
 }
 
 // acc[h][e][x] = sum_j dig_j[e][x] * key[j][h][mod(e)][x]; dig_j[e] is the source polynomial row e
 // when e is one of digit j's own limbs, else row of the converted complement (compact layout).
-struct DigitMap { int lo[4], hi[4]; };
+struct DigitMap { int lo[4], hi[4], base[4]; };   // base: first row of digit j's converted complement in conv
 __global__ void __launch_bounds__(256)
 k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __restrict__ conv, const u64* __restrict__ key,
            DigitMap dm, int nparts, int nl, int size_q, int size_p, int M, const ModInfo* __restrict__ mi, int n) {
@@ -64,7 +59,7 @@ k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __rest
         if (e >= dm.lo[j] && e < dm.hi[j]) d = src[(size_t)e * n + x];
         else {
             int r = e < dm.lo[j] ? e : e - (dm.hi[j] - dm.lo[j]);
-            d = conv[((size_t)j * next + r) * n + x];
+            d = conv[((size_t)dm.base[j] + r) * n + x];
         }
         const u64* kb = key + ((size_t)(j * 2 + 0) * M + mid) * n + x;
         mac128(l0, h0, d, kb[0]);
@@ -77,34 +72,41 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
     KL(c);
     ProfScope ps(c, KC_KSINNER, 8.0 * c->n * (t.nl + c->size_p) * (3.0 * t.nparts + 2));
     DigitMap dm;
-    for (int j = 0; j < 4; j++) { dm.lo[j] = j < t.nparts ? t.dig_lo[j] : 0; dm.hi[j] = j < t.nparts ? t.dig_hi[j] : 0; }
+    for (int j = 0, b = 0; j < 4; j++) {
+        dm.lo[j] = j < t.nparts ? t.dig_lo[j] : 0; dm.hi[j] = j < t.nparts ? t.dig_hi[j] : 0; dm.base[j] = b;
+        if (j < t.nparts) b += t.modup[j].nout;
+    }
     dim3 grid((c->n + 255) / 256, t.nl + c->size_p);
     k_ks_inner<<<grid, 256, 0, c->stream>>>(acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
 }
 
-// out[i] = addend[i] + (acc[i] - conv[i]) * P^-1 mod q_i   (ApproxModDown epilogue; addend optional).
-// With auto_k != 0 the result is written through the automorphism X -> X^k (EVALUATION-format index
-// permutation of OpenFHE's PrecomputeAutoMap): out[p] = value[src(p)].
-__global__ void k_moddown_final(u64* out, const u64* acc, const u64* conv, const u64* addend, const u64* pinv,
-                                const u64* pinv_sh, const ModInfo* mi, int n, int logn, u32 auto_k) {
+// ApproxModDown epilogue for both polynomials h = 0,1 of a key switch:
+//   out[h][i] = addend_h[i] + (acc[h][i] - conv[h][i]) * P^-1 mod q_i          (addends optional)
+// With auto_k != 0 the result is written through the automorphism X -> X^k (EVALUATION-format index permutation
+// of OpenFHE's PrecomputeAutoMap): out[p] = value[src(p)].
+__global__ void k_moddown_final(u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, const u64* pinv,
+                                const u64* pinv_sh, const ModInfo* mi, int n, int logn, int nl, int next, u32 auto_k) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    int i = blockIdx.y; u64 q = mi[i].q;
+    const int h = blockIdx.y / nl, i = blockIdx.y % nl;
+    const u64 q = mi[i].q;
     int x = p;
     if (auto_k) {
         u32 j = __brev((u32)p) >> (32 - logn);
         u32 idx = (u32)((((2ull * j + 1) * auto_k) & (2ull * n - 1)) >> 1);
         x = (int)(__brev(idx) >> (32 - logn));
     }
-    size_t o = (size_t)i * n + x;
-    u64 r = shoup_mul(sub_mod(acc[o], conv[o], q), pinv[i], pinv_sh[i], q);
+    const size_t o = (size_t)i * n + x;
+    u64 r = shoup_mul(sub_mod(acc[(size_t)h * next * n + o], conv[(size_t)h * nl * n + o], q), pinv[i], pinv_sh[i], q);
+    const u64* addend = h ? add1 : add0;
     if (addend) r = add_mod(r, addend[o], q);
-    out[(size_t)i * n + p] = r;
+    out[((size_t)h * nl + i) * n + p] = r;
 }
-void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* addend, int nl,
+void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, int nl,
                           uint32_t auto_k, const KsTables& t) {
     KL(c);
-    ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (addend ? 4 : 3));
-    dim3 grid((c->n + 255) / 256, nl);
-    k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, addend, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, auto_k);
+    ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (6 + (add0 ? 1 : 0) + (add1 ? 1 : 0)));
+    dim3 grid((c->n + 255) / 256, 2 * nl);
+    k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, add0, add1, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, nl,
+                                                 nl + c->size_p, auto_k);
 }

@@ -94,14 +94,17 @@ __device__ __forceinline__ void round8(u64 (&r)[8], const tw_t* __restrict__ W, 
 }
 
 struct NttArgs {
-    u64* dst;                // [rows][n]
-    const u64* src;          // [rows][n] (== dst for in-place)
+    u64* dst;                // limb rows; logical row r lives at row_of(dmap, r)
+    const u64* src;          // (== dst for in-place)
+    RowMap smap, dmap;
     const ModInfo* mi;
     const tw_t* tw;          // [M][n] forward or inverse twiddle pairs
     const tw_t* scale;       // INV only: final factor (n^-1 [* extra]) as Shoup pair, indexed by modulus id
     int logn, T, a;          // T = tile bits, a = logn - T stages in pass A
     int pass;                // 0 = pass A (strided), 1 = pass B (contiguous)
     int final_pass;          // this pass produces the final output (canonicalise / scale)
+    int first_pass;          // this pass reads the launch's input (prologue applies)
+    NttFuse f;               // optional work fused into the first load / last store (engine.h)
 };
 
 // rounds of one pass: window position p and stage range [J0,J1) per round (host fills, <= 4 rounds)
@@ -154,8 +157,8 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
     const int cb = T - a_;                                // cb: column bits of a pass-A tile
     const tw_t* W = A.tw + ((size_t)mid << logn);
-    const u64* src = A.src + ((size_t)row << logn);
-    u64* dst = A.dst + ((size_t)row << logn);
+    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
+    u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
     const int tile = blockIdx.x, u = threadIdx.x;
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     // global word offset of tile-local index L
@@ -165,6 +168,15 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     // position of tile-local bit 0 in the element index, and the index bits above the tile
     // pass B: E = tile << T | L.   pass A: E = (row bits = L >> cb) << T | (tile << cb | col): stages only touch
     // the row bits, whose position in E is T + (bit - cb).
+    if (!strided) {
+        // pass B touches, per local stage sl, the contiguous run W[2^(a+sl) + tile 2^sl + [0, 2^sl)) exactly once: pull
+        // all of it (2^T - 1 pairs, one 128-byte line per prefetch) into L1 now so that no round waits on DRAM
+        for (int sl = 3; sl < T; sl++) {
+            const tw_t* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
+            for (int g = u * 8; g < (1 << sl); g += 8 * (1 << (T - 3)))
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
+        }
+    }
     u64 r[8];
     int t_done = 0;   // inverse: number of GS stages already applied to the data (for the lazy offset)
     if (INV) t_done = strided ? T : 0;
@@ -174,6 +186,18 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         if (ri == 0) {
 #pragma unroll
             for (int k = 0; k < 8; k++) r[k] = src[gaddr(local_index(u, k, p))];
+            if (!INV && A.first_pass && A.f.pro == PRO_SWITCHMOD) {
+                // rescale: the source limb holds coefficients mod q_last; centred switch to this row's modulus
+                const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const bool neg = r[k] > half;
+                    u64 a = neg ? ql - r[k] : r[k];
+                    a -= __umul64hi(a, mi.qrecip) * q;
+                    if (a >= q) a -= q;
+                    r[k] = neg ? (a ? q - a : 0) : a;
+                }
+            }
         } else {
             __syncthreads();
 #pragma unroll
@@ -197,6 +221,16 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
                     for (int k = 0; k < 8; k++) {   // any value < 2^64 -> [0, q)
                         u64 v = r[k] - __umul64hi(r[k], mi.qrecip) * q;
                         r[k] = v >= q ? v - q : v;
+                    }
+                    if (A.f.epi == EPI_RESCALE) {
+                        // out = (in - NTT(switched last limb)) * q_last^-1   (DropLastElementAndScale)
+                        const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
+                        const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            const u64 x = ein[gaddr(local_index(u, k, p))];
+                            r[k] = shoup_mul(sub_mod(x, r[k], q), sc.x, sc.y, q);
+                        }
                     }
                 } else {
                     const tw_t sc = A.scale[mid];
@@ -235,7 +269,8 @@ static void launch_pass(Context* c, dim3 grid, int threads, size_t smem, const N
     }
 }
 
-void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs) {
+void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs,
+                   RowMap smap, RowMap dmap, const NttFuse* fuse) {
     c->stats.kernel_launches += (c->log_n > TB_MAX) ? 2 : 1;
     if (c->dry || rows == 0) return;
     ProfScope ps(c, KC_NTT, 16.0 * rows * c->n, (c->log_n > TB_MAX) ? 2 : 1);
@@ -245,6 +280,9 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     dim3 grid(c->n >> T, rows);
     NttArgs A;
     A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a;
+    A.smap = smap; A.dmap = dmap;
+    if (fuse) A.f = *fuse; else A.f = NttFuse{};
+    A.first_pass = 1;
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : c->d_ninv_pairs);
     if (!inverse) {
@@ -252,7 +290,7 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
         if (a > 0) {
             A.pass = 0; A.final_pass = 0;
             launch_pass<false, 0>(c, grid, threads, smem, A, make_sched(T, a, false), m);
-            A.src = dst;
+            A.src = dst; A.smap = dmap; A.first_pass = 0;
         }
         A.pass = 1; A.final_pass = 1;
         launch_pass<false, 1>(c, grid, threads, smem, A, make_sched(T, T, false), m);
@@ -260,12 +298,12 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
         A.src = src; A.pass = 1; A.final_pass = a == 0;
         launch_pass<true, 1>(c, grid, threads, smem, A, make_sched(T, T, true), m);
         if (a > 0) {
-            A.src = dst; A.pass = 0; A.final_pass = 1;
+            A.src = dst; A.smap = dmap; A.pass = 0; A.final_pass = 1; A.first_pass = 0;
             launch_pass<true, 0>(c, grid, threads, smem, A, make_sched(T, a, true), m);
         }
     }
 }
 
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse) {
-    launch_ntt_ex(c, data, data, rows, m, inverse, nullptr);
+    launch_ntt_ex(c, data, data, rows, m, inverse, nullptr, RowMap{}, RowMap{}, nullptr);
 }
