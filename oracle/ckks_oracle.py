@@ -9,7 +9,7 @@ core/lattice/hal/default/dcrtpoly-impl.h) from knowledge of that source.
 
 PARITY STATUS: "parity unpinned" at the limb level -- no reference test pins a ciphertext
 limb, and OpenFHE cannot be built here.  What IS pinned: the decrypted known-answer vectors of
-tests/CompareTest.cpp, tests/SignTest.cpp (see tests/test_oracle_kat.py) and the level budgets
+tests/CompareTest.cpp, tests/SignTest.cpp (see tests/test_golden.py) and the level budgets
 of src/sort_algo.h:87-201.
 
 Array primitives are in oracle/ckks_prims.c (plain C); this module holds the context tables,

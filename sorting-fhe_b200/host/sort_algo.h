@@ -78,7 +78,22 @@ template <int N> class DirectSort : public SortBase<N> {
         for (auto& e : depth) if (e[0] == N) d = e[1];
         if (!d) throw std::runtime_error("DirectSort: unsupported array size");
         parameters.SetMultiplicativeDepth(d);
-        rotations = requiredRotations(parameters.GetRingDim() ? (int)parameters.GetRingDim() : (1 << 17));
+        const int ringDim = parameters.GetRingDim() ? (int)parameters.GetRingDim() : (1 << 17);
+        rotations = (ringDim == (1 << 17) && N >= 256) ? referenceKeySet() : requiredRotations(ringDim);
+    }
+
+    // The reference's literal key sets for N >= 256 at ring 2^17 (:125-148) are not the set of rotation amounts
+    // sort() asks for: some amounts are left to RotationComposer's decomposition, some keys are never used.  They
+    // are reproduced here (as their generating pattern) so that a caller gets the same keys, hence the same op
+    // sequence, as with the reference.
+    static std::vector<int> referenceKeySet() {
+        std::set<int> r;
+        auto range = [&](int lo, int hi, int step) { for (int v = lo; v <= hi; v += step) r.insert(v); };
+        if (N == 256) { range(1, 16, 1); range(24, 128, 8); range(129, 135, 1); range(144, 256, 16); }
+        else if (N == 512) { range(1, 16, 1); range(24, 64, 8); range(80, 512, 16); for (int b = 1; b < 8; b++) range(64 * b + 1, 64 * b + 7, 1); }
+        else if (N == 1024) { range(1, 35, 1); for (int b = 2; b < 32; b++) range(32 * b, 32 * b + 3, 1); r.insert(1024); }
+        for (int v = 512; v <= 32768; v *= 2) r.insert(v);
+        return std::vector<int>(r.begin(), r.end());
     }
 
     // ---- plaintext pattern generators (:206-306)
