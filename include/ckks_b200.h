@@ -91,6 +91,12 @@ int ckks_eval_square(ckks_ctx_t* ctx, const ckks_ct_t* a, ckks_ct_t** out);
 /* EvalRotate(ct, index) -- rotation.h:224,231; fails if no key for index (OpenFHE throws) */
 int ckks_eval_rotate(ckks_ctx_t* ctx, const ckks_ct_t* a, int32_t index, ckks_ct_t** out);
 int ckks_has_rotation_key(ckks_ctx_t* ctx, int32_t index);
+/* EvalFastRotationPrecompute(ct) / EvalFastRotation(ct, index, M, digits) -- rotation.h:286,344-347 (RotationTree).
+ * The precomputed ModUp digits are a handle of their own (free with ckks_ct_free); results are bit-identical to
+ * ckks_eval_rotate.  ckks_eval_rotate itself keeps the digits of a ciphertext it has rotated once, so repeated
+ * rotations of one handle (the sorters' baby steps, sort_algo.h:425-431,733-736) are hoisted transparently. */
+int ckks_fast_rotation_precompute(ckks_ctx_t* ctx, const ckks_ct_t* ct, ckks_ct_t** precomp);
+int ckks_fast_rotation(ckks_ctx_t* ctx, const ckks_ct_t* ct, int32_t index, const ckks_ct_t* precomp, ckks_ct_t** out);
 /* EvalChebyshevSeriesPS(ct, coeffs, a, b) -- sort_algo.h:727-728, sign.cpp:76 */
 int ckks_eval_chebyshev_series_ps(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, double a, double b,
                                   ckks_ct_t** out);

@@ -281,6 +281,14 @@ class Engine:
         o = ctypes.c_void_p()
         return self._out(_L.ckks_eval_rotate(_vp(self.h), _vp(a.h), int(r), ctypes.byref(o)), o)
 
+    def EvalFastRotationPrecompute(self, a):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_fast_rotation_precompute(self.h, a.h, ctypes.byref(o)), o)
+
+    def EvalFastRotation(self, a, r, m, digits):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_fast_rotation(self.h, a.h, ctypes.c_int32(r), digits.h, ctypes.byref(o)), o)
+
     def EvalChebyshevSeriesPS(self, x, coeffs, a=-1.0, b=1.0):
         v = np.ascontiguousarray(coeffs, dtype=np.float64)
         o = ctypes.c_void_p()

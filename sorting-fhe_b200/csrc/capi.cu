@@ -37,6 +37,7 @@ void context_release(Context* c) {
     if (!c->dry) {
         cudaStreamSynchronize(c->stream);
         cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs);
+        for (auto& kv : c->ninv_pairs_rep) cudaFree(kv.second);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
         if (c->enc_pinned) cudaFreeHost(c->enc_pinned);
         for (auto e : c->enc_events) if (e) cudaEventDestroy(e);
@@ -226,7 +227,11 @@ int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
     API_BEGIN
     const Ct* p = G(ct); size_t w = (size_t)p->parts * p->nl * p->ctx->n;
     if (cap < w) throw std::runtime_error("ct_export: buffer too small");
-    d2h(p->ctx, host, p->d, w);
+    if (p->lrep) {   // compact plaintext: export the full-length limbs
+        Ct* f = ct_full(p);
+        try { d2h(p->ctx, host, f->d, w); } catch (...) { ct_free(f); throw; }
+        ct_free(f);
+    } else d2h(p->ctx, host, p->d, w);
     API_END
 }
 int ckks_ct_import(ckks_ctx_t* x, const uint64_t* host, int polys, int limbs, int level, int deg, double sf, int slots, ckks_ct_t** out) {
@@ -252,6 +257,23 @@ int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_B
 int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
     API_BEGIN (void)C(x);
     if (count < 1) throw std::runtime_error("EvalAddMany: empty list");
+    {   // all operands already aligned (the sorters' case): one pass over the inputs.  Modular addition is
+        // associative, so the result equals the pairwise tree's bit for bit.
+        const Ct* f = G(cts[0]); bool same = count <= 32 && f->parts == 2 && f->lrep == 0;
+        for (int i = 1; i < count && same; i++) {
+            const Ct* g = G(cts[i]);
+            same = g->parts == f->parts && g->nl == f->nl && g->level == f->level && g->deg == f->deg && g->sf == f->sf && g->lrep == 0;
+        }
+        if (same && count > 2) {
+            int slots = 0; std::vector<const u64*> ins;
+            for (int i = 0; i < count; i++) { ins.push_back(G(cts[i])->d); slots = std::max(slots, G(cts[i])->slots); }
+            Ct* r = ct_new(f->ctx, f->parts, f->nl, f->level, f->deg, f->sf, slots);
+            f->ctx->stats.ops[{"add", f->nl}] += count - 1;
+            launch_add_many(f->ctx, r->d, ins.data(), count, f->parts * f->nl, f->nl);
+            *out = box(r);
+            return 0;
+        }
+    }
     std::vector<Ct*> cur; std::vector<bool> owned;
     for (int i = 0; i < count; i++) { cur.push_back(const_cast<Ct*>(G(cts[i]))); owned.push_back(false); }
     while (cur.size() > 1) {   // binary tree, same association as oracle EvalAddMany
@@ -271,6 +293,10 @@ int ckks_eval_mult(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_c
 int ckks_eval_mult_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult_const(G(a), v)); API_END }
 int ckks_eval_square(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult(G(a), G(a))); API_END }
 int ckks_eval_rotate(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_rotate(G(a), index)); API_END }
+int ckks_fast_rotation_precompute(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(fast_rotation_precompute(G(a))); API_END }
+int ckks_fast_rotation(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, const ckks_ct_t* precomp, ckks_ct_t** out) {
+    API_BEGIN (void)C(x); *out = box(eval_fast_rotate(G(a), index, G(precomp))); API_END
+}
 int ckks_has_rotation_key(ckks_ctx_t* x, int32_t index) {
     try { Context* c = C(x); return c->rot.count(auto_index(c, index)) ? 1 : 0; } catch (...) { return 0; }
 }

@@ -78,6 +78,7 @@ Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& w
     for (size_t i = 1; i < cts.size(); i++) if (cts[i]->level > cts[mi]->level) mi = i;
     for (size_t i = 0; i < cts.size(); i++) if (i != mi) adjust_levels_and_depth(cts[i], cts[mi]);
     if (cts[mi]->deg == 2) for (size_t i = 0; i < cts.size(); i++) rescale(cts[i]);
+    if (Ct* fused = eval_wsum_aligned(cts, w)) return fused;
     CtP acc = wrap(eval_mult_const(cts[0], w[0]));
     for (size_t i = 1; i < cts.size(); i++) { CtP t = wrap(eval_mult_const(cts[i], w[i])); acc = add(acc, t); }
     return ct_clone(acc.get());

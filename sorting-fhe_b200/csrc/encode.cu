@@ -149,13 +149,14 @@ static double* stage_values(Context* c, const double* h_values, int nvals) {
     return p;
 }
 
-void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl) {
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep) {
+    const int n_c = c->n >> lrep;   // compact row length (engine.h Ct::lrep)
     int bits = 0; while ((1 << bits) < slots) bits++;
     const int big_stages = bits > 11 ? bits - 11 : 0;
     c->stats.kernel_launches += big_stages + 2;
     if (c->dry) return;
     {
-        ProfScope ps(c, KC_ENCODE, 8.0 * c->n * nl, big_stages + 2);
+        ProfScope ps(c, KC_ENCODE, 8.0 * n_c * nl, big_stages + 2);
         double* d_in = (double*)dev_alloc(c, (size_t)(nvals > 0 ? nvals : 1));
         double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
         double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
@@ -174,11 +175,11 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
         const int bsz = slots < 2048 ? slots : 2048, threads = bsz / 2 < 32 ? 32 : (bsz / 2 > 1024 ? 1024 : bsz / 2);
         k_fft_inv_tail<<<slots / bsz, threads, (size_t)bsz * sizeof(double2), c->stream>>>(
             b, a, d_in, nvals, from_real, slots, bits, (const double2*)c->d_ksi, c->d_rot, M, 1.0 / (double)slots, sf, mx);
-        dim3 grid((c->n + 255) / 256, nl);
-        k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, c->n, slots, mx);
+        dim3 grid((n_c + 255) / 256, nl);
+        k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, n_c, slots, mx);
         dev_free(c, d_in); dev_free(c, a); dev_free(c, b); dev_free(c, mx);
     }
-    launch_ntt(c, out, nl, mods_q(nl), false);
+    launch_ntt_ex(c, out, out, nl, mods_q(nl), false, nullptr, RowMap{}, RowMap{}, nullptr, lrep);
 }
 
 // centred CRT of limbs (0,1) (or limb 0 alone) -> double, then gather slots with 1/sf

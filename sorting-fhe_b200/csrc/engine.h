@@ -86,6 +86,7 @@ struct Context {
     std::vector<ModInfo> h_mod;
     u64 *d_tw = nullptr, *d_itw = nullptr;   // [M][n] (w, Shoup companion) pairs: psi / psi^-1 powers, bit-reversed
     u64* d_ninv_pairs = nullptr;             // [M] (n^-1, Shoup companion): default final factor of the inverse NTT
+    std::map<int, u64*> ninv_pairs_rep;      // lrep -> [M] ((n >> lrep)^-1, Shoup) for transforms of compact plaintexts
     double* d_ksi = nullptr;                // [2n+1] complex roots for the special FFT
     uint32_t* d_rot = nullptr;              // [n/2] 5^j mod 2n
     std::map<int, KsTables> ks;             // keyed by nl
@@ -119,6 +120,11 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     double sf;
     int slots;
     mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
+    mutable u64* modup = nullptr; // cached ModUp of c1 (owned): shared by all rotations of this ciphertext (hoisting)
+    // Plaintexts only: log2 of the replication factor.  A plaintext with s slots is G(X^gap), gap = n / (2 s), so its
+    // EVALUATION form is the (n / gap)-point transform of G with every value repeated gap times in a row
+    // (ntt.cu).  Such a plaintext is stored compact, [limb][n >> lrep], and element x of the full form is d[x >> lrep].
+    int lrep = 0;
 };
 
 void context_release(Context* c);
@@ -141,18 +147,26 @@ LimbMods mods_range(int lo, int hi);              // moduli lo..hi-1
 void launch_ntt(Context* c, u64* data, int rows, const LimbMods& m, bool inverse);
 // out-of-place capable form; scale_pairs (inverse only): [M] (factor, Shoup) pairs indexed by modulus id that
 // replace the n^-1 factor (nullptr = n^-1)
+// lrep > 0: the rows are compact plaintext limbs of n >> lrep words (same twiddle tables: the first stages of the
+// n-point transform restricted to the multiples of 2^lrep ARE the (n >> lrep)-point transform)
 void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs,
-                   RowMap smap, RowMap dmap, const NttFuse* fuse = nullptr);
+                   RowMap smap, RowMap dmap, const NttFuse* fuse = nullptr, int lrep = 0);
 
 void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op /*0 add 1 sub*/);
 void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m);
-void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m);
-void launch_mul_scalar(Context* c, u64* out, const u64* in, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/);
+void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m, int lrep_b = 0);
+void launch_mul_scalar(Context* c, u64* out, const u64* in, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/, int lrep = 0);
 // out[0] = (negate ? -in[0] : in[0]) + s ; out[p>0] = (negate ? -in[p] : in[p])
 void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* h_scalars, bool negate);
 // out[p] = (p < xparts ? x[p] : 0) +- (p < yparts ? y[p] : 0), p < max(xparts, yparts)
-void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub);
-void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in);
+// lrep_x / lrep_y: the 1-part operand may be a compact plaintext
+void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub,
+                         int lrep_x = 0, int lrep_y = 0);
+void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep);   // compact -> full rows
+// out = sum_i in_i * s_i with per-limb integer scalars h_scalars[i * nl + l] (EvalLinearWSum in one pass)
+void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* h_scalars, int cnt, int parts, int nl);
+void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int rows, int nl);
+void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep = 0);
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
 #define MAX_CONV_IN 24
@@ -172,7 +186,7 @@ void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint
 void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream);
 void launch_evk_combine(Context* c, u64* b, const u64* a, const u64* e, const u64* s_new, const u64* s_old,
                         int lo, int hi);
-void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl);
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep = 0);
 void launch_decode(Context* c, double* h_out, const u64* m /*[<=2][n] coeff*/, int nlimbs, double sf, int slots);
 void launch_decrypt_combine(Context* c, u64* out, const Ct* ct, int use);
 void launch_encrypt_combine(Context* c, u64* out, const u64* pt, const u64* v, const u64* e0, const u64* e1, int nl);

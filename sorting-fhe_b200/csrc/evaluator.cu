@@ -15,21 +15,25 @@
 
 typedef __int128 i128;
 
-static inline size_t words(const Context* c, int rows) { return (size_t)rows * c->n; }
+static inline size_t words(const Context* c, int rows, int lrep = 0) { return (size_t)rows * (c->n >> lrep); }
 static void count(Context* c, const char* name, int nl) { c->stats.ops[{name, nl}]++; }
 
-Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots) {
+Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots, int lrep) {
     Ct* t = new Ct{c, nullptr, parts, nl, level, deg, sf, slots};
-    t->d = dev_alloc(c, words(c, parts * nl));
+    t->lrep = lrep;
+    t->d = dev_alloc(c, words(c, parts * nl, lrep));
     c->live_cts++;
     return t;
 }
 Ct* ct_clone(const Ct* a) {
-    Ct* t = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
-    launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl));
+    Ct* t = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots, a->lrep);
+    launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl, a->lrep));
     return t;
 }
-static void drop_twin(const Ct* a) { if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); } }
+static void drop_twin(const Ct* a) {
+    if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); }
+    if (a->modup) { dev_free(a->ctx, a->modup); a->modup = nullptr; }
+}
 void ct_free(Ct* a) {
     if (!a) return;
     Context* c = a->ctx;
@@ -42,7 +46,7 @@ void ct_free(Ct* a) {
 static void ct_steal(Ct* a, Ct* t) {
     drop_twin(a);
     dev_free(a->ctx, a->d);
-    a->d = t->d; a->parts = t->parts; a->nl = t->nl; a->level = t->level; a->deg = t->deg; a->sf = t->sf;
+    a->d = t->d; a->parts = t->parts; a->nl = t->nl; a->level = t->level; a->deg = t->deg; a->sf = t->sf; a->lrep = t->lrep;
     a->resc = t->resc; t->resc = nullptr;
     t->d = nullptr;
     ct_free(t);
@@ -57,8 +61,8 @@ static Ct* rescale_new(const Ct* a) {
     Context* c = a->ctx; const int nl = a->nl, parts = a->parts;
     if (nl < 2) throw std::runtime_error("rescale: no limb left to drop (multiplicative depth exhausted)");
     count(c, "rescale", nl);
-    Ct* out = ct_new(c, parts, nl - 1, a->level + 1, a->deg - 1, a->sf / (double)c->moduli[nl - 1], a->slots);
-    launch_rescale(c, out->d, a->d, parts, nl);
+    Ct* out = ct_new(c, parts, nl - 1, a->level + 1, a->deg - 1, a->sf / (double)c->moduli[nl - 1], a->slots, a->lrep);
+    launch_rescale(c, out->d, a->d, parts, nl, a->lrep);
     return out;
 }
 // the rescaled twin of a pristine ciphertext is computed once and cached on it: under FLEXIBLEAUTO the same
@@ -86,16 +90,17 @@ static Ct* mult_const_new(const Ct* a, double x) {   // EvalMultCore(ct, double)
     const double sf = c->sf_real[a->level];
     i128 v = (i128)(x * sf + 0.5);
     u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
-    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg + 1, a->sf * sf, a->slots);
-    launch_mul_scalar(c, r->d, a->d, a->parts * a->nl, mods_q(a->nl), s);
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg + 1, a->sf * sf, a->slots, a->lrep);
+    launch_mul_scalar(c, r->d, a->d, a->parts * a->nl, mods_q(a->nl), s, a->lrep);
     return r;
 }
 static Ct* level_reduce_new(const Ct* a, int levels) {
     Context* c = a->ctx; const int nl2 = a->nl - levels;
     if (nl2 < 1) throw std::runtime_error("level_reduce: not enough limbs");
-    Ct* r = ct_new(c, a->parts, nl2, a->level + levels, a->deg, a->sf, a->slots);
+    Ct* r = ct_new(c, a->parts, nl2, a->level + levels, a->deg, a->sf, a->slots, a->lrep);
     for (int p = 0; p < a->parts; p++)
-        launch_copy_rows(c, c->dry ? nullptr : r->d + words(c, p * nl2), c->dry ? nullptr : a->d + words(c, p * a->nl), words(c, nl2));
+        launch_copy_rows(c, c->dry ? nullptr : r->d + words(c, p * nl2, a->lrep), c->dry ? nullptr : a->d + words(c, p * a->nl, a->lrep),
+                         words(c, nl2, a->lrep));
     return r;
 }
 static void op_mult_const(Opnd& o, double x) { o.set_own(mult_const_new(o.v, x)); }
@@ -106,6 +111,16 @@ static void op_set_sf(Opnd& o, double sf) {
     if (!o.own) o.set_own(ct_clone(o.v));
     o.own->sf = sf;
 }
+
+// full-length copy of a compact plaintext (ops without a compact form use this)
+static Ct* expand_new(const Ct* a) {
+    Context* c = a->ctx;
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_expand_rep(c, r->d, a->d, a->parts * a->nl, a->lrep);
+    return r;
+}
+Ct* ct_full(const Ct* a) { return a->lrep ? expand_new(a) : ct_clone(a); }
+static void op_full(Opnd& o) { if (o.v->lrep) o.set_own(expand_new(o.v)); }
 
 // LeveledSHECKKSRNS::AdjustLevelsAndDepthInPlace on operand views
 static void adjust_levels_and_depth(Opnd& A, Opnd& B) {
@@ -172,16 +187,13 @@ void adjust_levels_and_depth(Ct* a, Ct* b) {
     commit(a, x); commit(b, y);
 }
 
-// KeySwitchHYBRID::KeySwitchCore (+ optional addends): out[h] = add_h + ModDown(sum_j d_j * evk_j[h]);
-// auto_k != 0 additionally applies the automorphism X -> X^k to both outputs while writing them
-void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1,
-                uint32_t auto_k) {
-    count(c, "keyswitch", nl);
-    if (!c->dry && !key.d) throw std::runtime_error("key switch: evaluation key not generated");
+// ModUp of one polynomial (EvalKeySwitchPrecomputeCore): INTT (x n^-1 Qhat^-1 fused) -> basis conversion of every
+// digit -> NTT of all converted limbs.  Returns the converted complements [sum_j nout_j][n] (caller frees).
+u64* key_switch_modup(Context* c, const u64* src, int nl) {
     const KsTables& t = get_ks_tables(c, nl);
     const int K = c->size_p, next = nl + K;
     if (K > MAX_CONV_IN || c->alpha > MAX_CONV_IN || next > MAX_CONV_OUT) throw std::runtime_error("key switch: parameter set too large");
-    // ---- ModUp: INTT (x n^-1 Qhat^-1 fused) -> basis conversion of every digit -> NTT of all converted limbs
+    count(c, "modup", nl);
     u64* coef = dev_alloc(c, words(c, nl));
     launch_ntt_ex(c, coef, src, nl, mods_q(nl), true, t.d_modup_scale, RowMap{}, RowMap{});
     int conv_rows = 0;
@@ -207,10 +219,25 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
             }
         }
     }
+    dev_free(c, coef);
+    return conv;
+}
+
+// KeySwitchHYBRID::KeySwitchCore (+ optional addends): out[h] = add_h + ModDown(sum_j d_j * evk_j[h]);
+// auto_k != 0 additionally applies the automorphism X -> X^k to both outputs while writing them.
+// modup != nullptr: precomputed ModUp of src (hoisting: EvalFastRotationPrecompute / the per-ciphertext cache)
+void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1,
+                uint32_t auto_k, const u64* modup) {
+    count(c, "keyswitch", nl);
+    if (!c->dry && !key.d) throw std::runtime_error("key switch: evaluation key not generated");
+    const KsTables& t = get_ks_tables(c, nl);
+    const int K = c->size_p, next = nl + K;
+    u64* own_conv = modup ? nullptr : key_switch_modup(c, src, nl);
+    const u64* conv = modup ? modup : own_conv;
     // ---- inner product with the evaluation key over Q_l u P
     u64* acc = dev_alloc(c, words(c, 2 * next));
     launch_ks_inner2(c, acc, src, conv, key, t);
-    dev_free(c, coef); dev_free(c, conv);
+    if (own_conv) dev_free(c, own_conv);
     // ---- ModDown of both polynomials: INTT of the P limbs (x n^-1 Phat^-1) -> conversion to Q_l -> NTT -> epilogue
     u64* pp = dev_alloc(c, words(c, 2 * K));
     {
@@ -234,7 +261,8 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
 
 // ------------------------------------------------------------------ public evaluator ops
 // EvalAdd(ct, double): add round(|x| * scalingFactor) (signed) to c0
-Ct* eval_add_const(const Ct* a, double x) {
+Ct* eval_add_const(const Ct* a_in, double x) {
+    Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
     Context* c = a->ctx;
     i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
     if (x < 0) v = -v;
@@ -244,7 +272,8 @@ Ct* eval_add_const(const Ct* a, double x) {
     return r;
 }
 // EvalSub(double, ct) = -ct + x in one pass
-Ct* eval_const_sub(double x, const Ct* a) {
+Ct* eval_const_sub(double x, const Ct* a_in) {
+    Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
     Context* c = a->ctx;
     i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
     if (x < 0) v = -v;
@@ -254,7 +283,8 @@ Ct* eval_const_sub(double x, const Ct* a) {
     return r;
 }
 
-Ct* eval_negate(const Ct* a) {
+Ct* eval_negate(const Ct* a_in) {
+    Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
     Ct* r = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
     launch_neg(a->ctx, r->d, a->d, a->parts * a->nl, mods_q(a->nl));
     return r;
@@ -265,12 +295,13 @@ Ct* eval_add(const Ct* a, const Ct* b, int sign) {
     Context* c = a->ctx;
     Opnd x(a), y(b);
     adjust_levels_and_depth(x, y);
+    if (x.v->parts == 1 && y.v->parts == 1) { op_full(x); op_full(y); }   // plaintext +- plaintext: no compact form
     const Ct *X = x.v, *Y = y.v;
     const int nl = X->nl, parts = std::max(X->parts, Y->parts);
     count(c, "add", nl);
     Ct* r = ct_new(c, parts, nl, X->level, X->deg, X->sf, std::max(a->slots, b->slots));
     // out[p] = (p < X.parts ? X[p] : 0) +- (p < Y.parts ? Y[p] : 0)
-    launch_addsub_parts(c, r->d, X->d, X->parts, Y->d, Y->parts, nl, sign < 0);
+    launch_addsub_parts(c, r->d, X->d, X->parts, Y->d, Y->parts, nl, sign < 0, X->lrep, Y->lrep);
     return r;
 }
 
@@ -278,6 +309,29 @@ Ct* eval_mult_const(const Ct* a, double x) {
     Opnd o(a);
     if (o.v->deg == 2) op_rescale(o);
     return mult_const_new(o.v, x);
+}
+
+// sum_i cts[i] * w[i] for operands that are already aligned (same level, limbs, noiseScaleDeg 1): the per-term
+// EvalMult(ct, double) + EvalAdd chain of EvalLinearWSumMutable in one pass.  Returns nullptr when not applicable.
+Ct* eval_wsum_aligned(const std::vector<Ct*>& cts, const std::vector<double>& w) {
+    const Ct* f = cts[0]; Context* c = f->ctx;
+    if (cts.size() < 2 || f->deg != 1 || f->lrep) return nullptr;
+    for (const Ct* g : cts)
+        if (g->parts != f->parts || g->nl != f->nl || g->level != f->level || g->deg != 1 || g->sf != f->sf || g->lrep) return nullptr;
+    const double sf = c->sf_real[f->level];
+    std::vector<u64> sc(cts.size() * (size_t)f->nl);
+    std::vector<const u64*> ins(cts.size());
+    int slots = 0;
+    for (size_t i = 0; i < cts.size(); i++) {
+        i128 v = (i128)(w[i] * sf + 0.5);                 // same rounding as mult_const_new
+        int_residues(c, v, f->nl, sc.data() + i * f->nl);
+        ins[i] = cts[i]->d; slots = std::max(slots, cts[i]->slots);
+        count(c, "mult_const", f->nl);
+        if (i) count(c, "add", f->nl);
+    }
+    Ct* r = ct_new(c, f->parts, f->nl, f->level, 2, f->sf * sf, slots);
+    launch_wsum(c, r->d, ins.data(), sc.data(), (int)cts.size(), f->parts, f->nl);
+    return r;
 }
 
 // EvalMult(ct,ct) with relinearisation / EvalMult(ct,pt)
@@ -301,7 +355,7 @@ Ct* eval_mult(const Ct* a, const Ct* b) {
         if (ct->parts != 2 || pt->parts != 1) throw std::runtime_error("eval_mult: unsupported operand shapes");
         count(c, "mult_pt", nl);
         r = ct_new(c, 2, nl, X->level, X->deg + Y->deg, X->sf * Y->sf, ct->slots);
-        launch_mul(c, r->d, ct->d, pt->d, 2 * nl, nl, mods_q(nl));
+        launch_mul(c, r->d, ct->d, pt->d, 2 * nl, nl, mods_q(nl), pt->lrep);
     }
     return r;
 }
@@ -331,7 +385,37 @@ Ct* eval_rotate(const Ct* a, int r) {
     count(c, "rotate", a->nl);
     const int nl = a->nl;
     Ct* out = ct_new(c, 2, nl, a->level, a->deg, a->sf, a->slots);
-    key_switch(c, c->dry ? nullptr : a->d + words(c, nl), nl, it->second, out->d, a->d, nullptr, k);
+    // hoisting: the ModUp of c1 is computed on the first rotation of a ciphertext and kept on the handle, so the
+    // baby-step rotations of one input (sort_algo.h:425-431, 733-736) share it.  Same limbs as EvalRotate: ModUp does
+    // not depend on the rotation index (EvalFastRotation == EvalRotate bit for bit).
+    const u64* c1 = c->dry ? nullptr : a->d + words(c, nl);
+    if (!a->modup) { u64* m = key_switch_modup(c, c1, nl); a->modup = c->dry ? (u64*)1 : m; }   // dry: sentinel (dev_free ignores it)
+    else count(c, "modup_reused", nl);
+    key_switch(c, c1, nl, it->second, out->d, a->d, nullptr, k, a->modup);
+    return out;
+}
+
+// EvalFastRotationPrecompute (rotation.h:286): the ModUp digits of c1 as a handle of their own (parts == 0)
+Ct* fast_rotation_precompute(const Ct* a) {
+    Context* c = a->ctx;
+    if (a->parts != 2) throw std::runtime_error("EvalFastRotationPrecompute: ciphertext must have 2 components");
+    Ct* p = new Ct{c, nullptr, 0, a->nl, a->level, a->deg, a->sf, a->slots};
+    c->live_cts++;
+    p->d = key_switch_modup(c, c->dry ? nullptr : a->d + words(c, a->nl), a->nl);
+    return p;
+}
+// EvalFastRotation(ct, index, m, digits) (rotation.h:344-347)
+Ct* eval_fast_rotate(const Ct* a, int r, const Ct* pre) {
+    Context* c = a->ctx;
+    if (a->parts != 2 || pre->parts != 0 || pre->nl != a->nl) throw std::runtime_error("EvalFastRotation: digits do not match the ciphertext");
+    if (r == 0) return ct_clone(a);
+    uint32_t k = auto_index(c, r);
+    auto it = c->rot.find(k);
+    if (it == c->rot.end()) throw std::runtime_error("EvalFastRotation: no rotation key for index " + std::to_string(r));
+    count(c, "rotate", a->nl);
+    const int nl = a->nl;
+    Ct* out = ct_new(c, 2, nl, a->level, a->deg, a->sf, a->slots);
+    key_switch(c, c->dry ? nullptr : a->d + words(c, nl), nl, it->second, out->d, a->d, nullptr, k, c->dry ? (const u64*)1 : pre->d);
     return out;
 }
 
@@ -410,14 +494,18 @@ Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level
     if (c->ext && level == 0) { sf = c->sf_big[0]; deg = 2; }
     else { sf = std::pow(c->sf_real[level], (double)scale_deg); deg = scale_deg; }
     const int nl = c->size_q - level;
-    Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots);
+    // compact form: the plaintext is G(X^gap), gap = n / (2 slots); keep at least 2^8 words per limb
+    int lrep = 0;
+    while ((2 * slots << lrep) < c->n && c->log_n - lrep > 8) lrep++;
+    Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
     count(c, "encode", nl);
-    launch_encode(c, pt->d, values, nvals, slots, sf, nl);
+    launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
     return pt;
 }
 
-Ct* encrypt(Context* c, const Ct* pt) {
-    if (pt->parts != 1) throw std::runtime_error("Encrypt: operand is not a plaintext");
+Ct* encrypt(Context* c, const Ct* pt_in) {
+    if (pt_in->parts != 1) throw std::runtime_error("Encrypt: operand is not a plaintext");
+    Opnd fp(pt_in); op_full(fp); const Ct* pt = fp.v;
     if (!c->d_pk && !c->dry) throw std::runtime_error("Encrypt: no public key");
     const int nl = pt->nl; uint64_t cnt = c->enc_counter++;
     u64* t = dev_alloc(c, words(c, 3 * nl));
@@ -431,7 +519,8 @@ Ct* encrypt(Context* c, const Ct* pt) {
     return ct;
 }
 
-void decrypt(const Ct* ct, double* out, int out_len) {
+void decrypt(const Ct* ct_in, double* out, int out_len) {
+    Opnd fc(ct_in); op_full(fc); const Ct* ct = fc.v;
     Context* c = ct->ctx;
     const int use = std::min(2, ct->nl);
     u64* m = dev_alloc(c, words(c, use));

@@ -6,7 +6,8 @@
 void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits, int ext,
                       uint64_t seed, int dry);
 
-Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots);
+Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots, int lrep = 0);
+Ct* ct_full(const Ct* a);   // full-length copy of a (possibly compact) plaintext / ciphertext
 Ct* ct_clone(const Ct* a);
 void ct_free(Ct* a);
 
@@ -14,8 +15,9 @@ void mult_core_const(Ct* a, double x);
 void rescale(Ct* a);
 void level_reduce(Ct* a, int levels);
 void adjust_levels_and_depth(Ct* a, Ct* b);
+u64* key_switch_modup(Context* c, const u64* src, int nl);
 void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out, const u64* add0, const u64* add1,
-                uint32_t auto_k);
+                uint32_t auto_k, const u64* modup = nullptr);
 
 Ct* eval_add(const Ct* a, const Ct* b, int sign);
 Ct* eval_add_const(const Ct* a, double x);
@@ -23,7 +25,10 @@ Ct* eval_const_sub(double x, const Ct* a);
 Ct* eval_negate(const Ct* a);
 Ct* eval_mult(const Ct* a, const Ct* b);
 Ct* eval_mult_const(const Ct* a, double x);
+Ct* eval_wsum_aligned(const std::vector<Ct*>& cts, const std::vector<double>& w);   // nullptr if operands are not aligned
 Ct* eval_rotate(const Ct* a, int r);
+Ct* fast_rotation_precompute(const Ct* a);
+Ct* eval_fast_rotate(const Ct* a, int r, const Ct* pre);
 uint32_t auto_index(const Context* c, int r);
 
 void keygen(Context* c);

@@ -50,15 +50,19 @@ void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m)
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n); k_neg<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, m, c->d_mod, c->n);
 }
 
-__global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b) {
+__global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b, int lrep_b) {
     X2_PROLOGUE;
     int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
-    size_t o = (size_t)row * n + x, ob = (size_t)(row % rows_b) * n + x;
-    const u64x2 va = ld2(a, o), vb = ld2(b, ob);
+    size_t o = (size_t)row * n + x;
+    const u64x2 va = ld2(a, o);
+    u64x2 vb;
+    if (lrep_b == 0) vb = ld2(b, (size_t)(row % rows_b) * n + x);
+    else { const u64 t = b[(size_t)(row % rows_b) * (n >> lrep_b) + (x >> lrep_b)]; vb = make_ulonglong2(t, t); }   // x even: x, x+1 share a group
     st2(out, o, barrett_mul(va.x, vb.x, m), barrett_mul(va.y, vb.y, m));
 }
-void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows_out * c->n); k_mul<<<grid_for2(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b);
+void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m, int lrep_b) {
+    KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * (2.0 * rows_out + (double)rows_out / (1 << lrep_b)));
+    k_mul<<<grid_for2(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b, lrep_b);
 }
 
 __global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
@@ -68,11 +72,12 @@ __global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInf
     const u64x2 v = ld2(d, o);
     st2(out, o, shoup_mul(v.x, s.v[l], s.sh[l], q), shoup_mul(v.y, s.v[l], s.sh[l], q));
 }
-void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const LimbMods& m, const u64* hs) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n);
+void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const LimbMods& m, const u64* hs, int lrep) {
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * (c->n >> lrep));
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
-    k_mul_scalar<<<grid_for2(c, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, c->n, s);
+    const int n = c->n >> lrep;
+    k_mul_scalar<<<dim3((n / 2 + 255) / 256, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, n, s);
 }
 
 __global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, int nl, LimbScalars s, int negate) {
@@ -92,19 +97,84 @@ void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, c
 }
 
 __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
-                               int sub) {
+                               int sub, int lrx, int lry) {
     X2_PROLOGUE;
     int row = blockIdx.y, p = row / nl; u64 q = mi[row % nl].q;
     size_t o = (size_t)row * n + x;
     const u64x2 z = make_ulonglong2(0, 0);
-    const u64x2 a = p < xparts ? ld2(xs, o) : z, b = p < yparts ? ld2(ys, o) : z;
+    u64x2 a = z, b = z;
+    if (p < xparts) { if (lrx == 0) a = ld2(xs, o); else { const u64 t = xs[(size_t)row * (n >> lrx) + (x >> lrx)]; a = make_ulonglong2(t, t); } }
+    if (p < yparts) { if (lry == 0) b = ld2(ys, o); else { const u64 t = ys[(size_t)row * (n >> lry) + (x >> lry)]; b = make_ulonglong2(t, t); } }
     if (sub) st2(out, o, sub_mod(a.x, b.x, q), sub_mod(a.y, b.y, q));
     else st2(out, o, add_mod(a.x, b.x, q), add_mod(a.y, b.y, q));
 }
-void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub) {
+void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub, int lrx, int lry) {
     int parts = xparts > yparts ? xparts : yparts;
-    KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * (xparts + yparts + parts));
-    k_addsub_parts<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * ((double)xparts / (1 << lrx) + (double)yparts / (1 << lry) + parts));
+    k_addsub_parts<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0, lrx, lry);
+}
+
+// compact plaintext rows [rows][n >> lrep] -> full rows [rows][n]
+__global__ void k_expand_rep(u64* out, const u64* in, int n, int lrep) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
+    out[(size_t)blockIdx.y * n + x] = in[(size_t)blockIdx.y * (n >> lrep) + (x >> lrep)];
+}
+void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep) {
+    KL(c); ProfScope ps(c, KC_COPY, 8.0 * rows * c->n); k_expand_rep<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, lrep);
+}
+
+// out[row] = sum_i in_i[row] * s_i[limb]  (EvalLinearWSum: one pass instead of cnt scalar products + cnt-1 additions)
+#define WSUM_MAX_IN 16
+#define WSUM_MAX_PAIRS 640
+struct WsumArgs { int cnt, acc; const u64* in[WSUM_MAX_IN]; u64 pairs[WSUM_MAX_PAIRS][2]; };   // passed by value (<= 32 KB of parameters)
+__global__ void k_wsum(u64* out, const __grid_constant__ WsumArgs A, const ModInfo* mi, int n, int nl) {
+    X2_PROLOGUE;
+    const int row = blockIdx.y, l = row % nl; const u64 q = mi[l].q;
+    const size_t o = (size_t)row * n + x;
+    u64 r0 = 0, r1 = 0;
+    if (A.acc) { const u64x2 v = ld2(out, o); r0 = v.x; r1 = v.y; }
+    for (int i = 0; i < A.cnt; i++) {
+        const u64x2 v = ld2(A.in[i], o);
+        const u64 w = A.pairs[i * nl + l][0], ws = A.pairs[i * nl + l][1];
+        r0 = add_mod(r0, shoup_mul(v.x, w, ws, q), q);
+        r1 = add_mod(r1, shoup_mul(v.y, w, ws, q), q);
+    }
+    st2(out, o, r0, r1);
+}
+void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* hs, int cnt, int parts, int nl) {
+    int per = WSUM_MAX_PAIRS / nl; if (per > WSUM_MAX_IN) per = WSUM_MAX_IN;
+    for (int i0 = 0; i0 < cnt; i0 += per) {
+        const int k = cnt - i0 < per ? cnt - i0 : per;
+        c->stats.kernel_launches++;
+        if (c->dry) continue;
+        ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * parts * nl * (k + 1 + (i0 ? 1 : 0)));
+        WsumArgs A; A.cnt = k; A.acc = i0 ? 1 : 0;
+        for (int i = 0; i < k; i++) {
+            A.in[i] = ins[i0 + i];
+            for (int l = 0; l < nl; l++) {
+                const u64 w = hs[(size_t)(i0 + i) * nl + l];
+                A.pairs[i * nl + l][0] = w; A.pairs[i * nl + l][1] = host_shoup(w, c->moduli[l]);
+            }
+        }
+        k_wsum<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, A, c->d_mod, c->n, nl);
+    }
+}
+
+// out[row] = sum_i in_i[row]  (EvalAddMany)
+struct ManyArgs { int cnt; const u64* in[32]; };
+__global__ void k_add_many(u64* out, const ManyArgs A, const ModInfo* mi, int n, int nl) {
+    X2_PROLOGUE;
+    const int row = blockIdx.y; const u64 q = mi[row % nl].q;
+    const size_t o = (size_t)row * n + x;
+    u64x2 r = ld2(A.in[0], o);
+    for (int i = 1; i < A.cnt; i++) { const u64x2 v = ld2(A.in[i], o); r.x = add_mod(r.x, v.x, q); r.y = add_mod(r.y, v.y, q); }
+    st2(out, o, r.x, r.y);
+}
+void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int rows, int nl) {
+    KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * rows * (cnt + 1));
+    ManyArgs A; A.cnt = cnt;
+    for (int i = 0; i < cnt; i++) A.in[i] = ins[i];
+    k_add_many<<<grid_for2(c, rows), 256, 0, c->stream>>>(out, A, c->d_mod, c->n, nl);
 }
 
 // (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
@@ -144,11 +214,11 @@ static u64 host_powmod(u64 a, u64 e, u64 q) {
 // DropLastElementAndScale of `parts` polynomials with nl_in limbs each -> out [parts][nl_in-1][n]:
 // INTT of the last limbs, then ONE forward NTT launch over all remaining limbs whose prologue switches the last
 // limb's coefficients to the row modulus and whose epilogue forms (c_i - that) * q_last^-1.
-void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in) {
+void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep) {
     const int nl = nl_in, nlo = nl_in - 1;
-    const size_t n = c->n;
+    const size_t n = c->n >> lrep;
     u64* last = dev_alloc(c, (size_t)parts * n);
-    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, nullptr, RowMap{1, nl, nl - 1, 1}, RowMap{});
+    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, nullptr, RowMap{1, nl, nl - 1, 1}, RowMap{}, nullptr, lrep);
     auto it = c->rescale_pairs.find(nl);
     if (it == c->rescale_pairs.end()) {
         std::vector<u64> v(2 * (size_t)c->M(), 0); u64 ql = c->moduli[nl - 1];
@@ -164,7 +234,7 @@ void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in) {
     {
         ProfScope ps(c, KC_RESCALE, 0.0, 0);   // the fused launch is accounted to the NTT class
     }
-    launch_ntt_ex(c, out, last, parts * nlo, mods_q(nlo), false, nullptr, RowMap{nlo, 1, 0, 0}, RowMap{}, &f);
+    launch_ntt_ex(c, out, last, parts * nlo, mods_q(nlo), false, nullptr, RowMap{nlo, 1, 0, 0}, RowMap{}, &f, lrep);
     dev_free(c, last);
 }
 

@@ -22,6 +22,7 @@
 // Results are canonical residues, bit-identical to the oracle.
 #include "engine.h"
 #include <utility>
+#include <vector>
 
 static constexpr int TB_MAX = 11;
 typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
@@ -101,6 +102,7 @@ struct NttArgs {
     const tw_t* tw;          // [M][n] forward or inverse twiddle pairs
     const tw_t* scale;       // INV only: final factor (n^-1 [* extra]) as Shoup pair, indexed by modulus id
     int logn, T, a;          // T = tile bits, a = logn - T stages in pass A
+    int twlog;               // log2 of the twiddle table row length (ring size; >= logn, see compact plaintexts)
     int pass;                // 0 = pass A (strided), 1 = pass B (contiguous)
     int final_pass;          // this pass produces the final output (canonicalise / scale)
     int first_pass;          // this pass reads the launch's input (prologue applies)
@@ -156,7 +158,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     const u64 q = mi.q;
     const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
     const int cb = T - a_;                                // cb: column bits of a pass-A tile
-    const tw_t* W = A.tw + ((size_t)mid << logn);
+    const tw_t* W = A.tw + ((size_t)mid << A.twlog);
     const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
     u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
     const int tile = blockIdx.x, u = threadIdx.x;
@@ -260,31 +262,50 @@ ntt_kernel(NttArgs A, Sched S, LimbMods mods) {
 
 template <bool INV, int PASS_C>
 static void launch_pass(Context* c, dim3 grid, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
-    switch (c->log_n) {   // compile-time schedules for the ring sizes of the reference's fixtures
+    switch (A.logn) {   // compile-time schedules for the ring sizes of the reference's fixtures (+ their compact plaintexts)
         case 17: ntt_kernel<INV, 17, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
         case 16: ntt_kernel<INV, 16, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        case 15: ntt_kernel<INV, 15, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
         case 13: ntt_kernel<INV, 13, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
         case 12: ntt_kernel<INV, 12, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
         default: ntt_kernel<INV, 0, 0><<<grid, threads, smem, c->stream>>>(A, S, m); break;
     }
 }
 
+static const u64* ninv_pairs_for(Context* c, int lrep) {
+    if (lrep == 0) return c->d_ninv_pairs;
+    auto it = c->ninv_pairs_rep.find(lrep);
+    if (it != c->ninv_pairs_rep.end()) return it->second;
+    const int M = c->M();
+    std::vector<u64> v(2 * (size_t)M);
+    for (int i = 0; i < M; i++) {   // (n >> lrep)^-1 = n^-1 * 2^lrep mod q
+        const u64 q = c->moduli[i];
+        const u64 w = (u64)((unsigned __int128)c->h_mod[i].ninv * ((1ull << lrep) % q) % q);
+        v[2 * i] = w; v[2 * i + 1] = (u64)((((unsigned __int128)w) << 64) / q);
+    }
+    u64* d = nullptr;
+    cudaMalloc(&d, v.size() * sizeof(u64));
+    cudaMemcpy(d, v.data(), v.size() * sizeof(u64), cudaMemcpyHostToDevice);
+    c->ninv_pairs_rep[lrep] = d;
+    return d;
+}
+
 void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs,
-                   RowMap smap, RowMap dmap, const NttFuse* fuse) {
-    c->stats.kernel_launches += (c->log_n > TB_MAX) ? 2 : 1;
+                   RowMap smap, RowMap dmap, const NttFuse* fuse, int lrep) {
+    const int logn = c->log_n - lrep, T = logn < TB_MAX ? logn : TB_MAX, a = logn - T;
+    c->stats.kernel_launches += (logn > TB_MAX) ? 2 : 1;
     if (c->dry || rows == 0) return;
-    ProfScope ps(c, KC_NTT, 16.0 * rows * c->n, (c->log_n > TB_MAX) ? 2 : 1);
-    const int logn = c->log_n, T = logn < TB_MAX ? logn : TB_MAX, a = logn - T;
+    ProfScope ps(c, KC_NTT, 16.0 * rows * (c->n >> lrep), (logn > TB_MAX) ? 2 : 1);
     const int threads = (1 << T) / 8;
     const size_t smem = (size_t)((1 << T) + ((1 << T) >> 3) + 8) * sizeof(u64);
-    dim3 grid(c->n >> T, rows);
+    dim3 grid((c->n >> lrep) >> T, rows);
     NttArgs A;
-    A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a;
+    A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a; A.twlog = c->log_n;
     A.smap = smap; A.dmap = dmap;
     if (fuse) A.f = *fuse; else A.f = NttFuse{};
     A.first_pass = 1;
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
-    A.scale = (const tw_t*)(scale_pairs ? scale_pairs : c->d_ninv_pairs);
+    A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
     if (!inverse) {
         A.src = src;
         if (a > 0) {

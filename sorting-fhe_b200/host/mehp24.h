@@ -1,0 +1,122 @@
+// mehp24.h -- MEHP24 ranking sort ("Efficient Ranking, Order Statistics, and Sorting under CKKS"), the
+// single-ciphertext sortFG path and its matrix-in-slots utilities, with the reference's names
+// (reference src/mehp24/mehp24_utils.{h,cpp}:21-261, src/mehp24/mehp24_sort.cpp:251-282).
+//
+// A length-N vector lives in an N x N slot matrix (row-major, N^2 slots).  Orchestration only: every cc-> call is
+// a CUDA kernel schedule inside libckks_b200.so.  The reference reaches the context through
+// c->GetCryptoContext(); here the context is an explicit first argument.
+#pragma once
+#include <cmath>
+#include <vector>
+#include "comparison.h"
+
+namespace mehp24 {
+namespace utils {
+
+typedef Ciphertext<DCRTPoly> CT;
+typedef CryptoContext<DCRTPoly> CC;
+
+inline size_t log2ceil(size_t x) { size_t l = 0; while (((size_t)1 << l) < x) l++; return l; }
+
+// operator<< / operator>> of mehp24_utils.h:32-40
+inline CT rotl(const CC& cc, const CT& a, int32_t index) { return cc->EvalRotate(a, index); }
+inline CT rotr(const CC& cc, const CT& a, int32_t index) { return cc->EvalRotate(a, -index); }
+// ciphertext * vector<double>: one-argument MakeCKKSPackedPlaintext (level 0, batch-size slots), mehp24_utils.h:66-72
+inline CT mulVec(const CC& cc, const CT& a, const std::vector<double>& v) { return cc->EvalMult(a, cc->MakeCKKSPackedPlaintext(v)); }
+inline CT addVec(const CC& cc, const CT& a, const std::vector<double>& v) { return cc->EvalAdd(a, cc->MakeCKKSPackedPlaintext(v)); }
+
+inline CT maskRow(const CC& cc, const CT& c, size_t n, size_t row) {        // mehp24_utils.cpp:21-30
+    std::vector<double> m(n * n, 0.0);
+    for (size_t i = 0; i < n; i++) m[n * row + i] = 1.0;
+    return mulVec(cc, c, m);
+}
+inline CT maskColumn(const CC& cc, const CT& c, size_t n, size_t col) {     // :32-42
+    std::vector<double> m(n * n, 0.0);
+    for (size_t i = 0; i < n; i++) m[n * i + col] = 1.0;
+    return mulVec(cc, c, m);
+}
+inline CT replicateRow(const CC& cc, CT c, size_t n) {                      // :44-50  row 0 -> every row
+    for (size_t i = 0; i < log2ceil(n); i++) c = cc->EvalAdd(c, rotr(cc, c, 1 << (log2ceil(n) + i)));
+    return c;
+}
+inline CT replicateColumn(const CC& cc, CT c, size_t n) {                   // :52-58  column 0 -> every column
+    for (size_t i = 0; i < log2ceil(n); i++) c = cc->EvalAdd(c, rotr(cc, c, 1 << i));
+    return c;
+}
+inline CT sumRows(const CC& cc, CT c, size_t n, bool maskOutput = false, size_t outputRow = 0) {   // :60-69
+    for (size_t i = 0; i < log2ceil(n); i++) c = cc->EvalAdd(c, rotr(cc, c, 1 << (log2ceil(n) + i)));
+    return maskOutput ? maskRow(cc, c, n, outputRow) : c;
+}
+inline CT sumColumns(const CC& cc, CT c, size_t n, bool maskOutput = false) {                       // :71-80
+    for (size_t i = 0; i < log2ceil(n); i++) c = cc->EvalAdd(c, rotl(cc, c, 1 << i));
+    return maskOutput ? maskColumn(cc, c, n, 0) : c;
+}
+inline CT transposeRow(const CC& cc, CT c, size_t n, bool maskOutput = false) {                     // :82-91
+    for (size_t i = 1; i <= log2ceil(n); i++) c = cc->EvalAdd(c, rotr(cc, c, (int32_t)(n * (n - 1) / ((size_t)1 << i))));
+    return maskOutput ? maskColumn(cc, c, n, 0) : c;
+}
+inline CT transposeColumn(const CC& cc, CT c, size_t n, bool maskOutput = false) {                  // :93-103
+    for (size_t i = 1; i <= log2ceil(n); i++) c = cc->EvalAdd(c, rotl(cc, c, (int32_t)(n * (n - 1) / ((size_t)1 << i))));
+    return maskOutput ? maskRow(cc, c, n, 0) : c;
+}
+
+// signAdv (:246-261): dg x g_3, (df - 1) x f_3, then f_3 rescaled to (1 + sign) / 2, all through EvalPolyLinear
+inline CT signAdv(const CC& cc, CT c, size_t dg, size_t df) {
+    const std::vector<double> f3 = {0, 35.0 / 16.0, 0, -35.0 / 16.0, 0, 21.0 / 16.0, 0, -5.0 / 16.0};
+    const std::vector<double> f3_final = {0.5, 35.0 / 32.0, 0, -35.0 / 32.0, 0, 21.0 / 32.0, 0, -5.0 / 32.0};
+    const std::vector<double> g3 = {0, 4589.0 / 1024.0, 0, -16577.0 / 1024.0, 0, 25614.0 / 1024.0, 0, -12860.0 / 1024.0};
+    for (size_t d = 0; d < dg; d++) c = cc->EvalPolyLinear(c, g3);
+    for (size_t d = 0; d + 1 < df; d++) c = cc->EvalPolyLinear(c, f3);
+    return cc->EvalPolyLinear(c, f3_final);
+}
+// indicatorAdv (:166-174): 1 where |x| < 1/2 on x in (-b, b)
+inline CT indicatorAdv(const CC& cc, const CT& c, double b, size_t dg, size_t df) {
+    CT tmp = cc->EvalMult(c, 1.0 / b);
+    CT c1 = signAdv(cc, cc->EvalAdd(tmp, 0.5 / b), dg, df);
+    CT c2 = signAdv(cc, cc->EvalSub(tmp, 0.5 / b), dg, df);
+    return cc->EvalMult(c1, cc->EvalSub(1.0, c2));
+}
+// getRotationIndices (:186-213)
+inline std::vector<int32_t> getRotationIndices(size_t matrixSize) {
+    int sz = (int)matrixSize;
+    std::vector<int32_t> idx;
+    if (matrixSize > 256) {
+        for (size_t i = 0; i < matrixSize / 256; i++) { idx.push_back((int32_t)(i * 256)); idx.push_back(-(int32_t)(i * 256)); }
+        sz = 256;
+    }
+    const int lg = (int)log2ceil((size_t)sz);
+    for (int i = 0; i < lg; i++) {
+        idx.push_back(1 << i); idx.push_back(-(1 << i));
+        idx.push_back(-(1 << (lg + i)));
+        const int32_t t = sz * (sz - 1) / (1 << (i + 1));
+        idx.push_back(t); idx.push_back(-t);
+    }
+    return idx;
+}
+// multiplicative depth of the fixture per N (tests/mehp24/Mehp24SortTest.cpp:39-72)
+inline int fixtureDepth(int n) {
+    switch (n) { case 4: return 31; case 8: case 16: return 35; case 32: case 64: return 42; case 128: return 46;
+                 case 256: return 49; case 512: return 57; case 1024: return 60; case 2048: return 64; default: return 0; }
+}
+
+}  // namespace utils
+
+// sortFG, single ciphertext, Comparison-based overload (mehp24_sort.cpp:251-282)
+inline Ciphertext<DCRTPoly> sortFG(Ciphertext<DCRTPoly> c, const size_t vectorLength, SignFunc SignFunc, SignConfig& Cfg,
+                                   std::unique_ptr<Comparison>& comp, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> m_cc) {
+    using namespace utils;
+    const size_t n = vectorLength;
+    CT VR = replicateRow(m_cc, c, n);                                               // every row = the vector
+    CT VC = replicateColumn(m_cc, transposeRow(m_cc, c, n, true), n);               // every column = the vector
+    CT C = comp->compare(m_cc, VR, VC, SignFunc, Cfg);                              // C[i][j] = (v_j > v_i)
+    CT R = sumRows(m_cc, C, n);                                                     // rank of v_j (+1/2) in every row
+    std::vector<double> subMask(n * n);
+    for (size_t i = 0; i < n; i++) for (size_t j = 0; j < n; j++) subMask[i * n + j] = -1.0 * (double)i - 0.5;
+    CT M = indicatorAdv(m_cc, addVec(m_cc, R, subMask), (double)n, dg_i, df_i);     // M[i][j] = [rank_j == i]
+    CT tmp = m_cc->EvalMult(M, VR);                                                 // (computed twice in the reference, :275-277)
+    CT S = sumColumns(m_cc, m_cc->EvalMult(M, VR), n, true);                        // column 0: sorted values
+    (void)tmp;
+    return transposeColumn(m_cc, S, n, true);                                       // back to row 0
+}
+
+}  // namespace mehp24

@@ -219,6 +219,13 @@ class CryptoContextImpl {
     CT EvalRotate(const CT& a, int32_t index) const {
         ckks_ct_t* o = nullptr; ckks_check(ckks_eval_rotate(ctx, a->h, index, &o), "EvalRotate"); return wrap(o);
     }
+    // EvalFastRotationPrecompute / EvalFastRotation (rotation.h:286,344-347): the digits are an opaque handle
+    CT EvalFastRotationPrecompute(const CT& a) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_fast_rotation_precompute(ctx, a->h, &o), "EvalFastRotationPrecompute"); return wrap(o);
+    }
+    CT EvalFastRotation(const CT& a, int32_t index, uint32_t /*cyclotomicOrder*/, const CT& digits) const {
+        ckks_ct_t* o = nullptr; ckks_check(ckks_fast_rotation(ctx, a->h, index, digits->h, &o), "EvalFastRotation"); return wrap(o);
+    }
     bool HasRotationKey(int32_t index) const { return ckks_has_rotation_key(ctx, index) != 0; }
     // ---- polynomial evaluators (sort_algo.h:727-728, sign.cpp:76, mehp24_utils.cpp:256-259)
     CT EvalChebyshevSeriesPS(const CT& x, const std::vector<double>& coeffs, double a, double b) const {

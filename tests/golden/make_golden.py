@@ -158,7 +158,8 @@ def oracle_limbs():
     cc = OracleCC(Context(Params(10, depth, 40, 60, 0, True, 1)))
     cc.keygen(); cc.relin_keygen(); cc.rot_keygen(rots)
     arr = np.random.default_rng(n).permutation(n) / n
-    res = algos.DirectSort(cc, n, rots).sort(cc.encrypt(cc.encode(arr, slots=n)), (3, 2, 2))
+    ct_in = cc.encrypt(cc.encode(arr, slots=n))       # encryption counter 0; the sorter's zero cache takes counter 1
+    res = algos.DirectSort(cc, n, rots).sort(ct_in, (3, 2, 2))
     out["direct_sort_n4_ring10_seed1"] = {
         "params": {"log_n": 10, "depth": depth, "scale": 40, "seed": 1, "rots": rots, "sign_cfg": [3, 2, 2]},
         "input": arr.tolist(), "sha256": digest(res.d), "level": int(res.level),

@@ -150,7 +150,8 @@ def test_engine_direct_sort_n4_matches_committed_digest():
     eng = sf.Engine(p["log_n"], p["depth"], p["scale"], seed=p["seed"])
     eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(p["rots"])
     arr = np.array(g["input"])
-    out = sf.DirectSort(eng, 4, p["rots"]).sort(eng.encrypt(eng.encode(arr, slots=4)), tuple(p["sign_cfg"]))
+    ct_in = eng.encrypt(eng.encode(arr, slots=4))     # encryption counter 0, as in make_golden.py
+    out = sf.DirectSort(eng, 4, p["rots"]).sort(ct_in, tuple(p["sign_cfg"]))
     assert out.level == g["level"] and digest(out.export()) == g["sha256"]
     assert np.allclose(eng.decrypt(out, 4), g["decrypted"], atol=1e-12)
     assert np.max(np.abs(eng.decrypt(out, 4) - np.sort(arr))) < 0.01      # tests/DirectSortTest.cpp:194

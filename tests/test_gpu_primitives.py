@@ -124,3 +124,38 @@ def test_missing_rotation_key_fails(pair12):
     ct = eng.encrypt(eng.encode([1.0, 2.0], slots=2))
     with pytest.raises(sf.CkksError):
         eng.EvalRotate(ct, 3)
+
+
+def test_hoisted_rotations_bit_exact(pair12):
+    """EvalFastRotationPrecompute / EvalFastRotation (src/rotation.h:286,344-347) and the per-handle ModUp cache of
+    EvalRotate give the same limbs as an un-hoisted EvalRotate (the oracle's)"""
+    eng, orc = pair12
+    x = np.linspace(-0.9, 0.9, 8)
+    co = orc.encrypt(orc.encode(x, slots=8))
+    ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+    digits = eng.EvalFastRotationPrecompute(ce)
+    for r in (1, -1, 5):
+        want = orc.EvalRotate(co, r)
+        same(eng.EvalFastRotation(ce, r, 2 * eng.n, digits), want)
+        same(eng.EvalRotate(ce, r), want)        # 2nd and 3rd call reuse the digits cached on the handle
+    sq = eng.EvalMult(ce, ce)                    # deeper level, noiseScaleDeg 2
+    same(eng.EvalRotate(eng.EvalRotate(sq, 1), 5), orc.EvalRotate(orc.EvalRotate(orc.EvalMult(co, co), 1), 5))
+
+
+def test_compact_plaintext_ops_bit_exact(pair12):
+    """sparsely packed plaintexts are kept compact on the device (one value per replication group); every op that
+    consumes them must give the limbs of the full-length form"""
+    eng, orc = pair12
+    x = np.array([0.25, -0.5, 0.75, 0.1])
+    co = orc.encrypt(orc.encode(x, slots=4))
+    ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+    for slots in (4, 64, eng.n // 2):
+        v = np.arange(slots) / slots - 0.3
+        for level in (0, 2):
+            po, pe = orc.MakeCKKSPackedPlaintext(v, 1, level, None, slots), eng.MakeCKKSPackedPlaintext(v, 1, level, None, slots)
+            assert np.array_equal(pe.export(), po.d)
+            same(eng.EvalMult(ce, pe), orc.EvalMult(co, po))
+            same(eng.EvalAdd(ce, pe), orc.EvalAdd(co, po))
+            same(eng.EvalSub(pe, ce), orc.EvalSub(po, co))
+            assert np.allclose(eng.decrypt(eng.encrypt(pe), slots)[:4], v[:4], atol=1e-6)
+            assert np.allclose(eng.decrypt(pe, slots)[:4], v[:4], atol=1e-6)
