@@ -36,7 +36,7 @@ static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_err
 void context_release(Context* c) {
     if (!c->dry) {
         cudaStreamSynchronize(c->stream);
-        cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs);
+        cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs); cudaFree(c->d_twd); cudaFree(c->d_itwd);
         for (auto& kv : c->ninv_pairs_rep) cudaFree(kv.second);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
         if (c->enc_pinned) cudaFreeHost(c->enc_pinned);

@@ -7,6 +7,7 @@
 // (tests/DirectSortTest.cpp:29-44, src/sort_algo.h:87-201, src/kway_adapter.h:41-64).
 // Host-side setup code only; nothing here is on the timed path.
 #include "engine.h"
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <stdexcept>
@@ -160,6 +161,16 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
     }
     c->d_mod = upload(c, c->h_mod);
     c->d_tw = upload(c, tw); c->d_itw = upload(c, itw); c->d_ninv_pairs = upload(c, ninvp);
+    {   // double copies of the twiddles for the FP64 butterfly path (ntt.cu); rows of wider moduli stay zero
+        std::vector<double> twd((size_t)M * n, 0.0), itwd((size_t)M * n, 0.0);
+        bool any = false;
+        for (int i = 0; i < M; i++) {
+            if (c->h_mod[i].bits > 44) continue;
+            any = true;
+            for (int k = 0; k < n; k++) { const size_t o = (size_t)i * n + k; twd[o] = (double)tw[2 * o]; itwd[o] = (double)itw[2 * o]; }
+        }
+        if (any && !getenv("CKKS_B200_NO_FP64_NTT")) { c->d_twd = upload(c, twd); c->d_itwd = upload(c, itwd); }
+    }
     // special FFT tables (same expressions as oracle Context.fft_tables)
     const int Mc = 2 * n;
     std::vector<double> ksi(2 * (size_t)(Mc + 1));

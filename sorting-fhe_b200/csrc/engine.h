@@ -85,6 +85,7 @@ struct Context {
     ModInfo* d_mod = nullptr;               // [M]
     std::vector<ModInfo> h_mod;
     u64 *d_tw = nullptr, *d_itw = nullptr;   // [M][n] (w, Shoup companion) pairs: psi / psi^-1 powers, bit-reversed
+    double *d_twd = nullptr, *d_itwd = nullptr;   // [M][n] the same twiddles as doubles (moduli <= 44 bits; FP64 butterflies)
     u64* d_ninv_pairs = nullptr;             // [M] (n^-1, Shoup companion): default final factor of the inverse NTT
     std::map<int, u64*> ninv_pairs_rep;      // lrep -> [M] ((n >> lrep)^-1, Shoup) for transforms of compact plaintexts
     double* d_ksi = nullptr;                // [2n+1] complex roots for the special FFT

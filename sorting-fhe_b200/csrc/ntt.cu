@@ -100,6 +100,7 @@ struct NttArgs {
     RowMap smap, dmap;
     const ModInfo* mi;
     const tw_t* tw;          // [M][n] forward or inverse twiddle pairs
+    const double* twd;       // [M][n] the same twiddles as doubles (rows of moduli <= FP_BITS bits), or nullptr
     const tw_t* scale;       // INV only: final factor (n^-1 [* extra]) as Shoup pair, indexed by modulus id
     int logn, T, a;          // T = tile bits, a = logn - T stages in pass A
     int twlog;               // log2 of the twiddle table row length (ring size; >= logn, see compact plaintexts)
@@ -150,8 +151,8 @@ __device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, in
 // LOGN_C != 0: ring size, pass and round schedule are compile-time constants (all index arithmetic folds);
 // LOGN_C == 0: generic runtime form.
 template <bool INV, bool FIX, int LOGN_C, int PASS_C>
-__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const int row, const int mid, const ModInfo& mi,
-                                         u64* sm) {
+__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const int row, const int tile, const int mid,
+                                         const ModInfo& mi, u64* sm, const u64 (&vin)[8]) {
     constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
     constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
     const Sched& S = LOGN_C ? SC : SR;
@@ -161,7 +162,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     const tw_t* W = A.tw + ((size_t)mid << A.twlog);
     const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
     u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
-    const int tile = blockIdx.x, u = threadIdx.x;
+    const int u = threadIdx.x;
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     // global word offset of tile-local index L
     auto gaddr = [&](int L) -> size_t {
@@ -187,7 +188,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         const int p = S.p[ri];
         if (ri == 0) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) r[k] = src[gaddr(local_index(u, k, p))];
+            for (int k = 0; k < 8; k++) r[k] = vin[k];
             if (!INV && A.first_pass && A.f.pro == PRO_SWITCHMOD) {
                 // rescale: the source limb holds coefficients mod q_last; centred switch to this row's modulus
                 const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
@@ -248,27 +249,232 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// FP64 butterflies for moduli of at most FP_BITS bits (the 40-bit scaling primes: 30 of the 32 Q limbs of the
+// DirectSort card).  B200 issues DFMA at the same rate as IMAD (64 lanes/clk/SM), and a double carries a 53-bit
+// product piece where an IMAD carries 32 bits, so x*w mod q costs 6 FP64 instructions instead of ~20 integer ones:
+//     h = x*w (rounded), l = fma(x, w, -h) (exact low part), qh = rint(h / q), r = fma(-qh, q, h) + l
+// Every intermediate is an integer below 2^53, hence exact; residues are centred, |r| <= q/2 + 1.  Values stay
+// lazy (forward: +q/2 per stage; inverse: doubling, folded back every second round) and are canonicalised once on
+// the final store, so the results are the same residues as the integer path, bit for bit.
+#define FP_BITS 44
+#define FP_MAGIC 6755399441055744.0   // 1.5 * 2^52: adding and subtracting it rounds to the nearest integer
+#define FP_2P52 4503599627370496.0
+__device__ __forceinline__ double fp_from_u64(u64 v) {   // v < 2^52
+    return __dadd_rn(__longlong_as_double((long long)(v | 0x4330000000000000ULL)), -FP_2P52);
+}
+__device__ __forceinline__ u64 fp_to_u64(double y) {     // integer y in [0, 2^52)
+    return (u64)__double_as_longlong(__dadd_rn(y, FP_2P52)) & 0x000FFFFFFFFFFFFFULL;
+}
+__device__ __forceinline__ double fp_mulmod(double a, double w, double q, double qinv) {
+    const double h = __dmul_rn(a, w);
+    const double l = __fma_rn(a, w, -h);
+    const double qh = __dadd_rn(__fma_rn(h, qinv, FP_MAGIC), -FP_MAGIC);
+    return __dadd_rn(__fma_rn(-qh, q, h), l);
+}
+__device__ __forceinline__ double fp_reduce(double x, double q, double qinv) {   // -> [-q/2 - 1, q/2 + 1]
+    const double t = __dadd_rn(__fma_rn(x, qinv, FP_MAGIC), -FP_MAGIC);
+    return __fma_rn(-t, q, x);
+}
+__device__ __forceinline__ u64 fp_canon(double x, double q, double qinv) {
+    double y = fp_reduce(x, q, qinv);
+    if (y < 0.0) y = __dadd_rn(y, q);
+    return fp_to_u64(y);
+}
+
+template <bool INV, int J0, int J1>
+__device__ __forceinline__ void round8_fp(double (&r)[8], const double* __restrict__ W, const u32 ehi, const int s0, const double q,
+                                          const double qinv) {
+    if (!INV) {
+#pragma unroll
+        for (int j = J0; j < J1; j++) {
+            const int bit = 4 >> j;
+            const double* Ws = W + ((1u << (s0 + j)) + (ehi << j));
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                const double T = fp_mulmod(r[k | bit], __ldg(Ws + (k >> (3 - j))), q, qinv);
+                const double x = r[k];
+                r[k] = __dadd_rn(x, T);
+                r[k | bit] = __dadd_rn(x, -T);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = J1 - 1; j >= J0; j--) {
+            const int bit = 4 >> j;
+            const double* Ws = W + ((1u << (s0 + j)) + (ehi << j));
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                const double x = r[k], y = r[k | bit];
+                r[k] = __dadd_rn(x, y);
+                r[k | bit] = fp_mulmod(__dadd_rn(x, -y), __ldg(Ws + (k >> (3 - j))), q, qinv);
+            }
+        }
+    }
+}
+template <bool INV>
+__device__ __forceinline__ void do_round_fp(double (&r)[8], const double* W, u32 ehi, int s0, double q, double qinv, int j0, int j1) {
+    if (j0 == 0 && j1 == 3) round8_fp<INV, 0, 3>(r, W, ehi, s0, q, qinv);
+    else if (j0 == 1 && j1 == 3) round8_fp<INV, 1, 3>(r, W, ehi, s0, q, qinv);
+    else if (j0 == 2 && j1 == 3) round8_fp<INV, 2, 3>(r, W, ehi, s0, q, qinv);
+    else if (j0 == 0 && j1 == 2) round8_fp<INV, 0, 2>(r, W, ehi, s0, q, qinv);
+    else round8_fp<INV, 0, 1>(r, W, ehi, s0, q, qinv);
+}
+
+// same tiling, passes and round schedule as ntt_tile; between the two passes of a transform the buffer holds the
+// raw bits of the (lazy) doubles
 template <bool INV, int LOGN_C, int PASS_C>
-__global__ void __launch_bounds__(256)
-ntt_kernel(NttArgs A, Sched S, LimbMods mods) {
+__device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, const int row, const int tile, const int mid,
+                                            const ModInfo& mi, u64* sm, const u64 (&vin)[8]) {
+    constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
+    constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
+    const Sched& S = LOGN_C ? SC : SR;
+    const u64 qi = mi.q;
+    const double q = (double)qi, qinv = __drcp_rn(q);
+    const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
+    const int cb = T - a_;
+    const double* W = A.twd + ((size_t)mid << A.twlog);
+    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
+    u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
+    double* smd = reinterpret_cast<double*>(sm);
+    const int u = threadIdx.x;
+    const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
+    auto gaddr = [&](int L) -> size_t {
+        return strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
+    };
+    if (!strided) {
+        for (int sl = 3; sl < T; sl++) {   // pull this tile's twiddles (2^T - 1 doubles) into L1, one 128-byte line per prefetch
+            const double* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
+            for (int g = u * 16; g < (1 << sl); g += 16 * (1 << (T - 3)))
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
+        }
+    }
+    double r[8];
+    const int nr = LOGN_C ? SC.nr : SR.nr;
+#pragma unroll
+    for (int ri = 0; ri < (LOGN_C ? SC.nr : SR.nr); ri++) {
+        const int p = S.p[ri];
+        if (ri == 0) {
+            u64 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) v[k] = vin[k];
+            if (A.first_pass) {
+                if (!INV && A.f.pro == PRO_SWITCHMOD) {   // rescale: centred switch of the q_last residues to this row's modulus
+                    const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        const bool neg = v[k] > half;
+                        u64 a = neg ? ql - v[k] : v[k];
+                        a -= __umul64hi(a, mi.qrecip) * qi;
+                        if (a >= qi) a -= qi;
+                        v[k] = neg ? (a ? qi - a : 0) : a;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++) r[k] = fp_from_u64(v[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; k++) r[k] = __longlong_as_double((long long)v[k]);
+            }
+        } else {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; k++) r[k] = smd[padi(local_index(u, k, p))];
+        }
+        if (INV && (ri & 1) == 0 && !(ri == 0 && A.first_pass)) {   // fold the doubling of the GS sums back below q
+#pragma unroll
+            for (int k = 0; k < 8; k++) r[k] = fp_reduce(r[k], q, qinv);
+        }
+        const int L0 = local_index(u, 0, p);
+        u32 ehi; int s0;
+        if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = a_ - 1 - (p + 2 - cb); }
+        else { ehi = (u32)(((size_t)tile << T | (size_t)L0) >> (p + 3)); s0 = logn - 1 - (p + 2); }
+        do_round_fp<INV>(r, W, ehi, s0, q, qinv, S.j0[ri], S.j1[ri]);
+        if (ri + 1 < nr) {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; k++) smd[padi(local_index(u, k, p))] = r[k];
+        } else if (A.final_pass) {
+            u64 v[8];
+            if (!INV) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
+                if (A.f.epi == EPI_RESCALE) {
+                    const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
+                    const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        const u64 x = ein[gaddr(local_index(u, k, p))];
+                        v[k] = shoup_mul(sub_mod(x, v[k], qi), sc.x, sc.y, qi);
+                    }
+                }
+            } else {
+                const double sc = (double)A.scale[mid].x;
+#pragma unroll
+                for (int k = 0; k < 8; k++) v[k] = fp_canon(fp_mulmod(r[k], sc, q, qinv), q, qinv);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = v[k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = (u64)__double_as_longlong(r[k]);
+        }
+    }
+}
+
+// first-round words of tile `tile` of limb row `row` (the same index pattern for the integer and the FP64 path)
+template <bool INV, int LOGN_C, int PASS_C>
+__device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, const int row, const int tile, u64 (&v)[8]) {
+    constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
+    constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
+    const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
+    const int cb = T - a_, p = LOGN_C ? SC.p[0] : SR.p[0];
+    const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
+    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int L = local_index(threadIdx.x, k, p);
+        const size_t g = strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
+        v[k] = src[g];
+    }
+}
+
+// One CTA per work item id -> (row = id / tiles_per_row, tile = id % tiles_per_row).  (A persistent variant that
+// prefetched the next tile's words into registers was measured slower on B200: 80 registers cut the resident CTAs
+// from 4 to 3 per SM and 2048 tiles over 444 CTAs quantise badly -- 65 us vs 56 us for a 32-limb 2^17 transform.)
+template <bool INV, int LOGN_C, int PASS_C>
+__global__ void __launch_bounds__(256, 4)
+ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ LimbMods mods, int total,
+           int tpr_log) {
     extern __shared__ u64 sm[];
-    const int row = blockIdx.y;
+    const int id = blockIdx.x;
+    if (id >= total) return;
+    const int row = id >> tpr_log, tile = id & ((1 << tpr_log) - 1);
+    u64 v[8];
+    load_tile<INV, LOGN_C, PASS_C>(A, S, row, tile, v);
     const int mid = mods.m[row % mods.n];
     const ModInfo mi = A.mi[mid];
     const bool fix = INV ? (mi.bits > 46) : (mi.bits > 58);
-    if (fix) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, row, mid, mi, sm);
-    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, row, mid, mi, sm);
+    if (mi.bits <= FP_BITS && A.twd) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
+    else if (fix) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
+    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
 }
 
+template <bool INV, int LOGN_C, int PASS_C>
+static void launch_one(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
+    ntt_kernel<INV, LOGN_C, PASS_C><<<total, threads, smem, c->stream>>>(A, S, m, total, tpr_log);
+}
 template <bool INV, int PASS_C>
-static void launch_pass(Context* c, dim3 grid, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
+static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
     switch (A.logn) {   // compile-time schedules for the ring sizes of the reference's fixtures (+ their compact plaintexts)
-        case 17: ntt_kernel<INV, 17, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
-        case 16: ntt_kernel<INV, 16, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
-        case 15: ntt_kernel<INV, 15, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
-        case 13: ntt_kernel<INV, 13, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
-        case 12: ntt_kernel<INV, 12, PASS_C><<<grid, threads, smem, c->stream>>>(A, S, m); break;
-        default: ntt_kernel<INV, 0, 0><<<grid, threads, smem, c->stream>>>(A, S, m); break;
+        case 17: launch_one<INV, 17, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
+        case 16: launch_one<INV, 16, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
+        case 15: launch_one<INV, 15, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
+        case 13: launch_one<INV, 13, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
+        case 12: launch_one<INV, 12, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
+        default: launch_one<INV, 0, 0>(c, total, tpr_log, threads, smem, A, S, m); break;
     }
 }
 
@@ -298,29 +504,30 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     ProfScope ps(c, KC_NTT, 16.0 * rows * (c->n >> lrep), (logn > TB_MAX) ? 2 : 1);
     const int threads = (1 << T) / 8;
     const size_t smem = (size_t)((1 << T) + ((1 << T) >> 3) + 8) * sizeof(u64);
-    dim3 grid((c->n >> lrep) >> T, rows);
+    const int tpr_log = logn - T, total = rows << tpr_log;   // tiles per row (log2), work items
     NttArgs A;
     A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a; A.twlog = c->log_n;
     A.smap = smap; A.dmap = dmap;
     if (fuse) A.f = *fuse; else A.f = NttFuse{};
     A.first_pass = 1;
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
+    A.twd = inverse ? c->d_itwd : c->d_twd;
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
     if (!inverse) {
         A.src = src;
         if (a > 0) {
             A.pass = 0; A.final_pass = 0;
-            launch_pass<false, 0>(c, grid, threads, smem, A, make_sched(T, a, false), m);
+            launch_pass<false, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, false), m);
             A.src = dst; A.smap = dmap; A.first_pass = 0;
         }
         A.pass = 1; A.final_pass = 1;
-        launch_pass<false, 1>(c, grid, threads, smem, A, make_sched(T, T, false), m);
+        launch_pass<false, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, false), m);
     } else {
         A.src = src; A.pass = 1; A.final_pass = a == 0;
-        launch_pass<true, 1>(c, grid, threads, smem, A, make_sched(T, T, true), m);
+        launch_pass<true, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, true), m);
         if (a > 0) {
             A.src = dst; A.smap = dmap; A.pass = 0; A.final_pass = 1; A.first_pass = 0;
-            launch_pass<true, 0>(c, grid, threads, smem, A, make_sched(T, a, true), m);
+            launch_pass<true, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, true), m);
         }
     }
 }
