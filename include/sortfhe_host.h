@@ -43,6 +43,28 @@ int sortfhe_decompose(int n, int rotation, int wrap, int algo, const int32_t* ro
 /* selectDoubledSincCoefficients<N>() / selectCoefficients<N>() (src/sort_algo.h:725-728, 627-629) */
 int sortfhe_sinc_coefficients(int n, int doubled, double* coeffs, int cap, int* count);
 
+/* MEHP24 ranking sort (reference src/mehp24/): getRotationIndices (mehp24_utils.cpp:186-213) + the fixture's depth
+ * table (tests/mehp24/Mehp24SortTest.cpp:39-72); sortFG single-ciphertext, Comparison-based overload
+ * (mehp24_sort.cpp:251-282) on a length-n vector stored in an n x n slot matrix; the matrix utilities
+ * (mehp24_utils.cpp:44-103; op: 0 replicateRow, 1 replicateColumn, 2 sumRows, 3 sumColumns, 4 transposeRow,
+ * 5 transposeColumn); indicatorAdv (mehp24_utils.cpp:166-174). */
+int sortfhe_mehp24_params(int n, int* mult_depth, int32_t* rotations, int cap, int* count);
+int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sign_n, int dg, int df, int dg_i, int df_i,
+                           ckks_ct_t** out);
+int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out);
+int sortfhe_mehp24_indicator_adv(ckks_ctx_t* ctx, const ckks_ct_t* x, double b, int dg, int df, ckks_ct_t** out);
+
+/* k-way sorting network of HKC+21 (reference src/k-way/, src/kway_adapter.h): KWayAdapter<N>::getSizeParameters
+ * (kway_adapter.h:41-64); Masking sortType / getRotateDistance / genIndices (Masking.cpp:26-167); Sorter::sorter
+ * (Sorter.cpp:284-404) over stages [first_stage, last_stage) (last_stage < 0: all), k in {2, 3}, on a copy of the
+ * input as KWayAdapter::sort does.  mult_depth is SignConfig::multDepth, the budget checkLevelAndBoot tests; the
+ * call fails where the reference would bootstrap (EvalBootstrap is not implemented). */
+int sortfhe_kway_params(int n, int* mult_depth, int* scaling_mod_size, int* first_mod_size, int32_t* rotations, int cap, int* count);
+int sortfhe_kway_sort_type(int k, int M, int stage, int* m, int* log_dist, int* slope, int* stage_count, int64_t* rotate_distance);
+int sortfhe_kway_gen_indices(int num_slots, int k, int M, int m, int log_dist, int slope, int32_t* out);
+int sortfhe_kway_sort(ckks_ctx_t* ctx, const ckks_ct_t* input, int num_slots, int k, int M, int sign_n, int dg, int df,
+                      int mult_depth, int first_stage, int last_stage, ckks_ct_t** out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -233,3 +233,99 @@ class DirectSort:
         """DirectSort::sort (:752-774)"""
         rank = self.construct_rank(ct_in, sign_cfg)
         return self.rotation_index_check_n(rank, ct_in)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# MEHP24 single-ciphertext sortFG (reference src/mehp24/mehp24_sort.cpp:251-282, mehp24_utils.cpp:21-261)
+F3_POLY = [0, 35.0 / 16.0, 0, -35.0 / 16.0, 0, 21.0 / 16.0, 0, -5.0 / 16.0]
+F3_FINAL_POLY = [0.5, 35.0 / 32.0, 0, -35.0 / 32.0, 0, 21.0 / 32.0, 0, -5.0 / 32.0]
+G3_POLY = [0, 4589.0 / 1024.0, 0, -16577.0 / 1024.0, 0, 25614.0 / 1024.0, 0, -12860.0 / 1024.0]
+
+
+def _lg(n):
+    return int(np.ceil(np.log2(n)))
+
+
+class Mehp24:
+    """matrix-in-slots utilities on an n x n slot matrix; batch = n*n slots (tests/mehp24/Mehp24SortTest.cpp:36-37)"""
+
+    def __init__(self, cc, n):
+        self.cc, self.n, self.batch = cc, n, n * n
+
+    def _pt(self, v):  # one-argument MakeCKKSPackedPlaintext: level 0, batch-size slots (mehp24_utils.h:66-72)
+        return self.cc.MakeCKKSPackedPlaintext(v, 1, 0, None, self.batch)
+
+    def mask_row(self, c, row):  # mehp24_utils.cpp:21-30
+        m = np.zeros(self.batch); m[self.n * row:self.n * (row + 1)] = 1.0
+        return self.cc.EvalMult(c, self._pt(m))
+
+    def mask_column(self, c, col):  # :32-42
+        m = np.zeros(self.batch); m[col::self.n] = 1.0
+        return self.cc.EvalMult(c, self._pt(m))
+
+    def _fold(self, c, amounts):
+        for r in amounts:
+            c = self.cc.EvalAdd(c, self.cc.EvalRotate(c, r))
+        return c
+
+    def replicate_row(self, c):  # :44-50
+        return self._fold(c, [-(1 << (_lg(self.n) + i)) for i in range(_lg(self.n))])
+
+    def replicate_column(self, c):  # :52-58
+        return self._fold(c, [-(1 << i) for i in range(_lg(self.n))])
+
+    def sum_rows(self, c, mask=False, row=0):  # :60-69
+        c = self._fold(c, [-(1 << (_lg(self.n) + i)) for i in range(_lg(self.n))])
+        return self.mask_row(c, row) if mask else c
+
+    def sum_columns(self, c, mask=False):  # :71-80
+        c = self._fold(c, [1 << i for i in range(_lg(self.n))])
+        return self.mask_column(c, 0) if mask else c
+
+    def transpose_row(self, c, mask=False):  # :82-91
+        n = self.n
+        c = self._fold(c, [-(n * (n - 1) // (1 << i)) for i in range(1, _lg(n) + 1)])
+        return self.mask_column(c, 0) if mask else c
+
+    def transpose_column(self, c, mask=False):  # :93-103
+        n = self.n
+        c = self._fold(c, [n * (n - 1) // (1 << i) for i in range(1, _lg(n) + 1)])
+        return self.mask_row(c, 0) if mask else c
+
+    def sign_adv(self, c, dg, df):  # :246-261
+        for _ in range(dg):
+            c = self.cc.EvalPolyLinear(c, G3_POLY)
+        for _ in range(df - 1):
+            c = self.cc.EvalPolyLinear(c, F3_POLY)
+        return self.cc.EvalPolyLinear(c, F3_FINAL_POLY)
+
+    def indicator_adv(self, c, b, dg, df):  # :166-174
+        cc = self.cc
+        tmp = cc.EvalMult(c, 1.0 / b)
+        c1 = self.sign_adv(cc.EvalAdd(tmp, 0.5 / b), dg, df)
+        c2 = self.sign_adv(cc.EvalSub(tmp, 0.5 / b), dg, df)
+        return cc.EvalMult(c1, cc.EvalSub(1.0, c2))
+
+    def sort_fg(self, c, sign_cfg, dg_i, df_i):  # mehp24_sort.cpp:251-282
+        cc, n = self.cc, self.n
+        VR = self.replicate_row(c)
+        VC = self.replicate_column(self.transpose_row(c, True))
+        C = compare(cc, VR, VC, *sign_cfg)
+        R = self.sum_rows(C)
+        sub = np.repeat(-1.0 * np.arange(n) - 0.5, n)
+        M = self.indicator_adv(cc.EvalAdd(R, self._pt(sub)), float(n), dg_i, df_i)
+        cc.EvalMult(M, VR)  # computed twice in the reference (:275-277)
+        S = self.sum_columns(cc.EvalMult(M, VR), True)
+        return self.transpose_column(S, True)
+
+
+def mehp24_rotation_indices(n):  # getRotationIndices (mehp24_utils.cpp:186-213)
+    sz, idx = n, []
+    if n > 256:
+        for i in range(n // 256):
+            idx += [i * 256, -i * 256]
+        sz = 256
+    lg = _lg(sz)
+    for i in range(lg):
+        idx += [1 << i, -(1 << i), -(1 << (lg + i)), sz * (sz - 1) // (1 << (i + 1)), -(sz * (sz - 1) // (1 << (i + 1)))]
+    return idx

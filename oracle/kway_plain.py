@@ -95,3 +95,66 @@ def gen_indices(num_slots, k, M, m, log_dist, slope):
 def gen_mask(indices, index0, index1):
     """Masking.cpp:145-155"""
     return ((indices[0] == index0) & (indices[1] == index1)).astype(np.float64)
+
+
+def network_plain(x, k, M, compare=None, first_stage=0, last_stage=None):
+    """Sorter::sorter (Sorter.cpp:284-404) on plain doubles for k in {2, 3}: `x` has next_pow2(k^M) entries (the
+    ciphertext's slot count, kway_adapter.h:44), zero beyond k^M; rotations wrap at len(x).  `compare(a, b)` defaults
+    to the exact (a > b) with 1/2 on ties -- the function Comparison::compare approximates."""
+    n = k ** M
+    x = np.array(x, dtype=np.float64)
+    B = len(x)
+    if compare is None:
+        compare = lambda a, b: (np.sign(a - b) + 1.0) / 2.0
+    left = lambda v, r: np.roll(v, -r)
+    right = lambda v, r: np.roll(v, r)
+    pad = lambda m: np.concatenate([m, np.zeros(B - n)])
+
+    def partner(v, idx, log_dist, slope):  # rightRotateForSort (:180-249)
+        mask_left = pad((idx[1] < idx[0]).astype(float))
+        mask_right = [pad(((idx[0] > 0) & (idx[0] == idx[1]) & (idx[0] - 1 == i)).astype(float)) for i in range(k)]
+        rot = get_rotate_distance(k, log_dist, slope)
+        lft = v * mask_left
+        fix = None
+        if slope == 0 or slope == k // 2 + 1:
+            top = k - 1 if slope == 0 else k - 2
+            rgt = v * mask_right[top]
+            if slope != 0:
+                fix = v - lft - rgt
+            out = right(lft, rot) + left(rgt, top * rot)
+        else:
+            rgt = [v * mask_right[i] for i in range(k)]
+            fix = v - lft - sum(rgt)
+            out = right(lft, rot)
+            for i in range(1, k):
+                out = out + left(rgt[i], i * rot)
+        return out, fix
+
+    def run_two(v, idx, shift, comp):  # runTwoSorter (:8-38)
+        m2 = pad(gen_mask(idx, 2, 1))
+        lo, hi = two_sorter(v, left(v, shift), comp)
+        return lo * m2 + right(hi * m2, shift)
+
+    def run_three(v, idx, shift, comp):  # runThreeSorter (:40-70) with slotMatching3 (SortUtils.cpp:212-236)
+        m3 = pad(gen_mask(idx, 3, 1))
+        arr = [left(v, i * shift) for i in range(3)]
+        comps = [m3 - left(comp, shift), comp, m3 - left(comp, 2 * shift)]
+        lo, mid, hi = three_sorter(arr, comps)
+        return lo * m3 + right(mid * m3, shift) + right(hi * m3, 2 * shift)
+
+    stages = M + M * (M - 1) // 2 * ((k + 1) // 2)
+    for stage in range(first_stage, stages if last_stage is None else last_stage):
+        m, log_dist, slope = sort_type(k, M, stage)
+        shift = get_rotate_distance(k, log_dist, slope)
+        idx = gen_indices(n, k, M, m, log_dist, slope)
+        rot, fix = partner(x, idx, log_dist, slope)
+        comp = compare(x, rot)
+        if slope == 0:
+            x = run_two(x, idx, shift, comp) if k == 2 else run_three(x, idx, shift, comp)
+        elif slope == k // 2 + 1:
+            x = run_two(x, idx, shift, comp) + fix
+        elif k == 3 and slope == 1:
+            x = run_two(x, idx, shift, comp) + fix + run_three(x, idx, shift, comp)
+        else:
+            x = run_two(x, idx, shift, comp) + fix
+    return x

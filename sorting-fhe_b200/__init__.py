@@ -283,11 +283,11 @@ class Engine:
 
     def EvalFastRotationPrecompute(self, a):
         o = ctypes.c_void_p()
-        return self._out(_L.ckks_fast_rotation_precompute(self.h, a.h, ctypes.byref(o)), o)
+        return self._out(_L.ckks_fast_rotation_precompute(_vp(self.h), _vp(a.h), ctypes.byref(o)), o)
 
     def EvalFastRotation(self, a, r, m, digits):
         o = ctypes.c_void_p()
-        return self._out(_L.ckks_fast_rotation(self.h, a.h, ctypes.c_int32(r), digits.h, ctypes.byref(o)), o)
+        return self._out(_L.ckks_fast_rotation(_vp(self.h), _vp(a.h), int(r), _vp(digits.h), ctypes.byref(o)), o)
 
     def EvalChebyshevSeriesPS(self, x, coeffs, a=-1.0, b=1.0):
         v = np.ascontiguousarray(coeffs, dtype=np.float64)
@@ -353,6 +353,14 @@ _H.sortfhe_indicator.argtypes = [_vp, _vp, _d, _i, _i, _i, _pp]
 _H.sortfhe_rotate.argtypes = [_vp, _vp, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_decompose.argtypes = [_i, _i, _i, _i, _i32p, _i, _i32p, _i, _ip]
 _H.sortfhe_sinc_coefficients.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_double), _i, _ip]
+_H.sortfhe_kway_params.argtypes = [_i, _ip, _ip, _ip, _i32p, _i, _ip]
+_H.sortfhe_kway_sort_type.argtypes = [_i, _i, _i, _ip, _ip, _ip, _ip, ctypes.POINTER(ctypes.c_int64)]
+_H.sortfhe_kway_gen_indices.argtypes = [_i, _i, _i, _i, _i, _i, _i32p]
+_H.sortfhe_kway_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _pp]
+_H.sortfhe_mehp24_params.argtypes = [_i, _ip, _i32p, _i, _ip]
+_H.sortfhe_mehp24_sort_fg.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _pp]
+_H.sortfhe_mehp24_matrix_op.argtypes = [_vp, _vp, _i, _i, _i, _pp]
+_H.sortfhe_mehp24_indicator_adv.argtypes = [_vp, _vp, _d, _i, _i, _pp]
 
 
 def _hchk(rc):
@@ -432,3 +440,66 @@ def sinc_coefficients(n, doubled=True):
     buf = np.zeros(16384, dtype=np.float64)
     _hchk(_H.sortfhe_sinc_coefficients(n, 1 if doubled else 0, _f64p(buf), buf.size, ctypes.byref(cnt)))
     return buf[:cnt.value].copy()
+
+
+# ---------------------------------------------------------------- MEHP24 (reference src/mehp24/)
+MEHP24_OPS = {"replicateRow": 0, "replicateColumn": 1, "sumRows": 2, "sumColumns": 3, "transposeRow": 4, "transposeColumn": 5}
+
+
+def mehp24_params(n):
+    """(fixture multDepth, getRotationIndices(n)) -- tests/mehp24/Mehp24SortTest.cpp:39-72, mehp24_utils.cpp:186-213"""
+    depth, cnt = ctypes.c_int(), ctypes.c_int()
+    buf = (ctypes.c_int32 * 256)()
+    _hchk(_H.sortfhe_mehp24_params(n, ctypes.byref(depth), buf, 256, ctypes.byref(cnt)))
+    return depth.value, list(buf[:cnt.value])
+
+
+def mehp24_sort_fg(eng, ct, n, sign_cfg=(3, 2, 2), dg_i=None, df_i=2):
+    """mehp24::sortFG, single ciphertext (mehp24_sort.cpp:251-282); dg_i defaults to (log2 n + 1) / 2 as in the fixture"""
+    if dg_i is None:
+        dg_i = (int(np.log2(n)) + 1) // 2
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_sort_fg(_vp(eng.h), _vp(ct.h), n, *sign_cfg, dg_i, df_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_matrix_op(eng, ct, n, op, mask_output=False):
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_matrix_op(_vp(eng.h), _vp(ct.h), n, MEHP24_OPS[op], int(mask_output), ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_indicator_adv(eng, ct, b, dg, df):
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_indicator_adv(_vp(eng.h), _vp(ct.h), float(b), dg, df, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+# ---------------------------------------------------------------- k-way network (reference src/k-way/)
+def kway_params(n):
+    """KWayAdapter<N>::getSizeParameters -> (multDepth, scalingModSize, firstModSize, rotations)"""
+    d, sc, fm, cnt = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    buf = (ctypes.c_int32 * 64)()
+    _hchk(_H.sortfhe_kway_params(n, ctypes.byref(d), ctypes.byref(sc), ctypes.byref(fm), buf, 64, ctypes.byref(cnt)))
+    return d.value, sc.value, fm.value, list(buf[:cnt.value])
+
+
+def kway_sort_type(k, M, stage):
+    """sortType + stage count + getRotateDistance -> (m, logDist, slope, stage_count, shift)"""
+    m, ld, sl, sc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rd = ctypes.c_int64()
+    _hchk(_H.sortfhe_kway_sort_type(k, M, stage, ctypes.byref(m), ctypes.byref(ld), ctypes.byref(sl), ctypes.byref(sc), ctypes.byref(rd)))
+    return m.value, ld.value, sl.value, sc.value, rd.value
+
+
+def kway_gen_indices(num_slots, k, M, m, log_dist, slope):
+    out = np.zeros((2, num_slots), dtype=np.int32)
+    _hchk(_H.sortfhe_kway_gen_indices(num_slots, k, M, m, log_dist, slope, out.ctypes.data_as(_i32p)))
+    return out
+
+
+def kway_sort(eng, ct, num_slots, k, M, sign_cfg=(3, 2, 2), mult_depth=100, first_stage=0, last_stage=-1):
+    """kwaySort::Sorter::sorter over stages [first_stage, last_stage) (Sorter.cpp:284-404)"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_kway_sort(_vp(eng.h), _vp(ct.h), num_slots, k, M, *sign_cfg, mult_depth, first_stage, last_stage, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)

@@ -2,6 +2,8 @@
 #include "../../include/sortfhe_host.h"
 #include <cstring>
 #include "sort_algo.h"
+#include "mehp24.h"
+#include "kway.h"
 
 namespace {
 thread_local std::string g_err;
@@ -156,6 +158,83 @@ int sortfhe_sinc_coefficients(int n, int doubled, double* coeffs, int cap, int* 
         }
         return 0;
     });
+    HOST_END
+}
+
+// ---- MEHP24 (reference src/mehp24/)
+int sortfhe_mehp24_params(int n, int* mult_depth, int32_t* rotations, int cap, int* count) {
+    HOST_BEGIN
+    std::vector<int32_t> r = mehp24::utils::getRotationIndices((size_t)n);
+    if ((int)r.size() > cap) throw std::runtime_error("mehp24_params: rotation buffer too small");
+    *mult_depth = mehp24::utils::fixtureDepth(n); *count = (int)r.size();
+    for (size_t i = 0; i < r.size(); i++) rotations[i] = r[i];
+    HOST_END
+}
+int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sn, int dg, int df, int dg_i, int df_i, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (n < 2 || (n & (n - 1))) throw std::runtime_error("mehp24 sortFG: vector length must be a power of two");
+    auto cc = borrow(ctx, n * n);                       // batch size N^2 (tests/mehp24/Mehp24SortTest.cpp:36-37)
+    SignConfig cfg = make_cfg(sn, dg, df);
+    std::unique_ptr<Comparison> comp(new Comparison());
+    *out = release(mehp24::sortFG(borrow(input), (size_t)n, SignFunc::CompositeSign, cfg, comp, (uint32_t)dg_i, (uint32_t)df_i, cc));
+    HOST_END
+}
+int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out) {
+    HOST_BEGIN
+    using namespace mehp24::utils;
+    auto cc = borrow(ctx, n * n); CT c = borrow(input), r;
+    switch (op) {
+        case 0: r = replicateRow(cc, c, n); break;
+        case 1: r = replicateColumn(cc, c, n); break;
+        case 2: r = sumRows(cc, c, n, mask_output != 0); break;
+        case 3: r = sumColumns(cc, c, n, mask_output != 0); break;
+        case 4: r = transposeRow(cc, c, n, mask_output != 0); break;
+        case 5: r = transposeColumn(cc, c, n, mask_output != 0); break;
+        default: throw std::runtime_error("mehp24_matrix_op: unknown op");
+    }
+    *out = release(r);
+    HOST_END
+}
+int sortfhe_mehp24_indicator_adv(ckks_ctx_t* ctx, const ckks_ct_t* x, double b, int dg, int df, ckks_ct_t** out) {
+    HOST_BEGIN
+    *out = release(mehp24::utils::indicatorAdv(borrow(ctx, 0), borrow(x), b, (size_t)dg, (size_t)df));
+    HOST_END
+}
+
+// ---- k-way network (reference src/k-way/, src/kway_adapter.h)
+int sortfhe_kway_params(int n, int* mult_depth, int* scaling_mod_size, int* first_mod_size, int32_t* rotations, int cap, int* count) {
+    HOST_BEGIN
+    CCParams<CryptoContextCKKSRNS> p; std::vector<int> r;
+    kwaySort::adapterParameters(n, p, r);
+    if ((int)r.size() > cap) throw std::runtime_error("kway_params: rotation buffer too small");
+    *mult_depth = (int)p.multDepth; *scaling_mod_size = (int)p.scalingModSize; *first_mod_size = (int)p.firstModSize;
+    *count = (int)r.size();
+    for (size_t i = 0; i < r.size(); i++) rotations[i] = r[i];
+    HOST_END
+}
+int sortfhe_kway_sort_type(int k, int M, int stage, int* m, int* log_dist, int* slope, int* stage_count, int64_t* rotate_distance) {
+    HOST_BEGIN
+    auto t = kwaySort::sortType(k, M, stage);
+    *m = std::get<0>(t); *log_dist = std::get<1>(t); *slope = std::get<2>(t);
+    *stage_count = M + M * (M - 1) / 2 * ((k + 1) / 2);
+    *rotate_distance = kwaySort::getRotateDistance(k, *log_dist, *slope);
+    HOST_END
+}
+int sortfhe_kway_gen_indices(int num_slots, int k, int M, int m, int log_dist, int slope, int32_t* out /*[2][num_slots]*/) {
+    HOST_BEGIN
+    auto r = kwaySort::genIndices(num_slots, k, M, m, log_dist, slope);
+    for (int h = 0; h < 2; h++) for (int i = 0; i < num_slots; i++) out[(size_t)h * num_slots + i] = r[h][i];
+    HOST_END
+}
+int sortfhe_kway_sort(ckks_ctx_t* ctx, const ckks_ct_t* input, int num_slots, int k, int M, int sn, int dg, int df, int mult_depth,
+                      int first_stage, int last_stage, ckks_ct_t** out) {
+    HOST_BEGIN
+    auto cc = borrow(ctx, num_slots);
+    kwaySort::Sorter s(cc, nullptr, num_slots, k, M);
+    SignConfig cfg(CompositeSignConfig(sn, dg, df), mult_depth);
+    CT work = borrow(input)->Clone(), res;           // KWayAdapter::sort works on a copy (kway_adapter.h:66-72)
+    s.sorter(work, res, cfg, first_stage, last_stage);
+    *out = release(res);
     HOST_END
 }
 }  // extern "C"

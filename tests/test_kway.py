@@ -1,0 +1,102 @@
+"""k-way sorting network of HKC+21 (reference src/k-way/, tests/k-way/*Test.cpp, tests/KWaySortTest.cpp): index logic
+and plaintext model on CPU; compare-swap stages on the GPU against the plaintext model (no bootstrapping: a network
+runs as far as the multiplicative depth allows)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from oracle import kway_plain as kp
+
+sf = importlib.import_module("sorting-fhe_b200")
+
+
+def next_pow2(n):
+    b = 1
+    while b < n:
+        b *= 2
+    return b
+
+
+@pytest.mark.parametrize("k,M", [(2, 3), (2, 7), (3, 3)])
+def test_index_logic_matches_plain_model(k, M):
+    """the product's sortType / getRotateDistance / genIndices (host/kway.h) == the oracle restatement of Masking.cpp"""
+    stages = sf.kway_sort_type(k, M, 0)[3]
+    assert stages == M + M * (M - 1) // 2 * ((k + 1) // 2)      # Sorter.cpp:298 (k=2, M=7 -> 28 stages)
+    for st in range(stages):
+        m, ld, sl, _, shift = sf.kway_sort_type(k, M, st)
+        assert (m, ld, sl) == kp.sort_type(k, M, st) and shift == kp.get_rotate_distance(k, ld, sl)
+        assert np.array_equal(sf.kway_gen_indices(k ** M, k, M, m, ld, sl), kp.gen_indices(k ** M, k, M, m, ld, sl))
+
+
+def test_adapter_parameters():
+    """KWayAdapter<N>::getSizeParameters (kway_adapter.h:41-64)"""
+    depth, scale, first, rots = sf.kway_params(128)
+    assert (depth, scale, first) == (40, 59, 60)
+    assert rots == [s * (1 << i) for i in range(7) for s in (1, -1)]
+
+
+@pytest.mark.parametrize("k,M", [(2, 1), (2, 4), (2, 7), (3, 2), (3, 3)])
+def test_plain_network_sorts(k, M):
+    """the network with an exact comparator sorts (what tests/k-way/SorterTest.cpp:313-381 checks on 8 / 3 / 5 elements)"""
+    n = k ** M
+    rng = np.random.default_rng(k * 10 + M)
+    for _ in range(4):
+        v = rng.permutation(n) / n + 0.5 / n
+        y = kp.network_plain(np.concatenate([v, np.zeros(next_pow2(n) - n)]), k, M)
+        assert np.allclose(y[:n], np.sort(v))
+
+
+def test_stage_levels_dry_run():
+    """one k=2 stage at the adapter's card (depth 40, scale 59): mask (1) + Sign(3,2,2) compare (13) + fcnL (1) +
+    output mask (1) = 16 levels; the third stage would need the bootstrap the reference performs there"""
+    n, k, M = 128, 2, 7
+    depth, scale, first, rots = sf.kway_params(n)
+    eng = sf.Engine(17, depth, scale, first, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    ct = eng.encrypt(eng.encode(np.arange(n) / n, slots=n))
+    s1 = sf.kway_sort(eng, ct, n, k, M, (3, 2, 2), depth, 0, 1)
+    assert s1.level == 16
+    s2 = sf.kway_sort(eng, s1, n, k, M, (3, 2, 2), depth, 1, 2)
+    assert s2.level == 32
+    with pytest.raises(sf.CkksError, match="EvalBootstrap"):
+        sf.kway_sort(eng, s2, n, k, M, (3, 2, 2), depth, 2, 3)
+    eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k,M", [(2, 2), (3, 1)])
+def test_small_network_sorts_on_gpu(k, M):
+    """whole network on k^M elements with enough depth to need no bootstrap (ring 2^11, 50-bit scaling); decrypted
+    output = sorted input within the reference's 0.01 gate (tests/k-way/KWaySort2Test.cpp:214)"""
+    n = k ** M
+    B = next_pow2(n)
+    stages = sf.kway_sort_type(k, M, 0)[3]
+    depth = 20 * stages + 4
+    rots = [s * (1 << i) for i in range(max(1, int(np.log2(B)))) for s in (1, -1)]
+    eng = sf.Engine(11, depth, 50, 60, seed=5)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    v = np.random.default_rng(7).permutation(n) / n + 0.5 / n
+    ct = eng.encrypt(eng.encode(np.concatenate([v, np.zeros(B - n)]), slots=B))
+    out = sf.kway_sort(eng, ct, n, k, M, (3, 3, 2), depth)
+    got = eng.decrypt(out, B)[:n]
+    assert np.max(np.abs(got - np.sort(v))) < 0.01, got
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_n128_compare_swap_stages_ring17():
+    """BASELINE config 4 shape: k=2, M=7, N=128 at the adapter's card (ring 2^17, depth 40, first 60 / scaling 59).
+    The first two compare-swap stages (all that fit before the reference's first bootstrap) equal the plaintext
+    network with an exact comparator within 0.01."""
+    n, k, M = 128, 2, 7
+    depth, scale, first, rots = sf.kway_params(n)
+    eng = sf.Engine(17, depth, scale, first, seed=2)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    v = np.random.default_rng(3).permutation(n) / n
+    out = sf.kway_sort(eng, eng.encrypt(eng.encode(v, slots=n)), n, k, M, (3, 3, 2), depth, 0, 2)
+    want = kp.network_plain(v, k, M, last_stage=2)
+    got = eng.decrypt(out, n)
+    assert out.level <= depth
+    assert np.max(np.abs(got - want)) < 0.01
+    eng.close()
