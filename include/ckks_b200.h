@@ -42,6 +42,9 @@ int ckks_ctx_sync(ckks_ctx_t* ctx);
 /* what: 0 ring dim (GetRingDimension, sort_algo.h:80), 1 #Q limbs, 2 #P limbs, 3 digit size alpha, 4 #digits,
  * 5 cyclotomic order (rotation.h:267), 6 kernel launches so far, 7 device bytes of keys */
 int ckks_ctx_info(ckks_ctx_t* ctx, int what, int64_t* out);
+/* the n-th Encrypt of a context draws its randomness from sampler stream n; resetting the counter replays it
+ * (reproducible tests: e.g. two sorter objects built after the same reset hold the same encryption of zeros) */
+int ckks_ctx_set_encryption_counter(ckks_ctx_t* ctx, uint64_t counter);
 int ckks_ctx_get_moduli(ckks_ctx_t* ctx, uint64_t* moduli, uint64_t* roots, int cap);   /* Q then P */
 int ckks_ctx_get_scaling_factors(ckks_ctx_t* ctx, double* sf_real, double* sf_big, int cap);
 
@@ -75,6 +78,13 @@ int ckks_ct_get_scaling_factor(const ckks_ct_t* ct, double* out);
 int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap_words);
 int ckks_ct_import(ckks_ctx_t* ctx, const uint64_t* host, int polys, int limbs, int level, int noise_scale_deg,
                    double scaling_factor, int slots, ckks_ct_t** out);
+
+/* multi-GPU exchange of partial ciphertext sums (replaces the `omp critical` + EvalAddInPlace accumulation of
+ * sort_algo.h:471-472, 740-741 when the comparison batches are sharded across GPUs): the caller all-reduces (SUM) the
+ * raw uint64 limbs in place through the device pointer (NCCL), then ckks_ct_mod_reduce folds every word back below
+ * its limb modulus.  Exact for up to 8 addends (residues < 2^61). */
+int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words);
+int ckks_ct_mod_reduce(ckks_ctx_t* ctx, ckks_ct_t* ct);
 
 /* EvalAdd / EvalSub over (ct,ct) (ct,pt) (pt,ct) -- ~130 call sites, e.g. sort_algo.h:358,454,708,720 */
 int ckks_eval_add(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out);

@@ -27,6 +27,21 @@ int sortfhe_construct_rank(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int s
 int sortfhe_rotation_index_check(ckks_ctx_t* ctx, const ckks_ct_t* rank, const ckks_ct_t* input, int n,
                                  const int32_t* rot_indices, int rot_count, ckks_ct_t** out);
 
+/* The shardable halves of DirectSort for shapes with num_batch > 1 (N >= 512 at ring 2^17; any N > ring/2N on small
+ * rings): the comparison batches of constructRank (src/sort_algo.h:438-492) and the index-check batches
+ * (:713-742) are independent.  *_partial sums the batches [b_lo, b_hi); exactly one shard passes seed = 1 (the
+ * accumulator's cached encryption of zeros, :433); the partial sums are combined limb-wise (ckks_ct_device_ptr +
+ * NCCL all-reduce + ckks_ct_mod_reduce) and handed to finish_* (rotate-and-sum, :494-504, :744-748).  With one shard
+ * [0, num_batch) the result equals sortfhe_construct_rank / sortfhe_rotation_index_check bit for bit. */
+int sortfhe_num_batches(int n, int ring_dim, int* num_batch);
+int sortfhe_construct_rank_partial(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sign_n, int dg, int df,
+                                   const int32_t* rot_indices, int rot_count, int b_lo, int b_hi, int seed, ckks_ct_t** out);
+int sortfhe_finish_rank(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n, const int32_t* rot_indices, int rot_count, ckks_ct_t** out);
+int sortfhe_index_check_partial(ckks_ctx_t* ctx, const ckks_ct_t* rank, const ckks_ct_t* input, int n,
+                                const int32_t* rot_indices, int rot_count, int b_lo, int b_hi, int seed, ckks_ct_t** out);
+int sortfhe_finish_index_check(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n, const int32_t* rot_indices, int rot_count,
+                               ckks_ct_t** out);
+
 /* Comparison::compare (src/comparison.cpp:4-22) and sign() (src/sign.cpp:635-651), CompositeSign only */
 int sortfhe_compare(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, int sign_n, int dg, int df, ckks_ct_t** out);
 int sortfhe_sign(ckks_ctx_t* ctx, const ckks_ct_t* x, int sign_n, int dg, int df, ckks_ct_t** out);

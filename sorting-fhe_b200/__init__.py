@@ -281,6 +281,18 @@ class Engine:
         o = ctypes.c_void_p()
         return self._out(_L.ckks_eval_rotate(_vp(self.h), _vp(a.h), int(r), ctypes.byref(o)), o)
 
+    def set_encryption_counter(self, counter):
+        _chk(_L.ckks_ctx_set_encryption_counter(_vp(self.h), ctypes.c_uint64(counter)))
+
+    def ct_device_ptr(self, ct):
+        """(device pointer, words) of a ciphertext's limbs -- for collectives on the data where it lies"""
+        p, w = ctypes.c_void_p(), ctypes.c_size_t()
+        _chk(_L.ckks_ct_device_ptr(_vp(ct.h), ctypes.byref(p), ctypes.byref(w)))
+        return p.value, w.value
+
+    def ct_mod_reduce(self, ct):
+        _chk(_L.ckks_ct_mod_reduce(_vp(self.h), _vp(ct.h)))
+
     def EvalFastRotationPrecompute(self, a):
         o = ctypes.c_void_p()
         return self._out(_L.ckks_fast_rotation_precompute(_vp(self.h), _vp(a.h), ctypes.byref(o)), o)
@@ -353,6 +365,11 @@ _H.sortfhe_indicator.argtypes = [_vp, _vp, _d, _i, _i, _i, _pp]
 _H.sortfhe_rotate.argtypes = [_vp, _vp, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_decompose.argtypes = [_i, _i, _i, _i, _i32p, _i, _i32p, _i, _ip]
 _H.sortfhe_sinc_coefficients.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_double), _i, _ip]
+_H.sortfhe_num_batches.argtypes = [_i, _i, _ip]
+_H.sortfhe_construct_rank_partial.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _i, _i, _i, _pp]
+_H.sortfhe_finish_rank.argtypes = [_vp, _vp, _i, _i32p, _i, _pp]
+_H.sortfhe_index_check_partial.argtypes = [_vp, _vp, _vp, _i, _i32p, _i, _i, _i, _i, _pp]
+_H.sortfhe_finish_index_check.argtypes = [_vp, _vp, _i, _i32p, _i, _pp]
 _H.sortfhe_kway_params.argtypes = [_i, _ip, _ip, _ip, _i32p, _i, _ip]
 _H.sortfhe_kway_sort_type.argtypes = [_i, _i, _i, _ip, _ip, _ip, _ip, ctypes.POINTER(ctypes.c_int64)]
 _H.sortfhe_kway_gen_indices.argtypes = [_i, _i, _i, _i, _i, _i, _i32p]
@@ -380,6 +397,13 @@ def direct_sort_params(n, ring_dim=1 << 17):
     return depth.value, list(buf[:cnt.value])
 
 
+def num_batches(n, ring_dim=1 << 17):
+    """num_batch of DirectSort<N> at a ring dimension (src/sort_algo.h:378-380)"""
+    v = ctypes.c_int()
+    _hchk(_H.sortfhe_num_batches(n, ring_dim, ctypes.byref(v)))
+    return v.value
+
+
 class DirectSort:
     """DirectSort<N> over an Engine (reference src/sort_algo.h:61-774)"""
 
@@ -400,6 +424,25 @@ class DirectSort:
 
     def rotation_index_check(self, rank, ct):
         return self._run(_H.sortfhe_rotation_index_check, _vp(rank.h), _vp(ct.h), self.n)
+
+    # shardable halves (multi-GPU, see shard.py): batches [lo, hi) of the two batch loops, and the folds after the all-reduce
+    def _run_tail(self, f, head, *tail):
+        a, c = _idx(self.rots)
+        o = ctypes.c_void_p()
+        _hchk(f(_vp(self.eng.h), *head, a, c, *tail, ctypes.byref(o)))
+        return Ciphertext(self.eng, o.value)
+
+    def construct_rank_partial(self, ct, sign_cfg, lo, hi, seed=True):
+        return self._run_tail(_H.sortfhe_construct_rank_partial, (_vp(ct.h), self.n, *sign_cfg), lo, hi, int(seed))
+
+    def finish_rank(self, partial):
+        return self._run_tail(_H.sortfhe_finish_rank, (_vp(partial.h), self.n))
+
+    def index_check_partial(self, rank, ct, lo, hi, seed=True):
+        return self._run_tail(_H.sortfhe_index_check_partial, (_vp(rank.h), _vp(ct.h), self.n), lo, hi, int(seed))
+
+    def finish_index_check(self, partial):
+        return self._run_tail(_H.sortfhe_finish_index_check, (_vp(partial.h), self.n))
 
 
 def compare(eng, a, b, sign_cfg=(4, 3, 3)):

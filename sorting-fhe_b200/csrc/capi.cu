@@ -234,6 +234,23 @@ int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
     } else d2h(p->ctx, host, p->d, w);
     API_END
 }
+int ckks_ctx_set_encryption_counter(ckks_ctx_t* x, uint64_t counter) { API_BEGIN C(x)->enc_counter = counter; API_END }
+int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
+    API_BEGIN
+    const Ct* p = G(ct);
+    if (p->lrep) throw std::runtime_error("ct_device_ptr: compact plaintexts have no full-length device form");
+    *dev_ptr = p->d; *words = (size_t)p->parts * p->nl * p->ctx->n;
+    API_END
+}
+int ckks_ct_mod_reduce(ckks_ctx_t* x, ckks_ct_t* ct) {
+    API_BEGIN
+    Context* c = C(x); Ct* p = const_cast<Ct*>(G(ct));
+    if (p->lrep) throw std::runtime_error("ct_mod_reduce: compact plaintext");
+    if (p->resc) { ct_free(p->resc); p->resc = nullptr; }            // the limbs are about to change: drop derived caches
+    if (p->modup) { dev_free(c, p->modup); p->modup = nullptr; }
+    launch_mod_reduce(c, p->d, p->parts * p->nl, p->nl);
+    API_END
+}
 int ckks_ct_import(ckks_ctx_t* x, const uint64_t* host, int polys, int limbs, int level, int deg, double sf, int slots, ckks_ct_t** out) {
     API_BEGIN
     Context* c = C(x);

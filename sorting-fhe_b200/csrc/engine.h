@@ -166,6 +166,7 @@ void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u
 void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep);   // compact -> full rows
 // out = sum_i in_i * s_i with per-limb integer scalars h_scalars[i * nl + l] (EvalLinearWSum in one pass)
 void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* h_scalars, int cnt, int parts, int nl);
+void launch_mod_reduce(Context* c, u64* d, int rows, int nl);
 void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int rows, int nl);
 void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep = 0);
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);

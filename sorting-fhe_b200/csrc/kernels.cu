@@ -160,6 +160,22 @@ void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* hs, int
     }
 }
 
+// d[row][x] <- d[row][x] mod q_limb for words < 2^64: folds a multi-GPU integer sum of residues (NCCL all-reduce of the raw
+// limbs of partial ciphertexts, at most 8 addends < 2^61) back to canonical residues
+__global__ void k_mod_reduce(u64* d, const ModInfo* mi, int n, int nl) {
+    X2_PROLOGUE;
+    const int row = blockIdx.y; const ModInfo m = mi[row % nl];
+    const size_t o = (size_t)row * n + x;
+    u64x2 v = ld2(d, o);
+    v.x -= __umul64hi(v.x, m.qrecip) * m.q; if (v.x >= m.q) v.x -= m.q;
+    v.y -= __umul64hi(v.y, m.qrecip) * m.q; if (v.y >= m.q) v.y -= m.q;
+    st2(d, o, v.x, v.y);
+}
+void launch_mod_reduce(Context* c, u64* d, int rows, int nl) {
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * c->n * rows);
+    k_mod_reduce<<<grid_for2(c, rows), 256, 0, c->stream>>>(d, c->d_mod, c->n, nl);
+}
+
 // out[row] = sum_i in_i[row]  (EvalAddMany)
 struct ManyArgs { int cnt; const u64* in[32]; };
 __global__ void k_add_many(u64* out, const ManyArgs A, const ModInfo* mi, int n, int nl) {

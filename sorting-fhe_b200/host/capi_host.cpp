@@ -161,6 +161,58 @@ int sortfhe_sinc_coefficients(int n, int doubled, double* coeffs, int cap, int* 
     HOST_END
 }
 
+// ---- shardable halves of DirectSort (multi-GPU: SURVEY 8e row 2)
+int sortfhe_num_batches(int n, int ring_dim, int* num_batch) {
+    HOST_BEGIN
+    const int P = std::min(n, ring_dim / 2 / n);
+    if (P < 1) throw std::runtime_error("num_batches: array does not fit the ring");
+    *num_batch = n / P;
+    HOST_END
+}
+int sortfhe_construct_rank_partial(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sn, int dg, int df, const int32_t* idx, int cnt,
+                                   int b_lo, int b_hi, int seed, ckks_ct_t** out) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        SignConfig cfg = make_cfg(sn, dg, df);
+        *out = release(s->constructRankPartial(borrow(input), SignFunc::CompositeSign, cfg, b_lo, b_hi, seed != 0));
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_finish_rank(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n, const int32_t* idx, int cnt, ckks_ct_t** out) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        *out = release(s->finishRank(borrow(partial)->Clone()));
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_index_check_partial(ckks_ctx_t* ctx, const ckks_ct_t* rank, const ckks_ct_t* input, int n, const int32_t* idx, int cnt,
+                                int b_lo, int b_hi, int seed, ckks_ct_t** out) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        *out = release(s->rotationIndexCheckPartial(borrow(rank), borrow(input), b_lo, b_hi, seed != 0));
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_finish_index_check(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n, const int32_t* idx, int cnt, ckks_ct_t** out) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        *out = release(s->finishIndexCheck(borrow(partial)->Clone()));
+        return 0;
+    });
+    HOST_END
+}
+
 // ---- MEHP24 (reference src/mehp24/)
 int sortfhe_mehp24_params(int n, int* mult_depth, int32_t* rotations, int cap, int* count) {
     HOST_BEGIN
@@ -229,7 +281,8 @@ int sortfhe_kway_gen_indices(int num_slots, int k, int M, int m, int log_dist, i
 int sortfhe_kway_sort(ckks_ctx_t* ctx, const ckks_ct_t* input, int num_slots, int k, int M, int sn, int dg, int df, int mult_depth,
                       int first_stage, int last_stage, ckks_ct_t** out) {
     HOST_BEGIN
-    auto cc = borrow(ctx, num_slots);
+    int batch = 1; while (batch < num_slots) batch <<= 1;   // SetBatchSize(next_power_of_two(N)), kway_adapter.h:44
+    auto cc = borrow(ctx, batch);
     kwaySort::Sorter s(cc, nullptr, num_slots, k, M);
     SignConfig cfg(CompositeSignConfig(sn, dg, df), mult_depth);
     CT work = borrow(input)->Clone(), res;           // KWayAdapter::sort works on a copy (kway_adapter.h:66-72)

@@ -139,23 +139,38 @@ template <int N> class DirectSort : public SortBase<N> {
 
     // constructRank (:368-506): rank_i = #{j : a_j < a_i}
     CT constructRank(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) {
-        const int num_partition = std::min(N, max_batch / N), num_batch = N / num_partition;
+        return finishRank(constructRankPartial(input_array, SignFunc, Cfg, 0, numBatches(), true));
+    }
+    int numBatches() const { return N / std::min(N, max_batch / N); }
+    // The comparison batches i in [b_lo, b_hi) of constructRank's loop (:438-492), summed.  The batches are independent
+    // (the reference runs them under OpenMP for N >= 512): this is the unit that shards across GPUs, the partial sums
+    // being combined by an all-reduce of the ciphertext limbs.  `seed` adds the cached encryption of zeros the
+    // reference starts its accumulator from (:433) -- exactly one shard must pass true.
+    CT constructRankPartial(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg, int b_lo, int b_hi, bool seed) {
+        const int num_partition = std::min(N, max_batch / N);
         const int num_slots = N * num_partition;
         const int np = std::min(directsort_detail::rankBabySteps(N), num_partition);
+        if (b_lo < 0 || b_hi > N / num_partition || b_lo >= b_hi) throw std::runtime_error("constructRankPartial: empty or invalid batch range");
         std::vector<CT> babySteps(np);
         for (int i = 0; i < np; i++) { babySteps[i] = rot.rotate(input_array, i); babySteps[i]->SetSlots(num_slots); }
-        CT rank = this->getZero()->Clone();
-        rank->SetSlots(num_slots);
-        for (int i = 0; i < num_batch; i++) {
+        CT rank;
+        if (seed) { rank = this->getZero()->Clone(); rank->SetSlots(num_slots); }
+        for (int i = b_lo; i < b_hi; i++) {
             CT shifted = vecRotsOpt(babySteps, num_partition, num_slots, np, i);
             CT dup = input_array->Clone();
             dup->SetSlots(num_slots);
-            m_cc->EvalAddInPlace(rank, comp.compare(m_cc, dup, shifted, SignFunc, Cfg));
+            CT c = comp.compare(m_cc, dup, shifted, SignFunc, Cfg);
+            if (rank) m_cc->EvalAddInPlace(rank, c); else rank = c;
         }
+        return rank;
+    }
+    // rotate-and-sum over the partitions, then remove the self comparison's 1/2 (:494-504)
+    CT finishRank(CT rank) {
+        const int num_partition = std::min(N, max_batch / N), num_slots = N * num_partition;
         for (int i = 1; i < std::log2(num_partition) + 1; i++)
             m_cc->EvalAddInPlace(rank, rot.rotate(rank, num_slots / (1 << i)));
         rank->SetSlots(N);
-        return m_cc->EvalSub(rank, 0.5);   // self comparison contributes 1/2
+        return m_cc->EvalSub(rank, 0.5);
     }
 
     // blindRotationOptN (:561-584)
@@ -176,14 +191,20 @@ template <int N> class DirectSort : public SortBase<N> {
 
     // rotationIndexCheckN (:658-750): out_j = sum_i a_i [rank_i = j] through the doubled-sinc indicator
     CT rotationIndexCheckN(const CT& ctx_Rank, const CT& input_array) {
-        CT output = this->getZero()->Clone();
-        const int num_partition = std::min(N, max_batch / N), num_batch = N / num_partition;
+        return finishIndexCheck(rotationIndexCheckPartial(ctx_Rank, input_array, 0, numBatches(), true));
+    }
+    // batches b in [b_lo, b_hi) of the index-check loop (:713-742), summed; same sharding contract as constructRankPartial
+    CT rotationIndexCheckPartial(const CT& ctx_Rank, const CT& input_array, int b_lo, int b_hi, bool seed) {
+        const int num_partition = std::min(N, max_batch / N);
         const int num_slots = num_partition * N, np = directsort_detail::indexBabySteps(N);
+        if (b_lo < 0 || b_hi > N / num_partition || b_lo >= b_hi) throw std::runtime_error("rotationIndexCheckPartial: empty or invalid batch range");
+        CT output;
+        if (seed) output = this->getZero()->Clone();
         Plaintext index_vector = m_cc->MakeCKKSPackedPlaintext(generateIndexVector(), 1, (uint32_t)ctx_Rank->GetLevel(), nullptr, N);
         CT index_minus_rank = m_cc->EvalSub(index_vector, ctx_Rank);
         index_minus_rank->SetSlots(num_slots);
         input_array->SetSlots(num_slots);   // mutates the caller's ciphertext metadata, as the reference does (:711)
-        for (int b = 0; b < num_batch; b++) {
+        for (int b = b_lo; b < b_hi; b++) {
             Plaintext chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(num_slots, b * num_partition), 1,
                                                           (uint32_t)index_minus_rank->GetLevel(), nullptr, num_slots);
             CT rotIndex = m_cc->EvalSub(index_minus_rank, chk);
@@ -192,8 +213,13 @@ template <int N> class DirectSort : public SortBase<N> {
             CT masked_input = m_cc->EvalMult(rotIndex, input_array);
             std::vector<CT> masked_inputs(np);
             for (int i = 0; i < np; i++) masked_inputs[i] = rot.rotate(masked_input, i);
-            m_cc->EvalAddInPlace(output, blindRotationOptN(masked_inputs, num_slots, np, b, num_partition));
+            CT r = blindRotationOptN(masked_inputs, num_slots, np, b, num_partition);
+            if (output) m_cc->EvalAddInPlace(output, r); else output = r;
         }
+        return output;
+    }
+    CT finishIndexCheck(CT output) {   // (:744-748)
+        const int num_partition = std::min(N, max_batch / N), num_slots = num_partition * N;
         for (int i = 1; i < std::log2(num_partition) + 1; i++)
             m_cc->EvalAddInPlace(output, rot.rotate(output, num_slots / (1 << i)));
         output->SetSlots(N);

@@ -1,0 +1,91 @@
+"""Multi-GPU partitioning of the sorting path (one process per GPU, torch.distributed).
+
+Two shapes shard naturally:
+  * a batch of independent sorts        -> `shard_range` over the array index, evaluation keys replicated per GPU,
+                                           no data-path collective;
+  * DirectSort with num_batch > 1       -> the comparison batches of constructRank (reference src/sort_algo.h:438-492)
+                                           and the index-check batches (:713-742) are independent; each rank sums its
+                                           batches and the partial ciphertexts are combined by ONE all-reduce each,
+                                           replacing the `omp critical` + EvalAddInPlace of :471-472 and :740-741.
+The all-reduce is a plain integer SUM of the raw uint64 limbs (NCCL over NVLink on GPUs, gloo in the CPU tests)
+followed by one `mod q_limb` pass: residues are < 2^61, so up to 8 addends stay below 2^63, and modular addition is
+associative -- the result is bit-identical to the single-GPU sum.  A single DirectSort with num_batch == 1 (N <= 256 at
+ring 2^17) is one dependent chain and does not shard: replicas only.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(num_items, rank, world):
+    """contiguous, balanced [lo, hi) share of `num_items` independent units for `rank` of `world`"""
+    base, extra = divmod(num_items, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def allreduce_limbs(limbs, moduli, group=None):
+    """in-place SUM all-reduce of residue rows followed by `mod q_row`.  limbs: int64 tensor [rows, n] holding residues
+    in [0, q_row); moduli: one modulus per row.  Device-agnostic (this is the form the gloo tests exercise); on CUDA
+    the engine's own kernel does the reduction step, see allreduce_ciphertext."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world > 8:
+        raise ValueError("allreduce_limbs: more than 8 addends could overflow 63 bits")
+    if world > 1:
+        dist.all_reduce(limbs, op=dist.ReduceOp.SUM, group=group)
+    q = torch.as_tensor(np.asarray(moduli, dtype=np.int64), device=limbs.device).view(-1, 1)
+    limbs.remainder_(q)
+    return limbs
+
+
+class _DevView:
+    """zero-copy view of a ciphertext's device limbs for torch (CUDA array interface)"""
+
+    def __init__(self, ptr, words):
+        self.__cuda_array_interface__ = {"shape": (words,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+
+
+def allreduce_ciphertext(eng, ct, group=None):
+    """sum a partial ciphertext over all ranks, in place: NCCL all-reduce on the limbs where they lie, then the
+    engine's mod-reduce kernel (ckks_ct_device_ptr / ckks_ct_mod_reduce of include/ckks_b200.h)"""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return ct
+    ptr, words = eng.ct_device_ptr(ct)
+    eng.sync()                                            # the limbs are produced on the engine's stream
+    t = torch.as_tensor(_DevView(ptr, words), device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    torch.cuda.current_stream().synchronize()
+    eng.ct_mod_reduce(ct)
+    return ct
+
+
+def direct_sort_sharded(eng, n, rots, ct, sign_cfg, group=None):
+    """DirectSort<N>::sort with the comparison / index-check batches split over the ranks of `group` (every rank holds
+    the same input ciphertext and keys and returns the same sorted ciphertext).  Falls back to the plain sort when
+    the shape has a single batch."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    from . import DirectSort, num_batches
+    nb = num_batches(n, eng.n)
+    sorter = DirectSort(eng, n, rots)
+    if world == 1 or nb == 1:
+        return sorter.sort(ct, sign_cfg)
+    if nb % world:
+        raise ValueError("direct_sort_sharded: %d batches do not split evenly over %d ranks" % (nb, world))
+    lo, hi = shard_range(nb, rank, world)
+    part = sorter.construct_rank_partial(ct, sign_cfg, lo, hi, seed=(rank == 0))
+    rank_ct = sorter.finish_rank(allreduce_ciphertext(eng, part, group))
+    part = sorter.index_check_partial(rank_ct, ct, lo, hi, seed=(rank == 0))
+    return sorter.finish_index_check(allreduce_ciphertext(eng, part, group))
+
+
+def sort_batch_sharded(eng, n, rots, cts, sign_cfg, group=None):
+    """a batch of independent sorts: rank r sorts cts[lo:hi] of its own; no collective on the data path.
+    Returns (lo, [sorted ciphertexts])."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    from . import DirectSort
+    lo, hi = shard_range(len(cts), rank, world)
+    sorter = DirectSort(eng, n, rots)
+    return lo, [sorter.sort(c, sign_cfg) for c in cts[lo:hi]]
