@@ -22,6 +22,7 @@ import time
 
 import numpy as np
 
+os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p.log")   # rank 0 prints ONE JSON line: NCCL's banner goes to a file
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -42,43 +43,72 @@ def parse():
     return ap.parse_args()
 
 
+_SAMPLER_SRC = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[1]))
+print("max", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
+while True:
+    try:
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+    except Exception:
+        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+    print("s", time.time(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), r, flush=True)
+    time.sleep(0.5)
+"""
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons of one GPU, sampled through NVML twice a second by a small child process that is
+    started before the warm-up; stop() keeps the samples that fall inside the timed region.  (A looping
+    `nvidia-smi -lms` child per rank stalled the kernel launches of the other ranks on a multi-GPU box -- the 2-GPU
+    step took 2.8x longer with it -- and NVML queries themselves stall the driver for a few ms each: at 10 Hz the N=1 step was 20-50 % slower, so the
+    rate is 2 Hz.)"""
+    BAD = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.t0 = index, None, [], None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
         except OSError:
             self.proc = None
 
+    def mark(self):                 # the timed region starts here
+        self.t0 = time.time()
+
     def stop(self):
+        t1 = time.time()
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml sampler unavailable"]}
+        time.sleep(0.15)
         self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        sm, mx, reasons = [], None, set()
+        for ln in list(self.lines):
+            f = ln.split()
+            if f and f[0] == "max":
+                mx = float(f[1])
+            elif f and f[0] == "s" and len(f) == 4 and (self.t0 or 0) <= float(f[1]) <= t1 + 0.15:
+                sm.append(float(f[2]))
+                for name, bit in self.BAD:
+                    if int(f[3]) & bit:
+                        reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": mx, "reasons": ["no NVML samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload_name(n, log_n, depth, cfg, nrots):
+    return ("DirectSort N=%d (Optimized Rank Sort), ring 2^%d, multDepth %d, scaling 40 bit, Sign%s, %d rotation keys"
+            % (n, log_n, depth, str(cfg), nrots))
+
+
+def sf_rots(n, log_n):
+    return importlib.import_module("sorting-fhe_b200").direct_sort_params(n, 1 << log_n)[1]
 
 
 def measured_peak():
@@ -185,8 +215,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": "DirectSort N=%d, ring 2^%d, depth %d, Sign%s" % (args.n, args.log_n, depth, str(cfg)),
-                   "arm": "CPU oracle port (OpenFHE 1.1.4 unavailable offline)"},
+        "config": {"workload": workload_name(args.n, args.log_n, depth, cfg, len(sf_rots(args.n, args.log_n))),
+                   "arm": "CPU oracle port (OpenFHE 1.1.4 unavailable offline), %d host threads" % cb["cores"]},
         "cpu_baseline": cb, "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -224,15 +254,17 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0 and os.environ.get("BENCH_NO_CLOCK_SAMPLER") != "1":
+        sampler.start()
     for i in range(W):                                   # warm-up (also fills the stream-ordered memory pool)
         out = sorter.sort(cts[i % len(cts)], cfg)
     eng.sync()
 
     # ---- timed region 1: inputs resident in HBM
     eng.stats(reset=True)
-    eng.profile_enable(["ntt"])
-    eng.profile()
-    sampler = ClockSampler(local); sampler.start()
+    eng.profile_enable([])
+    sampler.mark()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
@@ -243,12 +275,21 @@ def run_b200(args):
     e1.record(stream)
     barrier()
     t_dev = e0.elapsed_time(e1) / 1e3
-    clocks = sampler.stop()
-    prof_ntt = eng.profile()["ntt"]
-    eng.profile_enable([])
+    clocks = sampler.stop() if rank == 0 else None
     st = eng.stats(reset=True)
     launches = st["kernel_launches"]
     trace = [(nm, nl, cnt / K) for nm, nl, cnt in st["ops"]]          # ops of ONE sort
+
+    # ---- the same K steps again with CUDA events around every NTT launch (the roofline's kernel time; the events
+    # cost ~6 % of a step, so they stay out of region 1)
+    eng.profile_enable(["ntt"])
+    eng.profile()
+    for i in range(K):
+        cts[i].slots = n
+        sorter.sort(cts[i], cfg)
+    prof_ntt = eng.profile()["ntt"]
+    eng.profile_enable([])
+    eng.stats(reset=True)
 
     # ---- correctness of what was timed
     errs = [float(np.max(np.abs(eng.decrypt(o, n) - np.sort(a)))) for o, a in zip(outs, arrays)]
@@ -279,6 +320,11 @@ def run_b200(args):
     t_dev, t_e2e = float(tt[0]), float(tt[1])
     if rank == 0:
         peak, peak_src = measured_peak()
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_ntt_traffic.json")) as f:
+                traffic_ratio = float(json.load(f)["traffic_over_algorithmic"])
+        except Exception:
+            traffic_ratio = None
         dom = max(breakdown, key=lambda k: breakdown[k]["ms"])
         ach = prof_ntt["bytes"] / max(prof_ntt["ms"], 1e-9) / 1e6     # GB/s over the timed region's NTT launches
         total_ms = sum(v["ms"] for v in breakdown.values())
@@ -286,8 +332,7 @@ def run_b200(args):
             "metric": METRIC, "value": t_dev / (K * world), "unit": "s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": t_dev / K * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "DirectSort N=%d (Optimized Rank Sort), ring 2^%d, multDepth %d, scaling 40 bit, "
-                                   "Sign%s, %d rotation keys" % (n, log_n, depth, str(cfg), len(rots)),
+            "config": {"workload": workload_name(n, log_n, depth, cfg, len(rots)),
                        "parallelism": "replicas: one independent sort per GPU per step" if world > 1 else "single GPU",
                        "l2": "working set (%.1f GB of evaluation keys streamed per sort) exceeds the 126 MB L2" % (key_bytes / 1e9),
                        "max_abs_err": max(errs), "size_q": eng.size_q, "size_p": eng.size_p, "dnum": eng.num_part_q},
@@ -296,10 +341,17 @@ def run_b200(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "ntt_kernel (all NTT/INTT launches of the timed region)",
-                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": traffic_ratio * prof_ntt["bytes"] / max(prof_ntt["launches"], 1) if traffic_ratio else None,
+                         "traffic_note": "DRAM bytes per average launch = algorithmic bytes per launch x %.2f, the dram read+write "
+                                         "over algorithmic ratio of one ncu --set full capture of the 32-limb transform "
+                                         "(profiles/r01_ntt_traffic.json): pass B also streams the per-tile twiddles" % (traffic_ratio or 0),
+                         "algorithmic_bytes_per_launch": prof_ntt["bytes"] / max(prof_ntt["launches"], 1),
                          "peak_source": peak_src, "launches": prof_ntt["launches"],
                          "avg_launch_us": prof_ntt["ms"] * 1e3 / max(prof_ntt["launches"], 1),
-                         "share_of_step": breakdown["ntt"]["ms"] / max(total_ms, 1e-9), "dominant_class": dom},
+                         "share_of_step": breakdown["ntt"]["ms"] / max(total_ms, 1e-9), "dominant_class": dom,
+                         "second_bound": "FP64 / integer issue: 40-bit limbs run 8 DFMA-pipe ops per butterfly, 60-bit limbs "
+                                         "~40 IMAD/IADD3 ops (DESIGN.md section 3)"},
             "breakdown_ms": {k: round(v["ms"], 3) for k, v in breakdown.items()},
             "breakdown_GBs": {k: round(v["bytes"] / v["ms"] / 1e6, 1) for k, v in breakdown.items() if v["ms"] > 0},
             "breakdown_launches": {k: v["launches"] for k, v in breakdown.items()},

@@ -70,7 +70,12 @@ __global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, i
         double2 z = v[xx / gap];
         double val = rint(ldexp(x < nh ? z.x : z.y, -log_approx));
         long long iv = (long long)val;
-        if (iv >= 0) r = (u64)iv % q; else { u64 mm = ((u64)(-iv)) % q; r = mm ? q - mm : 0; }
+        {   // |iv| mod q without a 64-bit division: x - mulhi(x, floor(2^64 / q)) q lies in [0, 2q)
+            u64 a = iv >= 0 ? (u64)iv : (u64)(-iv);
+            a -= __umul64hi(a, m.qrecip) * q;
+            if (a >= q) a -= q;
+            r = iv >= 0 ? a : (a ? q - a : 0);
+        }
         if (log_approx) r = barrett_mul(r, (1ull << log_approx) % q, m);
     }
     out[(size_t)l * n + x] = r;
@@ -91,10 +96,11 @@ k_fft_inv_tail(double2* __restrict__ out, const double2* __restrict__ v, const d
     }
     __syncthreads();
     for (int len = bsz; len >= 2; len >>= 1) {
-        const int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
+        // len, lenq = 4 len and M are powers of two: shifts and masks instead of integer division
+        const int lenh = len >> 1, lenq = len << 2, lg = 31 - __clz(lenh), gshift = (31 - __clz(M)) - (31 - __clz(lenq));
         for (int t = threadIdx.x; t < bsz / 2; t += blockDim.x) {
-            const int i = (t / lenh) * len, j = t % lenh;
-            const int idx = (lenq - (int)(rot[j] % (uint32_t)lenq)) * gap;
+            const int i = (t >> lg) << (lg + 1), j = t & (lenh - 1);
+            const int idx = (lenq - (int)(rot[j] & (uint32_t)(lenq - 1))) << gshift;
             const double2 a = blk[i + j], b = blk[i + j + lenh], w = ksi[idx];
             const double ur = __dadd_rn(a.x, b.x), ui = __dadd_rn(a.y, b.y), vr = __dsub_rn(a.x, b.x), vi = __dsub_rn(a.y, b.y);
             const double p1 = __dmul_rn(vr, w.x), p2 = __dmul_rn(vi, w.y), p3 = __dmul_rn(vr, w.y), p4 = __dmul_rn(vi, w.x);
@@ -119,9 +125,9 @@ __global__ void k_fft_inv_stage_big(double2* v, const double* __restrict__ real_
                                     const double2* ksi, const uint32_t* rot, int M) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= size / 2) return;
-    int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
-    int i = (t / lenh) * len, j = t % lenh;
-    int idx = (lenq - (int)(rot[j] % (uint32_t)lenq)) * gap;
+    const int lenh = len >> 1, lenq = len << 2, lg = 31 - __clz(lenh), gshift = (31 - __clz(M)) - (31 - __clz(lenq));
+    const int i = (t >> lg) << (lg + 1), j = t & (lenh - 1);
+    const int idx = (lenq - (int)(rot[j] & (uint32_t)(lenq - 1))) << gshift;
     double2 a, b;
     if (from_real) {
         a = make_double2(i + j < nvals ? real_in[i + j] : 0.0, 0.0);
