@@ -35,7 +35,9 @@ static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_err
 
 void context_release(Context* c) {
     if (!c->dry) {
+        if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
         cudaStreamSynchronize(c->stream);
+        for (auto e : c->ev_pool) cudaEventDestroy(e);
         cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs); cudaFree(c->d_twd); cudaFree(c->d_itwd);
         for (auto& kv : c->ninv_pairs_rep) cudaFree(kv.second);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
@@ -53,6 +55,7 @@ void context_release(Context* c) {
         for (auto& kv : c->rot) dev_free(c, kv.second.d);
         cudaStreamSynchronize(c->stream);
         if (c->own_stream) cudaStreamDestroy(c->stream);
+        if (c->enc_stream) cudaStreamDestroy(c->enc_stream);
         cudaGetLastError();
     }
     delete reinterpret_cast<ckks_ctx*>(c);   // Context is the first (only) member of ckks_ctx
@@ -95,7 +98,10 @@ int ckks_ctx_set_stream(ckks_ctx_t* x, void* s) {
 int ckks_ctx_sync(ckks_ctx_t* x) {
     API_BEGIN
     Context* c = C(x);
-    if (!c->dry) { cudaError_t e = cudaStreamSynchronize(c->stream); if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); check_cuda("sync"); }
+    if (!c->dry) {
+        if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
+        cudaError_t e = cudaStreamSynchronize(c->stream); if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); check_cuda("sync");
+    }
     API_END
 }
 int ckks_ctx_info(ckks_ctx_t* x, int what, int64_t* out) {
@@ -227,6 +233,7 @@ int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
     API_BEGIN
     const Ct* p = G(ct); size_t w = (size_t)p->parts * p->nl * p->ctx->n;
     if (cap < w) throw std::runtime_error("ct_export: buffer too small");
+    ct_wait(p);
     if (p->lrep) {   // compact plaintext: export the full-length limbs
         Ct* f = ct_full(p);
         try { d2h(p->ctx, host, f->d, w); } catch (...) { ct_free(f); throw; }
@@ -239,6 +246,7 @@ int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
     API_BEGIN
     const Ct* p = G(ct);
     if (p->lrep) throw std::runtime_error("ct_device_ptr: compact plaintexts have no full-length device form");
+    ct_wait(p);
     *dev_ptr = p->d; *words = (size_t)p->parts * p->nl * p->ctx->n;
     API_END
 }

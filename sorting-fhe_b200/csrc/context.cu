@@ -156,6 +156,10 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
     }
     if (!c->dry) {
         if (!c->stream) { cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking); c->own_stream = true; }
+        if (!getenv("CKKS_B200_NO_ENCODE_STREAM")) {
+            int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);
+            cudaStreamCreateWithPriority(&c->enc_stream, cudaStreamNonBlocking, hi);
+        }
         cudaMemPool_t pool; int dev = 0; cudaGetDevice(&dev);
         if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) { uint64_t thr = UINT64_MAX; cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr); }
     }
@@ -260,6 +264,7 @@ ProfScope::ProfScope(Context* c_, int cls, double alg_bytes, int nlaunch) : c(c_
 ProfScope::~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof.pending[idx].e1, c->stream); }
 void prof_collect(Context* c) {
     if (c->dry) return;
+    if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
     cudaStreamSynchronize(c->stream);
     for (auto& r : c->prof.pending) {
         float ms = 0; cudaEventElapsedTime(&ms, r.e0, r.e1);

@@ -103,6 +103,10 @@ struct Context {
     uint64_t enc_ring_pos = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    // plaintext encodes (small FFT + compact NTT: a few CTAs) run on their own high-priority stream so that they overlap
+    // the main stream's full-width kernels; a consumer waits on the plaintext's `ready` event (evaluator.cu ct_wait)
+    cudaStream_t enc_stream = nullptr;
+    std::vector<cudaEvent_t> ev_pool;
     Stats stats;
     Prof prof;
     std::string last_error;
@@ -121,6 +125,7 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     double sf;
     int slots;
     mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
+    mutable cudaEvent_t ready = nullptr;   // recorded on the encode stream; the first consumer makes the main stream wait on it
     mutable u64* modup = nullptr; // cached ModUp of c1 (owned): shared by all rotations of this ciphertext (hoisting)
     // Plaintexts only: log2 of the replication factor.  A plaintext with s slots is G(X^gap), gap = n / (2 s), so its
     // EVALUATION form is the (n / gap)-point transform of G with every value repeated gap times in a row

@@ -25,7 +25,15 @@ Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slo
     c->live_cts++;
     return t;
 }
+void ct_wait(const Ct* a) {
+    if (!a->ready) return;
+    Context* c = a->ctx;
+    cudaStreamWaitEvent(c->stream, a->ready, 0);
+    c->ev_pool.push_back(a->ready);          // everything queued on the main stream from here on is ordered after it
+    a->ready = nullptr;
+}
 Ct* ct_clone(const Ct* a) {
+    ct_wait(a);
     Ct* t = ct_new(a->ctx, a->parts, a->nl, a->level, a->deg, a->sf, a->slots, a->lrep);
     launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl, a->lrep));
     return t;
@@ -37,6 +45,7 @@ static void drop_twin(const Ct* a) {
 void ct_free(Ct* a) {
     if (!a) return;
     Context* c = a->ctx;
+    ct_wait(a);                               // the buffer is released on the main stream
     drop_twin(a);
     dev_free(c, a->d);
     delete a;
@@ -78,7 +87,7 @@ static const Ct* rescaled_twin(const Ct* a) {
 struct Opnd {
     const Ct* v;        // current value
     Ct* own = nullptr;  // == v when the value is a private temporary
-    explicit Opnd(const Ct* src) : v(src) {}
+    explicit Opnd(const Ct* src) : v(src) { ct_wait(src); }
     ~Opnd() { if (own) ct_free(own); }
     Opnd(const Opnd&) = delete;
     void set_own(Ct* t) { if (own) ct_free(own); own = t; v = t; }
@@ -115,6 +124,7 @@ static void op_set_sf(Opnd& o, double sf) {
 // full-length copy of a compact plaintext (ops without a compact form use this)
 static Ct* expand_new(const Ct* a) {
     Context* c = a->ctx;
+    ct_wait(a);
     Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
     launch_expand_rep(c, r->d, a->d, a->parts * a->nl, a->lrep);
     return r;
@@ -497,9 +507,26 @@ Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level
     // compact form: the plaintext is G(X^gap), gap = n / (2 slots); keep at least 2^8 words per limb
     int lrep = 0;
     while ((2 * slots << lrep) < c->n && c->log_n - lrep > 8) lrep++;
-    Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
     count(c, "encode", nl);
-    launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
+    if (c->dry || !c->enc_stream) {
+        Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
+        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
+        return pt;
+    }
+    // the whole encode (allocation, FFT, expansion, NTT) is queued on the encode stream
+    cudaStream_t main = c->stream;
+    c->stream = c->enc_stream;
+    Ct* pt = nullptr;
+    try {
+        pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
+        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
+        cudaEvent_t ev;
+        if (!c->ev_pool.empty()) { ev = c->ev_pool.back(); c->ev_pool.pop_back(); }
+        else cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        cudaEventRecord(ev, c->enc_stream);
+        pt->ready = ev;
+    } catch (...) { c->stream = main; throw; }
+    c->stream = main;
     return pt;
 }
 
