@@ -24,7 +24,7 @@
 #include <utility>
 #include <vector>
 
-static constexpr int TB_MAX = 11;
+static constexpr int TB_MAX = 10;
 typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
 
 __device__ __forceinline__ int padi(int e) { return e + (e >> 3); }
