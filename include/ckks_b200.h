@@ -110,6 +110,11 @@ int ckks_fast_rotation(ckks_ctx_t* ctx, const ckks_ct_t* ct, int32_t index, cons
 /* EvalChebyshevSeriesPS(ct, coeffs, a, b) -- sort_algo.h:727-728, sign.cpp:76 */
 int ckks_eval_chebyshev_series_ps(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, double a, double b,
                                   ckks_ct_t** out);
+/* EvalChebyshevSeries(ct, coeffs, a, b): the linear evaluator below degree 5, Paterson-Stockmeyer from there on; the
+ * series step of EvalChebyshevFunction (mehp24_utils.cpp:109-163, sign.cpp:616-633 -- the coefficients of the
+ * function are computed on the host, see host/openfhe_shim.h EvalChebyshevCoefficients) */
+int ckks_eval_chebyshev_series(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, double a, double b,
+                               ckks_ct_t** out);
 /* EvalPolyLinear(ct, coeffs) -- mehp24_utils.cpp:256-259 */
 int ckks_eval_poly_linear(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, ckks_ct_t** out);
 

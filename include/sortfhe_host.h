@@ -34,6 +34,17 @@ int sortfhe_rotation_index_check(ckks_ctx_t* ctx, const ckks_ct_t* rank, const c
  * NCCL all-reduce + ckks_ct_mod_reduce) and handed to finish_* (rotate-and-sum, :494-504, :744-748).  With one shard
  * [0, num_batch) the result equals sortfhe_construct_rank / sortfhe_rotation_index_check bit for bit. */
 int sortfhe_num_batches(int n, int ring_dim, int* num_batch);
+
+/* Hybrid sorters (src/sort_algo.h:1051-1065 sort_hybrid, :1214-1230 sort_hybrid1, :1375-1391 sort_hybrid2): constructRank
+ * followed by the matrix-style index check of :893-1049 / :1067-1211 / :1232-1372.  variant 0 = sort_hybrid (sinc below
+ * N = 256, composite-sign indicator above), 1 = sort_hybrid1 (MEHP24 indicatorAdv), 2 = sort_hybrid2 (sinc).  The
+ * reference's PrivateKey argument is debug-only and has no counterpart.  Parameters: multiplicative depth and rotation
+ * key set of tests/DirectSortHTest.cpp:28-92, DirectSortH1Test.cpp:37-101, DirectSortH2Test.cpp:37-101. */
+int sortfhe_hybrid_sort_params(int n, int variant, int ring_dim, int* mult_depth, int32_t* rotations, int cap, int* count);
+int sortfhe_hybrid_sort(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int variant, int sign_n, int dg, int df,
+                        const int32_t* rot_indices, int rot_count, ckks_ct_t** out);
+int sortfhe_hybrid_index_check(ckks_ctx_t* ctx, const ckks_ct_t* rank, const ckks_ct_t* input, int n, int variant,
+                               const int32_t* rot_indices, int rot_count, ckks_ct_t** out);
 int sortfhe_construct_rank_partial(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sign_n, int dg, int df,
                                    const int32_t* rot_indices, int rot_count, int b_lo, int b_hi, int seed, ckks_ct_t** out);
 int sortfhe_finish_rank(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n, const int32_t* rot_indices, int rot_count, ckks_ct_t** out);
@@ -45,6 +56,9 @@ int sortfhe_finish_index_check(ckks_ctx_t* ctx, const ckks_ct_t* partial, int n,
 /* Comparison::compare (src/comparison.cpp:4-22) and sign() (src/sign.cpp:635-651), CompositeSign only */
 int sortfhe_compare(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, int sign_n, int dg, int df, ckks_ct_t** out);
 int sortfhe_sign(ckks_ctx_t* ctx, const ckks_ct_t* x, int sign_n, int dg, int df, ckks_ct_t** out);
+/* sign(x, cc, func, cfg) with func in the order of enum SignFunc (src/sign.h:6-11): 0 CompositeSign, 2 Tanh (degree-1006
+ * Chebyshev, sign.cpp:625-633), 3 NaiveDiscrete (degree-119 step, sign.cpp:610-623); 1 SignumPolycircuit is refused */
+int sortfhe_sign_func(ckks_ctx_t* ctx, const ckks_ct_t* x, int func, int sign_n, int dg, int df, ckks_ct_t** out);
 /* Comparison::indicator (src/comparison.cpp:24-40) */
 int sortfhe_indicator(ckks_ctx_t* ctx, const ckks_ct_t* x, double c, int sign_n, int dg, int df, ckks_ct_t** out);
 
@@ -52,6 +66,11 @@ int sortfhe_indicator(ckks_ctx_t* ctx, const ckks_ct_t* x, double c, int sign_n,
  * algo: 0 NAF, 1 BNAF, 2 BINARY.  steps receives the signed step sizes. */
 int sortfhe_rotate(ckks_ctx_t* ctx, const ckks_ct_t* x, int n, int rotation, const int32_t* rot_indices, int rot_count,
                    ckks_ct_t** out);
+/* RotationTree<N> (src/rotation.h:239-358): builds the tree for the rotations start..end and returns treeRotate(x, r)
+ * for every r in that range (hoisted EvalFastRotation below the root and below steps wider than 2); outs receives
+ * end - start + 1 fresh handles */
+int sortfhe_tree_rotate(ckks_ctx_t* ctx, const ckks_ct_t* x, int n, int start, int end, int algo, const int32_t* rot_indices,
+                        int rot_count, ckks_ct_t** outs);
 int sortfhe_decompose(int n, int rotation, int wrap, int algo, const int32_t* rot_indices, int rot_count, int32_t* steps,
                       int cap, int* count);
 

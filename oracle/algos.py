@@ -9,7 +9,7 @@ import math
 
 import numpy as np
 
-from .cheby import truncated_doubled_sinc_coeffs
+from .cheby import truncated_doubled_sinc_coeffs, truncated_sinc_coeffs
 
 G4_COEFFS = [
     0.0, 1.077117252745569, 0.0, -0.36166113998402755, 0.0, 0.2137420717859748, 0.0, -0.15635204788780485,
@@ -76,6 +76,15 @@ def compare(cc, a, b, n, dg, df):
     """Comparison::compare (comparison.cpp:4-22): (sign(a-b)+1)*0.5"""
     s = composite_sign(cc, cc.EvalSub(a, b), n, dg, df)
     return cc.EvalMult(cc.EvalAdd(s, 1.0), 0.5)
+
+
+def indicator(cc, x, c, n, dg, df):
+    """Comparison::indicator (comparison.cpp:24-40): 1 where |x| < c"""
+    s1 = composite_sign(cc, cc.EvalAdd(x, c), n, dg, df)
+    s2 = composite_sign(cc, cc.EvalSub(x, c), n, dg, df)
+    c1 = cc.EvalMult(cc.EvalAdd(s1, 1.0), 0.5)
+    c2 = cc.EvalMult(cc.EvalAdd(s2, 1.0), 0.5)
+    return cc.EvalMult(c1, cc.EvalSub(1.0, c2))
 
 
 class Rotator:
@@ -228,6 +237,60 @@ class DirectSort:
             out = cc.EvalAdd(out, self.rot.rotate(out, num_slots // (1 << i)))
         out.slots = N
         return out
+
+    def _fold_to_target(self, c, size, target, first_step, row_mask):
+        """sumColumnsToTarget (:825-858) / transposeColumnTarget (:860-890)"""
+        cc, lg = self.cc, int(math.log2(size))
+        c = c.clone(); c.slots = size * size
+        step = first_step
+        for i in range(lg):
+            right = (target >> (lg - 1 - i)) & 1
+            c = cc.EvalAdd(c, self.rot.rotate(c, -step if right else step))
+            step >>= 1
+        m = np.zeros(size * size)
+        if row_mask:
+            m[size * target:size * (target + 1)] = 1.0
+        else:
+            m[target::size] = 1.0
+        return cc.EvalMult(c, cc.MakeCKKSPackedPlaintext(m, 1, c.level, None, size * size))
+
+    def rotation_index_check_hybrid(self, rank, ct_in, variant):
+        """rotationIndexCheckHybrid (:893-1049, variant 0), Hybrid1 (:1067-1211, variant 1), Hybrid2 (:1232-1372, 2)"""
+        cc, N = self.cc, self.N
+        num_slots, num_batch = (self.max_batch, N // 256) if N > 256 else (N * N, 1)
+        size = min(N, 256)
+        scaled = variant != 1
+        rank = rank.clone(); rank.slots = num_slots
+        r = cc.EvalMult(rank, 1.0 / N) if scaled else rank
+        ct_in = ct_in.clone(); ct_in.slots = num_slots
+        rots_rank = [self.rot.rotate(r, b * 256) for b in range(num_batch)]
+        rots_in = [self.rot.rotate(ct_in, b * 256) for b in range(num_batch)]
+        dg_i, df_i = int((math.log2(N) + 1) / 2), 2
+        masked = []
+        for b in range(num_batch):
+            sub = np.zeros(num_slots)
+            rows = np.repeat(np.arange(size, dtype=np.float64) + b * size, size)
+            sub[:size * size] = rows / float(N) if scaled else rows
+            psub = cc.MakeCKKSPackedPlaintext(sub, 1, rank.level, None, num_slots)
+            acc = self.zero.clone(); acc.slots = num_slots
+            for k in range(num_batch):
+                m = cc.EvalSub(psub, rots_rank[k])
+                if variant == 1:
+                    m = Mehp24(cc, size).indicator_adv(m, float(N), dg_i, df_i)
+                elif variant == 2 or N < 256:
+                    if not hasattr(self, "_sinc1"):
+                        self._sinc1 = truncated_sinc_coeffs(N)
+                    m = cc.EvalChebyshevSeriesPS(m, self._sinc1, -1, 1)
+                else:
+                    m = indicator(cc, m, 0.5 / N, 3, 4 if N < 512 else 5, 2)
+                acc = cc.EvalAdd(acc, cc.EvalMult(rots_in[k], m))
+            acc = self._fold_to_target(acc, N // num_batch, b, (N // num_batch) >> 1, False)
+            masked.append(self._fold_to_target(acc, N // num_batch, b, (N // num_batch) * (N // num_batch - 1) // 2, True))
+        return cc.EvalAddMany(masked)
+
+    def sort_hybrid(self, ct_in, sign_cfg, variant):
+        """sort_hybrid / sort_hybrid1 / sort_hybrid2 (:1051-1065, 1214-1230, 1375-1391)"""
+        return self.rotation_index_check_hybrid(self.construct_rank(ct_in, sign_cfg), ct_in, variant)
 
     def sort(self, ct_in, sign_cfg):
         """DirectSort::sort (:752-774)"""

@@ -307,6 +307,24 @@ class Engine:
         return self._out(_L.ckks_eval_chebyshev_series_ps(_vp(self.h), _vp(x.h), _f64p(v), v.size, _d(a), _d(b),
                                                           ctypes.byref(o)), o)
 
+    def EvalChebyshevSeries(self, x, coeffs, a=-1.0, b=1.0):
+        v = np.ascontiguousarray(coeffs, dtype=np.float64)
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_chebyshev_series(_vp(self.h), _vp(x.h), _f64p(v), v.size, _d(a), _d(b),
+                                                       ctypes.byref(o)), o)
+
+    @staticmethod
+    def EvalChebyshevCoefficients(func, a, b, degree):
+        """interpolation at the degree+1 Chebyshev nodes of [a, b]; c_0 doubled (halved again by the evaluators)"""
+        cnt = degree + 1
+        j = np.arange(cnt) + 0.5
+        f = np.array([func(v) for v in np.cos(np.pi / cnt * j) * 0.5 * (b - a) + 0.5 * (b + a)], dtype=np.float64)
+        return np.array([np.sum(f * np.cos(np.pi / cnt * i * j)) for i in range(cnt)]) * 2.0 / cnt
+
+    def EvalChebyshevFunction(self, func, x, a, b, degree):
+        """mehp24_utils.cpp:109-163, sign.cpp:616-633"""
+        return self.EvalChebyshevSeries(x, self.EvalChebyshevCoefficients(func, a, b, degree), a, b)
+
     def EvalPolyLinear(self, x, coeffs):
         v = np.ascontiguousarray(coeffs, dtype=np.float64)
         o = ctypes.c_void_p()
@@ -333,6 +351,7 @@ _L.ckks_eval_add_const.argtypes = [_vp, _vp, _d, _pp]
 _L.ckks_eval_sub_const.argtypes = [_vp, _vp, _d, _pp]
 _L.ckks_eval_mult_const.argtypes = [_vp, _vp, _d, _pp]
 _L.ckks_eval_const_sub.argtypes = [_vp, _d, _vp, _pp]
+_L.ckks_eval_chebyshev_series.argtypes = [_vp, _vp, ctypes.POINTER(ctypes.c_double), _i, _d, _d, _pp]
 _L.ckks_eval_chebyshev_series_ps.argtypes = [_vp, _vp, ctypes.POINTER(ctypes.c_double), _i, _d, _d, _pp]
 _L.ckks_make_packed_plaintext.argtypes = [_vp, ctypes.POINTER(ctypes.c_double), _i, _i, _i, _i, _pp]
 _L.ckks_ct_export.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_size_t]
@@ -356,13 +375,18 @@ _H.sortfhe_last_error.restype = ctypes.c_char_p
 _i32p = ctypes.POINTER(ctypes.c_int32)
 _ip = ctypes.POINTER(ctypes.c_int)
 _H.sortfhe_direct_sort_params.argtypes = [_i, _i, _ip, _i32p, _i, _ip]
+_H.sortfhe_hybrid_sort_params.argtypes = [_i, _i, _i, _ip, _i32p, _i, _ip]
+_H.sortfhe_hybrid_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i32p, _i, _pp]
+_H.sortfhe_hybrid_index_check.argtypes = [_vp, _vp, _vp, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_direct_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_construct_rank.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_rotation_index_check.argtypes = [_vp, _vp, _vp, _i, _i32p, _i, _pp]
 _H.sortfhe_compare.argtypes = [_vp, _vp, _vp, _i, _i, _i, _pp]
 _H.sortfhe_sign.argtypes = [_vp, _vp, _i, _i, _i, _pp]
+_H.sortfhe_sign_func.argtypes = [_vp, _vp, _i, _i, _i, _i, _pp]
 _H.sortfhe_indicator.argtypes = [_vp, _vp, _d, _i, _i, _i, _pp]
 _H.sortfhe_rotate.argtypes = [_vp, _vp, _i, _i, _i32p, _i, _pp]
+_H.sortfhe_tree_rotate.argtypes = [_vp, _vp, _i, _i, _i, _i, _i32p, _i, _pp]
 _H.sortfhe_decompose.argtypes = [_i, _i, _i, _i, _i32p, _i, _i32p, _i, _ip]
 _H.sortfhe_sinc_coefficients.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_double), _i, _ip]
 _H.sortfhe_num_batches.argtypes = [_i, _i, _ip]
@@ -397,6 +421,17 @@ def direct_sort_params(n, ring_dim=1 << 17):
     return depth.value, list(buf[:cnt.value])
 
 
+HYBRID_VARIANTS = {"hybrid": 0, "hybrid1": 1, "hybrid2": 2}
+
+
+def hybrid_sort_params(n, variant="hybrid1", ring_dim=1 << 17):
+    """(multDepth, rotation key indices) of sort_hybrid / sort_hybrid1 / sort_hybrid2 (tests/DirectSortH*Test.cpp)"""
+    depth, cnt = ctypes.c_int(), ctypes.c_int()
+    buf = (ctypes.c_int32 * 4096)()
+    _hchk(_H.sortfhe_hybrid_sort_params(n, HYBRID_VARIANTS[variant], ring_dim, ctypes.byref(depth), buf, 4096, ctypes.byref(cnt)))
+    return depth.value, list(buf[:cnt.value])
+
+
 def num_batches(n, ring_dim=1 << 17):
     """num_batch of DirectSort<N> at a ring dimension (src/sort_algo.h:378-380)"""
     v = ctypes.c_int()
@@ -425,6 +460,13 @@ class DirectSort:
     def rotation_index_check(self, rank, ct):
         return self._run(_H.sortfhe_rotation_index_check, _vp(rank.h), _vp(ct.h), self.n)
 
+    def sort_hybrid(self, ct, sign_cfg=(3, 3, 2), variant="hybrid1"):
+        """sort_hybrid / sort_hybrid1 / sort_hybrid2 (src/sort_algo.h:1051-1065, 1214-1230, 1375-1391)"""
+        return self._run(_H.sortfhe_hybrid_sort, _vp(ct.h), self.n, HYBRID_VARIANTS[variant], *sign_cfg)
+
+    def hybrid_index_check(self, rank, ct, variant="hybrid1"):
+        return self._run(_H.sortfhe_hybrid_index_check, _vp(rank.h), _vp(ct.h), self.n, HYBRID_VARIANTS[variant])
+
     # shardable halves (multi-GPU, see shard.py): batches [lo, hi) of the two batch loops, and the folds after the all-reduce
     def _run_tail(self, f, head, *tail):
         a, c = _idx(self.rots)
@@ -451,9 +493,12 @@ def compare(eng, a, b, sign_cfg=(4, 3, 3)):
     return Ciphertext(eng, o.value)
 
 
-def sign(eng, x, sign_cfg=(3, 0, 1)):
+SIGN_FUNCS = {"CompositeSign": 0, "SignumPolycircuit": 1, "Tanh": 2, "NaiveDiscrete": 3}
+
+
+def sign(eng, x, sign_cfg=(3, 0, 1), func="CompositeSign"):
     o = ctypes.c_void_p()
-    _hchk(_H.sortfhe_sign(_vp(eng.h), _vp(x.h), *sign_cfg, ctypes.byref(o)))
+    _hchk(_H.sortfhe_sign_func(_vp(eng.h), _vp(x.h), SIGN_FUNCS[func], *sign_cfg, ctypes.byref(o)))
     return Ciphertext(eng, o.value)
 
 
@@ -468,6 +513,14 @@ def rotate(eng, x, n, rotation, rot_indices):
     o = ctypes.c_void_p()
     _hchk(_H.sortfhe_rotate(_vp(eng.h), _vp(x.h), n, rotation, a, c, ctypes.byref(o)))
     return Ciphertext(eng, o.value)
+
+
+def tree_rotate(eng, x, n, start, end, rot_indices, algo="NAF"):
+    """RotationTree<N>::buildTree(start, end) + treeRotate for every rotation of the range -> list of ciphertexts"""
+    a, c = _idx(rot_indices)
+    outs = (ctypes.c_void_p * (end - start + 1))()
+    _hchk(_H.sortfhe_tree_rotate(_vp(eng.h), _vp(x.h), n, start, end, {"NAF": 0, "BNAF": 1, "BINARY": 2}[algo], a, c, outs))
+    return [Ciphertext(eng, h) for h in outs]
 
 
 def decompose(n, rotation, wrap, rot_indices, algo="BINARY"):

@@ -331,6 +331,12 @@ int ckks_eval_chebyshev_series_ps(ckks_ctx_t* x, const ckks_ct_t* ct, const doub
     *out = box(eval_chebyshev_series_ps(G(ct), std::vector<double>(coeffs, coeffs + count), a, b));
     API_END
 }
+int ckks_eval_chebyshev_series(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, double a, double b, ckks_ct_t** out) {
+    API_BEGIN (void)C(x);
+    if (count < 2) throw std::runtime_error("EvalChebyshevSeries: need at least 2 coefficients");
+    *out = box(eval_chebyshev_series(G(ct), std::vector<double>(coeffs, coeffs + count), a, b));
+    API_END
+}
 int ckks_eval_poly_linear(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, ckks_ct_t** out) {
     API_BEGIN (void)C(x); *out = box(eval_poly_linear(G(ct), std::vector<double>(coeffs, coeffs + count))); API_END
 }

@@ -180,6 +180,37 @@ Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coefficient
     return ct_clone(res.get());
 }
 
+// EvalChebyshevSeriesLinear: all T_1..T_n by the doubling recurrences, one weighted sum, + c_0 / 2.  OpenFHE takes
+// this route for degree < 5 (EvalChebyshevSeries), which none of the reference's call sites reach.
+Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coefficients, double a, double b) {
+    const int k = (int)coefficients.size() - 1;
+    if (k < 1) throw std::runtime_error("EvalChebyshevSeriesLinear: degree must be >= 1");
+    std::vector<CtP> T(k);
+    if (std::fabs(a + 1.0) < 1e-10 && std::fabs(b - 1.0) < 1e-10) T[0] = wrap(ct_clone(x));
+    else {
+        double alpha = 2.0 / (b - a), beta = 2.0 * a / (b - a);
+        T[0] = addc(wrap(eval_mult_const(x, alpha)), -1.0 - beta);
+    }
+    CtP y = wrap(ct_clone(T[0].get()));
+    for (int i = 2; i <= k; i++) {
+        if (i % 2 == 0) {
+            CtP sq = mul(T[i / 2 - 1], T[i / 2 - 1]);
+            T[i - 1] = addc(add(sq, sq), -1.0);
+        } else {
+            CtP pr = mul(T[i / 2 - 1], T[i / 2]);
+            T[i - 1] = sub(add(pr, pr), y);
+        }
+    }
+    for (int i = 1; i < k; i++) adjust_levels_and_depth(T[i - 1].get(), T[k - 1].get());
+    CtP acc = wsum(T, k, coefficients);
+    return ct_clone(addc(acc, coefficients[0] / 2.0).get());
+}
+
+Ct* eval_chebyshev_series(const Ct* x, const std::vector<double>& coefficients, double a, double b) {
+    return degree(coefficients) < 5 ? eval_chebyshev_series_linear(x, coefficients, a, b)
+                                    : eval_chebyshev_series_ps(x, coefficients, a, b);
+}
+
 Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs) {
     const int n = (int)coeffs.size() - 1;
     if (n < 1) throw std::runtime_error("EvalPolyLinear: degree must be >= 1");

@@ -42,6 +42,8 @@ void decrypt(const Ct* ct, double* out, int out_len);
 // cheby.cu
 Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& weights);
 Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coeffs, double a, double b);
+Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coeffs, double a, double b);
+Ct* eval_chebyshev_series(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs);
 void long_division_chebyshev(const std::vector<double>& f, const std::vector<double>& g, std::vector<double>& q,
                              std::vector<double>& r);

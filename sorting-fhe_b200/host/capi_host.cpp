@@ -102,6 +102,50 @@ int sortfhe_rotation_index_check(ckks_ctx_t* ctx, const ckks_ct_t* rank, const c
     HOST_END
 }
 
+int sortfhe_hybrid_sort_params(int n, int variant, int ring_dim, int* mult_depth, int32_t* rotations, int cap, int* count) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        CCParams<CryptoContextCKKSRNS> p; p.SetRingDim((uint32_t)ring_dim);
+        std::vector<int> r;
+        DirectSort<N>::getHybridParameters(variant, p, r);
+        if ((int)r.size() > cap) throw std::runtime_error("hybrid_sort_params: rotation buffer too small");
+        *mult_depth = (int)p.GetMultiplicativeDepth(); *count = (int)r.size();
+        for (size_t i = 0; i < r.size(); i++) rotations[i] = r[i];
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_hybrid_sort(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int variant, int sn, int dg, int df, const int32_t* idx,
+                        int cnt, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (variant < 0 || variant > 2) throw std::runtime_error("hybrid sort: variant must be 0, 1 or 2");
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        SignConfig cfg = make_cfg(sn, dg, df);
+        typedef typename DirectSort<N>::HybridIndicator K;
+        *out = release(s->sort_hybrid(borrow(input), SignFunc::CompositeSign, cfg,
+                                      variant == 0 ? K::SincOrCompare : variant == 1 ? K::Mehp24 : K::Sinc));
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_hybrid_index_check(ckks_ctx_t* ctx, const ckks_ct_t* rank, const ckks_ct_t* input, int n, int variant,
+                               const int32_t* idx, int cnt, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (variant < 0 || variant > 2) throw std::runtime_error("hybrid sort: variant must be 0, 1 or 2");
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        auto s = make_sorter<N>(ctx, idx, cnt);
+        typedef typename DirectSort<N>::HybridIndicator K;
+        *out = release(s->rotationIndexCheckHybrid(borrow(rank), borrow(input),
+                                                   variant == 0 ? K::SincOrCompare : variant == 1 ? K::Mehp24 : K::Sinc));
+        return 0;
+    });
+    HOST_END
+}
+
 int sortfhe_compare(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, int sn, int dg, int df, ckks_ct_t** out) {
     HOST_BEGIN
     SignConfig cfg = make_cfg(sn, dg, df);
@@ -112,6 +156,12 @@ int sortfhe_compare(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, int
 int sortfhe_sign(ckks_ctx_t* ctx, const ckks_ct_t* x, int sn, int dg, int df, ckks_ct_t** out) {
     HOST_BEGIN
     *out = release(sign(borrow(x), borrow(ctx, 0), SignFunc::CompositeSign, make_cfg(sn, dg, df)));
+    HOST_END
+}
+int sortfhe_sign_func(ckks_ctx_t* ctx, const ckks_ct_t* x, int func, int sn, int dg, int df, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (func < 0 || func > 3) throw std::runtime_error("sign_func: func must be 0..3 (SignFunc order of src/sign.h:6-11)");
+    *out = release(sign(borrow(x), borrow(ctx, 0), (SignFunc)func, make_cfg(sn, dg, df)));
     HOST_END
 }
 int sortfhe_indicator(ckks_ctx_t* ctx, const ckks_ct_t* x, double c, int sn, int dg, int df, ckks_ct_t** out) {
@@ -128,6 +178,25 @@ int sortfhe_rotate(ckks_ctx_t* ctx, const ckks_ct_t* x, int n, int rotation, con
         constexpr int N = decltype(tag)::value;
         RotationComposer<N> rc(borrow(ctx, 0), nullptr, std::vector<int>(idx, idx + cnt));
         *out = release(rc.rotate(borrow(x), rotation));
+        return 0;
+    });
+    HOST_END
+}
+int sortfhe_tree_rotate(ckks_ctx_t* ctx, const ckks_ct_t* x, int n, int start, int end, int algo, const int32_t* idx, int cnt,
+                        ckks_ct_t** outs /*[end - start + 1]*/) {
+    HOST_BEGIN
+    dispatch_n(n, [&](auto tag) {
+        constexpr int N = decltype(tag)::value;
+        RotationTree<N> tree(borrow(ctx, 0), std::vector<int>(idx, idx + cnt),
+                             algo == 0 ? DecomposeAlgo::NAF : algo == 1 ? DecomposeAlgo::BNAF : DecomposeAlgo::BINARY);
+        tree.buildTree(start, end);
+        CT in = borrow(x);
+        for (int r = start; r <= end; r++) outs[r - start] = nullptr;
+        for (int r = start; r <= end; r++) {
+            ckks_ct_t* o = nullptr;                     // results may be shared tree nodes (or the input): hand out clones
+            ckks_check(ckks_ct_clone(tree.treeRotate(in, r)->h, &o), "clone");
+            outs[r - start] = o;
+        }
         return 0;
     });
     HOST_END

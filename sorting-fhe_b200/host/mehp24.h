@@ -69,6 +69,24 @@ inline CT signAdv(const CC& cc, CT c, size_t dg, size_t df) {
     for (size_t d = 0; d + 1 < df; d++) c = cc->EvalPolyLinear(c, f3);
     return cc->EvalPolyLinear(c, f3_final);
 }
+// Chebyshev-interpolated predicates on c1 - c2 in [a, b] (:105-163); `error` is the dead zone around zero
+inline CT equal(const CC& cc, const CT& c1, const CT& c2, double a, double b, uint32_t degree, double error = 0.00001) {
+    return cc->EvalChebyshevFunction([error](double v) -> double { return (v > error || v < -error) ? 0.0 : 1.0; },
+                                     cc->EvalSub(c1, c2), a, b, degree);
+}
+inline CT compare(const CC& cc, const CT& c1, const CT& c2, double a, double b, uint32_t degree, double error = 0.00001) {
+    return cc->EvalChebyshevFunction([error](double v) -> double { return v > error ? 1.0 : v >= -error ? 0.5 : 0.0; },
+                                     cc->EvalSub(c1, c2), a, b, degree);
+}
+inline CT compareGt(const CC& cc, const CT& c1, const CT& c2, double a, double b, uint32_t degree, double error = 0.00001) {
+    return cc->EvalChebyshevFunction([error](double v) -> double { return v > error ? 1.0 : 0.0; }, cc->EvalSub(c1, c2), a, b,
+                                     degree);
+}
+inline CT compareAdv(const CC& cc, const CT& c1, const CT& c2, size_t dg, size_t df) { return signAdv(cc, cc->EvalSub(c1, c2), dg, df); }
+inline CT indicator(const CC& cc, const CT& c, double a1, double b1, double a, double b, uint32_t degree) {
+    return cc->EvalChebyshevFunction([a1, b1](double v) -> double { return (v < a1 || v > b1) ? 0.0 : 1.0; }, c, a, b, degree);
+}
+
 // indicatorAdv (:166-174): 1 where |x| < 1/2 on x in (-b, b)
 inline CT indicatorAdv(const CC& cc, const CT& c, double b, size_t dg, size_t df) {
     CT tmp = cc->EvalMult(c, 1.0 / b);

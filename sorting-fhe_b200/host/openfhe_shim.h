@@ -234,7 +234,27 @@ class CryptoContextImpl {
         return wrap(o);
     }
     CT EvalChebyshevSeries(const CT& x, const std::vector<double>& coeffs, double a, double b) const {
-        return EvalChebyshevSeriesPS(x, coeffs, a, b);
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_eval_chebyshev_series(ctx, x->h, coeffs.data(), (int)coeffs.size(), a, b, &o), "EvalChebyshevSeries");
+        return wrap(o);
+    }
+    // Chebyshev interpolation at the degree+1 Chebyshev nodes of [a, b] (the reference's EvalChebyshevFunction call
+    // sites: mehp24_utils.cpp:109-163, sign.cpp:616-633); c_0 is stored doubled, the series evaluators halve it
+    static std::vector<double> EvalChebyshevCoefficients(const std::function<double(double)>& func, double a, double b,
+                                                         uint32_t degree) {
+        const uint32_t cnt = degree + 1;
+        const double half = 0.5 * (b - a), mid = 0.5 * (b + a), step = M_PI / cnt;
+        std::vector<double> f(cnt), c(cnt);
+        for (uint32_t j = 0; j < cnt; j++) f[j] = func(std::cos(step * (j + 0.5)) * half + mid);
+        for (uint32_t i = 0; i < cnt; i++) {
+            double acc = 0;
+            for (uint32_t j = 0; j < cnt; j++) acc += f[j] * std::cos(step * i * (j + 0.5));
+            c[i] = acc * 2.0 / cnt;
+        }
+        return c;
+    }
+    CT EvalChebyshevFunction(const std::function<double(double)>& func, const CT& x, double a, double b, uint32_t degree) const {
+        return EvalChebyshevSeries(x, EvalChebyshevCoefficients(func, a, b, degree), a, b);
     }
     CT EvalPolyLinear(const CT& x, const std::vector<double>& coeffs) const {
         ckks_ct_t* o = nullptr;

@@ -4,6 +4,8 @@
 #pragma once
 #include <algorithm>
 #include <cstdint>
+#include <map>
+#include <memory>
 #include <set>
 #include <vector>
 #include "encryption.h"
@@ -101,4 +103,73 @@ template <int N> class RotationComposer {
     }
     const std::set<int>& getRotationCalls() const { return rotation_calls; }
     void clearRotationCalls() { rotation_calls.clear(); }
+};
+
+// RotationTree<N> (reference src/rotation.h:239-358): a trie over the step sequences of the rotations start..end.
+// Rotating through it memoises every intermediate ciphertext on its node, and the children of one node are produced
+// from ONE set of hoisted ModUp digits (EvalFastRotationPrecompute / EvalFastRotation) -- the reference's only use
+// of hoisting.  As in the reference, the cache belongs to the first input the tree is used with.
+template <int N> class RotationTree {
+  public:
+    struct RotationNode {
+        int stepSize;
+        RotationNode* parent;
+        std::map<int, std::unique_ptr<RotationNode>> children;
+        std::vector<int> finalValues;                 // rotations that end at this node
+        Ciphertext<DCRTPoly> rotatedCiphertext;       // memoised result of the path root -> this node
+        Ciphertext<DCRTPoly> cPrecomp;                // hoisted digits of the ciphertext at this node
+        RotationNode(int step, RotationNode* p = nullptr) : stepSize(step), parent(p) {}
+    };
+
+  private:
+    std::unique_ptr<RotationNode> root;
+    Decomposer<N> m_decomposer;
+    DecomposeAlgo m_algo;
+    CryptoContext<DCRTPoly> m_cc;
+    uint32_t M;
+
+    RotationNode* descend(RotationNode* node, int step, bool create) {
+        auto it = node->children.find(step);
+        if (it != node->children.end()) return it->second.get();
+        if (!create) return nullptr;
+        auto& slot = node->children[step];
+        slot.reset(new RotationNode(step, node));
+        return slot.get();
+    }
+
+  public:
+    RotationTree(CryptoContext<DCRTPoly> cc, const std::vector<int>& rotIndices, DecomposeAlgo algo = DecomposeAlgo::NAF)
+        : root(new RotationNode(0)), m_decomposer(rotIndices), m_algo(algo), m_cc(cc), M(cc->GetCyclotomicOrder()) {}
+
+    void buildTree(int start, int end) {              // (:271-279)
+        for (int i = start; i <= end; ++i) {
+            RotationNode* node = root.get();
+            for (const Step& s : m_decomposer.decompose(i, end, m_algo))
+                if (s.value != 0) node = descend(node, s.stepSize, true);
+            node->finalValues.push_back(i);
+        }
+    }
+
+    Ciphertext<DCRTPoly> treeRotate(const Ciphertext<DCRTPoly>& input, int rotation) {   // (:281-291, 315-357)
+        if (!root->cPrecomp) root->cPrecomp = m_cc->EvalFastRotationPrecompute(input);
+        Ciphertext<DCRTPoly> cur = input;
+        RotationNode* node = root.get();
+        for (const Step& s : m_decomposer.decompose(rotation, (int)input->GetSlots(), m_algo)) {
+            if (s.value == 0) continue;
+            RotationNode* child = descend(node, s.stepSize, false);
+            if (!child) return cur;                    // not in the tree: the reference reports and returns what it has
+            if (!child->rotatedCiphertext) {
+                if (std::abs(node->stepSize) > 2 || node->stepSize == 0) {   // hoisted below the root and below wide steps
+                    if (!node->cPrecomp) node->cPrecomp = m_cc->EvalFastRotationPrecompute(cur);
+                    child->rotatedCiphertext = m_cc->EvalFastRotation(cur, child->stepSize, M, node->cPrecomp);
+                } else {
+                    child->rotatedCiphertext = m_cc->EvalRotate(cur, child->stepSize);
+                }
+            }
+            cur = child->rotatedCiphertext;
+            node = child;
+        }
+        return cur;
+    }
+    const RotationNode* getRoot() const { return root.get(); }
 };

@@ -1,3 +1,5 @@
+#include <cmath>
+#include <cstdlib>
 // sign.cpp -- compositeSign<3>, compositeSign<4> and the dispatcher (reference src/sign.cpp:9-185,635-651).
 // Polynomials: g_3/f_3 degree-7 odd (sign.cpp:18-21,41-44), g_4 degree-27 Chebyshev series (sign.cpp:68-75),
 // f_4 degree-15 odd (sign.cpp:81-88).  The evaluation ORDER is the reference's, because under
@@ -77,9 +79,23 @@ Ciphertext<DCRTPoly> compositeSign(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPol
 template Ciphertext<DCRTPoly> compositeSign<3>(Ciphertext<DCRTPoly>, CryptoContext<DCRTPoly>, const SignConfig&);
 template Ciphertext<DCRTPoly> compositeSign<4>(Ciphertext<DCRTPoly>, CryptoContext<DCRTPoly>, const SignConfig&);
 
+// Chebyshev-interpolated alternatives (sign.cpp:610-633): a degree-119 step function and a degree-1006 steep tanh
+Ciphertext<DCRTPoly> naive_discrete_sign(Ciphertext<DCRTPoly> a, CryptoContext<DCRTPoly> cc) {
+    return cc->EvalChebyshevFunction([](double v) -> double { return v >= 0 ? 1.0 : 0.0; }, a, -1.0, 1.0, 119);
+}
+Ciphertext<DCRTPoly> tanh(Ciphertext<DCRTPoly> a, CryptoContext<DCRTPoly> cc) {
+    return cc->EvalChebyshevFunction([](double v) -> double { return std::tanh(v * (double)RAND_MAX); }, a, -1.0, 1.0, 1006);
+}
+
 Ciphertext<DCRTPoly> sign(Ciphertext<DCRTPoly> x, CryptoContext<DCRTPoly> cc, SignFunc func, const SignConfig& Cfg) {
-    if (func != SignFunc::CompositeSign)
-        throw std::runtime_error("sign: only SignFunc::CompositeSign is on the sorter hot path (SURVEY.md section 2 row 4)");
+    switch (func) {
+        case SignFunc::CompositeSign: break;
+        case SignFunc::Tanh: return tanh(x, cc);
+        case SignFunc::NaiveDiscrete: return naive_discrete_sign(x, cc);
+        default:
+            throw std::runtime_error("sign: SignFunc::SignumPolycircuit (a hard-coded degree-1023 table of a third-party circuit) is not "
+                                     "provided; use CompositeSign, Tanh or NaiveDiscrete");
+    }
     switch (Cfg.compos.n) {
         case 3: return compositeSign<3>(x, cc, Cfg);
         case 4: return compositeSign<4>(x, cc, Cfg);

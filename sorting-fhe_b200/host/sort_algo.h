@@ -9,6 +9,7 @@
 #include <vector>
 #include "cheb_coeffs.h"
 #include "comparison.h"
+#include "mehp24.h"
 #include "rotation.h"
 
 enum class SortAlgo { DirectSort, BitonicSort };
@@ -80,6 +81,42 @@ template <int N> class DirectSort : public SortBase<N> {
         parameters.SetMultiplicativeDepth(d);
         const int ringDim = parameters.GetRingDim() ? (int)parameters.GetRingDim() : (1 << 17);
         rotations = (ringDim == (1 << 17) && N >= 256) ? referenceKeySet() : requiredRotations(ringDim);
+    }
+
+    // parameters of the hybrid sorters: depth tables of tests/DirectSortHTest.cpp:28-92, DirectSortH1Test.cpp:37-101,
+    // DirectSortH2Test.cpp:37-101; key set = the rank phase's amounts plus the fold steps of
+    // sumColumnsToTarget / transposeColumnTarget for every block (the tests' literal tables, as their pattern)
+    static void getHybridParameters(int variant, CCParams<CryptoContextCKKSRNS>& parameters, std::vector<int>& rotations) {
+        static const int sizes[9] = {4, 8, 16, 32, 64, 128, 256, 512, 1024};
+        static const int depth[3][9] = {{24, 25, 25, 29, 30, 31, 44, 47, 50},     // sort_hybrid
+                                        {31, 35, 35, 42, 42, 46, 49, 53, 56},     // sort_hybrid1
+                                        {24, 25, 25, 29, 30, 31, 35, 36, 40}};    // sort_hybrid2
+        if (variant < 0 || variant > 2) throw std::runtime_error("hybrid sort: variant must be 0, 1 or 2");
+        int d = 0;
+        for (int i = 0; i < 9; i++) if (sizes[i] == N) d = depth[variant][i];
+        if (!d) throw std::runtime_error("hybrid sort: unsupported array size");
+        parameters.SetBatchSize(N);
+        parameters.SetScalingModSize(40);
+        parameters.SetMultiplicativeDepth(d);
+        using namespace directsort_detail;
+        const int ringDim = parameters.GetRingDim() ? (int)parameters.GetRingDim() : (1 << 17);
+        const int P = std::min(N, ringDim / 2 / N), B = N / P, S = N * P;
+        std::set<int> r;
+        const int np = std::min(rankBabySteps(N), P);
+        for (int i = 1; i < np; i++) r.insert(i);
+        for (int b = 0; b < B; b++) for (int j = 0; j < P / np; j++) r.insert(b * P + j * np);
+        for (int i = 1; i <= log2i(P); i++) r.insert(S >> i);
+        const int blocks = N > 256 ? N / 256 : 1, side = N / blocks, lg = log2i(side);
+        for (int b = 0; b < blocks; b++) {
+            r.insert(b * 256);
+            for (int i = 0; i < lg; i++) {
+                const int sgn = ((b >> (lg - 1 - i)) & 1) ? -1 : 1;
+                r.insert(sgn * ((side >> 1) >> i));
+                r.insert(sgn * ((side * (side - 1) / 2) >> i));
+            }
+        }
+        r.erase(0);
+        rotations.assign(r.begin(), r.end());
     }
 
     // The reference's literal key sets for N >= 256 at ring 2^17 (:125-148) are not the set of rotation amounts
@@ -225,6 +262,83 @@ template <int N> class DirectSort : public SortBase<N> {
         output->SetSlots(N);
         return output;
     }
+
+    // ---- hybrid index checks (:776-1391): the N x N "rank_j == i" matrix of MEHP24 in one ciphertext of N*N slots
+    // (256 x 256 blocks above N = 256), folded along columns and transposed back to a row -- no baby/giant rotations.
+    // The three published variants differ only in the indicator they put on (i - rank_j):
+    enum class HybridIndicator {
+        SincOrCompare,   // sort_hybrid  (:893-1049): sinc below N = 256, composite-sign indicator from there on
+        Mehp24,          // sort_hybrid1 (:1067-1211): mehp24::utils::indicatorAdv on the unscaled difference
+        Sinc             // sort_hybrid2 (:1232-1372): sinc for every N
+    };
+
+    // fold by log2(matrixSize) rotations towards column `columnIndex` (:825-858) / row `rowIndex` (:860-890); the sign of
+    // each step follows the bits of the target, most significant first (getBinaryPath, :815-821)
+    CT foldToTarget(CT c, size_t matrixSize, size_t target, size_t firstStep, bool rowMask) {
+        const size_t lg = (size_t)std::log2((double)matrixSize);
+        c->SetSlots((uint32_t)(matrixSize * matrixSize));
+        size_t step = firstStep;
+        for (size_t i = 0; i < lg; i++, step >>= 1) {
+            const bool right = (target >> (lg - 1 - i)) & 1;
+            c = m_cc->EvalAdd(c, rot.rotate(c, right ? -(int)step : (int)step));
+        }
+        std::vector<double> msk(matrixSize * matrixSize, 0.0);
+        for (size_t i = 0; i < matrixSize; i++) msk[rowMask ? matrixSize * target + i : matrixSize * i + target] = 1.0;
+        Plaintext pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)c->GetLevel(), nullptr, (uint32_t)(matrixSize * matrixSize));
+        return m_cc->EvalMult(c, pmsk);
+    }
+    CT sumColumnsToTarget(CT c, size_t matrixSize, size_t columnIndex) { return foldToTarget(c, matrixSize, columnIndex, matrixSize >> 1, false); }
+    CT transposeColumnTarget(CT c, size_t matrixSize, size_t rowIndex) { return foldToTarget(c, matrixSize, rowIndex, matrixSize * (matrixSize - 1) / 2, true); }
+
+    CT rotationIndexCheckHybrid(const CT& ctx_Rank, const CT& input_array, HybridIndicator kind) {
+        const size_t maxArraySize = 256;
+        const size_t num_slots = (size_t)N > maxArraySize ? (size_t)max_batch : (size_t)N * N;
+        const size_t num_batch = (size_t)N > maxArraySize ? N / maxArraySize : 1;
+        const size_t array_size = std::min((size_t)N, maxArraySize);
+        const bool scaled = kind != HybridIndicator::Mehp24;          // ranks and row indices divided by N (:912, 1250)
+        ctx_Rank->SetSlots((uint32_t)num_slots);
+        CT r = scaled ? m_cc->EvalMult(ctx_Rank, 1.0 / N) : ctx_Rank;
+        input_array->SetSlots((uint32_t)num_slots);
+
+        std::vector<CT> rots_Rank(num_batch), rots_Input(num_batch);
+        for (size_t b = 0; b < num_batch; b++) rots_Rank[b] = rot.rotate(r, (int)(b * maxArraySize));
+        for (size_t b = 0; b < num_batch; b++) rots_Input[b] = rot.rotate(input_array, (int)(b * maxArraySize));
+        const uint32_t dg_i = (uint32_t)((std::log2((double)N) + 1) / 2), df_i = 2;   // (:1126-1127)
+
+        std::vector<CT> Masked(num_batch);
+        for (size_t b = 0; b < num_batch; b++) {
+            std::vector<double> subMask(num_slots, 0.0);
+            for (size_t i = 0; i < array_size; i++)
+                for (size_t j = 0; j < array_size; j++) {
+                    const double row = (double)(b * array_size + i);
+                    subMask[i * array_size + j] = scaled ? row / (double)N : row;
+                }
+            Plaintext subMaskPtx = m_cc->MakeCKKSPackedPlaintext(subMask, 1, (uint32_t)ctx_Rank->GetLevel(), nullptr, (uint32_t)num_slots);
+            CT subMasked = this->getZero()->Clone();
+            subMasked->SetSlots((uint32_t)num_slots);
+            for (size_t k = 0; k < num_batch; k++) {
+                CT rotationMask = m_cc->EvalSub(subMaskPtx, rots_Rank[k]);
+                if (kind == HybridIndicator::Mehp24)
+                    rotationMask = mehp24::utils::indicatorAdv(m_cc, rotationMask, (double)N, dg_i, df_i);
+                else if (kind == HybridIndicator::Sinc || N < 256)
+                    rotationMask = m_cc->EvalChebyshevSeriesPS(rotationMask, selectCoefficients<N>(), -1, 1);
+                else {
+                    SignConfig Cfg = SignConfig(CompositeSignConfig(3, N < 512 ? 4 : 5, 2));
+                    rotationMask = comp.indicator(m_cc, rotationMask, 0.5 / N, SignFunc::CompositeSign, Cfg);
+                }
+                subMasked = m_cc->EvalAdd(subMasked, m_cc->EvalMult(rots_Input[k], rotationMask));
+            }
+            subMasked = sumColumnsToTarget(subMasked, N / num_batch, b);
+            Masked[b] = transposeColumnTarget(subMasked, N / num_batch, b);
+        }
+        return m_cc->EvalAddMany(Masked);
+    }
+    CT sort_hybrid(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg, HybridIndicator kind = HybridIndicator::SincOrCompare) {
+        CT rank = constructRank(input_array, SignFunc, Cfg);
+        return rotationIndexCheckHybrid(rank, input_array, kind);
+    }
+    CT sort_hybrid1(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) { return sort_hybrid(input_array, SignFunc, Cfg, HybridIndicator::Mehp24); }
+    CT sort_hybrid2(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) { return sort_hybrid(input_array, SignFunc, Cfg, HybridIndicator::Sinc); }
 
     CT sort(const CT& input_array, SignFunc SignFunc, SignConfig& Cfg) override {   // (:752-774)
         CT rank = constructRank(input_array, SignFunc, Cfg);

@@ -156,3 +156,35 @@ def test_engine_direct_sort_n4_matches_committed_digest():
     assert np.allclose(eng.decrypt(out, 4), g["decrypted"], atol=1e-12)
     assert np.max(np.abs(eng.decrypt(out, 4) - np.sort(arr))) < 0.01      # tests/DirectSortTest.cpp:194
     eng.close()
+
+
+@pytest.mark.gpu
+def test_engine_rotation_tree_kat():
+    """tests/RotationTest.cpp:77-109 through RotationTree<8> on the GPU: the nine literal rows (1e-6), and every
+    result bit-identical to the oracle's un-hoisted EvalRotate chain over the same NAF steps"""
+    sf = importlib.import_module("sorting-fhe_b200")
+    k = KAT["rotation_tree"]
+    rots = [-1, -2, -4, 1, 2, 4]
+    ctx = Context(Params(12, 2, 50))
+    orc = OracleCC(ctx); orc.keygen(); orc.rot_keygen(rots)
+    eng = sf.Engine(12, 2, 50); eng.KeyGen(); eng.EvalRotateKeyGen(rots)
+    try:
+        co = orc.encrypt(orc.encode(np.array(k["input"]), slots=8))
+        ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+        # buildTree(start, end) decomposes with `end` as the wrap length (src/rotation.h:271-279) while treeRotate wraps at
+        # the slot count: build up to 8 = slots so that both agree, and check the KAT's nine rows -4..4
+        outs = sf.tree_rotate(eng, ce, 8, -4, 8, rots, "NAF")
+        assert len(outs) == 13
+        for r, out in zip(range(-4, 9), outs):
+            row = k["expected"][r + 4] if r <= 4 else np.roll(k["input"], -r)
+            assert np.allclose(eng.decrypt(out, 8), row, atol=k["tol"]), r
+            want = co
+            for step in sf.decompose(8, r, 8, rots, "NAF"):
+                want = orc.EvalRotate(want, step)
+            assert np.array_equal(out.export(), want.d), r
+        # the reference's own call, buildTree(-4, 4): steps that are multiples of 4 were dropped at build time, so -4 / 4
+        # are not in the tree and treeRotate hands back the input (:297-300, 323-327)
+        quirk = sf.tree_rotate(eng, ce, 8, -4, 4, rots, "NAF")
+        assert np.array_equal(quirk[0].export(), co.d) and np.array_equal(quirk[5].export(), outs[5].export())
+    finally:
+        eng.close()

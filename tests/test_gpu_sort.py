@@ -71,6 +71,41 @@ def test_direct_sort_bit_exact_small(n, cfg):
     eng.close()
 
 
+@pytest.mark.parametrize("variant,vid", [("hybrid1", 1), ("hybrid2", 2), ("hybrid", 0)])
+def test_hybrid_sort_bit_exact_small(variant, vid):
+    """sort_hybrid / sort_hybrid1 / sort_hybrid2 (src/sort_algo.h:1051-1065, 1214-1230, 1375-1391) for N = 4 at ring
+    2^10 with the parameters of tests/DirectSortH*Test.cpp: every limb identical to the oracle restatement, and the
+    reference tests' 0.01 gate on the decrypted output"""
+    n, cfg = 4, (3, 2, 2)
+    depth, rots = sf.hybrid_sort_params(n, variant, 1 << 10)
+    assert (depth, rots) == ({"hybrid": 24, "hybrid1": 31, "hybrid2": 24}[variant], [1, 2, 3, 4, 6, 8])
+    eng, orc = make_pair(10, depth, rots=rots)
+    x = np.random.default_rng(40 + vid).permutation(n) / n
+    co = orc.encrypt(orc.encode(x, slots=n))
+    ce = eng.encrypt(eng.encode(x, slots=n))
+    ro = algos.DirectSort(orc, n, rots).sort_hybrid(co, cfg, vid)
+    re = sf.DirectSort(eng, n, rots).sort_hybrid(ce, cfg, variant)
+    same(re, ro)
+    assert np.max(np.abs(eng.decrypt(re, n * n)[:n] - np.sort(x))) < 0.01
+    eng.close()
+
+
+def test_hybrid1_sort_n128_ring17_properties():
+    """sort_hybrid1 at the only size the reference publishes a time for (README: N = 128, 74.12 s): depth 46, the 36
+    rotation keys of tests/DirectSortH1Test.cpp:68-75, output sorted within the test's 0.01 gate"""
+    n = 128
+    depth, rots = sf.hybrid_sort_params(n, "hybrid1")
+    assert depth == 46 and len(rots) == 36 and rots[-1] == 8192 and 127 in rots and 8128 in rots
+    eng = sf.Engine(17, depth, 40, 60, seed=5)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    x = np.random.default_rng(5).permutation(n) / n
+    out = sf.DirectSort(eng, n, rots).sort_hybrid(eng.encrypt(eng.encode(x, slots=n)), (3, 3, 2), "hybrid1")
+    got = eng.decrypt(out, n * n)
+    assert np.max(np.abs(got[:n] - np.sort(x))) < 0.01
+    assert np.max(np.abs(got[n:])) < 0.01              # everything outside row 0 is masked off
+    eng.close()
+
+
 def test_rotation_composer_matches_evalrotate():
     """tests/RotationTest.cpp:63-75,111-130: composed rotations equal direct ones; +-r round trip"""
     eng, orc = make_pair(12, 2, rots=[1, 2, 4, 8, 16, 32, -4])
@@ -102,3 +137,34 @@ def test_direct_sort_n128_ring17_properties():
     assert err < 1e-3, err
     assert np.all(np.diff(got) > 0)
     eng.close()
+
+
+@pytest.mark.gpu
+def test_chebyshev_function_paths():
+    """EvalChebyshevFunction (mehp24_utils.cpp:105-163, sign.cpp:610-633): host-side coefficients + series evaluation.
+    Degree >= 5 goes through Paterson-Stockmeyer and is bit-identical to the oracle's; degree < 5 takes the linear
+    evaluator (checked against numpy's Chebyshev evaluation); NaiveDiscrete is the degree-119 step of sign.cpp:610."""
+    from numpy.polynomial import chebyshev as C
+    eng, orc = make_pair(12, 9, scale=50)
+    try:
+        x = np.array([-0.8, -0.35, -0.1, 0.15, 0.4, 0.7, 0.9, -0.6])
+        co = orc.encrypt(orc.encode(x, slots=8))
+        ce = eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+        f = lambda v: 1.0 / (1.0 + np.exp(-4.0 * v))
+        coeffs = eng.EvalChebyshevCoefficients(f, -1.0, 1.0, 27)
+        got = eng.EvalChebyshevFunction(f, ce, -1.0, 1.0, 27)
+        same(got, orc.EvalChebyshevSeriesPS(co, list(coeffs), -1.0, 1.0))
+        assert np.allclose(eng.decrypt(got, 8), f(x), atol=1e-6)
+        # shifted interval + low degree: linear evaluator
+        c4 = eng.EvalChebyshevCoefficients(lambda v: v * v * v - 0.5 * v, -2.0, 2.0, 4)
+        low = eng.EvalChebyshevSeries(eng.EvalMult(ce, 2.0), c4, -2.0, 2.0)
+        c4h = c4.copy(); c4h[0] /= 2
+        assert np.allclose(eng.decrypt(low, 8), C.chebval(x, c4h), atol=1e-7)
+        assert np.allclose(C.chebval(x, c4h), (2 * x) ** 3 - 0.5 * 2 * x, atol=1e-9)
+        step = sf.sign(eng, ce, (3, 0, 0), func="NaiveDiscrete")
+        d = eng.decrypt(step, 8)
+        assert np.all(np.abs(d - (x >= 0))[np.abs(x) > 0.1] < 0.1), d
+        with pytest.raises(RuntimeError):
+            sf.sign(eng, ce, (3, 0, 0), func="SignumPolycircuit")
+    finally:
+        eng.close()

@@ -99,7 +99,26 @@ def mehp24(n=256):
     return res
 
 
+def hybrid1(n=128):
+    """sort_hybrid1 at N = 128: the reference README's only published time (74.12 s, its CPU, 2^17 ring, depth 46)"""
+    depth, rots = sf.hybrid_sort_params(n, "hybrid1")
+    eng, stream = engine(17, depth, rots=rots, seed=5)
+    x = np.random.default_rng(n).permutation(n) / n
+    ct = eng.encrypt(eng.encode(x, slots=n))
+    s = sf.DirectSort(eng, n, rots)
+
+    def run():
+        ct.slots = n
+        return s.sort_hybrid(ct, (3, 3, 2), "hybrid1")
+    ms, out = timed(eng, stream, run)
+    res = {"ms": ms, "depth": depth, "rotation_keys": len(rots), "key_bytes": eng.info(7), "reference_published_s": 74.12,
+           "max_abs_err": float(np.max(np.abs(eng.decrypt(out, n * n)[:n] - np.sort(x))))}
+    eng.close()
+    return res
+
+
 CONFIGS = {
+    "sort_hybrid1_n128": hybrid1,
     "direct_sort_n16": lambda: direct_sort(16, (3, 2, 2)),
     "compare_sign433_full_slot": compare_full_slot,
     "direct_sort_n128": lambda: direct_sort(128, (3, 3, 2)),
