@@ -91,7 +91,12 @@ int ckks_eval_add(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_
 int ckks_eval_sub(ckks_ctx_t* ctx, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out);
 int ckks_eval_add_const(ckks_ctx_t* ctx, const ckks_ct_t* a, double c, ckks_ct_t** out);   /* comparison.cpp:19 */
 int ckks_eval_sub_const(ckks_ctx_t* ctx, const ckks_ct_t* a, double c, ckks_ct_t** out);   /* sort_algo.h:504 */
-int ckks_eval_const_sub(ckks_ctx_t* ctx, double c, const ckks_ct_t* a, ckks_ct_t** out);   /* comparison.cpp:38 */
+int ckks_eval_const_sub(ckks_ctx_t* ctx, double c, const ckks_ct_t* a, ckks_ct_t** out);   /* T = init; for i < count: T = EvalAdd(T, EvalMult(cts[i], pts[i])) -- the masked baby-step sums of vecRotsOpt and
+ * blindRotationOptN (src/sort_algo.h:336-345, 567-577) as one call.  Same limbs as the chain of calls; aligned operands
+ * take a single fused pass over HBM. */
+int ckks_eval_inner_product_plain(ckks_ctx_t* ctx, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts,
+                                  int count, ckks_ct_t** out);
+/* comparison.cpp:38 */
 int ckks_eval_negate(ckks_ctx_t* ctx, const ckks_ct_t* a, ckks_ct_t** out);
 int ckks_eval_add_many(ckks_ctx_t* ctx, const ckks_ct_t* const* cts, int count, ckks_ct_t** out); /* sort_algo.h:364 */
 /* EvalMult(ct,ct) == EvalMultAndRelinearize, EvalMult(ct,pt), EvalMult(ct,double), EvalSquare -- sign.cpp:23-56 */

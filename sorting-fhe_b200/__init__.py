@@ -266,6 +266,13 @@ class Engine:
         o = ctypes.c_void_p()
         return self._out(_L.ckks_eval_add_many(_vp(self.h), arr, len(cts), ctypes.byref(o)), o)
 
+    def EvalInnerProductPlain(self, init, cts, pts):
+        """T = init; T = EvalAdd(T, EvalMult(cts[i], pts[i])) for every i, one engine call (same limbs as the chain)"""
+        a = (ctypes.c_void_p * len(cts))(*[c.h for c in cts])
+        p = (ctypes.c_void_p * len(pts))(*[c.h for c in pts])
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_inner_product_plain(_vp(self.h), _vp(init.h), a, p, len(cts), ctypes.byref(o)), o)
+
     def EvalMult(self, a, b):
         if isinstance(b, (int, float)):
             return self._cst(_L.ckks_eval_mult_const, a, b)

@@ -279,6 +279,15 @@ int ckks_eval_const_sub(ckks_ctx_t* x, double v, const ckks_ct_t* a, ckks_ct_t**
     API_END
 }
 int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_negate(G(a))); API_END }
+int ckks_eval_inner_product_plain(ckks_ctx_t* x, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts, int count,
+                                  ckks_ct_t** out) {
+    API_BEGIN (void)C(x);
+    if (count < 0) throw std::runtime_error("EvalInnerProductPlain: negative count");
+    std::vector<const Ct*> a(count), p(count);
+    for (int i = 0; i < count; i++) { a[i] = G(cts[i]); p[i] = G(pts[i]); }
+    *out = box(eval_inner_product_plain(G(init), a.data(), p.data(), count));
+    API_END
+}
 int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
     API_BEGIN (void)C(x);
     if (count < 1) throw std::runtime_error("EvalAddMany: empty list");

@@ -154,6 +154,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
             x = mulmod(x, psi, qi); y = mulmod(y, ipsi, qi);
         }
     }
+    if (getenv("CKKS_B200_NO_PDL")) c->pdl = false;
     if (!c->dry) {
         if (!c->stream) { cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking); c->own_stream = true; }
         if (!getenv("CKKS_B200_NO_ENCODE_STREAM")) {

@@ -11,6 +11,7 @@
 #define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
 
 __global__ void k_fft_inv_stage(double2* v, int size, int len, const double2* ksi, const uint32_t* rot, int M) {
+    pdl_sync();
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= size / 2) return;
     int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
@@ -23,6 +24,7 @@ __global__ void k_fft_inv_stage(double2* v, int size, int len, const double2* ks
     v[i + j + lenh] = make_double2(__dsub_rn(p1, p2), __dadd_rn(p3, p4));
 }
 __global__ void k_fft_fwd_stage(double2* v, int size, int len, const double2* ksi, const uint32_t* rot, int M) {
+    pdl_sync();
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= size / 2) return;
     int lenh = len >> 1, lenq = len << 2, gap = M / lenq;
@@ -37,6 +39,7 @@ __global__ void k_fft_fwd_stage(double2* v, int size, int len, const double2* ks
 // out[i] = in[bitrev(i)] * scale (* sf, tracking max |.| as raw double bits when maxbits != nullptr)
 __global__ void k_bitrev_scale(double2* out, const double2* in, int size, int bits, double scale, int do_scale, double sf,
                                u64* maxbits) {
+    pdl_sync();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= size) return;
     int j = bits ? (int)(__brev((u32)i) >> (32 - bits)) : 0;
@@ -53,6 +56,7 @@ __global__ void k_bitrev_scale(double2* out, const double2* in, int size, int bi
 // v holds the scaled slot values.  Values beyond 61 bits are divided by 2^logApprox before rounding and the
 // residues multiplied back by 2^logApprox mod q (OpenFHE CKKSPackedEncoding::Encode, 64-bit native path).
 __global__ void k_encode_expand(u64* out, const double2* v, const ModInfo* mi, int n, int slots, const u64* maxbits) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
     int l = blockIdx.y, nh = n >> 1, gap = nh / slots;
@@ -88,6 +92,7 @@ __global__ void __launch_bounds__(1024)
 k_fft_inv_tail(double2* __restrict__ out, const double2* __restrict__ v, const double* __restrict__ real_in, int nvals, int from_real,
                int size, int bits, const double2* __restrict__ ksi, const uint32_t* __restrict__ rot, int M, double inv_size,
                double sf, u64* maxbits) {
+    pdl_sync();
     extern __shared__ double2 blk[];
     const int bsz = size < 2048 ? size : 2048, base = blockIdx.x * bsz;
     for (int i = threadIdx.x; i < bsz; i += blockDim.x) {
@@ -123,6 +128,7 @@ k_fft_inv_tail(double2* __restrict__ out, const double2* __restrict__ v, const d
 // one stage with len > 2048 (pairs further apart than a block); from_real as above
 __global__ void k_fft_inv_stage_big(double2* v, const double* __restrict__ real_in, int nvals, int from_real, int size, int len,
                                     const double2* ksi, const uint32_t* rot, int M) {
+    pdl_sync();
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= size / 2) return;
     const int lenh = len >> 1, lenq = len << 2, lg = 31 - __clz(lenh), gshift = (31 - __clz(M)) - (31 - __clz(lenq));
@@ -174,15 +180,15 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
         const int M = 2 * c->n;
         int from_real = 1;
         for (int len = slots; len > 2048; len >>= 1) {
-            k_fft_inv_stage_big<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(a, d_in, nvals, from_real, slots, len,
+            launch_pdl(c, k_fft_inv_stage_big, (slots / 2 + 255) / 256, 256, 0, a, d_in, nvals, from_real, slots, len,
                                                                                   (const double2*)c->d_ksi, c->d_rot, M);
             from_real = 0;
         }
         const int bsz = slots < 2048 ? slots : 2048, threads = bsz / 2 < 32 ? 32 : (bsz / 2 > 1024 ? 1024 : bsz / 2);
-        k_fft_inv_tail<<<slots / bsz, threads, (size_t)bsz * sizeof(double2), c->stream>>>(
+        launch_pdl(c, k_fft_inv_tail, slots / bsz, threads, (size_t)bsz * sizeof(double2), 
             b, a, d_in, nvals, from_real, slots, bits, (const double2*)c->d_ksi, c->d_rot, M, 1.0 / (double)slots, sf, mx);
         dim3 grid((n_c + 255) / 256, nl);
-        k_encode_expand<<<grid, 256, 0, c->stream>>>(out, b, c->d_mod, n_c, slots, mx);
+        launch_pdl(c, k_encode_expand, grid, 256, 0, out, b, c->d_mod, n_c, slots, mx);
         dev_free(c, d_in); dev_free(c, a); dev_free(c, b); dev_free(c, mx);
     }
     launch_ntt_ex(c, out, out, nl, mods_q(nl), false, nullptr, RowMap{}, RowMap{}, nullptr, lrep);
@@ -190,6 +196,7 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
 
 // centred CRT of limbs (0,1) (or limb 0 alone) -> double, then gather slots with 1/sf
 __global__ void k_crt_gather(double2* v, const u64* m, int nlimbs, const ModInfo* mi, int n, int slots, double sf, u64 q0inv_q1) {
+    pdl_sync();
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= slots) return;
     int nh = n >> 1, gap = nh / slots;
@@ -230,11 +237,11 @@ void launch_decode(Context* c, double* h_out, const u64* m, int nlimbs, double s
         while (e) { if (e & 1) r = r * bb % q1; bb = bb * bb % q1; e >>= 1; }
         q0inv = (u64)r;
     }
-    k_crt_gather<<<(slots + 255) / 256, 256, 0, c->stream>>>(a, m, nlimbs, c->d_mod, c->n, slots, sf, q0inv);
-    k_bitrev_scale<<<(slots + 255) / 256, 256, 0, c->stream>>>(b, a, slots, bits, 1.0, 0, 1.0, nullptr);
+    launch_pdl(c, k_crt_gather, (slots + 255) / 256, 256, 0, a, m, nlimbs, c->d_mod, c->n, slots, sf, q0inv);
+    launch_pdl(c, k_bitrev_scale, (slots + 255) / 256, 256, 0, b, a, slots, bits, 1.0, 0, 1.0, nullptr);
     const int M = 2 * c->n;
     for (int len = 2; len <= slots; len <<= 1)
-        k_fft_fwd_stage<<<(slots / 2 + 255) / 256, 256, 0, c->stream>>>(b, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
+        launch_pdl(c, k_fft_fwd_stage, (slots / 2 + 255) / 256, 256, 0, b, slots, len, (const double2*)c->d_ksi, c->d_rot, M);
     std::vector<double> h(2 * (size_t)slots);
     cudaMemcpyAsync(h.data(), b, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
     cudaStreamSynchronize(c->stream);

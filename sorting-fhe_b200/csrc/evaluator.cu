@@ -9,6 +9,7 @@
 // can be checked on a machine without a GPU.  Bit-level behaviour is pinned by oracle/ckks_ops.py.
 #include "engine.h"
 #include "evaluator.h"
+#include <memory>
 #include <cmath>
 #include <stdexcept>
 #include <algorithm>
@@ -341,6 +342,58 @@ Ct* eval_wsum_aligned(const std::vector<Ct*>& cts, const std::vector<double>& w)
     }
     Ct* r = ct_new(c, f->parts, f->nl, f->level, 2, f->sf * sf, slots);
     launch_wsum(c, r->d, ins.data(), sc.data(), (int)cts.size(), f->parts, f->nl);
+    return r;
+}
+
+// T = init; for i: T = EvalAdd(T, EvalMult(cts[i], pts[i]))   (vecRotsOpt / blindRotationOptN of the reference,
+// src/sort_algo.h:336-345, 567-577).  Every pair is adjusted exactly as EvalMult would (lazy rescale of the ciphertext
+// through its cached twin, lift + rescale of the plaintext), the accumulator exactly as the first EvalAdd would; when
+// the adjusted products then share level, limbs and scale -- the sorters' case -- the cnt multiplications and additions
+// are one fused pass.  Anything else runs the chain itself.  Both give the same limbs.
+static Ct* inner_product_chain(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt) {
+    init->ctx->stats.ops[{"inner_product_chain", init->nl}]++;
+    Ct* T = ct_clone(init);
+    for (int i = 0; i < cnt; i++) {
+        Ct* pr = eval_mult(cts[i], pts[i]);
+        Ct* nx = eval_add(T, pr, 1);
+        ct_free(pr); ct_free(T); T = nx;
+    }
+    return T;
+}
+Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt) {
+    Context* c = init->ctx;
+    bool ok = cnt >= 1 && cnt <= IP_MAX && init->parts == 2 && init->lrep == 0;
+    for (int i = 0; i < cnt && ok; i++) ok = cts[i]->parts == 2 && pts[i]->parts == 1 && cts[i]->lrep == 0;
+    if (!ok) return inner_product_chain(init, cts, pts, cnt);
+    std::vector<std::unique_ptr<Opnd>> X(cnt), Y(cnt);
+    for (int i = 0; i < cnt; i++) {
+        X[i].reset(new Opnd(cts[i])); Y[i].reset(new Opnd(pts[i]));
+        adjust_to_one(*X[i], *Y[i]);
+    }
+    const Ct* f = X[0]->v;
+    const int nl = f->nl, L = f->level;
+    const double psf = f->sf * Y[0]->v->sf;
+    for (int i = 0; i < cnt && ok; i++) {
+        const Ct *a = X[i]->v, *p = Y[i]->v;
+        ok = a->nl == nl && a->level == L && p->nl == nl && p->level == L && a->deg + p->deg == 2 && a->sf * p->sf == psf && nl <= 64;
+    }
+    // the accumulator must be the operand the first EvalAdd adjusts (it is the shallower one in the sorters)
+    ok = ok && (init->level < L || (init->level == L && init->deg <= 2));
+    if (!ok) return inner_product_chain(init, cts, pts, cnt);
+    Ct prod{c, nullptr, 2, nl, L, 2, psf, 0};              // metadata of the first product; never touched by the adjustment
+    Opnd T(init), P(&prod);
+    adjust_levels_and_depth(T, P);
+    if (P.v != &prod || P.own || T.v->nl != nl || T.v->level != L || T.v->deg != 2) throw std::runtime_error("EvalInnerProductPlain: adjustment invariant broken");
+    IpArgs A; A.cnt = cnt; A.init = T.v->d;
+    int slots = init->slots;
+    for (int i = 0; i < cnt; i++) {
+        A.ct[i] = X[i]->v->d; A.pt[i] = Y[i]->v->d; A.lrep[i] = Y[i]->v->lrep;
+        slots = std::max(slots, cts[i]->slots);
+        count(c, "mult_pt", nl); count(c, "add", nl);
+    }
+    c->stats.ops[{"inner_product_fused", nl}]++;
+    Ct* r = ct_new(c, 2, nl, L, 2, T.v->sf, slots);
+    launch_ip_plain(c, r->d, A, nl);
     return r;
 }
 

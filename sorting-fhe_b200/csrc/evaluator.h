@@ -44,6 +44,7 @@ Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& w
 Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_chebyshev_series(const Ct* x, const std::vector<double>& coeffs, double a, double b);
+Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt);
 Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs);
 void long_division_chebyshev(const std::vector<double>& f, const std::vector<double>& g, std::vector<double>& q,
                              std::vector<double>& r);

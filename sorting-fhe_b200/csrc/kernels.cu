@@ -32,25 +32,28 @@ LimbMods mods_range(int lo, int hi) { LimbMods m; m.n = hi - lo; for (int i = lo
 static u64 host_shoup(u64 w, u64 q) { return (u64)((((unsigned __int128)w) << 64) / q); }
 
 __global__ void k_addsub(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int op) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
     size_t o = (size_t)row * n + x;
     out[o] = op == 0 ? add_mod(a[o], b[o], q) : sub_mod(a[o], b[o], q);
 }
 void launch_add(Context* c, u64* out, const u64* a, const u64* b, int rows, const LimbMods& m, int op) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows * c->n); k_addsub<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, op);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 24.0 * rows * c->n); launch_pdl(c, k_addsub, grid_for(c, rows), 256, 0, out, a, b, m, c->d_mod, c->n, op);
 }
 
 __global__ void k_neg(u64* out, const u64* a, LimbMods mods, const ModInfo* mi, int n) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
     size_t o = (size_t)row * n + x; out[o] = neg_mod(a[o], q);
 }
 void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n); k_neg<<<grid_for(c, rows), 256, 0, c->stream>>>(out, a, m, c->d_mod, c->n);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n); launch_pdl(c, k_neg, grid_for(c, rows), 256, 0, out, a, m, c->d_mod, c->n);
 }
 
 __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b, int lrep_b) {
+    pdl_sync();
     X2_PROLOGUE;
     int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
     size_t o = (size_t)row * n + x;
@@ -62,10 +65,11 @@ __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const
 }
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m, int lrep_b) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * (2.0 * rows_out + (double)rows_out / (1 << lrep_b)));
-    k_mul<<<grid_for2(c, rows_out), 256, 0, c->stream>>>(out, a, b, m, c->d_mod, c->n, rows_b, lrep_b);
+    launch_pdl(c, k_mul, grid_for2(c, rows_out), 256, 0, out, a, b, m, c->d_mod, c->n, rows_b, lrep_b);
 }
 
 __global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
+    pdl_sync();
     X2_PROLOGUE;
     int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
     size_t o = (size_t)row * n + x;
@@ -77,10 +81,11 @@ void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const Li
     LimbScalars s;
     for (int i = 0; i < m.n; i++) { s.v[i] = hs[i]; s.sh[i] = host_shoup(hs[i], c->moduli[m.m[i]]); }
     const int n = c->n >> lrep;
-    k_mul_scalar<<<dim3((n / 2 + 255) / 256, rows), 256, 0, c->stream>>>(out, data, m, c->d_mod, n, s);
+    launch_pdl(c, k_mul_scalar, dim3((n / 2 + 255) / 256, rows), 256, 0, out, data, m, c->d_mod, n, s);
 }
 
 __global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, int nl, LimbScalars s, int negate) {
+    pdl_sync();
     X2_PROLOGUE;
     int row = blockIdx.y, l = row % nl; u64 q = mi[l].q;
     size_t o = (size_t)row * n + x;
@@ -93,11 +98,12 @@ void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, c
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * parts * nl * c->n);
     LimbScalars s;
     for (int i = 0; i < nl; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
-    k_add_scalar<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
+    launch_pdl(c, k_add_scalar, grid_for2(c, parts * nl), 256, 0, out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
 }
 
 __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
                                int sub, int lrx, int lry) {
+    pdl_sync();
     X2_PROLOGUE;
     int row = blockIdx.y, p = row / nl; u64 q = mi[row % nl].q;
     size_t o = (size_t)row * n + x;
@@ -111,16 +117,17 @@ __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* y
 void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub, int lrx, int lry) {
     int parts = xparts > yparts ? xparts : yparts;
     KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * ((double)xparts / (1 << lrx) + (double)yparts / (1 << lry) + parts));
-    k_addsub_parts<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0, lrx, lry);
+    launch_pdl(c, k_addsub_parts, grid_for2(c, parts * nl), 256, 0, out, x, xparts, y, yparts, c->d_mod, c->n, nl, sub ? 1 : 0, lrx, lry);
 }
 
 // compact plaintext rows [rows][n >> lrep] -> full rows [rows][n]
 __global__ void k_expand_rep(u64* out, const u64* in, int n, int lrep) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     out[(size_t)blockIdx.y * n + x] = in[(size_t)blockIdx.y * (n >> lrep) + (x >> lrep)];
 }
 void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep) {
-    KL(c); ProfScope ps(c, KC_COPY, 8.0 * rows * c->n); k_expand_rep<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, lrep);
+    KL(c); ProfScope ps(c, KC_COPY, 8.0 * rows * c->n); launch_pdl(c, k_expand_rep, grid_for(c, rows), 256, 0, out, in, c->n, lrep);
 }
 
 // out[row] = sum_i in_i[row] * s_i[limb]  (EvalLinearWSum: one pass instead of cnt scalar products + cnt-1 additions)
@@ -128,6 +135,7 @@ void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep) 
 #define WSUM_MAX_PAIRS 640
 struct WsumArgs { int cnt, acc; const u64* in[WSUM_MAX_IN]; u64 pairs[WSUM_MAX_PAIRS][2]; };   // passed by value (<= 32 KB of parameters)
 __global__ void k_wsum(u64* out, const __grid_constant__ WsumArgs A, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
     X2_PROLOGUE;
     const int row = blockIdx.y, l = row % nl; const u64 q = mi[l].q;
     const size_t o = (size_t)row * n + x;
@@ -156,13 +164,42 @@ void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* hs, int
                 A.pairs[i * nl + l][0] = w; A.pairs[i * nl + l][1] = host_shoup(w, c->moduli[l]);
             }
         }
-        k_wsum<<<grid_for2(c, parts * nl), 256, 0, c->stream>>>(out, A, c->d_mod, c->n, nl);
+        launch_pdl(c, k_wsum, grid_for2(c, parts * nl), 256, 0, out, A, c->d_mod, c->n, nl);
     }
+}
+
+// out[p][l] = init[p][l] + sum_i ct_i[p][l] (.) pt_i[l]   -- the  T = EvalAdd(T, EvalMult(ct_i, pt_i))  chains of the
+// sorters' masked baby-step sums (src/sort_algo.h:336-345, 567-577) in one pass: every product goes into a 128-bit
+// accumulator (<= 16 terms of q^2 < q * 2^64 for q < 2^60), reduced once.  Modular addition and multiplication are
+// exact, so the result equals the chain's bit for bit.
+__global__ void k_ip_plain(u64* out, const __grid_constant__ IpArgs A, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
+    X2_PROLOGUE;
+    const int row = blockIdx.y, l = row % nl; const ModInfo m = mi[l];
+    const size_t o = (size_t)row * n + x;
+    const u64x2 v0 = ld2(A.init, o);
+    u64 l0 = v0.x, h0 = 0, l1 = v0.y, h1 = 0;
+    for (int i = 0; i < A.cnt; i++) {
+        const u64x2 a = ld2(A.ct[i], o);
+        u64x2 b;
+        if (A.lrep[i] == 0) b = ld2(A.pt[i], (size_t)l * n + x);
+        else { const u64 t = A.pt[i][(size_t)l * (n >> A.lrep[i]) + (x >> A.lrep[i])]; b = make_ulonglong2(t, t); }
+        mac128(l0, h0, a.x, b.x); mac128(l1, h1, a.y, b.y);
+    }
+    const u64 t0 = mont_reduce(l0, h0, m.q, m.qinv), t1 = mont_reduce(l1, h1, m.q, m.qinv);   // T * 2^-64
+    st2(out, o, mont_reduce(t0 * m.r2, __umul64hi(t0, m.r2), m.q, m.qinv), mont_reduce(t1 * m.r2, __umul64hi(t1, m.r2), m.q, m.qinv));
+}
+void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl) {
+    KL(c);
+    double pt = 0; for (int i = 0; i < A.cnt; i++) pt += 1.0 / (1 << A.lrep[i]);
+    ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * (2.0 * (A.cnt + 2) + pt));
+    launch_pdl(c, k_ip_plain, grid_for2(c, 2 * nl), 256, 0, out, A, c->d_mod, c->n, nl);
 }
 
 // d[row][x] <- d[row][x] mod q_limb for words < 2^64: folds a multi-GPU integer sum of residues (NCCL all-reduce of the raw
 // limbs of partial ciphertexts, at most 8 addends < 2^61) back to canonical residues
 __global__ void k_mod_reduce(u64* d, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
     X2_PROLOGUE;
     const int row = blockIdx.y; const ModInfo m = mi[row % nl];
     const size_t o = (size_t)row * n + x;
@@ -173,12 +210,13 @@ __global__ void k_mod_reduce(u64* d, const ModInfo* mi, int n, int nl) {
 }
 void launch_mod_reduce(Context* c, u64* d, int rows, int nl) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * c->n * rows);
-    k_mod_reduce<<<grid_for2(c, rows), 256, 0, c->stream>>>(d, c->d_mod, c->n, nl);
+    launch_pdl(c, k_mod_reduce, grid_for2(c, rows), 256, 0, d, c->d_mod, c->n, nl);
 }
 
 // out[row] = sum_i in_i[row]  (EvalAddMany)
 struct ManyArgs { int cnt; const u64* in[32]; };
 __global__ void k_add_many(u64* out, const ManyArgs A, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
     X2_PROLOGUE;
     const int row = blockIdx.y; const u64 q = mi[row % nl].q;
     const size_t o = (size_t)row * n + x;
@@ -190,11 +228,12 @@ void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int r
     KL(c); ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * rows * (cnt + 1));
     ManyArgs A; A.cnt = cnt;
     for (int i = 0; i < cnt; i++) A.in[i] = ins[i];
-    k_add_many<<<grid_for2(c, rows), 256, 0, c->stream>>>(out, A, c->d_mod, c->n, nl);
+    launch_pdl(c, k_add_many, grid_for2(c, rows), 256, 0, out, A, c->d_mod, c->n, nl);
 }
 
 // (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
 __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
     X2_PROLOGUE;
     int l = blockIdx.y; const ModInfo m = mi[l];
     size_t o = (size_t)l * n + x, P = (size_t)nl * n;
@@ -205,11 +244,12 @@ __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi,
     st2(d3, o + 2 * P, barrett_mul(a1.x, b1.x, m), barrett_mul(a1.y, b1.y, m));
 }
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl) {
-    KL(c); ProfScope ps(c, KC_POINTWISE, 56.0 * nl * c->n); k_tensor<<<grid_for2(c, nl), 256, 0, c->stream>>>(d3, a, b, c->d_mod, c->n, nl);
+    KL(c); ProfScope ps(c, KC_POINTWISE, 56.0 * nl * c->n); launch_pdl(c, k_tensor, grid_for2(c, nl), 256, 0, d3, a, b, c->d_mod, c->n, nl);
 }
 
 // out[p] = in[brev(idx)], j = brev(p), idx = ((2j+1)k mod 2n) >> 1  (PrecomputeAutoMap)
 __global__ void k_automorph(u64* out, const u64* in, int n, int logn, u32 k) {
+    pdl_sync();
     int p = blockIdx.x * blockDim.x + threadIdx.x; if (p >= n) return;
     size_t ro = (size_t)blockIdx.y * n;
     u32 j = __brev((u32)p) >> (32 - logn);
@@ -219,7 +259,7 @@ __global__ void k_automorph(u64* out, const u64* in, int n, int logn, u32 k) {
     out[ro + p] = in[ro + src];
 }
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k) {
-    KL(c); ProfScope ps(c, KC_AUTOMORPH, 16.0 * rows * c->n); k_automorph<<<grid_for(c, rows), 256, 0, c->stream>>>(out, in, c->n, c->log_n, k);
+    KL(c); ProfScope ps(c, KC_AUTOMORPH, 16.0 * rows * c->n); launch_pdl(c, k_automorph, grid_for(c, rows), 256, 0, out, in, c->n, c->log_n, k);
 }
 
 static u64 host_powmod(u64 a, u64 e, u64 q) {
@@ -259,14 +299,15 @@ void launch_copy_rows(Context* c, u64* dst, const u64* src, size_t words) {
 }
 
 __global__ void k_mont(u64* d, LimbMods mods, const ModInfo* mi, int n, int to) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
     size_t o = (size_t)row * n + x;
     if (to) { u64 v = d[o]; u64 lo = v * m.r2, hi = __umul64hi(v, m.r2); d[o] = mont_reduce(lo, hi, m.q, m.qinv); }
     else d[o] = mont_reduce(d[o], 0, m.q, m.qinv);
 }
-void launch_to_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); k_mont<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, 1); }
-void launch_from_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); k_mont<<<grid_for(c, rows), 256, 0, c->stream>>>(data, m, c->d_mod, c->n, 0); }
+void launch_to_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); launch_pdl(c, k_mont, grid_for(c, rows), 256, 0, data, m, c->d_mod, c->n, 1); }
+void launch_from_mont(Context* c, u64* data, int rows, const LimbMods& m) { KL(c); launch_pdl(c, k_mont, grid_for(c, rows), 256, 0, data, m, c->d_mod, c->n, 0); }
 
 // ---- counter-based sampling (spec shared with oracle/ckks_prims.c orc_hash / orc_sample) ----
 __device__ __forceinline__ u64 mix64(u64 x) {
@@ -276,6 +317,7 @@ __device__ __forceinline__ u64 hash3(u64 seed, u64 stream, u64 idx) {
     return mix64(mix64(seed + 0x9E3779B97F4A7C15ULL * (stream + 1)) ^ mix64(idx + 0xD1B54A32D192ED03ULL));
 }
 __global__ void k_sample_small(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream, int kind) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
     u64 h = hash3(seed, stream, (u64)x), r;
@@ -284,20 +326,22 @@ __global__ void k_sample_small(u64* out, LimbMods mods, const ModInfo* mi, int n
     out[(size_t)row * n + x] = r;
 }
 void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream, int kind) {
-    KL(c); k_sample_small<<<grid_for(c, rows), 256, 0, c->stream>>>(out, m, c->d_mod, c->n, c->seed, stream, kind);
+    KL(c); launch_pdl(c, k_sample_small, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, c->seed, stream, kind);
 }
 __global__ void k_sample_uniform(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y, mid = mods.m[row % mods.n]; u64 q = mi[mid].q;
     out[(size_t)row * n + x] = hash3(seed, stream, (((u64)mid + 1) << 32) + (u64)x) % q;
 }
 void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream) {
-    KL(c); k_sample_uniform<<<grid_for(c, rows), 256, 0, c->stream>>>(out, m, c->d_mod, c->n, c->seed, stream);
+    KL(c); launch_pdl(c, k_sample_uniform, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, c->seed, stream);
 }
 
 // evk part: b = -a*s_new + e (+ P*s_old on the digit's own limbs [lo,hi)); all [M][n] EVALUATION
 __global__ void k_evk_combine(u64* b, const u64* a, const u64* e, const u64* sn, const u64* so, const ModInfo* mi, int n,
                               int lo, int hi, LimbScalars pm) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; const ModInfo m = mi[row];
     size_t o = (size_t)row * n + x;
@@ -313,12 +357,13 @@ void launch_evk_combine(Context* c, u64* b, const u64* a, const u64* e, const u6
         for (int k = 0; k < c->size_p; k++) p = p * (c->moduli[c->size_q + k] % q) % q;
         pm.v[i] = (u64)p; pm.sh[i] = host_shoup((u64)p, q);
     }
-    k_evk_combine<<<grid_for(c, c->M()), 256, 0, c->stream>>>(b, a, e, s_new, s_old, c->d_mod, c->n, lo, hi, pm);
+    launch_pdl(c, k_evk_combine, grid_for(c, c->M()), 256, 0, b, a, e, s_new, s_old, c->d_mod, c->n, lo, hi, pm);
 }
 
 // Encrypt: c0 = b*v + e0 + m, c1 = a*v + e1 ; pk = [2][sizeQ][n]
 __global__ void k_encrypt(u64* out, const u64* pt, const u64* pk, const u64* v, const u64* e0, const u64* e1,
                           const ModInfo* mi, int n, int nl, int size_q) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int l = blockIdx.y; const ModInfo m = mi[l];
     size_t o = (size_t)l * n + x;
@@ -327,11 +372,12 @@ __global__ void k_encrypt(u64* out, const u64* pt, const u64* pk, const u64* v, 
     out[(size_t)nl * n + o] = add_mod(barrett_mul(pk[(size_t)size_q * n + o], vv, m), e1[o], m.q);
 }
 void launch_encrypt_combine(Context* c, u64* out, const u64* pt, const u64* v, const u64* e0, const u64* e1, int nl) {
-    KL(c); k_encrypt<<<grid_for(c, nl), 256, 0, c->stream>>>(out, pt, c->d_pk, v, e0, e1, c->d_mod, c->n, nl, c->size_q);
+    KL(c); launch_pdl(c, k_encrypt, grid_for(c, nl), 256, 0, out, pt, c->d_pk, v, e0, e1, c->d_mod, c->n, nl, c->size_q);
 }
 
 // Decrypt core on the first `use` limbs: out = c0 + c1*s (+ c2*s^2)
 __global__ void k_decrypt(u64* out, const u64* d, const u64* s, const ModInfo* mi, int n, int nl, int parts) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int l = blockIdx.y; const ModInfo m = mi[l];
     size_t o = (size_t)l * n + x, P = (size_t)nl * n;
@@ -341,5 +387,5 @@ __global__ void k_decrypt(u64* out, const u64* d, const u64* s, const ModInfo* m
     out[o] = r;
 }
 void launch_decrypt_combine(Context* c, u64* out, const Ct* ct, int use) {
-    KL(c); k_decrypt<<<grid_for(c, use), 256, 0, c->stream>>>(out, ct->d, c->d_secret, c->d_mod, c->n, ct->nl, ct->parts);
+    KL(c); launch_pdl(c, k_decrypt, grid_for(c, use), 256, 0, out, ct->d, c->d_secret, c->d_mod, c->n, ct->nl, ct->parts);
 }

@@ -18,6 +18,7 @@
 // Up to 4 groups per launch: the digits of a ModUp, or the two polynomials of a ModDown.
 __global__ void __launch_bounds__(256)
 k_conv_batch(u64* __restrict__ out, const u64* __restrict__ in, const ConvBatch B, const ModInfo* __restrict__ mi, int n, int ysplit) {
+    pdl_sync();
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
     const int gi = blockIdx.y / ysplit, part = blockIdx.y % ysplit;
@@ -39,7 +40,7 @@ void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) 
     ProfScope ps(c, KC_BASECONV, 8.0 * c->n * rows);
     const int ysplit = 4;
     dim3 grid((c->n + 255) / 256, B.ng * ysplit);
-    k_conv_batch<<<grid, 256, 0, c->stream>>>(out, in, B, c->d_mod, c->n, ysplit);
+    launch_pdl(c, k_conv_batch, grid, 256, 0, out, in, B, c->d_mod, c->n, ysplit);
 }
 
 // acc[h][e][x] = sum_j dig_j[e][x] * key[j][h][mod(e)][x]; dig_j[e] is the source polynomial row e
@@ -48,6 +49,7 @@ struct DigitMap { int lo[4], hi[4], base[4]; };   // base: first row of digit j'
 __global__ void __launch_bounds__(256)
 k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __restrict__ conv, const u64* __restrict__ key,
            DigitMap dm, int nparts, int nl, int size_q, int size_p, int M, const ModInfo* __restrict__ mi, int n) {
+    pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
     const int e = blockIdx.y, next = nl + size_p;
@@ -77,7 +79,7 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
         if (j < t.nparts) b += t.modup[j].nout;
     }
     dim3 grid((c->n + 255) / 256, t.nl + c->size_p);
-    k_ks_inner<<<grid, 256, 0, c->stream>>>(acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
+    launch_pdl(c, k_ks_inner, grid, 256, 0, acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
 }
 
 // ApproxModDown epilogue for both polynomials h = 0,1 of a key switch:
@@ -86,6 +88,7 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
 // of OpenFHE's PrecomputeAutoMap): out[p] = value[src(p)].
 __global__ void k_moddown_final(u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, const u64* pinv,
                                 const u64* pinv_sh, const ModInfo* mi, int n, int logn, int nl, int next, u32 auto_k) {
+    pdl_sync();
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int h = blockIdx.y / nl, i = blockIdx.y % nl;
@@ -107,6 +110,6 @@ void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv,
     KL(c);
     ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (6 + (add0 ? 1 : 0) + (add1 ? 1 : 0)));
     dim3 grid((c->n + 255) / 256, 2 * nl);
-    k_moddown_final<<<grid, 256, 0, c->stream>>>(out, acc, conv, add0, add1, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, nl,
+    launch_pdl(c, k_moddown_final, grid, 256, 0, out, acc, conv, add0, add1, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, nl,
                                                  nl + c->size_p, auto_k);
 }

@@ -448,6 +448,7 @@ template <bool INV, int LOGN_C, int PASS_C>
 __global__ void __launch_bounds__(256, 4)
 ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ LimbMods mods, int total,
            int tpr_log) {
+    pdl_sync();
     extern __shared__ u64 sm[];
     const int id = blockIdx.x;
     if (id >= total) return;
@@ -464,7 +465,7 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
 
 template <bool INV, int LOGN_C, int PASS_C>
 static void launch_one(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
-    ntt_kernel<INV, LOGN_C, PASS_C><<<total, threads, smem, c->stream>>>(A, S, m, total, tpr_log);
+    launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C>, total, threads, smem, A, S, m, total, tpr_log);
 }
 template <bool INV, int PASS_C>
 static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {

@@ -204,6 +204,18 @@ class CryptoContextImpl {
         ckks_ct_t* o = nullptr; ckks_check(ckks_eval_add_many(ctx, hs.data(), (int)hs.size(), &o), "EvalAddMany");
         return wrap(o);
     }
+    // Extension (not an OpenFHE call): T = init; T = EvalAdd(T, EvalMult(cts[i], pts[i])) for every i, as one engine call
+    // (the masked sums of src/sort_algo.h:336-345, 567-577).  Same result as the chain.
+    CT EvalInnerProductPlain(const CT& init, const std::vector<CT>& cts, const std::vector<Plaintext>& pts) const {
+        if (cts.size() != pts.size()) throw std::runtime_error("EvalInnerProductPlain: size mismatch");
+        std::vector<const ckks_ct_t*> a, p;
+        for (auto& c : cts) a.push_back(c->h);
+        for (auto& q : pts) p.push_back(enc_of(q)->h);
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_eval_inner_product_plain(ctx, init->h, a.data(), p.data(), (int)a.size(), &o), "EvalInnerProductPlain");
+        CT r = wrap(o);
+        return r;
+    }
     // ---- multiplications (sign.cpp:23-56,100-156; comparison.cpp:19,35-38; sort_algo.h:358,576,723,730)
     CT EvalMult(const CT& a, const CT& b) const { return bin(ckks_eval_mult, a, b, "EvalMult"); }
     CT EvalMult(const CT& a, const Plaintext& p) const { return bin(ckks_eval_mult, a, enc_of(p), "EvalMult"); }

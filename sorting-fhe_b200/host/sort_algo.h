@@ -164,11 +164,13 @@ template <int N> class DirectSort : public SortBase<N> {
         for (int j = 0; j < num_partition / np; j++) {
             CT T = this->getZero()->Clone();
             T->SetSlots(num_slots);
+            std::vector<Plaintext> pmsk(np);
             for (int i = 0; i < np; i++) {
                 auto msk = vectorRotate(generateMaskVector(num_slots, np * j + i), -is * num_partition - j * np);
-                auto pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, 0, nullptr, num_slots);
-                T = m_cc->EvalAdd(T, m_cc->EvalMult(preRotatedArrays[i], pmsk));
+                pmsk[i] = m_cc->MakeCKKSPackedPlaintext(msk, 1, 0, nullptr, num_slots);
             }
+            // T = EvalAdd(T, EvalMult(preRotatedArrays[i], pmsk[i])) for every i (:343-344), as one engine call
+            T = m_cc->EvalInnerProductPlain(T, std::vector<CT>(preRotatedArrays.begin(), preRotatedArrays.begin() + np), pmsk);
             outer[j] = rot.rotate(T, is * num_partition + j * np);
         }
         return m_cc->EvalAddMany(outer);
@@ -215,11 +217,12 @@ template <int N> class DirectSort : public SortBase<N> {
         CT result = this->getZero()->Clone();
         for (int i = 0; i < (num_slots / N) / np; i++) {
             CT tmp = this->getZero()->Clone();
+            std::vector<Plaintext> pmsk(np);
             for (int j = 0; j < np; j++) {
                 auto msk = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j);
-                Plaintext pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)masked_inputs[j]->GetLevel(), nullptr, num_slots);
-                m_cc->EvalAddInPlace(tmp, m_cc->EvalMult(masked_inputs[j], pmsk));
+                pmsk[j] = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)masked_inputs[j]->GetLevel(), nullptr, num_slots);
             }
+            tmp = m_cc->EvalInnerProductPlain(tmp, std::vector<CT>(masked_inputs.begin(), masked_inputs.begin() + np), pmsk);   // (:575-576)
             tmp = rot.rotate(tmp, ib * num_partition + i * np);
             m_cc->EvalAddInPlace(result, tmp);
         }

@@ -159,3 +159,34 @@ def test_compact_plaintext_ops_bit_exact(pair12):
             same(eng.EvalSub(pe, ce), orc.EvalSub(po, co))
             assert np.allclose(eng.decrypt(eng.encrypt(pe), slots)[:4], v[:4], atol=1e-6)
             assert np.allclose(eng.decrypt(pe, slots)[:4], v[:4], atol=1e-6)
+
+
+def test_inner_product_plain_bit_exact(pair12):
+    """ckks_eval_inner_product_plain (the masked sums of src/sort_algo.h:336-345, 567-577 as one call): the fused pass
+    and the fallback chain both equal the oracle's EvalAdd(T, EvalMult(ct, pt)) chain limb for limb"""
+    eng, orc = pair12
+    rng = np.random.default_rng(7)
+    xs = [rng.uniform(-1, 1, 8) for _ in range(3)]
+    cos = [orc.encrypt(orc.encode(x, slots=8)) for x in xs]
+    ces = [eng.import_ct(c.d, c.level, c.deg, c.sf, c.slots) for c in cos]
+    zo = orc.encrypt(orc.encode(np.zeros(8), slots=8))
+    ze = eng.import_ct(zo.d, zo.level, zo.deg, zo.sf, zo.slots)
+    for slots in (8, 64, eng.n // 2):                       # compact and full-length plaintexts
+        ms = [rng.integers(0, 2, slots).astype(np.float64) for _ in range(3)]
+        pos = [orc.MakeCKKSPackedPlaintext(m, 1, 0, None, slots) for m in ms]
+        pes = [eng.MakeCKKSPackedPlaintext(m, 1, 0, None, slots) for m in ms]
+        want = zo
+        for c, p in zip(cos, pos):
+            want = orc.EvalAdd(want, orc.EvalMult(c, p))
+        same(eng.EvalInnerProductPlain(ze, ces, pes), want)                 # aligned: fused pass (lifts the deg-1 accumulator)
+        same(eng.EvalInnerProductPlain(eng.EvalInnerProductPlain(ze, ces[:1], pes[:1]), ces[1:], pes[1:]), want)   # deg-2 accumulator
+    # operands that need adjusting (noiseScaleDeg 2 inputs) take the chain
+    sq_o = [orc.EvalMult(c, c) for c in cos]
+    sq_e = [eng.EvalMult(c, c) for c in ces]
+    ms = [rng.integers(0, 2, 8).astype(np.float64) for _ in range(3)]
+    pos = [orc.MakeCKKSPackedPlaintext(m, 1, 0, None, 8) for m in ms]
+    pes = [eng.MakeCKKSPackedPlaintext(m, 1, 0, None, 8) for m in ms]
+    want = zo
+    for c, p in zip(sq_o, pos):
+        want = orc.EvalAdd(want, orc.EvalMult(c, p))
+    same(eng.EvalInnerProductPlain(ze, sq_e, pes), want)
