@@ -199,6 +199,14 @@ static void fill_conv(Context* c, ConvTables& t, const std::vector<int>& in_ids,
             hatmod[(size_t)i * t.nout + j] = (u64)(((u128)hm << 64) % tj);   // Montgomery form
         }
     }
+    {   // k_conv_split: digit (< 2^20) x half (< 2^32, < 2^28) products, at most 12 per 64-bit column; all moduli < 2^60
+        bool ok = t.nin <= 12;
+        for (int id : in_ids) ok = ok && (c->moduli[id] >> 60) == 0;
+        for (int id : out_ids) ok = ok && (c->moduli[id] >> 60) == 0;
+        t.split_ok = ok;
+    }
+    t.wide = 0;
+    for (int i = 0; i < t.nin && i < 32; i++) if (c->moduli[in_ids[i]] >> 40) t.wide |= 1u << i;
     for (int j = 0; j < t.nout; j++) t.out_ids[j] = (short)out_ids[j];
     t.d_hatinv = upload(c, hatinv); t.d_hatinv_sh = upload(c, hatinv_sh); t.d_hatmod = upload(c, hatmod);
 }

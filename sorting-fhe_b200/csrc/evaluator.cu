@@ -211,12 +211,13 @@ u64* key_switch_modup(Context* c, const u64* src, int nl) {
     for (int j = 0; j < t.nparts; j++) conv_rows += t.modup[j].nout;
     u64* conv = dev_alloc(c, words(c, conv_rows));
     {
-        ConvBatch B; B.ng = t.nparts;
+        ConvBatch B; B.ng = t.nparts; B.split_ok = true;
+        for (int j = 0; j < t.nparts; j++) B.split_ok = B.split_ok && t.modup[j].split_ok;
         LimbMods m; m.n = 0;
         int row0 = 0;
         for (int j = 0; j < t.nparts; j++) {
             const ConvTables& ct = t.modup[j];
-            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod};
+            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod, ct.wide};
             for (int i = 0; i < ct.nout; i++) { B.out_ids[j][i] = ct.out_ids[i]; if (m.n < MAX_LIMBS) m.m[m.n++] = ct.out_ids[i]; }
             row0 += ct.nout;
         }
@@ -258,9 +259,9 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
     }
     u64* conv2 = dev_alloc(c, words(c, 2 * nl));
     {
-        ConvBatch B; B.ng = 2;
+        ConvBatch B; B.ng = 2; B.split_ok = t.moddown.split_ok;
         for (int h = 0; h < 2; h++) {
-            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod};
+            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod, t.moddown.wide};
             for (int i = 0; i < nl; i++) B.out_ids[h][i] = (short)i;
         }
         launch_conv_batch(c, conv2, pp, B);

@@ -9,6 +9,8 @@
 // The evaluation key stream (2 * digits * (l+K) limbs) is the irreducible HBM term; keys are
 // kept in Montgomery form so that sum_j d_j * key_j is one 128-bit accumulation + one reduction.
 #include "engine.h"
+#include <algorithm>
+#include <cstdlib>
 
 #define KL(c) (c)->stats.kernel_launches++; if ((c)->dry) return
 
@@ -33,14 +35,103 @@ k_conv_batch(u64* __restrict__ out, const u64* __restrict__ in, const ConvBatch 
         out[(size_t)(g.out_row0 + j) * n + x] = mont_reduce(lo, hi, m.q, m.qinv);
     }
 }
+// The same conversion arranged for the fma pipe, for groups of at most 12 inputs (every key switch of the sorters'
+// parameter sets: alpha = 11 limbs per digit, 8 special primes).  The constants are cut into 20-bit digits (two for a
+// 40-bit target modulus, three for a 60-bit one) and staged in shared memory; the residues of two coefficients stay in
+// registers as 32-bit halves (y0, y1 < 2^28).  Every partial product digit x half is below 2^52, so twelve of them add
+// up in a 64-bit column sum with no carry: a term costs four (six) IMAD.WIDE.U32 and nothing else, instead of a full
+// 64 x 64 -> 128 multiply-accumulate with its carry chain.  The columns are recombined once per output,
+//   total = c00 + c10 2^20 + c01 2^32 + c20 2^40 + c11 2^52 + c21 2^72,
+// which is the integer k_conv_batch accumulates; same Montgomery reduction, same result.
+__device__ __forceinline__ void add_shifted(u64& lo, u64& hi, u64 s, int sh) {   // (hi:lo) += s << sh, 0 < sh < 64
+    const u64 t = s << sh;
+    lo += t;
+    hi += (s >> (64 - sh)) + (lo < t);
+}
+__device__ __forceinline__ void madw(u64& acc, u32 a, u32 b) { asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b)); }
+template <int NI>
+__global__ void __launch_bounds__(256)
+k_conv_split(u64* __restrict__ out, const u64* __restrict__ in, const __grid_constant__ ConvBatch B, const ModInfo* __restrict__ mi, int n,
+             int ysplit) {
+    pdl_sync();
+    extern __shared__ uint4 sh_h[];                       // [jc][NI]: digits (h & 0xFFFFF, (h >> 20) & 0xFFFFF, h >> 40, -)
+    const int gi = blockIdx.y / ysplit, part = blockIdx.y - gi * ysplit;
+    const int nin = B.g[gi].nin, nout = B.g[gi].nout;
+    const int per = (nout + ysplit - 1) / ysplit, jlo = part * per, jc = min(per, nout - jlo);
+    if (jc <= 0) return;
+    const u64* __restrict__ hat = B.g[gi].hatmod;
+    for (int t = threadIdx.x; t < NI * jc; t += blockDim.x) {
+        const int jj = t / NI, i = t - jj * NI;
+        const u64 h = i < nin ? hat[(size_t)i * nout + jlo + jj] : 0;
+        sh_h[t] = make_uint4((u32)h & 0xFFFFFu, (u32)(h >> 20) & 0xFFFFFu, (u32)(h >> 40), 0u);
+    }
+    __syncthreads();
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (x >= n) return;
+    u32 a0[NI], a1[NI], b0[NI], b1[NI];
+    const u64* src = in + (size_t)B.g[gi].in_row0 * n + x;
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        ulonglong2 v = make_ulonglong2(0, 0);
+        if (i < nin) v = *reinterpret_cast<const ulonglong2*>(src + (size_t)i * n);
+        a0[i] = (u32)v.x; a1[i] = (u32)(v.x >> 32); b0[i] = (u32)v.y; b1[i] = (u32)(v.y >> 32);
+    }
+    u64* dst = out + (size_t)(B.g[gi].out_row0 + jlo) * n + x;
+    for (int jj = 0; jj < jc; jj++) {
+        const uint4* hp = sh_h + jj * NI;
+        const ModInfo m = mi[B.out_ids[gi][jlo + jj]];
+        u64 a00 = 0, a10 = 0, a01 = 0, a11 = 0, a20 = 0, a21 = 0, b00 = 0, b10 = 0, b01 = 0, b11 = 0, b20 = 0, b21 = 0;
+        if (m.bits <= 40) {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const uint4 h = hp[i];
+                madw(a00, h.x, a0[i]); madw(a10, h.y, a0[i]); madw(a01, h.x, a1[i]); madw(a11, h.y, a1[i]);
+                madw(b00, h.x, b0[i]); madw(b10, h.y, b0[i]); madw(b01, h.x, b1[i]); madw(b11, h.y, b1[i]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const uint4 h = hp[i];
+                madw(a00, h.x, a0[i]); madw(a10, h.y, a0[i]); madw(a20, h.z, a0[i]);
+                madw(a01, h.x, a1[i]); madw(a11, h.y, a1[i]); madw(a21, h.z, a1[i]);
+                madw(b00, h.x, b0[i]); madw(b10, h.y, b0[i]); madw(b20, h.z, b0[i]);
+                madw(b01, h.x, b1[i]); madw(b11, h.y, b1[i]); madw(b21, h.z, b1[i]);
+            }
+        }
+        u64 al = a00, ah = a21 << 8, bl = b00, bh = b21 << 8;
+        add_shifted(al, ah, a10, 20); add_shifted(al, ah, a01, 32); add_shifted(al, ah, a20, 40); add_shifted(al, ah, a11, 52);
+        add_shifted(bl, bh, b10, 20); add_shifted(bl, bh, b01, 32); add_shifted(bl, bh, b20, 40); add_shifted(bl, bh, b11, 52);
+        *reinterpret_cast<ulonglong2*>(dst + (size_t)jj * n) = make_ulonglong2(mont_reduce(al, ah, m.q, m.qinv), mont_reduce(bl, bh, m.q, m.qinv));
+    }
+}
+template <int NI>
+static void launch_conv_split(Context* c, dim3 grid, size_t smem, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
+    launch_pdl(c, k_conv_split<NI>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+}
 void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) {
     KL(c);
-    double rows = 0;
-    for (int i = 0; i < B.ng; i++) rows += B.g[i].nin + B.g[i].nout;
+    double rows = 0; int max_in = 0, max_out = 0;
+    for (int i = 0; i < B.ng; i++) { rows += B.g[i].nin + B.g[i].nout; max_in = std::max(max_in, B.g[i].nin); max_out = std::max(max_out, B.g[i].nout); }
     ProfScope ps(c, KC_BASECONV, 8.0 * c->n * rows);
-    const int ysplit = 4;
-    dim3 grid((c->n + 255) / 256, B.ng * ysplit);
-    launch_pdl(c, k_conv_batch, grid, 256, 0, out, in, B, c->d_mod, c->n, ysplit);
+    static const int ysplit = getenv("CKKS_B200_CONV_YSPLIT") ? atoi(getenv("CKKS_B200_CONV_YSPLIT")) : 2;
+    static const bool generic = getenv("CKKS_B200_GENERIC_CONV") != nullptr;
+    if (B.split_ok && !generic && c->n >= 512) {
+        dim3 grid((c->n / 2 + 255) / 256, B.ng * ysplit);
+        const int ni = max_in <= 2 ? 2 : max_in <= 4 ? 4 : max_in <= 6 ? 6 : max_in <= 8 ? 8 : max_in <= 10 ? 10 : max_in <= 11 ? 11 : 12;
+        const size_t smem = (size_t)ni * ((max_out + ysplit - 1) / ysplit) * sizeof(uint4);
+        switch (ni) {
+            case 2: launch_conv_split<2>(c, grid, smem, out, in, B, ysplit); break;
+            case 4: launch_conv_split<4>(c, grid, smem, out, in, B, ysplit); break;
+            case 6: launch_conv_split<6>(c, grid, smem, out, in, B, ysplit); break;
+            case 8: launch_conv_split<8>(c, grid, smem, out, in, B, ysplit); break;
+            case 10: launch_conv_split<10>(c, grid, smem, out, in, B, ysplit); break;
+            case 11: launch_conv_split<11>(c, grid, smem, out, in, B, ysplit); break;
+            default: launch_conv_split<12>(c, grid, smem, out, in, B, ysplit); break;
+        }
+    } else {
+        dim3 grid((c->n + 255) / 256, B.ng * ysplit);
+        launch_pdl(c, k_conv_batch, grid, 256, 0, out, in, B, c->d_mod, c->n, ysplit);
+    }
 }
 
 // acc[h][e][x] = sum_j dig_j[e][x] * key[j][h][mod(e)][x]; dig_j[e] is the source polynomial row e
