@@ -38,7 +38,7 @@ void context_release(Context* c) {
         if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
         cudaStreamSynchronize(c->stream);
         for (auto e : c->ev_pool) cudaEventDestroy(e);
-        cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs); cudaFree(c->d_twd); cudaFree(c->d_itwd);
+        cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs); cudaFree(c->d_twd); cudaFree(c->d_itwd); cudaFree(c->d_twb); cudaFree(c->d_itwb);
         for (auto& kv : c->ninv_pairs_rep) cudaFree(kv.second);
         cudaFree(c->d_ksi); cudaFree(c->d_rot);
         if (c->enc_pinned) cudaFreeHost(c->enc_pinned);

@@ -155,6 +155,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         }
     }
     if (getenv("CKKS_B200_NO_PDL")) c->pdl = false;
+    if (getenv("CKKS_B200_NO_ENC_OFFLOAD")) c->enc_offload = false;
     if (!c->dry) {
         if (!c->stream) { cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking); c->own_stream = true; }
         if (!getenv("CKKS_B200_NO_ENCODE_STREAM")) {
@@ -174,7 +175,18 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
             any = true;
             for (int k = 0; k < n; k++) { const size_t o = (size_t)i * n + k; twd[o] = (double)tw[2 * o]; itwd[o] = (double)itw[2 * o]; }
         }
-        if (any && !getenv("CKKS_B200_NO_FP64_NTT")) { c->d_twd = upload(c, twd); c->d_itwd = upload(c, itwd); }
+        if (any && !getenv("CKKS_B200_NO_FP64_NTT")) {
+            c->d_twd = upload(c, twd); c->d_itwd = upload(c, itwd);
+            if (n >= 64 && !getenv("CKKS_B200_NO_OT_TWIDDLES")) {   // every 4th twiddle of the last stage, packed
+                std::vector<double> b((size_t)M * (n / 8)), ib((size_t)M * (n / 8));
+                for (int i = 0; i < M; i++)
+                    for (int e = 0; e < n / 8; e++) {
+                        b[(size_t)i * (n / 8) + e] = twd[(size_t)i * n + n / 2 + 4 * e];
+                        ib[(size_t)i * (n / 8) + e] = itwd[(size_t)i * n + n / 2 + 4 * e];
+                    }
+                c->d_twb = upload(c, b); c->d_itwb = upload(c, ib);
+            }
+        }
     }
     // special FFT tables (same expressions as oracle Context.fft_tables)
     const int Mc = 2 * n;

@@ -83,6 +83,7 @@ struct Context {
     int size_q = 0, size_p = 0, alpha = 0, num_part_q = 0;
     uint64_t seed = 1;
     bool dry = false;      // metadata-only mode: no device allocations, no kernel launches
+    bool enc_offload = true;   // plaintext level / scale adjustments run on the encode stream (CKKS_B200_NO_ENC_OFFLOAD=1 turns it off)
     bool pdl = true;       // programmatic dependent launch on the engine's kernels (CKKS_B200_NO_PDL=1 turns it off)
     std::vector<u64> moduli, psi;           // Q then P
     std::vector<double> sf_real, sf_big;
@@ -90,6 +91,7 @@ struct Context {
     ModInfo* d_mod = nullptr;               // [M]
     std::vector<ModInfo> h_mod;
     u64 *d_tw = nullptr, *d_itw = nullptr;   // [M][n] (w, Shoup companion) pairs: psi / psi^-1 powers, bit-reversed
+    double *d_twb = nullptr, *d_itwb = nullptr;   // [M][n/8] base twiddles W[n/2 + 4e] of the last stage (ntt.cu, on-the-fly twiddles)
     double *d_twd = nullptr, *d_itwd = nullptr;   // [M][n] the same twiddles as doubles (moduli <= 44 bits; FP64 butterflies)
     u64* d_ninv_pairs = nullptr;             // [M] (n^-1, Shoup companion): default final factor of the inverse NTT
     std::map<int, u64*> ninv_pairs_rep;      // lrep -> [M] ((n >> lrep)^-1, Shoup) for transforms of compact plaintexts
@@ -132,6 +134,12 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
     mutable cudaEvent_t ready = nullptr;   // recorded on the encode stream; the first consumer makes the main stream wait on it
     mutable u64* modup = nullptr; // cached ModUp of c1 (owned): shared by all rotations of this ciphertext (hoisting)
+    // Plaintexts are encoded on the encode stream, and the level / scale adjustments a multiplication applies to them
+    // (lift, rescale, level drop -- OpenFHE's plaintext morphing) stay there too: enc_home marks data whose producer is
+    // ordered on that stream; enc_reader is recorded after the last encode-stream kernel that READS this buffer, so
+    // that it is not released (on the main stream) under it.
+    bool enc_home = false;
+    mutable cudaEvent_t enc_reader = nullptr;
     // Plaintexts only: log2 of the replication factor.  A plaintext with s slots is G(X^gap), gap = n / (2 s), so its
     // EVALUATION form is the (n / gap)-point transform of G with every value repeated gap times in a row
     // (ntt.cu).  Such a plaintext is stored compact, [limb][n >> lrep], and element x of the full form is d[x >> lrep].

@@ -43,10 +43,45 @@ static void drop_twin(const Ct* a) {
     if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); }
     if (a->modup) { dev_free(a->ctx, a->modup); a->modup = nullptr; }
 }
+static void wait_enc_reader(const Ct* a) {
+    if (!a->enc_reader) return;
+    Context* c = a->ctx;
+    cudaStreamWaitEvent(c->stream, a->enc_reader, 0);
+    c->ev_pool.push_back(a->enc_reader);
+    a->enc_reader = nullptr;
+}
+static cudaEvent_t enc_event(Context* c) {
+    cudaEvent_t ev;
+    if (!c->ev_pool.empty()) { ev = c->ev_pool.back(); c->ev_pool.pop_back(); }
+    else cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    cudaEventRecord(ev, c->enc_stream);
+    return ev;
+}
+// true when an out-of-place op on plaintext `a` can be queued on the encode stream (its input is ordered there)
+static bool enc_offload(const Ct* a) {
+    Context* c = a->ctx;
+    return a->parts == 1 && a->enc_home && c->enc_stream && !c->dry && c->stream != c->enc_stream && c->enc_offload;
+}
+// run fn (allocation + launches on c->stream) on the encode stream; the result carries its completion event, the source
+// remembers the reader
+template <class F> static Ct* on_enc_stream(const Ct* src, F&& fn) {
+    Context* c = src->ctx;
+    cudaStream_t main = c->stream;
+    c->stream = c->enc_stream;
+    Ct* r = nullptr;
+    try { r = fn(); } catch (...) { c->stream = main; throw; }
+    r->enc_home = true;
+    r->ready = enc_event(c);
+    if (src->enc_reader) c->ev_pool.push_back(src->enc_reader);   // an older reader on the same stream is subsumed
+    src->enc_reader = enc_event(c);
+    c->stream = main;
+    return r;
+}
 void ct_free(Ct* a) {
     if (!a) return;
     Context* c = a->ctx;
     ct_wait(a);                               // the buffer is released on the main stream
+    wait_enc_reader(a);
     drop_twin(a);
     dev_free(c, a->d);
     delete a;
@@ -55,9 +90,11 @@ void ct_free(Ct* a) {
 // a takes over t's buffer and metadata (t is consumed)
 static void ct_steal(Ct* a, Ct* t) {
     drop_twin(a);
+    ct_wait(a); wait_enc_reader(a);
     dev_free(a->ctx, a->d);
     a->d = t->d; a->parts = t->parts; a->nl = t->nl; a->level = t->level; a->deg = t->deg; a->sf = t->sf; a->lrep = t->lrep;
     a->resc = t->resc; t->resc = nullptr;
+    a->ready = t->ready; t->ready = nullptr; a->enc_reader = t->enc_reader; t->enc_reader = nullptr; a->enc_home = t->enc_home;
     t->d = nullptr;
     ct_free(t);
 }
@@ -68,6 +105,7 @@ static void int_residues(const Context* c, i128 v, int nl, u64* out) {
 
 // ModReduceInternal -> DropLastElementAndScale, out of place
 static Ct* rescale_new(const Ct* a) {
+    if (enc_offload(a)) return on_enc_stream(a, [&] { return rescale_new(a); });
     Context* c = a->ctx; const int nl = a->nl, parts = a->parts;
     if (nl < 2) throw std::runtime_error("rescale: no limb left to drop (multiplicative depth exhausted)");
     count(c, "rescale", nl);
@@ -96,6 +134,7 @@ struct Opnd {
 };
 
 static Ct* mult_const_new(const Ct* a, double x) {   // EvalMultCore(ct, double), out of place
+    if (enc_offload(a)) return on_enc_stream(a, [&] { return mult_const_new(a, x); });
     Context* c = a->ctx;
     const double sf = c->sf_real[a->level];
     i128 v = (i128)(x * sf + 0.5);
@@ -105,6 +144,7 @@ static Ct* mult_const_new(const Ct* a, double x) {   // EvalMultCore(ct, double)
     return r;
 }
 static Ct* level_reduce_new(const Ct* a, int levels) {
+    if (enc_offload(a)) return on_enc_stream(a, [&] { return level_reduce_new(a, levels); });
     Context* c = a->ctx; const int nl2 = a->nl - levels;
     if (nl2 < 1) throw std::runtime_error("level_reduce: not enough limbs");
     Ct* r = ct_new(c, a->parts, nl2, a->level + levels, a->deg, a->sf, a->slots, a->lrep);
@@ -309,6 +349,7 @@ Ct* eval_add(const Ct* a, const Ct* b, int sign) {
     adjust_levels_and_depth(x, y);
     if (x.v->parts == 1 && y.v->parts == 1) { op_full(x); op_full(y); }   // plaintext +- plaintext: no compact form
     const Ct *X = x.v, *Y = y.v;
+    ct_wait(X); ct_wait(Y);                               // adjusted plaintexts come from the encode stream
     const int nl = X->nl, parts = std::max(X->parts, Y->parts);
     count(c, "add", nl);
     Ct* r = ct_new(c, parts, nl, X->level, X->deg, X->sf, std::max(a->slots, b->slots));
@@ -388,6 +429,7 @@ Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* con
     IpArgs A; A.cnt = cnt; A.init = T.v->d;
     int slots = init->slots;
     for (int i = 0; i < cnt; i++) {
+        ct_wait(X[i]->v); ct_wait(Y[i]->v);
         A.ct[i] = X[i]->v->d; A.pt[i] = Y[i]->v->d; A.lrep[i] = Y[i]->v->lrep;
         slots = std::max(slots, cts[i]->slots);
         count(c, "mult_pt", nl); count(c, "add", nl);
@@ -405,6 +447,7 @@ Ct* eval_mult(const Ct* a, const Ct* b) {
     if (a == b) { if (x.v->deg == 2) op_rescale(x); y.v = x.v; }   // EvalSquare: one operand, rescaled once
     else adjust_to_one(x, y);
     const Ct *X = x.v, *Y = y.v;
+    ct_wait(X); ct_wait(Y);
     const int nl = X->nl;
     Ct* r;
     if (X->parts == 2 && Y->parts == 2) {
@@ -574,11 +617,8 @@ Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level
     try {
         pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
         launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
-        cudaEvent_t ev;
-        if (!c->ev_pool.empty()) { ev = c->ev_pool.back(); c->ev_pool.pop_back(); }
-        else cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
-        cudaEventRecord(ev, c->enc_stream);
-        pt->ready = ev;
+        pt->ready = enc_event(c);
+        pt->enc_home = true;
     } catch (...) { c->stream = main; throw; }
     c->stream = main;
     return pt;

@@ -141,25 +141,26 @@ __global__ void __launch_bounds__(256)
 k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __restrict__ conv, const u64* __restrict__ key,
            DigitMap dm, int nparts, int nl, int size_q, int size_p, int M, const ModInfo* __restrict__ mi, int n) {
     pdl_sync();
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);       // two coefficients per thread, 16-byte accesses
     if (x >= n) return;
     const int e = blockIdx.y, next = nl + size_p;
     const int mid = e < nl ? e : size_q + (e - nl);
     const ModInfo m = mi[mid];
-    u64 l0 = 0, h0 = 0, l1 = 0, h1 = 0;
+    u64 l0 = 0, h0 = 0, l1 = 0, h1 = 0, l2 = 0, h2 = 0, l3 = 0, h3 = 0;
     for (int j = 0; j < nparts; j++) {
-        u64 d;
-        if (e >= dm.lo[j] && e < dm.hi[j]) d = src[(size_t)e * n + x];
+        ulonglong2 d;
+        if (e >= dm.lo[j] && e < dm.hi[j]) d = *reinterpret_cast<const ulonglong2*>(src + (size_t)e * n + x);
         else {
             int r = e < dm.lo[j] ? e : e - (dm.hi[j] - dm.lo[j]);
-            d = conv[((size_t)dm.base[j] + r) * n + x];
+            d = *reinterpret_cast<const ulonglong2*>(conv + ((size_t)dm.base[j] + r) * n + x);
         }
         const u64* kb = key + ((size_t)(j * 2 + 0) * M + mid) * n + x;
-        mac128(l0, h0, d, kb[0]);
-        mac128(l1, h1, d, kb[(size_t)M * n]);
+        const ulonglong2 k0 = *reinterpret_cast<const ulonglong2*>(kb), k1 = *reinterpret_cast<const ulonglong2*>(kb + (size_t)M * n);
+        mac128(l0, h0, d.x, k0.x); mac128(l1, h1, d.x, k1.x);
+        mac128(l2, h2, d.y, k0.y); mac128(l3, h3, d.y, k1.y);
     }
-    acc[(size_t)e * n + x] = mont_reduce(l0, h0, m.q, m.qinv);
-    acc[((size_t)next + e) * n + x] = mont_reduce(l1, h1, m.q, m.qinv);
+    *reinterpret_cast<ulonglong2*>(acc + (size_t)e * n + x) = make_ulonglong2(mont_reduce(l0, h0, m.q, m.qinv), mont_reduce(l2, h2, m.q, m.qinv));
+    *reinterpret_cast<ulonglong2*>(acc + ((size_t)next + e) * n + x) = make_ulonglong2(mont_reduce(l1, h1, m.q, m.qinv), mont_reduce(l3, h3, m.q, m.qinv));
 }
 void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, const EvalKey& k, const KsTables& t) {
     KL(c);
@@ -169,7 +170,7 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
         dm.lo[j] = j < t.nparts ? t.dig_lo[j] : 0; dm.hi[j] = j < t.nparts ? t.dig_hi[j] : 0; dm.base[j] = b;
         if (j < t.nparts) b += t.modup[j].nout;
     }
-    dim3 grid((c->n + 255) / 256, t.nl + c->size_p);
+    dim3 grid((c->n / 2 + 255) / 256, t.nl + c->size_p);
     launch_pdl(c, k_ks_inner, grid, 256, 0, acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
 }
 
@@ -196,10 +197,31 @@ __global__ void k_moddown_final(u64* out, const u64* acc, const u64* conv, const
     if (addend) r = add_mod(r, addend[o], q);
     out[((size_t)h * nl + i) * n + p] = r;
 }
+// the same epilogue without an automorphism (relinearisation), two coefficients per thread with 16-byte accesses
+__global__ void k_moddown_final2(u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, const u64* pinv,
+                                 const u64* pinv_sh, const ModInfo* mi, int n, int nl, int next) {
+    pdl_sync();
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (x >= n) return;
+    const int h = blockIdx.y / nl, i = blockIdx.y % nl;
+    const u64 q = mi[i].q, w = pinv[i], ws = pinv_sh[i];
+    const size_t o = (size_t)i * n + x;
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(acc + (size_t)h * next * n + o);
+    const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(conv + (size_t)h * nl * n + o);
+    u64 r0 = shoup_mul(sub_mod(a.x, b.x, q), w, ws, q), r1 = shoup_mul(sub_mod(a.y, b.y, q), w, ws, q);
+    const u64* addend = h ? add1 : add0;
+    if (addend) { const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(addend + o); r0 = add_mod(r0, d.x, q); r1 = add_mod(r1, d.y, q); }
+    *reinterpret_cast<ulonglong2*>(out + ((size_t)h * nl + i) * n + x) = make_ulonglong2(r0, r1);
+}
 void launch_moddown_final(Context* c, u64* out, const u64* acc, const u64* conv, const u64* add0, const u64* add1, int nl,
                           uint32_t auto_k, const KsTables& t) {
     KL(c);
     ProfScope ps(c, KC_MODDOWN, 8.0 * c->n * nl * (6 + (add0 ? 1 : 0) + (add1 ? 1 : 0)));
+    if (!auto_k) {
+        launch_pdl(c, k_moddown_final2, dim3((c->n / 2 + 255) / 256, 2 * nl), 256, 0, out, acc, conv, add0, add1, t.d_pinv, t.d_pinv_sh, c->d_mod,
+                   c->n, nl, nl + c->size_p);
+        return;
+    }
     dim3 grid((c->n + 255) / 256, 2 * nl);
     launch_pdl(c, k_moddown_final, grid, 256, 0, out, acc, conv, add0, add1, t.d_pinv, t.d_pinv_sh, c->d_mod, c->n, c->log_n, nl,
                                                  nl + c->size_p, auto_k);

@@ -101,6 +101,7 @@ struct NttArgs {
     const ModInfo* mi;
     const tw_t* tw;          // [M][n] forward or inverse twiddle pairs
     const double* twd;       // [M][n] the same twiddles as doubles (rows of moduli <= FP_BITS bits), or nullptr
+    const double* twb;       // [M][n/8] W[n/2 + 4e]: base of the last three stages' twiddles (full-size transforms), or nullptr
     const tw_t* scale;       // INV only: final factor (n^-1 [* extra]) as Shoup pair, indexed by modulus id
     int logn, T, a;          // T = tile bits, a = logn - T stages in pass A
     int twlog;               // log2 of the twiddle table row length (ring size; >= logn, see compact plaintexts)
@@ -314,6 +315,49 @@ __device__ __forceinline__ void round8_fp(double (&r)[8], const double* __restri
         }
     }
 }
+// The last three stages of a transform (window at bit 0) use, per thread, the 1 + 2 + 4 twiddles
+//   W[m/4 + e], W[m/2 + 2e + {0,1}], W[m + 4e + {0,1,2,3}]   (m = n/2, e = element index >> 3),
+// 7/8 of all the twiddles a limb has.  With W[k] = psi^bitrev(k) they are all powers of b = W[m + 4e]:
+//   W[m + 4e + c] = b * {1, W[1], W[2], W[3]}[c],   W[m/2 + 2e + c] = b^2 * {1, W[1]}[c],   W[m/4 + e] = b^4
+// (W[1] = psi^(n/2) = sqrt(-1), W[2], W[3] the primitive 8th roots; the inverse table satisfies the same identities).
+// So the round loads one double from the packed base table and spends six more multiplications, instead of
+// streaming seven table entries per thread from L2/HBM.  The derived values are the same residues (centred instead of
+// canonical), and the final canonicalisation makes the outputs identical.
+template <bool INV>
+__device__ __forceinline__ void round8_fp_ot(double (&r)[8], const double* __restrict__ W, const double b, const double q, const double qinv) {
+    const double wi = __ldg(W + 1), we = __ldg(W + 2), we3 = __ldg(W + 3);
+    const double b2 = fp_mulmod(b, b, q, qinv), b4 = fp_mulmod(b2, b2, q, qinv);
+    const double t1[2] = {b2, fp_mulmod(b2, wi, q, qinv)};
+    const double t2[4] = {b, fp_mulmod(b, wi, q, qinv), fp_mulmod(b, we, q, qinv), fp_mulmod(b, we3, q, qinv)};
+    if (!INV) {
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const int bit = 4 >> j;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                const double w = j == 0 ? b4 : j == 1 ? t1[k >> 2] : t2[k >> 1];
+                const double T = fp_mulmod(r[k | bit], w, q, qinv);
+                const double x = r[k];
+                r[k] = __dadd_rn(x, T);
+                r[k | bit] = __dadd_rn(x, -T);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = 2; j >= 0; j--) {
+            const int bit = 4 >> j;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (k & bit) continue;
+                const double w = j == 0 ? b4 : j == 1 ? t1[k >> 2] : t2[k >> 1];
+                const double x = r[k], y = r[k | bit];
+                r[k] = __dadd_rn(x, y);
+                r[k | bit] = fp_mulmod(__dadd_rn(x, -y), w, q, qinv);
+            }
+        }
+    }
+}
 template <bool INV>
 __device__ __forceinline__ void do_round_fp(double (&r)[8], const double* W, u32 ehi, int s0, double q, double qinv, int j0, int j1) {
     if (j0 == 0 && j1 == 3) round8_fp<INV, 0, 3>(r, W, ehi, s0, q, qinv);
@@ -345,7 +389,9 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
         return strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
     };
     if (!strided) {
-        for (int sl = 3; sl < T; sl++) {   // pull this tile's twiddles (2^T - 1 doubles) into L1, one 128-byte line per prefetch
+        const bool ot = A.twb && A.twlog == logn && T >= 3;
+        if (ot && u * 16 < (1 << (T - 3))) asm volatile("prefetch.global.L1 [%0];" ::"l"(A.twb + ((size_t)mid << (A.twlog - 3)) + ((size_t)tile << (T - 3)) + u * 16));
+        for (int sl = 3; sl < (ot ? T - 3 : T); sl++) {   // pull this tile's twiddles (2^T - 1 doubles) into L1, one 128-byte line per prefetch
             const double* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
             for (int g = u * 16; g < (1 << sl); g += 16 * (1 << (T - 3)))
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
@@ -391,7 +437,10 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
         u32 ehi; int s0;
         if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = a_ - 1 - (p + 2 - cb); }
         else { ehi = (u32)(((size_t)tile << T | (size_t)L0) >> (p + 3)); s0 = logn - 1 - (p + 2); }
-        do_round_fp<INV>(r, W, ehi, s0, q, qinv, S.j0[ri], S.j1[ri]);
+        if (!strided && p == 0 && S.j0[ri] == 0 && S.j1[ri] == 3 && A.twb && A.twlog == logn)
+            round8_fp_ot<INV>(r, W, __ldg(A.twb + ((size_t)mid << (A.twlog - 3)) + ehi), q, qinv);
+        else
+            do_round_fp<INV>(r, W, ehi, s0, q, qinv, S.j0[ri], S.j1[ri]);
         if (ri + 1 < nr) {
             __syncthreads();
 #pragma unroll
@@ -513,6 +562,7 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     A.first_pass = 1;
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
     A.twd = inverse ? c->d_itwd : c->d_twd;
+    A.twb = inverse ? c->d_itwb : c->d_twb;
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
     if (!inverse) {
         A.src = src;
