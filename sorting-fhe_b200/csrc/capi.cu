@@ -354,7 +354,8 @@ int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
     API_BEGIN
     Context* c = C(x);
     std::ostringstream os;
-    os << "{\"kernel_launches\": " << c->stats.kernel_launches << ", \"ops\": [";
+    os << "{\"kernel_launches\": " << c->stats.kernel_launches << ", \"host_ns\": [" << c->stats.host_ns[0] << ", " << c->stats.host_ns[1] << ", " << c->stats.host_ns[2] << ", " << c->stats.host_ns[3]
+       << "], \"host_calls\": [" << c->stats.host_calls[0] << ", " << c->stats.host_calls[1] << ", " << c->stats.host_calls[2] << ", " << c->stats.host_calls[3] << "], \"ops\": [";
     bool first = true;
     for (auto& kv : c->stats.ops) { os << (first ? "" : ", ") << "[\"" << kv.first.first << "\", " << kv.first.second << ", " << kv.second << "]"; first = false; }
     os << "]}";

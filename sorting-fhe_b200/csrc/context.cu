@@ -48,11 +48,12 @@ static int bitlen(u64 x) { int b = 0; while (x) { b++; x >>= 1; } return b; }
 u64* dev_alloc(Context* c, size_t words) {
     if (c->dry) return nullptr;
     void* p = nullptr;
+    HostTimer ht(c, 1);
     cudaError_t e = cudaMallocAsync(&p, words * sizeof(u64), c->stream);
     if (e != cudaSuccess) throw std::runtime_error(std::string("cudaMallocAsync: ") + cudaGetErrorString(e));
     return (u64*)p;
 }
-void dev_free(Context* c, void* p) { if (p && !c->dry) cudaFreeAsync(p, c->stream); }
+void dev_free(Context* c, void* p) { if (p && !c->dry) { HostTimer ht(c, 2); cudaFreeAsync(p, c->stream); } }
 
 template <class T> static T* upload(Context* c, const std::vector<T>& h) {
     if (c->dry) return nullptr;
@@ -155,6 +156,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         }
     }
     if (getenv("CKKS_B200_NO_PDL")) c->pdl = false;
+    if (getenv("CKKS_B200_HOST_PROF")) c->host_prof = true;
     if (getenv("CKKS_B200_NO_ENC_OFFLOAD")) c->enc_offload = false;
     if (!c->dry) {
         if (!c->stream) { cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking); c->own_stream = true; }

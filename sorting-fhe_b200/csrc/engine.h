@@ -4,6 +4,7 @@
 // and keys stay in EVALUATION (bit-reversed negacyclic NTT) format, like OpenFHE's DCRTPoly.
 // Modulus index space: 0..sizeQ-1 = Q chain, sizeQ..sizeQ+sizeP-1 = special primes P.
 #pragma once
+#include <chrono>
 #include <stdexcept>
 #include <string>
 #include <cstdint>
@@ -75,7 +76,8 @@ struct Prof {
     long launches[KC_COUNT] = {0};
 };
 
-struct Stats { std::map<std::pair<std::string, int>, long> ops; long kernel_launches = 0; };
+struct Stats { std::map<std::pair<std::string, int>, long> ops; long kernel_launches = 0;
+               long host_ns[4] = {0, 0, 0, 0}, host_calls[4] = {0, 0, 0, 0}; /* host time in launch / alloc / free / other API calls (CKKS_B200_HOST_PROF=1) */ };
 
 struct Context {
     // parameters
@@ -84,6 +86,7 @@ struct Context {
     uint64_t seed = 1;
     bool dry = false;      // metadata-only mode: no device allocations, no kernel launches
     bool enc_offload = true;   // plaintext level / scale adjustments run on the encode stream (CKKS_B200_NO_ENC_OFFLOAD=1 turns it off)
+    bool host_prof = false;
     bool pdl = true;       // programmatic dependent launch on the engine's kernels (CKKS_B200_NO_PDL=1 turns it off)
     std::vector<u64> moduli, psi;           // Q then P
     std::vector<double> sf_real, sf_big;
@@ -222,6 +225,15 @@ const KsTables& get_ks_tables(Context* c, int nl);
 // writes are visible, so consecutive dependent kernels lose the drain + launch gap (about 1-2 us on each of the ~6700
 // launches of a sort) without any change to what they read or write.  A kernel launched without the attribute sees
 // both instructions as no-ops.
+struct HostTimer {   // accumulates host wall time of a CUDA API call class when CKKS_B200_HOST_PROF is set
+    Context* c; int cls; std::chrono::steady_clock::time_point t0;
+    HostTimer(Context* c_, int cls_) : c(c_), cls(cls_) { if (c->host_prof) t0 = std::chrono::steady_clock::now(); }
+    ~HostTimer() {
+        if (!c->host_prof) return;
+        c->stats.host_ns[cls] += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+        c->stats.host_calls[cls]++;
+    }
+};
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_sync() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -235,6 +247,7 @@ inline void launch_pdl(Context* c, void (*kern)(KArgs...), dim3 grid, dim3 block
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = c->pdl ? 1 : 0;
+    HostTimer ht(c, 0);
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
     if (e != cudaSuccess) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString(e));
 }

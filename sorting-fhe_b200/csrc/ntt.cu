@@ -121,7 +121,7 @@ __host__ __device__ constexpr Sched make_sched(int T, int ns, bool inverse) {
     int ct = T - 1, rem = ns;
     bool first = true;
     while (rem > 0) {
-        const int S = rem < 3 ? rem : 3;
+        const int S = (first && rem % 3) ? rem % 3 : 3;           // a short round, if any, comes first: the last round always spans 3 stages
         int p = 0, j0 = 0, j1 = 0;
         if (S == 3) { p = ct - 2; j0 = 0; j1 = 3; }
         else if (first) { p = ct - 2; j0 = 0; j1 = S; }          // short first round: top S bits of the window
