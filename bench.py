@@ -345,7 +345,7 @@ def run_b200(args):
                          "traffic": traffic_ratio * prof_ntt["bytes"] / max(prof_ntt["launches"], 1) if traffic_ratio else None,
                          "traffic_note": "DRAM bytes per average launch = algorithmic bytes per launch x %.2f, the dram read+write "
                                          "over algorithmic ratio of one ncu --set full capture of the 32-limb transform "
-                                         "(profiles/r01_ntt_traffic.json): pass B also streams the per-tile twiddles" % (traffic_ratio or 0),
+                                         "(profiles/r01_ntt_traffic.json): pass B also reads the twiddles its first rounds need (the last three stages derive theirs on the fly)" % (traffic_ratio or 0),
                          "algorithmic_bytes_per_launch": prof_ntt["bytes"] / max(prof_ntt["launches"], 1),
                          "peak_source": peak_src, "launches": prof_ntt["launches"],
                          "avg_launch_us": prof_ntt["ms"] * 1e3 / max(prof_ntt["launches"], 1),
