@@ -211,7 +211,7 @@ def run_reference(args):
         vals.append(cpu_baseline(args.n, args.log_n, cfg, trace))
     cb = min(vals, key=lambda d: d["value"])
     v = cb["value"]
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
@@ -358,15 +358,25 @@ def run_b200(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(n, log_n, cfg, trace)
-        print(json.dumps(line))
+        emit(line)
     del cts, sorter
     eng.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(obj):
+    """the ONE JSON line of the contract, on the process's original stdout"""
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
 if __name__ == "__main__":
     a = parse()
+    # libraries (NCCL's version banner, torchrun notices) must not add lines to stdout: everything but the JSON line
+    # goes to stderr for the duration of the run
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
