@@ -30,6 +30,45 @@ def three_sorter(x, comp):
     return mn, (x[0] + x[1] + x[2]) - mn - mx, mx
 
 
+def four_sorter(x, comp):
+    """x = [a, b, c, d], comp = [(a>b), (a>c), (a>d), (b>c), (b>d), (c>d)] -> ascending   (SortUtils.cpp:80-129)"""
+    lo1, hi1 = two_sorter(x[0], x[1], comp[0])
+    lo2, hi2 = two_sorter(x[2], x[3], comp[5])
+    lo1_c, hi1_c = two_sorter(comp[1], comp[3], comp[0])      # min/max(a,b) against c
+    lo1_d, hi1_d = two_sorter(comp[2], comp[4], comp[0])      # ... against d
+    hi1_lo2, hi1_hi2 = two_sorter(hi1_c, hi1_d, comp[5])      # max(a,b) against min/max(c,d)
+    lo1_lo2, lo1_hi2 = two_sorter(lo1_c, lo1_d, comp[5])
+    mx = fcn_l(hi1, hi2, hi1_hi2)
+    left = fcn_l(lo1, hi2, lo1_hi2)
+    right = fcn_l(hi1, lo2, hi1_lo2)
+    second_max = fcn_l(left, right, hi1_hi2)
+    mn = fcn_l(lo2, lo1, lo1_lo2)                             # compareMin
+    second_min = (x[0] + x[1] + x[2] + x[3]) - mn - second_max - mx
+    return mn, second_min, second_max, mx
+
+
+def five_sorter(x, comp):
+    """x = [a..e], comp = [a>b a>c a>d a>e b>c b>d b>e c>d c>e d>e] -> ascending   (SortUtils.cpp:131-200)"""
+    abc_comp = [comp[0], comp[1], comp[4]]
+    abc = three_sorter([x[0], x[1], x[2]], abc_comp)
+    de = two_sorter(x[3], x[4], comp[9])
+    vs_d = three_sorter([comp[2], comp[5], comp[7]], abc_comp)
+    vs_e = three_sorter([comp[3], comp[6], comp[8]], abc_comp)
+    M = two_sorter(vs_d[2], vs_e[2], comp[9])                 # max(abc) against min/max(d,e)
+    D = two_sorter(vs_d[1], vs_e[1], comp[9])                 # mid(abc) ...
+    m = two_sorter(vs_d[0], vs_e[0], comp[9])                 # min(abc) ...
+    s4 = fcn_l(abc[2], de[1], M[1])
+    s0 = fcn_l(de[0], abc[0], m[0])
+    left = fcn_l(abc[1], de[1], D[1])
+    right = fcn_l(abc[2], de[0], M[0])
+    s3 = fcn_l(left, right, M[1])
+    left = fcn_l(de[0], abc[1], D[0])
+    right = fcn_l(de[1], abc[0], m[1])
+    s1 = fcn_l(right, left, m[0])
+    s2 = sum(x) - s0 - s1 - s3 - s4
+    return s0, s1, s2, s3, s4
+
+
 def sort_type(k, M, stage):
     """stage -> (m, logDist, slope)   (Masking.cpp:26-47)"""
     up = (k + 1) // 2
@@ -98,7 +137,7 @@ def gen_mask(indices, index0, index1):
 
 
 def network_plain(x, k, M, compare=None, first_stage=0, last_stage=None):
-    """Sorter::sorter (Sorter.cpp:284-404) on plain doubles for k in {2, 3}: `x` has next_pow2(k^M) entries (the
+    """Sorter::sorter (Sorter.cpp:284-404) on plain doubles for k in {2, 3, 5}: `x` has next_pow2(k^M) entries (the
     ciphertext's slot count, kway_adapter.h:44), zero beyond k^M; rotations wrap at len(x).  `compare(a, b)` defaults
     to the exact (a > b) with 1/2 on ties -- the function Comparison::compare approximates."""
     n = k ** M
@@ -142,6 +181,48 @@ def network_plain(x, k, M, compare=None, first_stage=0, last_stage=None):
         lo, mid, hi = three_sorter(arr, comps)
         return lo * m3 + right(mid * m3, shift) + right(hi * m3, 2 * shift)
 
+    def size_mask(idx, sizes):
+        return pad(((idx[1] == 1) & np.isin(idx[0], sizes)).astype(float))
+
+    def assemble(parts, shift):  # slotAssemble (SortUtils.cpp:425-433)
+        out = parts[0]
+        for i in range(1, len(parts)):
+            out = out + right(parts[i], i * shift)
+        return out
+
+    def run_four(v, idx, shift, c1, c2):  # runFourSorter (:71-87) with slotMatching4 (SortUtils.cpp:239-284)
+        m4 = pad(gen_mask(idx, 4, 1))
+        comps = [m4 - left(c1, shift), c2, c1, m4 - left(c1, 2 * shift), left(c2, shift), m4 - left(c1, 3 * shift)]
+        arr = [left(v, i * shift) * m4 for i in range(4)]
+        return assemble(list(four_sorter(arr, comps)), shift)
+
+    def run_five(v, idx, shift, c1, c2):  # runFiveSorter (:89-119) with slotMatching5 (SortUtils.cpp:286-323)
+        m5 = pad(gen_mask(idx, 5, 1))
+        comps = [None] * 10
+        comps[3] = c1; comps[0] = left(c1, shift); comps[4] = left(c1, 2 * shift); comps[7] = left(c1, 3 * shift); comps[9] = left(c1, 4 * shift)
+        comps[2] = c2; comps[6] = left(c2, shift); comps[1] = left(c2, 2 * shift); comps[5] = left(c2, 3 * shift); comps[8] = left(c2, 4 * shift)
+        for i in (0, 1, 4, 5, 7, 8, 9):
+            comps[i] = m5 - comps[i]
+        arr = [left(v, i * shift) for i in range(5)]
+        return assemble([p * m5 for p in five_sorter(arr, comps)], shift)
+
+    def run_2345(v, idx, shift, c1, c2):  # run2345Sorter (:121-178) with slotMatching2345 (SortUtils.cpp:325-423)
+        m2345, m45, m345 = size_mask(idx, [2, 3, 4, 5]), size_mask(idx, [4, 5]), size_mask(idx, [3, 4, 5])
+        m3, m4, m5 = size_mask(idx, [3]), size_mask(idx, [4]), size_mask(idx, [5])
+        arr = [left(v, i * shift) for i in range(5)]
+        comps = [m2345 - left(c1, shift),
+                 c1 * m3 + (m45 - left(c2, 2 * shift) * m45),
+                 c1 * m4 + c2 * m5,
+                 c1 * m5,
+                 m345 - left(c1, 2 * shift) * m345,
+                 m45 - left(c2, 3 * shift) * m45,
+                 left(c2, shift) * m5,
+                 m45 - left(c1, 3 * shift) * m45,
+                 m5 - left(c2, 4 * shift) * m5,
+                 m5 - left(c1, 4 * shift) * m5]
+        s0, s1, s2, s3, s4 = five_sorter(arr, comps)
+        return assemble([s0 * m2345, s1 * m2345, s2 * m345, s3 * m45, s4 * m5], shift)
+
     stages = M + M * (M - 1) // 2 * ((k + 1) // 2)
     for stage in range(first_stage, stages if last_stage is None else last_stage):
         m, log_dist, slope = sort_type(k, M, stage)
@@ -149,11 +230,20 @@ def network_plain(x, k, M, compare=None, first_stage=0, last_stage=None):
         idx = gen_indices(n, k, M, m, log_dist, slope)
         rot, fix = partner(x, idx, log_dist, slope)
         comp = compare(x, rot)
-        if slope == 0:
+        if k == 5 and slope != 2:  # two partner comparisons (comparisonForSort2, :264-282)
+            rot2, _ = partner(rot, idx, log_dist, slope)
+            comp2 = compare(x, rot2)
+            if slope == 0:
+                x = run_five(x, idx, shift, comp, comp2)
+            elif slope == 3:
+                x = run_four(x, idx, shift, comp, comp2) + fix
+            else:
+                x = run_2345(x, idx, shift, comp, comp2) + fix
+        elif slope == 0:
             x = run_two(x, idx, shift, comp) if k == 2 else run_three(x, idx, shift, comp)
         elif slope == k // 2 + 1:
             x = run_two(x, idx, shift, comp) + fix
-        elif k == 3 and slope == 1:
+        elif (k == 3 and slope == 1) or (k == 5 and slope == 2):
             x = run_two(x, idx, shift, comp) + fix + run_three(x, idx, shift, comp)
         else:
             x = run_two(x, idx, shift, comp) + fix

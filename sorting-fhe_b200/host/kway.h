@@ -1,8 +1,8 @@
 // kway.h -- the k-way sorting network of HKC+21 with the reference's names (namespace kwaySort): Masking
 // (src/k-way/Masking.cpp:26-167), EvalUtils (src/k-way/EvalUtils.cpp:18-147), SortUtils (src/k-way/SortUtils.cpp:5-82,
 // 202-236), Sorter (src/k-way/Sorter.cpp:8-70,180-262,284-404) and KWayAdapter's parameter card
-// (src/kway_adapter.h:41-64).  k = 2 and k = 3 are implemented (BASELINE config 4 is k = 2); the 4-/5-sorters of
-// k = 5 are not.  checkLevelAndBoot calls cc->EvalBootstrap exactly where the reference does -- the B200 engine has
+// (src/kway_adapter.h:41-64).  k = 2, 3 and 5 (BASELINE config 4 is k = 2; k = 5 adds the 4-/5-sorters, SortUtils.cpp:80-200,
+// 239-433, Sorter.cpp:71-178, 264-282).  checkLevelAndBoot calls cc->EvalBootstrap exactly where the reference does -- the B200 engine has
 // no bootstrapping yet, so a network runs as far as the multiplicative depth allows and the call
 // throws beyond that.  Orchestration only: every cc-> call is a CUDA kernel schedule inside libckks_b200.so.
 #pragma once
@@ -158,6 +158,48 @@ class SortUtils : public EvalUtils {
         CT sum = m_cc->EvalAdd(m_cc->EvalAdd(ctxt[0], ctxt[1]), ctxt[2]);
         sorted[1] = m_cc->EvalSub(m_cc->EvalSub(sum, sorted[0]), sorted[2]);
     }
+    // ctxt = [a, b, c, d], comp = [(a>b), (a>c), (a>d), (b>c), (b>d), (c>d)] -> ascending   (:80-129)
+    void fourSorter(CT* ctxt, CT* comp, CT* sorted) {
+        CT ab[2], cd[2], abVsC[2], abVsD[2], hiVs[2], loVs[2], left, right;
+        twoSorter(ctxt[0], ctxt[1], comp[0], ab);
+        twoSorter(ctxt[2], ctxt[3], comp[5], cd);
+        twoSorter(comp[1], comp[3], comp[0], abVsC);        // min / max(a, b) against c
+        twoSorter(comp[2], comp[4], comp[0], abVsD);        // ... against d
+        twoSorter(abVsC[1], abVsD[1], comp[5], hiVs);       // max(a, b) against min / max(c, d)
+        twoSorter(abVsC[0], abVsD[0], comp[5], loVs);       // min(a, b) against min / max(c, d)
+        compareMax(ab[1], cd[1], hiVs[1], sorted[3]);
+        compareMax(ab[0], cd[1], loVs[1], left);
+        compareMax(ab[1], cd[0], hiVs[0], right);
+        compareMax(left, right, hiVs[1], sorted[2]);
+        compareMin(ab[0], cd[0], loVs[0], sorted[0]);
+        sorted[1] = ctxt[0];
+        for (int i = 1; i < 4; i++) sorted[1] = m_cc->EvalAdd(sorted[1], ctxt[i]);
+        for (int i = 0; i < 4; i++) if (i != 1) sorted[1] = m_cc->EvalSub(sorted[1], sorted[i]);
+    }
+    // ctxt = [a..e], comp = [a>b a>c a>d a>e b>c b>d b>e c>d c>e d>e] -> ascending   (:131-200)
+    void fiveSorter(CT* ctxt, CT* comp, CT* sorted) {
+        CT abc[3] = {ctxt[0], ctxt[1], ctxt[2]}, abcComp[3] = {comp[0], comp[1], comp[4]}, abcSorted[3], de[2];
+        threeSorter(abc, abcComp, abcSorted);
+        twoSorter(ctxt[3], ctxt[4], comp[9], de);
+        CT vsD[3] = {comp[2], comp[5], comp[7]}, vsE[3] = {comp[3], comp[6], comp[8]}, vsDs[3], vsEs[3];
+        threeSorter(vsD, abcComp, vsDs);
+        threeSorter(vsE, abcComp, vsEs);
+        CT hi[2], mid[2], lo[2], left, right;
+        twoSorter(vsDs[2], vsEs[2], comp[9], hi);           // max(a,b,c) against min / max(d, e)
+        twoSorter(vsDs[1], vsEs[1], comp[9], mid);
+        twoSorter(vsDs[0], vsEs[0], comp[9], lo);
+        compareMax(abcSorted[2], de[1], hi[1], sorted[4]);
+        compareMin(abcSorted[0], de[0], lo[0], sorted[0]);
+        compareMax(abcSorted[1], de[1], mid[1], left);
+        compareMax(abcSorted[2], de[0], hi[0], right);
+        compareMax(left, right, hi[1], sorted[3]);
+        compareMin(abcSorted[1], de[0], mid[0], left);
+        compareMin(abcSorted[0], de[1], lo[1], right);
+        compareMin(left, right, lo[0], sorted[1]);
+        sorted[2] = ctxt[0];
+        for (int i = 1; i < 5; i++) sorted[2] = m_cc->EvalAdd(sorted[2], ctxt[i]);
+        for (int i = 0; i < 5; i++) if (i != 2) sorted[2] = m_cc->EvalSub(sorted[2], sorted[i]);
+    }
     void slotMatching2(CT& ctxt, CT& comp, std::vector<std::vector<int>>&, long shift, CT* out, CT& comp_out) {   // :202-210
         out[0] = ctxt;
         leftRotate(ctxt, shift, out[1]);
@@ -173,6 +215,84 @@ class SortUtils : public EvalUtils {
         leftRotate(comp, 2 * shift, comp_out[2]);
         flipCtxt(comp_out[0], mask3Plain);
         flipCtxt(comp_out[2], mask3Plain);
+    }
+    // 4 elements spaced `shift` apart and their six comparison bits out of the two partner comparisons (:239-284; the
+    // masked products the reference computes first at :259-264 are overwritten at :267-273 and left out here)
+    void slotMatching4(CT& ctxt, CT& comp1, CT& comp2, std::vector<std::vector<int>>& indices, long shift, CT* arr, CT* comp_arr) {
+        std::vector<double> m;
+        genMask(indices, 4, 1, m);
+        Plaintext mask = m_cc->MakeCKKSPackedPlaintext(m);
+        comp_arr[2] = comp1;
+        leftRotate(comp1, 1 * shift, comp_arr[0]);
+        leftRotate(comp1, 2 * shift, comp_arr[3]);
+        leftRotate(comp1, 3 * shift, comp_arr[5]);
+        comp_arr[1] = comp2;
+        leftRotate(comp2, 1 * shift, comp_arr[4]);
+        flipCtxt(comp_arr[0], mask);
+        flipCtxt(comp_arr[3], mask);
+        flipCtxt(comp_arr[5], mask);
+        for (int i = 0; i < 4; i++) {
+            leftRotate(ctxt, i * shift, arr[i]);
+            arr[i] = m_cc->EvalMult(arr[i], mask);
+        }
+    }
+    void slotMatching5(CT& ctxt, CT& comp1, CT& comp2, std::vector<std::vector<int>>& indices, long shift, CT* arr, CT* comp_arr) {   // :286-323
+        std::vector<double> m;
+        genMask(indices, 5, 1, m);
+        Plaintext mask = m_cc->MakeCKKSPackedPlaintext(m);
+        for (int i = 0; i < 5; i++) leftRotate(ctxt, i * shift, arr[i]);
+        comp_arr[3] = comp1;
+        leftRotate(comp1, shift, comp_arr[0]);
+        leftRotate(comp1, 2 * shift, comp_arr[4]);
+        leftRotate(comp1, 3 * shift, comp_arr[7]);
+        leftRotate(comp1, 4 * shift, comp_arr[9]);
+        comp_arr[2] = comp2;
+        leftRotate(comp2, shift, comp_arr[6]);
+        leftRotate(comp2, 2 * shift, comp_arr[1]);
+        leftRotate(comp2, 3 * shift, comp_arr[5]);
+        leftRotate(comp2, 4 * shift, comp_arr[8]);
+        for (int i : {0, 1, 4, 5, 7, 8, 9}) flipCtxt(comp_arr[i], mask);
+    }
+    // role masks of a mixed stage: bit s of `sizes` selects the groups of size s (first position)
+    Plaintext sizeMask(const std::vector<std::vector<int>>& indices, unsigned sizes) {
+        std::vector<double> m((size_t)m_numSlots, 0.0);
+        for (long i = 0; i < m_numSlots; i++)
+            if (indices[1][i] == 1 && indices[0][i] >= 2 && indices[0][i] <= 5 && ((sizes >> indices[0][i]) & 1)) m[(size_t)i] = 1.0;
+        return m_cc->MakeCKKSPackedPlaintext(m);
+    }
+    // groups of 2, 3, 4 and 5 elements in the same stage, all fed to the 5-sorter (:325-423)
+    void slotMatching2345(CT& ctxt, CT& comp1, CT& comp2, std::vector<std::vector<int>>& indices, long shift, CT* arr, CT* comp_arr) {
+        for (int i = 0; i < 5; i++) leftRotate(ctxt, i * shift, arr[i]);
+        Plaintext m2345 = sizeMask(indices, 0x3C), m45 = sizeMask(indices, 0x30), m345 = sizeMask(indices, 0x38),
+                  m3 = sizeMask(indices, 0x08), m4 = sizeMask(indices, 0x10), m5 = sizeMask(indices, 0x20);
+        leftRotate(comp1, shift, comp_arr[0]);                                   // a > b
+        flipCtxt(comp_arr[0], m2345);
+        CT tmp = m_cc->EvalMult(comp1, m3), tmp2 = comp2->Clone();               // a > c
+        leftRotate(tmp2, 2 * shift, tmp2);
+        tmp2 = m_cc->EvalMult(tmp2, m45);
+        flipCtxt(tmp2, m45);
+        comp_arr[1] = m_cc->EvalAdd(tmp, tmp2);
+        comp_arr[2] = m_cc->EvalAdd(m_cc->EvalMult(comp1, m4), m_cc->EvalMult(comp2, m5));   // a > d
+        comp_arr[3] = m_cc->EvalMult(comp1, m5);                                 // a > e
+        auto rotMaskFlip = [&](CT& src, long r, Plaintext& mask, bool flip, CT& out) {
+            leftRotate(src, r, out);
+            out = m_cc->EvalMult(out, mask);
+            if (flip) flipCtxt(out, mask);
+        };
+        rotMaskFlip(comp1, 2 * shift, m345, true, comp_arr[4]);                  // b > c
+        rotMaskFlip(comp2, 3 * shift, m45, true, comp_arr[5]);                   // b > d
+        rotMaskFlip(comp2, shift, m5, false, comp_arr[6]);                       // b > e
+        rotMaskFlip(comp1, 3 * shift, m45, true, comp_arr[7]);                   // c > d
+        rotMaskFlip(comp2, 4 * shift, m5, true, comp_arr[8]);                    // c > e
+        rotMaskFlip(comp1, 4 * shift, m5, true, comp_arr[9]);                    // d > e
+    }
+    void slotAssemble(CT* sorted, long num, long shift, CT& out) {   // :425-433
+        out = sorted[0];
+        for (long i = 1; i < num; i++) {
+            CT rotated;
+            rightRotate(sorted[i], i * shift, rotated);
+            out = m_cc->EvalAdd(out, rotated);
+        }
     }
 };
 
@@ -211,6 +331,33 @@ class Sorter : public SortUtils {
         rightRotate(sorted[1], shift, r1);
         rightRotate(sorted[2], 2 * shift, r2);
         ctxt_out = m_cc->EvalAdd(m_cc->EvalAdd(sorted[0], r1), r2);
+    }
+
+    void runFourSorter(CT& ctxt, std::vector<std::vector<int>>& indices, long shift, CT& comp1, CT& comp2, CT& ctxt_out) {   // :71-87
+        CT arr[4], comp_arr[6], sorted[4];
+        slotMatching4(ctxt, comp1, comp2, indices, shift, arr, comp_arr);
+        fourSorter(arr, comp_arr, sorted);
+        slotAssemble(sorted, 4, shift, ctxt_out);
+    }
+    void runFiveSorter(CT& ctxt, std::vector<std::vector<int>>& indices, long shift, CT& comp1, CT& comp2, CT& ctxt_out) {   // :89-119
+        Plaintext mask5Plain = roleMask(indices, 5, 1);
+        CT arr[5], comp_arr[10], sorted[5];
+        slotMatching5(ctxt, comp1, comp2, indices, shift, arr, comp_arr);
+        fiveSorter(arr, comp_arr, sorted);
+        for (int i = 0; i < 5; i++) sorted[i] = m_cc->EvalMult(sorted[i], mask5Plain);
+        slotAssemble(sorted, 5, shift, ctxt_out);
+    }
+    void run2345Sorter(CT& ctxt, std::vector<std::vector<int>>& indices, long shift, CT& comp1, CT& comp2, CT& ctxt_out) {   // :121-178
+        Plaintext m2345 = sizeMask(indices, 0x3C), m45 = sizeMask(indices, 0x30), m345 = sizeMask(indices, 0x38), m5 = sizeMask(indices, 0x20);
+        CT arr[5], comp_arr[10], sorted[5];
+        slotMatching2345(ctxt, comp1, comp2, indices, shift, arr, comp_arr);
+        fiveSorter(arr, comp_arr, sorted);
+        sorted[0] = m_cc->EvalMult(sorted[0], m2345);
+        sorted[1] = m_cc->EvalMult(sorted[1], m2345);
+        sorted[2] = m_cc->EvalMult(sorted[2], m345);
+        sorted[3] = m_cc->EvalMult(sorted[3], m45);
+        sorted[4] = m_cc->EvalMult(sorted[4], m5);
+        slotAssemble(sorted, 5, shift, ctxt_out);
     }
 
     // partner alignment: ctxt_rot[i] = the element slot i is compared with; ctxt_fix = the slots that sit this stage
@@ -252,6 +399,16 @@ class Sorter : public SortUtils {
         ctxt_comp = comp.compare(m_cc, ctxt->Clone(), ctxt_rot, SignFunc::CompositeSign, Cfg);
     }
 
+    // the partners one and two steps away (k = 5 groups need both)   (:264-282)
+    void comparisonForSort2(CT& ctxt, std::vector<std::vector<int>>& indices, long logDist, long slope, CT& comp1, CT& comp2,
+                            CT& ctxt_fix, SignConfig& Cfg) {
+        CT rot1, rot2, dummy;
+        rightRotateForSort(ctxt, indices, logDist, slope, rot1, ctxt_fix);
+        rightRotateForSort(rot1, indices, logDist, slope, rot2, dummy);
+        comp1 = comp.compare(m_cc, ctxt->Clone(), rot1, SignFunc::CompositeSign, Cfg);
+        comp2 = comp.compare(m_cc, ctxt->Clone(), rot2, SignFunc::CompositeSign, Cfg);
+    }
+
     int stageCount() const { return (int)(m_M + m_M * (m_M - 1) / 2 * ((m_k + 1) / 2)); }   // :298
 
     // one stage of the network, in place on ctxt (body of the loop at :300-397)
@@ -261,8 +418,20 @@ class Sorter : public SortUtils {
         { auto t = sortType((int)m_k, (int)m_M, stage); m = std::get<0>(t); logDist = std::get<1>(t); slope = std::get<2>(t); }
         const long shift = getRotateDistance(m_k, logDist, slope);
         auto indices = genIndices(m_numSlots, m_k, m_M, m, logDist, slope);
-        CT ctxt_fix, ctxt_comp1;
-        if (m_k != 2 && m_k != 3) throw std::runtime_error("kwaySort::Sorter: only k = 2 and k = 3 are implemented");
+        CT ctxt_fix, ctxt_comp1, ctxt_comp2;
+        if (m_k != 2 && m_k != 3 && m_k != 5) throw std::runtime_error("kwaySort::Sorter: k must be 2, 3 or 5");
+        if (m_k == 5 && slope != 2) {               // k = 5: two partner comparisons feed a 5-, 4- or mixed sorter (:326-366)
+            const size_t lv = slope == 5 / 2 + 1 ? 4 : 5;
+            checkLevelAndBoot(ctxt, m_level[lv], multDepth);
+            comparisonForSort2(ctxt, indices, logDist, slope, ctxt_comp1, ctxt_comp2, ctxt_fix, Cfg);
+            if (slope == 5 / 2 + 1) checkLevelAndBoot(ctxt, m_level[lv], multDepth);
+            checkLevelAndBoot2(ctxt_comp1, ctxt_comp2, m_level[lv], multDepth);
+            if (slope == 0) { runFiveSorter(ctxt, indices, shift, ctxt_comp1, ctxt_comp2, ctxt); return; }
+            if (slope == 5 / 2 + 1) runFourSorter(ctxt, indices, shift, ctxt_comp1, ctxt_comp2, ctxt);
+            else run2345Sorter(ctxt, indices, shift, ctxt_comp1, ctxt_comp2, ctxt);   // slope 1
+            ctxt = m_cc->EvalAdd(ctxt, ctxt_fix);
+            return;
+        }
         if (slope == 0) {
             checkLevelAndBoot(ctxt, m_level[(size_t)m_k], multDepth);
             comparisonForSort(ctxt, indices, logDist, slope, ctxt_comp1, ctxt_fix, Cfg);
@@ -275,7 +444,7 @@ class Sorter : public SortUtils {
             checkLevelAndBoot(ctxt_comp1, m_level[(size_t)m_k - 1], multDepth);
             runTwoSorter(ctxt, indices, shift, ctxt_comp1, ctxt);
             ctxt = m_cc->EvalAdd(ctxt, ctxt_fix);
-        } else if (m_k == 3 && slope == 1) {        // diagonals of 2 and of 3 in the same stage
+        } else if ((m_k == 3 && slope == 1) || (m_k == 5 && slope == 2)) {   // diagonals of 2 and of 3 in the same stage
             CT ctxt2, ctxt3;
             checkLevelAndBoot(ctxt, m_level[3], multDepth);
             comparisonForSort(ctxt, indices, logDist, slope, ctxt_comp1, ctxt_fix, Cfg);

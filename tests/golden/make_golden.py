@@ -100,7 +100,7 @@ def reference_kat():
     # ---- tests/k-way/SortUtilsTest.cpp (fcnL, two/three-sorter literal vectors)
     L = src("tests/k-way/SortUtilsTest.cpp")
     cases, pos = [], 1
-    for name in ("FcnL", "TwoSorter", "ThreeSorter"):
+    for name in ("FcnL", "TwoSorter", "ThreeSorter", "FourSorter", "FiveSorter"):
         try:
             t = find(L, r"TEST_F\(\w+, \w*%s\w*\)" % name)
         except KeyError:
@@ -108,9 +108,12 @@ def reference_kat():
         end = find(L, r"^}", t)
         vecs = {}
         for i in range(t, end):
-            m = re.search(r"std::vector<double> (\w+) = \{", L[i - 1])
+            m = re.search(r"std::vector<(?:std::vector<)?double>+ (\w+) = \{", L[i - 1])
             if m:
-                vecs[m.group(1)], _ = brace_list(L, i, m.group(1))
+                try:
+                    vecs[m.group(1)], _ = brace_list(L, i, m.group(1))
+                except Exception:
+                    pass                      # lists of identifiers (inputs = {input1, ...}) are not literal data
         cases.append({"test": name, "lines": "%d-%d" % (t, end), "vectors": vecs})
     out["kway_sortutils"] = {"cite": "tests/k-way/SortUtilsTest.cpp", "cases": cases, "tol": 0.1}
     # ---- src/sort_algo.h getSizeParameters

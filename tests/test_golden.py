@@ -89,7 +89,7 @@ def test_direct_sort_params_kat():
 
 
 def test_kway_kat_plain():
-    """tests/k-way/SortUtilsTest.cpp fcnL / two- / three-sorter literal vectors and MaskingTest getRotateDistance:
+    """tests/k-way/SortUtilsTest.cpp fcnL / two- / three- / four- / five-sorter literal vectors and MaskingTest getRotateDistance:
     the plaintext model of the k-way building blocks reproduces them"""
     from oracle import kway_plain
     for c in KAT["kway_sortutils"]["cases"]:
@@ -102,6 +102,13 @@ def test_kway_kat_plain():
         elif c["test"] == "ThreeSorter":
             lo, mid, hi = kway_plain.three_sorter([v["input1"], v["input2"], v["input3"]], [v["comp1"], v["comp2"], v["comp3"]])
             assert np.allclose(lo, v["expectedMin"]) and np.allclose(mid, v["expectedMid"]) and np.allclose(hi, v["expectedMax"])
+        elif c["test"] == "FourSorter":      # tests/k-way/SortUtilsTest.cpp:157-202
+            got = kway_plain.four_sorter([v["input%d" % i] for i in range(1, 5)], [v["comp%d" % i] for i in range(1, 7)])
+            assert np.allclose(np.array(got), v["expected"])
+        elif c["test"] == "FiveSorter":      # tests/k-way/SortUtilsTest.cpp:204-255
+            got = kway_plain.five_sorter(list(v["inputs"]), list(v["comps"]))
+            assert np.allclose(np.array(got), v["expected"])
+    assert {c["test"] for c in KAT["kway_sortutils"]["cases"]} >= {"FcnL", "TwoSorter", "ThreeSorter", "FourSorter", "FiveSorter"}
     for d in KAT["kway_masking"]["rotate_distance"]:
         assert kway_plain.get_rotate_distance(d["k"], d["logDist"], d["slope"]) == d["expected"]
 

@@ -18,7 +18,7 @@ def next_pow2(n):
     return b
 
 
-@pytest.mark.parametrize("k,M", [(2, 3), (2, 7), (3, 3)])
+@pytest.mark.parametrize("k,M", [(2, 3), (2, 7), (3, 3), (5, 2), (5, 3)])
 def test_index_logic_matches_plain_model(k, M):
     """the product's sortType / getRotateDistance / genIndices (host/kway.h) == the oracle restatement of Masking.cpp"""
     stages = sf.kway_sort_type(k, M, 0)[3]
@@ -36,7 +36,7 @@ def test_adapter_parameters():
     assert rots == [s * (1 << i) for i in range(7) for s in (1, -1)]
 
 
-@pytest.mark.parametrize("k,M", [(2, 1), (2, 4), (2, 7), (3, 2), (3, 3)])
+@pytest.mark.parametrize("k,M", [(2, 1), (2, 4), (2, 7), (3, 2), (3, 3), (5, 1), (5, 2), (5, 3)])
 def test_plain_network_sorts(k, M):
     """the network with an exact comparator sorts (what tests/k-way/SorterTest.cpp:313-381 checks on 8 / 3 / 5 elements)"""
     n = k ** M
@@ -64,15 +64,64 @@ def test_stage_levels_dry_run():
     eng.close()
 
 
+def test_four_five_sorter_exhaustive():
+    """SortUtils::fourSorter / fiveSorter (src/k-way/SortUtils.cpp:80-200) on exact comparison bits: every order of 4 and
+    of 5 distinct values comes out ascending (the literal vectors of tests/k-way/SortUtilsTest.cpp:157-255 are checked
+    in tests/test_golden.py)"""
+    import itertools
+    for n, f in ((4, kp.four_sorter), (5, kp.five_sorter)):
+        for perm in itertools.permutations(range(n)):
+            x = [np.array([float(v)]) for v in perm]
+            comp = [(x[i] > x[j]).astype(float) for i in range(n) for j in range(i + 1, n)]
+            assert [float(v[0]) for v in f(x, comp)] == list(range(n)), perm
+
+
+def test_k5_stage_levels_dry_run():
+    """k = 5, M = 2 (25 elements): the five stages are a 5-sorter, a 5-sorter, the mixed 2/3/4/5 stage, the 2+3 stage and a
+    4-sorter (Sorter.cpp:326-380); level use = mask + Sign(3,3,2) compare (16) + the sorter's own levels"""
+    k, M, n, B = 5, 2, 25, 32
+    rots = [s * (1 << i) for i in range(5) for s in (1, -1)]
+    eng = sf.Engine(11, 34, 50, 60, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    assert sf.kway_sort_type(k, M, 0)[3] == 5
+    levels = []
+    for st in range(5):
+        ct = eng.encrypt(eng.encode(np.arange(B) / B, slots=B))
+        levels.append(sf.kway_sort(eng, ct, n, k, M, (3, 3, 2), 34, st, st + 1).level)
+    assert [sf.kway_sort_type(k, M, st)[2] for st in range(5)] == [0, 0, 1, 2, 3]
+    assert levels == [24, 24, 25, 20, 22]
+    eng.close()
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("k,M", [(2, 2), (3, 1)])
+def test_k5_stages_match_plain_network_on_gpu():
+    """every stage of the k = 5, M = 2 network on the GPU, started from the plaintext network's state before that stage,
+    equals the plaintext network's state after it within 0.01 (4-, 5- and mixed sorters, slot matching, assembly)"""
+    k, M, n, B = 5, 2, 25, 32
+    rots = [s * (1 << i) for i in range(5) for s in (1, -1)]
+    eng = sf.Engine(11, 34, 50, 60, seed=9)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    v = np.random.default_rng(25).permutation(n) / n + 0.5 / n
+    state = np.concatenate([v, np.zeros(B - n)])
+    for st in range(5):
+        want = kp.network_plain(state, k, M, first_stage=st, last_stage=st + 1)
+        out = sf.kway_sort(eng, eng.encrypt(eng.encode(state, slots=B)), n, k, M, (3, 3, 2), 34, st, st + 1)
+        got = eng.decrypt(out, B)
+        assert np.max(np.abs(got - want)) < 0.01, (st, got, want)
+        state = want
+    assert np.allclose(state[:n], np.sort(v))
+    eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k,M", [(2, 2), (3, 1), (5, 1)])
 def test_small_network_sorts_on_gpu(k, M):
     """whole network on k^M elements with enough depth to need no bootstrap (ring 2^11, 50-bit scaling); decrypted
     output = sorted input within the reference's 0.01 gate (tests/k-way/KWaySort2Test.cpp:214)"""
     n = k ** M
     B = next_pow2(n)
     stages = sf.kway_sort_type(k, M, 0)[3]
-    depth = 20 * stages + 4
+    depth = 20 * stages + (8 if k == 5 else 4)
     rots = [s * (1 << i) for i in range(max(1, int(np.log2(B)))) for s in (1, -1)]
     eng = sf.Engine(11, depth, 50, 60, seed=5)
     eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
