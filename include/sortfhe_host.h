@@ -85,6 +85,11 @@ int sortfhe_sinc_coefficients(int n, int doubled, double* coeffs, int cap, int* 
 int sortfhe_mehp24_params(int n, int* mult_depth, int32_t* rotations, int cap, int* count);
 int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int sign_n, int dg, int df, int dg_i, int df_i,
                            ckks_ct_t** out);
+/* mehp24::sortLargeArrayFG (src/mehp24/mehp24_sort.cpp:625-645): splitCiphertext -> multi-ciphertext sortFG (:445-605) ->
+ * combineCiphertext, for total_len = m * sub_len values in one ciphertext of sub_len^2 slots (the reference uses sub_len = 256
+ * for N = 512..2048, tests/mehp24/Mehp24SortTest.cpp:150-157).  Needs the rotation keys of sortfhe_mehp24_params(total_len). */
+int sortfhe_mehp24_sort_large(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int sign_n, int dg, int df,
+                              int dg_i, int df_i, ckks_ct_t** out);
 int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out);
 int sortfhe_mehp24_indicator_adv(ckks_ctx_t* ctx, const ckks_ct_t* x, double b, int dg, int df, ckks_ct_t** out);
 

@@ -382,6 +382,45 @@ class Mehp24:
         return self.transpose_column(S, True)
 
 
+def mehp24_sort_large(cc, c, total_len, sub_len, sign_cfg, dg_i, df_i):
+    """sortLargeArrayFG (mehp24_sort.cpp:625-645) = splitCiphertext (mehp24_utils.cpp:266-289) -> multi-ciphertext sortFG,
+    Comparison-based overload (mehp24_sort.cpp:445-605) -> combineCiphertext (mehp24_utils.cpp:291-302)"""
+    mh, n = Mehp24(cc, sub_len), sub_len
+    nc = total_len // sub_len
+    parts = []
+    for i in range(nc):
+        mask = np.zeros(total_len); mask[i * n:(i + 1) * n] = 1.0
+        p = cc.EvalMult(c, mh._pt(mask))
+        parts.append(cc.EvalRotate(p, i * n) if i else p)
+    repl_r = [mh.replicate_row(p) for p in parts]
+    repl_c = [mh.replicate_column(mh.transpose_row(p, True)) for p in parts]
+    acc = lambda a, x: x if a is None else cc.EvalAdd(a, x)
+    cv, ch, s = [None] * nc, [None] * nc, [None] * nc
+    for j in range(nc):
+        for k in range(j, nc):
+            cjk = compare(cc, repl_r[j], repl_c[k], *sign_cfg)
+            cv[j] = acc(cv[j], cjk)
+            if j != k:
+                ch[k] = acc(ch[k], cc.EvalSub(1.0, cjk))
+    for j in range(nc):
+        s[j] = acc(s[j], mh.sum_rows(cv[j]))
+    for j in range(1, nc):
+        s[j] = acc(s[j], mh.replicate_row(mh.transpose_column(mh.sum_columns(ch[j], True), True)))
+    result = []
+    for j in range(nc):
+        sub = np.repeat(-1.0 * (np.arange(n) + j * n) - 0.5, n)
+        srt = None
+        for k in range(nc):
+            ind = mh.indicator_adv(cc.EvalAdd(s[k], mh._pt(sub)), float(total_len), dg_i, df_i)
+            srt = acc(srt, cc.EvalMult(ind, repl_r[k]))
+        result.append(mh.sum_columns(srt, True))
+    result = [mh.transpose_column(r, True) for r in result]
+    out = result[0]
+    for i in range(1, nc):
+        out = cc.EvalAdd(out, cc.EvalRotate(result[i], -i * n))
+    return out
+
+
 def mehp24_rotation_indices(n):  # getRotationIndices (mehp24_utils.cpp:186-213)
     sz, idx = n, []
     if n > 256:

@@ -407,6 +407,7 @@ _H.sortfhe_kway_gen_indices.argtypes = [_i, _i, _i, _i, _i, _i, _i32p]
 _H.sortfhe_kway_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_params.argtypes = [_i, _ip, _i32p, _i, _ip]
 _H.sortfhe_mehp24_sort_fg.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _pp]
+_H.sortfhe_mehp24_sort_large.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_matrix_op.argtypes = [_vp, _vp, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_indicator_adv.argtypes = [_vp, _vp, _d, _i, _i, _pp]
 
@@ -563,6 +564,15 @@ def mehp24_sort_fg(eng, ct, n, sign_cfg=(3, 2, 2), dg_i=None, df_i=2):
         dg_i = (int(np.log2(n)) + 1) // 2
     o = ctypes.c_void_p()
     _hchk(_H.sortfhe_mehp24_sort_fg(_vp(eng.h), _vp(ct.h), n, *sign_cfg, dg_i, df_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_sort_large(eng, ct, total_len, sub_len, sign_cfg, dg_i=None, df_i=2):
+    """mehp24::sortLargeArrayFG (split -> multi-ciphertext sortFG -> combine), src/mehp24/mehp24_sort.cpp:445-645"""
+    if dg_i is None:
+        dg_i = int((np.log2(total_len) + 1) / 2)
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_sort_large(_vp(eng.h), _vp(ct.h), total_len, sub_len, *sign_cfg, dg_i, df_i, ctypes.byref(o)))
     return Ciphertext(eng, o.value)
 
 

@@ -300,6 +300,18 @@ int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int s
     *out = release(mehp24::sortFG(borrow(input), (size_t)n, SignFunc::CompositeSign, cfg, comp, (uint32_t)dg_i, (uint32_t)df_i, cc));
     HOST_END
 }
+int sortfhe_mehp24_sort_large(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int sn, int dg, int df, int dg_i, int df_i,
+                              ckks_ct_t** out) {
+    HOST_BEGIN
+    if (sub_len < 2 || (sub_len & (sub_len - 1)) || total_len < sub_len || total_len % sub_len)
+        throw std::runtime_error("mehp24 sortLargeArrayFG: sub length must be a power of two dividing the total length");
+    auto cc = borrow(ctx, sub_len * sub_len);            // one sub_len x sub_len matrix per ciphertext
+    SignConfig cfg = make_cfg(sn, dg, df);
+    std::unique_ptr<Comparison> comp(new Comparison());
+    *out = release(mehp24::sortLargeArrayFG(borrow(input), (size_t)total_len, (size_t)sub_len, SignFunc::CompositeSign, cfg, comp,
+                                            (uint32_t)dg_i, (uint32_t)df_i, cc));
+    HOST_END
+}
 int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out) {
     HOST_BEGIN
     using namespace mehp24::utils;

@@ -137,4 +137,70 @@ inline Ciphertext<DCRTPoly> sortFG(Ciphertext<DCRTPoly> c, const size_t vectorLe
     return transposeColumn(m_cc, S, n, true);                                       // back to row 0
 }
 
+// splitCiphertext / combineCiphertext (mehp24_utils.cpp:266-302): block i of subLength values moved to the front / back
+inline std::vector<Ciphertext<DCRTPoly>> splitCiphertext(const Ciphertext<DCRTPoly>& c, size_t totalLength, size_t subLength,
+                                                         CryptoContext<DCRTPoly>& cc) {
+    const size_t numParts = totalLength / subLength;
+    std::vector<Ciphertext<DCRTPoly>> result(numParts);
+    for (size_t i = 0; i < numParts; i++) {
+        std::vector<double> mask(totalLength, 0.0);
+        for (size_t j = 0; j < subLength; j++) mask[i * subLength + j] = 1.0;
+        auto part = cc->EvalMult(c, cc->MakeCKKSPackedPlaintext(mask));
+        if (i > 0) part = cc->EvalRotate(part, (int32_t)(i * subLength));
+        result[i] = part;
+    }
+    return result;
+}
+inline Ciphertext<DCRTPoly> combineCiphertext(const std::vector<Ciphertext<DCRTPoly>>& parts, size_t subLength, CryptoContext<DCRTPoly>& cc) {
+    auto result = parts[0];
+    for (size_t i = 1; i < parts.size(); i++) result = cc->EvalAdd(result, cc->EvalRotate(parts[i], -(int32_t)(i * subLength)));
+    return result;
+}
+
+// sortFG over several ciphertexts of subVectorLength values each, Comparison-based overload (mehp24_sort.cpp:445-605):
+// block (j, k) of the comparison matrix from one compare (the lower triangle is 1 - upper), ranks from row sums of the
+// column blocks plus transposed column sums of the row blocks, then one indicator per (target block, source block).
+// The reference runs the blocks under OpenMP with critical-section accumulation; the sums are order-independent.
+inline std::vector<Ciphertext<DCRTPoly>> sortFG(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength,
+                                                SignFunc SignFunc, SignConfig& Cfg, std::unique_ptr<Comparison>& comp,
+                                                uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> m_cc) {
+    using namespace utils;
+    const size_t nc = c.size(), n = subVectorLength, vectorLength = n * nc;
+    std::vector<CT> replR(nc), replC(nc), Cv(nc), Ch(nc), s(nc);
+    for (size_t j = 0; j < nc; j++) replR[j] = replicateRow(m_cc, c[j], n);
+    for (size_t j = 0; j < nc; j++) replC[j] = replicateColumn(m_cc, transposeRow(m_cc, c[j], n, true), n);
+    auto accumulate = [&](CT& acc, const CT& x) { acc = acc ? m_cc->EvalAdd(acc, x) : x; };
+    for (size_t j = 0; j < nc; j++)
+        for (size_t k = j; k < nc; k++) {
+            CT Cjk = comp->compare(m_cc, replR[j], replC[k], SignFunc, Cfg);
+            accumulate(Cv[j], Cjk);
+            if (j != k) accumulate(Ch[k], m_cc->EvalSub(1.0, Cjk));
+        }
+    for (size_t j = 0; j < nc; j++) accumulate(s[j], sumRows(m_cc, Cv[j], n));
+    for (size_t j = 1; j < nc; j++) {
+        CT shj = sumColumns(m_cc, Ch[j], n, true);
+        shj = transposeColumn(m_cc, shj, n, true);
+        accumulate(s[j], replicateRow(m_cc, shj, n));
+    }
+    std::vector<CT> result(nc);
+    for (size_t j = 0; j < nc; j++) {
+        std::vector<double> subMask(n * n);
+        for (size_t r = 0; r < n; r++) for (size_t q = 0; q < n; q++) subMask[r * n + q] = -1.0 * (double)(j * n + r) - 0.5;
+        CT subSorted;
+        for (size_t k = 0; k < nc; k++)
+            accumulate(subSorted, m_cc->EvalMult(indicatorAdv(m_cc, addVec(m_cc, s[k], subMask), (double)vectorLength, dg_i, df_i), replR[k]));
+        result[j] = sumColumns(m_cc, subSorted, n, true);
+    }
+    for (size_t j = 0; j < nc; j++) result[j] = transposeColumn(m_cc, result[j], n, true);
+    return result;
+}
+
+// sortLargeArrayFG (mehp24_sort.cpp:625-645): split -> multi-ciphertext sortFG -> combine
+inline Ciphertext<DCRTPoly> sortLargeArrayFG(Ciphertext<DCRTPoly> c, const size_t totalLength, const size_t subLength, SignFunc SignFunc,
+                                             SignConfig& Cfg, std::unique_ptr<Comparison>& comp, uint32_t dg_i, uint32_t df_i,
+                                             CryptoContext<DCRTPoly> cc) {
+    std::vector<Ciphertext<DCRTPoly>> parts = splitCiphertext(c, totalLength, subLength, cc);
+    return combineCiphertext(sortFG(parts, subLength, SignFunc, Cfg, comp, dg_i, df_i, cc), subLength, cc);
+}
+
 }  // namespace mehp24

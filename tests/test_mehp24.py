@@ -111,3 +111,34 @@ def test_sort_fg_n256_ring17_properties():
     assert np.max(np.abs(got - np.sort(x))) < 0.01
     assert np.array_equal(np.round(got * n).astype(int), np.arange(n))
     eng.close()
+
+
+def test_large_array_level_budget_dry_run():
+    """sortLargeArrayFG at the fixture's N = 512 card (depth 57, Sign(3,4,2), two 256 x 256 blocks, ring 2^17,
+    tests/mehp24/Mehp24SortTest.cpp:62-64,150-157) stays inside the depth; metadata-only run"""
+    depth, rots = sf.mehp24_params(512)
+    assert depth == 57 and 256 in rots and -256 in rots
+    eng = sf.Engine(17, depth, 40, 60, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    ct = eng.encrypt(eng.encode(np.arange(512) / 512, slots=65536))
+    out = sf.mehp24_sort_large(eng, ct, 512, 256, (3, 4, 2))
+    assert out.level <= depth
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_sort_large_array_bit_exact_small():
+    """mehp24::sortLargeArrayFG (split -> multi-ciphertext sortFG -> combine, src/mehp24/mehp24_sort.cpp:445-645) on 8 values
+    as two 4 x 4 blocks: every limb identical to the oracle restatement, decrypted output sorted within 0.01"""
+    total, sub = 8, 4
+    rots = sorted(set(sf.mehp24_params(sub)[1] + [sub, -sub]))
+    eng, orc = make_pair(10, 40, rots=rots)
+    x = np.random.default_rng(8).permutation(total) / total
+    co = orc.encrypt(orc.encode(x, slots=sub * sub))
+    ce = eng.encrypt(eng.encode(x, slots=sub * sub))
+    d = int((np.log2(total) + 1) / 2)
+    ro = algos.mehp24_sort_large(orc, co, total, sub, (3, 2, 2), d, 2)
+    re = sf.mehp24_sort_large(eng, ce, total, sub, (3, 2, 2), d, 2)
+    same(re, ro)
+    assert np.max(np.abs(eng.decrypt(re, sub * sub)[:total] - np.sort(x))) < 0.01
+    eng.close()

@@ -117,7 +117,21 @@ def hybrid1(n=128):
     return res
 
 
+def mehp24_large(n=512, sub=256):
+    """mehp24::sortLargeArrayFG N = 512 as two 256 x 256 blocks (fixture depth 57, Sign(3,4,2))"""
+    depth, rots = sf.mehp24_params(n)
+    eng, stream = engine(17, depth, rots=rots, seed=4)
+    x = np.random.default_rng(12).permutation(n) / n
+    ct = eng.encrypt(eng.encode(x, slots=sub * sub))
+    ms, out = timed(eng, stream, lambda: sf.mehp24_sort_large(eng, ct, n, sub, (3, 4, 2)), reps=2)
+    res = {"ms": ms, "depth": depth, "level": out.level, "rotation_keys": len(rots), "key_bytes": eng.info(7),
+           "max_abs_err": float(np.max(np.abs(eng.decrypt(out, sub * sub)[:n] - np.sort(x))))}
+    eng.close()
+    return res
+
+
 CONFIGS = {
+    "mehp24_sort_large_n512": mehp24_large,
     "sort_hybrid1_n128": hybrid1,
     "direct_sort_n16": lambda: direct_sort(16, (3, 2, 2)),
     "compare_sign433_full_slot": compare_full_slot,
