@@ -90,6 +90,23 @@ int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int s
  * for N = 512..2048, tests/mehp24/Mehp24SortTest.cpp:150-157).  Needs the rotation keys of sortfhe_mehp24_params(total_len). */
 int sortfhe_mehp24_sort_large(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int sign_n, int dg, int df,
                               int dg_i, int df_i, ckks_ct_t** out);
+/* Multi-ciphertext sortFG in shardable stages (the nc (nc + 1) / 2 block comparisons of
+ * src/mehp24/mehp24_sort.cpp:484-522 and the nc target blocks of :554-603 are independent; the reference runs them under
+ * OpenMP with `omp critical` accumulation).  split / combine = splitCiphertext / combineCiphertext (mehp24_utils.cpp:266-302;
+ * `out` of split holds total_len / sub_len handles).  block_compare_partial runs comparison units [u_lo, u_hi) of the upper
+ * triangle (j <= k, row-major) and returns the nc column-block sums cv_out[j] and the row-block sums ch_out[k] (k >= 1;
+ * ch_out[0] = NULL); accumulators the range never touched are exact zeros of the same level and scale, so the partial sums
+ * of all shards are combined limb-wise (ckks_ct_device_ptr + all-reduce + ckks_ct_mod_reduce).  block_ranks turns the
+ * combined sums into the nc rank matrices (:524-552), block_sorted computes target block j from them (:554-603).  With the
+ * full unit range the four calls are exactly sortfhe_mehp24_sort_large. */
+int sortfhe_mehp24_split(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, ckks_ct_t** out);
+int sortfhe_mehp24_combine(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, ckks_ct_t** out);
+int sortfhe_mehp24_block_compare_partial(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, int sign_n, int dg, int df,
+                                         int u_lo, int u_hi, ckks_ct_t** cv_out, ckks_ct_t** ch_out);
+int sortfhe_mehp24_block_ranks(ckks_ctx_t* ctx, const ckks_ct_t* const* cv, const ckks_ct_t* const* ch, int nc, int sub_len,
+                               ckks_ct_t** s_out);
+int sortfhe_mehp24_block_sorted(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, const ckks_ct_t* const* s, int nc, int sub_len, int j,
+                                int dg_i, int df_i, ckks_ct_t** out);
 int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out);
 int sortfhe_mehp24_indicator_adv(ckks_ctx_t* ctx, const ckks_ct_t* x, double b, int dg, int df, ckks_ct_t** out);
 

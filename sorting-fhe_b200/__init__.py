@@ -408,6 +408,11 @@ _H.sortfhe_kway_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _
 _H.sortfhe_mehp24_params.argtypes = [_i, _ip, _i32p, _i, _ip]
 _H.sortfhe_mehp24_sort_fg.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_sort_large.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _pp]
+_H.sortfhe_mehp24_split.argtypes = [_vp, _vp, _i, _i, _pp]
+_H.sortfhe_mehp24_combine.argtypes = [_vp, _pp, _i, _i, _pp]
+_H.sortfhe_mehp24_block_compare_partial.argtypes = [_vp, _pp, _i, _i, _i, _i, _i, _i, _i, _pp, _pp]
+_H.sortfhe_mehp24_block_ranks.argtypes = [_vp, _pp, _pp, _i, _i, _pp]
+_H.sortfhe_mehp24_block_sorted.argtypes = [_vp, _pp, _pp, _i, _i, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_matrix_op.argtypes = [_vp, _vp, _i, _i, _i, _pp]
 _H.sortfhe_mehp24_indicator_adv.argtypes = [_vp, _vp, _d, _i, _i, _pp]
 
@@ -573,6 +578,56 @@ def mehp24_sort_large(eng, ct, total_len, sub_len, sign_cfg, dg_i=None, df_i=2):
         dg_i = int((np.log2(total_len) + 1) / 2)
     o = ctypes.c_void_p()
     _hchk(_H.sortfhe_mehp24_sort_large(_vp(eng.h), _vp(ct.h), total_len, sub_len, *sign_cfg, dg_i, df_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def _harr(cts):
+    """array of ciphertext handles (NULL for None) for the `const ckks_ct_t* const*` parameters"""
+    return (ctypes.c_void_p * len(cts))(*[c.h if c is not None else None for c in cts])
+
+
+def _hout(eng, arr):
+    return [Ciphertext(eng, h) if h else None for h in arr]
+
+
+def mehp24_split(eng, ct, total_len, sub_len):
+    """mehp24::splitCiphertext (mehp24_utils.cpp:266-287)"""
+    out = (ctypes.c_void_p * (total_len // sub_len))()
+    _hchk(_H.sortfhe_mehp24_split(_vp(eng.h), _vp(ct.h), total_len, sub_len, out))
+    return _hout(eng, out)
+
+
+def mehp24_combine(eng, parts, sub_len):
+    """mehp24::combineCiphertext (mehp24_utils.cpp:289-302)"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_combine(_vp(eng.h), _harr(parts), len(parts), sub_len, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_compare_units(nc):
+    """number of block comparisons of the multi-ciphertext sortFG: the upper triangle of the nc x nc block matrix"""
+    return nc * (nc + 1) // 2
+
+
+def mehp24_block_compare_partial(eng, parts, sub_len, sign_cfg, u_lo, u_hi):
+    """comparison units [u_lo, u_hi) of mehp24_sort.cpp:484-522 -> (Cv[nc], Ch[nc] with Ch[0] = None), zero-filled"""
+    nc = len(parts)
+    cv, ch = (ctypes.c_void_p * nc)(), (ctypes.c_void_p * nc)()
+    _hchk(_H.sortfhe_mehp24_block_compare_partial(_vp(eng.h), _harr(parts), nc, sub_len, *sign_cfg, u_lo, u_hi, cv, ch))
+    return _hout(eng, cv), _hout(eng, ch)
+
+
+def mehp24_block_ranks(eng, cv, ch, sub_len):
+    """rank matrices of the nc blocks from the combined comparison sums (mehp24_sort.cpp:524-552)"""
+    out = (ctypes.c_void_p * len(cv))()
+    _hchk(_H.sortfhe_mehp24_block_ranks(_vp(eng.h), _harr(cv), _harr(ch), len(cv), sub_len, out))
+    return _hout(eng, out)
+
+
+def mehp24_block_sorted(eng, parts, s, sub_len, j, dg_i, df_i=2):
+    """target block j of the multi-ciphertext sortFG (mehp24_sort.cpp:554-603)"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_block_sorted(_vp(eng.h), _harr(parts), _harr(s), len(parts), sub_len, j, dg_i, df_i, ctypes.byref(o)))
     return Ciphertext(eng, o.value)
 
 

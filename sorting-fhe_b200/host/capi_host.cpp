@@ -312,6 +312,68 @@ int sortfhe_mehp24_sort_large(ckks_ctx_t* ctx, const ckks_ct_t* input, int total
                                             (uint32_t)dg_i, (uint32_t)df_i, cc));
     HOST_END
 }
+// multi-ciphertext sortFG in stages (mehp24.h namespace blocks): the shardable halves behind shard.py's mehp24_sort_large_sharded
+namespace {
+std::vector<CT> borrow_all(const ckks_ct_t* const* h, int cnt, int first = 0) {
+    std::vector<CT> v((size_t)cnt);
+    for (int i = first; i < cnt; i++) v[(size_t)i] = borrow(h[i]);
+    return v;
+}
+void check_blocks(int nc, int sub_len) {
+    if (nc < 1 || sub_len < 2 || (sub_len & (sub_len - 1))) throw std::runtime_error("mehp24 blocks: sub length must be a power of two, at least one block");
+}
+}  // namespace
+int sortfhe_mehp24_split(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (sub_len < 2 || (sub_len & (sub_len - 1)) || total_len < sub_len || total_len % sub_len)
+        throw std::runtime_error("mehp24 splitCiphertext: sub length must be a power of two dividing the total length");
+    auto cc = borrow(ctx, sub_len * sub_len);
+    std::vector<CT> parts = mehp24::splitCiphertext(borrow(input), (size_t)total_len, (size_t)sub_len, cc);
+    for (size_t i = 0; i < parts.size(); i++) out[i] = release(parts[i]);
+    HOST_END
+}
+int sortfhe_mehp24_combine(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, ckks_ct_t** out) {
+    HOST_BEGIN
+    check_blocks(nc, sub_len);
+    auto cc = borrow(ctx, sub_len * sub_len);
+    *out = release(mehp24::combineCiphertext(borrow_all(parts, nc), (size_t)sub_len, cc));
+    HOST_END
+}
+int sortfhe_mehp24_block_compare_partial(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, int sn, int dg, int df,
+                                         int u_lo, int u_hi, ckks_ct_t** cv_out, ckks_ct_t** ch_out) {
+    HOST_BEGIN
+    check_blocks(nc, sub_len);
+    if (u_lo < 0 || u_hi < u_lo || u_hi > (int)mehp24::blocks::numCompareUnits((size_t)nc))
+        throw std::runtime_error("mehp24 block compare: unit range outside [0, nc (nc + 1) / 2]");
+    auto cc = borrow(ctx, sub_len * sub_len);
+    SignConfig cfg = make_cfg(sn, dg, df);
+    std::unique_ptr<Comparison> comp(new Comparison());
+    std::vector<CT> replR, replC, Cv, Ch;
+    mehp24::blocks::replicas(cc, borrow_all(parts, nc), (size_t)sub_len, replR, replC);
+    mehp24::blocks::comparePartial(cc, replR, replC, (size_t)u_lo, (size_t)u_hi, SignFunc::CompositeSign, cfg, comp, Cv, Ch, true);
+    ch_out[0] = nullptr;
+    for (int j = 0; j < nc; j++) { cv_out[j] = release(Cv[(size_t)j]); if (j) ch_out[j] = release(Ch[(size_t)j]); }
+    HOST_END
+}
+int sortfhe_mehp24_block_ranks(ckks_ctx_t* ctx, const ckks_ct_t* const* cv, const ckks_ct_t* const* ch, int nc, int sub_len, ckks_ct_t** s_out) {
+    HOST_BEGIN
+    check_blocks(nc, sub_len);
+    auto cc = borrow(ctx, sub_len * sub_len);
+    std::vector<CT> s = mehp24::blocks::ranks(cc, borrow_all(cv, nc), borrow_all(ch, nc, 1), (size_t)sub_len);
+    for (int j = 0; j < nc; j++) s_out[j] = release(s[(size_t)j]);
+    HOST_END
+}
+int sortfhe_mehp24_block_sorted(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, const ckks_ct_t* const* s, int nc, int sub_len, int j,
+                                int dg_i, int df_i, ckks_ct_t** out) {
+    HOST_BEGIN
+    check_blocks(nc, sub_len);
+    if (j < 0 || j >= nc) throw std::runtime_error("mehp24 block sorted: target block outside [0, nc)");
+    auto cc = borrow(ctx, sub_len * sub_len);
+    std::vector<CT> replR, replC;
+    mehp24::blocks::replicas(cc, borrow_all(parts, nc), (size_t)sub_len, replR, replC);
+    *out = release(mehp24::blocks::sortedBlock(cc, replR, borrow_all(s, nc), (size_t)sub_len, (size_t)j, (uint32_t)dg_i, (uint32_t)df_i));
+    HOST_END
+}
 int sortfhe_mehp24_matrix_op(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int op, int mask_output, ckks_ct_t** out) {
     HOST_BEGIN
     using namespace mehp24::utils;

@@ -160,38 +160,82 @@ inline Ciphertext<DCRTPoly> combineCiphertext(const std::vector<Ciphertext<DCRTP
 // sortFG over several ciphertexts of subVectorLength values each, Comparison-based overload (mehp24_sort.cpp:445-605):
 // block (j, k) of the comparison matrix from one compare (the lower triangle is 1 - upper), ranks from row sums of the
 // column blocks plus transposed column sums of the row blocks, then one indicator per (target block, source block).
-// The reference runs the blocks under OpenMP with critical-section accumulation; the sums are order-independent.
+// The reference runs the blocks under OpenMP with critical-section accumulation; the sums are order-independent
+// (all addends of one accumulator sit at the same level and scale, so EvalAdd is a limb-wise modular addition).
+// The four stages are separate functions so that the block comparisons and the target blocks can be split over GPUs
+// (sorting-fhe_b200/shard.py mehp24_sort_large_sharded); sortFG below is their composition on full ranges.
+namespace blocks {
+using utils::CC; using utils::CT;
+inline void accumulate(const CC& cc, CT& acc, const CT& x) { acc = acc ? cc->EvalAdd(acc, x) : x; }
+// replR[j]: every row = block j; replC[j]: every column = block j  (:459-482)
+inline void replicas(const CC& cc, const std::vector<CT>& c, size_t n, std::vector<CT>& replR, std::vector<CT>& replC) {
+    replR.resize(c.size()); replC.resize(c.size());
+    for (size_t j = 0; j < c.size(); j++) replR[j] = utils::replicateRow(cc, c[j], n);
+    for (size_t j = 0; j < c.size(); j++) replC[j] = utils::replicateColumn(cc, utils::transposeRow(cc, c[j], n, true), n);
+}
+inline size_t numCompareUnits(size_t nc) { return nc * (nc + 1) / 2; }
+// comparison units u in [u_lo, u_hi) of the upper triangle (j <= k, row-major): Cv[j] += C_jk, Ch[k] += 1 - C_jk  (:484-522).
+// With `fill`, accumulators this range never touched become exact zeros at the comparisons' level and scale (x - x), so
+// that every shard hands the same set of same-shaped partial sums to the limb all-reduce.
+inline void comparePartial(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& replC, size_t u_lo, size_t u_hi,
+                           SignFunc SignFunc, SignConfig& Cfg, std::unique_ptr<Comparison>& comp, std::vector<CT>& Cv,
+                           std::vector<CT>& Ch, bool fill) {
+    const size_t nc = replR.size();
+    Cv.assign(nc, CT()); Ch.assign(nc, CT());
+    CT any;
+    size_t u = 0;
+    for (size_t j = 0; j < nc; j++)
+        for (size_t k = j; k < nc; k++, u++) {
+            if (u < u_lo || u >= u_hi) continue;
+            CT Cjk = comp->compare(cc, replR[j], replC[k], SignFunc, Cfg);
+            accumulate(cc, Cv[j], Cjk);
+            if (j != k) accumulate(cc, Ch[k], cc->EvalSub(1.0, Cjk));
+            any = Cjk;
+        }
+    if (!fill) return;
+    if (!any) throw std::runtime_error("mehp24 block compare: empty unit range (more shards than block comparisons)");
+    CT zero = cc->EvalSub(any, any);
+    for (size_t j = 0; j < nc; j++) {
+        if (!Cv[j]) Cv[j] = zero->Clone();
+        if (j > 0 && !Ch[j]) Ch[j] = zero->Clone();
+    }
+}
+// s[j] = sumRows(Cv[j]) (+ the transposed column sums of Ch[j] replicated over the rows, j >= 1)  (:524-552)
+inline std::vector<CT> ranks(const CC& cc, const std::vector<CT>& Cv, const std::vector<CT>& Ch, size_t n) {
+    const size_t nc = Cv.size();
+    std::vector<CT> s(nc);
+    for (size_t j = 0; j < nc; j++) accumulate(cc, s[j], utils::sumRows(cc, Cv[j], n));
+    for (size_t j = 1; j < nc; j++) {
+        CT shj = utils::sumColumns(cc, Ch[j], n, true);
+        shj = utils::transposeColumn(cc, shj, n, true);
+        accumulate(cc, s[j], utils::replicateRow(cc, shj, n));
+    }
+    return s;
+}
+// target block j: sum over the source blocks k of indicator(rank_k - (j n + r) - 1/2) * values_k, column sums, back to row 0  (:554-603)
+inline CT sortedBlock(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& s, size_t n, size_t j, uint32_t dg_i,
+                      uint32_t df_i) {
+    const size_t nc = replR.size(), vectorLength = n * nc;
+    std::vector<double> subMask(n * n);
+    for (size_t r = 0; r < n; r++) for (size_t q = 0; q < n; q++) subMask[r * n + q] = -1.0 * (double)(j * n + r) - 0.5;
+    CT subSorted;
+    for (size_t k = 0; k < nc; k++)
+        accumulate(cc, subSorted, cc->EvalMult(utils::indicatorAdv(cc, utils::addVec(cc, s[k], subMask), (double)vectorLength, dg_i, df_i), replR[k]));
+    return utils::transposeColumn(cc, utils::sumColumns(cc, subSorted, n, true), n, true);
+}
+}  // namespace blocks
+
 inline std::vector<Ciphertext<DCRTPoly>> sortFG(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength,
                                                 SignFunc SignFunc, SignConfig& Cfg, std::unique_ptr<Comparison>& comp,
                                                 uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> m_cc) {
-    using namespace utils;
-    const size_t nc = c.size(), n = subVectorLength, vectorLength = n * nc;
-    std::vector<CT> replR(nc), replC(nc), Cv(nc), Ch(nc), s(nc);
-    for (size_t j = 0; j < nc; j++) replR[j] = replicateRow(m_cc, c[j], n);
-    for (size_t j = 0; j < nc; j++) replC[j] = replicateColumn(m_cc, transposeRow(m_cc, c[j], n, true), n);
-    auto accumulate = [&](CT& acc, const CT& x) { acc = acc ? m_cc->EvalAdd(acc, x) : x; };
-    for (size_t j = 0; j < nc; j++)
-        for (size_t k = j; k < nc; k++) {
-            CT Cjk = comp->compare(m_cc, replR[j], replC[k], SignFunc, Cfg);
-            accumulate(Cv[j], Cjk);
-            if (j != k) accumulate(Ch[k], m_cc->EvalSub(1.0, Cjk));
-        }
-    for (size_t j = 0; j < nc; j++) accumulate(s[j], sumRows(m_cc, Cv[j], n));
-    for (size_t j = 1; j < nc; j++) {
-        CT shj = sumColumns(m_cc, Ch[j], n, true);
-        shj = transposeColumn(m_cc, shj, n, true);
-        accumulate(s[j], replicateRow(m_cc, shj, n));
-    }
+    using utils::CT;
+    const size_t nc = c.size(), n = subVectorLength;
+    std::vector<CT> replR, replC, Cv, Ch;
+    blocks::replicas(m_cc, c, n, replR, replC);
+    blocks::comparePartial(m_cc, replR, replC, 0, blocks::numCompareUnits(nc), SignFunc, Cfg, comp, Cv, Ch, false);
+    std::vector<CT> s = blocks::ranks(m_cc, Cv, Ch, n);
     std::vector<CT> result(nc);
-    for (size_t j = 0; j < nc; j++) {
-        std::vector<double> subMask(n * n);
-        for (size_t r = 0; r < n; r++) for (size_t q = 0; q < n; q++) subMask[r * n + q] = -1.0 * (double)(j * n + r) - 0.5;
-        CT subSorted;
-        for (size_t k = 0; k < nc; k++)
-            accumulate(subSorted, m_cc->EvalMult(indicatorAdv(m_cc, addVec(m_cc, s[k], subMask), (double)vectorLength, dg_i, df_i), replR[k]));
-        result[j] = sumColumns(m_cc, subSorted, n, true);
-    }
-    for (size_t j = 0; j < nc; j++) result[j] = transposeColumn(m_cc, result[j], n, true);
+    for (size_t j = 0; j < nc; j++) result[j] = blocks::sortedBlock(m_cc, replR, s, n, j, dg_i, df_i);
     return result;
 }
 

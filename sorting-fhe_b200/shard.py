@@ -11,6 +11,10 @@ The all-reduce is a plain integer SUM of the raw uint64 limbs (NCCL over NVLink 
 followed by one `mod q_limb` pass: residues are < 2^61, so up to 8 addends stay below 2^63, and modular addition is
 associative -- the result is bit-identical to the single-GPU sum.  A single DirectSort with num_batch == 1 (N <= 256 at
 ring 2^17) is one dependent chain and does not shard: replicas only.
+  * MEHP24 multi-ciphertext sortFG      -> the nc (nc + 1) / 2 block comparisons (reference src/mehp24/mehp24_sort.cpp:
+    (N > 256 as nc blocks)                 484-522) and the nc target blocks (:554-603) are independent; the comparison
+                                           sums are combined by the same limb all-reduce (2 nc - 1 ciphertexts), each
+                                           target block is computed by one rank and broadcast to the others.
 """
 import numpy as np
 import torch
@@ -89,3 +93,55 @@ def sort_batch_sharded(eng, n, rots, cts, sign_cfg, group=None):
     lo, hi = shard_range(len(cts), rank, world)
     sorter = DirectSort(eng, n, rots)
     return lo, [sorter.sort(c, sign_cfg) for c in cts[lo:hi]]
+
+
+def broadcast_ciphertext(eng, ct, src, group=None):
+    """every rank ends up with rank `src`'s ciphertext: metadata as a small tensor, limbs broadcast into a fresh handle
+    of that shape where they lie on the device.  `ct` is ignored on the other ranks."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return ct
+    rank = dist.get_rank(group)
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    meta = torch.zeros(6, dtype=torch.float64, device=dev)
+    if rank == src:
+        meta = torch.tensor([ct.parts, ct.nlimbs, ct.level, ct.deg, ct.sf, ct.slots], dtype=torch.float64, device=dev)
+    dist.broadcast(meta, src, group=group)
+    parts, nlimbs, level, deg, sf_, slots = (int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), float(meta[4]), int(meta[5]))
+    if rank != src:
+        ct = eng.import_ct(np.zeros((parts, nlimbs, eng.n), dtype=np.uint64), level, deg, sf_, slots)
+    ptr, words = eng.ct_device_ptr(ct)
+    eng.sync()
+    t = torch.as_tensor(_DevView(ptr, words), device="cuda")
+    dist.broadcast(t, src, group=group)
+    torch.cuda.current_stream().synchronize()
+    return ct
+
+
+def mehp24_sort_large_sharded(eng, ct, total_len, sub_len, sign_cfg, dg_i=None, df_i=2, group=None):
+    """mehp24::sortLargeArrayFG with the block comparisons and the target blocks of the multi-ciphertext sortFG split over
+    the ranks of `group`.  Every rank holds the same input ciphertext and keys and returns the same sorted ciphertext,
+    limb for limb the one `mehp24_sort_large` computes on a single GPU (the partial sums have one level and scale, and
+    modular addition is associative)."""
+    from . import (mehp24_split, mehp24_combine, mehp24_compare_units, mehp24_block_compare_partial, mehp24_block_ranks,
+                   mehp24_block_sorted, mehp24_sort_large)
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if dg_i is None:
+        dg_i = int((np.log2(total_len) + 1) / 2)
+    nc = total_len // sub_len
+    if world == 1 or nc == 1:
+        return mehp24_sort_large(eng, ct, total_len, sub_len, sign_cfg, dg_i, df_i)
+    units = mehp24_compare_units(nc)
+    if world > units:
+        raise ValueError("mehp24_sort_large_sharded: %d block comparisons do not occupy %d ranks" % (units, world))
+    parts = mehp24_split(eng, ct, total_len, sub_len)
+    lo, hi = shard_range(units, rank, world)
+    cv, ch = mehp24_block_compare_partial(eng, parts, sub_len, sign_cfg, lo, hi)
+    for c in cv + ch[1:]:
+        allreduce_ciphertext(eng, c, group)
+    s = mehp24_block_ranks(eng, cv, ch, sub_len)
+    owner = [next(r for r in range(world) if shard_range(nc, r, world)[0] <= j < shard_range(nc, r, world)[1]) for j in range(nc)]
+    mine = {j: mehp24_block_sorted(eng, parts, s, sub_len, j, dg_i, df_i) for j in range(nc) if owner[j] == rank}
+    blocks = [broadcast_ciphertext(eng, mine.get(j), owner[j], group) for j in range(nc)]
+    return mehp24_combine(eng, blocks, sub_len)

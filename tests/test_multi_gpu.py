@@ -181,3 +181,111 @@ def test_direct_sort_sharded_nccl_2gpu():
         p.join(120)
         assert p.exitcode == 0
     assert err < 0.01 and err_ref < 0.01 and same
+
+
+# ------------------------------------------------------------------ MEHP24 multi-ciphertext sortFG
+def _mehp24_engine(total, sub, dry=False, **kw):
+    rots = sorted(set(sf.mehp24_params(sub)[1] + [sub, -sub]))
+    eng = sf.Engine(10, 40, 40, dry_run=True) if dry else sf.Engine(10, 40, 40, **kw)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    return eng
+
+
+def test_mehp24_block_stages_dry_run_levels():
+    """8 values as two 4 x 4 blocks: the three block comparisons split 2 + 1 give same-level partial sums (zero-filled where
+    a shard has no addend), and the staged pipeline ends at the level of the unsharded sortLargeArrayFG"""
+    total, sub, cfg = 8, 4, (3, 2, 2)
+    eng = _mehp24_engine(total, sub, dry=True)
+    d = int((np.log2(total) + 1) / 2)
+    ct = eng.encrypt(eng.encode(np.arange(total) / total, slots=sub * sub))
+    full = sf.mehp24_sort_large(eng, ct, total, sub, cfg, d, 2)
+    parts = sf.mehp24_split(eng, ct, total, sub)
+    assert len(parts) == 2 and sf.mehp24_compare_units(2) == 3
+    cv0, ch0 = sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 0, 2)
+    cv1, ch1 = sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 2, 3)
+    assert ch0[0] is None and ch1[0] is None
+    for a, b in zip(cv0 + ch0[1:], cv1 + ch1[1:]):
+        assert (a.level, a.deg, a.nlimbs) == (b.level, b.deg, b.nlimbs)
+    cv = [eng.EvalAdd(a, b) for a, b in zip(cv0, cv1)]
+    ch = [None] + [eng.EvalAdd(a, b) for a, b in zip(ch0[1:], ch1[1:])]
+    s = sf.mehp24_block_ranks(eng, cv, ch, sub)
+    blocks = [sf.mehp24_block_sorted(eng, parts, s, sub, j, d, 2) for j in range(2)]
+    assert sf.mehp24_combine(eng, blocks, sub).level == full.level
+    with pytest.raises(sf.CkksError, match="empty unit range"):
+        sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 1, 1)
+    with pytest.raises(sf.CkksError, match="unit range outside"):
+        sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 0, 4)
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_mehp24_block_stages_recombine_bit_exact():
+    """the block comparisons of the two-block sortFG computed as two shards (units [0,2) and [2,3)), summed through the
+    raw-limb path, then ranks / target blocks / combine: every limb equals the unsharded sortLargeArrayFG (which the
+    oracle pins in tests/test_mehp24.py)"""
+    total, sub, cfg = 8, 4, (3, 2, 2)
+    eng = _mehp24_engine(total, sub, seed=9)
+    d = int((np.log2(total) + 1) / 2)
+    x = np.random.default_rng(8).permutation(total) / total
+    ct = eng.encrypt(eng.encode(x, slots=sub * sub))
+    want = sf.mehp24_sort_large(eng, ct, total, sub, cfg, d, 2)
+    parts = sf.mehp24_split(eng, ct, total, sub)
+    cv0, ch0 = sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 0, 2)
+    cv1, ch1 = sf.mehp24_block_compare_partial(eng, parts, sub, cfg, 2, 3)
+    assert not cv1[0].export().any()                                           # shard 1 = unit (1,1): nothing for Cv[0]
+
+    def combine(p0, p1):          # what allreduce_ciphertext does with world = 2, on one device
+        a, w = eng.ct_device_ptr(p0)
+        b, _ = eng.ct_device_ptr(p1)
+        eng.sync()
+        ta = torch.as_tensor(shard._DevView(a, w), device="cuda")
+        tb = torch.as_tensor(shard._DevView(b, w), device="cuda")
+        ta += tb
+        torch.cuda.synchronize()
+        eng.ct_mod_reduce(p0)
+        return p0
+
+    cv = [combine(a, b) for a, b in zip(cv0, cv1)]
+    ch = [None] + [combine(a, b) for a, b in zip(ch0[1:], ch1[1:])]
+    s = sf.mehp24_block_ranks(eng, cv, ch, sub)
+    got = sf.mehp24_combine(eng, [sf.mehp24_block_sorted(eng, parts, s, sub, j, d, 2) for j in range(2)], sub)
+    assert np.array_equal(got.export(), want.export())
+    assert np.max(np.abs(eng.decrypt(got, sub * sub)[:total] - np.sort(x))) < 0.01
+    eng.close()
+
+
+def _nccl_mehp24_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    total, sub, cfg = 8, 4, (3, 2, 2)
+    eng = _mehp24_engine(total, sub, seed=9)               # same seed on every rank: identical keys and input ciphertext
+    x = np.random.default_rng(8).permutation(total) / total
+    ct = eng.encrypt(eng.encode(x, slots=sub * sub))
+    got = shard.mehp24_sort_large_sharded(eng, ct, total, sub, cfg)
+    want = sf.mehp24_sort_large(eng, ct, total, sub, cfg)  # no encryption inside: the single-GPU limbs are the reference
+    exact = bool(np.array_equal(got.export(), want.export()))
+    err = float(np.max(np.abs(eng.decrypt(got, sub * sub)[:total] - np.sort(x))))
+    ok = torch.tensor([int(exact)], device="cuda")
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        out.put((err, bool(ok.item())))
+    eng.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_mehp24_sort_large_sharded_nccl_2gpu():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_nccl_mehp24_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    err, exact = out.get(timeout=300)
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert err < 0.01 and exact
