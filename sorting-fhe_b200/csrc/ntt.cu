@@ -29,6 +29,18 @@ typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
 
 __device__ __forceinline__ int padi(int e) { return e + (e >> 3); }
 
+// 256-bit global accesses (sm_100: LDG/STG.E.256).  In the round whose window sits at bit 0 a thread owns 8 consecutive
+// words (64 bytes); eight 8-byte accesses at a 64-byte lane stride touch 32 sectors per request, a quarter filled each
+// (ncu: 32 sectors and 16 wavefronts per store request) -- two 32-byte accesses write / read whole sectors.
+__device__ __forceinline__ void ld256(const u64* p, u64& a, u64& b, u64& c, u64& d) {
+    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+}
+__device__ __forceinline__ void st256(u64* p, u64 a, u64 b, u64 c, u64 d) {
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(a), "l"(b), "l"(c), "l"(d) : "memory");
+}
+__device__ __forceinline__ void load8(const u64* p, u64 (&v)[8]) { ld256(p, v[0], v[1], v[2], v[3]); ld256(p + 4, v[4], v[5], v[6], v[7]); }
+__device__ __forceinline__ void store8(u64* p, const u64 (&v)[8]) { st256(p, v[0], v[1], v[2], v[3]); st256(p + 4, v[4], v[5], v[6], v[7]); }
+
 // element index (tile-local) of register k of thread u in a round whose 3-bit window sits at bit p
 __device__ __forceinline__ int local_index(int u, int k, int p) {
     return ((u >> p) << (p + 3)) | (k << p) | (u & ((1 << p) - 1));
@@ -230,11 +242,14 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
                         // out = (in - NTT(switched last limb)) * q_last^-1   (DropLastElementAndScale)
                         const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
                         const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
+                        u64 xin[8];
+                        if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
+                        else {
 #pragma unroll
-                        for (int k = 0; k < 8; k++) {
-                            const u64 x = ein[gaddr(local_index(u, k, p))];
-                            r[k] = shoup_mul(sub_mod(x, r[k], q), sc.x, sc.y, q);
+                            for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
                         }
+#pragma unroll
+                        for (int k = 0; k < 8; k++) r[k] = shoup_mul(sub_mod(xin[k], r[k], q), sc.x, sc.y, q);
                     }
                 } else {
                     const tw_t sc = A.scale[mid];
@@ -244,8 +259,11 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
             } else if (INV && FIX) {
                 // between inverse passes the FIX path keeps values < 2q already
             }
+            if (!strided && p == 0) store8(dst + gaddr(local_index(u, 0, 0)), r);
+            else {
 #pragma unroll
-            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = r[k];
+                for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = r[k];
+            }
         }
     }
 }
@@ -453,22 +471,34 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
                 if (A.f.epi == EPI_RESCALE) {
                     const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
                     const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
+                    u64 xin[8];
+                    if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
+                    else {
 #pragma unroll
-                    for (int k = 0; k < 8; k++) {
-                        const u64 x = ein[gaddr(local_index(u, k, p))];
-                        v[k] = shoup_mul(sub_mod(x, v[k], qi), sc.x, sc.y, qi);
+                        for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
                     }
+#pragma unroll
+                    for (int k = 0; k < 8; k++) v[k] = shoup_mul(sub_mod(xin[k], v[k], qi), sc.x, sc.y, qi);
                 }
             } else {
                 const double sc = (double)A.scale[mid].x;
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(fp_mulmod(r[k], sc, q, qinv), q, qinv);
             }
+            if (!strided && p == 0) store8(dst + gaddr(local_index(u, 0, 0)), v);
+            else {
 #pragma unroll
-            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = v[k];
+                for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = v[k];
+            }
         } else {
+            u64 v[8];
 #pragma unroll
-            for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = (u64)__double_as_longlong(r[k]);
+            for (int k = 0; k < 8; k++) v[k] = (u64)__double_as_longlong(r[k]);
+            if (!strided && p == 0) store8(dst + gaddr(local_index(u, 0, 0)), v);
+            else {
+#pragma unroll
+                for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = v[k];
+            }
         }
     }
 }
@@ -482,6 +512,7 @@ __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, con
     const int cb = T - a_, p = LOGN_C ? SC.p[0] : SR.p[0];
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
+    if (!strided && p == 0) { load8(src + (((size_t)tile << T) | (size_t)(threadIdx.x * 8)), v); return; }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
         const int L = local_index(threadIdx.x, k, p);
