@@ -14,7 +14,7 @@
 //     (last T stages) on contiguous chunks;
 //   * every thread keeps 8 words in registers and runs up to 3 stages per round; the first round of a pass
 //     loads straight from global memory (coalesced 256 B runs), the last one stores straight back, only the
-//     rounds in between exchange through (padded, conflict-free) shared memory;
+//     rounds in between exchange through (XOR-swizzled, conflict-free) shared memory;
 //   * butterflies are lazy (Harvey): no per-butterfly correction for moduli < 2^58 forward / < 2^46 inverse
 //     (values may grow to (2s+1)q resp. 2^s q < 2^64); larger moduli use one conditional subtraction;
 //   * twiddles are (w, floor(w 2^64 / q)) pairs fetched with one 16-byte load; rounds touch 1, 2 and 4
@@ -27,7 +27,15 @@
 static constexpr int TB_MAX = 10;
 typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
 
-__device__ __forceinline__ int padi(int e) { return e + (e >> 3); }
+// Shared-memory slot of tile-local element e: an XOR swizzle, linear over GF(2), that sends the 16 elements a half-warp
+// touches in ANY round window (p = 0..7: element bits {6..3}, {0,6,5,4}, {1,0,6,5}, {2,1,0,6} or {3..0} vary) to 16
+// different 8-byte bank pairs.  (The former padding e + (e >> 3) was 2-way conflicted for every window at p >= 4:
+// ncu counted 786 432 excessive shared wavefronts per 32-limb pass, a third of the shared traffic.)
+__device__ __forceinline__ int swz(int e) { return e ^ ((e >> 4) & 7) ^ (((0x96 >> (e & 7)) & 1) << 3); }
+// slot of register k of thread u in the round at window p: swz is linear and the two index parts share no bits
+__device__ __forceinline__ int slot_of(int u, int k, int p) {
+    return swz(((u >> p) << (p + 3)) | (u & ((1 << p) - 1))) ^ swz(k << p);
+}
 
 // 256-bit global accesses (sm_100: LDG/STG.E.256).  In the round whose window sits at bit 0 a thread owns 8 consecutive
 // words (64 bytes); eight 8-byte accesses at a 64-byte lane stride touch 32 sectors per request, a quarter filled each
@@ -217,7 +225,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         } else {
             __syncthreads();
 #pragma unroll
-            for (int k = 0; k < 8; k++) r[k] = sm[padi(local_index(u, k, p))];
+            for (int k = 0; k < 8; k++) r[k] = sm[slot_of(u, k, p)];
         }
         // element-index bits above the window, and the global stage of window bit 2 (j = 0)
         const int L0 = local_index(u, 0, p);
@@ -229,7 +237,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         if (ri + 1 < (LOGN_C ? SC.nr : SR.nr)) {
             __syncthreads();
 #pragma unroll
-            for (int k = 0; k < 8; k++) sm[padi(local_index(u, k, p))] = r[k];
+            for (int k = 0; k < 8; k++) sm[slot_of(u, k, p)] = r[k];
         } else {
             if (A.final_pass) {
                 if (!INV) {
@@ -445,7 +453,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
         } else {
             __syncthreads();
 #pragma unroll
-            for (int k = 0; k < 8; k++) r[k] = smd[padi(local_index(u, k, p))];
+            for (int k = 0; k < 8; k++) r[k] = smd[slot_of(u, k, p)];
         }
         if (INV && (ri & 1) == 0 && !(ri == 0 && A.first_pass)) {   // fold the doubling of the GS sums back below q
 #pragma unroll
@@ -462,7 +470,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
         if (ri + 1 < nr) {
             __syncthreads();
 #pragma unroll
-            for (int k = 0; k < 8; k++) smd[padi(local_index(u, k, p))] = r[k];
+            for (int k = 0; k < 8; k++) smd[slot_of(u, k, p)] = r[k];
         } else if (A.final_pass) {
             u64 v[8];
             if (!INV) {
@@ -584,7 +592,7 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     if (c->dry || rows == 0) return;
     ProfScope ps(c, KC_NTT, 16.0 * rows * (c->n >> lrep), (logn > TB_MAX) ? 2 : 1);
     const int threads = (1 << T) / 8;
-    const size_t smem = (size_t)((1 << T) + ((1 << T) >> 3) + 8) * sizeof(u64);
+    const size_t smem = (size_t)((1 << T) < 16 ? 16 : (1 << T)) * sizeof(u64);
     const int tpr_log = logn - T, total = rows << tpr_log;   // tiles per row (log2), work items
     NttArgs A;
     A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a; A.twlog = c->log_n;
