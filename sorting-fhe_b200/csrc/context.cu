@@ -220,7 +220,7 @@ static void fill_conv(Context* c, ConvTables& t, const std::vector<int>& in_ids,
         t.split_ok = ok;
     }
     t.wide = 0;
-    for (int i = 0; i < t.nin && i < 32; i++) if (c->moduli[in_ids[i]] >> 40) t.wide |= 1u << i;
+    for (int i = 0; i < t.nin && i < 32; i++) if (c->moduli[in_ids[i]] >> 42) t.wide |= 1u << i;
     for (int j = 0; j < t.nout; j++) t.out_ids[j] = (short)out_ids[j];
     t.d_hatinv = upload(c, hatinv); t.d_hatinv_sh = upload(c, hatinv_sh); t.d_hatmod = upload(c, hatmod);
 }

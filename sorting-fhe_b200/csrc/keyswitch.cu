@@ -108,6 +108,86 @@ template <int NI>
 static void launch_conv_split(Context* c, dim3 grid, size_t smem, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
     launch_pdl(c, k_conv_split<NI>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
 }
+// The conversion on the FP64 pipe.  B200 issues DFMA at 64 lanes/clk/SM, twice the rate ncu shows for IMAD.WIDE (fma pipe
+// 36 % busy at 4 cycles per warp instruction in k_conv_split), and a double holds a 53-bit integer exactly: residues and
+// constants are cut into 21-bit pieces (two for a modulus of at most 42 bits -- the 40-bit scaling primes straddle 2^40 --,
+// three up to 60 bits), every product is below 2^42 and a column (all products of equal weight, at most 3 x 12 of them)
+// stays below 2^48.  A term costs 4 (narrow
+// residue x narrow constant) to 9 DFMA and nothing else; the columns are turned back into integers once per output,
+//   total = s0 + s1 2^21 + s2 2^42 + s3 2^63 + s4 2^84,
+// the same integer k_conv_batch / k_conv_split accumulate, followed by the same Montgomery reduction.
+// WMODE: 0 = every source modulus has at most 42 bits, 1 = only the first one is wider (the digit that holds q0),
+// 2 = any (third piece kept for every source limb: ModDown from the 60-bit special primes).
+__device__ __forceinline__ double piece_to_double(u32 v) { return __dadd_rn(__hiloint2double(0x43300000, (int)v), -4503599627370496.0); }
+__device__ __forceinline__ u64 column_to_u64(double s) {   // integer s in [0, 2^52)
+    return (u64)__double_as_longlong(__dadd_rn(s, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFULL;
+}
+template <int NI, int WMODE>
+__global__ void __launch_bounds__(256)
+k_conv_fp(u64* __restrict__ out, const u64* __restrict__ in, const __grid_constant__ ConvBatch B, const ModInfo* __restrict__ mi, int n,
+          int ysplit) {
+    pdl_sync();
+    extern __shared__ double2 sh_c[];                     // [jc][NI][2]: (c0, c1), (c2, 0) -- 21-bit digits of the constants
+    const int gi = blockIdx.y / ysplit, part = blockIdx.y - gi * ysplit;
+    const int nin = B.g[gi].nin, nout = B.g[gi].nout;
+    const int per = (nout + ysplit - 1) / ysplit, jlo = part * per, jc = min(per, nout - jlo);
+    if (jc <= 0) return;
+    const u64* __restrict__ hat = B.g[gi].hatmod;
+    for (int t = threadIdx.x; t < NI * jc; t += blockDim.x) {
+        const int jj = t / NI, i = t - jj * NI;
+        const u64 h = i < nin ? hat[(size_t)i * nout + jlo + jj] : 0;
+        sh_c[2 * t] = make_double2((double)((u32)h & 0x1FFFFFu), (double)((u32)(h >> 21) & 0x1FFFFFu));
+        sh_c[2 * t + 1] = make_double2((double)(u32)(h >> 42), 0.0);
+    }
+    __syncthreads();
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= n) return;
+    constexpr int NW = WMODE == 2 ? NI : 1;
+    double y0[NI], y1[NI], y2[NW];
+    const u64* src = in + (size_t)B.g[gi].in_row0 * n + x;
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        const u64 v = i < nin ? src[(size_t)i * n] : 0;
+        y0[i] = piece_to_double((u32)v & 0x1FFFFFu);
+        y1[i] = piece_to_double((u32)(v >> 21) & 0x1FFFFFu);
+        if (i < NW) y2[i] = piece_to_double((u32)(v >> 42));
+    }
+    u64* dst = out + (size_t)(B.g[gi].out_row0 + jlo) * n + x;
+    for (int jj = 0; jj < jc; jj++) {
+        const double2* hp = sh_c + 2 * jj * NI;
+        const ModInfo m = mi[B.out_ids[gi][jlo + jj]];
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+        if (m.bits <= 42) {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const double2 c = hp[2 * i];
+                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1);
+                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2);
+                if (WMODE == 2 || (WMODE == 1 && i == 0)) { s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const double2 c = hp[2 * i];
+                const double c2 = hp[2 * i + 1].x;
+                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1); s2 = __fma_rn(y0[i], c2, s2);
+                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2); s3 = __fma_rn(y1[i], c2, s3);
+                if (WMODE == 2 || (WMODE == 1 && i == 0)) {
+                    s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); s4 = __fma_rn(y2[i], c2, s4);
+                }
+            }
+        }
+        u64 lo = column_to_u64(s0), hi = column_to_u64(s4) << 20;
+        add_shifted(lo, hi, column_to_u64(s1), 21); add_shifted(lo, hi, column_to_u64(s2), 42); add_shifted(lo, hi, column_to_u64(s3), 63);
+        dst[(size_t)jj * n] = mont_reduce(lo, hi, m.q, m.qinv);
+    }
+}
+template <int NI>
+static void launch_conv_fp(Context* c, dim3 grid, size_t smem, int wmode, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
+    if (wmode == 0) launch_pdl(c, k_conv_fp<NI, 0>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+    else if (wmode == 1) launch_pdl(c, k_conv_fp<NI, 1>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+    else launch_pdl(c, k_conv_fp<NI, 2>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+}
 void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) {
     KL(c);
     double rows = 0; int max_in = 0, max_out = 0;
@@ -115,7 +195,23 @@ void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) 
     ProfScope ps(c, KC_BASECONV, 8.0 * c->n * rows);
     static const int ysplit = getenv("CKKS_B200_CONV_YSPLIT") ? atoi(getenv("CKKS_B200_CONV_YSPLIT")) : 2;
     static const bool generic = getenv("CKKS_B200_GENERIC_CONV") != nullptr;
-    if (B.split_ok && !generic && c->n >= 512) {
+    static const bool int_conv = getenv("CKKS_B200_INT_CONV") != nullptr;   // A/B switch: the integer-pipe kernel
+    if (B.split_ok && !generic && !int_conv && c->n >= 512) {
+        int wmode = 0;
+        for (int i = 0; i < B.ng; i++) wmode = std::max(wmode, B.g[i].wide == 0 ? 0 : B.g[i].wide == 1 ? 1 : 2);
+        dim3 grid((c->n + 255) / 256, B.ng * ysplit);
+        const int ni = max_in <= 2 ? 2 : max_in <= 4 ? 4 : max_in <= 6 ? 6 : max_in <= 8 ? 8 : max_in <= 10 ? 10 : max_in <= 11 ? 11 : 12;
+        const size_t smem = (size_t)ni * ((max_out + ysplit - 1) / ysplit) * 2 * sizeof(double2);
+        switch (ni) {
+            case 2: launch_conv_fp<2>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            case 4: launch_conv_fp<4>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            case 6: launch_conv_fp<6>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            case 8: launch_conv_fp<8>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            case 10: launch_conv_fp<10>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            case 11: launch_conv_fp<11>(c, grid, smem, wmode, out, in, B, ysplit); break;
+            default: launch_conv_fp<12>(c, grid, smem, wmode, out, in, B, ysplit); break;
+        }
+    } else if (B.split_ok && !generic && c->n >= 512) {
         dim3 grid((c->n / 2 + 255) / 256, B.ng * ysplit);
         const int ni = max_in <= 2 ? 2 : max_in <= 4 ? 4 : max_in <= 6 ? 6 : max_in <= 8 ? 8 : max_in <= 10 ? 10 : max_in <= 11 ? 11 : 12;
         const size_t smem = (size_t)ni * ((max_out + ysplit - 1) / ysplit) * sizeof(uint4);
