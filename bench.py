@@ -34,7 +34,7 @@ SIGN_CFG = {4: (3, 2, 2), 8: (3, 2, 2), 16: (3, 2, 2), 32: (3, 3, 2), 64: (3, 3,
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--n", type=int, default=128)
@@ -61,10 +61,12 @@ while True:
 
 class ClockSampler:
     """SM clock and throttle reasons of one GPU, sampled through NVML twice a second by a small child process that is
-    started before the warm-up; stop() keeps the samples that fall inside the timed region.  (A looping
-    `nvidia-smi -lms` child per rank stalled the kernel launches of the other ranks on a multi-GPU box -- the 2-GPU
-    step took 2.8x longer with it -- and NVML queries themselves stall the driver for a few ms each: at 10 Hz the N=1 step was 20-50 % slower, so the
-    rate is 2 Hz.)"""
+    started (and has initialised NVML) before the warm-up; stop() keeps the samples that fall inside the timed region.
+    (A looping `nvidia-smi -lms` child per rank stalled the kernel launches of the other ranks on a multi-GPU box -- the
+    2-GPU step took 2.8x longer with it -- and every NVML query stalls the launch path for ~10 ms: at 10 Hz the N=1 step
+    was 20-50 % slower, so the rate is 2 Hz and the default region is 10 steps (~0.77 s, two samples, +3 % on `value`;
+    with 3 steps the region was bimodal, 75 or 81-83 ms per sort depending on whether a sample fell inside).  Samples
+    requested from the parent at fixed points of the region were measured worse: 80-156 ms per sort.)"""
     BAD = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
@@ -72,14 +74,16 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(self.index)], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.lines.append(self.proc.stdout.readline())   # "max ...": NVML is initialised (its attach stalls the GPU) before anything is timed
+            threading.Thread(target=lambda: [self.lines.append(ln) for ln in self.proc.stdout], daemon=True).start()
         except OSError:
             self.proc = None
 
     def mark(self):                 # the timed region starts here
         self.t0 = time.time()
+
 
     def stop(self):
         t1 = time.time()
@@ -272,6 +276,8 @@ def run_b200(args):
     for i in range(K):
         cts[i].slots = n                                 # sort() widens the caller's metadata (sort_algo.h:711)
         outs.append(sorter.sort(cts[i], cfg))
+        eng.sync()                                       # one result at a time, as in the e2e region: the host never runs
+                                                         # more than one sort (6 000 launches) ahead of the device
     e1.record(stream)
     barrier()
     t_dev = e0.elapsed_time(e1) / 1e3

@@ -520,12 +520,14 @@ __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, con
     const int cb = T - a_, p = LOGN_C ? SC.p[0] : SR.p[0];
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
-    if (!strided && p == 0) { load8(src + (((size_t)tile << T) | (size_t)(threadIdx.x * 8)), v); return; }
+    if (!strided && p == 0) load8(src + (((size_t)tile << T) | (size_t)(threadIdx.x * 8)), v);
+    else {
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const int L = local_index(threadIdx.x, k, p);
-        const size_t g = strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
-        v[k] = src[g];
+        for (int k = 0; k < 8; k++) {
+            const int L = local_index(threadIdx.x, k, p);
+            const size_t g = strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
+            v[k] = src[g];
+        }
     }
 }
 
