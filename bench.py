@@ -130,6 +130,15 @@ def cpu_op_times(log_n, depth, nls, reps=1, slots=16384):
     from oracle.ckks_eval import Ct
     from oracle.ckks_oracle import Context, Params
     from oracle.ckks_ops import OracleCC
+    threads = os.cpu_count() if "OMP_NUM_THREADS" not in os.environ else int(os.environ["OMP_NUM_THREADS"])
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm runs on rank 0 alone and may use every host core
+        import ctypes
+        threads = os.cpu_count()
+        try:
+            ctypes.CDLL("libgomp.so.1").omp_set_num_threads(threads)
+        except OSError:
+            threads = int(os.environ.get("OMP_NUM_THREADS", "1"))
     cc = OracleCC(Context(Params(log_n, depth, 40)))
     cc.keygen(); cc.relin_keygen(); cc.rot_keygen([1])
     c = cc.ctx
@@ -155,7 +164,7 @@ def cpu_op_times(log_n, depth, nls, reps=1, slots=16384):
             out["rescale"][nl] = best(lambda: cc.rescale(a.clone()))
         vals = rng.random(slots)
         out["encode"][nl] = best(lambda: cc.encode(vals, 1, lvl, slots))
-    return out, (os.cpu_count() if "OMP_NUM_THREADS" not in os.environ else int(os.environ["OMP_NUM_THREADS"]))
+    return out, threads
 
 
 def cpu_estimate(trace, times):
