@@ -13,6 +13,13 @@ extern "C" {
 
 const char* sortfhe_last_error(void);
 
+/* The sorter layer keeps one CryptoContext wrapper per engine context; it owns the encoded-plaintext cache (the 0/1 masks
+ * and index patterns of reference src/sort_algo.h:341,356,573,706,718 depend on (N, ring, level) only and are encoded once
+ * per context instead of once per sort).  sortfhe_ctx_release drops that wrapper and its cached plaintext handles: call it
+ * before ckks_ctx_destroy.  sortfhe_plaintext_cache_stats reports entries / device bytes (upper bound) / hits / misses. */
+int sortfhe_ctx_release(ckks_ctx_t* ctx);
+int sortfhe_plaintext_cache_stats(ckks_ctx_t* ctx, int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* misses);
+
 /* DirectSort<N>::getSizeParameters (reference src/sort_algo.h:87-201): multiplicative depth and rotation key
  * set for array size n at the given ring dimension.  Returns the number of rotations through *count. */
 int sortfhe_direct_sort_params(int n, int ring_dim, int* mult_depth, int32_t* rotations, int cap, int* count);

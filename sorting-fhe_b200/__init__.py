@@ -120,8 +120,15 @@ class Engine:
 
     def close(self):
         if self.h:
+            _H.sortfhe_ctx_release(_vp(self.h))      # sorter-layer wrapper + its cached plaintext handles
             _L.ckks_ctx_destroy(_vp(self.h))
             self.h = None
+
+    def plaintext_cache_stats(self):
+        """(entries, device bytes upper bound, hits, misses) of the sorter layer's encoded-plaintext cache"""
+        v = [ctypes.c_int64() for _ in range(4)]
+        _hchk(_H.sortfhe_plaintext_cache_stats(_vp(self.h), *[ctypes.byref(x) for x in v]))
+        return tuple(x.value for x in v)
 
     def info(self, what):
         o = ctypes.c_int64()
@@ -381,6 +388,8 @@ _H = ctypes.CDLL(HOST_LIB_PATH)
 _H.sortfhe_last_error.restype = ctypes.c_char_p
 _i32p = ctypes.POINTER(ctypes.c_int32)
 _ip = ctypes.POINTER(ctypes.c_int)
+_H.sortfhe_ctx_release.argtypes = [_vp]
+_H.sortfhe_plaintext_cache_stats.argtypes = [_vp] + [ctypes.POINTER(ctypes.c_int64)] * 4
 _H.sortfhe_direct_sort_params.argtypes = [_i, _i, _ip, _i32p, _i, _ip]
 _H.sortfhe_hybrid_sort_params.argtypes = [_i, _i, _i, _ip, _i32p, _i, _ip]
 _H.sortfhe_hybrid_sort.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i32p, _i, _pp]

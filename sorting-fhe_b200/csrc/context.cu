@@ -12,6 +12,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <algorithm>
+#include <atomic>
 
 typedef unsigned __int128 u128;
 
@@ -69,6 +70,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
                       uint64_t seed, int dry) {
     c->log_n = log_n; c->n = 1 << log_n; c->mult_depth = mult_depth; c->scaling_bits = scaling_bits;
     c->first_bits = first_bits; c->ext = ext; c->seed = seed; c->dry = dry != 0;
+    { static std::atomic<uint64_t> next_uid{1}; c->uid = next_uid++; }
     if (log_n < 8 || log_n > 17) throw std::runtime_error("ring dimension must be 2^8..2^17");
     const u64 m = 2ull * c->n;
     const int num_primes = mult_depth + 1, size_q = num_primes + (ext ? 1 : 0);

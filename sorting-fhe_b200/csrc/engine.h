@@ -84,6 +84,7 @@ struct Context {
     int log_n = 0, n = 0, mult_depth = 0, scaling_bits = 0, first_bits = 0, ext = 1;
     int size_q = 0, size_p = 0, alpha = 0, num_part_q = 0;
     uint64_t seed = 1;
+    uint64_t uid = 0;      // process-unique id (ckks_ctx_info selector 8): lets caches keyed by the handle detect address reuse
     bool dry = false;      // metadata-only mode: no device allocations, no kernel launches
     bool enc_offload = true;   // plaintext level / scale adjustments run on the encode stream (CKKS_B200_NO_ENC_OFFLOAD=1 turns it off)
     bool host_prof = false;
@@ -135,6 +136,7 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     double sf;
     int slots;
     mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
+    mutable Ct* lift = nullptr;   // plaintexts only: cached x 1.0 twin (noiseScaleDeg + 1, owned); see lifted_twin()
     mutable cudaEvent_t ready = nullptr;   // recorded on the encode stream; the first consumer makes the main stream wait on it
     mutable u64* modup = nullptr; // cached ModUp of c1 (owned): shared by all rotations of this ciphertext (hoisting)
     // Plaintexts are encoded on the encode stream, and the level / scale adjustments a multiplication applies to them

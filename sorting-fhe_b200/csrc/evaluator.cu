@@ -41,6 +41,7 @@ Ct* ct_clone(const Ct* a) {
 }
 static void drop_twin(const Ct* a) {
     if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); }
+    if (a->lift) { Ct* t = a->lift; a->lift = nullptr; ct_free(t); }
     if (a->modup) { dev_free(a->ctx, a->modup); a->modup = nullptr; }
 }
 static void wait_enc_reader(const Ct* a) {
@@ -94,6 +95,7 @@ static void ct_steal(Ct* a, Ct* t) {
     dev_free(a->ctx, a->d);
     a->d = t->d; a->parts = t->parts; a->nl = t->nl; a->level = t->level; a->deg = t->deg; a->sf = t->sf; a->lrep = t->lrep;
     a->resc = t->resc; t->resc = nullptr;
+    a->lift = t->lift; t->lift = nullptr;
     a->ready = t->ready; t->ready = nullptr; a->enc_reader = t->enc_reader; t->enc_reader = nullptr; a->enc_home = t->enc_home;
     t->d = nullptr;
     ct_free(t);
@@ -153,7 +155,18 @@ static Ct* level_reduce_new(const Ct* a, int levels) {
                          words(c, nl2, a->lrep));
     return r;
 }
-static void op_mult_const(Opnd& o, double x) { o.set_own(mult_const_new(o.v, x)); }
+// A pristine plaintext that has to gain a scale degree (EvalMult(ct of degree 2, pt): AdjustLevelsAndDepth multiplies
+// the plaintext by 1.0) gets that twin cached on the handle like the rescaled one: the sorters' masks are the same
+// handles in every sort (host/openfhe_shim.h plaintext cache), so the adjustment is computed once per context.
+static const Ct* lifted_twin(const Ct* a) {
+    if (!a->lift) a->lift = mult_const_new(a, 1.0);
+    else count(a->ctx, "lift_cached", a->nl);
+    return a->lift;
+}
+static void op_mult_const(Opnd& o, double x) {
+    if (!o.own && o.v->parts == 1 && x == 1.0) { o.v = lifted_twin(o.v); ct_wait(o.v); return; }
+    o.set_own(mult_const_new(o.v, x));
+}
 static void op_rescale(Opnd& o) { if (o.own) o.set_own(rescale_new(o.v)); else o.v = rescaled_twin(o.v); }
 static void op_level_reduce(Opnd& o, int levels) { if (levels > 0) o.set_own(level_reduce_new(o.v, levels)); }
 static void op_set_sf(Opnd& o, double sf) {
@@ -224,8 +237,12 @@ static void adjust_to_one(Opnd& a, Opnd& b) {
 static void commit(Ct* a, Opnd& o) {
     if (o.v == a) return;
     if (o.own) { ct_steal(a, o.release()); return; }
-    // o.v is a's cached twin: a becomes its twin
-    Ct* t = a->resc; a->resc = nullptr;
+    // o.v is one of a's cached twins: a becomes that twin
+    Ct* t;
+    if (o.v == a->resc) { t = a->resc; a->resc = nullptr; }
+    else if (o.v == a->lift) { t = a->lift; a->lift = nullptr; }
+    else if (a->lift && o.v == a->lift->resc) { t = a->lift->resc; a->lift->resc = nullptr; }
+    else throw std::runtime_error("internal: operand view is not a twin of its ciphertext");
     ct_steal(a, t);
 }
 void mult_core_const(Ct* a, double x) { Opnd o(a); op_mult_const(o, x); commit(a, o); }

@@ -1,6 +1,8 @@
 // capi_host.cpp -- extern "C" boundary of the sorter layer (include/sortfhe_host.h).
 #include "../../include/sortfhe_host.h"
 #include <cstring>
+#include <map>
+#include <mutex>
 #include "sort_algo.h"
 #include "mehp24.h"
 #include "kway.h"
@@ -12,7 +14,24 @@ typedef Ciphertext<DCRTPoly> CT;
 #define HOST_BEGIN try {
 #define HOST_END return 0; } catch (const std::exception& e) { g_err = e.what(); return 1; } catch (...) { g_err = "unknown error"; return 2; }
 
-CryptoContext<DCRTPoly> borrow(ckks_ctx_t* c, int batch) { return std::make_shared<CryptoContextImpl>(c, false, (uint32_t)batch); }
+// One persistent CryptoContext wrapper per (engine context, batch size): it carries the encoded-plaintext cache
+// (openfhe_shim.h), which has to outlive the individual C calls.  The engine's process-unique context id guards against a
+// new context reusing the address of a destroyed one; sortfhe_ctx_release drops the wrappers (and with them the cached
+// plaintext handles that keep the engine context alive) -- callers invoke it before ckks_ctx_destroy.
+std::mutex g_reg_mu;
+struct RegEntry { int64_t uid = 0; std::map<int, CryptoContext<DCRTPoly>> by_batch; };
+std::map<ckks_ctx_t*, RegEntry> g_reg;
+CryptoContext<DCRTPoly> borrow(ckks_ctx_t* c, int batch) {
+    if (!c) throw std::runtime_error("null context");
+    int64_t uid = 0;
+    ckks_check(ckks_ctx_info(c, 8, &uid), "ctx_info");
+    std::lock_guard<std::mutex> g(g_reg_mu);
+    RegEntry& e = g_reg[c];
+    if (e.uid != uid) { e.by_batch.clear(); e.uid = uid; }
+    auto& w = e.by_batch[batch];
+    if (!w) w = std::make_shared<CryptoContextImpl>(c, false, (uint32_t)batch);
+    return w;
+}
 CT borrow(const ckks_ct_t* h) {
     if (!h) throw std::runtime_error("null ciphertext handle");
     return std::make_shared<CiphertextImpl>(const_cast<ckks_ct_t*>(h), false);
@@ -50,6 +69,31 @@ template <int N> std::unique_ptr<DirectSort<N>> make_sorter(ckks_ctx_t* ctx, con
 
 extern "C" {
 const char* sortfhe_last_error(void) { return g_err.c_str(); }
+
+int sortfhe_ctx_release(ckks_ctx_t* ctx) {
+    HOST_BEGIN
+    std::map<int, CryptoContext<DCRTPoly>> drop;
+    {
+        std::lock_guard<std::mutex> g(g_reg_mu);
+        auto it = g_reg.find(ctx);
+        if (it != g_reg.end()) { drop.swap(it->second.by_batch); g_reg.erase(it); }
+    }
+    drop.clear();   // frees the cached plaintext handles outside the registry lock
+    HOST_END
+}
+int sortfhe_plaintext_cache_stats(ckks_ctx_t* ctx, int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* misses) {
+    HOST_BEGIN
+    *entries = *bytes = *hits = *misses = 0;
+    std::lock_guard<std::mutex> g(g_reg_mu);
+    auto it = g_reg.find(ctx);
+    if (it != g_reg.end())
+        for (auto& kv : it->second.by_batch) {
+            std::lock_guard<std::mutex> g2(kv.second->pt_mu);
+            *entries += (int64_t)kv.second->pt_cache.size(); *bytes += (int64_t)kv.second->pt_bytes;
+            *hits += (int64_t)kv.second->pt_hits; *misses += (int64_t)kv.second->pt_misses;
+        }
+    HOST_END
+}
 
 int sortfhe_direct_sort_params(int n, int ring_dim, int* mult_depth, int32_t* rotations, int cap, int* count) {
     HOST_BEGIN

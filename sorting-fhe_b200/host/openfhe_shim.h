@@ -9,13 +9,18 @@
 // to one extern "C" entry point.  OpenFHE exceptions become std::runtime_error carrying ckks_last_error().
 // No arithmetic happens on the host: every member ends in a CUDA kernel launch inside libckks_b200.so.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
+#include <deque>
 #include <functional>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/ckks_b200.h"
@@ -159,10 +164,39 @@ class CryptoContextImpl {
     void ClearEvalAutomorphismKeys() {}
 
     // ---- encode / encrypt / decrypt
-    Plaintext MakeCKKSPackedPlaintext(const std::vector<double>& v, size_t scaleDeg = 1, uint32_t level = 0,
-                                      const void* params = nullptr, uint32_t slots = 0) const {
-        (void)params;
-        uint32_t s = slots ? slots : (batchSize ? batchSize : GetRingDimension() / 2);
+    // Encoded-plaintext cache.  The sorters encode the same 0/1 masks and index patterns in every sort (258 per
+    // DirectSort<128>::sort: reference src/sort_algo.h:341,356,573,706,718); they depend on (N, ring, level, slots) only.
+    // An encoded Plaintext is immutable, so MakeCKKSPackedPlaintext hands out the SAME handle for the same
+    // (values, scaleDeg, level, slots) -- bit-identical by construction, and the level / scale adjustments the engine
+    // caches on a plaintext handle (rescaled and lifted twins) are reused with it.  Entries are found by a 128-bit hash
+    // of the values and confirmed by comparing the values themselves; the keyed form below skips generating and hashing
+    // the vector.  FIFO eviction above SORTFHE_PT_CACHE_MB (default 16384) of device bytes; SORTFHE_PT_CACHE_MB=0 turns
+    // the cache off.  Guarded by a mutex: the reference encodes from OpenMP threads (sort_algo.h:349-362).
+    struct PtKey {
+        uint64_t h[2]; uint32_t scaleDeg, level, slots, len;
+        bool operator<(const PtKey& o) const {
+            return std::tie(h[0], h[1], scaleDeg, level, slots, len) < std::tie(o.h[0], o.h[1], o.scaleDeg, o.level, o.slots, o.len);
+        }
+    };
+    struct PtEntry { std::vector<double> values; Plaintext pt; size_t bytes; };
+    mutable std::mutex pt_mu;
+    mutable std::map<PtKey, PtEntry> pt_cache;
+    mutable std::deque<PtKey> pt_order;
+    mutable size_t pt_bytes = 0, pt_hits = 0, pt_misses = 0;
+    static size_t pt_cap_bytes() {
+        static const size_t cap = [] { const char* e = getenv("SORTFHE_PT_CACHE_MB"); return (size_t)(e ? atoll(e) : 16384) << 20; }();
+        return cap;
+    }
+    static void hash128(const void* data, size_t bytes, uint64_t out[2]) {   // two multiply-xorshift lanes over 8-byte words
+        const uint64_t* w = (const uint64_t*)data; const size_t nw = bytes / 8;
+        uint64_t a = 0x9E3779B97F4A7C15ull ^ bytes, b = 0xC2B2AE3D27D4EB4Full + bytes;
+        for (size_t i = 0; i < nw; i++) {
+            a = (a ^ w[i]) * 0xFF51AFD7ED558CCDull; a ^= a >> 32;
+            b = (b + w[i]) * 0xC4CEB9FE1A85EC53ull; b ^= b >> 29;
+        }
+        out[0] = a; out[1] = b;
+    }
+    Plaintext encodeNow(const std::vector<double>& v, size_t scaleDeg, uint32_t level, uint32_t s) const {
         ckks_ct_t* o = nullptr;
         ckks_check(ckks_make_packed_plaintext(ctx, v.data(), (int)v.size(), (int)scaleDeg, (int)level, (int)s, &o),
                    "MakeCKKSPackedPlaintext");
@@ -170,6 +204,60 @@ class CryptoContextImpl {
         p->enc = wrap(o);
         return p;
     }
+    void ptInsert(const PtKey& k, PtEntry&& e) const {   // pt_mu held
+        const size_t cap = pt_cap_bytes();
+        while (!pt_order.empty() && pt_bytes + e.bytes > cap) {
+            auto it = pt_cache.find(pt_order.front());
+            if (it != pt_cache.end()) { pt_bytes -= it->second.bytes; pt_cache.erase(it); }
+            pt_order.pop_front();
+        }
+        if (e.bytes > cap) return;
+        pt_bytes += e.bytes;
+        pt_order.push_back(k);
+        pt_cache.emplace(k, std::move(e));
+    }
+    size_t ptDeviceBytes(uint32_t level, uint32_t slots) const {
+        // encoded form plus its two cached twins; compact storage keeps min(ring, 2 * slots) (>= 256) words per limb
+        const size_t ring = (size_t)info(0), words = std::min(ring, std::max<size_t>(256, 2 * (size_t)slots));
+        return (size_t)3 * (size_t)std::max<int64_t>(1, info(1) - (int64_t)level) * words * 8;
+    }
+    Plaintext MakeCKKSPackedPlaintext(const std::vector<double>& v, size_t scaleDeg = 1, uint32_t level = 0,
+                                      const void* params = nullptr, uint32_t slots = 0) const {
+        (void)params;
+        uint32_t s = slots ? slots : (batchSize ? batchSize : GetRingDimension() / 2);
+        if (pt_cap_bytes() == 0) return encodeNow(v, scaleDeg, level, s);
+        PtKey k; hash128(v.data(), v.size() * sizeof(double), k.h);
+        k.scaleDeg = (uint32_t)scaleDeg; k.level = level; k.slots = s; k.len = (uint32_t)v.size();
+        std::lock_guard<std::mutex> g(pt_mu);
+        auto it = pt_cache.find(k);
+        if (it != pt_cache.end() && it->second.values == v) { pt_hits++; return it->second.pt; }
+        pt_misses++;
+        Plaintext p = encodeNow(v, scaleDeg, level, s);
+        if (it == pt_cache.end()) ptInsert(k, PtEntry{v, p, ptDeviceBytes(level, s)});
+        return p;
+    }
+    // Keyed form for generated patterns: `key` names the pattern (generator tag + its integer arguments); the vector is
+    // only generated on a miss.  Extension used by host/sort_algo.h; the result is the handle the plain call would return.
+    template <class Gen>
+    Plaintext MakeCKKSPackedPlaintextKeyed(const std::vector<int64_t>& key, Gen&& gen, size_t scaleDeg, uint32_t level,
+                                           uint32_t slots) const {
+        if (pt_cap_bytes() == 0) return encodeNow(gen(), scaleDeg, level, slots);
+        PtKey k; hash128(key.data(), key.size() * sizeof(int64_t), k.h);
+        k.h[0] ^= 0x5bd1e9955bd1e995ull;                  // keyed entries live in their own hash space
+        k.scaleDeg = (uint32_t)scaleDeg; k.level = level; k.slots = slots; k.len = (uint32_t)key.size() | 0x80000000u;
+        std::lock_guard<std::mutex> g(pt_mu);
+        auto it = pt_cache.find(k);
+        if (it != pt_cache.end() && it->second.values.size() == key.size() &&
+            std::equal(key.begin(), key.end(), it->second.values.begin(), [](int64_t a, double b) { return (double)a == b; })) {
+            pt_hits++;
+            return it->second.pt;
+        }
+        pt_misses++;
+        Plaintext p = encodeNow(gen(), scaleDeg, level, slots);
+        if (it == pt_cache.end()) ptInsert(k, PtEntry{std::vector<double>(key.begin(), key.end()), p, ptDeviceBytes(level, slots)});
+        return p;
+    }
+    void ClearPlaintextCache() const { std::lock_guard<std::mutex> g(pt_mu); pt_cache.clear(); pt_order.clear(); pt_bytes = 0; }
     CT Encrypt(const PublicKey<DCRTPoly>&, const Plaintext& pt) const {
         ckks_ct_t* o = nullptr; ckks_check(ckks_encrypt(ctx, enc_of(pt)->h, &o), "Encrypt"); return wrap(o);
     }

@@ -166,8 +166,10 @@ template <int N> class DirectSort : public SortBase<N> {
             T->SetSlots(num_slots);
             std::vector<Plaintext> pmsk(np);
             for (int i = 0; i < np; i++) {
-                auto msk = vectorRotate(generateMaskVector(num_slots, np * j + i), -is * num_partition - j * np);
-                pmsk[i] = m_cc->MakeCKKSPackedPlaintext(msk, 1, 0, nullptr, num_slots);
+                // the masks depend on (N, slots, block, shift) only: encoded once per context, same handle every sort
+                const int k = np * j + i, shift = -is * num_partition - j * np;
+                pmsk[i] = m_cc->MakeCKKSPackedPlaintextKeyed({1, N, num_slots, k, shift},
+                    [&] { return vectorRotate(generateMaskVector(num_slots, k), shift); }, 1, 0, (uint32_t)num_slots);
             }
             // T = EvalAdd(T, EvalMult(preRotatedArrays[i], pmsk[i])) for every i (:343-344), as one engine call
             T = m_cc->EvalInnerProductPlain(T, std::vector<CT>(preRotatedArrays.begin(), preRotatedArrays.begin() + np), pmsk);
@@ -219,8 +221,9 @@ template <int N> class DirectSort : public SortBase<N> {
             CT tmp = this->getZero()->Clone();
             std::vector<Plaintext> pmsk(np);
             for (int j = 0; j < np; j++) {
-                auto msk = vectorRotate(generateMaskVectorN(num_slots, np * i + j), j);
-                pmsk[j] = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)masked_inputs[j]->GetLevel(), nullptr, num_slots);
+                const int k = np * i + j;
+                pmsk[j] = m_cc->MakeCKKSPackedPlaintextKeyed({2, N, num_slots, k, j},
+                    [&] { return vectorRotate(generateMaskVectorN(num_slots, k), j); }, 1, (uint32_t)masked_inputs[j]->GetLevel(), (uint32_t)num_slots);
             }
             tmp = m_cc->EvalInnerProductPlain(tmp, std::vector<CT>(masked_inputs.begin(), masked_inputs.begin() + np), pmsk);   // (:575-576)
             tmp = rot.rotate(tmp, ib * num_partition + i * np);
@@ -240,13 +243,13 @@ template <int N> class DirectSort : public SortBase<N> {
         if (b_lo < 0 || b_hi > N / num_partition || b_lo >= b_hi) throw std::runtime_error("rotationIndexCheckPartial: empty or invalid batch range");
         CT output;
         if (seed) output = this->getZero()->Clone();
-        Plaintext index_vector = m_cc->MakeCKKSPackedPlaintext(generateIndexVector(), 1, (uint32_t)ctx_Rank->GetLevel(), nullptr, N);
+        Plaintext index_vector = m_cc->MakeCKKSPackedPlaintextKeyed({3, N}, [&] { return generateIndexVector(); }, 1, (uint32_t)ctx_Rank->GetLevel(), N);
         CT index_minus_rank = m_cc->EvalSub(index_vector, ctx_Rank);
         index_minus_rank->SetSlots(num_slots);
         input_array->SetSlots(num_slots);   // mutates the caller's ciphertext metadata, as the reference does (:711)
         for (int b = b_lo; b < b_hi; b++) {
-            Plaintext chk = m_cc->MakeCKKSPackedPlaintext(generateCheckingVectorN(num_slots, b * num_partition), 1,
-                                                          (uint32_t)index_minus_rank->GetLevel(), nullptr, num_slots);
+            Plaintext chk = m_cc->MakeCKKSPackedPlaintextKeyed({4, N, num_slots, b * num_partition},
+                [&] { return generateCheckingVectorN(num_slots, b * num_partition); }, 1, (uint32_t)index_minus_rank->GetLevel(), (uint32_t)num_slots);
             CT rotIndex = m_cc->EvalSub(index_minus_rank, chk);
             m_cc->EvalMultInPlace(rotIndex, 1.0 / N / 2);   // (-2N, N) -> (-1, 1/2)
             rotIndex = m_cc->EvalChebyshevSeriesPS(rotIndex, selectDoubledSincCoefficients<N>(), -1, 1);
@@ -285,9 +288,10 @@ template <int N> class DirectSort : public SortBase<N> {
             const bool right = (target >> (lg - 1 - i)) & 1;
             c = m_cc->EvalAdd(c, rot.rotate(c, right ? -(int)step : (int)step));
         }
-        std::vector<double> msk(matrixSize * matrixSize, 0.0);
-        for (size_t i = 0; i < matrixSize; i++) msk[rowMask ? matrixSize * target + i : matrixSize * i + target] = 1.0;
-        Plaintext pmsk = m_cc->MakeCKKSPackedPlaintext(msk, 1, (uint32_t)c->GetLevel(), nullptr, (uint32_t)(matrixSize * matrixSize));
+        Plaintext pmsk = m_cc->MakeCKKSPackedPlaintextKeyed({5, (int64_t)matrixSize, (int64_t)target, rowMask ? 1 : 0}, [&] {
+            std::vector<double> msk(matrixSize * matrixSize, 0.0);
+            for (size_t i = 0; i < matrixSize; i++) msk[rowMask ? matrixSize * target + i : matrixSize * i + target] = 1.0;
+            return msk; }, 1, (uint32_t)c->GetLevel(), (uint32_t)(matrixSize * matrixSize));
         return m_cc->EvalMult(c, pmsk);
     }
     CT sumColumnsToTarget(CT c, size_t matrixSize, size_t columnIndex) { return foldToTarget(c, matrixSize, columnIndex, matrixSize >> 1, false); }
@@ -310,13 +314,14 @@ template <int N> class DirectSort : public SortBase<N> {
 
         std::vector<CT> Masked(num_batch);
         for (size_t b = 0; b < num_batch; b++) {
-            std::vector<double> subMask(num_slots, 0.0);
-            for (size_t i = 0; i < array_size; i++)
-                for (size_t j = 0; j < array_size; j++) {
-                    const double row = (double)(b * array_size + i);
-                    subMask[i * array_size + j] = scaled ? row / (double)N : row;
-                }
-            Plaintext subMaskPtx = m_cc->MakeCKKSPackedPlaintext(subMask, 1, (uint32_t)ctx_Rank->GetLevel(), nullptr, (uint32_t)num_slots);
+            Plaintext subMaskPtx = m_cc->MakeCKKSPackedPlaintextKeyed({6, N, (int64_t)b, scaled ? 1 : 0, (int64_t)array_size, (int64_t)num_slots}, [&] {
+                std::vector<double> subMask(num_slots, 0.0);
+                for (size_t i = 0; i < array_size; i++)
+                    for (size_t j = 0; j < array_size; j++) {
+                        const double row = (double)(b * array_size + i);
+                        subMask[i * array_size + j] = scaled ? row / (double)N : row;
+                    }
+                return subMask; }, 1, (uint32_t)ctx_Rank->GetLevel(), (uint32_t)num_slots);
             CT subMasked = this->getZero()->Clone();
             subMasked->SetSlots((uint32_t)num_slots);
             for (size_t k = 0; k < num_batch; k++) {
