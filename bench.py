@@ -9,7 +9,8 @@ reference's parameter card: ring 2^17, multDepth 30, 40-bit scaling, Sign(3,3,2)
 ciphertexts already resident in HBM; `e2e` times the same K steps through the C-ABI with HOST buffers
 (ckks_ct_import from pinned memory -> sortfhe_direct_sort -> ckks_ct_export).  With N GPUs every rank sorts its
 own arrays (replicas, no data-path collective: SURVEY 8e) and `value` is seconds per sort over the whole job.
-`--impl reference` times the CPU arm (the oracle port of the same op sequence, OpenMP on the host cores).
+`--impl reference` EXECUTES whole sorts with the CPU arm (the oracle port of the same op sequence, OpenMP on the host
+cores) and reports the number of sorts it ran as `steps`.
 """
 import argparse
 import importlib
@@ -111,10 +112,6 @@ def workload_name(n, log_n, depth, cfg, nrots):
             % (n, log_n, depth, str(cfg), nrots))
 
 
-def sf_rots(n, log_n):
-    return importlib.import_module("sorting-fhe_b200").direct_sort_params(n, 1 << log_n)[1]
-
-
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -124,12 +121,10 @@ def measured_peak():
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
-def cpu_op_times(log_n, depth, nls, reps=1, slots=16384):
-    """Time the ORACLE's ops (the CPU restatement: oracle/ckks_ops.py over oracle/ckks_fast.c, OpenMP) at the
-    bench parameters for a few limb counts.  Returns {op: {nl: seconds}} and the thread count used."""
-    from oracle.ckks_eval import Ct
-    from oracle.ckks_oracle import Context, Params
-    from oracle.ckks_ops import OracleCC
+# OpenFHE 1.1.4 (the reference's arithmetic) is an un-vendored dependency that cannot be built offline, so
+# the CPU arm is the oracle port (oracle/ckks_ops.py over oracle/ckks_fast.c, OpenMP on every host core) EXECUTING the
+# reference's op sequence (oracle/algos.py DirectSort).  Nothing here imports the product package.
+def _omp_all_cores():
     threads = os.cpu_count() if "OMP_NUM_THREADS" not in os.environ else int(os.environ["OMP_NUM_THREADS"])
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
         # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm runs on rank 0 alone and may use every host core
@@ -139,97 +134,92 @@ def cpu_op_times(log_n, depth, nls, reps=1, slots=16384):
             ctypes.CDLL("libgomp.so.1").omp_set_num_threads(threads)
         except OSError:
             threads = int(os.environ.get("OMP_NUM_THREADS", "1"))
-    cc = OracleCC(Context(Params(log_n, depth, 40)))
-    cc.keygen(); cc.relin_keygen(); cc.rot_keygen([1])
-    c = cc.ctx
-    rng = np.random.default_rng(0)
-    out = {k: {} for k in ("mult", "rotate", "rescale", "mult_pt", "add", "encode")}
-
-    def best(fn):
-        ts = []
-        for _ in range(reps):
-            t = time.perf_counter(); fn(); ts.append(time.perf_counter() - t)
-        return min(ts)
-
-    for nl in nls:
-        lvl = c.size_q - nl
-        mk = lambda parts: Ct(np.stack([np.stack([rng.integers(0, c.q[i], c.n, dtype=np.uint64) for i in range(nl)])
-                                        for _ in range(parts)]), lvl, 1, c.sf_real[lvl], slots)
-        a, b, p = mk(2), mk(2), mk(1)
-        out["mult"][nl] = best(lambda: cc.EvalMult(a, b))          # tensor + hybrid key switch (no rescale: deg 1)
-        out["rotate"][nl] = best(lambda: cc.EvalRotate(a, 1))      # hybrid key switch + automorphism
-        out["mult_pt"][nl] = best(lambda: cc.EvalMult(a, p))
-        out["add"][nl] = best(lambda: cc.EvalAdd(a, b))
-        if nl >= 2:
-            out["rescale"][nl] = best(lambda: cc.rescale(a.clone()))
-        vals = rng.random(slots)
-        out["encode"][nl] = best(lambda: cc.encode(vals, 1, lvl, slots))
-    return out, threads
+    return threads
 
 
-def cpu_estimate(trace, times):
-    """seconds of CPU work for an op trace [(name, nl, count)], piecewise-linear in nl between the sampled points"""
-    total, used = 0.0, 0
-    for name, nl, cnt in trace:
-        if name not in times or not times[name]:
-            continue   # 'keyswitch' is contained in mult / rotate
-        xs = sorted(times[name]); ys = [times[name][x] for x in xs]
-        total += cnt * float(np.interp(nl, xs, ys))
-        used += cnt
-    return total, used
+def _oracle_sorter(n, log_n):
+    from oracle import algos
+    from oracle.ckks_oracle import Context, Params
+    from oracle.ckks_ops import OracleCC
+    depth, rots = algos.DIRECT_SORT_PARAMS[n]
+    if log_n != 17:
+        raise SystemExit("the CPU arm follows the reference's ring 2^17 parameter card")
+    cc = OracleCC(Context(Params(log_n, depth, 40, 60, 0, True, 1)))
+    cc.keygen(); cc.relin_keygen(); cc.rot_keygen(list(rots))
+    return cc, algos.DirectSort(cc, n, rots), depth, rots
 
 
-def dry_trace(n, log_n, cfg):
-    """op trace of one sort from a metadata-only (dry_run) engine context: no GPU needed"""
-    sf = importlib.import_module("sorting-fhe_b200")
-    depth, rots = sf.direct_sort_params(n, 1 << log_n)
-    eng = sf.Engine(log_n, depth, 40, dry_run=True)
-    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
-    ct = eng.encrypt(eng.encode(np.arange(n) / n, slots=n))
-    eng.stats(reset=True)
-    sf.DirectSort(eng, n, rots).sort(ct, cfg)
-    tr = [tuple(x) for x in eng.stats()["ops"]]
-    eng.close()
-    return depth, tr
+def _golden_ratio(n):
+    """full sort seconds / index-check seconds of the committed full-size oracle run (tests/golden/fullsize_limbs.json)"""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "fullsize_limbs.json")) as f:
+            t = json.load(f)["direct_sort_n%d" % n]["oracle_seconds"]
+        return t["sort"] / t["index_check"], t
+    except Exception:
+        return None, None
 
 
-def cpu_baseline(n, log_n, cfg, trace=None, reps=1):
-    depth = None
-    if trace is None:
-        depth, trace = dry_trace(n, log_n, cfg)
-    sf = importlib.import_module("sorting-fhe_b200")
-    depth = depth or sf.direct_sort_params(n, 1 << log_n)[0]
-    size_q = depth + 2
-    nls = sorted({size_q, max(2, (size_q * 2) // 3), max(2, size_q // 3), 2})
+def cpu_baseline(n, log_n, cfg):
+    """Bounded CPU sample for the GPU arm's JSON line: the index-check phase of one sort (rotationIndexCheckN,
+    reference src/sort_algo.h:658-750: 128 mask encodes, the degree-848 Paterson-Stockmeyer series, 29 rotations) is
+    EXECUTED by the oracle port on a fresh encryption of the plaintext ranks at the rank ciphertext's level; `value`
+    scales that time to a whole sort with the phase ratio of the committed full-size oracle run.  The unscaled
+    measurement and the ratio are both in the object; `bench.py --impl reference` executes the whole sort."""
+    threads = _omp_all_cores()
     t0 = time.perf_counter()
-    times, cores = cpu_op_times(log_n, depth, nls, reps=reps, slots=min(n * n, (1 << log_n) // 2))
-    est, used = cpu_estimate(trace, times)
-    return {"value": est, "unit": "s", "cores": cores, "kind": "port",
-            "sample": "oracle (CPU restatement, OpenMP) ops mult+relin / rotate / rescale / ct*pt / add / encode timed at "
-                      "limb counts %s on the bench parameters (%.1f s of CPU work), piecewise-linear in the limb count, "
-                      "summed over the %d ops of one sort's op trace" % (nls, time.perf_counter() - t0, round(used))}
+    cc, sorter, depth, rots = _oracle_sorter(n, log_n)
+    t_setup = time.perf_counter() - t0
+    x = np.random.default_rng(100).permutation(n) / n
+    ct = cc.encrypt(cc.encode(x, slots=n))
+    rank_level = {4: 14, 8: 14, 16: 14, 32: 17, 64: 17, 128: 17, 256: 20, 512: 20, 1024: 23}[n]   # 1 + 3 (dg + df) + 1
+    rank = cc.encrypt(cc.encode(np.argsort(np.argsort(x)).astype(np.float64), 2, rank_level, n))
+    t0 = time.perf_counter()
+    out = sorter.rotation_index_check_n(rank, ct)
+    t_phase = time.perf_counter() - t0
+    err = float(np.max(np.abs(cc.decrypt(out, n) - np.sort(x))))
+    ratio, gold = _golden_ratio(n)
+    return {"value": t_phase * ratio if ratio else None, "unit": "s", "cores": threads, "kind": "port",
+            "sample_seconds": t_phase, "sample_max_abs_err": err, "setup_seconds": t_setup,
+            "phase_ratio": ratio, "phase_ratio_source": gold,
+            "sample": "oracle port (OpenMP, %d host threads) EXECUTING the index-check phase of one DirectSort N=%d sort "
+                      "(rotationIndexCheckN on an encryption of the plaintext ranks at level %d): %.1f s measured; value = "
+                      "that x the whole-sort / index-check ratio of the committed full-size oracle run; the whole sort is "
+                      "executed by `bench.py --impl reference`" % (threads, n, rank_level, t_phase)}
 
 
 def run_reference(args):
-    """--impl reference: the CPU arm.  OpenFHE 1.1.4 (the reference's arithmetic) is an un-vendored dependency that
-    cannot be built here, so the arm is the oracle port on all host threads; each step is the bounded
-    op sample of cpu_baseline()."""
+    """--impl reference: the CPU arm EXECUTES whole sorts -- min(steps, BENCH_REF_SORTS, default 1) of them, no warm-up
+    (one sort is minutes of CPU work) -- and reports what it ran: `steps` is the number of sorts executed."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cfg = SIGN_CFG[args.n]
-    depth, trace = dry_trace(args.n, args.log_n, cfg)
-    vals = []
-    for _ in range(max(1, min(args.steps, 3))):
-        vals.append(cpu_baseline(args.n, args.log_n, cfg, trace))
-    cb = min(vals, key=lambda d: d["value"])
-    v = cb["value"]
+    n, log_n, cfg = args.n, args.log_n, SIGN_CFG[args.n]
+    threads = _omp_all_cores()
+    t0 = time.perf_counter()
+    cc, sorter, depth, rots = _oracle_sorter(n, log_n)
+    t_setup = time.perf_counter() - t0
+    runs = max(1, min(args.steps, int(os.environ.get("BENCH_REF_SORTS", "1"))))
+    rng = np.random.default_rng(100)
+    times, errs = [], []
+    for _ in range(runs):
+        x = rng.permutation(n) / n
+        ct = cc.encrypt(cc.encode(x, slots=n))
+        t = time.perf_counter()
+        out = sorter.sort(ct, cfg)
+        times.append(time.perf_counter() - t)
+        errs.append(float(np.max(np.abs(cc.decrypt(out, n) - np.sort(x)))))
+    v = float(np.mean(times))
+    cb = {"value": v, "unit": "s", "cores": threads, "kind": "port",
+          "sample": "%d whole DirectSort N=%d sort(s) executed by the oracle port (OpenMP, %d host threads), %.1f s each; "
+                    "key generation (%.1f s) outside the timed region" % (runs, n, threads, v, t_setup)}
     emit(({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": runs,
+        "warmup": 0, "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": workload_name(args.n, args.log_n, depth, cfg, len(sf_rots(args.n, args.log_n))),
-                   "arm": "CPU oracle port (OpenFHE 1.1.4 unavailable offline), %d host threads" % cb["cores"]},
+        "config": {"workload": workload_name(n, log_n, depth, cfg, len(rots)), "max_abs_err": max(errs),
+                   "arm": "CPU oracle port (OpenFHE 1.1.4 unavailable offline), %d host threads; %d whole sort(s) executed, "
+                          "no warm-up" % (threads, runs)},
         "cpu_baseline": cb, "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -372,7 +362,7 @@ def run_b200(args):
             "breakdown_launches": {k: v["launches"] for k, v in breakdown.items()},
         }
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(n, log_n, cfg, trace)
+            line["cpu_baseline"] = cpu_baseline(n, log_n, cfg)
         emit(line)
     del cts, sorter
     eng.close()

@@ -32,18 +32,24 @@ const char* ckks_last_error(void);
 /* GenCryptoContext(CCParams<CryptoContextCKKSRNS>) -- tests/DirectSortTest.cpp:29-44,
  * src/sort_algo.h:87-201 (SetMultiplicativeDepth, SetScalingModSize, SetRingDim),
  * src/kway_adapter.h:45-46 (SetFirstModSize).  scaling_technique: 1 = FLEXIBLEAUTOEXT (OpenFHE
- * default), 0 = FLEXIBLEAUTO.  num_large_digits 0 = OpenFHE default.  seed drives the
- * counter-based sampler for keys and encryption randomness. */
+ * default), 0 = FLEXIBLEAUTO.  num_large_digits 0 = OpenFHE default (at most 4 digits are supported).  seed drives the
+ * counter-based sampler for keys and encryption randomness: a non-zero seed makes every key and ciphertext
+ * reproducible (parity tests; NOT secure -- anyone who knows it can recompute the secret key); seed 0 draws the
+ * key of the sampler from OS entropy (getrandom).  See INTEGRATION.md "Randomness". */
 int ckks_ctx_create(ckks_ctx_t** out, int log_ring_dim, int mult_depth, int scaling_mod_size, int first_mod_size,
                     int num_large_digits, int scaling_technique, uint64_t seed, int dry_run);
 int ckks_ctx_destroy(ckks_ctx_t* ctx); /* ClearEvalMultKeys/ClearEvalAutomorphismKeys/ReleaseAllContexts */
 int ckks_ctx_set_stream(ckks_ctx_t* ctx, void* cuda_stream);
 int ckks_ctx_sync(ckks_ctx_t* ctx);
 /* what: 0 ring dim (GetRingDimension, sort_algo.h:80), 1 #Q limbs, 2 #P limbs, 3 digit size alpha, 4 #digits,
- * 5 cyclotomic order (rotation.h:267), 6 kernel launches so far, 7 device bytes of keys */
+ * 5 cyclotomic order (rotation.h:267), 6 kernel launches so far, 7 device bytes of keys, 8 process-unique context id */
 int ckks_ctx_info(ckks_ctx_t* ctx, int what, int64_t* out);
 /* the n-th Encrypt of a context draws its randomness from sampler stream n; resetting the counter replays it
  * (reproducible tests: e.g. two sorter objects built after the same reset hold the same encryption of zeros) */
+/* options: 0 = EvalAdd(ct, double) convention on noiseScaleDeg > 1 (0: round(|c| * ciphertext scale), default;
+ * 1: OpenFHE 1.1.4 GetElementForEvalAddOrSub form, round(|c| * sf_level) times round(sf_level) per extra degree);
+ * 1 = number of ciphertext handles that may keep their hoisted ModUp digits (default 8, 0 disables the cache) */
+int ckks_ctx_set_option(ckks_ctx_t* ctx, int what, int64_t value);
 int ckks_ctx_set_encryption_counter(ckks_ctx_t* ctx, uint64_t counter);
 int ckks_ctx_get_moduli(ckks_ctx_t* ctx, uint64_t* moduli, uint64_t* roots, int cap);   /* Q then P */
 int ckks_ctx_get_scaling_factors(ckks_ctx_t* ctx, double* sf_real, double* sf_big, int cap);

@@ -188,10 +188,20 @@ class OracleCC(ChebyshevMixin, Evaluator):
             return self.EvalAdd(self.EvalNegate(b), float(a))
         return self.EvalAdd(a, b, sign=-1)
 
+    add_const_mode = 0
+
     def _add_const(self, ct, x):
-        """EvalAddInPlace(ct,double): add round(|x| * ct.scalingFactor) (sign applied) to c0"""
+        """EvalAddInPlace(ct,double): add the scaled constant (sign applied) to c0.
+        add_const_mode 0: round(|x| * ct.scalingFactor).
+        add_const_mode 1: OpenFHE 1.1.4 LeveledSHECKKSRNS::GetElementForEvalAddOrSub as recalled (unverifiable offline,
+        SURVEY 8c'-7): round(|x| * sf_level) multiplied by round(sf_level) once per extra noiseScaleDeg (CRTMult); at
+        level 0 under FLEXIBLEAUTOEXT the big scaling factor is used and the degree loop is skipped."""
         c = self.ctx
-        v = int(abs(x) * ct.sf + 0.5)
+        if self.add_const_mode == 0 or ct.deg <= 1 or (c.p.ext and ct.level == 0):
+            v = int(abs(x) * ct.sf + 0.5)
+        else:
+            sf = c.sf_real[ct.level]
+            v = int(abs(x) * sf + 0.5) * int(sf + 0.5) ** (ct.deg - 1)
         if x < 0:
             v = -v
         for i in range(ct.nlimbs):

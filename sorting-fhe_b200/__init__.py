@@ -124,6 +124,10 @@ class Engine:
             _L.ckks_ctx_destroy(_vp(self.h))
             self.h = None
 
+    def set_option(self, what, value):
+        """ckks_ctx_set_option: what = "add_const_mode" (0 | 1) or "modup_cache" (handles that keep hoisted ModUp digits)"""
+        _chk(_L.ckks_ctx_set_option(_vp(self.h), {"add_const_mode": 0, "modup_cache": 1}[what], ctypes.c_int64(value)))
+
     def plaintext_cache_stats(self):
         """(entries, device bytes upper bound, hits, misses) of the sorter layer's encoded-plaintext cache"""
         v = [ctypes.c_int64() for _ in range(4)]
@@ -359,6 +363,7 @@ class Engine:
                                     0 if rotation is None else rotation, _vp(out_ptr)))
 
 
+_L.ckks_ctx_set_option.argtypes = [_vp, _i, ctypes.c_int64]
 _L.ckks_ctx_create.argtypes = [_pp, _i, _i, _i, _i, _i, _i, _u64, _i]
 _L.ckks_ct_import.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), _i, _i, _i, _i, _d, _i, _pp]
 _L.ckks_eval_add_const.argtypes = [_vp, _vp, _d, _pp]

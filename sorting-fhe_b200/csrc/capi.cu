@@ -30,6 +30,19 @@ static void require_device(bool dry) {
     }
 }
 static ckks_ct* box(Ct* p) { return new ckks_ct{p}; }
+// Scope of one C entry point: holds the context mutex (engine.h) and, when the entry point released the last handle of a
+// closed context, tears the context down after unlocking.
+struct Locked {
+    Context* c; std::unique_lock<std::recursive_mutex> lk;
+    explicit Locked(Context* c_) : c(c_), lk(c_->mu) {}
+    explicit Locked(const Context* c_) : Locked(const_cast<Context*>(c_)) {}
+    ~Locked() {
+        const bool rel = c->release_pending;
+        if (rel) c->release_pending = false;
+        lk.unlock();
+        if (rel) context_release(c);
+    }
+};
 static Context* C(ckks_ctx_t* x) { if (!x) throw std::runtime_error("null context"); return &x->c; }
 static const Ct* G(const ckks_ct_t* x) { if (!x || !x->p) throw std::runtime_error("null ciphertext handle"); return x->p; }
 
@@ -80,15 +93,16 @@ int ckks_ctx_destroy(ckks_ctx_t* x) {
     API_BEGIN
     if (!x) return 0;
     Context* c = &x->c;
+    Locked lk_(c);
     if (c->closed) return 0;
     c->closed = true;
-    if (c->live_cts == 0) context_release(c);   // otherwise the last ckks_ct_free finishes the teardown
+    if (c->live_cts == 0) c->release_pending = true;   // otherwise the last ckks_ct_free finishes the teardown
     API_END
 }
 
 int ckks_ctx_set_stream(ckks_ctx_t* x, void* s) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (c->dry) return 0;
     cudaStreamSynchronize(c->stream);
     if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
@@ -97,7 +111,7 @@ int ckks_ctx_set_stream(ckks_ctx_t* x, void* s) {
 }
 int ckks_ctx_sync(ckks_ctx_t* x) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (!c->dry) {
         if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
         cudaError_t e = cudaStreamSynchronize(c->stream); if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); check_cuda("sync");
@@ -106,7 +120,7 @@ int ckks_ctx_sync(ckks_ctx_t* x) {
 }
 int ckks_ctx_info(ckks_ctx_t* x, int what, int64_t* out) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     switch (what) {
         case 0: *out = c->n; break;
         case 1: *out = c->size_q; break;
@@ -121,25 +135,35 @@ int ckks_ctx_info(ckks_ctx_t* x, int what, int64_t* out) {
     }
     API_END
 }
+int ckks_ctx_set_option(ckks_ctx_t* x, int what, int64_t value) {
+    API_BEGIN
+    Context* c = C(x); Locked lk_(c);
+    switch (what) {
+        case 0: if (value != 0 && value != 1) throw std::runtime_error("add_const_mode must be 0 or 1"); c->add_const_mode = (int)value; break;
+        case 1: if (value < 0) throw std::runtime_error("modup cache size must be >= 0"); c->modup_cap = (int)value; break;
+        default: throw std::runtime_error("ckks_ctx_set_option: unknown option");
+    }
+    API_END
+}
 int ckks_ctx_get_moduli(ckks_ctx_t* x, uint64_t* moduli, uint64_t* roots, int cap) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (cap < c->M()) throw std::runtime_error("ckks_ctx_get_moduli: buffer too small");
     for (int i = 0; i < c->M(); i++) { moduli[i] = c->moduli[i]; if (roots) roots[i] = c->psi[i]; }
     API_END
 }
 int ckks_ctx_get_scaling_factors(ckks_ctx_t* x, double* sf_real, double* sf_big, int cap) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (cap < c->size_q) throw std::runtime_error("ckks_ctx_get_scaling_factors: buffer too small");
     for (int i = 0; i < c->size_q; i++) sf_real[i] = c->sf_real[i];
     if (sf_big) for (size_t i = 0; i < c->sf_big.size(); i++) sf_big[i] = c->sf_big[i];
     API_END
 }
 
-int ckks_keygen(ckks_ctx_t* x) { API_BEGIN keygen(C(x)); API_END }
-int ckks_eval_mult_keygen(ckks_ctx_t* x) { API_BEGIN relin_keygen(C(x)); API_END }
-int ckks_eval_rotate_keygen(ckks_ctx_t* x, const int32_t* idx, int count) { API_BEGIN rot_keygen(C(x), idx, count); API_END }
+int ckks_keygen(ckks_ctx_t* x) { API_BEGIN Locked lk_(C(x)); keygen(C(x)); API_END }
+int ckks_eval_mult_keygen(ckks_ctx_t* x) { API_BEGIN Locked lk_(C(x)); relin_keygen(C(x)); API_END }
+int ckks_eval_rotate_keygen(ckks_ctx_t* x, const int32_t* idx, int count) { API_BEGIN Locked lk_(C(x)); rot_keygen(C(x), idx, count); API_END }
 
 static void d2h(Context* c, uint64_t* host, const u64* dev, size_t words) {
     if (c->dry) { memset(host, 0, words * 8); return; }
@@ -156,7 +180,7 @@ static void h2d(Context* c, u64* dev, const uint64_t* host, size_t words) {
 
 int ckks_export_secret(ckks_ctx_t* x, uint64_t* host, size_t cap) {
     API_BEGIN
-    Context* c = C(x); size_t w = (size_t)c->M() * c->n;
+    Context* c = C(x); Locked lk_(c); size_t w = (size_t)c->M() * c->n;
     if (cap < w) throw std::runtime_error("export_secret: buffer too small");
     if (!c->d_secret && !c->dry) throw std::runtime_error("export_secret: no secret key");
     d2h(c, host, c->d_secret, w);
@@ -164,7 +188,7 @@ int ckks_export_secret(ckks_ctx_t* x, uint64_t* host, size_t cap) {
 }
 int ckks_export_public_key(ckks_ctx_t* x, uint64_t* host, size_t cap) {
     API_BEGIN
-    Context* c = C(x); size_t w = (size_t)2 * c->size_q * c->n;
+    Context* c = C(x); Locked lk_(c); size_t w = (size_t)2 * c->size_q * c->n;
     if (cap < w) throw std::runtime_error("export_public_key: buffer too small");
     if (!c->d_pk && !c->dry) throw std::runtime_error("export_public_key: no public key");
     d2h(c, host, c->d_pk, w);
@@ -179,7 +203,7 @@ static EvalKey* find_key(Context* c, int is_rot, int32_t index, bool create) {
 }
 int ckks_export_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, uint64_t* host, size_t cap) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     EvalKey* k = find_key(c, is_rot, index, false);
     if (!k || (!k->d && !c->dry)) throw std::runtime_error("export_eval_key: key not present");
     int rows = c->num_part_q * 2 * c->M(); size_t w = (size_t)rows * c->n;
@@ -193,7 +217,7 @@ int ckks_export_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, uint64_t* hos
 }
 int ckks_import_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, const uint64_t* host, size_t words_) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     int rows = c->num_part_q * 2 * c->M(); size_t w = (size_t)rows * c->n;
     if (words_ != w) throw std::runtime_error("import_eval_key: size mismatch");
     EvalKey* k = find_key(c, is_rot, index, true);
@@ -205,23 +229,23 @@ int ckks_import_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, const uint64_
 }
 
 int ckks_make_packed_plaintext(ckks_ctx_t* x, const double* v, int count, int scale_deg, int level, int slots, ckks_ct_t** out) {
-    API_BEGIN *out = box(encode(C(x), v, count, scale_deg, level, slots)); API_END
+    API_BEGIN Locked lk_(C(x)); *out = box(encode(C(x), v, count, scale_deg, level, slots)); API_END
 }
-int ckks_encrypt(ckks_ctx_t* x, const ckks_ct_t* pt, ckks_ct_t** out) { API_BEGIN *out = box(encrypt(C(x), G(pt))); API_END }
-int ckks_decrypt(ckks_ctx_t* x, const ckks_ct_t* ct, double* v, int count) { API_BEGIN (void)C(x); decrypt(G(ct), v, count); check_cuda("decrypt"); API_END }
+int ckks_encrypt(ckks_ctx_t* x, const ckks_ct_t* pt, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(encrypt(C(x), G(pt))); API_END }
+int ckks_decrypt(ckks_ctx_t* x, const ckks_ct_t* ct, double* v, int count) { API_BEGIN Locked lk_(C(x)); decrypt(G(ct), v, count); check_cuda("decrypt"); API_END }
 
-int ckks_ct_free(ckks_ct_t* ct) { API_BEGIN if (ct) { ct_free(ct->p); delete ct; } API_END }
-int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out) { API_BEGIN *out = box(ct_clone(G(ct))); API_END }
+int ckks_ct_free(ckks_ct_t* ct) { API_BEGIN if (ct) { if (ct->p) { Locked lk_(ct->p->ctx); ct_free(ct->p); } delete ct; } API_END }
+int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out) { API_BEGIN Locked lk_(G(ct)->ctx); *out = box(ct_clone(G(ct))); API_END }
 int ckks_ct_set_slots(ckks_ct_t* ct, int slots) {
     API_BEGIN
-    Ct* p = const_cast<Ct*>(G(ct));
+    Ct* p = const_cast<Ct*>(G(ct)); Locked lk_(p->ctx);
     if (slots <= 0 || (slots & (slots - 1)) || slots > p->ctx->n / 2) throw std::runtime_error("SetSlots: bad slot count");
     p->slots = slots;
     API_END
 }
 int ckks_ct_get(const ckks_ct_t* ct, int what, int64_t* out) {
     API_BEGIN
-    const Ct* p = G(ct);
+    const Ct* p = G(ct); Locked lk_(p->ctx);
     switch (what) {
         case 0: *out = p->slots; break; case 1: *out = p->level; break; case 2: *out = p->deg; break;
         case 3: *out = p->nl; break; case 4: *out = p->parts; break;
@@ -229,10 +253,10 @@ int ckks_ct_get(const ckks_ct_t* ct, int what, int64_t* out) {
     }
     API_END
 }
-int ckks_ct_get_scaling_factor(const ckks_ct_t* ct, double* out) { API_BEGIN *out = G(ct)->sf; API_END }
+int ckks_ct_get_scaling_factor(const ckks_ct_t* ct, double* out) { API_BEGIN Locked lk_(G(ct)->ctx); *out = G(ct)->sf; API_END }
 int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
     API_BEGIN
-    const Ct* p = G(ct); size_t w = (size_t)p->parts * p->nl * p->ctx->n;
+    const Ct* p = G(ct); Locked lk_(p->ctx); size_t w = (size_t)p->parts * p->nl * p->ctx->n;
     if (cap < w) throw std::runtime_error("ct_export: buffer too small");
     ct_wait(p);
     if (p->lrep) {   // compact plaintext: export the full-length limbs
@@ -242,10 +266,10 @@ int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
     } else d2h(p->ctx, host, p->d, w);
     API_END
 }
-int ckks_ctx_set_encryption_counter(ckks_ctx_t* x, uint64_t counter) { API_BEGIN C(x)->enc_counter = counter; API_END }
+int ckks_ctx_set_encryption_counter(ckks_ctx_t* x, uint64_t counter) { API_BEGIN Locked lk_(C(x)); C(x)->enc_counter = counter; API_END }
 int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
     API_BEGIN
-    const Ct* p = G(ct);
+    const Ct* p = G(ct); Locked lk_(p->ctx);
     if (p->lrep) throw std::runtime_error("ct_device_ptr: compact plaintexts have no full-length device form");
     ct_wait(p);
     *dev_ptr = p->d; *words = (size_t)p->parts * p->nl * p->ctx->n;
@@ -253,7 +277,7 @@ int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
 }
 int ckks_ct_mod_reduce(ckks_ctx_t* x, ckks_ct_t* ct) {
     API_BEGIN
-    Context* c = C(x); Ct* p = const_cast<Ct*>(G(ct));
+    Context* c = C(x); Locked lk_(c); Ct* p = const_cast<Ct*>(G(ct));
     if (p->lrep) throw std::runtime_error("ct_mod_reduce: compact plaintext");
     if (p->resc) { ct_free(p->resc); p->resc = nullptr; }            // the limbs are about to change: drop derived caches
     if (p->modup) { dev_free(c, p->modup); p->modup = nullptr; }
@@ -262,7 +286,7 @@ int ckks_ct_mod_reduce(ckks_ctx_t* x, ckks_ct_t* ct) {
 }
 int ckks_ct_import(ckks_ctx_t* x, const uint64_t* host, int polys, int limbs, int level, int deg, double sf, int slots, ckks_ct_t** out) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (polys < 1 || polys > 3 || limbs < 1 || limbs + level != c->size_q) throw std::runtime_error("ct_import: shape does not match context");
     Ct* p = ct_new(c, polys, limbs, level, deg, sf, slots);
     try { h2d(c, p->d, host, (size_t)polys * limbs * c->n); } catch (...) { ct_free(p); throw; }
@@ -270,19 +294,19 @@ int ckks_ct_import(ckks_ctx_t* x, const uint64_t* host, int polys, int limbs, in
     API_END
 }
 
-int ckks_eval_add(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add(G(a), G(b), 1)); API_END }
-int ckks_eval_sub(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add(G(a), G(b), -1)); API_END }
-int ckks_eval_add_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add_const(G(a), v)); API_END }
-int ckks_eval_sub_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_add_const(G(a), -v)); API_END }
+int ckks_eval_add(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_add(G(a), G(b), 1)); API_END }
+int ckks_eval_sub(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_add(G(a), G(b), -1)); API_END }
+int ckks_eval_add_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_add_const(G(a), v)); API_END }
+int ckks_eval_sub_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_add_const(G(a), -v)); API_END }
 int ckks_eval_const_sub(ckks_ctx_t* x, double v, const ckks_ct_t* a, ckks_ct_t** out) {
-    API_BEGIN (void)C(x);
+    API_BEGIN Locked lk_(C(x));
     *out = box(eval_const_sub(v, G(a)));
     API_END
 }
-int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_negate(G(a))); API_END }
+int ckks_eval_negate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_negate(G(a))); API_END }
 int ckks_eval_inner_product_plain(ckks_ctx_t* x, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts, int count,
                                   ckks_ct_t** out) {
-    API_BEGIN (void)C(x);
+    API_BEGIN Locked lk_(C(x));
     if (count < 0) throw std::runtime_error("EvalInnerProductPlain: negative count");
     std::vector<const Ct*> a(count), p(count);
     for (int i = 0; i < count; i++) { a[i] = G(cts[i]); p[i] = G(pts[i]); }
@@ -290,7 +314,7 @@ int ckks_eval_inner_product_plain(ckks_ctx_t* x, const ckks_ct_t* init, const ck
     API_END
 }
 int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
-    API_BEGIN (void)C(x);
+    API_BEGIN Locked lk_(C(x));
     if (count < 1) throw std::runtime_error("EvalAddMany: empty list");
     {   // all operands already aligned (the sorters' case): one pass over the inputs.  Modular addition is
         // associative, so the result equals the pairwise tree's bit for bit.
@@ -301,7 +325,7 @@ int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ck
         }
         if (same && count > 2) {
             int slots = 0; std::vector<const u64*> ins;
-            for (int i = 0; i < count; i++) { ins.push_back(G(cts[i])->d); slots = std::max(slots, G(cts[i])->slots); }
+            for (int i = 0; i < count; i++) { ct_wait(G(cts[i])); ins.push_back(G(cts[i])->d); slots = std::max(slots, G(cts[i])->slots); }
             Ct* r = ct_new(f->ctx, f->parts, f->nl, f->level, f->deg, f->sf, slots);
             f->ctx->stats.ops[{"add", f->nl}] += count - 1;
             launch_add_many(f->ctx, r->d, ins.data(), count, f->parts * f->nl, f->nl);
@@ -324,36 +348,36 @@ int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ck
     *out = box(owned[0] ? cur[0] : ct_clone(cur[0]));
     API_END
 }
-int ckks_eval_mult(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult(G(a), G(b))); API_END }
-int ckks_eval_mult_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult_const(G(a), v)); API_END }
-int ckks_eval_square(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_mult(G(a), G(a))); API_END }
-int ckks_eval_rotate(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(eval_rotate(G(a), index)); API_END }
-int ckks_fast_rotation_precompute(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN (void)C(x); *out = box(fast_rotation_precompute(G(a))); API_END }
+int ckks_eval_mult(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_mult(G(a), G(b))); API_END }
+int ckks_eval_mult_const(ckks_ctx_t* x, const ckks_ct_t* a, double v, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_mult_const(G(a), v)); API_END }
+int ckks_eval_square(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_mult(G(a), G(a))); API_END }
+int ckks_eval_rotate(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_rotate(G(a), index)); API_END }
+int ckks_fast_rotation_precompute(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(fast_rotation_precompute(G(a))); API_END }
 int ckks_fast_rotation(ckks_ctx_t* x, const ckks_ct_t* a, int32_t index, const ckks_ct_t* precomp, ckks_ct_t** out) {
-    API_BEGIN (void)C(x); *out = box(eval_fast_rotate(G(a), index, G(precomp))); API_END
+    API_BEGIN Locked lk_(C(x)); *out = box(eval_fast_rotate(G(a), index, G(precomp))); API_END
 }
 int ckks_has_rotation_key(ckks_ctx_t* x, int32_t index) {
-    try { Context* c = C(x); return c->rot.count(auto_index(c, index)) ? 1 : 0; } catch (...) { return 0; }
+    try { Context* c = C(x); Locked lk_(c); return c->rot.count(auto_index(c, index)) ? 1 : 0; } catch (...) { return 0; }
 }
 int ckks_eval_chebyshev_series_ps(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, double a, double b, ckks_ct_t** out) {
-    API_BEGIN (void)C(x);
+    API_BEGIN Locked lk_(C(x));
     if (count < 2) throw std::runtime_error("EvalChebyshevSeriesPS: need at least 2 coefficients");
     *out = box(eval_chebyshev_series_ps(G(ct), std::vector<double>(coeffs, coeffs + count), a, b));
     API_END
 }
 int ckks_eval_chebyshev_series(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, double a, double b, ckks_ct_t** out) {
-    API_BEGIN (void)C(x);
+    API_BEGIN Locked lk_(C(x));
     if (count < 2) throw std::runtime_error("EvalChebyshevSeries: need at least 2 coefficients");
     *out = box(eval_chebyshev_series(G(ct), std::vector<double>(coeffs, coeffs + count), a, b));
     API_END
 }
 int ckks_eval_poly_linear(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, ckks_ct_t** out) {
-    API_BEGIN (void)C(x); *out = box(eval_poly_linear(G(ct), std::vector<double>(coeffs, coeffs + count))); API_END
+    API_BEGIN Locked lk_(C(x)); *out = box(eval_poly_linear(G(ct), std::vector<double>(coeffs, coeffs + count))); API_END
 }
 
 int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     std::ostringstream os;
     os << "{\"kernel_launches\": " << c->stats.kernel_launches << ", \"host_ns\": [" << c->stats.host_ns[0] << ", " << c->stats.host_ns[1] << ", " << c->stats.host_ns[2] << ", " << c->stats.host_ns[3]
        << "], \"host_calls\": [" << c->stats.host_calls[0] << ", " << c->stats.host_calls[1] << ", " << c->stats.host_calls[2] << ", " << c->stats.host_calls[3] << "], \"ops\": [";
@@ -365,18 +389,18 @@ int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
     memcpy(buf, s.c_str(), s.size() + 1);
     API_END
 }
-int ckks_stats_reset(ckks_ctx_t* x) { API_BEGIN C(x)->stats = Stats(); API_END }
+int ckks_stats_reset(ckks_ctx_t* x) { API_BEGIN Locked lk_(C(x)); C(x)->stats = Stats(); API_END }
 
 int ckks_profile_enable(ckks_ctx_t* x, unsigned mask) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     prof_collect(c);
     c->prof.mask = mask;
     API_END
 }
 int ckks_profile_json(ckks_ctx_t* x, char* buf, size_t cap) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     prof_collect(c);
     static const char* names[KC_COUNT] = {"ntt", "baseconv", "ks_inner", "moddown", "pointwise", "rescale", "automorph",
                                           "encode", "copy"};
@@ -397,7 +421,7 @@ int ckks_profile_json(ckks_ctx_t* x, char* buf, size_t cap) {
 
 int ckks_ntt_host(ckks_ctx_t* x, uint64_t* data, int rows, const int32_t* mod_ids, int inverse) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (rows < 1 || rows > MAX_LIMBS) throw std::runtime_error("ntt_host: bad row count");
     LimbMods m; m.n = rows;
     for (int i = 0; i < rows; i++) { if (mod_ids[i] < 0 || mod_ids[i] >= c->M()) throw std::runtime_error("ntt_host: bad modulus id"); m.m[i] = (short)mod_ids[i]; }
@@ -412,14 +436,14 @@ int ckks_ntt_host(ckks_ctx_t* x, uint64_t* data, int rows, const int32_t* mod_id
 }
 int ckks_ntt_dev(ckks_ctx_t* x, void* dev, int rows, int first_mod, int inverse) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     if (rows < 1 || first_mod < 0 || first_mod + rows > c->M()) throw std::runtime_error("ntt_dev: bad limb range");
     launch_ntt(c, (u64*)dev, rows, mods_range(first_mod, first_mod + rows), inverse != 0);
     API_END
 }
 int ckks_key_switch_dev(ckks_ctx_t* x, const void* src, int limbs, int is_rot, int32_t index, void* out) {
     API_BEGIN
-    Context* c = C(x);
+    Context* c = C(x); Locked lk_(c);
     EvalKey* k = find_key(c, is_rot, index, false);
     if (!k) throw std::runtime_error("key_switch_dev: key not present");
     key_switch(c, (const u64*)src, limbs, *k, (u64*)out, nullptr, nullptr, 0);

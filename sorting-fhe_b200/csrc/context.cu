@@ -13,6 +13,7 @@
 #include <stdexcept>
 #include <algorithm>
 #include <atomic>
+#include <sys/random.h>
 
 typedef unsigned __int128 u128;
 
@@ -70,6 +71,11 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
                       uint64_t seed, int dry) {
     c->log_n = log_n; c->n = 1 << log_n; c->mult_depth = mult_depth; c->scaling_bits = scaling_bits;
     c->first_bits = first_bits; c->ext = ext; c->seed = seed; c->dry = dry != 0;
+    if (seed == 0) {   // no seed given: key material and encryption randomness are keyed from OS entropy (INTEGRATION.md "Randomness")
+        uint64_t s = 0;
+        if (getrandom(&s, sizeof s, 0) != (ssize_t)sizeof s || s == 0) throw std::runtime_error("getrandom failed: cannot seed the sampler");
+        c->seed = s;
+    }
     { static std::atomic<uint64_t> next_uid{1}; c->uid = next_uid++; }
     if (log_n < 8 || log_n > 17) throw std::runtime_error("ring dimension must be 2^8..2^17");
     const u64 m = 2ull * c->n;
@@ -101,7 +107,11 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
     int dnum = num_large_digits;
     if (dnum == 0) dnum = mult_depth > 3 ? 3 : (mult_depth > 0 ? 2 : 1);
     c->alpha = (size_q + dnum - 1) / dnum;
+    if (dnum < 1) throw std::runtime_error("numLargeDigits must be non-negative");
     c->num_part_q = (size_q + c->alpha - 1) / c->alpha;
+    if (c->num_part_q > MAX_DIGITS)
+        throw std::runtime_error("numLargeDigits = " + std::to_string(c->num_part_q) + ": the hybrid key switch supports at most " +
+                                 std::to_string(MAX_DIGITS) + " digits");
     int max_bits = 0;
     for (int j = 0; j < c->num_part_q; j++) {
         // bit length of the digit modulus product, via long double log2 with an exact fallback margin

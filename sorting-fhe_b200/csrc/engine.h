@@ -9,13 +9,16 @@
 #include <string>
 #include <cstdint>
 #include <cstddef>
+#include <deque>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <cuda_runtime.h>
 #include "modarith.cuh"
 
 #define MAX_LIMBS 96
+#define MAX_DIGITS 4   // hybrid key switch digits (ConvBatch groups, DigitMap): validated in context_generate
 
 struct LimbMods {          // passed by value to kernels: row r of a bundle uses modulus m[r % n]
     int n;
@@ -125,6 +128,15 @@ struct Context {
     // torn down when it is closed AND the last ciphertext handle is gone
     long live_cts = 0;
     bool closed = false;
+    bool release_pending = false;   // closed and the last handle is gone: the C entry point that notices tears the context down after unlocking
+    // Thread safety (SURVEY 8b "Threading": the reference calls cc-> from nested OpenMP regions, src/sort_algo.h:334,349,
+    // 425,713,757): every extern "C" entry point holds this mutex for its whole duration, so evaluator state (the
+    // stream swap of the encode path, stats, event pools, key-switch tables, the twin / ModUp caches written on const
+    // operands) is never touched by two host threads at once.  The GPU work is asynchronous; the lock covers enqueueing.
+    std::recursive_mutex mu;
+    std::deque<const struct Ct*> modup_lru;   // handles that carry a cached ModUp, oldest first (bounded: evaluator.cu)
+    int modup_cap = 8;
+    int add_const_mode = 0;         // EvalAdd(ct, double) on noiseScaleDeg > 1: 0 = round(|x| * ct scale), 1 = OpenFHE CRTMult form
     int M() const { return size_q + size_p; }
 };
 

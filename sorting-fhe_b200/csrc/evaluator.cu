@@ -39,10 +39,16 @@ Ct* ct_clone(const Ct* a) {
     launch_copy_rows(a->ctx, t->d, a->d, words(a->ctx, a->parts * a->nl, a->lrep));
     return t;
 }
-static void drop_twin(const Ct* a) {
+void ct_drop_caches(const Ct* a);
+static void drop_twin(const Ct* a) { ct_drop_caches(a); }
+void ct_drop_caches(const Ct* a) {
     if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); }
     if (a->lift) { Ct* t = a->lift; a->lift = nullptr; ct_free(t); }
-    if (a->modup) { dev_free(a->ctx, a->modup); a->modup = nullptr; }
+    if (a->modup) {
+        dev_free(a->ctx, a->modup); a->modup = nullptr;
+        auto& q = a->ctx->modup_lru;
+        for (auto it = q.begin(); it != q.end(); ++it) if (*it == a) { q.erase(it); break; }
+    }
 }
 static void wait_enc_reader(const Ct* a) {
     if (!a->enc_reader) return;
@@ -86,7 +92,7 @@ void ct_free(Ct* a) {
     drop_twin(a);
     dev_free(c, a->d);
     delete a;
-    if (--c->live_cts == 0 && c->closed) context_release(c);
+    if (--c->live_cts == 0 && c->closed) c->release_pending = true;   // torn down by the C entry point once it has unlocked
 }
 // a takes over t's buffer and metadata (t is consumed)
 static void ct_steal(Ct* a, Ct* t) {
@@ -329,13 +335,33 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
 }
 
 // ------------------------------------------------------------------ public evaluator ops
-// EvalAdd(ct, double): add round(|x| * scalingFactor) (signed) to c0
+// The integer EvalAdd(ct, double) adds to c0.  Context::add_const_mode 0: round(|x| * ct scale).  Mode 1: OpenFHE 1.1.4
+// LeveledSHECKKSRNS::GetElementForEvalAddOrSub as recalled (unverifiable offline, SURVEY 8c'-7): round(|x| * sf_level),
+// then multiplied by round(sf_level) mod q_i once per extra noiseScaleDeg (CRTMult); at level 0 under FLEXIBLEAUTOEXT the
+// big scaling factor is used and the degree loop is skipped (same integer as mode 0).  Oracle twin: ckks_ops._add_const.
+static void add_const_residues(const Ct* a, double x, u64* s) {
+    Context* c = a->ctx;
+    if (c->add_const_mode == 0 || a->deg <= 1 || (c->ext && a->level == 0)) {
+        i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
+        if (x < 0) v = -v;
+        int_residues(c, v, a->nl, s);
+        return;
+    }
+    const double sf = c->sf_real[a->level];
+    const i128 v0 = (i128)(std::fabs(x) * sf + 0.5), f = (i128)(sf + 0.5);
+    for (int i = 0; i < a->nl; i++) {
+        const i128 q = (i128)c->moduli[i];
+        i128 r = v0 % q;
+        for (int d = 1; d < a->deg; d++) r = (i128)((unsigned __int128)r * (unsigned __int128)(f % q) % (unsigned __int128)q);
+        if (x < 0 && r) r = q - r;
+        s[i] = (u64)r;
+    }
+}
+// EvalAdd(ct, double): add the scaled constant (signed) to c0
 Ct* eval_add_const(const Ct* a_in, double x) {
     Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
     Context* c = a->ctx;
-    i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
-    if (x < 0) v = -v;
-    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    u64 s[MAX_LIMBS]; add_const_residues(a, x, s);
     Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
     launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, false);
     return r;
@@ -344,9 +370,7 @@ Ct* eval_add_const(const Ct* a_in, double x) {
 Ct* eval_const_sub(double x, const Ct* a_in) {
     Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
     Context* c = a->ctx;
-    i128 v = (i128)(std::fabs(x) * a->sf + 0.5);
-    if (x < 0) v = -v;
-    u64 s[MAX_LIMBS]; int_residues(c, v, a->nl, s);
+    u64 s[MAX_LIMBS]; add_const_residues(a, x, s);
     Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
     launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, true);
     return r;
@@ -503,6 +527,7 @@ uint32_t auto_index(const Context* c, int r) {
 Ct* eval_rotate(const Ct* a, int r) {
     Context* c = a->ctx;
     if (a->parts != 2) throw std::runtime_error("EvalRotate: ciphertext must have 2 components");
+    if (r == 0) return ct_clone(a);   // EvalRotate / EvalAtIndex(ct, 0) returns a copy (no key involved)
     uint32_t k = auto_index(c, r);
     auto it = c->rot.find(k);
     if (it == c->rot.end()) throw std::runtime_error("EvalRotate: no rotation key for index " + std::to_string(r));
@@ -513,8 +538,16 @@ Ct* eval_rotate(const Ct* a, int r) {
     // baby-step rotations of one input (sort_algo.h:425-431, 733-736) share it.  Same limbs as EvalRotate: ModUp does
     // not depend on the rotation index (EvalFastRotation == EvalRotate bit for bit).
     const u64* c1 = c->dry ? nullptr : a->d + words(c, nl);
-    if (!a->modup) { u64* m = key_switch_modup(c, c1, nl); a->modup = c->dry ? (u64*)1 : m; }   // dry: sentinel (dev_free ignores it)
-    else count(c, "modup_reused", nl);
+    if (!a->modup) {
+        u64* m = key_switch_modup(c, c1, nl);
+        a->modup = c->dry ? (u64*)1 : m;   // dry: sentinel (dev_free ignores it)
+        // the cache is (beta (l + K) - l) limbs per handle (92 MB at l = 32): keep it on the most recently rotated handles only
+        c->modup_lru.push_back(a);
+        while ((int)c->modup_lru.size() > c->modup_cap) {
+            const Ct* old = c->modup_lru.front(); c->modup_lru.pop_front();
+            if (old != a && old->modup) { dev_free(c, old->modup); old->modup = nullptr; }
+        }
+    } else count(c, "modup_reused", nl);
     key_switch(c, c1, nl, it->second, out->d, a->d, nullptr, k, a->modup);
     return out;
 }

@@ -10,6 +10,7 @@ Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slo
 Ct* ct_full(const Ct* a);   // full-length copy of a (possibly compact) plaintext / ciphertext
 Ct* ct_clone(const Ct* a);
 void ct_free(Ct* a);
+void ct_drop_caches(const Ct* a);   // frees the cached twins and the ModUp digits of a handle whose limbs are about to change
 void ct_wait(const Ct* a);   // order the main stream after the (side-stream) producer of a
 
 void mult_core_const(Ct* a, double x);

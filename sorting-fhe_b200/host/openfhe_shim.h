@@ -45,7 +45,9 @@ template <> class CCParams<CryptoContextCKKSRNS> {
     uint32_t multDepth = 1, scalingModSize = 50, firstModSize = 60, batchSize = 0, ringDim = 0, numLargeDigits = 0;
     SecurityLevel security = HEStd_128_classic;
     ScalingTechnique scalTech = FLEXIBLEAUTOEXT;
-    uint64_t seed = 1;   // engine extension: seed of the counter-based sampler
+    uint64_t seed = 0;   // engine extension: seed of the counter-based sampler; 0 = keyed from OS entropy (the default, as
+                         // OpenFHE's PRNG); a fixed non-zero seed gives reproducible keys for parity tests and is not secure
+    void SetSeed(uint64_t s) { seed = s; }
     void SetMultiplicativeDepth(uint32_t d) { multDepth = d; }
     void SetScalingModSize(uint32_t b) { scalingModSize = b; }
     void SetFirstModSize(uint32_t b) { firstModSize = b; }
