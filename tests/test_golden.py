@@ -35,6 +35,17 @@ def test_oracle_compare_kat():
     assert np.all(np.abs(cc.decrypt(r, 4) - np.array(k["expected"])) < k["tol"])
 
 
+def test_oracle_compare_kat_as_written():
+    """tests/CompareTest.cpp:13-62 verbatim: a = {1,5,3,4}, b = {2,4,3,3} unscaled (the differences {-1,1,0,1} lie on the
+    boundary of sign's domain), ring 2^12, depth 50, scale 59, Sign(4,3,3) -> {0, 1, 0.5, 1} +- 0.1"""
+    k = KAT["compare"]
+    cc = OracleCC(Context(Params(12, 50, 59)))
+    cc.keygen(); cc.relin_keygen()
+    a, b = np.array(k["a"]), np.array(k["b"])
+    r = algos.compare(cc, cc.encrypt(cc.encode(a, slots=4)), cc.encrypt(cc.encode(b, slots=4)), *k["sign_cfg"])
+    assert np.all(np.abs(cc.decrypt(r, 4) - np.array(k["expected"])) < k["tol"])
+
+
 @pytest.mark.parametrize("name", ["sign3", "sign4"])
 def test_oracle_sign_kat(name):
     """tests/SignTest.cpp:41-80 (compositeSign<3>, dg=0 df=1) and :82-122 (compositeSign<4>, dg=df=3)"""

@@ -35,6 +35,23 @@ def test_compute_without_gpu_fails_loudly():
         sf.Engine(10, 2)
 
 
+def test_unsupported_digit_count_is_a_clean_error():
+    """numLargeDigits beyond the key switch's 4-digit tables must fail at context creation, not overflow"""
+    with pytest.raises(sf.CkksError, match="at most 4 digits"):
+        sf.Engine(10, 9, 40, 60, 6, dry_run=True)
+    sf.Engine(10, 9, 40, 60, 4, dry_run=True).close()
+
+
+def test_entropy_seeded_context_and_options():
+    eng = sf.Engine(10, 3, seed=0, dry_run=True)       # seed 0: the sampler key comes from getrandom()
+    eng.set_option("add_const_mode", 1)
+    eng.set_option("modup_cache", 0)
+    with pytest.raises(sf.CkksError):
+        eng.set_option("add_const_mode", 2)
+    assert eng.info(8) > 0
+    eng.close()
+
+
 def test_decomposer_reference_vectors():
     """tests/DecomposeTest.cpp:64-74: Decomposer<128>{1..64}, sum of steps == rotation for 15 values x 3 algos"""
     keys = [1, 2, 4, 8, 16, 32, 64]

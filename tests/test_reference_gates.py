@@ -1,0 +1,174 @@
+"""The reference's own known-answer vectors and unit gates, run as written (`-m gpu`), plus the behaviour switches and
+robustness items of the round-1 review:
+  * tests/CompareTest.cpp:13-62 verbatim (a = {1,5,3,4}, b = {2,4,3,3}, unscaled; ring 2^12, depth 50, scale 59);
+  * tests/DirectSortNTest.cpp:124 (every rank within 1e-4 of the integer rank), :199 (index check from plaintext ranks),
+    :221-281 (index check with +-1e-3 rank noise), at the fixture's ring 2^13 for N in {16, 64, 128} (N = 128 has
+    num_batch = 4 there, so it also runs the shardable batch halves on one GPU);
+  * the degree-848 doubled-sinc Paterson-Stockmeyer series of DirectSort<128> (src/sort_algo.h:725-728) bit-exact vs the oracle;
+  * EvalAdd(ct, double) conventions (SURVEY 8c'-7), EvalRotate(ct, 0), the encoded-plaintext cache, concurrent callers."""
+import importlib
+import threading
+
+import numpy as np
+import pytest
+
+from oracle import algos
+from oracle.cheby import truncated_doubled_sinc_coeffs
+from tests.common import make_pair, same
+
+pytestmark = pytest.mark.gpu
+sf = importlib.import_module("sorting-fhe_b200")
+SIGN = {16: (3, 2, 2), 64: (3, 3, 2), 128: (3, 3, 2)}
+
+
+def _import(eng, co):
+    return eng.import_ct(co.d, co.level, co.deg, co.sf, co.slots)
+
+
+def test_compare_kat_as_written():
+    eng, orc = make_pair(12, 50, scale=59)
+    try:
+        a, b = np.array([1.0, 5.0, 3.0, 4.0]), np.array([2.0, 4.0, 3.0, 3.0])
+        ca, cb = orc.encrypt(orc.encode(a, slots=4)), orc.encrypt(orc.encode(b, slots=4))
+        re = sf.compare(eng, _import(eng, ca), _import(eng, cb), (4, 3, 3))
+        ro = algos.compare(orc, ca, cb, 4, 3, 3)
+        same(re, ro)
+        got = eng.decrypt(re, 4)
+        assert np.all(np.abs(got - np.array([0.0, 1.0, 0.5, 1.0])) < 0.1), got
+    finally:
+        eng.close()
+
+
+@pytest.fixture(scope="module", params=[16, 64, 128])
+def ring13(request):
+    n = request.param
+    depth, rots = sf.direct_sort_params(n, 1 << 13)
+    eng = sf.Engine(13, depth, 40, seed=7)
+    eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+    yield n, eng, rots
+    eng.close()
+
+
+def test_construct_rank_gate(ring13):
+    n, eng, rots = ring13
+    x = np.random.default_rng(n).permutation(n) / n
+    rank = sf.DirectSort(eng, n, rots).construct_rank(eng.encrypt(eng.encode(x, slots=n)), SIGN[n])
+    got = eng.decrypt(rank, n)
+    want = np.argsort(np.argsort(x)).astype(np.float64)
+    assert np.max(np.abs(got - want)) < 1e-4, np.max(np.abs(got - want))      # DirectSortNTest.cpp:124
+
+
+@pytest.mark.parametrize("noise", [0.0, 1e-3])
+def test_rotation_index_check_from_plaintext_ranks(ring13, noise):
+    n, eng, rots = ring13
+    rng = np.random.default_rng(1000 + n)
+    x = rng.permutation(n) / n
+    ranks = np.argsort(np.argsort(x)).astype(np.float64) + rng.uniform(-noise, noise, n)
+    out = sf.DirectSort(eng, n, rots).rotation_index_check(eng.encrypt(eng.encode(ranks, slots=n)), eng.encrypt(eng.encode(x, slots=n)))
+    got = eng.decrypt(out, n)
+    assert np.max(np.abs(got - np.sort(x))) < 0.01, np.max(np.abs(got - np.sort(x)))   # DirectSortNTest.cpp:199, 276-280
+
+
+def test_ps_degree_848_bit_exact():
+    coeffs = truncated_doubled_sinc_coeffs(128)
+    assert len(coeffs) - 1 == 848
+    assert np.allclose(coeffs, sf.sinc_coefficients(128, doubled=True))
+    eng, orc = make_pair(12, 12)
+    try:
+        x = np.linspace(-0.95, 0.45, 16)
+        co = orc.encrypt(orc.encode(x, slots=16))
+        re = eng.EvalChebyshevSeriesPS(_import(eng, co), list(coeffs), -1.0, 1.0)
+        ro = orc.EvalChebyshevSeriesPS(co, list(coeffs), -1.0, 1.0)
+        same(re, ro)
+        from numpy.polynomial import chebyshev as C
+        c = np.array(coeffs); c[0] /= 2
+        assert np.max(np.abs(eng.decrypt(re, 16) - C.chebval(x, c))) < 1e-4
+    finally:
+        eng.close()
+
+
+def test_add_const_conventions():
+    eng, orc = make_pair(12, 6)
+    try:
+        x = np.array([0.25, -0.5, 0.75, 0.1])
+        co = orc.encrypt(orc.encode(x, slots=4))
+        ce = _import(eng, co)
+        m_o, m_e = orc.EvalMult(orc.EvalMult(co, co), co), eng.EvalMult(eng.EvalMult(ce, ce), ce)   # noiseScaleDeg 2 at level 2
+        assert m_e.deg == 2 and m_e.level >= 1
+        r0 = eng.EvalAdd(m_e, 1.0)
+        same(r0, orc.EvalAdd(m_o, 1.0))
+        eng.set_option("add_const_mode", 1); orc.add_const_mode = 1
+        r1 = eng.EvalAdd(m_e, 1.0)
+        same(r1, orc.EvalAdd(m_o, 1.0))
+        same(eng.EvalSub(1.0, m_e), orc.EvalSub(1.0, m_o))
+        same(eng.EvalSub(m_e, 0.5), orc.EvalSub(m_o, 0.5))
+        assert not np.array_equal(r0.export(), r1.export())      # the two conventions add different integers ...
+        assert np.allclose(eng.decrypt(r0, 4), eng.decrypt(r1, 4), atol=1e-9)   # ... that encode the same constant
+        assert np.allclose(eng.decrypt(r1, 4), x ** 3 + 1.0, atol=1e-6)
+        same(eng.EvalAdd(ce, 1.0), orc.EvalAdd(co, 1.0))         # level 0 (FLEXIBLEAUTOEXT): both conventions agree
+    finally:
+        orc.add_const_mode = 0
+        eng.close()
+
+
+def test_rotate_zero_is_a_copy_and_modup_cache_is_bounded():
+    eng, orc = make_pair(12, 4, rots=(1, 2))
+    try:
+        x = np.arange(8) / 8.0
+        cts = [eng.encrypt(eng.encode(x + i, slots=8)) for i in range(12)]
+        r0 = eng.EvalRotate(cts[0], 0)
+        assert np.array_equal(r0.export(), cts[0].export())
+        eng.set_option("modup_cache", 3)
+        first = [eng.EvalRotate(c, 1).export() for c in cts]     # 12 handles get digits, at most 3 keep them
+        again = [eng.EvalRotate(c, 1).export() for c in cts]     # evicted handles recompute: same limbs
+        assert all(np.array_equal(a, b) for a, b in zip(first, again))
+        assert np.allclose(eng.decrypt(eng.EvalRotate(cts[3], 2), 8), np.roll(x + 3, -2), atol=1e-6)
+    finally:
+        eng.close()
+
+
+def test_plaintext_cache_gives_identical_sorts():
+    n, cfg = 8, (3, 2, 2)
+    depth, rots = sf.direct_sort_params(n, 1 << 10)
+    eng = sf.Engine(10, depth, 40, seed=3)
+    try:
+        eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+        x = np.random.default_rng(2).permutation(n) / n
+        ct = eng.encrypt(eng.encode(x, slots=n))
+        sorter = sf.DirectSort(eng, n, rots)
+        outs = []
+        for _ in range(3):
+            eng.set_encryption_counter(1)
+            outs.append(sorter.sort(ct, cfg).export())
+        assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+        e, b, h, m = eng.plaintext_cache_stats()
+        assert e == m and h == 2 * m and m > 0, (e, b, h, m)      # every pattern encoded once, served from the cache twice
+    finally:
+        eng.close()
+
+
+def test_concurrent_callers_on_one_context():
+    """SURVEY 8b "Threading": the reference calls cc-> from OpenMP threads on shared read-only inputs.  Four host threads
+    multiply / rotate the same ciphertexts through one context; every result equals the serial one."""
+    eng, orc = make_pair(12, 6, rots=(1, 3))
+    try:
+        x = np.array([0.1, -0.2, 0.3, 0.4, -0.5, 0.6, 0.7, -0.8])
+        a = eng.encrypt(eng.encode(x, slots=8))
+        p = eng.MakeCKKSPackedPlaintext(x[::-1].copy(), 1, 0, None, 8)
+
+        def work(i):
+            sq = eng.EvalMult(a, a)
+            r = eng.EvalRotate(sq, 1 if i % 2 else 3)
+            return eng.EvalAdd(eng.EvalMult(r, p), eng.EvalMult(sq, 0.5)).export()
+
+        serial = [work(i) for i in range(8)]
+        res = [None] * 8
+        ths = [threading.Thread(target=lambda i=i: res.__setitem__(i, work(i))) for i in range(8)]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        for i in range(8):
+            assert np.array_equal(res[i], serial[i]), i
+    finally:
+        eng.close()
