@@ -16,9 +16,7 @@ import argparse
 import importlib
 import json
 import os
-import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -44,67 +42,48 @@ def parse():
     return ap.parse_args()
 
 
-_SAMPLER_SRC = r"""
-import sys, time
-import pynvml as nv
-nv.nvmlInit()
-h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[1]))
-print("max", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
-while True:
-    try:
-        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
-    except Exception:
-        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-    print("s", time.time(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), r, flush=True)
-    time.sleep(0.5)
-"""
-
-
 class ClockSampler:
-    """SM clock and throttle reasons of one GPU, sampled through NVML twice a second by a small child process that is
-    started (and has initialised NVML) before the warm-up; stop() keeps the samples that fall inside the timed region.
-    (A looping `nvidia-smi -lms` child per rank stalled the kernel launches of the other ranks on a multi-GPU box -- the
-    2-GPU step took 2.8x longer with it -- and every NVML query stalls the launch path for ~10 ms: at 10 Hz the N=1 step
-    was 20-50 % slower, so the rate is 2 Hz and the default region is 10 steps (~0.77 s, two samples, +3 % on `value`;
-    with 3 steps the region was bimodal, 75 or 81-83 ms per sort depending on whether a sample fell inside).  Samples
-    requested from the parent at fixed points of the region were measured worse: 80-156 ms per sort.)"""
+    """SM clock and throttle reasons of one GPU, read through NVML IN THIS PROCESS: one sample per step, taken right after
+    the step's kernels have been enqueued (the GPU is working through them), so every sample falls inside the timed region.
+    NVML is initialised and queried once before the warm-up: the first query costs ~30 ms, later ones ~0.02 ms
+    (tools/nvml_probe.py on a B200: 63.9 ms per sort with and without them).  A separate sampling process -- round 1's
+    design -- stalled this process's kernel launches on the round-2 boxes: 64 -> 78-157 ms per sort."""
     BAD = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
-        self.index, self.proc, self.lines, self.t0 = index, None, [], None
+        self.index, self.h, self.nv, self.samples, self.mx = index, None, None, [], None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(self.index)],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.lines.append(self.proc.stdout.readline())   # "max ...": NVML is initialised (its attach stalls the GPU) before anything is timed
-            threading.Thread(target=lambda: [self.lines.append(ln) for ln in self.proc.stdout], daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.sample(); self.samples.clear()
+        except Exception:
+            self.h = None
 
     def mark(self):                 # the timed region starts here
-        self.t0 = time.time()
+        self.samples.clear()
 
+    def sample(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        self.samples.append((float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)), int(r)))
 
     def stop(self):
-        t1 = time.time()
-        if not self.proc:
+        if self.h is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml sampler unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        for ln in list(self.lines):
-            f = ln.split()
-            if f and f[0] == "max":
-                mx = float(f[1])
-            elif f and f[0] == "s" and len(f) == 4 and (self.t0 or 0) <= float(f[1]) <= t1 + 0.15:
-                sm.append(float(f[2]))
-                for name, bit in self.BAD:
-                    if int(f[3]) & bit:
-                        reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": mx, "reasons": ["no NVML samples"]}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no NVML samples"]}
+        reasons = sorted({name for _, r in self.samples for name, bit in self.BAD if r & bit})
+        return {"sm_mhz": float(np.median([c for c, _ in self.samples])), "sm_max_mhz": self.mx, "reasons": reasons,
+                "samples": len(self.samples), "how": "in-process NVML, one sample per step while the step's kernels run"}
 
 
 def workload_name(n, log_n, depth, cfg, nrots):
@@ -292,8 +271,10 @@ def run_b200(args):
     for i in range(K):
         cts[i].slots = n                                 # sort() widens the caller's metadata (sort_algo.h:711)
         outs.append(sorter.sort(cts[i], cfg))
+        if rank == 0:
+            sampler.sample()                             # NVML read while the GPU works through this step (~0.02 ms on the host)
         eng.sync()                                       # one result at a time, as in the e2e region: the host never runs
-                                                         # more than one sort (6 000 launches) ahead of the device
+                                                         # more than one sort (3 300 launches) ahead of the device
     e1.record(stream)
     barrier()
     t_dev = e0.elapsed_time(e1) / 1e3

@@ -29,12 +29,12 @@ CryptoContext<DCRTPoly> borrow(ckks_ctx_t* c, int batch) {
     RegEntry& e = g_reg[c];
     if (e.uid != uid) { e.by_batch.clear(); e.uid = uid; }
     auto& w = e.by_batch[batch];
-    if (!w) w = std::make_shared<CryptoContextImpl>(c, false, (uint32_t)batch);
+    if (!w) w = std::make_shared<CryptoContextImpl<DCRTPoly>>(c, false, (uint32_t)batch);
     return w;
 }
 CT borrow(const ckks_ct_t* h) {
     if (!h) throw std::runtime_error("null ciphertext handle");
-    return std::make_shared<CiphertextImpl>(const_cast<ckks_ct_t*>(h), false);
+    return std::make_shared<CiphertextImpl<DCRTPoly>>(const_cast<ckks_ct_t*>(h), false);
 }
 ckks_ct_t* release(const CT& c) {   // hand a result to the caller (clone if the sorter returned a borrowed input)
     if (!c->owned) { ckks_ct_t* o = nullptr; ckks_check(ckks_ct_clone(c->h, &o), "clone"); return o; }

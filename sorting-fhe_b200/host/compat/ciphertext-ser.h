@@ -1,0 +1,3 @@
+// ciphertext-ser.h -- forwarding header (see openfhe.h in this directory)
+#pragma once
+#include "openfhe.h"

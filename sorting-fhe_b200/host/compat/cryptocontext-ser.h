@@ -1,0 +1,3 @@
+// cryptocontext-ser.h -- forwarding header (see openfhe.h in this directory)
+#pragma once
+#include "openfhe.h"

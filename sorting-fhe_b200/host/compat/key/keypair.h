@@ -1,0 +1,3 @@
+// key/keypair.h -- forwarding header (see openfhe.h in this directory)
+#pragma once
+#include "../openfhe.h"

@@ -1,0 +1,3 @@
+// lattice/hal/lat-backend.h -- forwarding header (see openfhe.h in this directory)
+#pragma once
+#include "../../openfhe.h"

@@ -63,13 +63,20 @@ template <> class CCParams<CryptoContextCKKSRNS> {
     uint32_t GetBatchSize() const { return batchSize; }
 };
 
-class CryptoContextImpl;
+template <class Element> class CryptoContextImpl;
 
-// Ciphertext<DCRTPoly> / encoded Plaintext: owns (or borrows) one ckks_ct_t handle.
-class CiphertextImpl {
+// Ciphertext<DCRTPoly> / encoded Plaintext: owns (or borrows) one ckks_ct_t handle.  A class template on the element tag,
+// like OpenFHE's, so that function templates over Ciphertext<Element> (reference src/mehp24/mehp24_utils.h:32-88) deduce.
+template <class Element> class CiphertextImpl {
   public:
     ckks_ct_t* h = nullptr;
     bool owned = true;
+    std::weak_ptr<CryptoContextImpl<Element>> cc;   // weak: the context's plaintext cache holds ciphertext handles
+    std::shared_ptr<CryptoContextImpl<Element>> GetCryptoContext() const {
+        auto p = cc.lock();
+        if (!p) throw std::runtime_error("GetCryptoContext: the ciphertext's context is gone");
+        return p;
+    }
     CiphertextImpl(ckks_ct_t* handle, bool own = true) : h(handle), owned(own) {}
     CiphertextImpl(const CiphertextImpl&) = delete;
     ~CiphertextImpl() { if (h && owned) ckks_ct_free(h); }
@@ -83,16 +90,18 @@ class CiphertextImpl {
     void SetSlots(size_t s) const { ckks_check(ckks_ct_set_slots(h, (int)s), "SetSlots"); }
     std::shared_ptr<CiphertextImpl> Clone() const {
         ckks_ct_t* o = nullptr; ckks_check(ckks_ct_clone(h, &o), "Clone");
-        return std::make_shared<CiphertextImpl>(o);
+        auto p = std::make_shared<CiphertextImpl>(o);
+        p->cc = cc;
+        return p;
     }
 };
-template <class E> using Ciphertext = std::shared_ptr<CiphertextImpl>;
-template <class E> using ConstCiphertext = std::shared_ptr<const CiphertextImpl>;
+template <class E> using Ciphertext = std::shared_ptr<CiphertextImpl<E>>;
+template <class E> using ConstCiphertext = std::shared_ptr<const CiphertextImpl<E>>;
 
 // Plaintext: either an encoded device polynomial (MakeCKKSPackedPlaintext) or a decrypted value vector.
 class PlaintextImpl {
   public:
-    std::shared_ptr<CiphertextImpl> enc;   // encoded form (1 polynomial)
+    std::shared_ptr<CiphertextImpl<DCRTPoly>> enc;   // encoded form (1 polynomial)
     std::vector<double> values;            // decoded form (Decrypt)
     double logPrecision = 0;
     void SetLength(size_t n) { values.resize(n); }
@@ -105,7 +114,7 @@ class PlaintextImpl {
 typedef std::shared_ptr<PlaintextImpl> Plaintext;
 typedef std::shared_ptr<const PlaintextImpl> ConstPlaintext;
 
-struct KeyImpl { CryptoContextImpl* cc; };
+struct KeyImpl { CryptoContextImpl<DCRTPoly>* cc; };
 template <class E> using PublicKey = std::shared_ptr<KeyImpl>;
 template <class E> using PrivateKey = std::shared_ptr<KeyImpl>;
 template <class E> struct KeyPair {
@@ -117,9 +126,13 @@ struct EncodingParamsImpl { uint32_t batch; uint32_t GetBatchSize() const { retu
 
 // CryptoContext<DCRTPoly>: one engine context (owned when created by GenCryptoContext, borrowed when
 // wrapped around a handle that arrived through the C entry points of sortfhe_host.h).
-class CryptoContextImpl {
-    typedef std::shared_ptr<CiphertextImpl> CT;
-    static CT wrap(ckks_ct_t* o) { return std::make_shared<CiphertextImpl>(o); }
+template <class Element> class CryptoContextImpl : public std::enable_shared_from_this<CryptoContextImpl<Element>> {
+    typedef std::shared_ptr<CiphertextImpl<Element>> CT;
+    CT wrap(ckks_ct_t* o) const {
+        auto p = std::make_shared<CiphertextImpl<Element>>(o);
+        p->cc = std::const_pointer_cast<CryptoContextImpl>(this->weak_from_this().lock());
+        return p;
+    }
     typedef int (*BinFn)(ckks_ctx_t*, const ckks_ct_t*, const ckks_ct_t*, ckks_ct_t**);
     typedef int (*CstFn)(ckks_ctx_t*, const ckks_ct_t*, double, ckks_ct_t**);
     CT bin(BinFn f, const CT& a, const CT& b, const char* name) const {
@@ -368,7 +381,16 @@ class CryptoContextImpl {
         throw std::runtime_error("EvalBootstrap: CKKS bootstrapping is not implemented by the B200 engine yet");
     }
 };
-template <class E> using CryptoContext = std::shared_ptr<CryptoContextImpl>;
+template <class E> using CryptoContext = std::shared_ptr<CryptoContextImpl<E>>;
+
+// Ciphertext operators of OpenFHE's ciphertext.h (used by reference src/mehp24/mehp24_sort.cpp:43,106,119,145)
+template <class E> Ciphertext<E> operator+(const Ciphertext<E>& a, const Ciphertext<E>& b) { return a->GetCryptoContext()->EvalAdd(a, b); }
+template <class E> Ciphertext<E> operator-(const Ciphertext<E>& a, const Ciphertext<E>& b) { return a->GetCryptoContext()->EvalSub(a, b); }
+template <class E> Ciphertext<E> operator*(const Ciphertext<E>& a, const Ciphertext<E>& b) { return a->GetCryptoContext()->EvalMult(a, b); }
+template <class E> Ciphertext<E> operator-(const Ciphertext<E>& a) { return a->GetCryptoContext()->EvalNegate(a); }
+template <class E> const Ciphertext<E>& operator+=(Ciphertext<E>& a, const Ciphertext<E>& b) { return a = a + b; }
+template <class E> const Ciphertext<E>& operator-=(Ciphertext<E>& a, const Ciphertext<E>& b) { return a = a - b; }
+template <class E> const Ciphertext<E>& operator*=(Ciphertext<E>& a, const Ciphertext<E>& b) { return a = a * b; }
 
 // GenCryptoContext(CCParams<CryptoContextCKKSRNS>) -- tests/DirectSortTest.cpp:29-44
 inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKSRNS>& p) {
@@ -380,7 +402,7 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     ckks_ctx_t* c = nullptr;
     ckks_check(ckks_ctx_create(&c, logn, (int)p.multDepth, (int)p.scalingModSize, (int)p.firstModSize, (int)p.numLargeDigits,
                                tech, p.seed, 0), "GenCryptoContext");
-    return std::make_shared<CryptoContextImpl>(c, true, p.batchSize);
+    return std::make_shared<CryptoContextImpl<DCRTPoly>>(c, true, p.batchSize);
 }
 
 }  // namespace lbcrypto
