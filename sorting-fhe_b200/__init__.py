@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 _DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_DIR, "libckks_b200.so")
+LIB_PATH = os.environ.get("CKKS_B200_LIB") or os.path.join(_DIR, "libckks_b200.so")   # env: kernel A/B builds (tools/build_variant.sh)
 if not os.path.exists(LIB_PATH):
     raise ImportError("libckks_b200.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
                       "(the CUDA extension is mandatory; there is no fallback path)")

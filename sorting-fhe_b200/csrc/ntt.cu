@@ -24,7 +24,10 @@
 #include <utility>
 #include <vector>
 
-static constexpr int TB_MAX = 10;
+#ifndef NTT_TB_MAX
+#define NTT_TB_MAX 10
+#endif
+static constexpr int TB_MAX = NTT_TB_MAX;   // log2 of the largest tile (words) a CTA owns
 typedef ulonglong2 tw_t;   // .x = w, .y = Shoup companion
 
 // Shared-memory slot of tile-local element e: an XOR swizzle, linear over GF(2), that sends the 16 elements a half-warp
@@ -535,7 +538,7 @@ __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, con
 // prefetched the next tile's words into registers was measured slower on B200: 80 registers cut the resident CTAs
 // from 4 to 3 per SM and 2048 tiles over 444 CTAs quantise badly -- 65 us vs 56 us for a 32-limb 2^17 transform.)
 template <bool INV, int LOGN_C, int PASS_C>
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__((1 << TB_MAX) / 8 > 256 ? (1 << TB_MAX) / 8 : 256, TB_MAX >= 12 ? 2 : 4)
 ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ LimbMods mods, int total,
            int tpr_log) {
     pdl_sync();

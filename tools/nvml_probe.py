@@ -49,4 +49,19 @@ def region(mode, K=10):
 for mode in ("none", "after_sync", "before_sync", "none"):
     ms, qs = region(mode)
     print(mode, "ms/step %.2f" % ms, [(c, r, round(t, 2)) for c, r, t in qs], flush=True)
+# per-step wall + device times: where does an occasional slow region come from?
+for rep in range(4):
+    rows = []
+    for i in range(10):
+        ct.slots = n
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        o = sorter.sort(ct, (3, 3, 2))
+        t1 = time.perf_counter()
+        e1.record(stream)
+        eng.sync()
+        t2 = time.perf_counter()
+        rows.append((round(e0.elapsed_time(e1), 1), round((t1 - t0) * 1e3, 1), round((t2 - t0) * 1e3, 1)))
+    print("rep", rep, "(device ms, host enqueue ms, wall ms):", rows, flush=True)
 eng.close()
