@@ -259,6 +259,21 @@ def run_b200(args):
     for i in range(W):                                   # warm-up (also fills the stream-ordered memory pool)
         out = sorter.sort(cts[i % len(cts)], cfg)
     eng.sync()
+    # The first CUDA process on a freshly leased box runs every kernel slowly for its first seconds (measured in round 2:
+    # 136 ms per sort in the first process, 62.5 ms in the next one, same binaries, SM clock 1965 MHz in both): keep
+    # warming up, untimed, until two consecutive steps agree within 2 % (at most 60 extra steps).
+    extra, prev = 0, None
+    while extra < 60:
+        cts[extra % len(cts)].slots = n
+        t0 = time.perf_counter()
+        out = sorter.sort(cts[extra % len(cts)], cfg)
+        eng.sync()
+        dt = time.perf_counter() - t0
+        extra += 1
+        if prev is not None and abs(dt - prev) <= 0.02 * prev and extra >= 2:
+            break
+        prev = dt
+    del out
 
     # ---- timed region 1: inputs resident in HBM
     eng.stats(reset=True)
@@ -332,7 +347,7 @@ def run_b200(args):
         ach = prof_ntt["bytes"] / max(prof_ntt["ms"], 1e-9) / 1e6     # GB/s over the timed region's NTT launches
         total_ms = sum(v["ms"] for v in breakdown.values())
         line = {
-            "metric": METRIC, "value": t_dev / (K * world), "unit": "s", "n_gpus": world, "steps": K, "warmup": W,
+            "metric": METRIC, "value": t_dev / (K * world), "unit": "s", "n_gpus": world, "steps": K, "warmup": W, "warmup_extra": extra,
             "ms_per_step": t_dev / K * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": workload_name(n, log_n, depth, cfg, len(rots)),

@@ -134,6 +134,20 @@ struct NttArgs {
     NttFuse f;               // optional work fused into the first load / last store (engine.h)
 };
 
+// Per-row launch table, passed by value (constant bank): physical limb rows of the source / destination / epilogue input,
+// modulus id, modulus, its reciprocal and which butterfly path the row takes.  Resolving the row maps on the host removes
+// three integer divisions (~190 of the ~625 instructions a thread of a pass executed) and the dependent ModInfo load from
+// the head of every CTA (ncu source page of round 2: prologue 225 instructions, 13 % of the stall samples on its first use).
+#define NTT_MAX_ROWS 96
+enum { ROW_FP = 0, ROW_INT = 1, ROW_INT_FIX = 2 };
+struct NttRows {
+    int src[NTT_MAX_ROWS], dst[NTT_MAX_ROWS], epi[NTT_MAX_ROWS];
+    u64 q[NTT_MAX_ROWS];
+    double qinv[NTT_MAX_ROWS];          // 1 / q, correctly rounded (== __drcp_rn)
+    short mid[NTT_MAX_ROWS];
+    unsigned char kind[NTT_MAX_ROWS];
+};
+
 // rounds of one pass: window position p and stage range [J0,J1) per round (host fills, <= 4 rounds)
 struct Sched { int nr; int p[4]; int j0[4]; int j1[4]; };
 
@@ -175,8 +189,10 @@ __device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, in
 // LOGN_C != 0: ring size, pass and round schedule are compile-time constants (all index arithmetic folds);
 // LOGN_C == 0: generic runtime form.
 template <bool INV, bool FIX, int LOGN_C, int PASS_C>
-__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const int row, const int tile, const int mid,
-                                         const ModInfo& mi, u64* sm, const u64 (&vin)[8]) {
+__device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile,
+                                         u64* sm, const u64 (&vin)[8]) {
+    const int mid = R.mid[row];
+    const ModInfo mi = A.mi[mid];
     constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
     constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
     const Sched& S = LOGN_C ? SC : SR;
@@ -184,8 +200,8 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
     const int cb = T - a_;                                // cb: column bits of a pass-A tile
     const tw_t* W = A.tw + ((size_t)mid << A.twlog);
-    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
-    u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
+    const u64* src = A.src + ((size_t)R.src[row] << logn);
+    u64* dst = A.dst + ((size_t)R.dst[row] << logn);
     const int u = threadIdx.x;
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
     // global word offset of tile-local index L
@@ -251,7 +267,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
                     }
                     if (A.f.epi == EPI_RESCALE) {
                         // out = (in - NTT(switched last limb)) * q_last^-1   (DropLastElementAndScale)
-                        const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
+                        const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
                         const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
                         u64 xin[8];
                         if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
@@ -399,18 +415,19 @@ __device__ __forceinline__ void do_round_fp(double (&r)[8], const double* W, u32
 // same tiling, passes and round schedule as ntt_tile; between the two passes of a transform the buffer holds the
 // raw bits of the (lazy) doubles
 template <bool INV, int LOGN_C, int PASS_C>
-__device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, const int row, const int tile, const int mid,
-                                            const ModInfo& mi, u64* sm, const u64 (&vin)[8]) {
+__device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile,
+                                            u64* sm, const u64 (&vin)[8]) {
+    const int mid = R.mid[row];
     constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
     constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
     const Sched& S = LOGN_C ? SC : SR;
-    const u64 qi = mi.q;
-    const double q = (double)qi, qinv = __drcp_rn(q);
+    const u64 qi = R.q[row];
+    const double q = (double)qi, qinv = R.qinv[row];
     const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
     const int cb = T - a_;
     const double* W = A.twd + ((size_t)mid << A.twlog);
-    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
-    u64* dst = A.dst + ((size_t)row_of(A.dmap, row) << logn);
+    const u64* src = A.src + ((size_t)R.src[row] << logn);
+    u64* dst = A.dst + ((size_t)R.dst[row] << logn);
     double* smd = reinterpret_cast<double*>(sm);
     const int u = threadIdx.x;
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
@@ -437,12 +454,12 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
             for (int k = 0; k < 8; k++) v[k] = vin[k];
             if (A.first_pass) {
                 if (!INV && A.f.pro == PRO_SWITCHMOD) {   // rescale: centred switch of the q_last residues to this row's modulus
-                    const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
+                    const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1, qrecip = A.mi[mid].qrecip;
 #pragma unroll
                     for (int k = 0; k < 8; k++) {
                         const bool neg = v[k] > half;
                         u64 a = neg ? ql - v[k] : v[k];
-                        a -= __umul64hi(a, mi.qrecip) * qi;
+                        a -= __umul64hi(a, qrecip) * qi;
                         if (a >= qi) a -= qi;
                         v[k] = neg ? (a ? qi - a : 0) : a;
                     }
@@ -480,7 +497,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
                 if (A.f.epi == EPI_RESCALE) {
-                    const u64* ein = A.f.epi_in + ((size_t)row_of(A.f.emap, row) << logn);
+                    const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
                     const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
                     u64 xin[8];
                     if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
@@ -516,13 +533,13 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
 
 // first-round words of tile `tile` of limb row `row` (the same index pattern for the integer and the FP64 path)
 template <bool INV, int LOGN_C, int PASS_C>
-__device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, const int row, const int tile, u64 (&v)[8]) {
+__device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile, u64 (&v)[8]) {
     constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
     constexpr Sched SC = make_sched(TC ? TC : 3, LOGN_C ? (PASS_C == 0 ? LOGN_C - TC : TC) : 3, INV);
     const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
     const int cb = T - a_, p = LOGN_C ? SC.p[0] : SR.p[0];
     const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
-    const u64* src = A.src + ((size_t)row_of(A.smap, row) << logn);
+    const u64* src = A.src + ((size_t)R.src[row] << logn);
     if (!strided && p == 0) load8(src + (((size_t)tile << T) | (size_t)(threadIdx.x * 8)), v);
     else {
 #pragma unroll
@@ -539,7 +556,7 @@ __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, con
 // from 4 to 3 per SM and 2048 tiles over 444 CTAs quantise badly -- 65 us vs 56 us for a 32-limb 2^17 transform.)
 template <bool INV, int LOGN_C, int PASS_C>
 __global__ void __launch_bounds__((1 << TB_MAX) / 8 > 256 ? (1 << TB_MAX) / 8 : 256, TB_MAX >= 12 ? 2 : 4)
-ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ LimbMods mods, int total,
+ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ NttRows R, int total,
            int tpr_log) {
     pdl_sync();
     extern __shared__ u64 sm[];
@@ -547,21 +564,19 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
     if (id >= total) return;
     const int row = id >> tpr_log, tile = id & ((1 << tpr_log) - 1);
     u64 v[8];
-    load_tile<INV, LOGN_C, PASS_C>(A, S, row, tile, v);
-    const int mid = mods.m[row % mods.n];
-    const ModInfo mi = A.mi[mid];
-    const bool fix = INV ? (mi.bits > 46) : (mi.bits > 58);
-    if (mi.bits <= FP_BITS && A.twd) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
-    else if (fix) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
-    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, row, tile, mid, mi, sm, v);
+    load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
+    const int kind = R.kind[row];
+    if (kind == ROW_FP) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    else if (kind == ROW_INT_FIX) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
 }
 
 template <bool INV, int LOGN_C, int PASS_C>
-static void launch_one(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
+static void launch_one(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
     launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C>, total, threads, smem, A, S, m, total, tpr_log);
 }
 template <bool INV, int PASS_C>
-static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const LimbMods& m) {
+static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
     switch (A.logn) {   // compile-time schedules for the ring sizes of the reference's fixtures (+ their compact plaintexts)
         case 17: launch_one<INV, 17, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
         case 16: launch_one<INV, 16, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
@@ -593,36 +608,50 @@ static const u64* ninv_pairs_for(Context* c, int lrep) {
 void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMods& m, bool inverse, const u64* scale_pairs,
                    RowMap smap, RowMap dmap, const NttFuse* fuse, int lrep) {
     const int logn = c->log_n - lrep, T = logn < TB_MAX ? logn : TB_MAX, a = logn - T;
-    c->stats.kernel_launches += (logn > TB_MAX) ? 2 : 1;
+    const int nchunks = (rows + NTT_MAX_ROWS - 1) / NTT_MAX_ROWS;
+    c->stats.kernel_launches += ((logn > TB_MAX) ? 2 : 1) * nchunks;
     if (c->dry || rows == 0) return;
-    ProfScope ps(c, KC_NTT, 16.0 * rows * (c->n >> lrep), (logn > TB_MAX) ? 2 : 1);
+    ProfScope ps(c, KC_NTT, 16.0 * rows * (c->n >> lrep), ((logn > TB_MAX) ? 2 : 1) * nchunks);
     const int threads = (1 << T) / 8;
     const size_t smem = (size_t)((1 << T) < 16 ? 16 : (1 << T)) * sizeof(u64);
-    const int tpr_log = logn - T, total = rows << tpr_log;   // tiles per row (log2), work items
+    const int tpr_log = logn - T;   // tiles per row (log2)
     NttArgs A;
     A.dst = dst; A.mi = c->d_mod; A.logn = logn; A.T = T; A.a = a; A.twlog = c->log_n;
     A.smap = smap; A.dmap = dmap;
     if (fuse) A.f = *fuse; else A.f = NttFuse{};
-    A.first_pass = 1;
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
     A.twd = inverse ? c->d_itwd : c->d_twd;
     A.twb = inverse ? c->d_itwb : c->d_twb;
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
-    if (!inverse) {
-        A.src = src;
-        if (a > 0) {
-            A.pass = 0; A.final_pass = 0;
-            launch_pass<false, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, false), m);
-            A.src = dst; A.smap = dmap; A.first_pass = 0;
+    for (int r0 = 0; r0 < rows; r0 += NTT_MAX_ROWS) {
+        const int cnt = rows - r0 < NTT_MAX_ROWS ? rows - r0 : NTT_MAX_ROWS, total = cnt << tpr_log;
+        NttRows R1, R2;                                     // first pass: src map -> dst map; second pass: in place in dst
+        for (int i = 0; i < cnt; i++) {
+            const int r = r0 + i, mid = m.m[r % m.n];
+            const ModInfo& mi = c->h_mod[mid];
+            R1.src[i] = row_of(smap, r); R1.dst[i] = row_of(dmap, r); R1.epi[i] = fuse ? row_of(fuse->emap, r) : 0;
+            R1.mid[i] = (short)mid; R1.q[i] = mi.q; R1.qinv[i] = 1.0 / (double)mi.q;
+            R1.kind[i] = (mi.bits <= FP_BITS && A.twd) ? ROW_FP : ((inverse ? mi.bits > 46 : mi.bits > 58) ? ROW_INT_FIX : ROW_INT);
         }
-        A.pass = 1; A.final_pass = 1;
-        launch_pass<false, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, false), m);
-    } else {
-        A.src = src; A.pass = 1; A.final_pass = a == 0;
-        launch_pass<true, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, true), m);
-        if (a > 0) {
-            A.src = dst; A.smap = dmap; A.pass = 0; A.final_pass = 1; A.first_pass = 0;
-            launch_pass<true, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, true), m);
+        R2 = R1;
+        for (int i = 0; i < cnt; i++) R2.src[i] = R1.dst[i];
+        A.first_pass = 1;
+        if (!inverse) {
+            A.src = src;
+            if (a > 0) {
+                A.pass = 0; A.final_pass = 0;
+                launch_pass<false, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, false), R1);
+                A.src = dst; A.first_pass = 0;
+            }
+            A.pass = 1; A.final_pass = 1;
+            launch_pass<false, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, false), a > 0 ? R2 : R1);
+        } else {
+            A.src = src; A.pass = 1; A.final_pass = a == 0;
+            launch_pass<true, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, true), R1);
+            if (a > 0) {
+                A.src = dst; A.pass = 0; A.final_pass = 1; A.first_pass = 0;
+                launch_pass<true, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, true), R2);
+            }
         }
     }
 }
