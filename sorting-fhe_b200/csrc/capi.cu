@@ -58,8 +58,8 @@ void context_release(Context* c) {
         for (auto e : c->enc_events) if (e) cudaEventDestroy(e);
         for (auto e : c->prof.pool) cudaEventDestroy(e);
         for (auto& kv : c->ks) {
-            for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); }
-            cudaFree(kv.second.moddown.d_hatinv); cudaFree(kv.second.moddown.d_hatinv_sh); cudaFree(kv.second.moddown.d_hatmod);
+            for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); cudaFree(t.d_hatplain); }
+            cudaFree(kv.second.moddown.d_hatinv); cudaFree(kv.second.moddown.d_hatinv_sh); cudaFree(kv.second.moddown.d_hatmod); cudaFree(kv.second.moddown.d_hatplain);
             cudaFree(kv.second.d_pinv); cudaFree(kv.second.d_pinv_sh);
             cudaFree(kv.second.d_modup_scale); cudaFree(kv.second.d_moddown_scale);
         }

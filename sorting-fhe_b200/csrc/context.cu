@@ -213,7 +213,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
 
 static void fill_conv(Context* c, ConvTables& t, const std::vector<int>& in_ids, const std::vector<int>& out_ids) {
     t.nin = (int)in_ids.size(); t.nout = (int)out_ids.size();
-    std::vector<u64> hatinv(t.nin), hatinv_sh(t.nin), hatmod((size_t)t.nin * t.nout);
+    std::vector<u64> hatinv(t.nin), hatinv_sh(t.nin), hatmod((size_t)t.nin * t.nout), hatplain((size_t)t.nin * t.nout);
     for (int i = 0; i < t.nin; i++) {
         t.in_ids[i] = (short)in_ids[i];
         u64 qi = c->moduli[in_ids[i]], h = 1;
@@ -223,6 +223,7 @@ static void fill_conv(Context* c, ConvTables& t, const std::vector<int>& in_ids,
             u64 tj = c->moduli[out_ids[j]], hm = 1;
             for (int k = 0; k < t.nin; k++) if (k != i) hm = mulmod(hm, c->moduli[in_ids[k]] % tj, tj);
             hatmod[(size_t)i * t.nout + j] = (u64)(((u128)hm << 64) % tj);   // Montgomery form
+            hatplain[(size_t)i * t.nout + j] = hm;
         }
     }
     {   // k_conv_split: digit (< 2^20) x half (< 2^32, < 2^28) products, at most 12 per 64-bit column; all moduli < 2^60
@@ -234,7 +235,7 @@ static void fill_conv(Context* c, ConvTables& t, const std::vector<int>& in_ids,
     t.wide = 0;
     for (int i = 0; i < t.nin && i < 32; i++) if (c->moduli[in_ids[i]] >> 42) t.wide |= 1u << i;
     for (int j = 0; j < t.nout; j++) t.out_ids[j] = (short)out_ids[j];
-    t.d_hatinv = upload(c, hatinv); t.d_hatinv_sh = upload(c, hatinv_sh); t.d_hatmod = upload(c, hatmod);
+    t.d_hatinv = upload(c, hatinv); t.d_hatinv_sh = upload(c, hatinv_sh); t.d_hatmod = upload(c, hatmod); t.d_hatplain = upload(c, hatplain);
 }
 
 const KsTables& get_ks_tables(Context* c, int nl) {

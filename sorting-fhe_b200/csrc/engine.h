@@ -47,6 +47,7 @@ struct ConvTables {        // ApproxSwitchCRTBasis tables for one (source basis 
     u64* d_hatinv;         // [nin]   (Qhat_i^-1 mod q_i)
     u64* d_hatinv_sh;      // [nin]   Shoup companions
     u64* d_hatmod;         // [nin][nout]  (Qhat_i mod t_j) * 2^64 mod t_j  (Montgomery form)
+    u64* d_hatplain;       // [nin][nout]  Qhat_i mod t_j (plain form: FP64 epilogue of k_conv_fp2 on targets of <= 42 bits)
     unsigned wide = 0;     // bit i: source modulus i has more than 42 bits
     bool split_ok = false; // the 32-bit-halves kernel's 64-bit column sums cannot overflow for this basis pair (keyswitch.cu)
 };
@@ -211,7 +212,7 @@ void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
 #define MAX_CONV_IN 24
 #define MAX_CONV_OUT 88
-struct ConvGroup { int in_row0, nin, out_row0, nout; const u64* hatmod; /* [nin][nout] Montgomery form */
+struct ConvGroup { int in_row0, nin, out_row0, nout; const u64* hatmod; /* [nin][nout] Montgomery form */ const u64* hatplain; /* plain form */
                    unsigned wide; /* bit i: source modulus i is wider than 42 bits (its residues have a third 21-bit piece, k_conv_fp) */ };
 struct ConvBatch { int ng; ConvGroup g[4]; short out_ids[4][MAX_CONV_OUT]; bool split_ok = false; /* every group passes ConvTables::split_ok */ };
 

@@ -280,7 +280,7 @@ u64* key_switch_modup(Context* c, const u64* src, int nl) {
         int row0 = 0;
         for (int j = 0; j < t.nparts; j++) {
             const ConvTables& ct = t.modup[j];
-            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod, ct.wide};
+            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod, ct.d_hatplain, ct.wide};
             for (int i = 0; i < ct.nout; i++) { B.out_ids[j][i] = ct.out_ids[i]; if (m.n < MAX_LIMBS) m.m[m.n++] = ct.out_ids[i]; }
             row0 += ct.nout;
         }
@@ -324,7 +324,7 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
     {
         ConvBatch B; B.ng = 2; B.split_ok = t.moddown.split_ok;
         for (int h = 0; h < 2; h++) {
-            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod, t.moddown.wide};
+            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod, t.moddown.d_hatplain, t.moddown.wide};
             for (int i = 0; i < nl; i++) B.out_ids[h][i] = (short)i;
         }
         launch_conv_batch(c, conv2, pp, B);

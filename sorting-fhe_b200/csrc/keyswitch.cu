@@ -182,6 +182,104 @@ k_conv_fp(u64* __restrict__ out, const u64* __restrict__ in, const __grid_consta
         dst[(size_t)jj * n] = mont_reduce(lo, hi, m.q, m.qinv);
     }
 }
+// k_conv_fp2: the same contraction with (1) no global ModInfo load per output -- the per-output scalars are staged in
+// shared memory next to the constants -- and (2) for target moduli of at most 42 bits (30 of the 32 Q limbs) an FP64
+// epilogue: the constants are the PLAIN residues Qhat_i mod t_j, the exact column sums s_k < 2^48 are folded with
+//   out = s0 + s1 * (2^21 mod t) + s2 * (2^42 mod t) [+ s3 * (2^63 mod t)]   mod t
+// by exact floating-point modular products (fp_mulmod of ntt.cu: every intermediate an integer below 2^53), instead of
+// rebuilding a 128-bit integer and Montgomery-reducing it on the integer pipes (~45 instructions per output, as many as
+// the contraction itself in k_conv_fp).  60-bit targets keep the Montgomery-form constants and the integer epilogue.
+// Both give the canonical residue of the same integer sum, so the output equals k_conv_batch's bit for bit.
+#define CV_MAGIC 6755399441055744.0
+__device__ __forceinline__ double cv_mulmod(double a, double w, double q, double qinv) {
+    const double h = __dmul_rn(a, w);
+    const double l = __fma_rn(a, w, -h);
+    const double qh = __dadd_rn(__fma_rn(h, qinv, CV_MAGIC), -CV_MAGIC);
+    return __dadd_rn(__fma_rn(-qh, q, h), l);
+}
+struct ConvOut { double q, qinv, w2, w3; u64 qi, qinv64; int narrow, pad; };   // 56 bytes -> padded to 64
+template <int NI, int WMODE>
+__global__ void __launch_bounds__(256)
+k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_constant__ ConvBatch B, const ModInfo* __restrict__ mi, int n,
+           int ysplit) {
+    pdl_sync();
+    extern __shared__ double4 sh_k[];                     // [jc][NI] (c0, c1, c2, -) then [jc] ConvOut
+    const int gi = blockIdx.y / ysplit, part = blockIdx.y - gi * ysplit;
+    const int nin = B.g[gi].nin, nout = B.g[gi].nout;
+    const int per = (nout + ysplit - 1) / ysplit, jlo = part * per, jc = min(per, nout - jlo);
+    if (jc <= 0) return;
+    ConvOut* sh_o = reinterpret_cast<ConvOut*>(sh_k + (size_t)per * NI);
+    for (int t = threadIdx.x; t < jc; t += blockDim.x) {
+        const ModInfo m = mi[B.out_ids[gi][jlo + t]];
+        ConvOut o;
+        o.qi = m.q; o.qinv64 = m.qinv; o.q = (double)m.q; o.qinv = __drcp_rn(o.q); o.narrow = m.bits <= 42 ? 1 : 0; o.pad = 0;
+        o.w2 = o.narrow ? (double)((1ull << 42) % m.q) : 0.0;
+        o.w3 = o.narrow ? (double)((1ull << 63) % m.q) : 0.0;
+        sh_o[t] = o;
+    }
+    for (int t = threadIdx.x; t < NI * jc; t += blockDim.x) {
+        const int jj = t / NI, i = t - jj * NI;
+        const bool narrow = mi[B.out_ids[gi][jlo + jj]].bits <= 42;
+        const u64* tab = narrow ? B.g[gi].hatplain : B.g[gi].hatmod;
+        const u64 h = i < nin ? tab[(size_t)i * nout + jlo + jj] : 0;
+        sh_k[t] = make_double4((double)((u32)h & 0x1FFFFFu), (double)((u32)(h >> 21) & 0x1FFFFFu), (double)(u32)(h >> 42), 0.0);
+    }
+    __syncthreads();
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= n) return;
+    constexpr int NW = WMODE == 2 ? NI : 1;
+    double y0[NI], y1[NI], y2[NW];
+    const u64* src = in + (size_t)B.g[gi].in_row0 * n + x;
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        const u64 v = i < nin ? src[(size_t)i * n] : 0;
+        y0[i] = piece_to_double((u32)v & 0x1FFFFFu);
+        y1[i] = piece_to_double((u32)(v >> 21) & 0x1FFFFFu);
+        if (i < NW) y2[i] = piece_to_double((u32)(v >> 42));
+    }
+    u64* dst = out + (size_t)(B.g[gi].out_row0 + jlo) * n + x;
+    for (int jj = 0; jj < jc; jj++) {
+        const double4* hp = sh_k + jj * NI;
+        const ConvOut o = sh_o[jj];
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+        if (o.narrow) {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const double4 c = hp[i];
+                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1);
+                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2);
+                if (WMODE == 2 || (WMODE == 1 && i == 0)) { s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); }
+            }
+            double r = __dadd_rn(s0, cv_mulmod(s1, 2097152.0, o.q, o.qinv));
+            r = __dadd_rn(r, cv_mulmod(s2, o.w2, o.q, o.qinv));
+            if (WMODE != 0) r = __dadd_rn(r, cv_mulmod(s3, o.w3, o.q, o.qinv));
+            const double t = __dadd_rn(__fma_rn(r, o.qinv, CV_MAGIC), -CV_MAGIC);
+            r = __fma_rn(-t, o.q, r);
+            if (r < 0.0) r = __dadd_rn(r, o.q);
+            dst[(size_t)jj * n] = column_to_u64(r);
+        } else {
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const double4 c = hp[i];
+                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1); s2 = __fma_rn(y0[i], c.z, s2);
+                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2); s3 = __fma_rn(y1[i], c.z, s3);
+                if (WMODE == 2 || (WMODE == 1 && i == 0)) {
+                    s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); s4 = __fma_rn(y2[i], c.z, s4);
+                }
+            }
+            u64 lo = column_to_u64(s0), hi = column_to_u64(s4) << 20;
+            add_shifted(lo, hi, column_to_u64(s1), 21); add_shifted(lo, hi, column_to_u64(s2), 42); add_shifted(lo, hi, column_to_u64(s3), 63);
+            dst[(size_t)jj * n] = mont_reduce(lo, hi, o.qi, o.qinv64);
+        }
+    }
+}
+template <int NI>
+static void launch_conv_fp2(Context* c, dim3 grid, int per, int wmode, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
+    const size_t smem = (size_t)NI * per * sizeof(double4) + (size_t)per * sizeof(ConvOut);
+    if (wmode == 0) launch_pdl(c, k_conv_fp2<NI, 0>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+    else if (wmode == 1) launch_pdl(c, k_conv_fp2<NI, 1>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+    else launch_pdl(c, k_conv_fp2<NI, 2>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
+}
 template <int NI>
 static void launch_conv_fp(Context* c, dim3 grid, size_t smem, int wmode, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
     if (wmode == 0) launch_pdl(c, k_conv_fp<NI, 0>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
@@ -196,7 +294,23 @@ void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) 
     static const int ysplit = getenv("CKKS_B200_CONV_YSPLIT") ? atoi(getenv("CKKS_B200_CONV_YSPLIT")) : 2;
     static const bool generic = getenv("CKKS_B200_GENERIC_CONV") != nullptr;
     static const bool int_conv = getenv("CKKS_B200_INT_CONV") != nullptr;   // A/B switch: the integer-pipe kernel
-    if (B.split_ok && !generic && !int_conv && c->n >= 512) {
+    static const bool old_fp = getenv("CKKS_B200_OLD_CONV") != nullptr;                 // A/B switch: round 1's k_conv_fp
+    if (B.split_ok && !generic && !int_conv && !old_fp && c->n >= 512) {
+        int wmode = 0;
+        for (int i = 0; i < B.ng; i++) wmode = std::max(wmode, B.g[i].wide == 0 ? 0 : B.g[i].wide == 1 ? 1 : 2);
+        dim3 grid((c->n + 255) / 256, B.ng * ysplit);
+        const int ni = max_in <= 2 ? 2 : max_in <= 4 ? 4 : max_in <= 6 ? 6 : max_in <= 8 ? 8 : max_in <= 10 ? 10 : max_in <= 11 ? 11 : 12;
+        const int per = (max_out + ysplit - 1) / ysplit;
+        switch (ni) {
+            case 2: launch_conv_fp2<2>(c, grid, per, wmode, out, in, B, ysplit); break;
+            case 4: launch_conv_fp2<4>(c, grid, per, wmode, out, in, B, ysplit); break;
+            case 6: launch_conv_fp2<6>(c, grid, per, wmode, out, in, B, ysplit); break;
+            case 8: launch_conv_fp2<8>(c, grid, per, wmode, out, in, B, ysplit); break;
+            case 10: launch_conv_fp2<10>(c, grid, per, wmode, out, in, B, ysplit); break;
+            case 11: launch_conv_fp2<11>(c, grid, per, wmode, out, in, B, ysplit); break;
+            default: launch_conv_fp2<12>(c, grid, per, wmode, out, in, B, ysplit); break;
+        }
+    } else if (B.split_ok && !generic && !int_conv && c->n >= 512) {
         int wmode = 0;
         for (int i = 0; i < B.ng; i++) wmode = std::max(wmode, B.g[i].wide == 0 ? 0 : B.g[i].wide == 1 ? 1 : 2);
         dim3 grid((c->n + 255) / 256, B.ng * ysplit);
