@@ -140,6 +140,17 @@ class Evaluator:
                 self.L.orc_automorph_eval(P(sp[i]), P(self.secret[i]), c.log_n, kinv)
             self.rot[k] = self._switch_key_gen(self.secret, sp, k)
 
+    def conj_keygen(self):
+        """key for the conjugation automorphism X -> X^(2n-1) (its own inverse); EvalBootstrapKeyGen generates it"""
+        c = self.ctx
+        k = 2 * c.n - 1
+        if k in self.rot:
+            return
+        sp = np.empty_like(self.secret)
+        for i in range(sp.shape[0]):
+            self.L.orc_automorph_eval(P(sp[i]), P(self.secret[i]), c.log_n, k)
+        self.rot[k] = self._switch_key_gen(self.secret, sp, k)
+
     # ------------------------------------------------------------------ encode / decode
     def encode(self, values, scale_deg=1, level=0, slots=None):
         """MakeCKKSPackedPlaintext(values, scaleDeg, level, nullptr, slots): special inverse FFT,
@@ -155,7 +166,12 @@ class Evaluator:
         else:
             sf, deg = c.sf_real[level] ** scale_deg, scale_deg
         v = np.zeros(2 * slots, dtype=np.float64)
-        v[0:2 * len(values):2] = np.asarray(values, dtype=np.float64)
+        vals = np.asarray(values)
+        if np.iscomplexobj(vals):                      # complex slot values (bootstrapping's linear-transform diagonals)
+            v[0:2 * len(values):2] = vals.real
+            v[1:2 * len(values):2] = vals.imag
+        else:
+            v[0:2 * len(values):2] = np.asarray(values, dtype=np.float64)
         ksi, rot, M = c.fft_tables()
         self.L.orc_fft_special_inv(PD(v), slots, PD(ksi), rot.ctypes.data_as(u32p), M)
         nh, gap = c.n // 2, (c.n // 2) // slots

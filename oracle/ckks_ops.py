@@ -270,13 +270,47 @@ class OracleCC(ChebyshevMixin, Evaluator):
     def EvalSquare(self, a):
         return self.EvalMult(a, a)
 
-    def EvalRotate(self, a, r):
+    def EvalConjugate(self, a):
+        """complex conjugation of every slot: EvalAutomorphism with index 2n - 1"""
+        return self.EvalRotate(a, None, k=2 * self.ctx.n - 1)
+
+    def mod_raise(self, ct, level):
+        """bootstrapping's ModRaise: the single limb of `ct` (mod q0), read as centred integers, in every limb of
+        `level`; noiseScaleDeg 1, scaling factor := the level's"""
+        c = self.ctx
+        assert ct.nlimbs == 1 and ct.deg == 1
+        nl = c.size_q - level
+        out = np.empty((ct.d.shape[0], nl, c.n), dtype=np.uint64)
+        for p in range(ct.d.shape[0]):
+            coef = ct.d[p, 0].copy()
+            c.intt(coef, 0)
+            for i in range(nl):
+                self.L.orc_switch_modulus(P(out[p, i]), P(coef), c.n, c.q[0], c.q[i])
+            c.ntt_rows(out[p], list(range(nl)))
+        return Ct(out, level, 1, c.sf_real[level], ct.slots)
+
+    # ---- bootstrapping (oracle/bootstrap.py)
+    def EvalBootstrapSetup(self, level_budget=(4, 4), dim1=(0, 0), slots=0):
+        from .bootstrap import Bootstrapper
+        if not hasattr(self, "_boot"):
+            self._boot = {}
+        slots = slots or self.ctx.n // 4
+        self._boot[slots] = Bootstrapper(self, level_budget, slots)
+
+    def EvalBootstrapKeyGen(self, slots):
+        self._boot[slots].keygen()
+
+    def EvalBootstrap(self, ct, iters=1, prec=0):
+        return self._boot[ct.slots].bootstrap(ct)
+
+    def EvalRotate(self, a, r, k=None):
         """EvalRotate -> EvalAutomorphism: key-switch c1 with the rotation key, THEN apply the
         automorphism index permutation to both polynomials (rotation.h:224,231)"""
         c = self.ctx
-        k = self.auto_index(r)
+        if k is None:
+            k = self.auto_index(r)
         if k not in self.rot:
-            raise KeyError("EvalRotate: no rotation key for index %d" % r)
+            raise KeyError("EvalRotate: no rotation key for index %s" % r)
         self._count("rotate", a.nlimbs)
         ks = self.key_switch_core(np.ascontiguousarray(a.d[1]), self.rot[k])
         out = np.empty_like(a.d)
