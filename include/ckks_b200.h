@@ -127,6 +127,20 @@ int ckks_eval_chebyshev_series_ps(ckks_ctx_t* ctx, const ckks_ct_t* x, const dou
 int ckks_eval_chebyshev_series(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, double a, double b,
                                ckks_ct_t** out);
 /* EvalPolyLinear(ct, coeffs) -- mehp24_utils.cpp:256-259 */
+/* CKKS bootstrapping (reference src/k-way/EvalUtils.cpp:76, src/sign.cpp:168; set-up as tests/k-way/KWaySort2Test.cpp:47-49):
+ * EvalBootstrapSetup(levelBudget, dim1, slots) precomputes the CoeffsToSlots / SlotsToCoeffs diagonals for `slots` (sparse
+ * packing, slots <= ring / 4; dim1 is accepted and ignored -- the diagonals of a group are evaluated with hoisted rotations),
+ * EvalBootstrapKeyGen generates the rotation and conjugation keys, EvalBootstrap refreshes a ciphertext whose level is
+ * below the multiplicative depth.  ckks_make_packed_plaintext_complex / ckks_eval_conjugate / ckks_mod_raise are the three
+ * primitives bootstrapping adds to the engine (exposed for the parity tests). */
+int ckks_eval_bootstrap_setup(ckks_ctx_t* ctx, int budget_c2s, int budget_s2c, int dim1_c2s, int dim1_s2c, int slots);
+int ckks_eval_bootstrap_keygen(ckks_ctx_t* ctx, int slots);
+int ckks_eval_bootstrap(ckks_ctx_t* ctx, const ckks_ct_t* ct, ckks_ct_t** out);
+int ckks_make_packed_plaintext_complex(ckks_ctx_t* ctx, const double* re_im, int count, int scale_deg, int level, int slots,
+                                       ckks_ct_t** out);
+int ckks_eval_conjugate(ckks_ctx_t* ctx, const ckks_ct_t* ct, ckks_ct_t** out);
+int ckks_mod_raise(ckks_ctx_t* ctx, const ckks_ct_t* ct, int level, ckks_ct_t** out);
+
 int ckks_eval_poly_linear(ckks_ctx_t* ctx, const ckks_ct_t* x, const double* coeffs, int count, ckks_ct_t** out);
 
 /* op statistics (JSON) for roofline accounting; reset clears counters */

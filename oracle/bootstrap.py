@@ -21,12 +21,29 @@ import math
 
 import numpy as np
 
-from .cheby import cheb_coefficients
 
 K_UNIFORM = 512          # bound on |I| + 1 for UNIFORM_TERNARY secrets (OpenFHE K_UNIFORM)
 R_UNIFORM = 6            # double-angle iterations (OpenFHE R_UNIFORM)
 CHEB_DEGREE = 119        # same Paterson-Stockmeyer depth (8 - 1) as OpenFHE's degree-89 table
 CORRECTION = 10          # message scaled by 2^-10 relative to q0 before the modular reduction
+
+
+def boot_cheb_coefficients():
+    """c_i = (2 / n) sum_j f(u_j) cos(step i (j + 1/2)), u_j = cos(step (j + 1/2)), f(u) = cos((2 pi K u - pi/2) / 2^R):
+    libm calls and plain left-to-right sums, the same operations in the same order as csrc/bootstrap.cu"""
+    n = CHEB_DEGREE + 1
+    step = math.pi / float(n)
+    f = []
+    for j in range(n):
+        u = math.cos(step * (float(j) + 0.5))
+        f.append(math.cos((2.0 * math.pi * float(K_UNIFORM) * u - 0.5 * math.pi) / float(1 << R_UNIFORM)))
+    c = []
+    for i in range(n):
+        acc = 0.0
+        for j in range(n):
+            acc += f[j] * math.cos(step * float(i) * (float(j) + 0.5))
+        c.append(acc * 2.0 / float(n))
+    return c
 
 
 def layer_groups(log_s, budget):
@@ -117,8 +134,7 @@ class Bootstrapper:
             if k == 0:
                 grp["alt"] = diagonals(re, im, 0.0, ss)                 # i G: applied to the imaginary-part ciphertext
             self.s2c.append(grp)
-        self.cheb = cheb_coefficients(
-            lambda u: math.cos((2.0 * math.pi * K_UNIFORM * u - 0.5 * math.pi) / float(1 << R_UNIFORM)), -1.0, 1.0, CHEB_DEGREE)
+        self.cheb = boot_cheb_coefficients()
         self._pt = {}
 
     # ---- EvalBootstrapKeyGen

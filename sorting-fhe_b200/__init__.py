@@ -311,6 +311,36 @@ class Engine:
     def ct_mod_reduce(self, ct):
         _chk(_L.ckks_ct_mod_reduce(_vp(self.h), _vp(ct.h)))
 
+    # ---- bootstrapping (csrc/bootstrap.cu)
+    def EvalBootstrapSetup(self, level_budget=(4, 4), dim1=(0, 0), slots=0):
+        _chk(_L.ckks_eval_bootstrap_setup(_vp(self.h), int(level_budget[0]), int(level_budget[1]), int(dim1[0]), int(dim1[1]), int(slots)))
+
+    def EvalBootstrapKeyGen(self, slots=0):
+        _chk(_L.ckks_eval_bootstrap_keygen(_vp(self.h), int(slots)))
+
+    def EvalBootstrap(self, ct, iters=1, prec=0):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_bootstrap(_vp(self.h), _vp(ct.h), ctypes.byref(o)), o)
+
+    def EvalConjugate(self, ct):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_eval_conjugate(_vp(self.h), _vp(ct.h), ctypes.byref(o)), o)
+
+    def mod_raise(self, ct, level):
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_mod_raise(_vp(self.h), _vp(ct.h), int(level), ctypes.byref(o)), o)
+
+    def encode_complex(self, values, scale_deg=1, level=0, slots=None):
+        v = np.asarray(values, dtype=np.complex128)
+        if slots is None:
+            slots = 1
+            while slots < len(v):
+                slots <<= 1
+        buf = np.empty(2 * len(v), dtype=np.float64)
+        buf[0::2], buf[1::2] = v.real, v.imag
+        o = ctypes.c_void_p()
+        return self._out(_L.ckks_make_packed_plaintext_complex(_vp(self.h), _f64p(buf), len(v), scale_deg, level, slots, ctypes.byref(o)), o)
+
     def EvalFastRotationPrecompute(self, a):
         o = ctypes.c_void_p()
         return self._out(_L.ckks_fast_rotation_precompute(_vp(self.h), _vp(a.h), ctypes.byref(o)), o)
@@ -363,6 +393,12 @@ class Engine:
                                     0 if rotation is None else rotation, _vp(out_ptr)))
 
 
+_L.ckks_eval_bootstrap_setup.argtypes = [_vp, _i, _i, _i, _i, _i]
+_L.ckks_eval_bootstrap_keygen.argtypes = [_vp, _i]
+_L.ckks_eval_bootstrap.argtypes = [_vp, _vp, _pp]
+_L.ckks_eval_conjugate.argtypes = [_vp, _vp, _pp]
+_L.ckks_mod_raise.argtypes = [_vp, _vp, _i, _pp]
+_L.ckks_make_packed_plaintext_complex.argtypes = [_vp, ctypes.POINTER(ctypes.c_double), _i, _i, _i, _i, _pp]
 _L.ckks_ctx_set_option.argtypes = [_vp, _i, ctypes.c_int64]
 _L.ckks_ctx_create.argtypes = [_pp, _i, _i, _i, _i, _i, _i, _u64, _i]
 _L.ckks_ct_import.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), _i, _i, _i, _i, _d, _i, _pp]

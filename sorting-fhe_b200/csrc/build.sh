@@ -7,7 +7,7 @@ OUT=../libckks_b200.so
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fno-strict-aliasing --fmad=false"
 OBJS=""
 PIDS=""
-for f in ntt kernels keyswitch encode context evaluator cheby capi; do
+for f in ntt kernels keyswitch encode context evaluator cheby bootstrap capi; do
   if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ engine.h -nt build/$f.o ] || [ modarith.cuh -nt build/$f.o ] || [ evaluator.h -nt build/$f.o ] || [ ../../include/ckks_b200.h -nt build/$f.o ]; then
     mkdir -p build
     rm -f build/$f.o

@@ -95,6 +95,7 @@ int ckks_ctx_destroy(ckks_ctx_t* x) {
     Context* c = &x->c;
     Locked lk_(c);
     if (c->closed) return 0;
+    boot_release(c);                                    // cached diagonal plaintexts are handles of this context
     c->closed = true;
     if (c->live_cts == 0) c->release_pending = true;   // otherwise the last ckks_ct_free finishes the teardown
     API_END
@@ -316,36 +317,9 @@ int ckks_eval_inner_product_plain(ckks_ctx_t* x, const ckks_ct_t* init, const ck
 int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
     API_BEGIN Locked lk_(C(x));
     if (count < 1) throw std::runtime_error("EvalAddMany: empty list");
-    {   // all operands already aligned (the sorters' case): one pass over the inputs.  Modular addition is
-        // associative, so the result equals the pairwise tree's bit for bit.
-        const Ct* f = G(cts[0]); bool same = count <= 32 && f->parts == 2 && f->lrep == 0;
-        for (int i = 1; i < count && same; i++) {
-            const Ct* g = G(cts[i]);
-            same = g->parts == f->parts && g->nl == f->nl && g->level == f->level && g->deg == f->deg && g->sf == f->sf && g->lrep == 0;
-        }
-        if (same && count > 2) {
-            int slots = 0; std::vector<const u64*> ins;
-            for (int i = 0; i < count; i++) { ct_wait(G(cts[i])); ins.push_back(G(cts[i])->d); slots = std::max(slots, G(cts[i])->slots); }
-            Ct* r = ct_new(f->ctx, f->parts, f->nl, f->level, f->deg, f->sf, slots);
-            f->ctx->stats.ops[{"add", f->nl}] += count - 1;
-            launch_add_many(f->ctx, r->d, ins.data(), count, f->parts * f->nl, f->nl);
-            *out = box(r);
-            return 0;
-        }
-    }
-    std::vector<Ct*> cur; std::vector<bool> owned;
-    for (int i = 0; i < count; i++) { cur.push_back(const_cast<Ct*>(G(cts[i]))); owned.push_back(false); }
-    while (cur.size() > 1) {   // binary tree, same association as oracle EvalAddMany
-        std::vector<Ct*> nxt; std::vector<bool> no;
-        for (size_t i = 0; i + 1 < cur.size(); i += 2) {
-            nxt.push_back(eval_add(cur[i], cur[i + 1], 1)); no.push_back(true);
-            if (owned[i]) ct_free(cur[i]);
-            if (owned[i + 1]) ct_free(cur[i + 1]);
-        }
-        if (cur.size() % 2) { nxt.push_back(cur.back()); no.push_back(owned.back()); }
-        cur.swap(nxt); owned.swap(no);
-    }
-    *out = box(owned[0] ? cur[0] : ct_clone(cur[0]));
+    std::vector<const Ct*> v;
+    for (int i = 0; i < count; i++) v.push_back(G(cts[i]));
+    *out = box(eval_add_many(v));
     API_END
 }
 int ckks_eval_mult(ckks_ctx_t* x, const ckks_ct_t* a, const ckks_ct_t* b, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_mult(G(a), G(b))); API_END }
@@ -374,6 +348,17 @@ int ckks_eval_chebyshev_series(ckks_ctx_t* x, const ckks_ct_t* ct, const double*
 int ckks_eval_poly_linear(ckks_ctx_t* x, const ckks_ct_t* ct, const double* coeffs, int count, ckks_ct_t** out) {
     API_BEGIN Locked lk_(C(x)); *out = box(eval_poly_linear(G(ct), std::vector<double>(coeffs, coeffs + count))); API_END
 }
+
+int ckks_make_packed_plaintext_complex(ckks_ctx_t* x, const double* re_im, int count, int scale_deg, int level, int slots, ckks_ct_t** out) {
+    API_BEGIN Locked lk_(C(x)); *out = box(encode(C(x), re_im, count, scale_deg, level, slots, 1)); API_END
+}
+int ckks_eval_conjugate(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(eval_conjugate(G(a))); API_END }
+int ckks_mod_raise(ckks_ctx_t* x, const ckks_ct_t* a, int level, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(mod_raise(G(a), level)); API_END }
+int ckks_eval_bootstrap_setup(ckks_ctx_t* x, int budget_c2s, int budget_s2c, int dim1_c2s, int dim1_s2c, int slots) {
+    API_BEGIN Locked lk_(C(x)); (void)dim1_c2s; (void)dim1_s2c; boot_setup(C(x), budget_c2s, budget_s2c, slots); API_END
+}
+int ckks_eval_bootstrap_keygen(ckks_ctx_t* x, int slots) { API_BEGIN Locked lk_(C(x)); boot_keygen(C(x), slots); API_END }
+int ckks_eval_bootstrap(ckks_ctx_t* x, const ckks_ct_t* a, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(boot_eval(G(a))); API_END }
 
 int ckks_stats_json(ckks_ctx_t* x, char* buf, size_t cap) {
     API_BEGIN

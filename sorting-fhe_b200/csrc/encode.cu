@@ -161,7 +161,8 @@ static double* stage_values(Context* c, const double* h_values, int nvals) {
     return p;
 }
 
-void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep) {
+// is_complex: h_values holds nvals (re, im) pairs (bootstrapping's linear-transform diagonals); nvals <= ring / 4
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep, int is_complex) {
     const int n_c = c->n >> lrep;   // compact row length (engine.h Ct::lrep)
     int bits = 0; while ((1 << bits) < slots) bits++;
     const int big_stages = bits > 11 ? bits - 11 : 0;
@@ -173,12 +174,20 @@ void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int 
         double2* a = (double2*)dev_alloc(c, 2 * (size_t)slots);
         double2* b = (double2*)dev_alloc(c, 2 * (size_t)slots);
         u64* mx = dev_alloc(c, 1);
-        double* staged = stage_values(c, h_values, nvals);
-        cudaMemcpyAsync(d_in, staged, (size_t)nvals * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+        int from_real = 1;
+        if (is_complex) {
+            if (2 * nvals > c->n / 2) throw std::runtime_error("complex encode: at most ring / 4 values");
+            double* staged = stage_values(c, h_values, 2 * nvals);
+            cudaMemsetAsync(a, 0, (size_t)slots * sizeof(double2), c->stream);
+            cudaMemcpyAsync(a, staged, (size_t)2 * nvals * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+            from_real = 0;
+        } else {
+            double* staged = stage_values(c, h_values, nvals);
+            cudaMemcpyAsync(d_in, staged, (size_t)nvals * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+        }
         cudaEventRecord(c->enc_events[(c->enc_ring_pos - 1) % c->enc_events.size()], c->stream);
         cudaMemsetAsync(mx, 0, sizeof(u64), c->stream);
         const int M = 2 * c->n;
-        int from_real = 1;
         for (int len = slots; len > 2048; len >>= 1) {
             launch_pdl(c, k_fft_inv_stage_big, (slots / 2 + 255) / 256, 256, 0, a, d_in, nvals, from_real, slots, len,
                                                                                   (const double2*)c->d_ksi, c->d_rot, M);

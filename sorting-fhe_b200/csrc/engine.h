@@ -135,6 +135,7 @@ struct Context {
     // stream swap of the encode path, stats, event pools, key-switch tables, the twin / ModUp caches written on const
     // operands) is never touched by two host threads at once.  The GPU work is asynchronous; the lock covers enqueueing.
     std::recursive_mutex mu;
+    std::map<int, struct BootPlan*> boot;     // slots -> bootstrapping plan (bootstrap.cu)
     std::deque<const struct Ct*> modup_lru;   // handles that carry a cached ModUp, oldest first (bounded: evaluator.cu)
     int modup_cap = 8;
     int add_const_mode = 0;         // EvalAdd(ct, double) on noiseScaleDeg > 1: 0 = round(|x| * ct scale), 1 = OpenFHE CRTMult form
@@ -228,7 +229,7 @@ void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint
 void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream);
 void launch_evk_combine(Context* c, u64* b, const u64* a, const u64* e, const u64* s_new, const u64* s_old,
                         int lo, int hi);
-void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep = 0);
+void launch_encode(Context* c, u64* out, const double* h_values, int nvals, int slots, double sf, int nl, int lrep = 0, int is_complex = 0);
 void launch_decode(Context* c, double* h_out, const u64* m /*[<=2][n] coeff*/, int nlimbs, double sf, int slots);
 void launch_decrypt_combine(Context* c, u64* out, const Ct* ct, int use);
 void launch_encrypt_combine(Context* c, u64* out, const u64* pt, const u64* v, const u64* e0, const u64* e1, int nl);

@@ -528,9 +528,17 @@ Ct* eval_rotate(const Ct* a, int r) {
     Context* c = a->ctx;
     if (a->parts != 2) throw std::runtime_error("EvalRotate: ciphertext must have 2 components");
     if (r == 0) return ct_clone(a);   // EvalRotate / EvalAtIndex(ct, 0) returns a copy (no key involved)
-    uint32_t k = auto_index(c, r);
+    return eval_automorphism(a, auto_index(c, r), ("EvalRotate: no rotation key for index " + std::to_string(r)).c_str());
+}
+// complex conjugation of the slots: the automorphism X -> X^(2n-1) (bootstrapping splits real and imaginary parts with it)
+Ct* eval_conjugate(const Ct* a) {
+    if (a->parts != 2) throw std::runtime_error("EvalConjugate: ciphertext must have 2 components");
+    return eval_automorphism(a, 2u * (uint32_t)a->ctx->n - 1u, "EvalConjugate: no conjugation key (EvalBootstrapKeyGen generates it)");
+}
+Ct* eval_automorphism(const Ct* a, uint32_t k, const char* what) {
+    Context* c = a->ctx;
     auto it = c->rot.find(k);
-    if (it == c->rot.end()) throw std::runtime_error("EvalRotate: no rotation key for index " + std::to_string(r));
+    if (it == c->rot.end()) throw std::runtime_error(what);
     count(c, "rotate", a->nl);
     const int nl = a->nl;
     Ct* out = ct_new(c, 2, nl, a->level, a->deg, a->sf, a->slots);
@@ -626,6 +634,19 @@ void relin_keygen(Context* c) {
     dev_free(c, s2);
 }
 
+void conj_keygen(Context* c) {
+    if (!c->d_secret && !c->dry) throw std::runtime_error("EvalBootstrapKeyGen: no secret key");
+    const uint32_t k = 2u * (uint32_t)c->n - 1u;              // its own inverse mod 2n
+    if (c->rot.count(k)) return;
+    const int M = c->M();
+    u64* sp = dev_alloc(c, words(c, M));
+    launch_automorph(c, sp, c->d_secret, M, k);
+    EvalKey key;
+    switch_key_gen(c, key, c->d_secret, sp, k);
+    c->rot[k] = key;
+    dev_free(c, sp);
+}
+
 void rot_keygen(Context* c, const int* indices, int count_) {
     if (!c->d_secret && !c->dry) throw std::runtime_error("EvalRotateKeyGen: no secret key");
     const int M = c->M(); const u64 m = 2ull * c->n;
@@ -643,7 +664,59 @@ void rot_keygen(Context* c, const int* indices, int count_) {
     dev_free(c, sp);
 }
 
-Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots) {
+// bootstrapping's ModRaise: the single limb of `a` (mod q0) is read as centred integers and reduced into every limb of
+// `level`; the result is declared noiseScaleDeg 1 at that level's scaling factor.  INTT of the q0 rows, then one forward
+// NTT launch whose prologue switches the q0 coefficients to each row's modulus (the rescale path's PRO_SWITCHMOD).
+Ct* mod_raise(const Ct* a, int level) {
+    Context* c = a->ctx;
+    if (a->nl != 1 || a->deg != 1 || a->lrep) throw std::runtime_error("ModRaise: expects one limb at noiseScaleDeg 1");
+    if (level < 0 || level >= c->size_q) throw std::runtime_error("ModRaise: bad level");
+    ct_wait(a);
+    const int nl = c->size_q - level, parts = a->parts;
+    count(c, "mod_raise", nl);
+    u64* coef = dev_alloc(c, words(c, parts));
+    LimbMods m0; m0.n = 1; m0.m[0] = 0;
+    launch_ntt_ex(c, coef, a->d, parts, m0, true, nullptr, RowMap{}, RowMap{});
+    Ct* out = ct_new(c, parts, nl, level, 1, c->sf_real[level], a->slots);
+    NttFuse f; f.pro = PRO_SWITCHMOD; f.pro_mod = 0;
+    launch_ntt_ex(c, out->d, coef, parts * nl, mods_q(nl), false, nullptr, RowMap{nl, 1, 0, 0}, RowMap{}, &f);
+    dev_free(c, coef);
+    return out;
+}
+
+// sum of ciphertexts; operands that already share level, limbs and scale (the common case) are added in one pass
+Ct* eval_add_many(const std::vector<const Ct*>& cts) {
+    if (cts.empty()) throw std::runtime_error("EvalAddMany: empty list");
+    const Ct* f = cts[0];
+    bool same = cts.size() <= 32 && f->parts == 2 && f->lrep == 0;
+    for (size_t i = 1; i < cts.size() && same; i++) {
+        const Ct* g = cts[i];
+        same = g->parts == f->parts && g->nl == f->nl && g->level == f->level && g->deg == f->deg && g->sf == f->sf && g->lrep == 0;
+    }
+    if (same && cts.size() > 2) {
+        int slots = 0; std::vector<const u64*> ins;
+        for (const Ct* g : cts) { ct_wait(g); ins.push_back(g->d); slots = std::max(slots, g->slots); }
+        Ct* r = ct_new(f->ctx, f->parts, f->nl, f->level, f->deg, f->sf, slots);
+        f->ctx->stats.ops[{"add", f->nl}] += (long)cts.size() - 1;
+        launch_add_many(f->ctx, r->d, ins.data(), (int)cts.size(), f->parts * f->nl, f->nl);
+        return r;
+    }
+    std::vector<Ct*> cur; std::vector<bool> owned;
+    for (const Ct* g : cts) { cur.push_back(const_cast<Ct*>(g)); owned.push_back(false); }
+    while (cur.size() > 1) {   // binary tree, same association as oracle EvalAddMany
+        std::vector<Ct*> nxt; std::vector<bool> no;
+        for (size_t i = 0; i + 1 < cur.size(); i += 2) {
+            nxt.push_back(eval_add(cur[i], cur[i + 1], 1)); no.push_back(true);
+            if (owned[i]) ct_free(cur[i]);
+            if (owned[i + 1]) ct_free(cur[i + 1]);
+        }
+        if (cur.size() % 2) { nxt.push_back(cur.back()); no.push_back(owned.back()); }
+        cur.swap(nxt); owned.swap(no);
+    }
+    return owned[0] ? cur[0] : ct_clone(cur[0]);
+}
+
+Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots, int is_complex) {
     if (slots <= 0) { slots = 1; while (slots < nvals) slots <<= 1; }
     if (nvals > slots || slots > c->n / 2 || (slots & (slots - 1))) throw std::runtime_error("MakeCKKSPackedPlaintext: bad slot count");
     if (level < 0 || level >= c->size_q) throw std::runtime_error("MakeCKKSPackedPlaintext: bad level");
@@ -657,7 +730,7 @@ Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level
     count(c, "encode", nl);
     if (c->dry || !c->enc_stream) {
         Ct* pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
-        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
+        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep, is_complex);
         return pt;
     }
     // the whole encode (allocation, FFT, expansion, NTT) is queued on the encode stream
@@ -666,7 +739,7 @@ Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level
     Ct* pt = nullptr;
     try {
         pt = ct_new(c, 1, nl, level, deg, sf, slots, lrep);
-        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep);
+        launch_encode(c, pt->d, values, nvals, slots, sf, nl, lrep, is_complex);
         pt->ready = enc_event(c);
         pt->enc_home = true;
     } catch (...) { c->stream = main; throw; }

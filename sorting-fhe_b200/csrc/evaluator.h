@@ -36,7 +36,17 @@ uint32_t auto_index(const Context* c, int r);
 void keygen(Context* c);
 void relin_keygen(Context* c);
 void rot_keygen(Context* c, const int* indices, int count);
-Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots);
+Ct* encode(Context* c, const double* values, int nvals, int scale_deg, int level, int slots, int is_complex = 0);
+void conj_keygen(Context* c);                                   // key of the conjugation automorphism X -> X^(2n-1)
+Ct* eval_automorphism(const Ct* a, uint32_t k, const char* what);   // key switch + index permutation for a keyed automorphism
+Ct* eval_conjugate(const Ct* a);
+Ct* mod_raise(const Ct* a, int level);                          // bootstrapping: q0 residues re-read in every limb of `level`
+Ct* eval_add_many(const std::vector<const Ct*>& cts);
+// bootstrap.cu
+void boot_setup(Context* c, int budget_c2s, int budget_s2c, int slots);
+void boot_keygen(Context* c, int slots);
+Ct* boot_eval(const Ct* ct);
+void boot_release(Context* c);
 Ct* encrypt(Context* c, const Ct* pt);
 void decrypt(const Ct* ct, double* out, int out_len);
 

@@ -376,9 +376,21 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
         ckks_check(ckks_eval_poly_linear(ctx, x->h, coeffs.data(), (int)coeffs.size(), &o), "EvalPolyLinear");
         return wrap(o);
     }
-    // EvalBootstrap (EvalUtils.cpp:76, sign.cpp:168): not part of this round's hot-path scope
-    CT EvalBootstrap(const CT&, uint32_t = 1, uint32_t = 0) const {
-        throw std::runtime_error("EvalBootstrap: CKKS bootstrapping is not implemented by the B200 engine yet");
+    // CKKS bootstrapping (EvalUtils.cpp:76, sign.cpp:168; set-up: tests/k-way/KWaySort2Test.cpp:47-49).  Sparse packing
+    // (slots <= ring / 4); dim1 is accepted and ignored; numIterations / precision of the Meta-BTS variant are ignored.
+    void EvalBootstrapSetup(std::vector<uint32_t> levelBudget = {5, 4}, std::vector<uint32_t> dim1 = {0, 0}, uint32_t slots = 0,
+                            uint32_t /*correctionFactor*/ = 0, bool /*precompute*/ = true) {
+        if (levelBudget.size() != 2) throw std::runtime_error("EvalBootstrapSetup: levelBudget needs two entries");
+        dim1.resize(2, 0);
+        ckks_check(ckks_eval_bootstrap_setup(ctx, (int)levelBudget[0], (int)levelBudget[1], (int)dim1[0], (int)dim1[1], (int)slots),
+                   "EvalBootstrapSetup");
+    }
+    void EvalBootstrapKeyGen(const PrivateKey<DCRTPoly>&, uint32_t slots) {
+        ckks_check(ckks_eval_bootstrap_keygen(ctx, (int)slots), "EvalBootstrapKeyGen");
+    }
+    CT EvalBootstrap(const CT& a, uint32_t /*numIterations*/ = 1, uint32_t /*precision*/ = 0) const {
+        if (!a) throw std::runtime_error("EvalBootstrap: null ciphertext");
+        ckks_ct_t* o = nullptr; ckks_check(ckks_eval_bootstrap(ctx, a->h, &o), "EvalBootstrap"); return wrap(o);
     }
 };
 template <class E> using CryptoContext = std::shared_ptr<CryptoContextImpl<E>>;

@@ -8,7 +8,7 @@ NAME=$1; EXTRA=$2; shift 2
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fno-strict-aliasing --fmad=false"
 OBJS=""
-for f in ntt kernels keyswitch encode context evaluator cheby capi; do
+for f in ntt kernels keyswitch encode context evaluator cheby bootstrap capi; do
   o=build/$f.o
   for v in "$@"; do if [ "$v" = "$f" ]; then o=build/${f}_$NAME.o; $NVCC $FLAGS $EXTRA -c $f.cu -o $o & fi; done
   OBJS="$OBJS $o"
