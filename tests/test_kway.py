@@ -149,3 +149,27 @@ def test_n128_compare_swap_stages_ring17():
     assert out.level <= depth
     assert np.max(np.abs(got - want)) < 0.01
     eng.close()
+
+
+@pytest.mark.gpu
+def test_n128_full_network_with_bootstrapping_ring17():
+    """BASELINE config 4 end to end: the whole k = 2, M = 7 network on 128 values (28 stages, src/k-way/Sorter.cpp:284-404) at
+    KWayAdapter's card (ring 2^17, depth 40, first 60 / scaling 59, level budget {4,4}: src/kway_adapter.h:41-64) with
+    EvalBootstrap wherever checkLevelAndBoot / sign's lazy bootstrap ask for it (EvalUtils.cpp:57-86, sign.cpp:164-171);
+    sign configuration of tests/k-way/KWaySort2Test.cpp:117-121,157; gate 0.01 (:214)."""
+    n, k, M = 128, 2, 7
+    depth, scale, first, rots = sf.kway_params(n)
+    eng = sf.Engine(17, depth, scale, first, seed=2)
+    try:
+        eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+        eng.EvalBootstrapSetup((4, 4), (0, 0), n)
+        eng.EvalBootstrapKeyGen(n)
+        v = np.random.default_rng(3).permutation(n) * ((1.0 - 1e-8) / n)      # getVectorWithMinDiff(N, 0, 1, (1 - 1e-8) / N)
+        eng.stats(reset=True)
+        out = sf.kway_sort(eng, eng.encrypt(eng.encode(v, slots=n)), n, k, M, (3, 2, 3), depth)
+        got = eng.decrypt(out, n)
+        boots = sum(cnt for name, nl, cnt in eng.stats()["ops"] if name == "bootstrap")
+        assert boots >= 10, boots
+        assert np.max(np.abs(got - np.sort(v))) < 0.01, np.max(np.abs(got - np.sort(v)))
+    finally:
+        eng.close()
