@@ -2,9 +2,10 @@
 // (src/k-way/Masking.cpp:26-167), EvalUtils (src/k-way/EvalUtils.cpp:18-147), SortUtils (src/k-way/SortUtils.cpp:5-82,
 // 202-236), Sorter (src/k-way/Sorter.cpp:8-70,180-262,284-404) and KWayAdapter's parameter card
 // (src/kway_adapter.h:41-64).  k = 2, 3 and 5 (BASELINE config 4 is k = 2; k = 5 adds the 4-/5-sorters, SortUtils.cpp:80-200,
-// 239-433, Sorter.cpp:71-178, 264-282).  checkLevelAndBoot calls cc->EvalBootstrap exactly where the reference does -- the B200 engine has
-// no bootstrapping yet, so a network runs as far as the multiplicative depth allows and the call
-// throws beyond that.  Orchestration only: every cc-> call is a CUDA kernel schedule inside libckks_b200.so.
+// 239-433, Sorter.cpp:71-178, 264-282).  checkLevelAndBoot calls cc->EvalBootstrap exactly where the reference does
+// (EvalUtils.cpp:57-86); the engine's bootstrapping (csrc/bootstrap.cu) refreshes the ciphertext there, so the whole
+// 28-stage k = 2, N = 128 network runs at KWayAdapter's depth-40 card.  Orchestration only: every cc-> call is a CUDA
+// kernel schedule inside libckks_b200.so.
 #pragma once
 #include <cmath>
 #include <tuple>

@@ -72,16 +72,26 @@ def compare_full_slot():
 
 
 def kway_stage():
-    """config 4: one compare-swap stage of the k=2, M=7 network on N=128 at the adapter's card"""
+    """config 4: the k=2, M=7 network on N=128 at the adapter's card: one compare-swap stage, one EvalBootstrap, and the
+    whole 28-stage network with bootstrapping (src/k-way/Sorter.cpp:284-404, level budget {4,4})"""
     n, k, M = 128, 2, 7
     depth, scale, first, rots = sf.kway_params(n)
     eng, stream = engine(17, depth, scale, first, rots)
-    x = np.random.default_rng(3).permutation(n) / n
+    eng.EvalBootstrapSetup((4, 4), (0, 0), n)
+    eng.EvalBootstrapKeyGen(n)
+    x = np.random.default_rng(3).permutation(n) * ((1.0 - 1e-8) / n)
     ct = eng.encrypt(eng.encode(x, slots=n))
-    ms, out = timed(eng, stream, lambda: sf.kway_sort(eng, ct, n, k, M, (3, 3, 2), depth, 0, 1))
-    ms2, out2 = timed(eng, stream, lambda: sf.kway_sort(eng, ct, n, k, M, (3, 3, 2), depth, 0, 2))
-    res = {"ms_first_stage": ms, "ms_two_stages": ms2, "levels_per_stage": out.level, "stages_total": 28,
-           "note": "28 stages need 13 bootstraps at depth 40; bootstrapping is not implemented"}
+    ms, out = timed(eng, stream, lambda: sf.kway_sort(eng, ct, n, k, M, (3, 2, 3), depth, 0, 1))
+    deep = eng.encrypt(eng.encode(x, 1, depth - 2, n))
+    ms_boot, fresh = timed(eng, stream, lambda: eng.EvalBootstrap(deep))
+    eng.stats(reset=True)
+    ms_all, res_ct = timed(eng, stream, lambda: sf.kway_sort(eng, ct, n, k, M, (3, 2, 3), depth))
+    boots = sum(cnt for name, nl, cnt in eng.stats()["ops"] if name == "bootstrap")
+    got = eng.decrypt(res_ct, n)
+    res = {"ms_first_stage": ms, "levels_first_stage": out.level, "ms_bootstrap": ms_boot, "level_after_bootstrap": fresh.level,
+           "bootstrap_max_abs_err": float(np.max(np.abs(eng.decrypt(fresh, n) - x))),
+           "ms_full_network_28_stages": ms_all, "bootstraps_per_run": boots / 4.0, "key_bytes": eng.info(7),
+           "max_abs_err": float(np.max(np.abs(got - np.sort(x))))}
     eng.close()
     return res
 
