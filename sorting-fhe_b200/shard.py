@@ -49,22 +49,38 @@ class _DevView:
         self.__cuda_array_interface__ = {"shape": (words,), "typestr": "<i8", "data": (ptr, False), "version": 2}
 
 
-def allreduce_ciphertext(eng, ct, group=None):
-    """sum a partial ciphertext over all ranks, in place: NCCL all-reduce on the limbs where they lie, then the
-    engine's mod-reduce kernel (ckks_ct_device_ptr / ckks_ct_mod_reduce of include/ckks_b200.h)"""
+def engine_stream(eng):
+    """the engine's CUDA stream as a torch stream: collectives are issued with it current, so NCCL orders itself after
+    the kernels that produce the limbs and the engine's next kernel after the collective -- no host synchronisation"""
+    s = getattr(eng, "_torch_stream", None)
+    if s is None:
+        s = eng._torch_stream = torch.cuda.ExternalStream(eng.info(9))
+    return s
+
+
+def allreduce_ciphertext(eng, ct, group=None, timing=None):
+    """sum a partial ciphertext over all ranks, in place: NCCL all-reduce on the limbs where they lie, enqueued behind the
+    engine's stream, then the engine's mod-reduce kernel (ckks_ct_device_ptr / ckks_ct_mod_reduce of include/ckks_b200.h).
+    timing: optional list that receives a (start, end) CUDA event pair around the collective (recorded on the engine stream)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
         return ct
     ptr, words = eng.ct_device_ptr(ct)
-    eng.sync()                                            # the limbs are produced on the engine's stream
     t = torch.as_tensor(_DevView(ptr, words), device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
-    torch.cuda.current_stream().synchronize()
+    s = engine_stream(eng)
+    with torch.cuda.stream(s):
+        if timing is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)   # the wait() of the blocking form is a stream wait for NCCL
+        if timing is not None:
+            e1.record(s)
+            timing.append((e0, e1))
     eng.ct_mod_reduce(ct)
     return ct
 
 
-def direct_sort_sharded(eng, n, rots, ct, sign_cfg, group=None):
+def direct_sort_sharded(eng, n, rots, ct, sign_cfg, group=None, timing=None, halves=False):
     """DirectSort<N>::sort with the comparison / index-check batches split over the ranks of `group` (every rank holds
     the same input ciphertext and keys and returns the same sorted ciphertext).  Falls back to the plain sort when
     the shape has a single batch."""
@@ -73,15 +89,16 @@ def direct_sort_sharded(eng, n, rots, ct, sign_cfg, group=None):
     from . import DirectSort, num_batches
     nb = num_batches(n, eng.n)
     sorter = DirectSort(eng, n, rots)
-    if world == 1 or nb == 1:
-        return sorter.sort(ct, sign_cfg)
-    if nb % world:
-        raise ValueError("direct_sort_sharded: %d batches do not split evenly over %d ranks" % (nb, world))
-    lo, hi = shard_range(nb, rank, world)
+    if nb == 1 or (world == 1 and not halves):
+        return sorter.sort(ct, sign_cfg)              # halves=True: the shardable halves on one rank (same calls, hence
+                                                      # the same zero-cache encryptions and limbs, as the multi-rank run)
+    if nb < world:
+        raise ValueError("direct_sort_sharded: %d batches cannot occupy %d ranks (use a sub-group)" % (nb, world))
+    lo, hi = shard_range(nb, rank, world)                 # balanced, the first nb % world ranks take one batch more
     part = sorter.construct_rank_partial(ct, sign_cfg, lo, hi, seed=(rank == 0))
-    rank_ct = sorter.finish_rank(allreduce_ciphertext(eng, part, group))
+    rank_ct = sorter.finish_rank(allreduce_ciphertext(eng, part, group, timing))
     part = sorter.index_check_partial(rank_ct, ct, lo, hi, seed=(rank == 0))
-    return sorter.finish_index_check(allreduce_ciphertext(eng, part, group))
+    return sorter.finish_index_check(allreduce_ciphertext(eng, part, group, timing))
 
 
 def sort_batch_sharded(eng, n, rots, cts, sign_cfg, group=None):
@@ -111,10 +128,9 @@ def broadcast_ciphertext(eng, ct, src, group=None):
     if rank != src:
         ct = eng.import_ct(np.zeros((parts, nlimbs, eng.n), dtype=np.uint64), level, deg, sf_, slots)
     ptr, words = eng.ct_device_ptr(ct)
-    eng.sync()
     t = torch.as_tensor(_DevView(ptr, words), device="cuda")
-    dist.broadcast(t, src, group=group)
-    torch.cuda.current_stream().synchronize()
+    with torch.cuda.stream(engine_stream(eng)):
+        dist.broadcast(t, src, group=group)
     return ct
 
 
