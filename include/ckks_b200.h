@@ -38,6 +38,12 @@ const char* ckks_last_error(void);
  * key of the sampler from OS entropy (getrandom).  See INTEGRATION.md "Randomness". */
 int ckks_ctx_create(ckks_ctx_t** out, int log_ring_dim, int mult_depth, int scaling_mod_size, int first_mod_size,
                     int num_large_digits, int scaling_technique, uint64_t seed, int dry_run);
+/* Context whose moduli (Q chain then P) and primitive 2n-th roots of unity come from an imported OpenFHE context
+ * (reference src/sort.h:34 DeserializeFromFile(ccLocation, ...)) instead of being re-derived; count must equal the limb
+ * counts the parameters imply, every modulus must be an NTT prime.  roots may be NULL (minimal roots are derived). */
+int ckks_ctx_create_from_moduli(ckks_ctx_t** out, int log_ring_dim, int mult_depth, int scaling_mod_size, int first_mod_size,
+                                int num_large_digits, int scaling_technique, uint64_t seed, int dry_run,
+                                const uint64_t* moduli, const uint64_t* roots, int count);
 int ckks_ctx_destroy(ckks_ctx_t* ctx); /* ClearEvalMultKeys/ClearEvalAutomorphismKeys/ReleaseAllContexts */
 int ckks_ctx_set_stream(ckks_ctx_t* ctx, void* cuda_stream);
 int ckks_ctx_sync(ckks_ctx_t* ctx);
@@ -64,7 +70,12 @@ int ckks_eval_rotate_keygen(ckks_ctx_t* ctx, const int32_t* indices, int count);
  * This is the hook the OpenFHE BINARY importer (sort.h:31-74) feeds. */
 int ckks_export_secret(ckks_ctx_t* ctx, uint64_t* host, size_t cap_words);
 int ckks_export_public_key(ckks_ctx_t* ctx, uint64_t* host, size_t cap_words);
+int ckks_import_secret(ckks_ctx_t* ctx, const uint64_t* host, size_t words);        /* [M][n] EVALUATION (tests; src/sort.h never loads one) */
+int ckks_import_public_key(ckks_ctx_t* ctx, const uint64_t* host, size_t words);    /* [2 (b, a)][sizeQ][n], sort.h:40 */
 int ckks_export_eval_key(ckks_ctx_t* ctx, int is_rotation, int32_t index, uint64_t* host, size_t cap_words);
+/* is_rotation: 0 = the relinearisation key, 1 = `index` is a rotation amount, 2 = `index` is the automorphism index (5^r mod 2n,
+ * or 2n - 1 for the conjugation) -- the key OpenFHE's EvalAutomorphismKey map uses (src/sort.h:63) */
+int ckks_list_automorphism_keys(ckks_ctx_t* ctx, uint32_t* automorphism_indices, int cap, int* count);
 int ckks_import_eval_key(ckks_ctx_t* ctx, int is_rotation, int32_t index, const uint64_t* host, size_t words);
 
 /* MakeCKKSPackedPlaintext(vec, scaleDeg, level, nullptr, slots) -- sort_algo.h:341,356,573,706,715.

@@ -89,6 +89,31 @@ int ckks_ctx_create(ckks_ctx_t** out, int log_n, int mult_depth, int scaling_bit
     API_END
 }
 
+int ckks_ctx_create_from_moduli(ckks_ctx_t** out, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits,
+                                int scaling_technique, uint64_t seed, int dry_run, const uint64_t* moduli, const uint64_t* roots, int count) {
+    API_BEGIN
+    require_device(dry_run != 0);
+    if (!moduli || count < 1) throw std::runtime_error("ctx_create_from_moduli: no moduli given");
+    if (!dry_run) cudaGetLastError();
+    ckks_ctx* x = new ckks_ctx();
+    try { context_generate(&x->c, log_n, mult_depth, scaling_bits, first_bits, num_large_digits, scaling_technique, seed, dry_run, moduli, roots, count); }
+    catch (...) { delete x; throw; }
+    if (!dry_run) check_cuda("context tables");
+    *out = x;
+    API_END
+}
+static void h2d(Context* c, u64* dev, const uint64_t* host, size_t words);
+static void import_rows(Context* c, u64** slot, const uint64_t* host, size_t words_, size_t expect, const char* what) {
+    if (words_ != expect) throw std::runtime_error(std::string(what) + ": size mismatch");
+    if (!*slot) *slot = dev_alloc(c, expect);
+    h2d(c, *slot, host, expect);
+}
+int ckks_import_secret(ckks_ctx_t* x, const uint64_t* host, size_t words_) {
+    API_BEGIN Context* c = C(x); Locked lk_(c); import_rows(c, &c->d_secret, host, words_, (size_t)c->M() * c->n, "import_secret"); API_END
+}
+int ckks_import_public_key(ckks_ctx_t* x, const uint64_t* host, size_t words_) {
+    API_BEGIN Context* c = C(x); Locked lk_(c); import_rows(c, &c->d_pk, host, words_, (size_t)2 * c->size_q * c->n, "import_public_key"); API_END
+}
 int ckks_ctx_destroy(ckks_ctx_t* x) {
     API_BEGIN
     if (!x) return 0;
@@ -198,7 +223,7 @@ int ckks_export_public_key(ckks_ctx_t* x, uint64_t* host, size_t cap) {
 }
 static EvalKey* find_key(Context* c, int is_rot, int32_t index, bool create) {
     if (!is_rot) return &c->relin;
-    uint32_t k = auto_index(c, index);
+    uint32_t k = is_rot == 2 ? (uint32_t)index : auto_index(c, index);   // 2: `index` is the automorphism index itself
     auto it = c->rot.find(k);
     if (it == c->rot.end()) { if (!create) return nullptr; return &c->rot[k]; }
     return &it->second;
@@ -215,6 +240,15 @@ int ckks_export_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, uint64_t* hos
     launch_from_mont(c, tmp, rows, mods_range(0, c->M()));
     d2h(c, host, tmp, w);
     dev_free(c, tmp);
+    API_END
+}
+int ckks_list_automorphism_keys(ckks_ctx_t* x, uint32_t* ks, int cap, int* count) {
+    API_BEGIN
+    Context* c = C(x); Locked lk_(c);
+    if ((int)c->rot.size() > cap) throw std::runtime_error("list_automorphism_keys: buffer too small");
+    int i = 0;
+    for (auto& kv : c->rot) ks[i++] = kv.first;
+    *count = i;
     API_END
 }
 int ckks_import_eval_key(ckks_ctx_t* x, int is_rot, int32_t index, const uint64_t* host, size_t words_) {

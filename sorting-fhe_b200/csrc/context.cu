@@ -68,7 +68,7 @@ template <class T> static T* upload(Context* c, const std::vector<T>& h) {
 static bool contains(const std::vector<u64>& v, size_t lo, size_t hi, u64 x) { for (size_t i = lo; i < hi; i++) if (v[i] == x) return true; return false; }
 
 void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits, int ext,
-                      uint64_t seed, int dry) {
+                      uint64_t seed, int dry, const uint64_t* given_moduli, const uint64_t* given_roots, int given_count) {
     c->log_n = log_n; c->n = 1 << log_n; c->mult_depth = mult_depth; c->scaling_bits = scaling_bits;
     c->first_bits = first_bits; c->ext = ext; c->seed = seed; c->dry = dry != 0;
     if (seed == 0) {   // no seed given: key material and encryption randomness are keyed from OS entropy (INTEGRATION.md "Randomness")
@@ -133,6 +133,20 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
     }
     c->moduli = q; c->moduli.insert(c->moduli.end(), p.begin(), p.end());
     if (c->M() > MAX_LIMBS) throw std::runtime_error("too many RNS limbs");
+    if (given_moduli) {
+        // imported context (OpenFHE serialisation, host/serial.h): the file's moduli and roots of unity are used as they
+        // are, never re-derived (SURVEY 8c'-2); the shape (limb counts) must be the one the parameters imply
+        if (given_count != c->M())
+            throw std::runtime_error("imported context: " + std::to_string(given_count) + " moduli given, the parameters imply " +
+                                     std::to_string(c->M()) + " (Q then P)");
+        for (int i = 0; i < given_count; i++) {
+            const u64 qi = given_moduli[i];
+            if (qi >> 61 || qi % m != 1 || !is_prime(qi)) throw std::runtime_error("imported context: modulus " + std::to_string(i) + " is not an NTT prime below 2^61");
+            if (given_roots && (powmod(given_roots[i], m / 2, qi) != qi - 1)) throw std::runtime_error("imported context: root " + std::to_string(i) + " is not a primitive 2n-th root of unity");
+            c->moduli[i] = qi;
+        }
+        for (int i = 0; i < size_q; i++) q[i] = c->moduli[i];
+    }
     // scaling factors
     c->sf_real.assign(size_q, 0.0);
     c->sf_real[0] = (double)q[size_q - 1];
@@ -157,7 +171,7 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         u64 r = (u64)((((u128)1) << 64) % qi); mi.r2 = mulmod(r, r, qi);
         mi.ninv = invmod(n % qi, qi); mi.ninv_sh = shoup(mi.ninv, qi);
         ninvp[2 * i] = mi.ninv; ninvp[2 * i + 1] = mi.ninv_sh;
-        u64 psi = min_root(m, qi), ipsi = invmod(psi, qi); c->psi[i] = psi;
+        u64 psi = (given_moduli && given_roots) ? given_roots[i] : min_root(m, qi), ipsi = invmod(psi, qi); c->psi[i] = psi;
         u64 x = 1, y = 1;
         for (int k = 0; k < n; k++) {
             uint32_t b = brev(k, log_n);

@@ -4,7 +4,8 @@
 #include <vector>
 
 void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, int first_bits, int num_large_digits, int ext,
-                      uint64_t seed, int dry);
+                      uint64_t seed, int dry, const uint64_t* given_moduli = nullptr, const uint64_t* given_roots = nullptr,
+                      int given_count = 0);
 
 Ct* ct_new(Context* c, int parts, int nl, int level, int deg, double sf, int slots, int lrep = 0);
 Ct* ct_full(const Ct* a);   // full-length copy of a (possibly compact) plaintext / ciphertext

@@ -1,3 +1,3 @@
-// ciphertext-ser.h -- forwarding header (see openfhe.h in this directory)
+// ciphertext-ser.h -- forwarding header: Serial / SerType over the engine (host/serial.h)
 #pragma once
-#include "openfhe.h"
+#include "../serial.h"

@@ -1,3 +1,3 @@
-// key/key-ser.h -- forwarding header (see openfhe.h in this directory)
+// key/key-ser.h -- forwarding header: Serial / SerType over the engine (host/serial.h)
 #pragma once
-#include "../openfhe.h"
+#include "../../serial.h"

@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <deque>
 #include <functional>
+#include <iostream>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -152,6 +153,19 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
     ckks_ctx_t* ctx = nullptr;
     bool owned = false;
     uint32_t batchSize = 0;
+    CCParams<CryptoContextCKKSRNS> params;   // as given to GenCryptoContext / read from a context file (host/serial.h)
+    bool hasParams = false;
+    // (de)serialisation of the evaluation-key maps (reference src/sort.h:52,63); defined by host/serial.h
+    template <class ST> bool DeserializeEvalMultKey(std::istream& s, const ST&) { return serial_keys_io(*this, &s, nullptr, false); }
+    template <class ST> bool DeserializeEvalAutomorphismKey(std::istream& s, const ST&) { return serial_keys_io(*this, &s, nullptr, true); }
+    template <class ST> bool SerializeEvalMultKey(std::ostream& s, const ST&, const std::string& = "") { return serial_keys_io(*this, nullptr, &s, false); }
+    template <class ST> bool SerializeEvalAutomorphismKey(std::ostream& s, const ST&, const std::string& = "") { return serial_keys_io(*this, nullptr, &s, true); }
+    // raw-limb landing hook of the importer
+    std::shared_ptr<CiphertextImpl<Element>> ImportCiphertext(const uint64_t* limbs, int polys, int nl, int level, int deg, double sf, int slots) const {
+        ckks_ct_t* o = nullptr;
+        ckks_check(ckks_ct_import(ctx, limbs, polys, nl, level, deg, sf, slots, &o), "ct_import");
+        return wrap(o);
+    }
     CryptoContextImpl(ckks_ctx_t* c, bool own, uint32_t batch) : ctx(c), owned(own), batchSize(batch) {}
     CryptoContextImpl(const CryptoContextImpl&) = delete;
     ~CryptoContextImpl() { if (ctx && owned) ckks_ctx_destroy(ctx); }
@@ -414,7 +428,9 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     ckks_ctx_t* c = nullptr;
     ckks_check(ckks_ctx_create(&c, logn, (int)p.multDepth, (int)p.scalingModSize, (int)p.firstModSize, (int)p.numLargeDigits,
                                tech, p.seed, 0), "GenCryptoContext");
-    return std::make_shared<CryptoContextImpl<DCRTPoly>>(c, true, p.batchSize);
+    auto cc = std::make_shared<CryptoContextImpl<DCRTPoly>>(c, true, p.batchSize);
+    cc->params = p; cc->hasParams = true;
+    return cc;
 }
 
 }  // namespace lbcrypto

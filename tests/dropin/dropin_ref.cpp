@@ -21,6 +21,7 @@
 #include "mehp24/mehp24_sort.h"
 #include "mehp24/mehp24_utils.h"
 #include "sign.h"
+#include "sort.h"        // the reference's SortContext<N> file API (src/sort.h), over host/serial.h
 #include "sort_algo.h"
 
 using namespace lbcrypto;
@@ -117,6 +118,53 @@ static void run_compare(const std::string& out) {                // tests/Compar
     std::cout << std::endl;
 }
 
+// src/sort.h end to end: context, public key, relinearisation key, rotation keys and the input ciphertext go through files
+// (Serial::SerializeToFile / SerializeEval*Key -> the reference's SortContext<4> constructor -> eval -> deserializeOutput).
+// The imported context keeps the file's moduli and roots; its encryption randomness is fresh, so the check is on values.
+static void run_serial(const std::string& out) {
+    constexpr int N = 4;
+    CCParams<CryptoContextCKKSRNS> parameters;
+    std::vector<int> rotations;
+    DirectSort<N>::getSizeParameters(parameters, rotations);
+    parameters.SetMultiplicativeDepth(45);                         // SortContext::eval uses Sign(4,3,3) (src/sort.h:93)
+    parameters.SetSecurityLevel(HEStd_NotSet);
+    parameters.SetRingDim(1u << 10);
+    parameters.SetSeed(1);
+    auto cc = GenCryptoContext(parameters);
+    cc->Enable(PKE); cc->Enable(KEYSWITCH); cc->Enable(LEVELEDSHE); cc->Enable(ADVANCEDSHE);
+    auto keys = cc->KeyGen();
+    cc->EvalRotateKeyGen(keys.secretKey, rotations);
+    cc->EvalMultKeyGen(keys.secretKey);
+    auto enc = std::make_shared<DebugEncryption>(cc, keys);
+    const std::vector<double> x = input(N, 3);
+    auto ct = enc->encryptInput(x);
+    const std::string d = out + "/";
+    bool ok = Serial::SerializeToFile(d + "cc.bin", cc, SerType::BINARY) && Serial::SerializeToFile(d + "pk.bin", keys.publicKey, SerType::BINARY) &&
+              Serial::SerializeToFile(d + "in.bin", ct, SerType::BINARY);
+    { std::ofstream f(d + "mult.bin", std::ios::binary); ok = ok && cc->SerializeEvalMultKey(f, SerType::BINARY); }
+    { std::ofstream f(d + "rot.bin", std::ios::binary); ok = ok && cc->SerializeEvalAutomorphismKey(f, SerType::BINARY); }
+    if (!ok) throw std::runtime_error("serialisation failed");
+    std::vector<uint64_t> sk((size_t)(cc->info(1) + cc->info(2)) * cc->GetRingDimension());
+    ckks_check(ckks_export_secret(cc->ctx, sk.data(), sk.size()), "export_secret");
+    // in-memory reference result
+    auto sorter = std::make_unique<DirectSort<N>>(cc, keys.publicKey, rotations, enc);
+    auto Cfg = SignConfig(CompositeSignConfig(4, 3, 3));
+    auto direct = sorter->sort(ct, SignFunc::CompositeSign, Cfg);
+    Plaintext p0; cc->Decrypt(keys.secretKey, direct, &p0);
+    // the reference's file-driven path, unmodified
+    SortContext<N> sc(d + "cc.bin", d + "pk.bin", d + "mult.bin", d + "rot.bin", d + "in.bin", d + "out.bin");
+    sc.eval(SortAlgo::DirectSort, rotations);
+    sc.deserializeOutput();
+    Ciphertext<DCRTPoly> back;
+    if (!Serial::DeserializeFromFile(d + "out.bin", back, SerType::BINARY)) throw std::runtime_error("cannot read the output file back");
+    ckks_check(ckks_import_secret(sc.m_cc->ctx, sk.data(), sk.size()), "import_secret");   // test only: decrypt in the imported context
+    Plaintext p1; sc.m_cc->Decrypt(nullptr, back, &p1);
+    std::ofstream r(out + "/serial.txt");
+    r.precision(17);
+    for (int i = 0; i < N; i++) r << x[i] << " " << p0->GetRealPackedValue()[i] << " " << p1->GetRealPackedValue()[i] << "\n";
+    std::cout << "serial level " << back->GetLevel() << " imported ring " << sc.m_cc->GetRingDimension() << std::endl;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) { std::fprintf(stderr, "usage: dropin_ref <outdir>\n"); return 2; }
     const std::string out = argv[1];
@@ -125,6 +173,7 @@ int main(int argc, char** argv) {
         run_direct_sort<8>(out, 10);
         run_mehp24(out, 10);
         run_compare(out);
+        run_serial(out);
     } catch (const std::exception& e) { std::fprintf(stderr, "dropin_ref: %s\n", e.what()); return 1; }
     std::cout << "dropin ok" << std::endl;
     return 0;

@@ -51,6 +51,11 @@ def test_reference_orchestration_on_the_engine_matches_host_layer(tmp_path):
     env = dict(os.environ, OMP_NUM_THREADS="4", OMP_NESTED="TRUE")
     r = subprocess.run([BIN, str(tmp_path)], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0 and "dropin ok" in r.stdout, (r.stdout[-1500:], r.stderr[-1500:])
+    # ---- src/sort.h's SortContext<4> through files (host/serial.h): same values as the in-memory sort, and sorted
+    rows = np.loadtxt(os.path.join(str(tmp_path), "serial.txt"))
+    assert rows.shape == (4, 3)
+    assert np.max(np.abs(rows[:, 1] - rows[:, 2])) < 1e-4, rows      # fresh encryption randomness in the imported context: values, not limbs
+    assert np.max(np.abs(rows[:, 2] - np.sort(rows[:, 0]))) < 0.01, rows
     # ---- DirectSort<4>, <8>
     for n in (4, 8):
         depth, rots = sf.direct_sort_params(n, 1 << 10)
