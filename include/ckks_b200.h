@@ -49,7 +49,8 @@ int ckks_ctx_set_stream(ckks_ctx_t* ctx, void* cuda_stream);
 int ckks_ctx_sync(ckks_ctx_t* ctx);
 /* what: 0 ring dim (GetRingDimension, sort_algo.h:80), 1 #Q limbs, 2 #P limbs, 3 digit size alpha, 4 #digits,
  * 5 cyclotomic order (rotation.h:267), 6 kernel launches so far, 7 device bytes of keys, 8 process-unique context id,
- * 9 the engine's cudaStream_t (as an integer: collectives are enqueued on it, sorting-fhe_b200/shard.py) */
+ * 9 the engine's cudaStream_t (as an integer: collectives are enqueued on it, sorting-fhe_b200/shard.py),
+ * 10 free device memory in bytes (the sorter layer sizes its encoded-plaintext cache from it) */
 int ckks_ctx_info(ckks_ctx_t* ctx, int what, int64_t* out);
 /* the n-th Encrypt of a context draws its randomness from sampler stream n; resetting the counter replays it
  * (reproducible tests: e.g. two sorter objects built after the same reset hold the same encryption of zeros) */

@@ -158,6 +158,7 @@ int ckks_ctx_info(ckks_ctx_t* x, int what, int64_t* out) {
         case 7: *out = (int64_t)((c->relin.d ? 1 : 0) + (int64_t)c->rot.size()) * c->num_part_q * 2 * c->M() * c->n * 8; break;
         case 8: *out = (int64_t)c->uid; break;
         case 9: *out = (int64_t)(intptr_t)c->stream; break;
+        case 10: { size_t fr = 0, tot = 0; if (c->dry || cudaMemGetInfo(&fr, &tot) != cudaSuccess) fr = 0; *out = (int64_t)fr; break; }
         default: throw std::runtime_error("ckks_ctx_info: unknown selector");
     }
     API_END

@@ -199,7 +199,7 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
     // (values, scaleDeg, level, slots) -- bit-identical by construction, and the level / scale adjustments the engine
     // caches on a plaintext handle (rescaled and lifted twins) are reused with it.  Entries are found by a 128-bit hash
     // of the values and confirmed by comparing the values themselves; the keyed form below skips generating and hashing
-    // the vector.  FIFO eviction above SORTFHE_PT_CACHE_MB (default 16384) of device bytes; SORTFHE_PT_CACHE_MB=0 turns
+    // the vector.  FIFO eviction above SORTFHE_PT_CACHE_MB of device bytes (default: half of the free device memory at first use); SORTFHE_PT_CACHE_MB=0 turns
     // the cache off.  Guarded by a mutex: the reference encodes from OpenMP threads (sort_algo.h:349-362).
     struct PtKey {
         uint64_t h[2]; uint32_t scaleDeg, level, slots, len;
@@ -212,9 +212,14 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
     mutable std::map<PtKey, PtEntry> pt_cache;
     mutable std::deque<PtKey> pt_order;
     mutable size_t pt_bytes = 0, pt_hits = 0, pt_misses = 0;
-    static size_t pt_cap_bytes() {
-        static const size_t cap = [] { const char* e = getenv("SORTFHE_PT_CACHE_MB"); return (size_t)(e ? atoll(e) : 16384) << 20; }();
-        return cap;
+    mutable size_t pt_cap = (size_t)-1;
+    size_t pt_cap_bytes() const {   // SORTFHE_PT_CACHE_MB, else half of the device memory that is free when the cache is first used
+        if (pt_cap == (size_t)-1) {
+            const char* e = getenv("SORTFHE_PT_CACHE_MB");
+            if (e) pt_cap = (size_t)atoll(e) << 20;
+            else { const int64_t fr = info(10); pt_cap = fr > 0 ? (size_t)fr / 2 : (size_t)16384 << 20; }
+        }
+        return pt_cap;
     }
     static void hash128(const void* data, size_t bytes, uint64_t out[2]) {   // two multiply-xorshift lanes over 8-byte words
         const uint64_t* w = (const uint64_t*)data; const size_t nw = bytes / 8;
