@@ -339,8 +339,10 @@ def run_b200(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         try:
-            with open(os.path.join(ROOT, "profiles", "r01_ntt_traffic.json")) as f:
-                traffic_ratio = float(json.load(f)["traffic_over_algorithmic"])
+            # in-sort capture: every NTT launch of one steady-state sort under ncu (tools/prof_sort.py + tools/ncu_traffic_digest.py);
+            # valid for the DirectSort N=128 ring 2^17 workload only -- other sizes report null
+            with open(os.path.join(ROOT, "profiles", "r02_ntt_traffic_in_sort.json")) as f:
+                traffic_ratio = float(json.load(f)["traffic_over_algorithmic"]) if (n, log_n) == (128, 17) else None
         except Exception:
             traffic_ratio = None
         dom = max(breakdown, key=lambda k: breakdown[k]["ms"])
@@ -361,9 +363,10 @@ def run_b200(args):
             "roofline": {"bound": "hbm", "kernel": "ntt_kernel (all NTT/INTT launches of the timed region)",
                          "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": traffic_ratio * prof_ntt["bytes"] / max(prof_ntt["launches"], 1) if traffic_ratio else None,
-                         "traffic_note": "DRAM bytes per average launch = algorithmic bytes per launch x %.2f, the dram read+write "
-                                         "over algorithmic ratio of one ncu --set full capture of the 32-limb transform "
-                                         "(profiles/r01_ntt_traffic.json): pass B also reads the twiddles its first rounds need (the last three stages derive theirs on the fly)" % (traffic_ratio or 0),
+                         "traffic_note": ("DRAM bytes per average launch = algorithmic bytes per launch x %.2f, the dram read+write over "
+                                          "algorithmic ratio summed over EVERY NTT launch of one steady-state sort of this workload captured "
+                                          "under ncu (profiles/r02_ntt_traffic_in_sort.json)" % traffic_ratio) if traffic_ratio else
+                                         "no in-sort ncu capture for this workload",
                          "algorithmic_bytes_per_launch": prof_ntt["bytes"] / max(prof_ntt["launches"], 1),
                          "peak_source": peak_src, "launches": prof_ntt["launches"],
                          "avg_launch_us": prof_ntt["ms"] * 1e3 / max(prof_ntt["launches"], 1),
