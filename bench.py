@@ -220,6 +220,44 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+def sharded_selftest(sf, rank, world):
+    """Untimed, N > 1 only: the one path of this repo that HAS a collective -- DirectSort with num_batch > 1 split over the
+    ranks with two NCCL limb all-reduces on the engine stream (sorting-fhe_b200/shard.py; reference src/sort_algo.h:438-492,
+    713-742) -- is run once at ring 2^10, N = 64 (8 batches) on every multi-GPU bench launch, so that the driver's scaling
+    runs exercise NCCL too.  The headline workload itself has a single batch and runs as replicas.
+    Reports: sorted within the reference gate, and the result limbs identical on every rank."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    shard = importlib.import_module("sorting-fhe_b200.shard")
+    try:
+        n, cfg = 64, (3, 3, 2)
+        depth, rots = sf.direct_sort_params(n, 1 << 10)
+        eng = sf.Engine(10, depth, 40, seed=9)
+        eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+        x = np.random.default_rng(1).permutation(n) / n
+        ct = eng.encrypt(eng.encode(x, slots=n))
+        timing = []
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s = shard.engine_stream(eng)
+        e0.record(s)
+        out = shard.direct_sort_sharded(eng, n, rots, ct, cfg, timing=timing)
+        e1.record(s)
+        eng.sync(); torch.cuda.synchronize()
+        err = float(np.max(np.abs(eng.decrypt(out, n) - np.sort(x))))
+        digest = hashlib.sha256(np.ascontiguousarray(out.export()).tobytes()).hexdigest()
+        digs = [None] * world
+        dist.all_gather_object(digs, digest)
+        res = {"ok": bool(err < 0.01 and all(d == digest for d in digs)), "what": "DirectSort N=64 ring 2^10, 8 batches over %d ranks" % world,
+               "max_abs_err": err, "ranks_agree_on_limbs": all(d == digest for d in digs), "sha256": digest,
+               "collectives": len(timing), "ms": e0.elapsed_time(e1),
+               "allreduce_ms": sum(p.elapsed_time(q) for p, q in timing)}
+        eng.close()
+        return res
+    except Exception as e:                                  # reported, never fatal for the bench line
+        return {"ok": False, "error": repr(e)[:300]}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -230,7 +268,8 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device (the engine has no CPU fallback)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(minutes=5))
     n, log_n, cfg = args.n, args.log_n, SIGN_CFG[args.n]
     K, W = args.steps, args.warmup
     depth, rots = sf.direct_sort_params(n, 1 << log_n)
@@ -332,6 +371,7 @@ def run_b200(args):
     breakdown = eng.profile()
     eng.profile_enable([])
 
+    selftest = sharded_selftest(sf, rank, world) if world > 1 and os.environ.get("BENCH_NO_SHARDED_SELFTEST") != "1" else None
     tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -377,6 +417,8 @@ def run_b200(args):
             "breakdown_GBs": {k: round(v["bytes"] / v["ms"] / 1e6, 1) for k, v in breakdown.items() if v["ms"] > 0},
             "breakdown_launches": {k: v["launches"] for k, v in breakdown.items()},
         }
+        if selftest is not None:
+            line["sharded_selftest"] = selftest
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(n, log_n, cfg)
         emit(line)
