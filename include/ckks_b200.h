@@ -172,6 +172,20 @@ int ckks_profile_json(ckks_ctx_t* ctx, char* buf, size_t cap);
 int ckks_ntt_host(ckks_ctx_t* ctx, uint64_t* data, int rows, const int32_t* modulus_ids, int inverse);
 int ckks_ntt_dev(ckks_ctx_t* ctx, void* dev_data, int rows, int first_modulus, int inverse);
 int ckks_key_switch_dev(ckks_ctx_t* ctx, const void* dev_src, int limbs, int is_rotation, int32_t index, void* dev_out);
+/* No counterpart in the reference: added for callers that cannot allocate (CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments and the same, bit-identical
+ * result as ckks_key_switch_dev (dev_src [limbs][n] -> dev_out [2][limbs][n], EVALUATION format), but every temporary
+ * lives in one file-scope static device array of 16 MiB (2^21 words) per GPU, resolved once per device with
+ * cudaGetSymbolAddress; the call performs no cudaMalloc / cudaFree / pool allocation.  It needs
+ * limbs + sum_j (limbs + sizeP - |digit j|) + 2 (limbs + sizeP) + 2 sizeP + 2 limbs rows of n words; a request beyond
+ * 2^21 words is rejected with an error that states both sizes (ring 2^13 fits up to 256 rows; a full-depth key switch
+ * at ring 2^17 does not fit and stays with ckks_key_switch_dev).  Preconditions, each reported as an error:
+ * the evaluation key exists; the constant tables of this limb count exist (they are allocated on first use -- one call of
+ * ckks_key_switch_dev or any EvalMult / EvalRotate at this level during set-up); per-class profiling is off; the context's
+ * device is current.  The first call on a device does the symbol lookup and must not run under stream capture.  All calls
+ * on a device share the array (it keeps the previous call's contents; every region is written before it is read): calls
+ * that overlap on the GPU -- two contexts or streams -- race and must be serialised by the caller. */
+int ckks_key_switch_dev_noalloc(ckks_ctx_t* ctx, const void* dev_src, int limbs, int is_rotation, int32_t index, void* dev_out);
 
 #ifdef __cplusplus
 }

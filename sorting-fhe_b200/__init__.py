@@ -392,6 +392,11 @@ class Engine:
         _chk(_L.ckks_key_switch_dev(_vp(self.h), _vp(src_ptr), limbs, 0 if rotation is None else 1,
                                     0 if rotation is None else rotation, _vp(out_ptr)))
 
+    def key_switch_dev_noalloc(self, src_ptr, limbs, out_ptr, rotation=None):
+        """allocation-free variant over the library's static device scratch (include/ckks_b200.h; no reference counterpart)"""
+        _chk(_L.ckks_key_switch_dev_noalloc(_vp(self.h), _vp(src_ptr), limbs, 0 if rotation is None else 1,
+                                            0 if rotation is None else rotation, _vp(out_ptr)))
+
 
 _L.ckks_eval_bootstrap_setup.argtypes = [_vp, _i, _i, _i, _i, _i]
 _L.ckks_eval_bootstrap_keygen.argtypes = [_vp, _i]

@@ -470,4 +470,103 @@ int ckks_key_switch_dev(ckks_ctx_t* x, const void* src, int limbs, int is_rot, i
     key_switch(c, (const u64*)src, limbs, *k, (u64*)out, nullptr, nullptr, 0);
     API_END
 }
+
+// ---------------------------------------------------------------- allocation-free key switch (no reference counterpart)
+// ckks_key_switch_dev_noalloc: the schedule of key_switch() (evaluator.cu) with every temporary -- INTT output, ModUp
+// complements, evk inner-product accumulators, ModDown P limbs and their conversion -- carved out of ONE file-scope device
+// array instead of the stream-ordered pool, for callers that may not allocate (CUDA graph capture, serving loops).
+// The array is shared by every call on a device and keeps the previous call's contents; every region is fully written
+// before it is read, so nothing needs clearing, but two calls that overlap on the GPU (different streams) race.
+#define NOALLOC_SCRATCH_WORDS (1u << 21)   /* 16 MiB per GPU that loads the library, held until exit */
+static __device__ __align__(256) u64 g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
+static std::mutex g_noalloc_mu;
+static u64* g_noalloc_ptr[64];             // device address of the array, per device ordinal (the host symbol is NOT an address)
+
+static u64* noalloc_scratch_of_current_device() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("key_switch_dev_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) throw std::runtime_error("key_switch_dev_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {             // set-up, once per device, with that device current
+        u64* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) throw std::runtime_error(std::string("key_switch_dev_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = p;
+    }
+    return g_noalloc_ptr[dev];
+}
+
+int ckks_key_switch_dev_noalloc(ckks_ctx_t* x, const void* src, int limbs, int is_rot, int32_t index, void* out) {
+    API_BEGIN
+    Context* c = C(x); Locked lk_(c);
+    if (c->dry) throw std::runtime_error("key_switch_dev_noalloc: needs a device (dry-run context)");
+    if (!src || !out) throw std::runtime_error("key_switch_dev_noalloc: null buffer");
+    if (limbs < 1 || limbs > c->size_q) throw std::runtime_error("key_switch_dev_noalloc: bad limb count");
+    const EvalKey* k = find_key(c, is_rot, index, false);
+    if (!k || !k->d) throw std::runtime_error("key_switch_dev_noalloc: key not present");
+    if (c->prof.mask) throw std::runtime_error("key_switch_dev_noalloc: per-class profiling creates CUDA events; disable it (ckks_profile_enable(ctx, 0))");
+    auto it = c->ks.find(limbs);
+    if (it == c->ks.end())
+        throw std::runtime_error("key_switch_dev_noalloc: the constant tables of this limb count are allocated on first use; run "
+                                 "ckks_key_switch_dev (or any EvalMult / EvalRotate at this level) once during set-up");
+    const KsTables& t = it->second;
+    const int nl = limbs, K = c->size_p, next = nl + K;
+    const size_t n = (size_t)c->n;
+    if (K > MAX_CONV_IN || c->alpha > MAX_CONV_IN || next > MAX_CONV_OUT) throw std::runtime_error("key switch: parameter set too large");
+    int conv_rows = 0;
+    for (int j = 0; j < t.nparts; j++) conv_rows += t.modup[j].nout;
+    const size_t rows = (size_t)nl + conv_rows + 2 * (size_t)next + 2 * (size_t)K + 2 * (size_t)nl;
+    if (rows * n > NOALLOC_SCRATCH_WORDS)
+        throw std::runtime_error("key_switch_dev_noalloc: needs " + std::to_string(rows) + " scratch rows of " + std::to_string(n) +
+                                 " words = " + std::to_string(rows * n * 8) + " bytes, beyond the static scratch of " +
+                                 std::to_string((size_t)NOALLOC_SCRATCH_WORDS * 8) + " bytes; use ckks_key_switch_dev");
+    u64* coef = noalloc_scratch_of_current_device();   // [nl][n]        INTT of src (x n^-1 Qhat^-1)
+    u64* conv = coef + (size_t)nl * n;                  // [conv_rows][n] ModUp complements of every digit
+    u64* acc = conv + (size_t)conv_rows * n;            // [2][nl+K][n]   sum_j d_j * evk_j
+    u64* pp = acc + 2 * (size_t)next * n;               // [2][K][n]      INTT of the P limbs (x n^-1 Phat^-1)
+    u64* conv2 = pp + 2 * (size_t)K * n;                // [2][nl][n]     their conversion to Q_l
+    c->stats.ops[{"keyswitch_noalloc", nl}]++;
+    // ---- ModUp
+    launch_ntt_ex(c, coef, (const u64*)src, nl, mods_q(nl), true, t.d_modup_scale, RowMap{}, RowMap{});
+    {
+        ConvBatch B; B.ng = t.nparts; B.split_ok = true;
+        for (int j = 0; j < t.nparts; j++) B.split_ok = B.split_ok && t.modup[j].split_ok;
+        LimbMods m; m.n = 0;
+        int row0 = 0;
+        for (int j = 0; j < t.nparts; j++) {
+            const ConvTables& ct = t.modup[j];
+            B.g[j] = ConvGroup{t.dig_lo[j], ct.nin, row0, ct.nout, ct.d_hatmod, ct.d_hatplain, ct.wide};
+            for (int i = 0; i < ct.nout; i++) { B.out_ids[j][i] = ct.out_ids[i]; if (m.n < MAX_LIMBS) m.m[m.n++] = ct.out_ids[i]; }
+            row0 += ct.nout;
+        }
+        launch_conv_batch(c, conv, coef, B);
+        if (conv_rows <= MAX_LIMBS) launch_ntt(c, conv, conv_rows, m, false);
+        else
+            for (int j = 0, r0 = 0; j < t.nparts; r0 += t.modup[j].nout, j++) {
+                LimbMods mj; mj.n = t.modup[j].nout;
+                for (int i = 0; i < mj.n; i++) mj.m[i] = t.modup[j].out_ids[i];
+                launch_ntt(c, conv + (size_t)r0 * n, mj.n, mj, false);
+            }
+    }
+    // ---- inner product with the evaluation key, ModDown of both polynomials
+    launch_ks_inner2(c, acc, (const u64*)src, conv, *k, t);
+    {
+        LimbMods mp; mp.n = K;
+        for (int i = 0; i < K; i++) mp.m[i] = (short)(c->size_q + i);
+        launch_ntt_ex(c, pp, acc, 2 * K, mp, true, t.d_moddown_scale, RowMap{K, next, nl}, RowMap{});
+    }
+    {
+        ConvBatch B; B.ng = 2; B.split_ok = t.moddown.split_ok;
+        for (int h = 0; h < 2; h++) {
+            B.g[h] = ConvGroup{h * K, K, h * nl, nl, t.moddown.d_hatmod, t.moddown.d_hatplain, t.moddown.wide};
+            for (int i = 0; i < nl; i++) B.out_ids[h][i] = (short)i;
+        }
+        launch_conv_batch(c, conv2, pp, B);
+    }
+    launch_ntt(c, conv2, 2 * nl, mods_q(nl), false);
+    launch_moddown_final(c, (u64*)out, acc, conv2, nullptr, nullptr, nl, 0, t);
+    check_cuda("key_switch_dev_noalloc");
+    API_END
+}
 }  // extern "C"
