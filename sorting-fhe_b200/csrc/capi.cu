@@ -60,7 +60,7 @@ void context_release(Context* c) {
         for (auto& kv : c->ks) {
             for (auto& t : kv.second.modup) { cudaFree(t.d_hatinv); cudaFree(t.d_hatinv_sh); cudaFree(t.d_hatmod); cudaFree(t.d_hatplain); }
             cudaFree(kv.second.moddown.d_hatinv); cudaFree(kv.second.moddown.d_hatinv_sh); cudaFree(kv.second.moddown.d_hatmod); cudaFree(kv.second.moddown.d_hatplain);
-            cudaFree(kv.second.d_pinv); cudaFree(kv.second.d_pinv_sh);
+            cudaFree(kv.second.d_pinv); cudaFree(kv.second.d_pinv_sh); cudaFree(kv.second.d_pinv_pairs);
             cudaFree(kv.second.d_modup_scale); cudaFree(kv.second.d_moddown_scale);
         }
         for (auto& kv : c->rescale_pairs) cudaFree(kv.second);

@@ -278,6 +278,11 @@ const KsTables& get_ks_tables(Context* c, int nl) {
         pinv[i] = invmod(pm, qi); pinv_sh[i] = shoup(pinv[i], qi);
     }
     t.d_pinv = upload(c, pinv); t.d_pinv_sh = upload(c, pinv_sh);
+    {
+        std::vector<u64> pairs(2 * (size_t)nl);
+        for (int i = 0; i < nl; i++) { pairs[2 * i] = pinv[i]; pairs[2 * i + 1] = pinv_sh[i]; }
+        t.d_pinv_pairs = upload(c, pairs);
+    }
     // fused final factors of the inverse NTTs that feed the basis conversions
     std::vector<u64> ms(2 * (size_t)c->M(), 0), ds(2 * (size_t)c->M(), 0);
     for (int j = 0; j < t.nparts; j++) {

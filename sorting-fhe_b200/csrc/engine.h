@@ -32,13 +32,19 @@ __host__ __device__ inline int row_of(const RowMap& m, int r) { return (r / m.gr
 // work fused into an NTT launch: a prologue applied to the words as they are first loaded, an epilogue applied to
 // the canonical results as they are stored
 enum { PRO_NONE = 0, PRO_SWITCHMOD = 1 };
-enum { EPI_NONE = 0, EPI_RESCALE = 1 };
+// EPI_RESCALE: out = (epi_in - NTT(..)) * pair.  EPI_MODDOWN (the ApproxModDown epilogue of a key switch, pair = P^-1 mod q_i):
+// the same, plus an optional addend per polynomial, optionally stored through an automorphism.
+enum { EPI_NONE = 0, EPI_RESCALE = 1, EPI_MODDOWN = 2 };
 struct NttFuse {
     int pro = PRO_NONE, pro_mod = 0;      // PRO_SWITCHMOD: modulus id the source limb is reduced by
     int epi = EPI_NONE;
-    const u64* epi_in = nullptr;          // EPI_RESCALE: minuend limbs, addressed through emap
+    const u64* epi_in = nullptr;          // minuend limbs, addressed through emap
     RowMap emap;
-    const u64* epi_pairs = nullptr;       // EPI_RESCALE: [M] (q_last^-1 mod q_i, Shoup) pairs
+    const u64* epi_pairs = nullptr;       // [M] (factor, Shoup) pairs indexed by modulus id
+    const u64* epi_add[2] = {nullptr, nullptr};   // EPI_MODDOWN: addend limbs [epi_add_grp][n] of logical rows r / epi_add_grp == 0, 1 (or nullptr)
+    int epi_add_grp = 1 << 30;
+    uint32_t auto_kinv = 0;               // != 0: result element e is stored at the EVALUATION-format image of e under X -> X^k (k kinv = 1 mod 2n)
+    int first_in_place = 0;               // two-pass forward transform: run the first pass in place in src (scratch), the second src -> dst
 };
 
 struct ConvTables {        // ApproxSwitchCRTBasis tables for one (source basis -> target basis)
@@ -59,6 +65,7 @@ struct KsTables {          // per number-of-Q-limbs tables of the hybrid key swi
     ConvTables moddown;              // P -> Q_l
     u64* d_pinv;                     // [nl] P^-1 mod q_i
     u64* d_pinv_sh;
+    u64* d_pinv_pairs;               // [nl] interleaved (P^-1 mod q_i, Shoup) pairs: the fused ModDown epilogue of the NTT (EPI_MODDOWN)
     u64* d_modup_scale;              // [M] pairs: n^-1 * Qhat_i^-1 (digit of limb i) -- final factor of the ModUp INTT
     u64* d_moddown_scale;            // [M] pairs: n^-1 * Phat_k^-1 -- final factor of the ModDown INTT
 };

@@ -9,6 +9,7 @@
 // can be checked on a machine without a GPU.  Bit-level behaviour is pinned by oracle/ckks_ops.py.
 #include "engine.h"
 #include "evaluator.h"
+#include <cstdlib>
 #include <memory>
 #include <cmath>
 #include <stdexcept>
@@ -329,8 +330,26 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
         }
         launch_conv_batch(c, conv2, pp, B);
     }
-    launch_ntt(c, conv2, 2 * nl, mods_q(nl), false);
-    launch_moddown_final(c, out, acc, conv2, add0, add1, nl, auto_k, t);
+    static const bool old_moddown = getenv("CKKS_B200_OLD_MODDOWN") != nullptr;   // A/B: separate epilogue kernel (round 1)
+    if (old_moddown) {
+        launch_ntt(c, conv2, 2 * nl, mods_q(nl), false);
+        launch_moddown_final(c, out, acc, conv2, add0, add1, nl, auto_k, t);
+    } else {
+        // the ApproxModDown epilogue rides on the last pass of the NTT of the converted limbs: (acc - NTT(conv)) P^-1 + addend,
+        // stored through the automorphism -- one launch and one round trip of 2 nl limbs less than NTT + k_moddown_final
+        NttFuse f;
+        f.epi = EPI_MODDOWN; f.epi_in = acc; f.emap = RowMap{nl, next, 0, 1}; f.epi_pairs = t.d_pinv_pairs;
+        f.epi_add[0] = add0; f.epi_add[1] = add1; f.epi_add_grp = nl;
+        f.first_in_place = 1;
+        if (auto_k) {   // inverse of auto_k modulo 2n (Newton iteration on the 2-adic inverse)
+            const uint32_t m = 2u * (uint32_t)c->n;
+            uint32_t x = auto_k;
+            for (int it = 0; it < 5; it++) x *= 2u - auto_k * x;
+            f.auto_kinv = x & (m - 1);
+            if (((uint64_t)f.auto_kinv * auto_k) % m != 1) throw std::runtime_error("internal: automorphism inverse");
+        }
+        launch_ntt_ex(c, out, conv2, 2 * nl, mods_q(nl), false, nullptr, RowMap{}, RowMap{}, &f);
+    }
     dev_free(c, pp); dev_free(c, conv2); dev_free(c, acc);
 }
 

@@ -21,6 +21,7 @@
 //     consecutive pairs per thread.
 // Results are canonical residues, bit-identical to the oracle.
 #include "engine.h"
+#include <cstdlib>
 #include <utility>
 #include <vector>
 
@@ -145,8 +146,60 @@ struct NttRows {
     u64 q[NTT_MAX_ROWS];
     double qinv[NTT_MAX_ROWS];          // 1 / q, correctly rounded (== __drcp_rn)
     short mid[NTT_MAX_ROWS];
+    short addrow[NTT_MAX_ROWS];         // EPI_MODDOWN: limb row inside the addend of this row's polynomial
     unsigned char kind[NTT_MAX_ROWS];
+    unsigned char addsel[NTT_MAX_ROWS]; // EPI_MODDOWN: which addend (polynomial index)
 };
+
+// EVALUATION-format (bit-reversed) index that element e moves to under the automorphism whose INVERSE index is kinv
+// (OpenFHE PrecomputeAutoMap gathers out[p] = in[F_k(p)]; F_kinv is the inverse permutation, so in[e] lands at F_kinv(e))
+__device__ __forceinline__ size_t auto_dest(size_t e, u32 kinv, int logn) {
+    const u32 j = __brev((u32)e) >> (32 - logn);
+    const u32 idx = (u32)((((2ull * j + 1) * kinv) & ((2ull << logn) - 1)) >> 1);
+    return (size_t)(__brev(idx) >> (32 - logn));
+}
+
+// Final store of a forward transform's canonical results v[8] (register k of thread u = tile-local element
+// local_index(u, k, p)): the fused epilogue, then the store -- vectorised, scalar, or scattered through an automorphism.
+template <class GA>
+__device__ __forceinline__ void epilogue_store(const NttArgs& A, const NttRows& R, const int row, const int logn, const bool vec8,
+                                               const int u, const int p, const u64 q, const int mid, u64 (&v)[8], u64* dst, GA gaddr) {
+    if (A.f.epi != EPI_NONE) {
+        // EPI_RESCALE: out = (in - NTT(switched last limb)) * q_last^-1 (DropLastElementAndScale)
+        // EPI_MODDOWN: out = (acc - NTT(converted P part)) * P^-1 [+ addend]    (ApproxModDown of a key switch)
+        const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
+        const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
+        u64 xin[8];
+        if (vec8) load8(ein + gaddr(local_index(u, 0, 0)), xin);
+        else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = shoup_mul(sub_mod(xin[k], v[k], q), sc.x, sc.y, q);
+        if (A.f.epi == EPI_MODDOWN) {
+            const u64* add = A.f.epi_add[R.addsel[row]];
+            if (add) {
+                add += (size_t)R.addrow[row] << logn;
+                if (vec8) load8(add + gaddr(local_index(u, 0, 0)), xin);
+                else {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) xin[k] = add[gaddr(local_index(u, k, p))];
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++) v[k] = add_mod(v[k], xin[k], q);
+            }
+        }
+    }
+    if (A.f.auto_kinv) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[auto_dest(gaddr(local_index(u, k, p)), A.f.auto_kinv, logn)] = v[k];
+    } else if (vec8) store8(dst + gaddr(local_index(u, 0, 0)), v);
+    else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[gaddr(local_index(u, k, p))] = v[k];
+    }
+}
 
 // rounds of one pass: window position p and stage range [J0,J1) per round (host fills, <= 4 rounds)
 struct Sched { int nr; int p[4]; int j0[4]; int j1[4]; };
@@ -265,19 +318,8 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
                         u64 v = r[k] - __umul64hi(r[k], mi.qrecip) * q;
                         r[k] = v >= q ? v - q : v;
                     }
-                    if (A.f.epi == EPI_RESCALE) {
-                        // out = (in - NTT(switched last limb)) * q_last^-1   (DropLastElementAndScale)
-                        const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
-                        const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
-                        u64 xin[8];
-                        if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
-                        else {
-#pragma unroll
-                            for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
-                        }
-#pragma unroll
-                        for (int k = 0; k < 8; k++) r[k] = shoup_mul(sub_mod(xin[k], r[k], q), sc.x, sc.y, q);
-                    }
+                    epilogue_store(A, R, row, logn, !strided && p == 0, u, p, q, mid, r, dst, gaddr);
+                    continue;
                 } else {
                     const tw_t sc = A.scale[mid];
 #pragma unroll
@@ -496,18 +538,8 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
             if (!INV) {
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
-                if (A.f.epi == EPI_RESCALE) {
-                    const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
-                    const tw_t sc = reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid];
-                    u64 xin[8];
-                    if (!strided && p == 0) load8(ein + gaddr(local_index(u, 0, 0)), xin);
-                    else {
-#pragma unroll
-                        for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
-                    }
-#pragma unroll
-                    for (int k = 0; k < 8; k++) v[k] = shoup_mul(sub_mod(xin[k], v[k], qi), sc.x, sc.y, qi);
-                }
+                epilogue_store(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr);
+                continue;
             } else {
                 const double sc = (double)A.scale[mid].x;
 #pragma unroll
@@ -626,12 +658,35 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     for (int r0 = 0; r0 < rows; r0 += NTT_MAX_ROWS) {
         const int cnt = rows - r0 < NTT_MAX_ROWS ? rows - r0 : NTT_MAX_ROWS, total = cnt << tpr_log;
         NttRows R1, R2;                                     // first pass: src map -> dst map; second pass: in place in dst
+        // Launch order of the rows: the FP64-butterfly rows (40-bit moduli) and the integer-butterfly rows (60-bit q0 and P
+        // primes, ~2.5x the time of an FP64 row) use different pipes, but consecutive CTA ids walk one row at a time, so an
+        // SM works on a single kind at any moment.  The rows of a key switch are 20-100 % integer ones: interleave the two
+        // kinds proportionally so that resident CTAs of both kinds share every SM (CKKS_B200_NTT_NO_INTERLEAVE=1: row order).
+        int order[NTT_MAX_ROWS];
+        {
+            static const bool no_mix = getenv("CKKS_B200_NTT_NO_INTERLEAVE") != nullptr;
+            int fp[NTT_MAX_ROWS], in_[NTT_MAX_ROWS], nfp = 0, nin = 0;
+            for (int i = 0; i < cnt; i++) {
+                const ModInfo& mi = c->h_mod[m.m[(r0 + i) % m.n]];
+                if (mi.bits <= FP_BITS && A.twd) fp[nfp++] = i; else in_[nin++] = i;
+            }
+            if (no_mix || nfp == 0 || nin == 0) for (int i = 0; i < cnt; i++) order[i] = i;
+            else {
+                int a_ = 0, b_ = 0;
+                for (int i = 0; i < cnt; i++) {       // Bresenham merge: after i rows, about i nin / cnt of them are integer rows
+                    const bool take_int = b_ < nin && (a_ >= nfp || (long)(b_ + 1) * cnt <= (long)(i + 1) * nin);
+                    order[i] = take_int ? in_[b_++] : fp[a_++];
+                }
+            }
+        }
         for (int i = 0; i < cnt; i++) {
-            const int r = r0 + i, mid = m.m[r % m.n];
+            const int r = r0 + order[i], mid = m.m[r % m.n];
             const ModInfo& mi = c->h_mod[mid];
             R1.src[i] = row_of(smap, r); R1.dst[i] = row_of(dmap, r); R1.epi[i] = fuse ? row_of(fuse->emap, r) : 0;
             R1.mid[i] = (short)mid; R1.q[i] = mi.q; R1.qinv[i] = 1.0 / (double)mi.q;
             R1.kind[i] = (mi.bits <= FP_BITS && A.twd) ? ROW_FP : ((inverse ? mi.bits > 46 : mi.bits > 58) ? ROW_INT_FIX : ROW_INT);
+            R1.addsel[i] = 0; R1.addrow[i] = 0;
+            if (fuse && fuse->epi == EPI_MODDOWN) { R1.addsel[i] = (unsigned char)((r / fuse->epi_add_grp) & 1); R1.addrow[i] = (short)(r % fuse->epi_add_grp); }
         }
         R2 = R1;
         for (int i = 0; i < cnt; i++) R2.src[i] = R1.dst[i];
@@ -640,6 +695,16 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
             A.src = src;
             if (a > 0) {
                 A.pass = 0; A.final_pass = 0;
+                if (fuse && fuse->first_in_place) {           // pass A in place in the (scratch) source, pass B source -> destination
+                    NttRows R0 = R1;
+                    for (int i = 0; i < cnt; i++) R0.dst[i] = R1.src[i];
+                    A.dst = const_cast<u64*>(src);
+                    launch_pass<false, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, false), R0);
+                    A.dst = dst; A.first_pass = 0;
+                    A.pass = 1; A.final_pass = 1;
+                    launch_pass<false, 1>(c, total, tpr_log, threads, smem, A, make_sched(T, T, false), R1);
+                    continue;
+                }
                 launch_pass<false, 0>(c, total, tpr_log, threads, smem, A, make_sched(T, a, false), R1);
                 A.src = dst; A.first_pass = 0;
             }
