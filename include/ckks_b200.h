@@ -56,7 +56,10 @@ int ckks_ctx_info(ckks_ctx_t* ctx, int what, int64_t* out);
  * (reproducible tests: e.g. two sorter objects built after the same reset hold the same encryption of zeros) */
 /* options: 0 = EvalAdd(ct, double) convention on noiseScaleDeg > 1 (0: round(|c| * ciphertext scale), default;
  * 1: OpenFHE 1.1.4 GetElementForEvalAddOrSub form, round(|c| * sf_level) times round(sf_level) per extra degree);
- * 1 = number of ciphertext handles that may keep their hoisted ModUp digits (default 8, 0 disables the cache) */
+ * 1 = number of ciphertext handles that may keep their hoisted ModUp digits (default 8, 0 disables the cache);
+ * 2 = capacity in MiB of the temporaries arena (freed temporaries are kept in exact-size bins per stream and reused
+ *     without a cudaMallocAsync / cudaFreeAsync call; default: an eighth of the free device memory, at most 16 GiB;
+ *     0 hands every cached buffer back to the pool and disables the arena; env CKKS_B200_ARENA_MB sets the default) */
 int ckks_ctx_set_option(ckks_ctx_t* ctx, int what, int64_t value);
 int ckks_ctx_set_encryption_counter(ckks_ctx_t* ctx, uint64_t counter);
 int ckks_ctx_get_moduli(ckks_ctx_t* ctx, uint64_t* moduli, uint64_t* roots, int cap);   /* Q then P */

@@ -97,6 +97,18 @@ int sortfhe_mehp24_sort_fg(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int s
  * for N = 512..2048, tests/mehp24/Mehp24SortTest.cpp:150-157).  Needs the rotation keys of sortfhe_mehp24_params(total_len). */
 int sortfhe_mehp24_sort_large(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int sign_n, int dg, int df,
                               int dg_i, int df_i, ckks_ct_t** out);
+/* The MEHP24 overloads that do not go through Comparison (SURVEY 8 A19 "other overloads"): sortFG with the f/g-composition
+ * predicates compareAdv / indicatorAdv, single ciphertext (src/mehp24/mehp24_sort.cpp:219-249) and split -> multi-ciphertext
+ * (:285-443) -> combine (sortLargeArrayFG :607-623); `sort` with the Chebyshev-interpolated compare / indicator predicates
+ * of degree degree_c / degree_i on [left_bound_c, right_bound_c], single ciphertext (:23-47: the sorted values land in
+ * column 0 of the matrix, NOT moved back to row 0) and over nc blocks (:49-217, out[nc]). */
+int sortfhe_mehp24_sort_fg_adv(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int dg_c, int df_c, int dg_i, int df_i, ckks_ct_t** out);
+int sortfhe_mehp24_sort_large_adv(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int dg_c, int df_c, int dg_i,
+                                  int df_i, ckks_ct_t** out);
+int sortfhe_mehp24_sort_cheb(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, double left_bound_c, double right_bound_c, int degree_c,
+                             int degree_i, ckks_ct_t** out);
+int sortfhe_mehp24_sort_cheb_multi(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, double left_bound_c,
+                                   double right_bound_c, int degree_c, int degree_i, ckks_ct_t** out);
 /* Multi-ciphertext sortFG in shardable stages (the nc (nc + 1) / 2 block comparisons of
  * src/mehp24/mehp24_sort.cpp:484-522 and the nc target blocks of :554-603 are independent; the reference runs them under
  * OpenMP with `omp critical` accumulation).  split / combine = splitCiphertext / combineCiphertext (mehp24_utils.cpp:266-302;

@@ -382,7 +382,27 @@ class Mehp24:
         return self.transpose_column(S, True)
 
 
-def mehp24_sort_large(cc, c, total_len, sub_len, sign_cfg, dg_i, df_i):
+    def sort_fg_adv(self, c, dg_c, df_c, dg_i, df_i):  # mehp24_sort.cpp:219-249 (compareAdv overload)
+        cc, n = self.cc, self.n
+        VR = self.replicate_row(c)
+        VC = self.replicate_column(self.transpose_row(c, True))
+        C = self.sign_adv(cc.EvalSub(VR, VC), dg_c, df_c)          # compareAdv, mehp24_utils.cpp:139-145
+        R = self.sum_rows(C)
+        sub = np.repeat(-1.0 * np.arange(n) - 0.5, n)
+        M = self.indicator_adv(cc.EvalAdd(R, self._pt(sub)), float(n), dg_i, df_i)
+        cc.EvalMult(M, VR)  # computed twice in the reference (:243-244)
+        S = self.sum_columns(cc.EvalMult(M, VR), True)
+        return self.transpose_column(S, True)
+
+
+def mehp24_sort_large_adv(cc, c, total_len, sub_len, dg_c, df_c, dg_i, df_i):
+    """sortLargeArrayFG, compareAdv overload (mehp24_sort.cpp:607-623 over the multi-ciphertext sortFG :285-443)"""
+    mh = Mehp24(cc, sub_len)
+    return mehp24_sort_large(cc, c, total_len, sub_len, None, dg_i, df_i,
+                             compare_blocks=lambda a, b: mh.sign_adv(cc.EvalSub(a, b), dg_c, df_c))
+
+
+def mehp24_sort_large(cc, c, total_len, sub_len, sign_cfg, dg_i, df_i, compare_blocks=None):
     """sortLargeArrayFG (mehp24_sort.cpp:625-645) = splitCiphertext (mehp24_utils.cpp:266-289) -> multi-ciphertext sortFG,
     Comparison-based overload (mehp24_sort.cpp:445-605) -> combineCiphertext (mehp24_utils.cpp:291-302)"""
     mh, n = Mehp24(cc, sub_len), sub_len
@@ -398,7 +418,7 @@ def mehp24_sort_large(cc, c, total_len, sub_len, sign_cfg, dg_i, df_i):
     cv, ch, s = [None] * nc, [None] * nc, [None] * nc
     for j in range(nc):
         for k in range(j, nc):
-            cjk = compare(cc, repl_r[j], repl_c[k], *sign_cfg)
+            cjk = compare_blocks(repl_r[j], repl_c[k]) if compare_blocks else compare(cc, repl_r[j], repl_c[k], *sign_cfg)
             cv[j] = acc(cv[j], cjk)
             if j != k:
                 ch[k] = acc(ch[k], cc.EvalSub(1.0, cjk))

@@ -636,6 +636,36 @@ def mehp24_sort_large(eng, ct, total_len, sub_len, sign_cfg, dg_i=None, df_i=2):
     return Ciphertext(eng, o.value)
 
 
+def mehp24_sort_fg_adv(eng, ct, n, dg_c, df_c, dg_i, df_i):
+    """mehp24::sortFG, compareAdv overload, single ciphertext (mehp24_sort.cpp:219-249)"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_sort_fg_adv(_vp(eng.h), _vp(ct.h), n, dg_c, df_c, dg_i, df_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_sort_large_adv(eng, ct, total_len, sub_len, dg_c, df_c, dg_i, df_i):
+    """mehp24::sortLargeArrayFG, compareAdv overload (mehp24_sort.cpp:285-443, 607-623)"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_sort_large_adv(_vp(eng.h), _vp(ct.h), total_len, sub_len, dg_c, df_c, dg_i, df_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_sort_cheb(eng, ct, n, left_bound_c, right_bound_c, degree_c, degree_i):
+    """mehp24::sort, single ciphertext (mehp24_sort.cpp:23-47): sorted values in column 0 of the n x n matrix"""
+    o = ctypes.c_void_p()
+    _hchk(_H.sortfhe_mehp24_sort_cheb(_vp(eng.h), _vp(ct.h), n, ctypes.c_double(left_bound_c), ctypes.c_double(right_bound_c),
+                                      degree_c, degree_i, ctypes.byref(o)))
+    return Ciphertext(eng, o.value)
+
+
+def mehp24_sort_cheb_multi(eng, parts, sub_len, left_bound_c, right_bound_c, degree_c, degree_i):
+    """mehp24::sort over several ciphertexts (mehp24_sort.cpp:49-217)"""
+    outs = (ctypes.c_void_p * len(parts))()
+    _hchk(_H.sortfhe_mehp24_sort_cheb_multi(_vp(eng.h), _harr(parts), len(parts), sub_len, ctypes.c_double(left_bound_c),
+                                            ctypes.c_double(right_bound_c), degree_c, degree_i, outs))
+    return [Ciphertext(eng, h) for h in outs]
+
+
 def _harr(cts):
     """array of ciphertext handles (NULL for None) for the `const ckks_ct_t* const*` parameters"""
     return (ctypes.c_void_p * len(cts))(*[c.h if c is not None else None for c in cts])

@@ -50,6 +50,7 @@ void context_release(Context* c) {
     if (!c->dry) {
         if (c->enc_stream) cudaStreamSynchronize(c->enc_stream);
         cudaStreamSynchronize(c->stream);
+        arena_trim(c);
         for (auto e : c->ev_pool) cudaEventDestroy(e);
         cudaFree(c->d_mod); cudaFree(c->d_tw); cudaFree(c->d_itw); cudaFree(c->d_ninv_pairs); cudaFree(c->d_twd); cudaFree(c->d_itwd); cudaFree(c->d_twb); cudaFree(c->d_itwb);
         for (auto& kv : c->ninv_pairs_rep) cudaFree(kv.second);
@@ -131,6 +132,7 @@ int ckks_ctx_set_stream(ckks_ctx_t* x, void* s) {
     Context* c = C(x); Locked lk_(c);
     if (c->dry) return 0;
     cudaStreamSynchronize(c->stream);
+    arena_trim(c);                       // the cached temporaries are ordered on the old stream
     if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
     c->stream = (cudaStream_t)s;
     API_END
@@ -169,6 +171,9 @@ int ckks_ctx_set_option(ckks_ctx_t* x, int what, int64_t value) {
     switch (what) {
         case 0: if (value != 0 && value != 1) throw std::runtime_error("add_const_mode must be 0 or 1"); c->add_const_mode = (int)value; break;
         case 1: if (value < 0) throw std::runtime_error("modup cache size must be >= 0"); c->modup_cap = (int)value; break;
+        case 2: if (value < 0) throw std::runtime_error("arena capacity must be >= 0 MiB"); c->arena_cap = (size_t)value << 20;
+                if (c->arena_cached > c->arena_cap && !c->dry) arena_trim(c);
+                break;
         default: throw std::runtime_error("ckks_ctx_set_option: unknown option");
     }
     API_END

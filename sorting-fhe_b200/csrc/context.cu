@@ -49,13 +49,51 @@ static int bitlen(u64 x) { int b = 0; while (x) { b++; x >>= 1; } return b; }
 
 u64* dev_alloc(Context* c, size_t words) {
     if (c->dry) return nullptr;
+    const size_t bytes = words * sizeof(u64);
+    if (c->arena_cap) {
+        auto it = c->arena_bins.find({c->stream, bytes});
+        if (it != c->arena_bins.end() && !it->second.empty()) {
+            void* p = it->second.back(); it->second.pop_back();
+            c->arena_cached -= bytes; c->arena_hits++;
+            return (u64*)p;
+        }
+    }
     void* p = nullptr;
     HostTimer ht(c, 1);
-    cudaError_t e = cudaMallocAsync(&p, words * sizeof(u64), c->stream);
+    cudaError_t e = cudaMallocAsync(&p, bytes, c->stream);
+    if (e != cudaSuccess && c->arena_cached) {       // the bins may hold what the pool lacks: hand everything back and retry once
+        cudaGetLastError();
+        arena_trim(c);
+        e = cudaMallocAsync(&p, bytes, c->stream);
+    }
     if (e != cudaSuccess) throw std::runtime_error(std::string("cudaMallocAsync: ") + cudaGetErrorString(e));
+    if (c->arena_cap) { c->arena_sizes[p] = bytes; c->arena_misses++; }
     return (u64*)p;
 }
-void dev_free(Context* c, void* p) { if (p && !c->dry) { HostTimer ht(c, 2); cudaFreeAsync(p, c->stream); } }
+void dev_free(Context* c, void* p) {
+    if (!p || c->dry) return;
+    if (c->arena_cap) {
+        auto it = c->arena_sizes.find(p);
+        if (it != c->arena_sizes.end()) {
+            const size_t bytes = it->second;
+            if (c->arena_cached + bytes <= c->arena_cap) {
+                c->arena_bins[{c->stream, bytes}].push_back(p);   // every use of p is ordered before this point of c->stream
+                c->arena_cached += bytes;
+                return;
+            }
+            c->arena_sizes.erase(it);
+        }
+    }
+    HostTimer ht(c, 2);
+    cudaFreeAsync(p, c->stream);
+}
+// hand every cached buffer back to the pool (context teardown, allocation failure, ckks_ctx_set_option(ctx, 2, 0))
+void arena_trim(Context* c) {
+    for (auto& kv : c->arena_bins)
+        for (void* p : kv.second) { c->arena_sizes.erase(p); cudaFreeAsync(p, kv.first.first); }
+    c->arena_bins.clear();
+    c->arena_cached = 0;
+}
 
 template <class T> static T* upload(Context* c, const std::vector<T>& h) {
     if (c->dry) return nullptr;
@@ -192,6 +230,11 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         }
         cudaMemPool_t pool; int dev = 0; cudaGetDevice(&dev);
         if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) { uint64_t thr = UINT64_MAX; cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr); }
+        {   // arena capacity: CKKS_B200_ARENA_MB (0 = off), default an eighth of the free device memory, at most 16 GiB
+            size_t fr = 0, tot = 0; cudaMemGetInfo(&fr, &tot);
+            const char* e = getenv("CKKS_B200_ARENA_MB");
+            c->arena_cap = e ? (size_t)atoll(e) << 20 : std::min<size_t>(fr / 8, (size_t)16 << 30);
+        }
     }
     c->d_mod = upload(c, c->h_mod);
     c->d_tw = upload(c, tw); c->d_itw = upload(c, itw); c->d_ninv_pairs = upload(c, ninvp);

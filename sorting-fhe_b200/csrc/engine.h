@@ -11,6 +11,7 @@
 #include <cstddef>
 #include <deque>
 #include <map>
+#include <unordered_map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -135,6 +136,13 @@ struct Context {
     // handle lifetime: ciphertexts may outlive ckks_ctx_destroy (shared_ptr / Python GC order); the context is
     // torn down when it is closed AND the last ciphertext handle is gone
     long live_cts = 0;
+    // Caching arena over the stream-ordered pool (context.cu dev_alloc / dev_free): freed temporaries are kept in exact-size
+    // bins PER STREAM and handed out again to allocations issued on the same stream -- reuse is then ordered by the stream
+    // itself, and a sort in steady state makes no cudaMallocAsync / cudaFreeAsync call at all (1 900 of each per sort before).
+    std::map<std::pair<cudaStream_t, size_t>, std::vector<void*>> arena_bins;
+    std::unordered_map<void*, size_t> arena_sizes;     // live and cached buffers -> bytes
+    size_t arena_cached = 0, arena_cap = 0;            // bytes held in the bins; beyond arena_cap a free goes back to the pool
+    long arena_hits = 0, arena_misses = 0;
     bool closed = false;
     bool release_pending = false;   // closed and the last handle is gone: the C entry point that notices tears the context down after unlocking
     // Thread safety (SURVEY 8b "Threading": the reference calls cc-> from nested OpenMP regions, src/sort_algo.h:334,349,
@@ -184,6 +192,7 @@ void prof_collect(Context* c);   // synchronises and folds pending event pairs i
 // ---- device memory helpers (stream-ordered pool) ----
 u64* dev_alloc(Context* c, size_t words);
 void dev_free(Context* c, void* p);
+void arena_trim(Context* c);
 
 // ---- kernel launchers (ntt.cu / kernels.cu / keyswitch.cu / encode.cu) ----
 LimbMods mods_q(int nl);                          // Q limbs 0..nl-1

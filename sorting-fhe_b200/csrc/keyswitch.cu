@@ -198,6 +198,10 @@ __device__ __forceinline__ double cv_mulmod(double a, double w, double q, double
     return __dadd_rn(__fma_rn(-qh, q, h), l);
 }
 struct ConvOut { double q, qinv, w2, w3; u64 qi, qinv64; int narrow, pad; };   // 56 bytes -> padded to 64
+#ifndef CONV_UNROLL
+#define CONV_UNROLL 1   /* 2 (two outputs in flight) measured 1 % slower at l = 32: 511.8 vs 506.0 us per key switch */
+#endif
+static constexpr int kConvUnroll = CONV_UNROLL;
 template <int NI, int WMODE>
 __global__ void __launch_bounds__(256)
 k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_constant__ ConvBatch B, const ModInfo* __restrict__ mi, int n,
@@ -238,38 +242,59 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
         if (i < NW) y2[i] = piece_to_double((u32)(v >> 42));
     }
     u64* dst = out + (size_t)(B.g[gi].out_row0 + jlo) * n + x;
-    for (int jj = 0; jj < jc; jj++) {
+    // Outputs come in at most three runs of one kind (q0, the other Q limbs, the P limbs); each run is a branch-free loop.
+    // The sums are exact integers below 2^53: splitting the middle columns into two accumulators changes nothing but the
+    // dependency chains (the ncu capture of round 2 had fixed-latency dependency waits as the top stall of this kernel).
+    auto narrow_out = [&](const int jj) {
         const double4* hp = sh_k + jj * NI;
         const ConvOut o = sh_o[jj];
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
-        if (o.narrow) {
+        double s0 = 0.0, s1 = 0.0, s1b = 0.0, s2 = 0.0, s3 = 0.0;
 #pragma unroll
-            for (int i = 0; i < NI; i++) {
-                const double4 c = hp[i];
-                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1);
-                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2);
-                if (WMODE == 2 || (WMODE == 1 && i == 0)) { s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); }
+        for (int i = 0; i < NI; i++) {
+            const double4 c = hp[i];
+            s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1);
+            s1b = __fma_rn(y1[i], c.x, s1b); s2 = __fma_rn(y1[i], c.y, s2);
+            if (WMODE == 2 || (WMODE == 1 && i == 0)) { s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); }
+        }
+        s1 = __dadd_rn(s1, s1b);
+        double r = __dadd_rn(s0, cv_mulmod(s1, 2097152.0, o.q, o.qinv));
+        r = __dadd_rn(r, cv_mulmod(s2, o.w2, o.q, o.qinv));
+        if (WMODE != 0) r = __dadd_rn(r, cv_mulmod(s3, o.w3, o.q, o.qinv));
+        const double t = __dadd_rn(__fma_rn(r, o.qinv, CV_MAGIC), -CV_MAGIC);
+        r = __fma_rn(-t, o.q, r);
+        if (r < 0.0) r = __dadd_rn(r, o.q);
+        dst[(size_t)jj * n] = column_to_u64(r);
+    };
+    auto wide_out = [&](const int jj) {
+        const double4* hp = sh_k + jj * NI;
+        const ConvOut o = sh_o[jj];
+        double s0 = 0.0, s1 = 0.0, s1b = 0.0, s2 = 0.0, s2b = 0.0, s3 = 0.0, s4 = 0.0;
+#pragma unroll
+        for (int i = 0; i < NI; i++) {
+            const double4 c = hp[i];
+            s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1); s2 = __fma_rn(y0[i], c.z, s2);
+            s1b = __fma_rn(y1[i], c.x, s1b); s2b = __fma_rn(y1[i], c.y, s2b); s3 = __fma_rn(y1[i], c.z, s3);
+            if (WMODE == 2 || (WMODE == 1 && i == 0)) {
+                s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); s4 = __fma_rn(y2[i], c.z, s4);
             }
-            double r = __dadd_rn(s0, cv_mulmod(s1, 2097152.0, o.q, o.qinv));
-            r = __dadd_rn(r, cv_mulmod(s2, o.w2, o.q, o.qinv));
-            if (WMODE != 0) r = __dadd_rn(r, cv_mulmod(s3, o.w3, o.q, o.qinv));
-            const double t = __dadd_rn(__fma_rn(r, o.qinv, CV_MAGIC), -CV_MAGIC);
-            r = __fma_rn(-t, o.q, r);
-            if (r < 0.0) r = __dadd_rn(r, o.q);
-            dst[(size_t)jj * n] = column_to_u64(r);
+        }
+        s1 = __dadd_rn(s1, s1b); s2 = __dadd_rn(s2, s2b);
+        u64 lo = column_to_u64(s0), hi = column_to_u64(s4) << 20;
+        add_shifted(lo, hi, column_to_u64(s1), 21); add_shifted(lo, hi, column_to_u64(s2), 42); add_shifted(lo, hi, column_to_u64(s3), 63);
+        dst[(size_t)jj * n] = mont_reduce(lo, hi, o.qi, o.qinv64);
+    };
+    int jj = 0;
+    while (jj < jc) {
+        const int kind = sh_o[jj].narrow;
+        int end = jj + 1;
+        while (end < jc && sh_o[end].narrow == kind) end++;
+        constexpr int kU = WMODE == 2 ? 1 : kConvUnroll;   // all-wide inputs (ModDown): two outputs in flight need 116 registers
+        if (kind) {
+#pragma unroll kU
+            for (; jj < end; jj++) narrow_out(jj);
         } else {
-#pragma unroll
-            for (int i = 0; i < NI; i++) {
-                const double4 c = hp[i];
-                s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1); s2 = __fma_rn(y0[i], c.z, s2);
-                s1 = __fma_rn(y1[i], c.x, s1); s2 = __fma_rn(y1[i], c.y, s2); s3 = __fma_rn(y1[i], c.z, s3);
-                if (WMODE == 2 || (WMODE == 1 && i == 0)) {
-                    s2 = __fma_rn(y2[i], c.x, s2); s3 = __fma_rn(y2[i], c.y, s3); s4 = __fma_rn(y2[i], c.z, s4);
-                }
-            }
-            u64 lo = column_to_u64(s0), hi = column_to_u64(s4) << 20;
-            add_shifted(lo, hi, column_to_u64(s1), 21); add_shifted(lo, hi, column_to_u64(s2), 42); add_shifted(lo, hi, column_to_u64(s3), 63);
-            dst[(size_t)jj * n] = mont_reduce(lo, hi, o.qi, o.qinv64);
+#pragma unroll kU
+            for (; jj < end; jj++) wide_out(jj);
         }
     }
 }

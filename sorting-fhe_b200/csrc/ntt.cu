@@ -597,6 +597,20 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
     const int row = id >> tpr_log, tile = id & ((1 << tpr_log) - 1);
     u64 v[8];
     load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
+    if (!INV && A.f.epi != EPI_NONE && A.final_pass && (LOGN_C ? PASS_C == 1 : A.pass == 1)) {
+        // the fused epilogue reads its minuend (and addend) tile only after the last round: pull the lines into L2/L1 now, the
+        // ncu capture of round 2 had long-scoreboard on those loads as the top stall of the ModDown NTT (profiles/r02_ks_kernels_ncu_summary.txt)
+        const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? (LOGN_C < TB_MAX ? LOGN_C : TB_MAX) : A.T;
+        const int lines = (1 << T) / 16;                       // 128-byte lines of one tile
+        if ((int)threadIdx.x < lines) {
+            const size_t off = ((size_t)tile << T) + (size_t)threadIdx.x * 16;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.f.epi_in + ((size_t)R.epi[row] << logn) + off));
+            if (A.f.epi == EPI_MODDOWN) {
+                const u64* add = A.f.epi_add[R.addsel[row]];
+                if (add) asm volatile("prefetch.global.L2 [%0];" ::"l"(add + ((size_t)R.addrow[row] << logn) + off));
+            }
+        }
+    }
     const int kind = R.kind[row];
     if (kind == ROW_FP) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
     else if (kind == ROW_INT_FIX) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
@@ -658,13 +672,14 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     for (int r0 = 0; r0 < rows; r0 += NTT_MAX_ROWS) {
         const int cnt = rows - r0 < NTT_MAX_ROWS ? rows - r0 : NTT_MAX_ROWS, total = cnt << tpr_log;
         NttRows R1, R2;                                     // first pass: src map -> dst map; second pass: in place in dst
-        // Launch order of the rows: the FP64-butterfly rows (40-bit moduli) and the integer-butterfly rows (60-bit q0 and P
-        // primes, ~2.5x the time of an FP64 row) use different pipes, but consecutive CTA ids walk one row at a time, so an
-        // SM works on a single kind at any moment.  The rows of a key switch are 20-100 % integer ones: interleave the two
-        // kinds proportionally so that resident CTAs of both kinds share every SM (CKKS_B200_NTT_NO_INTERLEAVE=1: row order).
+        // Launch order of the rows.  The FP64-butterfly rows (40-bit moduli) and the integer-butterfly rows (60-bit q0 and P
+        // primes, ~2.5x the time of an FP64 row) use different pipes, but consecutive CTA ids walk one row at a time, so an SM
+        // works on a single kind at any moment.  Interleaving the two kinds proportionally (CKKS_B200_NTT_INTERLEAVE=1) was
+        // measured in round 2 and does NOT pay: key switch at l = 32 512.3 vs 510.1 us, whole sort 63.5 vs 62.8 ms end to end --
+        // both kinds are bound by issue / dependency latency at ~55 % issue utilisation, not by their own pipe.  Row order stays.
         int order[NTT_MAX_ROWS];
         {
-            static const bool no_mix = getenv("CKKS_B200_NTT_NO_INTERLEAVE") != nullptr;
+            static const bool no_mix = getenv("CKKS_B200_NTT_INTERLEAVE") == nullptr;
             int fp[NTT_MAX_ROWS], in_[NTT_MAX_ROWS], nfp = 0, nin = 0;
             for (int i = 0; i < cnt; i++) {
                 const ModInfo& mi = c->h_mod[m.m[(r0 + i) % m.n]];

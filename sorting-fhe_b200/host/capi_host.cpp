@@ -367,6 +367,41 @@ void check_blocks(int nc, int sub_len) {
     if (nc < 1 || sub_len < 2 || (sub_len & (sub_len - 1))) throw std::runtime_error("mehp24 blocks: sub length must be a power of two, at least one block");
 }
 }  // namespace
+// the overloads that do not go through Comparison (mehp24_sort.cpp:23-47, 49-217, 219-249, 285-443, 607-623)
+int sortfhe_mehp24_sort_fg_adv(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, int dg_c, int df_c, int dg_i, int df_i, ckks_ct_t** out) {
+    HOST_BEGIN
+    if (n < 2 || (n & (n - 1))) throw std::runtime_error("mehp24 sortFG: vector length must be a power of two");
+    auto cc = borrow(ctx, n * n);
+    *out = release(mehp24::sortFG(borrow(input), (size_t)n, (uint32_t)dg_c, (uint32_t)df_c, (uint32_t)dg_i, (uint32_t)df_i, cc));
+    HOST_END
+}
+int sortfhe_mehp24_sort_large_adv(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, int dg_c, int df_c, int dg_i, int df_i,
+                                  ckks_ct_t** out) {
+    HOST_BEGIN
+    if (sub_len < 2 || (sub_len & (sub_len - 1)) || total_len < sub_len || total_len % sub_len)
+        throw std::runtime_error("mehp24 sortLargeArrayFG: sub length must be a power of two dividing the total length");
+    auto cc = borrow(ctx, sub_len * sub_len);
+    *out = release(mehp24::sortLargeArrayFG(borrow(input), (size_t)total_len, (size_t)sub_len, (uint32_t)dg_c, (uint32_t)df_c, (uint32_t)dg_i,
+                                            (uint32_t)df_i, cc));
+    HOST_END
+}
+int sortfhe_mehp24_sort_cheb(ckks_ctx_t* ctx, const ckks_ct_t* input, int n, double left_bound_c, double right_bound_c, int degree_c, int degree_i,
+                             ckks_ct_t** out) {
+    HOST_BEGIN
+    if (n < 2 || (n & (n - 1))) throw std::runtime_error("mehp24 sort: vector length must be a power of two");
+    auto cc = borrow(ctx, n * n);
+    *out = release(mehp24::sort(borrow(input), (size_t)n, left_bound_c, right_bound_c, (uint32_t)degree_c, (uint32_t)degree_i, cc));
+    HOST_END
+}
+int sortfhe_mehp24_sort_cheb_multi(ckks_ctx_t* ctx, const ckks_ct_t* const* parts, int nc, int sub_len, double left_bound_c, double right_bound_c,
+                                   int degree_c, int degree_i, ckks_ct_t** out) {
+    HOST_BEGIN
+    check_blocks(nc, sub_len);
+    auto cc = borrow(ctx, sub_len * sub_len);
+    std::vector<CT> r = mehp24::sort(borrow_all(parts, nc), (size_t)sub_len, left_bound_c, right_bound_c, (uint32_t)degree_c, (uint32_t)degree_i, cc);
+    for (size_t i = 0; i < r.size(); i++) out[i] = release(r[i]);
+    HOST_END
+}
 int sortfhe_mehp24_split(ckks_ctx_t* ctx, const ckks_ct_t* input, int total_len, int sub_len, ckks_ct_t** out) {
     HOST_BEGIN
     if (sub_len < 2 || (sub_len & (sub_len - 1)) || total_len < sub_len || total_len % sub_len)

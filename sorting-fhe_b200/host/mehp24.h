@@ -177,9 +177,9 @@ inline size_t numCompareUnits(size_t nc) { return nc * (nc + 1) / 2; }
 // comparison units u in [u_lo, u_hi) of the upper triangle (j <= k, row-major): Cv[j] += C_jk, Ch[k] += 1 - C_jk  (:484-522).
 // With `fill`, accumulators this range never touched become exact zeros at the comparisons' level and scale (x - x), so
 // that every shard hands the same set of same-shaped partial sums to the limb all-reduce.
-inline void comparePartial(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& replC, size_t u_lo, size_t u_hi,
-                           SignFunc SignFunc, SignConfig& Cfg, std::unique_ptr<Comparison>& comp, std::vector<CT>& Cv,
-                           std::vector<CT>& Ch, bool fill) {
+template <class CompareFn>
+inline void comparePartialWith(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& replC, size_t u_lo, size_t u_hi,
+                               CompareFn compareBlocks, std::vector<CT>& Cv, std::vector<CT>& Ch, bool fill) {
     const size_t nc = replR.size();
     Cv.assign(nc, CT()); Ch.assign(nc, CT());
     CT any;
@@ -187,7 +187,7 @@ inline void comparePartial(const CC& cc, const std::vector<CT>& replR, const std
     for (size_t j = 0; j < nc; j++)
         for (size_t k = j; k < nc; k++, u++) {
             if (u < u_lo || u >= u_hi) continue;
-            CT Cjk = comp->compare(cc, replR[j], replC[k], SignFunc, Cfg);
+            CT Cjk = compareBlocks(replR[j], replC[k]);
             accumulate(cc, Cv[j], Cjk);
             if (j != k) accumulate(cc, Ch[k], cc->EvalSub(1.0, Cjk));
             any = Cjk;
@@ -199,6 +199,12 @@ inline void comparePartial(const CC& cc, const std::vector<CT>& replR, const std
         if (!Cv[j]) Cv[j] = zero->Clone();
         if (j > 0 && !Ch[j]) Ch[j] = zero->Clone();
     }
+}
+inline void comparePartial(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& replC, size_t u_lo, size_t u_hi,
+                           SignFunc SignFunc, SignConfig& Cfg, std::unique_ptr<Comparison>& comp, std::vector<CT>& Cv,
+                           std::vector<CT>& Ch, bool fill) {
+    comparePartialWith(cc, replR, replC, u_lo, u_hi,
+                       [&](const CT& a, const CT& b) { return comp->compare(cc, a, b, SignFunc, Cfg); }, Cv, Ch, fill);
 }
 // s[j] = sumRows(Cv[j]) (+ the transposed column sums of Ch[j] replicated over the rows, j >= 1)  (:524-552)
 inline std::vector<CT> ranks(const CC& cc, const std::vector<CT>& Cv, const std::vector<CT>& Ch, size_t n) {
@@ -213,15 +219,22 @@ inline std::vector<CT> ranks(const CC& cc, const std::vector<CT>& Cv, const std:
     return s;
 }
 // target block j: sum over the source blocks k of indicator(rank_k - (j n + r) - 1/2) * values_k, column sums, back to row 0  (:554-603)
-inline CT sortedBlock(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& s, size_t n, size_t j, uint32_t dg_i,
-                      uint32_t df_i) {
-    const size_t nc = replR.size(), vectorLength = n * nc;
+// indicatorOf(x) = [|x| < 1/2]; backToRow: mask the column sums and move them to row 0 (the FG overloads do, `sort` does not)
+template <class IndicatorFn>
+inline CT sortedBlockWith(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& s, size_t n, size_t j, IndicatorFn indicatorOf,
+                          bool backToRow) {
+    const size_t nc = replR.size();
     std::vector<double> subMask(n * n);
     for (size_t r = 0; r < n; r++) for (size_t q = 0; q < n; q++) subMask[r * n + q] = -1.0 * (double)(j * n + r) - 0.5;
     CT subSorted;
-    for (size_t k = 0; k < nc; k++)
-        accumulate(cc, subSorted, cc->EvalMult(utils::indicatorAdv(cc, utils::addVec(cc, s[k], subMask), (double)vectorLength, dg_i, df_i), replR[k]));
+    for (size_t k = 0; k < nc; k++) accumulate(cc, subSorted, cc->EvalMult(indicatorOf(utils::addVec(cc, s[k], subMask)), replR[k]));
+    if (!backToRow) return utils::sumColumns(cc, subSorted, n);
     return utils::transposeColumn(cc, utils::sumColumns(cc, subSorted, n, true), n, true);
+}
+inline CT sortedBlock(const CC& cc, const std::vector<CT>& replR, const std::vector<CT>& s, size_t n, size_t j, uint32_t dg_i,
+                      uint32_t df_i) {
+    const double vectorLength = (double)(n * replR.size());
+    return sortedBlockWith(cc, replR, s, n, j, [&](const CT& x) { return utils::indicatorAdv(cc, x, vectorLength, dg_i, df_i); }, true);
 }
 }  // namespace blocks
 
@@ -245,6 +258,94 @@ inline Ciphertext<DCRTPoly> sortLargeArrayFG(Ciphertext<DCRTPoly> c, const size_
                                              CryptoContext<DCRTPoly> cc) {
     std::vector<Ciphertext<DCRTPoly>> parts = splitCiphertext(c, totalLength, subLength, cc);
     return combineCiphertext(sortFG(parts, subLength, SignFunc, Cfg, comp, dg_i, df_i, cc), subLength, cc);
+}
+
+
+// ---- the overloads that do not go through Comparison (SURVEY 8 A19 "other overloads"): Chebyshev-interpolated predicates
+// (`sort`) and the f/g-composition predicates of mehp24_utils (`sortFG` with dg_c / df_c).
+
+// sort, single ciphertext (mehp24_sort.cpp:23-47): result in column 0 of every row block (no masking, no transposition)
+inline Ciphertext<DCRTPoly> sort(Ciphertext<DCRTPoly> c, const size_t vectorLength, double leftBoundC, double rightBoundC, uint32_t degreeC,
+                                 uint32_t degreeI, CryptoContext<DCRTPoly> m_cc) {
+    using namespace utils;
+    const size_t n = vectorLength;
+    CT VR = replicateRow(m_cc, c, n);
+    CT VC = replicateColumn(m_cc, transposeRow(m_cc, c, n, true), n);
+    CT C = compare(m_cc, VR, VC, leftBoundC, rightBoundC, degreeC);
+    CT R = sumRows(m_cc, C, n);
+    std::vector<double> subMask(n * n);
+    for (size_t i = 0; i < n; i++) for (size_t j = 0; j < n; j++) subMask[i * n + j] = -1.0 * (double)i - 0.5;
+    CT M = indicator(m_cc, addVec(m_cc, R, subMask), -0.5, 0.5, -1.0 * (double)n, 1.0 * (double)n, degreeI);
+    return sumColumns(m_cc, m_cc->EvalMult(M, VR), n);
+}
+// sort over several ciphertexts (mehp24_sort.cpp:49-217): the block structure of the multi-ciphertext sortFG with the
+// Chebyshev predicates; the indicator's interval is +-1.01 vectorLength (:178-180)
+inline std::vector<Ciphertext<DCRTPoly>> sort(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength, double leftBoundC,
+                                              double rightBoundC, uint32_t degreeC, uint32_t degreeI, CryptoContext<DCRTPoly> m_cc) {
+    using utils::CT;
+    const size_t nc = c.size(), n = subVectorLength;
+    const double vectorLength = (double)(n * nc);
+    std::vector<CT> replR, replC, Cv, Ch;
+    blocks::replicas(m_cc, c, n, replR, replC);
+    blocks::comparePartialWith(m_cc, replR, replC, 0, blocks::numCompareUnits(nc),
+                               [&](const CT& a, const CT& b) { return utils::compare(m_cc, a, b, leftBoundC, rightBoundC, degreeC); }, Cv, Ch, false);
+    std::vector<CT> s = blocks::ranks(m_cc, Cv, Ch, n);
+    std::vector<CT> result(nc);
+    for (size_t j = 0; j < nc; j++)
+        result[j] = blocks::sortedBlockWith(m_cc, replR, s, n, j, [&](const CT& x) {
+            return utils::indicator(m_cc, x, -0.5, 0.5, -1.01 * vectorLength, 1.01 * vectorLength, degreeI); }, false);
+    return result;
+}
+// sortFG, single ciphertext, compareAdv overload (mehp24_sort.cpp:219-249)
+inline Ciphertext<DCRTPoly> sortFG(Ciphertext<DCRTPoly> c, const size_t vectorLength, uint32_t dg_c, uint32_t df_c, uint32_t dg_i, uint32_t df_i,
+                                   CryptoContext<DCRTPoly> m_cc) {
+    using namespace utils;
+    const size_t n = vectorLength;
+    CT VR = replicateRow(m_cc, c, n);
+    CT VC = replicateColumn(m_cc, transposeRow(m_cc, c, n, true), n);
+    CT C = compareAdv(m_cc, VR, VC, dg_c, df_c);
+    CT R = sumRows(m_cc, C, n);
+    std::vector<double> subMask(n * n);
+    for (size_t i = 0; i < n; i++) for (size_t j = 0; j < n; j++) subMask[i * n + j] = -1.0 * (double)i - 0.5;
+    CT M = indicatorAdv(m_cc, addVec(m_cc, R, subMask), (double)n, dg_i, df_i);
+    CT tmp = m_cc->EvalMult(M, VR);                                                 // computed twice in the reference (:243-244)
+    CT S = sumColumns(m_cc, m_cc->EvalMult(M, VR), n, true);
+    (void)tmp;
+    return transposeColumn(m_cc, S, n, true);
+}
+// sortFG over several ciphertexts, compareAdv overload (mehp24_sort.cpp:285-443)
+inline std::vector<Ciphertext<DCRTPoly>> sortFG(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength, uint32_t dg_c,
+                                                uint32_t df_c, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> m_cc) {
+    using utils::CT;
+    const size_t nc = c.size(), n = subVectorLength;
+    std::vector<CT> replR, replC, Cv, Ch;
+    blocks::replicas(m_cc, c, n, replR, replC);
+    blocks::comparePartialWith(m_cc, replR, replC, 0, blocks::numCompareUnits(nc),
+                               [&](const CT& a, const CT& b) { return utils::compareAdv(m_cc, a, b, dg_c, df_c); }, Cv, Ch, false);
+    std::vector<CT> s = blocks::ranks(m_cc, Cv, Ch, n);
+    std::vector<CT> result(nc);
+    for (size_t j = 0; j < nc; j++) result[j] = blocks::sortedBlock(m_cc, replR, s, n, j, dg_i, df_i);
+    return result;
+}
+// sortLargeArrayFG, compareAdv overload (mehp24_sort.cpp:607-623)
+inline Ciphertext<DCRTPoly> sortLargeArrayFG(Ciphertext<DCRTPoly> c, const size_t totalLength, const size_t subLength, uint32_t dg_c,
+                                             uint32_t df_c, uint32_t dg_i, uint32_t df_i, CryptoContext<DCRTPoly> cc) {
+    std::vector<Ciphertext<DCRTPoly>> parts = splitCiphertext(c, totalLength, subLength, cc);
+    return combineCiphertext(sortFG(parts, subLength, dg_c, df_c, dg_i, df_i, cc), subLength, cc);
+}
+
+// the reference's signatures without a context argument (the context is the ciphertext's own)
+inline Ciphertext<DCRTPoly> sort(Ciphertext<DCRTPoly> c, const size_t vectorLength, double leftBoundC, double rightBoundC, uint32_t degreeC,
+                                 uint32_t degreeI) {
+    return sort(c, vectorLength, leftBoundC, rightBoundC, degreeC, degreeI, c->GetCryptoContext());
+}
+inline std::vector<Ciphertext<DCRTPoly>> sort(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength, double leftBoundC,
+                                              double rightBoundC, uint32_t degreeC, uint32_t degreeI) {
+    return sort(c, subVectorLength, leftBoundC, rightBoundC, degreeC, degreeI, c.at(0)->GetCryptoContext());
+}
+inline std::vector<Ciphertext<DCRTPoly>> sortFG(const std::vector<Ciphertext<DCRTPoly>>& c, const size_t subVectorLength, uint32_t dg_c,
+                                                uint32_t df_c, uint32_t dg_i, uint32_t df_i) {
+    return sortFG(c, subVectorLength, dg_c, df_c, dg_i, df_i, c.at(0)->GetCryptoContext());
 }
 
 }  // namespace mehp24

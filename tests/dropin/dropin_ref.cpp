@@ -165,6 +165,43 @@ static void run_serial(const std::string& out) {
     std::cout << "serial level " << back->GetLevel() << " imported ring " << sc.m_cc->GetRingDimension() << std::endl;
 }
 
+// mehp24_sort.h:37-40 declares the single-ciphertext compareAdv overload without its df_i parameter, so the function that
+// mehp24_sort.cpp:219-221 defines is not reachable through the header; declare the defined signature here.
+namespace mehp24 {
+Ciphertext<DCRTPoly> sortFG(Ciphertext<DCRTPoly> c, const size_t vectorLength, uint32_t dg_c, uint32_t df_c, uint32_t dg_i, uint32_t df_i,
+                            CryptoContext<DCRTPoly> m_cc);
+}
+// The MEHP24 overloads that do not go through Comparison, from the reference's unmodified mehp24_sort.cpp:
+// sortFG with compareAdv / indicatorAdv (:219-249), sortLargeArrayFG over two blocks (:285-443, 607-623), and `sort` with
+// the Chebyshev predicates, single ciphertext (:23-47) and two blocks (:49-217).
+static void run_mehp24_overloads(const std::string& out, int logRing) {
+    constexpr int N = 4;
+    CCParams<CryptoContextCKKSRNS> parameters;
+    parameters.SetSecurityLevel(HEStd_NotSet);
+    parameters.SetRingDim(1u << logRing);
+    parameters.SetBatchSize(N * N);
+    parameters.SetMultiplicativeDepth(45);
+    parameters.SetScalingModSize(40);
+    parameters.SetSeed(1);
+    auto cc = GenCryptoContext(parameters);
+    cc->Enable(PKE); cc->Enable(KEYSWITCH); cc->Enable(LEVELEDSHE); cc->Enable(ADVANCEDSHE);
+    auto keys = cc->KeyGen();
+    cc->EvalMultKeyGen(keys.secretKey);
+    std::vector<int32_t> rots = mehp24::utils::getRotationIndices(N);
+    rots.push_back(N); rots.push_back(-N);                        // splitCiphertext / combineCiphertext of two blocks
+    cc->EvalRotateKeyGen(keys.secretKey, rots);
+    auto enc = std::make_shared<DebugEncryption>(cc, keys);
+    auto ct = enc->encryptInput(input(N, 2));
+    dump(out + "/mehp24_adv_4.bin", mehp24::sortFG(ct, (size_t)N, (uint32_t)3, (uint32_t)2, (uint32_t)2, (uint32_t)2, cc), cc);
+    dump(out + "/mehp24_cheb_4.bin", mehp24::sort(ct, N, -1.0, 1.0, 59, 119), cc);
+    auto ct8 = enc->encryptInput(input(2 * N, 3));
+    dump(out + "/mehp24_large_adv_8.bin", mehp24::sortLargeArrayFG(ct8, 2 * N, N, 3, 2, 2, 2, cc), cc);
+    auto parts = mehp24::utils::splitCiphertext(ct8, 2 * N, N, cc);
+    auto sorted = mehp24::sort(parts, N, -1.0, 1.0, 119, 247);   // 8 values 1/8 apart need the higher degrees (0.03 vs 0.14 max error)
+    dump(out + "/mehp24_cheb_multi_8_0.bin", sorted[0], cc);
+    dump(out + "/mehp24_cheb_multi_8_1.bin", sorted[1], cc);
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) { std::fprintf(stderr, "usage: dropin_ref <outdir>\n"); return 2; }
     const std::string out = argv[1];
@@ -172,6 +209,7 @@ int main(int argc, char** argv) {
         run_direct_sort<4>(out, 10);
         run_direct_sort<8>(out, 10);
         run_mehp24(out, 10);
+        run_mehp24_overloads(out, 10);
         run_compare(out);
         run_serial(out);
     } catch (const std::exception& e) { std::fprintf(stderr, "dropin_ref: %s\n", e.what()); return 1; }

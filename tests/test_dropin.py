@@ -44,13 +44,54 @@ def _load(path):
     return raw[6:].reshape(parts, nl, ring), level, deg, slots
 
 
-@pytest.mark.gpu
-def test_reference_orchestration_on_the_engine_matches_host_layer(tmp_path):
+@pytest.fixture(scope="module")
+def dropin_out(tmp_path_factory):
+    """one run of the reference-built driver; every test below reads its dumps"""
     if not os.path.exists(BIN):
         pytest.skip("tests/dropin/_ref/dropin_ref not built (needs /root/reference at build time)")
+    out = tmp_path_factory.mktemp("dropin")
     env = dict(os.environ, OMP_NUM_THREADS="4", OMP_NESTED="TRUE")
-    r = subprocess.run([BIN, str(tmp_path)], capture_output=True, text=True, env=env, timeout=600)
+    r = subprocess.run([BIN, str(out)], capture_output=True, text=True, env=env, timeout=900)
     assert r.returncode == 0 and "dropin ok" in r.stdout, (r.stdout[-1500:], r.stderr[-1500:])
+    return out
+
+
+@pytest.mark.gpu
+def test_reference_mehp24_overloads_match_host_layer(dropin_out):
+    """SURVEY 8 A19 "other overloads": the reference's own mehp24::sortFG (compareAdv, mehp24_sort.cpp:219-249),
+    sortLargeArrayFG over two blocks (:285-443, 607-623) and mehp24::sort with the Chebyshev predicates (:23-47, 49-217),
+    compiled unmodified and run on the engine, against this repo's host layer on the same seed: identical limbs."""
+    n = 4
+    rots = list(sf.mehp24_params(n)[1]) + [n, -n]
+    eng = sf.Engine(10, 45, 40, seed=1)
+    try:
+        eng.KeyGen(); eng.EvalMultKeyGen(); eng.EvalRotateKeyGen(rots)
+        x4, x8 = _input(n, 2), _input(2 * n, 3)
+        ct = eng.encrypt(eng.encode(x4, slots=n * n))                      # encryption counter 0, as in the driver
+        adv = sf.mehp24_sort_fg_adv(eng, ct, n, 3, 2, 2, 2)
+        cheb = sf.mehp24_sort_cheb(eng, ct, n, -1.0, 1.0, 59, 119)
+        ct8 = eng.encrypt(eng.encode(x8, slots=n * n))                     # counter 1
+        large = sf.mehp24_sort_large_adv(eng, ct8, 2 * n, n, 3, 2, 2, 2)
+        multi = sf.mehp24_sort_cheb_multi(eng, sf.mehp24_split(eng, ct8, 2 * n, n), n, -1.0, 1.0, 119, 247)
+        for name, got in (("mehp24_adv_4", adv), ("mehp24_cheb_4", cheb), ("mehp24_large_adv_8", large),
+                          ("mehp24_cheb_multi_8_0", multi[0]), ("mehp24_cheb_multi_8_1", multi[1])):
+            limbs, level, deg, slots = _load(os.path.join(str(dropin_out), name + ".bin"))
+            assert (level, deg) == (got.level, got.deg), name
+            assert np.array_equal(limbs, got.export()), name + ": reference orchestration and host layer differ"
+        assert np.max(np.abs(eng.decrypt(adv, n * n)[:n] - np.sort(x4))) < 0.01
+        assert np.max(np.abs(eng.decrypt(large, n * n)[:2 * n] - np.sort(x8))) < 0.01
+        # mehp24::sort leaves the sorted values in column 0 of the matrix (no masking, no transposition)
+        col0 = eng.decrypt(cheb, n * n).reshape(n, n)[:, 0]
+        assert np.max(np.abs(col0 - np.sort(x4))) < 0.1, col0
+        both = np.concatenate([eng.decrypt(m, n * n).reshape(n, n)[:, 0] for m in multi])
+        assert np.max(np.abs(both - np.sort(x8))) < 0.1, both
+    finally:
+        eng.close()
+
+
+@pytest.mark.gpu
+def test_reference_orchestration_on_the_engine_matches_host_layer(dropin_out):
+    tmp_path = dropin_out
     # ---- src/sort.h's SortContext<4> through files (host/serial.h): same values as the in-memory sort, and sorted
     rows = np.loadtxt(os.path.join(str(tmp_path), "serial.txt"))
     assert rows.shape == (4, 3)
