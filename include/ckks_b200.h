@@ -172,6 +172,9 @@ int ckks_profile_json(ckks_ctx_t* ctx, char* buf, size_t cap);
 
 /* kernel-level entry points on raw buffers, for parity tests and kernel benchmarks.
  * *_host variants stage through host memory; *_dev variants take device pointers. */
+/* the ChaCha20 block function (RFC 8439) behind the production sampler (contexts created with seed 0: key = 256 bits of
+ * getrandom(2), counter = sample index, nonce = sampler stream), evaluated on the host: known-answer hook for the tests */
+int ckks_rng_block(const uint32_t* key8, uint64_t stream, uint64_t index, uint32_t* out16);
 int ckks_ntt_host(ckks_ctx_t* ctx, uint64_t* data, int rows, const int32_t* modulus_ids, int inverse);
 int ckks_ntt_dev(ckks_ctx_t* ctx, void* dev_data, int rows, int first_modulus, int inverse);
 int ckks_key_switch_dev(ckks_ctx_t* ctx, const void* dev_src, int limbs, int is_rotation, int32_t index, void* dev_out);

@@ -30,6 +30,15 @@ class CkksError(RuntimeError):
     pass
 
 
+def rng_block(key, stream, index):
+    """ChaCha20 block (RFC 8439) of the production sampler, host instance (ckks_rng_block): key = 32 bytes -> 64 bytes"""
+    import struct
+    k = (ctypes.c_uint32 * 8)(*struct.unpack("<8I", bytes(key)))
+    o = (ctypes.c_uint32 * 16)()
+    _chk(_L.ckks_rng_block(k, ctypes.c_uint64(stream), ctypes.c_uint64(index), o))
+    return struct.pack("<16I", *o)
+
+
 def _chk(rc):
     if rc != 0:
         raise CkksError(_L.ckks_last_error().decode())

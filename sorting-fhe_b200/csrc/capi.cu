@@ -445,6 +445,12 @@ int ckks_profile_json(ckks_ctx_t* x, char* buf, size_t cap) {
     API_END
 }
 
+int ckks_rng_block(const uint32_t* key8, uint64_t stream, uint64_t index, uint32_t* out16) {
+    API_BEGIN
+    if (!key8 || !out16) throw std::runtime_error("rng_block: null buffer");
+    chacha20_block(key8, stream, index, out16);          // the host instance of the function the sampling kernels run
+    API_END
+}
 int ckks_ntt_host(ckks_ctx_t* x, uint64_t* data, int rows, const int32_t* mod_ids, int inverse) {
     API_BEGIN
     Context* c = C(x); Locked lk_(c);

@@ -113,6 +113,8 @@ void context_generate(Context* c, int log_n, int mult_depth, int scaling_bits, i
         uint64_t s = 0;
         if (getrandom(&s, sizeof s, 0) != (ssize_t)sizeof s || s == 0) throw std::runtime_error("getrandom failed: cannot seed the sampler");
         c->seed = s;
+        if (getrandom(c->rng_key, sizeof c->rng_key, 0) != (ssize_t)sizeof c->rng_key) throw std::runtime_error("getrandom failed: cannot key the sampler");
+        c->rng_secure = true;
     }
     { static std::atomic<uint64_t> next_uid{1}; c->uid = next_uid++; }
     if (log_n < 8 || log_n > 17) throw std::runtime_error("ring dimension must be 2^8..2^17");

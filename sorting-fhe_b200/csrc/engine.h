@@ -96,6 +96,10 @@ struct Context {
     int log_n = 0, n = 0, mult_depth = 0, scaling_bits = 0, first_bits = 0, ext = 1;
     int size_q = 0, size_p = 0, alpha = 0, num_part_q = 0;
     uint64_t seed = 1;
+    // seed == 0 at creation: production mode -- a 256-bit ChaCha20 key from getrandom(2) drives every sample (kernels.cu rng_*);
+    // a non-zero seed selects the reproducible 64-bit counter hash the oracle shares (tests, bench; NOT secure)
+    uint32_t rng_key[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool rng_secure = false;
     uint64_t uid = 0;      // process-unique id (ckks_ctx_info selector 8): lets caches keyed by the handle detect address reuse
     bool dry = false;      // metadata-only mode: no device allocations, no kernel launches
     bool enc_offload = true;   // plaintext level / scale adjustments run on the encode stream (CKKS_B200_NO_ENC_OFFLOAD=1 turns it off)
@@ -188,6 +192,31 @@ struct ProfScope {
     ~ProfScope();
 };
 void prof_collect(Context* c);   // synchronises and folds pending event pairs into Prof::ms   // capi.cu: free device tables + delete (called once closed && live_cts == 0)
+
+// ---- sampler key passed by value to the sampling kernels; ChaCha20 block function (RFC 8439) shared by host and device
+struct RngKey { uint32_t k[8]; uint64_t seed; int secure; };
+#ifdef __CUDACC__
+#define CKKS_HD __host__ __device__ __forceinline__
+#else
+#define CKKS_HD inline
+#endif
+CKKS_HD uint32_t chacha_rotl(uint32_t v, int c) { return (v << c) | (v >> (32 - c)); }
+// state: constants | key | counter = idx (64 bit) | nonce = stream (64 bit); out = the 16 words of one block
+CKKS_HD void chacha20_block(const uint32_t key[8], uint64_t stream, uint64_t idx, uint32_t out[16]) {
+    uint32_t x[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u, key[0], key[1], key[2], key[3], key[4], key[5], key[6], key[7],
+                      (uint32_t)idx, (uint32_t)(idx >> 32), (uint32_t)stream, (uint32_t)(stream >> 32)};
+    uint32_t w[16];
+    for (int i = 0; i < 16; i++) w[i] = x[i];
+#define CKKS_QR(a, b, c, d)                                                                         \
+    w[a] += w[b]; w[d] = chacha_rotl(w[d] ^ w[a], 16); w[c] += w[d]; w[b] = chacha_rotl(w[b] ^ w[c], 12); \
+    w[a] += w[b]; w[d] = chacha_rotl(w[d] ^ w[a], 8);  w[c] += w[d]; w[b] = chacha_rotl(w[b] ^ w[c], 7);
+    for (int r = 0; r < 10; r++) {
+        CKKS_QR(0, 4, 8, 12) CKKS_QR(1, 5, 9, 13) CKKS_QR(2, 6, 10, 14) CKKS_QR(3, 7, 11, 15)
+        CKKS_QR(0, 5, 10, 15) CKKS_QR(1, 6, 11, 12) CKKS_QR(2, 7, 8, 13) CKKS_QR(3, 4, 9, 14)
+    }
+#undef CKKS_QR
+    for (int i = 0; i < 16; i++) out[i] = w[i] + x[i];
+}
 
 // ---- device memory helpers (stream-ordered pool) ----
 u64* dev_alloc(Context* c, size_t words);

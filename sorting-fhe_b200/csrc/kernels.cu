@@ -316,26 +316,44 @@ __device__ __forceinline__ u64 mix64(u64 x) {
 __device__ __forceinline__ u64 hash3(u64 seed, u64 stream, u64 idx) {
     return mix64(mix64(seed + 0x9E3779B97F4A7C15ULL * (stream + 1)) ^ mix64(idx + 0xD1B54A32D192ED03ULL));
 }
-__global__ void k_sample_small(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream, int kind) {
+// production mode (Context::rng_secure): one ChaCha20 block per sample, keyed with 256 bits of OS entropy
+__device__ __forceinline__ void rng_words(const RngKey& k, u64 stream, u64 idx, u64& w0, u64& w1) {
+    if (!k.secure) { w0 = hash3(k.seed, stream, idx); w1 = 0; return; }
+    uint32_t b[16];
+    chacha20_block(k.k, stream, idx, b);
+    w0 = (u64)b[0] | ((u64)b[1] << 32); w1 = (u64)b[2] | ((u64)b[3] << 32);
+}
+static RngKey rng_key_of(const Context* c) {
+    RngKey k; for (int i = 0; i < 8; i++) k.k[i] = c->rng_key[i];
+    k.seed = c->seed; k.secure = c->rng_secure ? 1 : 0;
+    return k;
+}
+// kind 0: uniform ternary secret / encryption mask; kind 1: error, centred binomial of 2 x 20 bits (variance 10, sigma 3.16 --
+// the stand-in for OpenFHE's discrete Gaussian of sigma 3.19)
+__global__ void k_sample_small(u64* out, LimbMods mods, const ModInfo* mi, int n, const __grid_constant__ RngKey key, u64 stream, int kind) {
     pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y; u64 q = mi[mods.m[row % mods.n]].q;
-    u64 h = hash3(seed, stream, (u64)x), r;
-    if (kind == 0) { u64 t = h % 3; r = t == 0 ? 0 : (t == 1 ? 1 : q - 1); }
+    u64 h, h1, r;
+    rng_words(key, stream, (u64)x, h, h1);
+    if (kind == 0) { u64 t = key.secure ? (u64)((((unsigned __int128)h1 << 64) | h) % 3) : h % 3; r = t == 0 ? 0 : (t == 1 ? 1 : q - 1); }
     else { int e = __popcll(h & 0xFFFFF) - __popcll((h >> 20) & 0xFFFFF); r = e >= 0 ? (u64)e : q - (u64)(-e); }
     out[(size_t)row * n + x] = r;
 }
 void launch_sample_small(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream, int kind) {
-    KL(c); launch_pdl(c, k_sample_small, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, c->seed, stream, kind);
+    KL(c); launch_pdl(c, k_sample_small, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, rng_key_of(c), stream, kind);
 }
-__global__ void k_sample_uniform(u64* out, LimbMods mods, const ModInfo* mi, int n, u64 seed, u64 stream) {
+__global__ void k_sample_uniform(u64* out, LimbMods mods, const ModInfo* mi, int n, const __grid_constant__ RngKey key, u64 stream) {
     pdl_sync();
     int x = blockIdx.x * blockDim.x + threadIdx.x; if (x >= n) return;
     int row = blockIdx.y, mid = mods.m[row % mods.n]; u64 q = mi[mid].q;
-    out[(size_t)row * n + x] = hash3(seed, stream, (((u64)mid + 1) << 32) + (u64)x) % q;
+    u64 h, h1;
+    rng_words(key, stream, (((u64)mid + 1) << 32) + (u64)x, h, h1);
+    // test mode keeps the 64-bit residue the oracle shares; production reduces 128 bits (bias 2^-64 instead of up to 2^-4 for 60-bit q)
+    out[(size_t)row * n + x] = key.secure ? (u64)((((unsigned __int128)h1 << 64) | h) % q) : h % q;
 }
 void launch_sample_uniform(Context* c, u64* out, int rows, const LimbMods& m, uint64_t stream) {
-    KL(c); launch_pdl(c, k_sample_uniform, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, c->seed, stream);
+    KL(c); launch_pdl(c, k_sample_uniform, grid_for(c, rows), 256, 0, out, m, c->d_mod, c->n, rng_key_of(c), stream);
 }
 
 // evk part: b = -a*s_new + e (+ P*s_old on the digit's own limbs [lo,hi)); all [M][n] EVALUATION

@@ -91,3 +91,24 @@ def test_level_budget_dry_run(n, cfg):
     if n == 128:   # SURVEY 3.1 op table: 58 rotations, 258 encodes (+1 zero cache)
         assert ops["rotate"] == 58 and ops["encode"] in (258, 259, 260)
     eng.close()
+
+
+def test_production_sampler_block_function_known_answers():
+    """contexts created with seed 0 sample through ChaCha20 (key from getrandom, counter = sample index, nonce = sampler
+    stream); the host instance of that block function must reproduce RFC 8439 section 2.3.2 and, where the `cryptography`
+    package is present, the library's keystream for random keys / counters / nonces"""
+    import struct
+    key = bytes(range(32))
+    got = sf.rng_block(key, 0x4A000000, 1 | (0x09000000 << 32))       # counter 1, nonce 00:00:00:09 00:00:00:4a 00:00:00:00
+    want = ("e4e7f110 15593bd1 1fdd0f50 c47120a3 c7f4d1c7 0368c033 9aaa2204 4e6cd4c3 "
+            "466482d2 09aa9f07 05d7c214 a2028bd9 d19c12b5 b94e16de e883d0cb 4e3c50a2")
+    assert list(struct.unpack("<16I", got)) == [int(w, 16) for w in want.split()]
+    try:
+        from cryptography.hazmat.primitives.ciphers import Cipher, algorithms
+    except ImportError:
+        return
+    rng = np.random.default_rng(0)
+    for _ in range(8):
+        kb, stream, idx = rng.bytes(32), int(rng.integers(0, 2 ** 63)), int(rng.integers(0, 2 ** 63))
+        ks = Cipher(algorithms.ChaCha20(kb, struct.pack("<QQ", idx, stream)), mode=None).encryptor().update(b"\0" * 64)
+        assert ks == sf.rng_block(kb, stream, idx)

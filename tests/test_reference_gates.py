@@ -172,3 +172,29 @@ def test_concurrent_callers_on_one_context():
             assert np.array_equal(res[i], serial[i]), i
     finally:
         eng.close()
+
+
+def test_production_sampler_seed_zero():
+    """seed 0 = production mode (INTEGRATION.md "Randomness"): 256-bit ChaCha20 key from the OS, so two contexts never share
+    key material; the distributions are the specified ones and encryption still round-trips"""
+    a, b = sf.Engine(12, 3, 40, seed=0), sf.Engine(12, 3, 40, seed=0)
+    try:
+        for e in (a, b):
+            e.KeyGen(); e.EvalMultKeyGen()
+        sa, sb = a.export_secret(), b.export_secret()
+        assert not np.array_equal(sa, sb)
+        q0 = a.moduli()[0][0]
+        # coefficient form of the secret: INTT of limb 0 -> values in {0, 1, q - 1}, about a third each
+        coef = a.ntt_host(sa[:1].copy(), [0], inverse=True)[0]
+        vals, counts = np.unique(coef, return_counts=True)
+        assert set(int(v) for v in vals) <= {0, 1, q0 - 1} and np.all(np.abs(counts / coef.size - 1 / 3) < 0.03), (vals, counts)
+        x = np.linspace(-1, 1, 16)
+        cts = [a.encrypt(a.encode(x, slots=16)) for _ in range(2)]
+        assert not np.array_equal(cts[0].export(), cts[1].export())
+        assert np.allclose(a.decrypt(a.EvalMult(cts[0], cts[1]), 16), x * x, atol=1e-6)
+        # uniform part of the public key: mean of residues / q close to 1/2
+        pk = a.export_public_key()
+        u = pk[1, 0].astype(np.float64) / float(q0)
+        assert abs(u.mean() - 0.5) < 0.02 and abs(u.var() - 1 / 12) < 0.01
+    finally:
+        a.close(); b.close()
