@@ -65,6 +65,7 @@ void context_release(Context* c) {
             cudaFree(kv.second.d_modup_scale); cudaFree(kv.second.d_moddown_scale);
         }
         for (auto& kv : c->rescale_pairs) cudaFree(kv.second);
+        for (auto& kv : c->scal_tabs) cudaFree(kv.second);
         dev_free(c, c->d_secret); dev_free(c, c->d_pk); dev_free(c, c->relin.d);
         for (auto& kv : c->rot) dev_free(c, kv.second.d);
         cudaStreamSynchronize(c->stream);

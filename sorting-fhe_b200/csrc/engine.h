@@ -11,6 +11,7 @@
 #include <cstddef>
 #include <deque>
 #include <map>
+#include <tuple>
 #include <unordered_map>
 #include <mutex>
 #include <string>
@@ -42,6 +43,8 @@ struct NttFuse {
     const u64* epi_in = nullptr;          // minuend limbs, addressed through emap
     RowMap emap;
     const u64* epi_pairs = nullptr;       // [M] (factor, Shoup) pairs indexed by modulus id
+    const u64* epi_pre = nullptr;         // EPI_RESCALE: optional [M] (s mod q_i, Shoup) pairs -- the minuend is multiplied by s first
+                                          // (a scalar product folded into the rescale that follows it, evaluator.cu scaled_rescale_new)
     const u64* epi_add[2] = {nullptr, nullptr};   // EPI_MODDOWN: addend limbs [epi_add_grp][n] of logical rows r / epi_add_grp == 0, 1 (or nullptr)
     int epi_add_grp = 1 << 30;
     uint32_t auto_kinv = 0;               // != 0: result element e is stored at the EVALUATION-format image of e under X -> X^k (k kinv = 1 mod 2n)
@@ -119,6 +122,8 @@ struct Context {
     uint32_t* d_rot = nullptr;              // [n/2] 5^j mod 2n
     std::map<int, KsTables> ks;             // keyed by nl
     std::map<int, u64*> rescale_pairs;      // keyed by nl_in: device [M] (q_last^-1 mod q_i, Shoup) pairs
+    // (integer scalar s, lrep) -> device [2][M] pairs: (s mod q_i, Shoup) and ((n >> lrep)^-1 s mod q_i, Shoup); kernels.cu scaled_tables
+    std::map<std::tuple<u64, u64, int>, u64*> scal_tabs;
     // keys (device)
     u64* d_secret = nullptr;                // [M][n] EVALUATION
     u64* d_pk = nullptr;                    // [2][sizeQ][n]  (b, a)
@@ -254,6 +259,10 @@ void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl);
 void launch_mod_reduce(Context* c, u64* d, int rows, int nl);
 void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int rows, int nl);
 void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep = 0);
+// DropLastElementAndScale of (s * in) restricted to the first nl_keep < nl_in limbs: what EvalMult(ct, const) -> rescale ->
+// LevelReduce(nl_in - 1 - nl_keep) leaves, in one INTT + one fused NTT over parts * nl_keep rows.  s128 = the integer scalar
+// (low, high words of its two's complement).  Returns false (nothing launched) when the scalar-table cache is full.
+bool launch_rescale_scaled(Context* c, u64* out, const u64* in, int parts, int nl_in, int nl_keep, u64 s_lo, u64 s_hi, int lrep = 0);
 void launch_tensor(Context* c, u64* d3, const u64* a, const u64* b, int nl);
 void launch_automorph(Context* c, u64* out, const u64* in, int rows, uint32_t k);
 #define MAX_CONV_IN 24

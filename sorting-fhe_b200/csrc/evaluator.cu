@@ -175,6 +175,34 @@ static void op_mult_const(Opnd& o, double x) {
     o.set_own(mult_const_new(o.v, x));
 }
 static void op_rescale(Opnd& o) { if (o.own) o.set_own(rescale_new(o.v)); else o.v = rescaled_twin(o.v); }
+// EvalMultCore(ct, x) -> ModReduceInternal -> LevelReduceInternal(drop) in one step (kernels.cu launch_rescale_scaled): the scalar
+// rides on the inverse transform's final factor and on the rescale epilogue's minuend, and only the limbs that survive the level
+// reduction are computed.  Limb for limb the same residues as the three separate steps (every step is exact modular arithmetic).
+// DirectSort N=128 meets this adjustment 128 times per sort (EvalAdd / EvalMult of two depth-2 operands at different levels),
+// 18 of them from 32 limbs down to 2: 150 scalar-product launches and the transforms of ~1 400 discarded limbs per sort.
+static Ct* scaled_rescale_new(const Ct* a, double x, int drop) {
+    if (enc_offload(a)) return on_enc_stream(a, [&] { return scaled_rescale_new(a, x, drop); });
+    Context* c = a->ctx; const int nl = a->nl, keep = nl - 1 - drop;
+    const double sf = c->sf_real[a->level];
+    const i128 v = (i128)(x * sf + 0.5);                  // same rounding as mult_const_new
+    count(c, "rescale", nl); count(c, "rescale_scaled", nl);
+    Ct* out = ct_new(c, a->parts, keep, a->level + 1 + drop, a->deg, (a->sf * sf) / (double)c->moduli[nl - 1], a->slots, a->lrep);
+    if (!launch_rescale_scaled(c, out->d, a->d, a->parts, nl, keep, (u64)(unsigned __int128)v, (u64)((unsigned __int128)v >> 64), a->lrep)) {
+        ct_free(out);
+        throw std::runtime_error("internal: scalar-table cache exhausted");
+    }
+    return out;
+}
+static bool can_fuse_adjust(const Opnd& o, int drop) {
+    static const bool off = getenv("CKKS_B200_NO_FUSED_ADJUST") != nullptr;   // A/B switch: the three separate steps
+    return !off && o.v->parts >= 2 && o.v->nl - 1 - drop >= 1 && o.v->ctx->scal_tabs.size() < 4000;   // plaintexts keep their cached twins
+}
+static void op_level_reduce(Opnd& o, int levels);
+// a <- LevelReduce(Rescale(a * x), drop)
+static void op_mult_rescale_reduce(Opnd& o, double x, int drop) {
+    if (can_fuse_adjust(o, drop)) { o.set_own(scaled_rescale_new(o.v, x, drop)); return; }
+    op_mult_const(o, x); op_rescale(o); op_level_reduce(o, drop);
+}
 static void op_level_reduce(Opnd& o, int levels) { if (levels > 0) o.set_own(level_reduce_new(o.v, levels)); }
 static void op_set_sf(Opnd& o, double sf) {
     if (o.v->sf == sf) return;
@@ -208,17 +236,13 @@ static void adjust_levels_and_depth(Opnd& A, Opnd& B) {
     if (a.v->deg == 2) {
         if (b.v->deg == 2) {
             double q1 = (double)c->moduli[a.v->nl - 1];
-            op_mult_const(a, bsf / a.v->sf * q1 / scf);
-            op_rescale(a);
-            op_level_reduce(a, l2 - l1 - 1);
+            op_mult_rescale_reduce(a, bsf / a.v->sf * q1 / scf, l2 - l1 - 1);
             op_set_sf(a, bsf);
         } else if (l1 + 1 == l2) {
             op_rescale(a);
         } else {
             double q1 = (double)c->moduli[a.v->nl - 1];
-            op_mult_const(a, c->sf_big[l2 - 1] / a.v->sf * q1 / scf);
-            op_rescale(a);
-            op_level_reduce(a, l2 - l1 - 2);
+            op_mult_rescale_reduce(a, c->sf_big[l2 - 1] / a.v->sf * q1 / scf, l2 - l1 - 2);
             op_rescale(a);
             op_set_sf(a, bsf);
         }

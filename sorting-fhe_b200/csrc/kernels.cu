@@ -270,22 +270,75 @@ static u64 host_powmod(u64 a, u64 e, u64 q) {
 // DropLastElementAndScale of `parts` polynomials with nl_in limbs each -> out [parts][nl_in-1][n]:
 // INTT of the last limbs, then ONE forward NTT launch over all remaining limbs whose prologue switches the last
 // limb's coefficients to the row modulus and whose epilogue forms (c_i - that) * q_last^-1.
-void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep) {
-    const int nl = nl_in, nlo = nl_in - 1;
-    const size_t n = c->n >> lrep;
-    u64* last = dev_alloc(c, (size_t)parts * n);
-    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, nullptr, RowMap{1, nl, nl - 1, 1}, RowMap{}, nullptr, lrep);
+// Tables of an integer scalar s (two's complement in s_hi:s_lo) for the scaled rescale: [0][M] pairs (s mod q_i, Shoup), [1][M] pairs
+// ((n >> lrep)^-1 s mod q_i, Shoup).  The scalars of FLEXIBLEAUTOEXT's level adjustments are functions of the scaling factors
+// alone, so a sorter meets the same few dozen values in every sort: the tables are cached per context (bounded).
+static const u64* scaled_tables(Context* c, u64 s_lo, u64 s_hi, int lrep) {
+    const auto key = std::make_tuple(s_lo, s_hi, lrep);
+    auto it = c->scal_tabs.find(key);
+    if (it != c->scal_tabs.end()) return it->second;
+    if (c->scal_tabs.size() >= 4096) return nullptr;
+    const int M = c->M();
+    std::vector<u64> v(4 * (size_t)M);
+    const __int128 sv = (__int128)(((unsigned __int128)s_hi << 64) | s_lo);
+    for (int i = 0; i < M; i++) {
+        const u64 q = c->moduli[i];
+        __int128 r = sv % (__int128)q; if (r < 0) r += q;
+        const u64 si = (u64)r;
+        const u64 ninv = (u64)((unsigned __int128)c->h_mod[i].ninv * ((1ull << lrep) % q) % q);
+        const u64 w = (u64)((unsigned __int128)ninv * si % q);
+        v[2 * i] = si; v[2 * i + 1] = host_shoup(si, q);
+        v[2 * M + 2 * i] = w; v[2 * M + 2 * i + 1] = host_shoup(w, q);
+    }
+    u64* d = nullptr;
+    if (!c->dry) {
+        if (cudaMalloc(&d, v.size() * sizeof(u64)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        cudaMemcpy(d, v.data(), v.size() * sizeof(u64), cudaMemcpyHostToDevice);   // synchronous: visible to every stream of the context
+    } else d = reinterpret_cast<u64*>(8);   // dry contexts launch nothing; any non-null marker
+    c->scal_tabs.emplace(key, d);
+    return d;
+}
+
+static const u64* rescale_pairs_for(Context* c, int nl) {
     auto it = c->rescale_pairs.find(nl);
     if (it == c->rescale_pairs.end()) {
+        const int nlo = nl - 1;
         std::vector<u64> v(2 * (size_t)c->M(), 0); u64 ql = c->moduli[nl - 1];
         for (int i = 0; i < nlo; i++) { u64 q = c->moduli[i]; v[2 * i] = host_powmod(ql % q, q - 2, q); v[2 * i + 1] = host_shoup(v[2 * i], q); }
         u64* d = nullptr;
         if (!c->dry) { cudaMalloc(&d, v.size() * sizeof(u64)); cudaMemcpy(d, v.data(), v.size() * sizeof(u64), cudaMemcpyHostToDevice); }
         it = c->rescale_pairs.emplace(nl, d).first;
     }
+    return it->second;
+}
+
+bool launch_rescale_scaled(Context* c, u64* out, const u64* in, int parts, int nl_in, int nl_keep, u64 s_lo, u64 s_hi, int lrep) {
+    const u64* tabs = scaled_tables(c, s_lo, s_hi, lrep);
+    if (!tabs) return false;
+    const int nl = nl_in;
+    const size_t n = c->n >> lrep;
+    u64* last = dev_alloc(c, (size_t)parts * n);
+    // coefficients of s * (last limb): the scalar rides on the inverse transform's final factor
+    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, c->dry ? nullptr : tabs + 2 * (size_t)c->M(), RowMap{1, nl, nl - 1, 1}, RowMap{}, nullptr, lrep);
     NttFuse f;
     f.pro = PRO_SWITCHMOD; f.pro_mod = nl - 1;
-    f.epi = EPI_RESCALE; f.epi_in = in; f.emap = RowMap{nlo, nl, 0, 1}; f.epi_pairs = it->second;
+    f.epi = EPI_RESCALE; f.epi_in = in; f.emap = RowMap{nl_keep, nl, 0, 1}; f.epi_pairs = rescale_pairs_for(c, nl); f.epi_pre = tabs;
+    {
+        ProfScope ps(c, KC_RESCALE, 0.0, 0);   // the fused launch is accounted to the NTT class
+    }
+    launch_ntt_ex(c, out, last, parts * nl_keep, mods_q(nl_keep), false, nullptr, RowMap{nl_keep, 1, 0, 0}, RowMap{}, &f, lrep);
+    dev_free(c, last);
+    return true;
+}
+
+void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep) {
+    const int nl = nl_in, nlo = nl_in - 1;
+    const size_t n = c->n >> lrep;
+    u64* last = dev_alloc(c, (size_t)parts * n);
+    launch_ntt_ex(c, last, in, parts, mods_range(nl - 1, nl), true, nullptr, RowMap{1, nl, nl - 1, 1}, RowMap{}, nullptr, lrep);
+    NttFuse f;
+    f.pro = PRO_SWITCHMOD; f.pro_mod = nl - 1;
+    f.epi = EPI_RESCALE; f.epi_in = in; f.emap = RowMap{nlo, nl, 0, 1}; f.epi_pairs = rescale_pairs_for(c, nl);
     c->stats.kernel_launches += 0;
     {
         ProfScope ps(c, KC_RESCALE, 0.0, 0);   // the fused launch is accounted to the NTT class

@@ -175,6 +175,11 @@ __device__ __forceinline__ void epilogue_store(const NttArgs& A, const NttRows& 
 #pragma unroll
             for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
         }
+        if (A.f.epi_pre) {   // scaled rescale: the minuend is s * in (the scalar product that preceded the rescale, never materialised)
+            const tw_t ps = reinterpret_cast<const tw_t*>(A.f.epi_pre)[mid];
+#pragma unroll
+            for (int k = 0; k < 8; k++) xin[k] = shoup_mul(xin[k], ps.x, ps.y, q);
+        }
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = shoup_mul(sub_mod(xin[k], v[k], q), sc.x, sc.y, q);
         if (A.f.epi == EPI_MODDOWN) {
