@@ -22,6 +22,7 @@
 // Results are canonical residues, bit-identical to the oracle.
 #include "engine.h"
 #include <cstdlib>
+#include <cstring>
 #include <utility>
 #include <vector>
 
@@ -58,39 +59,61 @@ __device__ __forceinline__ int local_index(int u, int k, int p) {
     return ((u >> p) << (p + 3)) | (k << p) | (u & ((1 << p) - 1));
 }
 
-template <bool FIX>
-__device__ __forceinline__ void bf_fwd(u64& X, u64& Y, const tw_t w, const u64 q, const u64 q2) {
-    const u64 T = shoup_lazy(Y, w.x, w.y, q);   // [0, 2q)
+// x * w mod q in [0, 2q) for any x < 2^64, computed as x * w + floor(x w' / 2^64) * (2^64 - q): with the negated modulus the low
+// 64 bits are two chained IMAD.WIDE and four IMAD into the high word -- 6 instructions where `x * w - hi * q` compiles to 10 (two
+// separate 64-bit products, a negation and a 64-bit add; profiles/r02_sass_ntt.txt).  Same value, bit for bit.
+__device__ __forceinline__ u64 shoup_lazy_n(u64 x, u64 w, u64 wsh, u64 nq) {
+    const u64 hi = __umul64hi(x, wsh);
+    u64 T;
+    asm("{\n\t.reg .u32 x0,x1,w0,w1,h0,h1,n0,n1,t0,t1;\n\t.reg .u64 a;\n\t"
+        "mov.b64 {x0,x1}, %1;\n\tmov.b64 {w0,w1}, %2;\n\tmov.b64 {h0,h1}, %3;\n\tmov.b64 {n0,n1}, %4;\n\t"
+        "mul.wide.u32 a, x0, w0;\n\t"
+        "mad.wide.u32 a, h0, n0, a;\n\t"
+        "mov.b64 {t0,t1}, a;\n\t"
+        "mad.lo.u32 t1, x0, w1, t1;\n\t"
+        "mad.lo.u32 t1, x1, w0, t1;\n\t"
+        "mad.lo.u32 t1, h0, n1, t1;\n\t"
+        "mad.lo.u32 t1, h1, n0, t1;\n\t"
+        "mov.b64 %0, {t0,t1};\n\t}"
+        : "=l"(T) : "l"(x), "l"(w), "l"(hi), "l"(nq));
+    return T;
+}
+
+__device__ __forceinline__ void bf_fwd(u64& X, u64& Y, const tw_t w, const u64 nq, const u64 q2) {
+    const u64 T = shoup_lazy_n(Y, w.x, w.y, nq);   // [0, 2q)
     const u64 x = X;
     X = x + T;
     Y = x - T + q2;
-    (void)FIX;
 }
 template <bool FIX>
-__device__ __forceinline__ void bf_inv(u64& X, u64& Y, const tw_t w, const u64 q, const u64 q2, const u64 cq) {
+__device__ __forceinline__ void bf_inv(u64& X, u64& Y, const tw_t w, const u64 nq, const u64 q2, const u64 cq) {
     const u64 x = X, y = Y;
     if (FIX) {                       // operands < 2q
         u64 s = x + y;
         if (s >= q2) s -= q2;
         X = s;
-        Y = shoup_lazy(x - y + q2, w.x, w.y, q);
+        Y = shoup_lazy_n(x - y + q2, w.x, w.y, nq);
     } else {                         // operands < cq = 2^t q (t = stages done so far), no correction
         X = x + y;
-        Y = shoup_lazy(x - y + cq, w.x, w.y, q);
+        Y = shoup_lazy_n(x - y + cq, w.x, w.y, nq);
     }
 }
 
 // One round on the 8 registers of a thread: butterfly stages j in [J0, J1) of the 3-bit window.
 // s0 = global stage number of j = 0; ehi = all element-index bits above the window.
+// Forward FIX rows (moduli of 59 / 60 bits, q < 2^60): a stage adds at most 2q to a value, so a round of <= 3 stages needs its inputs
+// below 2^64 - 6q.  The fold at the head of a round is `r >= 2^63 ? r - 8q : r` -- a sign test on the high word instead of a 64-bit
+// compare (r >= 2^63 implies r >= 8q; afterwards r < max(2^63, 2^64 - 8q), and both plus 6q stay below 2^64) -- and `nofold` skips it
+// altogether in the first pass of a two-pass transform: canonical inputs grow to at most (2 * 7 + 1) q < 2^64 over its <= 7 stages.
 template <bool INV, bool FIX, int J0, int J1>
 __device__ __forceinline__ void round8(u64 (&r)[8], const tw_t* __restrict__ W, const u32 ehi, const int s0, const u64 q,
-                                       int t_done) {
-    const u64 q2 = q << 1;
+                                       int t_done, const bool nofold) {
+    const u64 q2 = q << 1, nq = 0 - q;
     if (!INV) {
-        if (FIX) {
+        if (FIX && !nofold) {
             const u64 q8 = q << 3;
 #pragma unroll
-            for (int k = 0; k < 8; k++) if (r[k] >= q8) r[k] -= q8;
+            for (int k = 0; k < 8; k++) if ((long long)r[k] < 0) r[k] -= q8;
         }
 #pragma unroll
         for (int j = J0; j < J1; j++) {
@@ -99,7 +122,7 @@ __device__ __forceinline__ void round8(u64 (&r)[8], const tw_t* __restrict__ W, 
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 if (k & bit) continue;
-                bf_fwd<FIX>(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), q, q2);
+                bf_fwd(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), nq, q2);
             }
         }
     } else {
@@ -111,7 +134,7 @@ __device__ __forceinline__ void round8(u64 (&r)[8], const tw_t* __restrict__ W, 
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 if (k & bit) continue;
-                bf_inv<FIX>(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), q, q2, cq);
+                bf_inv<FIX>(r[k], r[k | bit], __ldg(Ws + (k >> (3 - j))), nq, q2, cq);
             }
             t_done++;
         }
@@ -236,12 +259,12 @@ __host__ __device__ constexpr Sched make_sched(int T, int ns, bool inverse) {
 }
 
 template <bool INV, bool FIX>
-__device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, int s0, u64 q, int t_done, int j0, int j1) {
-    if (j0 == 0 && j1 == 3) round8<INV, FIX, 0, 3>(r, W, ehi, s0, q, t_done);
-    else if (j0 == 1 && j1 == 3) round8<INV, FIX, 1, 3>(r, W, ehi, s0, q, t_done);
-    else if (j0 == 2 && j1 == 3) round8<INV, FIX, 2, 3>(r, W, ehi, s0, q, t_done);
-    else if (j0 == 0 && j1 == 2) round8<INV, FIX, 0, 2>(r, W, ehi, s0, q, t_done);
-    else round8<INV, FIX, 0, 1>(r, W, ehi, s0, q, t_done);
+__device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, int s0, u64 q, int t_done, int j0, int j1, bool nofold) {
+    if (j0 == 0 && j1 == 3) round8<INV, FIX, 0, 3>(r, W, ehi, s0, q, t_done, nofold);
+    else if (j0 == 1 && j1 == 3) round8<INV, FIX, 1, 3>(r, W, ehi, s0, q, t_done, nofold);
+    else if (j0 == 2 && j1 == 3) round8<INV, FIX, 2, 3>(r, W, ehi, s0, q, t_done, nofold);
+    else if (j0 == 0 && j1 == 2) round8<INV, FIX, 0, 2>(r, W, ehi, s0, q, t_done, nofold);
+    else round8<INV, FIX, 0, 1>(r, W, ehi, s0, q, t_done, nofold);
 }
 
 // LOGN_C != 0: ring size, pass and round schedule are compile-time constants (all index arithmetic folds);
@@ -309,7 +332,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         u32 ehi; int s0;
         if (strided) { ehi = (u32)(L0 >> (p + 3)); s0 = a_ - 1 - (p + 2 - cb); }
         else { ehi = (u32)(((size_t)tile << T | (size_t)L0) >> (p + 3)); s0 = logn - 1 - (p + 2); }
-        do_round<INV, FIX>(r, W, ehi, s0, q, t_done, S.j0[ri], S.j1[ri]);
+        do_round<INV, FIX>(r, W, ehi, s0, q, t_done, S.j0[ri], S.j1[ri], strided && A.first_pass && a_ <= 7);
         if (INV) t_done += S.j1[ri] - S.j0[ri];
         if (ri + 1 < (LOGN_C ? SC.nr : SR.nr)) {
             __syncthreads();
@@ -318,10 +341,26 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         } else {
             if (A.final_pass) {
                 if (!INV) {
+                    if (FIX) {
+                        // q >= 2^58: floor(r / q) < 64 is estimated from the high word alone, k = (hi32(r) * floor(2^90 / q)) >> 58 in
+                        // {floor(r / q) - 1, floor(r / q)}, so r - k q lies in [0, 2q): one IMAD.HI and two multiply-adds with the negated
+                        // modulus instead of a 64 x 64 high product and a 64-bit product (the host keeps floor(2^90 / q) in the row's
+                        // otherwise unused FP64 reciprocal slot)
+                        const u32 m32 = (u32)__double_as_longlong(R.qinv[row]);
+                        const u64 nq = 0 - q;
 #pragma unroll
-                    for (int k = 0; k < 8; k++) {   // any value < 2^64 -> [0, q)
-                        u64 v = r[k] - __umul64hi(r[k], mi.qrecip) * q;
-                        r[k] = v >= q ? v - q : v;
+                        for (int k = 0; k < 8; k++) {
+                            const u32 kq = __umulhi((u32)(r[k] >> 32), m32) >> 26;
+                            u64 v = r[k] + (u64)kq * (u32)nq;
+                            v += (u64)(kq * (u32)(nq >> 32)) << 32;
+                            r[k] = v >= q ? v - q : v;
+                        }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {   // any value < 2^64 -> [0, q)
+                            u64 v = r[k] - __umul64hi(r[k], mi.qrecip) * q;
+                            r[k] = v >= q ? v - q : v;
+                        }
                     }
                     epilogue_store(A, R, row, logn, !strided && p == 0, u, p, q, mid, r, dst, gaddr);
                     continue;
@@ -628,7 +667,8 @@ static void launch_one(Context* c, int total, int tpr_log, int threads, size_t s
 }
 template <bool INV, int PASS_C>
 static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
-    switch (A.logn) {   // compile-time schedules for the ring sizes of the reference's fixtures (+ their compact plaintexts)
+    static const bool generic = getenv("CKKS_B200_NTT_GENERIC") != nullptr;   // A/B switch: the runtime-schedule (rolled-loop) form
+    switch (generic ? 0 : A.logn) {   // compile-time schedules for the ring sizes of the reference's fixtures (+ their compact plaintexts)
         case 17: launch_one<INV, 17, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
         case 16: launch_one<INV, 16, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
         case 15: launch_one<INV, 15, PASS_C>(c, total, tpr_log, threads, smem, A, S, m); break;
@@ -705,6 +745,11 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
             R1.src[i] = row_of(smap, r); R1.dst[i] = row_of(dmap, r); R1.epi[i] = fuse ? row_of(fuse->emap, r) : 0;
             R1.mid[i] = (short)mid; R1.q[i] = mi.q; R1.qinv[i] = 1.0 / (double)mi.q;
             R1.kind[i] = (mi.bits <= FP_BITS && A.twd) ? ROW_FP : ((inverse ? mi.bits > 46 : mi.bits > 58) ? ROW_INT_FIX : ROW_INT);
+            if (R1.kind[i] == ROW_INT_FIX && !inverse) {   // floor(2^90 / q) < 2^32 for the final canonicalisation (ntt_tile), as raw bits
+                const long long m32 = (long long)((((unsigned __int128)1) << 90) / mi.q);
+                static_assert(sizeof(double) == sizeof(long long), "bit copy");
+                memcpy(&R1.qinv[i], &m32, sizeof(double));
+            }
             R1.addsel[i] = 0; R1.addrow[i] = 0;
             if (fuse && fuse->epi == EPI_MODDOWN) { R1.addsel[i] = (unsigned char)((r / fuse->epi_add_grp) & 1); R1.addrow[i] = (short)(r % fuse->epi_add_grp); }
         }
