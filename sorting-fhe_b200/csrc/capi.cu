@@ -6,7 +6,7 @@
 #include <stdexcept>
 
 struct ckks_ctx { Context c; };
-struct ckks_ct { Ct* p; };
+struct ckks_ct { mutable Ct* p; };
 
 static thread_local std::string g_err;
 extern "C" const char* ckks_last_error(void) { return g_err.c_str(); }
@@ -277,13 +277,38 @@ int ckks_make_packed_plaintext(ckks_ctx_t* x, const double* v, int count, int sc
 int ckks_encrypt(ckks_ctx_t* x, const ckks_ct_t* pt, ckks_ct_t** out) { API_BEGIN Locked lk_(C(x)); *out = box(encrypt(C(x), G(pt))); API_END }
 int ckks_decrypt(ckks_ctx_t* x, const ckks_ct_t* ct, double* v, int count) { API_BEGIN Locked lk_(C(x)); decrypt(G(ct), v, count); check_cuda("decrypt"); API_END }
 
-int ckks_ct_free(ckks_ct_t* ct) { API_BEGIN if (ct) { if (ct->p) { Locked lk_(ct->p->ctx); ct_free(ct->p); } delete ct; } API_END }
-int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out) { API_BEGIN Locked lk_(G(ct)->ctx); *out = box(ct_clone(G(ct))); API_END }
+int ckks_ct_free(ckks_ct_t* ct) { API_BEGIN if (ct) { if (ct->p) { Locked lk_(ct->p->ctx); if (--ct->p->refs == 0) ct_free(ct->p); } delete ct; } API_END }
+// Clone is copy-on-write: every evaluator entry point is out of place on its operands, so a clone shares the source's limbs (and its
+// cached rescaled / adjusted twins and ModUp digits) until one of the three entry points that change a handle -- SetSlots, the
+// mod-reduce after an in-place all-reduce, or handing out the device pointer -- is applied to it.  The sorters seed every accumulator
+// with `getZero()->Clone()` (reference src/sort_algo.h:563-566): 64 MB copies at ring 2^17, each followed by a level adjustment of
+// the same limbs.  CKKS_B200_EAGER_CLONE=1 restores the copying clone (A/B).
+static Ct* unshared(const ckks_ct_t* ct) {
+    Ct* p = const_cast<Ct*>(G(ct));
+    if (p->refs > 1) { Ct* q = ct_clone(p); p->refs--; ct->p = q; return q; }
+    return p;
+}
+int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out) {
+    API_BEGIN
+    static const bool eager = getenv("CKKS_B200_EAGER_CLONE") != nullptr;
+    const Ct* p = G(ct); Locked lk_(p->ctx);
+    if (eager) *out = box(ct_clone(p));
+    else { p->refs++; *out = box(const_cast<Ct*>(p)); }
+    API_END
+}
 int ckks_ct_set_slots(ckks_ct_t* ct, int slots) {
     API_BEGIN
-    Ct* p = const_cast<Ct*>(G(ct)); Locked lk_(p->ctx);
-    if (slots <= 0 || (slots & (slots - 1)) || slots > p->ctx->n / 2) throw std::runtime_error("SetSlots: bad slot count");
-    p->slots = slots;
+    Locked lk_(G(ct)->ctx);
+    if (slots <= 0 || (slots & (slots - 1)) || slots > G(ct)->ctx->n / 2) throw std::runtime_error("SetSlots: bad slot count");
+    if (G(ct)->slots == slots) return 0;
+    Ct* p = unshared(ct);
+    struct Rec { static void set(const Ct* t, int s) {      // cached twins carry the slot count of their source
+        const_cast<Ct*>(t)->slots = s;
+        if (t->resc) set(t->resc, s);
+        if (t->lift) set(t->lift, s);
+        for (const AdjTwin& e : t->adj) set(e.t, s);
+    } };
+    Rec::set(p, slots);
     API_END
 }
 int ckks_ct_get(const ckks_ct_t* ct, int what, int64_t* out) {
@@ -312,7 +337,8 @@ int ckks_ct_export(const ckks_ct_t* ct, uint64_t* host, size_t cap) {
 int ckks_ctx_set_encryption_counter(ckks_ctx_t* x, uint64_t counter) { API_BEGIN Locked lk_(C(x)); C(x)->enc_counter = counter; API_END }
 int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
     API_BEGIN
-    const Ct* p = G(ct); Locked lk_(p->ctx);
+    Locked lk_(G(ct)->ctx);
+    const Ct* p = unshared(ct);                 // the caller may write through the pointer (shard.py all-reduces in place)
     if (p->lrep) throw std::runtime_error("ct_device_ptr: compact plaintexts have no full-length device form");
     ct_wait(p);
     *dev_ptr = p->d; *words = (size_t)p->parts * p->nl * p->ctx->n;
@@ -320,7 +346,7 @@ int ckks_ct_device_ptr(const ckks_ct_t* ct, void** dev_ptr, size_t* words) {
 }
 int ckks_ct_mod_reduce(ckks_ctx_t* x, ckks_ct_t* ct) {
     API_BEGIN
-    Context* c = C(x); Locked lk_(c); Ct* p = const_cast<Ct*>(G(ct));
+    Context* c = C(x); Locked lk_(c); Ct* p = unshared(ct);
     if (p->lrep) throw std::runtime_error("ct_mod_reduce: compact plaintext");
     if (p->resc) { ct_free(p->resc); p->resc = nullptr; }            // the limbs are about to change: drop derived caches
     if (p->modup) { dev_free(c, p->modup); p->modup = nullptr; }

@@ -166,6 +166,8 @@ struct Context {
     int M() const { return size_q + size_p; }
 };
 
+struct Ct;
+struct AdjTwin { double x; int drop; double sf; Ct* t; };   // evaluator.cu adjusted_twin()
 struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     Context* ctx;
     u64* d;
@@ -175,6 +177,8 @@ struct Ct {                // ciphertext (parts 2/3) or plaintext (parts 1)
     int slots;
     mutable Ct* resc = nullptr;   // cached rescaled twin (owned); see rescaled_twin() in evaluator.cu
     mutable Ct* lift = nullptr;   // plaintexts only: cached x 1.0 twin (noiseScaleDeg + 1, owned); see lifted_twin()
+    mutable int refs = 1;         // ckks_ct_t handles that share this object (capi.cu: ckks_ct_clone is copy-on-write)
+    mutable std::vector<AdjTwin> adj;   // cached level-adjusted twins LevelReduce(Rescale(this * x), drop) (owned, at most 4)
     mutable cudaEvent_t ready = nullptr;   // recorded on the encode stream; the first consumer makes the main stream wait on it
     mutable u64* modup = nullptr; // cached ModUp of c1 (owned): shared by all rotations of this ciphertext (hoisting)
     // Plaintexts are encoded on the encode stream, and the level / scale adjustments a multiplication applies to them

@@ -45,6 +45,7 @@ static void drop_twin(const Ct* a) { ct_drop_caches(a); }
 void ct_drop_caches(const Ct* a) {
     if (a->resc) { Ct* t = a->resc; a->resc = nullptr; ct_free(t); }
     if (a->lift) { Ct* t = a->lift; a->lift = nullptr; ct_free(t); }
+    while (!a->adj.empty()) { Ct* t = a->adj.back().t; a->adj.pop_back(); ct_free(t); }
     if (a->modup) {
         dev_free(a->ctx, a->modup); a->modup = nullptr;
         auto& q = a->ctx->modup_lru;
@@ -198,10 +199,28 @@ static bool can_fuse_adjust(const Opnd& o, int drop) {
     return !off && o.v->parts >= 2 && o.v->nl - 1 - drop >= 1 && o.v->ctx->scal_tabs.size() < 4000;   // plaintexts keep their cached twins
 }
 static void op_level_reduce(Opnd& o, int levels);
-// a <- LevelReduce(Rescale(a * x), drop)
-static void op_mult_rescale_reduce(Opnd& o, double x, int drop) {
-    if (can_fuse_adjust(o, drop)) { o.set_own(scaled_rescale_new(o.v, x, drop)); return; }
-    op_mult_const(o, x); op_rescale(o); op_level_reduce(o, drop);
+// The adjusted twin of a pristine operand is cached on it like the rescaled one: a sorter adds the same accumulator seed (the
+// context's zero ciphertext, a rank vector) to partial results at one and the same deeper level over and over.  Keyed by the
+// scalar, the level drop and the scaling factor the caller assigns afterwards (AdjustLevelsAndDepth sets it to the other operand's).
+// Clones made through ckks_ct_clone share the handle's data and therefore its twins (capi.cu), so the reference's
+// `getZero()->Clone()` seeds hit the cache as well.
+static const Ct* adjusted_twin(const Ct* a, double x, int drop, double sf) {
+    for (const AdjTwin& e : a->adj)
+        if (e.x == x && e.drop == drop && e.sf == sf) { count(a->ctx, "adjust_cached", a->nl); return e.t; }
+    Ct* t = scaled_rescale_new(a, x, drop);
+    t->sf = sf;
+    if (a->adj.size() >= 4) { Ct* old = a->adj.front().t; a->adj.erase(a->adj.begin()); ct_free(old); }
+    a->adj.push_back(AdjTwin{x, drop, sf, t});
+    return t;
+}
+static void op_set_sf(Opnd& o, double sf);
+// a <- LevelReduce(Rescale(a * x), drop) with the scaling factor set to sf
+static void op_mult_rescale_reduce(Opnd& o, double x, int drop, double sf) {
+    if (can_fuse_adjust(o, drop)) {
+        if (!o.own) { o.v = adjusted_twin(o.v, x, drop, sf); ct_wait(o.v); return; }
+        o.set_own(scaled_rescale_new(o.v, x, drop));
+    } else { op_mult_const(o, x); op_rescale(o); op_level_reduce(o, drop); }
+    op_set_sf(o, sf);
 }
 static void op_level_reduce(Opnd& o, int levels) { if (levels > 0) o.set_own(level_reduce_new(o.v, levels)); }
 static void op_set_sf(Opnd& o, double sf) {
@@ -236,13 +255,16 @@ static void adjust_levels_and_depth(Opnd& A, Opnd& B) {
     if (a.v->deg == 2) {
         if (b.v->deg == 2) {
             double q1 = (double)c->moduli[a.v->nl - 1];
-            op_mult_rescale_reduce(a, bsf / a.v->sf * q1 / scf, l2 - l1 - 1);
-            op_set_sf(a, bsf);
+            op_mult_rescale_reduce(a, bsf / a.v->sf * q1 / scf, l2 - l1 - 1, bsf);
         } else if (l1 + 1 == l2) {
             op_rescale(a);
         } else {
             double q1 = (double)c->moduli[a.v->nl - 1];
-            op_mult_rescale_reduce(a, c->sf_big[l2 - 1] / a.v->sf * q1 / scf, l2 - l1 - 2);
+            {   // the intermediate's scaling factor is its natural one: an owned temporary, no twin
+                const double x = c->sf_big[l2 - 1] / a.v->sf * q1 / scf; const int drop = l2 - l1 - 2;
+                if (can_fuse_adjust(a, drop)) a.set_own(scaled_rescale_new(a.v, x, drop));
+                else { op_mult_const(a, x); op_rescale(a); op_level_reduce(a, drop); }
+            }
             op_rescale(a);
             op_set_sf(a, bsf);
         }
@@ -273,6 +295,14 @@ static void commit(Ct* a, Opnd& o) {
     if (o.v == a->resc) { t = a->resc; a->resc = nullptr; }
     else if (o.v == a->lift) { t = a->lift; a->lift = nullptr; }
     else if (a->lift && o.v == a->lift->resc) { t = a->lift->resc; a->lift->resc = nullptr; }
+    else if ([&] {
+                 for (size_t i = 0; i < a->adj.size(); i++) {
+                     Ct* w = a->adj[i].t;
+                     if (w == o.v) { t = w; a->adj.erase(a->adj.begin() + i); return true; }
+                     if (w->resc && w->resc == o.v) { t = w->resc; w->resc = nullptr; return true; }
+                 }
+                 return false;
+             }()) {}
     else throw std::runtime_error("internal: operand view is not a twin of its ciphertext");
     ct_steal(a, t);
 }
