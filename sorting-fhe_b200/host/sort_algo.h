@@ -9,6 +9,8 @@
 #include <vector>
 #include "cheb_coeffs.h"
 #include "comparison.h"
+#include <map>
+#include <mutex>
 #include "mehp24.h"
 #include "rotation.h"
 
@@ -24,6 +26,24 @@ template <int N> class SortBase {
     virtual ~SortBase() = default;
     virtual Ciphertext<DCRTPoly> sort(const Ciphertext<DCRTPoly>& input_array, SignFunc SignFunc, SignConfig& Cfg) = 0;
     virtual const Ciphertext<DCRTPoly>& getZero() const { return m_zeroCache; }
+    // `getZero()->Clone()` with SetSlots(slots) applied (reference src/sort_algo.h:330-331,433-434): one handle per slot count, made
+    // once.  Every evaluator call is out of place, so the seed itself is never written; handing out the same handle lets the engine
+    // reuse the level adjustments it caches on it (evaluator.cu adjusted_twin) instead of copying and re-adjusting 2 x 32 limbs for
+    // each of the 16 baby-step blocks of every comparison batch.
+    Ciphertext<DCRTPoly> zeroSeed(uint32_t slots) const {
+        std::lock_guard<std::mutex> g(m_seedMu);
+        auto it = m_zeroSeeds.find(slots);
+        if (it == m_zeroSeeds.end()) {
+            Ciphertext<DCRTPoly> z = getZero()->Clone();
+            z->SetSlots(slots);
+            it = m_zeroSeeds.emplace(slots, z).first;
+        }
+        return it->second;
+    }
+  private:
+    mutable std::mutex m_seedMu;
+    mutable std::map<uint32_t, Ciphertext<DCRTPoly>> m_zeroSeeds;
+  public:
     constexpr size_t getArraySize() const { return N; }
 };
 
@@ -162,8 +182,7 @@ template <int N> class DirectSort : public SortBase<N> {
     CT vecRotsOpt(const std::vector<CT>& preRotatedArrays, int num_partition, int num_slots, int np, int is) {
         std::vector<CT> outer(num_partition / np);
         for (int j = 0; j < num_partition / np; j++) {
-            CT T = this->getZero()->Clone();
-            T->SetSlots(num_slots);
+            CT T = this->zeroSeed((uint32_t)num_slots);
             std::vector<Plaintext> pmsk(np);
             for (int i = 0; i < np; i++) {
                 // the masks depend on (N, slots, block, shift) only: encoded once per context, same handle every sort
@@ -195,7 +214,7 @@ template <int N> class DirectSort : public SortBase<N> {
         std::vector<CT> babySteps(np);
         for (int i = 0; i < np; i++) { babySteps[i] = rot.rotate(input_array, i); babySteps[i]->SetSlots(num_slots); }
         CT rank;
-        if (seed) { rank = this->getZero()->Clone(); rank->SetSlots(num_slots); }
+        if (seed) rank = this->zeroSeed((uint32_t)num_slots);
         for (int i = b_lo; i < b_hi; i++) {
             CT shifted = vecRotsOpt(babySteps, num_partition, num_slots, np, i);
             CT dup = input_array->Clone();
@@ -322,8 +341,7 @@ template <int N> class DirectSort : public SortBase<N> {
                         subMask[i * array_size + j] = scaled ? row / (double)N : row;
                     }
                 return subMask; }, 1, (uint32_t)ctx_Rank->GetLevel(), (uint32_t)num_slots);
-            CT subMasked = this->getZero()->Clone();
-            subMasked->SetSlots((uint32_t)num_slots);
+            CT subMasked = this->zeroSeed((uint32_t)num_slots);
             for (size_t k = 0; k < num_batch; k++) {
                 CT rotationMask = m_cc->EvalSub(subMaskPtx, rots_Rank[k]);
                 if (kind == HybridIndicator::Mehp24)
