@@ -118,6 +118,11 @@ int ckks_eval_const_sub(ckks_ctx_t* ctx, double c, const ckks_ct_t* a, ckks_ct_t
  * take a single fused pass over HBM. */
 int ckks_eval_inner_product_plain(ckks_ctx_t* ctx, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts,
                                   int count, ckks_ct_t** out);
+/* `groups` such sums over the same ciphertexts and seed, outs[g] = init + sum_i cts[i] * pts[g * count + i]: the num_partition / np
+ * mask sets of one vecRotsOpt / blindRotationOptN call (src/sort_algo.h:331-352, 563-580).  Same limbs as `groups` single calls;
+ * the ciphertexts are read once per four outputs. */
+int ckks_eval_inner_product_plain_multi(ckks_ctx_t* ctx, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts,
+                                        int count, int groups, ckks_ct_t** outs);
 /* comparison.cpp:38 */
 int ckks_eval_negate(ckks_ctx_t* ctx, const ckks_ct_t* a, ckks_ct_t** out);
 int ckks_eval_add_many(ckks_ctx_t* ctx, const ckks_ct_t* const* cts, int count, ckks_ct_t** out); /* sort_algo.h:364 */

@@ -293,6 +293,17 @@ class Engine:
         o = ctypes.c_void_p()
         return self._out(_L.ckks_eval_inner_product_plain(_vp(self.h), _vp(init.h), a, p, len(cts), ctypes.byref(o)), o)
 
+    def EvalInnerProductPlainMulti(self, init, cts, pts_groups):
+        """[EvalInnerProductPlain(init, cts, pts) for pts in pts_groups] as one engine call (ciphertexts read once per four outputs)"""
+        flat = [p for g in pts_groups for p in g]
+        if any(len(g) != len(cts) for g in pts_groups):
+            raise ValueError("EvalInnerProductPlainMulti: size mismatch")
+        a = (ctypes.c_void_p * len(cts))(*[c.h for c in cts])
+        p = (ctypes.c_void_p * len(flat))(*[c.h for c in flat])
+        outs = (ctypes.c_void_p * len(pts_groups))()
+        _chk(_L.ckks_eval_inner_product_plain_multi(_vp(self.h), _vp(init.h), a, p, len(cts), len(pts_groups), outs))
+        return [Ciphertext(self, h) for h in outs]
+
     def EvalMult(self, a, b):
         if isinstance(b, (int, float)):
             return self._cst(_L.ckks_eval_mult_const, a, b)

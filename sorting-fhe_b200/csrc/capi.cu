@@ -382,6 +382,19 @@ int ckks_eval_inner_product_plain(ckks_ctx_t* x, const ckks_ct_t* init, const ck
     *out = box(eval_inner_product_plain(G(init), a.data(), p.data(), count));
     API_END
 }
+int ckks_eval_inner_product_plain_multi(ckks_ctx_t* x, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts,
+                                        int count, int groups, ckks_ct_t** outs) {
+    API_BEGIN Locked lk_(C(x));
+    if (count < 1 || groups < 1) throw std::runtime_error("EvalInnerProductPlainMulti: count and groups must be positive");
+    std::vector<const Ct*> a(count), p((size_t)count * groups);
+    for (int i = 0; i < count; i++) a[i] = G(cts[i]);
+    for (int i = 0; i < count * groups; i++) p[i] = G(pts[i]);
+    std::vector<Ct*> r(groups, nullptr);
+    try { eval_inner_product_plain_multi(G(init), a.data(), p.data(), count, groups, r.data()); }
+    catch (...) { for (Ct* t : r) if (t) ct_free(t); throw; }
+    for (int g = 0; g < groups; g++) outs[g] = box(r[g]);
+    API_END
+}
 int ckks_eval_add_many(ckks_ctx_t* x, const ckks_ct_t* const* cts, int count, ckks_ct_t** out) {
     API_BEGIN Locked lk_(C(x));
     if (count < 1) throw std::runtime_error("EvalAddMany: empty list");

@@ -260,6 +260,9 @@ void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* h_scala
 #define IP_MAX 15
 struct IpArgs { int cnt; const u64* init; const u64* ct[IP_MAX]; const u64* pt[IP_MAX]; int lrep[IP_MAX]; };
 void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl);
+#define IP_GROUPS 4
+struct IpMultiArgs { int cnt, groups; const u64* init; const u64* ct[IP_MAX]; const u64* pt[IP_GROUPS][IP_MAX]; int lrep[IP_GROUPS][IP_MAX]; u64* out[IP_GROUPS]; };
+void launch_ip_plain_multi(Context* c, const IpMultiArgs& A, int nl);
 void launch_mod_reduce(Context* c, u64* d, int rows, int nl);
 void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int rows, int nl);
 void launch_rescale(Context* c, u64* out, const u64* in, int parts, int nl_in, int lrep = 0);

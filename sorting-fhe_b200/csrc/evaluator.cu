@@ -554,6 +554,52 @@ Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* con
     return r;
 }
 
+// `groups` inner products over the SAME ciphertexts and accumulator seed: outs[g] = init + sum_i cts[i] * pts[g * cnt + i].
+// vecRotsOpt / blindRotationOptN mask the same np baby steps with num_partition / np different mask sets (src/sort_algo.h:331-352,
+// 563-580); one pass that keeps up to four accumulators per coefficient reads the baby steps once per four outputs instead of
+// once per output (8 x 62 limbs = 0.5 GB per read at ring 2^17).  Each output has the limbs the single call would give it; operands
+// that do not align fall back to one call per group.
+void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt, int groups, Ct** outs) {
+    Context* c = init->ctx;
+    auto fallback = [&] { for (int g = 0; g < groups; g++) outs[g] = eval_inner_product_plain(init, cts, pts + (size_t)g * cnt, cnt); };
+    bool ok = groups >= 2 && cnt >= 1 && cnt <= IP_MAX && init->parts == 2 && init->lrep == 0;
+    for (int i = 0; i < cnt && ok; i++) ok = cts[i]->parts == 2 && cts[i]->lrep == 0;
+    for (int i = 0; i < cnt * groups && ok; i++) ok = pts[i]->parts == 1;
+    if (!ok) return fallback();
+    std::vector<std::unique_ptr<Opnd>> X((size_t)cnt * groups), Y((size_t)cnt * groups);
+    for (int k = 0; k < cnt * groups; k++) {
+        X[k].reset(new Opnd(cts[k % cnt])); Y[k].reset(new Opnd(pts[k]));
+        adjust_to_one(*X[k], *Y[k]);
+    }
+    const Ct* f = X[0]->v;
+    const int nl = f->nl, L = f->level;
+    const double psf = f->sf * Y[0]->v->sf;
+    for (int k = 0; k < cnt * groups && ok; k++) {
+        const Ct *a = X[k]->v, *p = Y[k]->v;
+        ok = a == X[k % cnt]->v && a->nl == nl && a->level == L && p->nl == nl && p->level == L && a->deg + p->deg == 2 && a->sf * p->sf == psf && nl <= 64;
+    }
+    ok = ok && (init->level < L || (init->level == L && init->deg <= 2));
+    if (!ok) { X.clear(); Y.clear(); return fallback(); }
+    Ct prod{c, nullptr, 2, nl, L, 2, psf, 0};
+    Opnd T(init), P(&prod);
+    adjust_levels_and_depth(T, P);
+    if (P.v != &prod || P.own || T.v->nl != nl || T.v->level != L || T.v->deg != 2) throw std::runtime_error("EvalInnerProductPlainMulti: adjustment invariant broken");
+    int slots = init->slots;
+    for (int i = 0; i < cnt; i++) slots = std::max(slots, cts[i]->slots);
+    for (int k = 0; k < cnt * groups; k++) { ct_wait(X[k]->v); ct_wait(Y[k]->v); count(c, "mult_pt", nl); count(c, "add", nl); }
+    for (int g0 = 0; g0 < groups; g0 += IP_GROUPS) {
+        IpMultiArgs A; A.cnt = cnt; A.groups = std::min(IP_GROUPS, groups - g0); A.init = T.v->d;
+        for (int i = 0; i < cnt; i++) A.ct[i] = X[i]->v->d;
+        for (int g = 0; g < A.groups; g++) {
+            outs[g0 + g] = ct_new(c, 2, nl, L, 2, T.v->sf, slots);
+            A.out[g] = outs[g0 + g]->d;
+            for (int i = 0; i < cnt; i++) { const Ct* p = Y[(size_t)(g0 + g) * cnt + i]->v; A.pt[g][i] = p->d; A.lrep[g][i] = p->lrep; }
+            c->stats.ops[{"inner_product_fused", nl}]++;
+        }
+        launch_ip_plain_multi(c, A, nl);
+    }
+}
+
 // EvalMult(ct,ct) with relinearisation / EvalMult(ct,pt)
 Ct* eval_mult(const Ct* a, const Ct* b) {
     Context* c = a->ctx;

@@ -57,6 +57,7 @@ Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coeffs, dou
 Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_chebyshev_series(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt);
+void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt, int groups, Ct** outs);
 Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs);
 void long_division_chebyshev(const std::vector<double>& f, const std::vector<double>& g, std::vector<double>& q,
                              std::vector<double>& r);

@@ -196,6 +196,49 @@ void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl) {
     launch_pdl(c, k_ip_plain, grid_for2(c, 2 * nl), 256, 0, out, A, c->d_mod, c->n, nl);
 }
 
+// G inner products over the same ciphertexts (evaluator.cu eval_inner_product_plain_multi): every ciphertext word is loaded once
+// and multiplied into G 128-bit accumulators, each reduced exactly as k_ip_plain reduces its own.
+template <int G>
+__global__ void __launch_bounds__(256) k_ip_plain_multi(const __grid_constant__ IpMultiArgs A, const ModInfo* mi, int n, int nl) {
+    pdl_sync();
+    X2_PROLOGUE;
+    const int row = blockIdx.y, l = row % nl; const ModInfo m = mi[l];
+    const size_t o = (size_t)row * n + x;
+    const u64x2 v0 = ld2(A.init, o);
+    u64 l0[G], h0[G], l1[G], h1[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) { l0[g] = v0.x; h0[g] = 0; l1[g] = v0.y; h1[g] = 0; }
+    for (int i = 0; i < A.cnt; i++) {
+        const u64x2 a = ld2(A.ct[i], o);
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            u64x2 b;
+            const int lr = A.lrep[g][i];
+            if (lr == 0) b = ld2(A.pt[g][i], (size_t)l * n + x);
+            else { const u64 t = A.pt[g][i][(size_t)l * (n >> lr) + (x >> lr)]; b = make_ulonglong2(t, t); }
+            mac128(l0[g], h0[g], a.x, b.x); mac128(l1[g], h1[g], a.y, b.y);
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        const u64 t0 = mont_reduce(l0[g], h0[g], m.q, m.qinv), t1 = mont_reduce(l1[g], h1[g], m.q, m.qinv);
+        st2(A.out[g], o, mont_reduce(t0 * m.r2, __umul64hi(t0, m.r2), m.q, m.qinv), mont_reduce(t1 * m.r2, __umul64hi(t1, m.r2), m.q, m.qinv));
+    }
+}
+void launch_ip_plain_multi(Context* c, const IpMultiArgs& A, int nl) {
+    KL(c);
+    double pt = 0;
+    for (int g = 0; g < A.groups; g++) for (int i = 0; i < A.cnt; i++) pt += 1.0 / (1 << A.lrep[g][i]);
+    ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * nl * (2.0 * (A.cnt + 1 + A.groups) + pt));
+    const dim3 grid = grid_for2(c, 2 * nl);
+    switch (A.groups) {
+        case 1: launch_pdl(c, k_ip_plain_multi<1>, grid, 256, 0, A, c->d_mod, c->n, nl); break;
+        case 2: launch_pdl(c, k_ip_plain_multi<2>, grid, 256, 0, A, c->d_mod, c->n, nl); break;
+        case 3: launch_pdl(c, k_ip_plain_multi<3>, grid, 256, 0, A, c->d_mod, c->n, nl); break;
+        default: launch_pdl(c, k_ip_plain_multi<4>, grid, 256, 0, A, c->d_mod, c->n, nl); break;
+    }
+}
+
 // d[row][x] <- d[row][x] mod q_limb for words < 2^64: folds a multi-GPU integer sum of residues (NCCL all-reduce of the raw
 // limbs of partial ciphertexts, at most 8 addends < 2^61) back to canonical residues
 __global__ void k_mod_reduce(u64* d, const ModInfo* mi, int n, int nl) {

@@ -338,6 +338,31 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
         CT r = wrap(o);
         return r;
     }
+    // outs[g] = EvalInnerProductPlain(init, cts, pts[g]) for every mask set g, as one engine call that reads the ciphertexts once per
+    // four outputs (ckks_eval_inner_product_plain_multi)
+    std::vector<CT> EvalInnerProductPlainMulti(const CT& init, const std::vector<CT>& cts, const std::vector<std::vector<Plaintext>>& pts) const {
+        std::vector<const ckks_ct_t*> a, p;
+        for (auto& c : cts) a.push_back(c->h);
+        for (auto& g : pts) {
+            if (g.size() != cts.size()) throw std::runtime_error("EvalInnerProductPlainMulti: size mismatch");
+            for (auto& q : g) p.push_back(enc_of(q)->h);
+        }
+        // Measured on B200 (DirectSort N=128, ring 2^17): the fused multi-set pass is SLOWER than one call per set, 53.05 vs 52.64 ms
+        // per sort -- four 128-bit accumulators per coefficient make the kernel integer-issue bound (8 multiply-accumulates per
+        // 16-byte ciphertext load), while the per-set kernel streams at 80 % of the copy peak and the baby steps it re-reads
+        // mostly hit the 126 MB L2.  The per-set form is therefore the default; SORTFHE_IP_MULTI=1 selects the fused pass.
+        static const bool single = getenv("SORTFHE_IP_MULTI") == nullptr;
+        if (single) {
+            std::vector<CT> r;
+            for (auto& g : pts) r.push_back(EvalInnerProductPlain(init, cts, g));
+            return r;
+        }
+        std::vector<ckks_ct_t*> o(pts.size(), nullptr);
+        ckks_check(ckks_eval_inner_product_plain_multi(ctx, init->h, a.data(), p.data(), (int)a.size(), (int)pts.size(), o.data()), "EvalInnerProductPlainMulti");
+        std::vector<CT> r;
+        for (ckks_ct_t* h : o) r.push_back(wrap(h));
+        return r;
+    }
     // ---- multiplications (sign.cpp:23-56,100-156; comparison.cpp:19,35-38; sort_algo.h:358,576,723,730)
     CT EvalMult(const CT& a, const CT& b) const { return bin(ckks_eval_mult, a, b, "EvalMult"); }
     CT EvalMult(const CT& a, const Plaintext& p) const { return bin(ckks_eval_mult, a, enc_of(p), "EvalMult"); }

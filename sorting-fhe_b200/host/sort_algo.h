@@ -180,20 +180,20 @@ template <int N> class DirectSort : public SortBase<N> {
 
     // vecRotsOpt (:326-366): sum_j Rot_{is*P + j*np}( sum_i mask_{np*j+i} (shifted right) * babyStep_i )
     CT vecRotsOpt(const std::vector<CT>& preRotatedArrays, int num_partition, int num_slots, int np, int is) {
-        std::vector<CT> outer(num_partition / np);
-        for (int j = 0; j < num_partition / np; j++) {
-            CT T = this->zeroSeed((uint32_t)num_slots);
-            std::vector<Plaintext> pmsk(np);
+        const int nb = num_partition / np;
+        std::vector<CT> outer(nb);
+        CT seed = this->zeroSeed((uint32_t)num_slots);      // `getZero()->Clone()` + SetSlots of the reference (:330-331)
+        std::vector<std::vector<Plaintext>> pmsk(nb, std::vector<Plaintext>(np));
+        for (int j = 0; j < nb; j++)
             for (int i = 0; i < np; i++) {
                 // the masks depend on (N, slots, block, shift) only: encoded once per context, same handle every sort
                 const int k = np * j + i, shift = -is * num_partition - j * np;
-                pmsk[i] = m_cc->MakeCKKSPackedPlaintextKeyed({1, N, num_slots, k, shift},
+                pmsk[j][i] = m_cc->MakeCKKSPackedPlaintextKeyed({1, N, num_slots, k, shift},
                     [&] { return vectorRotate(generateMaskVector(num_slots, k), shift); }, 1, 0, (uint32_t)num_slots);
             }
-            // T = EvalAdd(T, EvalMult(preRotatedArrays[i], pmsk[i])) for every i (:343-344), as one engine call
-            T = m_cc->EvalInnerProductPlain(T, std::vector<CT>(preRotatedArrays.begin(), preRotatedArrays.begin() + np), pmsk);
-            outer[j] = rot.rotate(T, is * num_partition + j * np);
-        }
+        // T_j = EvalAdd(T_j, EvalMult(preRotatedArrays[i], pmsk[j][i])) for every i (:343-344), all blocks j in one engine call
+        std::vector<CT> T = m_cc->EvalInnerProductPlainMulti(seed, std::vector<CT>(preRotatedArrays.begin(), preRotatedArrays.begin() + np), pmsk);
+        for (int j = 0; j < nb; j++) outer[j] = rot.rotate(T[j], is * num_partition + j * np);
         return m_cc->EvalAddMany(outer);
     }
 
@@ -236,18 +236,18 @@ template <int N> class DirectSort : public SortBase<N> {
     // blindRotationOptN (:561-584)
     CT blindRotationOptN(const std::vector<CT>& masked_inputs, int num_slots, int np, int ib, int num_partition) {
         CT result = this->getZero()->Clone();
-        for (int i = 0; i < (num_slots / N) / np; i++) {
-            CT tmp = this->getZero()->Clone();
-            std::vector<Plaintext> pmsk(np);
+        const int nb = (num_slots / N) / np;
+        std::vector<std::vector<Plaintext>> pmsk(nb, std::vector<Plaintext>(np));
+        for (int i = 0; i < nb; i++)
             for (int j = 0; j < np; j++) {
                 const int k = np * i + j;
-                pmsk[j] = m_cc->MakeCKKSPackedPlaintextKeyed({2, N, num_slots, k, j},
+                pmsk[i][j] = m_cc->MakeCKKSPackedPlaintextKeyed({2, N, num_slots, k, j},
                     [&] { return vectorRotate(generateMaskVectorN(num_slots, k), j); }, 1, (uint32_t)masked_inputs[j]->GetLevel(), (uint32_t)num_slots);
             }
-            tmp = m_cc->EvalInnerProductPlain(tmp, std::vector<CT>(masked_inputs.begin(), masked_inputs.begin() + np), pmsk);   // (:575-576)
-            tmp = rot.rotate(tmp, ib * num_partition + i * np);
-            m_cc->EvalAddInPlace(result, tmp);
-        }
+        // tmp_i = zero + sum_j masked_inputs[j] * pmsk[i][j] (:575-576) for every block i in one engine call
+        std::vector<CT> tmp = m_cc->EvalInnerProductPlainMulti(this->getZero(), std::vector<CT>(masked_inputs.begin(), masked_inputs.begin() + np), pmsk);
+        for (int i = 0; i < nb; i++)
+            m_cc->EvalAddInPlace(result, rot.rotate(tmp[i], ib * num_partition + i * np));
         return result;
     }
 

@@ -190,3 +190,42 @@ def test_inner_product_plain_bit_exact(pair12):
     for c, p in zip(sq_o, pos):
         want = orc.EvalAdd(want, orc.EvalMult(c, p))
     same(eng.EvalInnerProductPlain(ze, sq_e, pes), want)
+
+
+def test_inner_product_plain_multi_bit_exact(pair12):
+    """ckks_eval_inner_product_plain_multi (all mask sets of one vecRotsOpt / blindRotationOptN call, src/sort_algo.h:331-352,
+    563-580): every output equals the oracle's EvalAdd(T, EvalMult(ct, pt)) chain for its own mask set, for 1..6 sets (one to
+    two kernel passes of at most four accumulators), compact and full-length plaintexts, and through the per-set fallback"""
+    eng, orc = pair12
+    rng = np.random.default_rng(11)
+    xs = [rng.uniform(-1, 1, 8) for _ in range(3)]
+    cos = [orc.encrypt(orc.encode(x, slots=8)) for x in xs]
+    ces = [eng.import_ct(c.d, c.level, c.deg, c.sf, c.slots) for c in cos]
+    zo = orc.encrypt(orc.encode(np.zeros(8), slots=8))
+    ze = eng.import_ct(zo.d, zo.level, zo.deg, zo.sf, zo.slots)
+
+    def chain(cts, pts):
+        want = zo
+        for c, p in zip(cts, pts):
+            want = orc.EvalAdd(want, orc.EvalMult(c, p))
+        return want
+
+    for slots, groups in ((8, 1), (8, 2), (64, 3), (eng.n // 2, 4), (64, 6)):
+        ms = [[rng.integers(0, 2, slots).astype(np.float64) for _ in range(3)] for _ in range(groups)]
+        pos = [[orc.MakeCKKSPackedPlaintext(m, 1, 0, None, slots) for m in g] for g in ms]
+        pes = [[eng.MakeCKKSPackedPlaintext(m, 1, 0, None, slots) for m in g] for g in ms]
+        outs = eng.EvalInnerProductPlainMulti(ze, ces, pes)
+        assert len(outs) == groups
+        for g in range(groups):
+            same(outs[g], chain(cos, pos[g]))
+    # noiseScaleDeg-2 ciphertexts are rescaled through their cached twins first; still one fused pass per four sets
+    sq_o = [orc.EvalMult(c, c) for c in cos]
+    sq_e = [eng.EvalMult(c, c) for c in ces]
+    ms = [[rng.integers(0, 2, 8).astype(np.float64) for _ in range(3)] for _ in range(2)]
+    pos = [[orc.MakeCKKSPackedPlaintext(m, 1, 0, None, 8) for m in g] for g in ms]
+    pes = [[eng.MakeCKKSPackedPlaintext(m, 1, 0, None, 8) for m in g] for g in ms]
+    outs = eng.EvalInnerProductPlainMulti(ze, sq_e, pes)
+    for g in range(2):
+        same(outs[g], chain(sq_o, pos[g]))
+    with pytest.raises(ValueError):
+        eng.EvalInnerProductPlainMulti(ze, ces, [pes[0][:2]])
