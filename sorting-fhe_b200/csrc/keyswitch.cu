@@ -198,6 +198,14 @@ __device__ __forceinline__ double cv_mulmod(double a, double w, double q, double
     return __dadd_rn(__fma_rn(-qh, q, h), l);
 }
 struct ConvOut { double q, qinv, w2, w3; u64 qi, qinv64; int narrow, pad; };   // 56 bytes -> padded to 64
+#ifndef CONV_FOLD
+// 1: two-column epilogue for narrow targets (constants C_k = Qhat_i 2^(21k) mod t per input piece, one modular product per output
+// instead of three; see narrow_out).  Measured on B200 and left OFF: key switch 507.8 vs 499.3 us at l = 32, base-conversion class
+// 9.88 vs 9.36 ms and 55.2-56.2 vs 52.6 ms per DirectSort N=128 sort (tools/build_variant.sh fold "-DCONV_FOLD=1" keyswitch) -- the
+// per-CTA staging of the piece constants (two modular products per table entry ahead of the barrier) costs more than the 14 FP64
+// instructions per output it saves.
+#define CONV_FOLD 0
+#endif
 #ifndef CONV_UNROLL
 #define CONV_UNROLL 1   /* 2 (two outputs in flight) measured 1 % slower at l = 32: 511.8 vs 506.0 us per key switch */
 #endif
@@ -212,7 +220,12 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
     const int nin = B.g[gi].nin, nout = B.g[gi].nout;
     const int per = (nout + ysplit - 1) / ysplit, jlo = part * per, jc = min(per, nout - jlo);
     if (jc <= 0) return;
+#if CONV_FOLD
+    double2* sh_x = reinterpret_cast<double2*>(sh_k + (size_t)per * NI);   // [jc][NI] third-piece constants of narrow targets
+    ConvOut* sh_o = reinterpret_cast<ConvOut*>(sh_x + (size_t)per * NI);
+#else
     ConvOut* sh_o = reinterpret_cast<ConvOut*>(sh_k + (size_t)per * NI);
+#endif
     for (int t = threadIdx.x; t < jc; t += blockDim.x) {
         const ModInfo m = mi[B.out_ids[gi][jlo + t]];
         ConvOut o;
@@ -223,10 +236,26 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
     }
     for (int t = threadIdx.x; t < NI * jc; t += blockDim.x) {
         const int jj = t / NI, i = t - jj * NI;
-        const bool narrow = mi[B.out_ids[gi][jlo + jj]].bits <= 42;
+        const ModInfo mo = mi[B.out_ids[gi][jlo + jj]];
+        const bool narrow = mo.bits <= 42;
         const u64* tab = narrow ? B.g[gi].hatplain : B.g[gi].hatmod;
         const u64 h = i < nin ? tab[(size_t)i * nout + jlo + jj] : 0;
+#if CONV_FOLD
+        if (narrow) {
+            // C_k = Qhat_i 2^(21 k) mod t for the three input pieces k, each cut into its low and high 21 bits (see narrow_out)
+            const double q = (double)mo.q, qinv = __drcp_rn(q);
+            double h1 = cv_mulmod((double)h, 2097152.0, q, qinv); if (h1 < 0.0) h1 = __dadd_rn(h1, q);
+            double h2 = cv_mulmod(h1, 2097152.0, q, qinv); if (h2 < 0.0) h2 = __dadd_rn(h2, q);
+            const u64 u1 = column_to_u64(h1), u2 = column_to_u64(h2);
+            sh_k[t] = make_double4((double)((u32)h & 0x1FFFFFu), (double)(u32)(h >> 21), (double)((u32)u1 & 0x1FFFFFu), (double)(u32)(u1 >> 21));
+            sh_x[t] = make_double2((double)((u32)u2 & 0x1FFFFFu), (double)(u32)(u2 >> 21));
+        } else {
+            sh_k[t] = make_double4((double)((u32)h & 0x1FFFFFu), (double)((u32)(h >> 21) & 0x1FFFFFu), (double)(u32)(h >> 42), 0.0);
+            sh_x[t] = make_double2(0.0, 0.0);
+        }
+#else
         sh_k[t] = make_double4((double)((u32)h & 0x1FFFFFu), (double)((u32)(h >> 21) & 0x1FFFFFu), (double)(u32)(h >> 42), 0.0);
+#endif
     }
     __syncthreads();
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -245,6 +274,32 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
     // Outputs come in at most three runs of one kind (q0, the other Q limbs, the P limbs); each run is a branch-free loop.
     // The sums are exact integers below 2^53: splitting the middle columns into two accumulators changes nothing but the
     // dependency chains (the ncu capture of round 2 had fixed-latency dependency waits as the top stall of this kernel).
+#if CONV_FOLD
+    // Narrow targets (t <= 42 bits).  Writing x_i = sum_k y_k[i] 2^(21 k), the output is sum_i sum_k y_k[i] C_k[i] mod t with
+    // C_k[i] = Qhat_i 2^(21 k) mod t = C_k0 + C_k1 2^21: TWO exact column sums S0 = sum y_k C_k0, S1 = sum y_k C_k1 (at most
+    // 3 x 12 terms below 2^42 each) and out = S0 + S1 2^21 mod t -- one floating-point modular product in the epilogue instead of
+    // the three that the weight-ordered columns s0..s3 of k_conv_fp need (27 -> 13 FP64 instructions per output, the contraction's
+    // 2 FMAs per piece unchanged).  Same residue, bit for bit.
+    auto narrow_out = [&](const int jj) {
+        const double4* hp = sh_k + jj * NI;
+        const double2* hx = sh_x + jj * NI;
+        const ConvOut o = sh_o[jj];
+        double s0 = 0.0, s0b = 0.0, s1 = 0.0, s1b = 0.0;
+#pragma unroll
+        for (int i = 0; i < NI; i++) {
+            const double4 c = hp[i];
+            s0 = __fma_rn(y0[i], c.x, s0); s1 = __fma_rn(y0[i], c.y, s1);
+            s0b = __fma_rn(y1[i], c.z, s0b); s1b = __fma_rn(y1[i], c.w, s1b);
+            if (WMODE == 2 || (WMODE == 1 && i == 0)) { const double2 e = hx[i]; s0 = __fma_rn(y2[i], e.x, s0); s1 = __fma_rn(y2[i], e.y, s1); }
+        }
+        s0 = __dadd_rn(s0, s0b); s1 = __dadd_rn(s1, s1b);
+        double r = __dadd_rn(s0, cv_mulmod(s1, 2097152.0, o.q, o.qinv));
+        const double t = __dadd_rn(__fma_rn(r, o.qinv, CV_MAGIC), -CV_MAGIC);
+        r = __fma_rn(-t, o.q, r);
+        if (r < 0.0) r = __dadd_rn(r, o.q);
+        dst[(size_t)jj * n] = column_to_u64(r);
+    };
+#else
     auto narrow_out = [&](const int jj) {
         const double4* hp = sh_k + jj * NI;
         const ConvOut o = sh_o[jj];
@@ -265,6 +320,7 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
         if (r < 0.0) r = __dadd_rn(r, o.q);
         dst[(size_t)jj * n] = column_to_u64(r);
     };
+#endif
     auto wide_out = [&](const int jj) {
         const double4* hp = sh_k + jj * NI;
         const ConvOut o = sh_o[jj];
@@ -300,7 +356,7 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
 }
 template <int NI>
 static void launch_conv_fp2(Context* c, dim3 grid, int per, int wmode, u64* out, const u64* in, const ConvBatch& B, int ysplit) {
-    const size_t smem = (size_t)NI * per * sizeof(double4) + (size_t)per * sizeof(ConvOut);
+    const size_t smem = (size_t)NI * per * (sizeof(double4) + (CONV_FOLD ? sizeof(double2) : 0)) + (size_t)per * sizeof(ConvOut);
     if (wmode == 0) launch_pdl(c, k_conv_fp2<NI, 0>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
     else if (wmode == 1) launch_pdl(c, k_conv_fp2<NI, 1>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
     else launch_pdl(c, k_conv_fp2<NI, 2>, grid, 256, smem, out, in, B, c->d_mod, c->n, ysplit);
