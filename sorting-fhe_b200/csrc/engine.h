@@ -312,6 +312,10 @@ struct HostTimer {   // accumulates host wall time of a CUDA API call class when
     }
 };
 #ifdef __CUDACC__
+// The two halves on their own: a kernel whose prologue only reads context tables (written at set-up, never by a kernel of the
+// stream) can run it between pdl_trigger() and pdl_wait(), i.e. while its predecessor is still draining.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_sync() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");

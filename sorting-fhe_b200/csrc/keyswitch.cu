@@ -214,7 +214,7 @@ template <int NI, int WMODE>
 __global__ void __launch_bounds__(256)
 k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_constant__ ConvBatch B, const ModInfo* __restrict__ mi, int n,
            int ysplit) {
-    pdl_sync();
+    pdl_trigger();   // the constants below come from context tables: staged while the producer of `in` is still running
     extern __shared__ double4 sh_k[];                     // [jc][NI] (c0, c1, c2, -) then [jc] ConvOut
     const int gi = blockIdx.y / ysplit, part = blockIdx.y - gi * ysplit;
     const int nin = B.g[gi].nin, nout = B.g[gi].nout;
@@ -258,6 +258,7 @@ k_conv_fp2(u64* __restrict__ out, const u64* __restrict__ in, const __grid_const
 #endif
     }
     __syncthreads();
+    pdl_wait();
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= n) return;
     constexpr int NW = WMODE == 2 ? NI : 1;

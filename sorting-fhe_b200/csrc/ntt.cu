@@ -292,15 +292,6 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
     // position of tile-local bit 0 in the element index, and the index bits above the tile
     // pass B: E = tile << T | L.   pass A: E = (row bits = L >> cb) << T | (tile << cb | col): stages only touch
     // the row bits, whose position in E is T + (bit - cb).
-    if (!strided) {
-        // pass B touches, per local stage sl, the contiguous run W[2^(a+sl) + tile 2^sl + [0, 2^sl)) exactly once: pull
-        // all of it (2^T - 1 pairs, one 128-byte line per prefetch) into L1 now so that no round waits on DRAM
-        for (int sl = 3; sl < T; sl++) {
-            const tw_t* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
-            for (int g = u * 8; g < (1 << sl); g += 8 * (1 << (T - 3)))
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
-        }
-    }
     u64 r[8];
     int t_done = 0;   // inverse: number of GS stages already applied to the data (for the lazy offset)
     if (INV) t_done = strided ? T : 0;
@@ -520,15 +511,6 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
     auto gaddr = [&](int L) -> size_t {
         return strided ? (((size_t)(L >> cb) << T) | (size_t)((tile << cb) | (L & ((1 << cb) - 1)))) : (((size_t)tile << T) | (size_t)L);
     };
-    if (!strided) {
-        const bool ot = A.twb && A.twlog == logn && T >= 3;
-        if (ot && u * 16 < (1 << (T - 3))) asm volatile("prefetch.global.L1 [%0];" ::"l"(A.twb + ((size_t)mid << (A.twlog - 3)) + ((size_t)tile << (T - 3)) + u * 16));
-        for (int sl = 3; sl < (ot ? T - 3 : T); sl++) {   // pull this tile's twiddles (2^T - 1 doubles) into L1, one 128-byte line per prefetch
-            const double* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
-            for (int g = u * 16; g < (1 << sl); g += 16 * (1 << (T - 3)))
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
-        }
-    }
     double r[8];
     const int nr = LOGN_C ? SC.nr : SR.nr;
 #pragma unroll
@@ -607,6 +589,35 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
     }
 }
 
+// Pass B touches, per local stage sl, the contiguous run W[2^(a+sl) + tile 2^sl + [0, 2^sl)) of its row's twiddles exactly once:
+// pull all of it (2^T - 1 entries, one 128-byte line per prefetch) into L1 ahead of the rounds.  The tables are written at context
+// set-up, so the kernel issues these BEFORE griddepcontrol.wait, while its predecessor is still draining.
+template <int LOGN_C, int PASS_C>
+__device__ __forceinline__ void prefetch_twiddles(const NttArgs& A, const NttRows& R, const int row, const int tile) {
+    constexpr int TC = LOGN_C < TB_MAX ? LOGN_C : TB_MAX;
+    const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? TC : A.T, a_ = LOGN_C ? LOGN_C - TC : A.a;
+    const bool strided = LOGN_C ? (PASS_C == 0) : (A.pass == 0);
+    if (strided) return;
+    const int mid = R.mid[row], u = threadIdx.x;
+    if (R.kind[row] == ROW_FP) {
+        const double* W = A.twd + ((size_t)mid << A.twlog);
+        const bool ot = A.twb && A.twlog == logn && T >= 3;
+        if (ot && u * 16 < (1 << (T - 3))) asm volatile("prefetch.global.L1 [%0];" ::"l"(A.twb + ((size_t)mid << (A.twlog - 3)) + ((size_t)tile << (T - 3)) + u * 16));
+        for (int sl = 3; sl < (ot ? T - 3 : T); sl++) {
+            const double* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
+            for (int g = u * 16; g < (1 << sl); g += 16 * (1 << (T - 3)))
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
+        }
+    } else {
+        const tw_t* W = A.tw + ((size_t)mid << A.twlog);
+        for (int sl = 3; sl < T; sl++) {
+            const tw_t* base = W + ((size_t)1 << (a_ + sl)) + ((size_t)tile << sl);
+            for (int g = u * 8; g < (1 << sl); g += 8 * (1 << (T - 3)))
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(base + g));
+        }
+    }
+}
+
 // first-round words of tile `tile` of limb row `row` (the same index pattern for the integer and the FP64 path)
 template <bool INV, int LOGN_C, int PASS_C>
 __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile, u64 (&v)[8]) {
@@ -634,15 +645,15 @@ template <bool INV, int LOGN_C, int PASS_C>
 __global__ void __launch_bounds__((1 << TB_MAX) / 8 > 256 ? (1 << TB_MAX) / 8 : 256, TB_MAX >= 12 ? 2 : 4)
 ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ NttRows R, int total,
            int tpr_log) {
-    pdl_sync();
+    pdl_trigger();
     extern __shared__ u64 sm[];
     const int id = blockIdx.x;
     if (id >= total) return;
     const int row = id >> tpr_log, tile = id & ((1 << tpr_log) - 1);
-    u64 v[8];
-    load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
+    prefetch_twiddles<LOGN_C, PASS_C>(A, R, row, tile);
     if (!INV && A.f.epi != EPI_NONE && A.final_pass && (LOGN_C ? PASS_C == 1 : A.pass == 1)) {
-        // the fused epilogue reads its minuend (and addend) tile only after the last round: pull the lines into L2/L1 now, the
+        // the fused epilogue reads its minuend (and addend) tile only after the last round: pull the lines into L2 now (they were written
+        // before this transform's first pass, so this too happens ahead of griddepcontrol.wait), the
         // ncu capture of round 2 had long-scoreboard on those loads as the top stall of the ModDown NTT (profiles/r02_ks_kernels_ncu_summary.txt)
         const int logn = LOGN_C ? LOGN_C : A.logn, T = LOGN_C ? (LOGN_C < TB_MAX ? LOGN_C : TB_MAX) : A.T;
         const int lines = (1 << T) / 16;                       // 128-byte lines of one tile
@@ -655,6 +666,9 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
             }
         }
     }
+    pdl_wait();
+    u64 v[8];
+    load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
     const int kind = R.kind[row];
     if (kind == ROW_FP) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
     else if (kind == ROW_INT_FIX) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
