@@ -556,8 +556,8 @@ Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* con
 
 // `groups` inner products over the SAME ciphertexts and accumulator seed: outs[g] = init + sum_i cts[i] * pts[g * cnt + i].
 // vecRotsOpt / blindRotationOptN mask the same np baby steps with num_partition / np different mask sets (src/sort_algo.h:331-352,
-// 563-580); one pass that keeps up to four accumulators per coefficient reads the baby steps once per four outputs instead of
-// once per output (8 x 62 limbs = 0.5 GB per read at ring 2^17).  Each output has the limbs the single call would give it; operands
+// 563-580); one pass that keeps several accumulators per coefficient reads the baby steps once per pass instead of once per
+// output (8 x 62 limbs = 0.5 GB per read at ring 2^17).  Each output has the limbs the single call would give it; operands
 // that do not align fall back to one call per group.
 void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt, int groups, Ct** outs) {
     Context* c = init->ctx;
@@ -587,8 +587,12 @@ void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const 
     int slots = init->slots;
     for (int i = 0; i < cnt; i++) slots = std::max(slots, cts[i]->slots);
     for (int k = 0; k < cnt * groups; k++) { ct_wait(X[k]->v); ct_wait(Y[k]->v); count(c, "mult_pt", nl); count(c, "add", nl); }
-    for (int g0 = 0; g0 < groups; g0 += IP_GROUPS) {
-        IpMultiArgs A; A.cnt = cnt; A.groups = std::min(IP_GROUPS, groups - g0); A.init = T.v->d;
+    // accumulators per pass: two is the measured optimum on B200 (DirectSort N=128 per sort: 51.98 ms with one call per set, 51.76 /
+    // 51.49 / 51.65 / 52.20 ms with 1 / 2 / 3 / 4 sets per pass) -- the 128-bit multiply-accumulates make the kernel integer-issue
+    // bound beyond two, below two the baby steps are re-read once per set
+    static const int chunk = getenv("CKKS_B200_IP_GROUPS") ? std::max(1, std::min(IP_GROUPS, atoi(getenv("CKKS_B200_IP_GROUPS")))) : 2;
+    for (int g0 = 0; g0 < groups; g0 += chunk) {
+        IpMultiArgs A; A.cnt = cnt; A.groups = std::min(chunk, groups - g0); A.init = T.v->d;
         for (int i = 0; i < cnt; i++) A.ct[i] = X[i]->v->d;
         for (int g = 0; g < A.groups; g++) {
             outs[g0 + g] = ct_new(c, 2, nl, L, 2, T.v->sf, slots);

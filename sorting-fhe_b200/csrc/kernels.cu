@@ -53,9 +53,10 @@ void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m)
 }
 
 __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b, int lrep_b) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     int row = blockIdx.y; const ModInfo m = mi[mods.m[row % mods.n]];
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)row * n + x;
     const u64x2 va = ld2(a, o);
     u64x2 vb;
@@ -69,9 +70,10 @@ void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, 
 }
 
 __global__ void k_mul_scalar(u64* out, const u64* d, LimbMods mods, const ModInfo* mi, int n, LimbScalars s) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     int row = blockIdx.y, l = row % mods.n; u64 q = mi[mods.m[l]].q;
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)row * n + x;
     const u64x2 v = ld2(d, o);
     st2(out, o, shoup_mul(v.x, s.v[l], s.sh[l], q), shoup_mul(v.y, s.v[l], s.sh[l], q));
@@ -85,9 +87,10 @@ void launch_mul_scalar(Context* c, u64* out, const u64* data, int rows, const Li
 }
 
 __global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, int nl, LimbScalars s, int negate) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     int row = blockIdx.y, l = row % nl; u64 q = mi[l].q;
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)row * n + x;
     u64x2 v = ld2(d, o);
     if (negate) { v.x = neg_mod(v.x, q); v.y = neg_mod(v.y, q); }
@@ -103,9 +106,10 @@ void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, c
 
 __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
                                int sub, int lrx, int lry) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     int row = blockIdx.y, p = row / nl; u64 q = mi[row % nl].q;
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)row * n + x;
     const u64x2 z = make_ulonglong2(0, 0);
     u64x2 a = z, b = z;
@@ -135,9 +139,10 @@ void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep) 
 #define WSUM_MAX_PAIRS 640
 struct WsumArgs { int cnt, acc; const u64* in[WSUM_MAX_IN]; u64 pairs[WSUM_MAX_PAIRS][2]; };   // passed by value (<= 32 KB of parameters)
 __global__ void k_wsum(u64* out, const __grid_constant__ WsumArgs A, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     const int row = blockIdx.y, l = row % nl; const u64 q = mi[l].q;
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     u64 r0 = 0, r1 = 0;
     if (A.acc) { const u64x2 v = ld2(out, o); r0 = v.x; r1 = v.y; }
@@ -173,9 +178,10 @@ void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* hs, int
 // accumulator (<= 16 terms of q^2 < q * 2^64 for q < 2^60), reduced once.  Modular addition and multiplication are
 // exact, so the result equals the chain's bit for bit.
 __global__ void k_ip_plain(u64* out, const __grid_constant__ IpArgs A, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     const int row = blockIdx.y, l = row % nl; const ModInfo m = mi[l];
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     const u64x2 v0 = ld2(A.init, o);
     u64 l0 = v0.x, h0 = 0, l1 = v0.y, h1 = 0;
@@ -200,9 +206,10 @@ void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl) {
 // and multiplied into G 128-bit accumulators, each reduced exactly as k_ip_plain reduces its own.
 template <int G>
 __global__ void __launch_bounds__(256) k_ip_plain_multi(const __grid_constant__ IpMultiArgs A, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     const int row = blockIdx.y, l = row % nl; const ModInfo m = mi[l];
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     const u64x2 v0 = ld2(A.init, o);
     u64 l0[G], h0[G], l1[G], h1[G];
@@ -242,9 +249,10 @@ void launch_ip_plain_multi(Context* c, const IpMultiArgs& A, int nl) {
 // d[row][x] <- d[row][x] mod q_limb for words < 2^64: folds a multi-GPU integer sum of residues (NCCL all-reduce of the raw
 // limbs of partial ciphertexts, at most 8 addends < 2^61) back to canonical residues
 __global__ void k_mod_reduce(u64* d, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     const int row = blockIdx.y; const ModInfo m = mi[row % nl];
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     u64x2 v = ld2(d, o);
     v.x -= __umul64hi(v.x, m.qrecip) * m.q; if (v.x >= m.q) v.x -= m.q;
@@ -259,9 +267,10 @@ void launch_mod_reduce(Context* c, u64* d, int rows, int nl) {
 // out[row] = sum_i in_i[row]  (EvalAddMany)
 struct ManyArgs { int cnt; const u64* in[32]; };
 __global__ void k_add_many(u64* out, const ManyArgs A, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     const int row = blockIdx.y; const u64 q = mi[row % nl].q;
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     u64x2 r = ld2(A.in[0], o);
     for (int i = 1; i < A.cnt; i++) { const u64x2 v = ld2(A.in[i], o); r.x = add_mod(r.x, v.x, q); r.y = add_mod(r.y, v.y, q); }
@@ -276,9 +285,10 @@ void launch_add_many(Context* c, u64* out, const u64* const* ins, int cnt, int r
 
 // (a0,a1) x (b0,b1) -> (a0b0, a0b1 + a1b0, a1b1), one pass over the four inputs
 __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi, int n, int nl) {
-    pdl_sync();
+    pdl_trigger();
     X2_PROLOGUE;
     int l = blockIdx.y; const ModInfo m = mi[l];
+    pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)l * n + x, P = (size_t)nl * n;
     const u64x2 a0 = ld2(a, o), a1 = ld2(a, o + P), b0 = ld2(b, o), b1 = ld2(b, o + P);
     st2(d3, o, barrett_mul(a0.x, b0.x, m), barrett_mul(a0.y, b0.y, m));

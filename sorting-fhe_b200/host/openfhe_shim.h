@@ -339,7 +339,7 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
         return r;
     }
     // outs[g] = EvalInnerProductPlain(init, cts, pts[g]) for every mask set g, as one engine call that reads the ciphertexts once per
-    // four outputs (ckks_eval_inner_product_plain_multi)
+    // pass of two outputs (ckks_eval_inner_product_plain_multi)
     std::vector<CT> EvalInnerProductPlainMulti(const CT& init, const std::vector<CT>& cts, const std::vector<std::vector<Plaintext>>& pts) const {
         std::vector<const ckks_ct_t*> a, p;
         for (auto& c : cts) a.push_back(c->h);
@@ -347,11 +347,9 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
             if (g.size() != cts.size()) throw std::runtime_error("EvalInnerProductPlainMulti: size mismatch");
             for (auto& q : g) p.push_back(enc_of(q)->h);
         }
-        // Measured on B200 (DirectSort N=128, ring 2^17): the fused multi-set pass is SLOWER than one call per set, 53.05 vs 52.64 ms
-        // per sort -- four 128-bit accumulators per coefficient make the kernel integer-issue bound (8 multiply-accumulates per
-        // 16-byte ciphertext load), while the per-set kernel streams at 80 % of the copy peak and the baby steps it re-reads
-        // mostly hit the 126 MB L2.  The per-set form is therefore the default; SORTFHE_IP_MULTI=1 selects the fused pass.
-        static const bool single = getenv("SORTFHE_IP_MULTI") == nullptr;
+        // SORTFHE_NO_IP_MULTI=1: one engine call per mask set (A/B; 51.98 vs 51.49 ms per DirectSort N=128 sort on B200 with the
+        // engine's default of two sets per pass)
+        static const bool single = getenv("SORTFHE_NO_IP_MULTI") != nullptr;
         if (single) {
             std::vector<CT> r;
             for (auto& g : pts) r.push_back(EvalInnerProductPlain(init, cts, g));
