@@ -399,6 +399,11 @@ __device__ __forceinline__ double fp_reduce(double x, double q, double qinv) {  
     const double t = __dadd_rn(__fma_rn(x, qinv, FP_MAGIC), -FP_MAGIC);
     return __fma_rn(-t, q, x);
 }
+// canonical residue of an already reduced value, |y| < q (fp_mulmod returns |y| <= q/2 (1 + 2^-8) + 2^31 for lazy operands)
+__device__ __forceinline__ u64 fp_canon_reduced(double y, double q) {
+    if (y < 0.0) y = __dadd_rn(y, q);
+    return fp_to_u64(y);
+}
 __device__ __forceinline__ u64 fp_canon(double x, double q, double qinv) {
     double y = fp_reduce(x, q, qinv);
     if (y < 0.0) y = __dadd_rn(y, q);
@@ -569,7 +574,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
             } else {
                 const double sc = (double)A.scale[mid].x;
 #pragma unroll
-                for (int k = 0; k < 8; k++) v[k] = fp_canon(fp_mulmod(r[k], sc, q, qinv), q, qinv);
+                for (int k = 0; k < 8; k++) v[k] = fp_canon_reduced(fp_mulmod(r[k], sc, q, qinv), q);   // the product is reduced already
             }
             if (!strided && p == 0) store8(dst + gaddr(local_index(u, 0, 0)), v);
             else {
@@ -726,7 +731,8 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     if (fuse) A.f = *fuse; else A.f = NttFuse{};
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
     A.twd = inverse ? c->d_itwd : c->d_twd;
-    A.twb = inverse ? c->d_itwb : c->d_twb;
+    static const bool no_ot = getenv("CKKS_B200_NTT_NO_OT") != nullptr;   // A/B switch: last round's twiddles from the table
+    A.twb = no_ot ? nullptr : (inverse ? c->d_itwb : c->d_twb);
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
     for (int r0 = 0; r0 < rows; r0 += NTT_MAX_ROWS) {
         const int cnt = rows - r0 < NTT_MAX_ROWS ? rows - r0 : NTT_MAX_ROWS, total = cnt << tpr_log;
