@@ -229,3 +229,39 @@ def test_inner_product_plain_multi_bit_exact(pair12):
         same(outs[g], chain(sq_o, pos[g]))
     with pytest.raises(ValueError):
         eng.EvalInnerProductPlainMulti(ze, ces, [pes[0][:2]])
+
+
+def test_clone_is_copy_on_write_and_adjusted_twins_bit_exact(pair12):
+    """ckks_ct_clone shares the source's limbs until SetSlots / ckks_ct_mod_reduce / ckks_ct_device_ptr is applied to one of the
+    handles (capi.cu); the level adjustment of two depth-2 operands at different levels (scaled rescale, cached as an adjusted twin
+    on the shallower handle) gives the oracle's limbs on the first use, on the cached second use, through a clone, and after the
+    source handle has been freed"""
+    eng, orc = pair12
+    rng = np.random.default_rng(21)
+    xs = [rng.uniform(-1, 1, 8) for _ in range(3)]
+    cos = [orc.encrypt(orc.encode(x, slots=8)) for x in xs]
+    ces = [eng.import_ct(c.d, c.level, c.deg, c.sf, c.slots) for c in cos]
+    # shallow = depth-2 product at the top; deep = the same kind of product three levels further down
+    sh_o, sh_e = orc.EvalMult(cos[0], cos[1]), eng.EvalMult(ces[0], ces[1])
+    d_o, d_e = cos[2], ces[2]
+    for _ in range(3):
+        d_o, d_e = orc.EvalMult(d_o, d_o), eng.EvalMult(d_e, d_e)
+    assert sh_e.deg == 2 and d_e.deg == 2 and d_e.level > sh_e.level + 1
+    want = orc.EvalAdd(sh_o, d_o)
+    same(eng.EvalAdd(sh_e, d_e), want)                       # first use: scaled rescale + level drop in one step
+    same(eng.EvalAdd(sh_e, d_e), want)                       # cached adjusted twin
+    cl = sh_e.clone()
+    same(eng.EvalAdd(cl, d_e), want)                         # the clone shares limbs and twins
+    before = sh_e.export().copy()
+    cl.slots = 4                                             # unshares the clone only
+    assert sh_e.slots == 8 and cl.slots == 4
+    ptr, words = eng.ct_device_ptr(cl)
+    ptr0, _ = eng.ct_device_ptr(sh_e)
+    assert ptr != ptr0
+    cl2 = sh_e.clone()
+    eng.ct_mod_reduce(cl2)                                   # in-place entry point on a shared handle: works on a private copy
+    assert np.array_equal(sh_e.export(), before) and np.array_equal(cl2.export(), before)
+    del sh_e                                                 # the clone keeps its own data alive
+    eng.sync()
+    assert np.array_equal(cl.export(), before)
+    same(eng.EvalAdd(cl2, d_e), want)
