@@ -646,7 +646,12 @@ __device__ __forceinline__ void load_tile(const NttArgs& A, const Sched& SR, con
 // One CTA per work item id -> (row = id / tiles_per_row, tile = id % tiles_per_row).  (A persistent variant that
 // prefetched the next tile's words into registers was measured slower on B200: 80 registers cut the resident CTAs
 // from 4 to 3 per SM and 2048 tiles over 444 CTAs quantise badly -- 65 us vs 56 us for a 32-limb 2^17 transform.)
-template <bool INV, int LOGN_C, int PASS_C>
+// KM: which butterfly paths the instantiation contains (bit 0 FP64, bit 1 integer, bit 2 integer with folds).  A launch whose rows
+// are all of one kind (the special-prime rows of a ModUp at <= alpha limbs, the ModDown INTT, the rescale INTT of a 40-bit limb)
+// runs a kernel a third of the size: the round-3 ncu source page of the mixed kernel has instruction fetch (no_instruction) as the
+// top stall of sub-wave forward integer launches, 35-44 % of the warp samples, concentrated where the 97 KB kernel jumps to the
+// integer path (profiles/r03_ks8_ntt_ncu_summary.txt).
+template <bool INV, int LOGN_C, int PASS_C, int KM>
 __global__ void __launch_bounds__((1 << TB_MAX) / 8 > 256 ? (1 << TB_MAX) / 8 : 256, TB_MAX >= 12 ? 2 : 4)
 ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, const __grid_constant__ NttRows R, int total,
            int tpr_log) {
@@ -675,14 +680,20 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
     u64 v[8];
     load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
     const int kind = R.kind[row];
-    if (kind == ROW_FP) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
-    else if (kind == ROW_INT_FIX) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
-    else ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    if (KM == 1 || ((KM & 1) && kind == ROW_FP)) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    else if (KM == 4 || ((KM & 4) && kind == ROW_INT_FIX)) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    else if (KM & 2) ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
 }
 
 template <bool INV, int LOGN_C, int PASS_C>
 static void launch_one(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
-    launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C>, total, threads, smem, A, S, m, total, tpr_log);
+    static const bool mixed_only = getenv("CKKS_B200_NTT_MIXED_ONLY") != nullptr;   // A/B switch: always the three-path kernel
+    int km = 0;
+    const int rows = total >> tpr_log;
+    for (int i = 0; i < rows; i++) km |= 1 << m.kind[i];
+    if (LOGN_C == 17 && !mixed_only && km == 1) launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 1>, total, threads, smem, A, S, m, total, tpr_log);
+    else if (LOGN_C == 17 && !mixed_only && km == 4) launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 4>, total, threads, smem, A, S, m, total, tpr_log);
+    else launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 7>, total, threads, smem, A, S, m, total, tpr_log);
 }
 template <bool INV, int PASS_C>
 static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
