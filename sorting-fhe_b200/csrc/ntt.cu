@@ -184,10 +184,10 @@ __device__ __forceinline__ size_t auto_dest(size_t e, u32 kinv, int logn) {
 
 // Final store of a forward transform's canonical results v[8] (register k of thread u = tile-local element
 // local_index(u, k, p)): the fused epilogue, then the store -- vectorised, scalar, or scattered through an automorphism.
-template <class GA>
+template <bool FUSE, class GA>
 __device__ __forceinline__ void epilogue_store(const NttArgs& A, const NttRows& R, const int row, const int logn, const bool vec8,
                                                const int u, const int p, const u64 q, const int mid, u64 (&v)[8], u64* dst, GA gaddr) {
-    if (A.f.epi != EPI_NONE) {
+    if (FUSE && A.f.epi != EPI_NONE) {
         // EPI_RESCALE: out = (in - NTT(switched last limb)) * q_last^-1 (DropLastElementAndScale)
         // EPI_MODDOWN: out = (acc - NTT(converted P part)) * P^-1 [+ addend]    (ApproxModDown of a key switch)
         const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
@@ -219,7 +219,7 @@ __device__ __forceinline__ void epilogue_store(const NttArgs& A, const NttRows& 
             }
         }
     }
-    if (A.f.auto_kinv) {
+    if (FUSE && A.f.auto_kinv) {
 #pragma unroll
         for (int k = 0; k < 8; k++) dst[auto_dest(gaddr(local_index(u, k, p)), A.f.auto_kinv, logn)] = v[k];
     } else if (vec8) store8(dst + gaddr(local_index(u, 0, 0)), v);
@@ -269,7 +269,7 @@ __device__ __forceinline__ void do_round(u64 (&r)[8], const tw_t* W, u32 ehi, in
 
 // LOGN_C != 0: ring size, pass and round schedule are compile-time constants (all index arithmetic folds);
 // LOGN_C == 0: generic runtime form.
-template <bool INV, bool FIX, int LOGN_C, int PASS_C>
+template <bool INV, bool FIX, int LOGN_C, int PASS_C, bool FUSE>
 __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile,
                                          u64* sm, const u64 (&vin)[8]) {
     const int mid = R.mid[row];
@@ -301,7 +301,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
         if (ri == 0) {
 #pragma unroll
             for (int k = 0; k < 8; k++) r[k] = vin[k];
-            if (!INV && A.first_pass && A.f.pro == PRO_SWITCHMOD) {
+            if (FUSE && !INV && A.first_pass && A.f.pro == PRO_SWITCHMOD) {
                 // rescale: the source limb holds coefficients mod q_last; centred switch to this row's modulus
                 const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
 #pragma unroll
@@ -353,7 +353,7 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
                             r[k] = v >= q ? v - q : v;
                         }
                     }
-                    epilogue_store(A, R, row, logn, !strided && p == 0, u, p, q, mid, r, dst, gaddr);
+                    epilogue_store<FUSE>(A, R, row, logn, !strided && p == 0, u, p, q, mid, r, dst, gaddr);
                     continue;
                 } else {
                     const tw_t sc = A.scale[mid];
@@ -496,7 +496,7 @@ __device__ __forceinline__ void do_round_fp(double (&r)[8], const double* W, u32
 
 // same tiling, passes and round schedule as ntt_tile; between the two passes of a transform the buffer holds the
 // raw bits of the (lazy) doubles
-template <bool INV, int LOGN_C, int PASS_C>
+template <bool INV, int LOGN_C, int PASS_C, bool FUSE>
 __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, const NttRows& R, const int row, const int tile,
                                             u64* sm, const u64 (&vin)[8]) {
     const int mid = R.mid[row];
@@ -526,7 +526,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
 #pragma unroll
             for (int k = 0; k < 8; k++) v[k] = vin[k];
             if (A.first_pass) {
-                if (!INV && A.f.pro == PRO_SWITCHMOD) {   // rescale: centred switch of the q_last residues to this row's modulus
+                if (FUSE && !INV && A.f.pro == PRO_SWITCHMOD) {   // rescale: centred switch of the q_last residues to this row's modulus
                     const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1, qrecip = A.mi[mid].qrecip;
 #pragma unroll
                     for (int k = 0; k < 8; k++) {
@@ -569,7 +569,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
             if (!INV) {
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
-                epilogue_store(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr);
+                epilogue_store<FUSE>(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr);
                 continue;
             } else {
                 const double sc = (double)A.scale[mid].x;
@@ -661,7 +661,8 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
     if (id >= total) return;
     const int row = id >> tpr_log, tile = id & ((1 << tpr_log) - 1);
     prefetch_twiddles<LOGN_C, PASS_C>(A, R, row, tile);
-    if (!INV && A.f.epi != EPI_NONE && A.final_pass && (LOGN_C ? PASS_C == 1 : A.pass == 1)) {
+    constexpr bool FUSE = (KM & 8) != 0;   // bit 3: the launch carries a fused prologue / epilogue / automorphism (NttFuse)
+    if (FUSE && !INV && A.f.epi != EPI_NONE && A.final_pass && (LOGN_C ? PASS_C == 1 : A.pass == 1)) {
         // the fused epilogue reads its minuend (and addend) tile only after the last round: pull the lines into L2 now (they were written
         // before this transform's first pass, so this too happens ahead of griddepcontrol.wait), the
         // ncu capture of round 2 had long-scoreboard on those loads as the top stall of the ModDown NTT (profiles/r02_ks_kernels_ncu_summary.txt)
@@ -680,9 +681,9 @@ ntt_kernel(const __grid_constant__ NttArgs A, const __grid_constant__ Sched S, c
     u64 v[8];
     load_tile<INV, LOGN_C, PASS_C>(A, S, R, row, tile, v);
     const int kind = R.kind[row];
-    if (KM == 1 || ((KM & 1) && kind == ROW_FP)) ntt_tile_fp<INV, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
-    else if (KM == 4 || ((KM & 4) && kind == ROW_INT_FIX)) ntt_tile<INV, true, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
-    else if (KM & 2) ntt_tile<INV, false, LOGN_C, PASS_C>(A, S, R, row, tile, sm, v);
+    if ((KM & 7) == 1 || ((KM & 1) && kind == ROW_FP)) ntt_tile_fp<INV, LOGN_C, PASS_C, FUSE>(A, S, R, row, tile, sm, v);
+    else if ((KM & 7) == 4 || ((KM & 4) && kind == ROW_INT_FIX)) ntt_tile<INV, true, LOGN_C, PASS_C, FUSE>(A, S, R, row, tile, sm, v);
+    else if (KM & 2) ntt_tile<INV, false, LOGN_C, PASS_C, FUSE>(A, S, R, row, tile, sm, v);
 }
 
 template <bool INV, int LOGN_C, int PASS_C>
@@ -691,9 +692,18 @@ static void launch_one(Context* c, int total, int tpr_log, int threads, size_t s
     int km = 0;
     const int rows = total >> tpr_log;
     for (int i = 0; i < rows; i++) km |= 1 << m.kind[i];
-    if (LOGN_C == 17 && !mixed_only && km == 1) launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 1>, total, threads, smem, A, S, m, total, tpr_log);
-    else if (LOGN_C == 17 && !mixed_only && km == 4) launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 4>, total, threads, smem, A, S, m, total, tpr_log);
-    else launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, 7>, total, threads, smem, A, S, m, total, tpr_log);
+    // fused work this PASS executes: the prologue rides on the first pass, the epilogue / automorphism on the final one
+    const bool fuse = !INV && ((A.first_pass && A.f.pro != PRO_NONE) || (A.final_pass && (A.f.epi != EPI_NONE || A.f.auto_kinv != 0)));
+#define NTT_LAUNCH(KMV) launch_pdl(c, ntt_kernel<INV, LOGN_C, PASS_C, KMV>, total, threads, smem, A, S, m, total, tpr_log)
+    if (LOGN_C != 17 || mixed_only) { NTT_LAUNCH(15); return; }
+    if (INV) {          // inverse transforms never carry fused work
+        if (km == 1) NTT_LAUNCH(1); else if (km == 4) NTT_LAUNCH(4); else if (km == 5) NTT_LAUNCH(5); else NTT_LAUNCH(7);
+    } else if (fuse) {
+        if (km == 1) NTT_LAUNCH(9); else if (km == 4) NTT_LAUNCH(12); else if (km == 5) NTT_LAUNCH(13); else NTT_LAUNCH(15);
+    } else {
+        if (km == 1) NTT_LAUNCH(1); else if (km == 4) NTT_LAUNCH(4); else if (km == 5) NTT_LAUNCH(5); else NTT_LAUNCH(7);
+    }
+#undef NTT_LAUNCH
 }
 template <bool INV, int PASS_C>
 static void launch_pass(Context* c, int total, int tpr_log, int threads, size_t smem, const NttArgs& A, const Sched& S, const NttRows& m) {
