@@ -52,6 +52,27 @@ void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m)
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * rows * c->n); launch_pdl(c, k_neg, grid_for(c, rows), 256, 0, out, a, m, c->d_mod, c->n);
 }
 
+// ---- FP64 modular products for moduli of at most 44 bits (the 40-bit scaling primes: 30 of the 32 Q limbs).  Same arithmetic as
+// ntt.cu's FP64 butterflies: h = a*b (rounded), l = fma(a, b, -h) (exact low part), qh = rint(h / q), r = fma(-qh, q, h) + l, every
+// intermediate an exactly representable integer, |r| <= q/2 (1 + 2^-8) + 2^28 for operands below q.  Six FP64-pipe instructions
+// instead of the ~45 integer instructions of the 128-bit Barrett product; the canonical residue is the same, bit for bit.
+#define PW_FP_BITS 44
+#define PW_MAGIC 6755399441055744.0   // 1.5 * 2^52
+#define PW_2P52 4503599627370496.0
+__device__ __forceinline__ double pw_from_u64(u64 v) { return __dadd_rn(__longlong_as_double((long long)(v | 0x4330000000000000ULL)), -PW_2P52); }   // v < 2^52
+__device__ __forceinline__ u64 pw_to_u64(double y) { return (u64)__double_as_longlong(__dadd_rn(y, PW_2P52)) & 0x000FFFFFFFFFFFFFULL; }                 // integer y in [0, 2^52)
+__device__ __forceinline__ double pw_mulmod(double a, double b, double q, double qinv) {
+    const double h = __dmul_rn(a, b);
+    const double l = __fma_rn(a, b, -h);
+    const double qh = __dadd_rn(__fma_rn(h, qinv, PW_MAGIC), -PW_MAGIC);
+    return __dadd_rn(__fma_rn(-qh, q, h), l);
+}
+__device__ __forceinline__ u64 pw_canon_reduced(double y, double q) { if (y < 0.0) y = __dadd_rn(y, q); return pw_to_u64(y); }   // |y| < q
+__device__ __forceinline__ u64 pw_canon(double x, double q, double qinv) {                                                        // |x| < 2^51
+    const double t = __dadd_rn(__fma_rn(x, qinv, PW_MAGIC), -PW_MAGIC);
+    return pw_canon_reduced(__fma_rn(-t, q, x), q);
+}
+
 __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const ModInfo* mi, int n, int rows_b, int lrep_b) {
     pdl_trigger();
     X2_PROLOGUE;
@@ -62,6 +83,12 @@ __global__ void k_mul(u64* out, const u64* a, const u64* b, LimbMods mods, const
     u64x2 vb;
     if (lrep_b == 0) vb = ld2(b, (size_t)(row % rows_b) * n + x);
     else { const u64 t = b[(size_t)(row % rows_b) * (n >> lrep_b) + (x >> lrep_b)]; vb = make_ulonglong2(t, t); }   // x even: x, x+1 share a group
+    if (m.bits <= PW_FP_BITS) {
+        const double q = (double)m.q, qinv = __drcp_rn(q);
+        st2(out, o, pw_canon_reduced(pw_mulmod(pw_from_u64(va.x), pw_from_u64(vb.x), q, qinv), q),
+            pw_canon_reduced(pw_mulmod(pw_from_u64(va.y), pw_from_u64(vb.y), q, qinv), q));
+        return;
+    }
     st2(out, o, barrett_mul(va.x, vb.x, m), barrett_mul(va.y, vb.y, m));
 }
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m, int lrep_b) {
@@ -291,6 +318,16 @@ __global__ void k_tensor(u64* d3, const u64* a, const u64* b, const ModInfo* mi,
     pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)l * n + x, P = (size_t)nl * n;
     const u64x2 a0 = ld2(a, o), a1 = ld2(a, o + P), b0 = ld2(b, o), b1 = ld2(b, o + P);
+    if (m.bits <= PW_FP_BITS) {
+        const double q = (double)m.q, qinv = __drcp_rn(q);
+        const double x0 = pw_from_u64(a0.x), x1 = pw_from_u64(a1.x), y0 = pw_from_u64(b0.x), y1 = pw_from_u64(b1.x);
+        const double u0 = pw_from_u64(a0.y), u1 = pw_from_u64(a1.y), v0 = pw_from_u64(b0.y), v1 = pw_from_u64(b1.y);
+        st2(d3, o, pw_canon_reduced(pw_mulmod(x0, y0, q, qinv), q), pw_canon_reduced(pw_mulmod(u0, v0, q, qinv), q));
+        st2(d3, o + P, pw_canon(__dadd_rn(pw_mulmod(x0, y1, q, qinv), pw_mulmod(x1, y0, q, qinv)), q, qinv),
+            pw_canon(__dadd_rn(pw_mulmod(u0, v1, q, qinv), pw_mulmod(u1, v0, q, qinv)), q, qinv));
+        st2(d3, o + 2 * P, pw_canon_reduced(pw_mulmod(x1, y1, q, qinv), q), pw_canon_reduced(pw_mulmod(u1, v1, q, qinv), q));
+        return;
+    }
     st2(d3, o, barrett_mul(a0.x, b0.x, m), barrett_mul(a0.y, b0.y, m));
     st2(d3, o + P, add_mod(barrett_mul(a0.x, b1.x, m), barrett_mul(a1.x, b0.x, m), m.q),
         add_mod(barrett_mul(a0.y, b1.y, m), barrett_mul(a1.y, b0.y, m), m.q));
