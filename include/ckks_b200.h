@@ -120,7 +120,7 @@ int ckks_eval_inner_product_plain(ckks_ctx_t* ctx, const ckks_ct_t* init, const 
                                   int count, ckks_ct_t** out);
 /* `groups` such sums over the same ciphertexts and seed, outs[g] = init + sum_i cts[i] * pts[g * count + i]: the num_partition / np
  * mask sets of one vecRotsOpt / blindRotationOptN call (src/sort_algo.h:331-352, 563-580).  Same limbs as `groups` single calls;
- * the ciphertexts are read once per pass of (by default) two outputs. */
+ * the ciphertexts are read once per pass of (by default) four outputs. */
 int ckks_eval_inner_product_plain_multi(ckks_ctx_t* ctx, const ckks_ct_t* init, const ckks_ct_t* const* cts, const ckks_ct_t* const* pts,
                                         int count, int groups, ckks_ct_t** outs);
 /* comparison.cpp:38 */

@@ -294,7 +294,7 @@ class Engine:
         return self._out(_L.ckks_eval_inner_product_plain(_vp(self.h), _vp(init.h), a, p, len(cts), ctypes.byref(o)), o)
 
     def EvalInnerProductPlainMulti(self, init, cts, pts_groups):
-        """[EvalInnerProductPlain(init, cts, pts) for pts in pts_groups] as one engine call (ciphertexts read once per pass of two outputs)"""
+        """[EvalInnerProductPlain(init, cts, pts) for pts in pts_groups] as one engine call (ciphertexts read once per pass of four outputs)"""
         flat = [p for g in pts_groups for p in g]
         if any(len(g) != len(cts) for g in pts_groups):
             raise ValueError("EvalInnerProductPlainMulti: size mismatch")

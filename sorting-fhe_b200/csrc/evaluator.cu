@@ -587,10 +587,11 @@ void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const 
     int slots = init->slots;
     for (int i = 0; i < cnt; i++) slots = std::max(slots, cts[i]->slots);
     for (int k = 0; k < cnt * groups; k++) { ct_wait(X[k]->v); ct_wait(Y[k]->v); count(c, "mult_pt", nl); count(c, "add", nl); }
-    // accumulators per pass: two is the measured optimum on B200 (DirectSort N=128 per sort: 51.98 ms with one call per set, 51.76 /
-    // 51.49 / 51.65 / 52.20 ms with 1 / 2 / 3 / 4 sets per pass) -- the 128-bit multiply-accumulates make the kernel integer-issue
-    // bound beyond two, below two the baby steps are re-read once per set
-    static const int chunk = getenv("CKKS_B200_IP_GROUPS") ? std::max(1, std::min(IP_GROUPS, atoi(getenv("CKKS_B200_IP_GROUPS")))) : 2;
+    // accumulators per pass (CKKS_B200_IP_GROUPS, A/B).  With the 128-bit integer multiply-accumulate on every limb two sets per pass
+    // were the optimum (DirectSort N=128 per sort: 51.98 ms with one call per set, 51.76 / 51.49 / 51.65 / 52.20 ms with 1 / 2 / 3 / 4
+    // sets per pass -- integer-issue bound beyond two); with the FP64 products on the 40-bit limbs (k_ip_plain_multi) four sets per
+    // pass stay memory-bound: 49.13 / 48.99 / 49.00 ms with 2 / 3 / 4
+    static const int chunk = getenv("CKKS_B200_IP_GROUPS") ? std::max(1, std::min(IP_GROUPS, atoi(getenv("CKKS_B200_IP_GROUPS")))) : IP_GROUPS;
     for (int g0 = 0; g0 < groups; g0 += chunk) {
         IpMultiArgs A; A.cnt = cnt; A.groups = std::min(chunk, groups - g0); A.init = T.v->d;
         for (int i = 0; i < cnt; i++) A.ct[i] = X[i]->v->d;

@@ -239,6 +239,31 @@ __global__ void __launch_bounds__(256) k_ip_plain_multi(const __grid_constant__ 
     pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     const size_t o = (size_t)row * n + x;
     const u64x2 v0 = ld2(A.init, o);
+    if (m.bits <= PW_FP_BITS) {
+        // 40-bit limbs: every product is reduced on the FP64 pipe and the (at most 16) centred residues are summed exactly in a
+        // double -- 15 FP64 instructions per term against ~30 integer ones for the 128-bit multiply-accumulate, which is what lets
+        // four accumulators per pass stay ahead of the memory system
+        const double q = (double)m.q, qinv = __drcp_rn(q);
+        double s0[G], s1[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) { s0[g] = pw_from_u64(v0.x); s1[g] = pw_from_u64(v0.y); }
+        for (int i = 0; i < A.cnt; i++) {
+            const u64x2 a = ld2(A.ct[i], o);
+            const double a0 = pw_from_u64(a.x), a1 = pw_from_u64(a.y);
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const int lr = A.lrep[g][i];
+                double b0, b1;
+                if (lr == 0) { const u64x2 b = ld2(A.pt[g][i], (size_t)l * n + x); b0 = pw_from_u64(b.x); b1 = pw_from_u64(b.y); }
+                else { b0 = b1 = pw_from_u64(A.pt[g][i][(size_t)l * (n >> lr) + (x >> lr)]); }
+                s0[g] = __dadd_rn(s0[g], pw_mulmod(a0, b0, q, qinv));
+                s1[g] = __dadd_rn(s1[g], pw_mulmod(a1, b1, q, qinv));
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) st2(A.out[g], o, pw_canon(s0[g], q, qinv), pw_canon(s1[g], q, qinv));
+        return;
+    }
     u64 l0[G], h0[G], l1[G], h1[G];
 #pragma unroll
     for (int g = 0; g < G; g++) { l0[g] = v0.x; h0[g] = 0; l1[g] = v0.y; h1[g] = 0; }

@@ -339,7 +339,7 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
         return r;
     }
     // outs[g] = EvalInnerProductPlain(init, cts, pts[g]) for every mask set g, as one engine call that reads the ciphertexts once per
-    // pass of two outputs (ckks_eval_inner_product_plain_multi)
+    // pass of four outputs (ckks_eval_inner_product_plain_multi)
     std::vector<CT> EvalInnerProductPlainMulti(const CT& init, const std::vector<CT>& cts, const std::vector<std::vector<Plaintext>>& pts) const {
         std::vector<const ckks_ct_t*> a, p;
         for (auto& c : cts) a.push_back(c->h);
@@ -347,8 +347,8 @@ template <class Element> class CryptoContextImpl : public std::enable_shared_fro
             if (g.size() != cts.size()) throw std::runtime_error("EvalInnerProductPlainMulti: size mismatch");
             for (auto& q : g) p.push_back(enc_of(q)->h);
         }
-        // SORTFHE_NO_IP_MULTI=1: one engine call per mask set (A/B; 51.98 vs 51.49 ms per DirectSort N=128 sort on B200 with the
-        // engine's default of two sets per pass)
+        // SORTFHE_NO_IP_MULTI=1: one engine call per mask set (A/B; measured with the integer accumulate: 51.98 vs 51.49 ms per
+        // DirectSort N=128 sort on B200 at two sets per pass; the FP64 accumulate of the 40-bit limbs made four sets per pass the default)
         static const bool single = getenv("SORTFHE_NO_IP_MULTI") != nullptr;
         if (single) {
             std::vector<CT> r;
