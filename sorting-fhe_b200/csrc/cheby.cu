@@ -8,6 +8,7 @@
 // produce identical doubles and identical ciphertext limbs.
 #include "evaluator.h"
 #include <cmath>
+#include <cstdlib>
 #include <memory>
 #include <stdexcept>
 
@@ -84,9 +85,24 @@ Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& w
     return ct_clone(acc.get());
 }
 
+// ---- batched leaves.  Every weighted sum of one Paterson-Stockmeyer evaluation combines a prefix of the same baby-step basis
+// T_1..T_{k-1}, and which sums are formed, in which order and with which weights depends on the coefficients alone.  ps_plan walks
+// the recursion of ps_core on the coefficients only and lists them; wsum_precompute then forms them in that order -- so that the
+// in-place adjustments EvalLinearWSumMutable applies to the T_i happen in OpenFHE's order -- but up to four at a time in one pass
+// over the inputs (evaluator.cu eval_wsum_aligned_multi); ps_core's wsum() calls pick the results up.  DirectSort N=128's degree-848
+// doubled-sinc indicator has 61 such sums over up to 31 inputs of 16 limbs: 61 passes over 15 GB become 16 over 5.
+struct WsumItem { int cnt; std::vector<double> w; };
+struct WsumQueue { std::vector<WsumItem> items; std::vector<CtP> res; size_t next = 0; };
+static thread_local WsumQueue* g_wq = nullptr;
+
 static CtP wsum(std::vector<CtP>& T, int cnt, const std::vector<double>& coeffs) {
     std::vector<Ct*> cts(cnt); std::vector<double> w(cnt);
     for (int i = 0; i < cnt; i++) { cts[i] = T[i].get(); w[i] = coeffs[i + 1]; }
+    if (g_wq) {
+        if (g_wq->next >= g_wq->items.size() || g_wq->items[g_wq->next].cnt != cnt || g_wq->items[g_wq->next].w != w)
+            throw std::runtime_error("internal: Paterson-Stockmeyer plan and evaluation disagree");
+        return g_wq->res[g_wq->next++];
+    }
     return wrap(eval_linear_wsum_mutable(cts, w));
 }
 
@@ -100,6 +116,82 @@ static CtP ps_leaf(const std::vector<double>& coeffs, int k, std::vector<CtP>& T
     for (int i = 0; i < doublings; i++) s = add(s, s);
     acc = acc ? add(acc, s) : s;
     return addc(acc, coeffs[0] / 2.0);
+}
+
+static void plan_wsum(std::vector<WsumItem>& items, int cnt, const std::vector<double>& coeffs) {
+    WsumItem it; it.cnt = cnt; it.w.resize(cnt);
+    for (int i = 0; i < cnt; i++) it.w[i] = coeffs[i + 1];
+    items.push_back(std::move(it));
+}
+static void plan_leaf(const std::vector<double>& coeffs, int k, std::vector<WsumItem>& items) {
+    std::vector<double> cc(k, 0.0);
+    for (int i = 0; i < k && i < (int)coeffs.size(); i++) cc[i] = coeffs[i];
+    const int d = degree(cc);
+    if (d > 0) plan_wsum(items, d, coeffs);
+}
+// the coefficient arithmetic of ps_core, nothing else; `uses_t0` reports a T_1 * constant product formed before the first sum
+// (it would see T_1 before the first sum's in-place rescale: the plan is then not used)
+static void ps_plan(const std::vector<double>& f, int k, int m, std::vector<WsumItem>& items, bool& t0_before_first_sum) {
+    const int k2m2k = k * (1 << (m - 1)) - k;
+    std::vector<double> tkm(k2m2k + k + 1, 0.0); tkm.back() = 1.0;
+    std::vector<double> q, r;
+    long_division_chebyshev(f, tkm, q, r);
+    std::vector<double> r2 = r;
+    if (k2m2k - degree(r) <= 0) {
+        if ((int)r2.size() < k2m2k + 1) r2.resize(k2m2k + 1, 0.0);
+        r2[k2m2k] -= 1.0;
+        r2.resize(degree(r2) + 1);
+    } else {
+        r2.resize(k2m2k + 1, 0.0);
+        r2.back() = -1.0;
+    }
+    std::vector<double> cq, s;
+    long_division_chebyshev(r2, q, cq, s);
+    std::vector<double> s2 = s;
+    s2.resize(k2m2k + 1, 0.0);
+    s2.back() = 1.0;
+    const int dc = degree(cq);
+    if (dc == 1 && cq[1] != 1 && items.empty()) t0_before_first_sum = true;
+    if (dc >= 2) plan_wsum(items, dc, cq);
+    if (degree(q) > k) ps_plan(q, k, m - 1, items, t0_before_first_sum); else plan_leaf(q, k, items);
+    if (degree(s2) > k) ps_plan(s2, k, m - 1, items, t0_before_first_sum); else plan_leaf(s2, k, items);
+}
+// true when EvalLinearWSumMutable on T[0..cnt) would leave its operands as they are (aligned, noiseScaleDeg 1)
+static bool wsum_inputs_settled(const std::vector<CtP>& T, int cnt) {
+    const Ct* f = T[0].get();
+    for (int i = 0; i < cnt; i++) {
+        const Ct* g = T[i].get();
+        if (g->deg != 1 || g->level != f->level || g->nl != f->nl || g->sf != f->sf || g->parts != f->parts || g->lrep) return false;
+    }
+    return true;
+}
+static void wsum_precompute(std::vector<CtP>& T, WsumQueue& Q) {
+    const size_t n = Q.items.size();
+    Q.res.resize(n);
+    size_t i = 0;
+    while (i < n) {
+        size_t j = i;
+        if (wsum_inputs_settled(T, Q.items[i].cnt)) {
+            while (j < n && j - i < WSUM_GROUPS && Q.items[j].cnt >= 2 && wsum_inputs_settled(T, Q.items[j].cnt)) j++;
+        }
+        if (j - i >= 2) {
+            int cmax = 0;
+            std::vector<std::vector<double>> w;
+            for (size_t t = i; t < j; t++) { cmax = std::max(cmax, Q.items[t].cnt); w.push_back(Q.items[t].w); }
+            std::vector<Ct*> cts(cmax);
+            for (int t = 0; t < cmax; t++) cts[t] = T[t].get();
+            Ct* outs[WSUM_GROUPS] = {nullptr, nullptr, nullptr, nullptr};
+            if (eval_wsum_aligned_multi(cts, w, outs)) {
+                for (size_t t = i; t < j; t++) Q.res[t] = wrap(outs[t - i]);
+                i = j;
+                continue;
+            }
+        }
+        std::vector<Ct*> cts(Q.items[i].cnt);
+        for (int t = 0; t < Q.items[i].cnt; t++) cts[t] = T[t].get();
+        Q.res[i] = wrap(eval_linear_wsum_mutable(cts, Q.items[i].w));     // also the step that settles the inputs
+        i++;
+    }
 }
 
 static CtP ps_core(const std::vector<double>& f, int k, int m, std::vector<CtP>& T, std::vector<CtP>& T2) {
@@ -175,7 +267,18 @@ Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coefficient
     const int k2m2k = k * (1 << (m - 1)) - k;
     f2.resize(2 * k2m2k + k + 1, 0.0);
     f2.back() = 1.0;
-    CtP res = ps_core(f2, k, m, T, T2);
+    static const bool no_batch = getenv("CKKS_B200_NO_WSUM_BATCH") != nullptr;   // A/B switch: one pass per weighted sum
+    WsumQueue Q;
+    bool t0_first = false;
+    if (!no_batch) ps_plan(f2, k, m, Q.items, t0_first);
+    const bool use_plan = !no_batch && !t0_first && Q.items.size() >= 2;
+    CtP res;
+    if (use_plan) {
+        wsum_precompute(T, Q);
+        struct Guard { WsumQueue* prev; Guard(WsumQueue* q) : prev(g_wq) { g_wq = q; } ~Guard() { g_wq = prev; } } guard(&Q);
+        res = ps_core(f2, k, m, T, T2);
+        if (Q.next != Q.items.size()) throw std::runtime_error("internal: Paterson-Stockmeyer plan longer than the evaluation");
+    } else res = ps_core(f2, k, m, T, T2);
     res = sub(res, T2km1);
     return ct_clone(res.get());
 }

@@ -257,6 +257,10 @@ void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u
 void launch_expand_rep(Context* c, u64* out, const u64* in, int rows, int lrep);   // compact -> full rows
 // out = sum_i in_i * s_i with per-limb integer scalars h_scalars[i * nl + l] (EvalLinearWSum in one pass)
 void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* h_scalars, int cnt, int parts, int nl);
+#define WSUM_GROUPS 4
+#define WSUM_MULTI_MAX_IN 64
+struct WsumMultiArgs { int cnt; const u64* in[WSUM_MULTI_MAX_IN]; u64* out[WSUM_GROUPS]; };
+void launch_wsum_multi(Context* c, u64* const* outs, int groups, const u64* const* ins, const u64* h_scalars, int cnt, int parts, int nl);
 #define IP_MAX 15
 struct IpArgs { int cnt; const u64* init; const u64* ct[IP_MAX]; const u64* pt[IP_MAX]; int lrep[IP_MAX]; };
 void launch_ip_plain(Context* c, u64* out, const IpArgs& A, int nl);

@@ -501,6 +501,43 @@ Ct* eval_wsum_aligned(const std::vector<Ct*>& cts, const std::vector<double>& w)
     return r;
 }
 
+// `groups` weighted sums over a common, already aligned input list: outs[g] = sum_{i < cnt[g]} cts[i] * w[g][i], each exactly what
+// eval_wsum_aligned(cts[0..cnt[g]), w[g]) returns, in one pass over the inputs (kernels.cu k_wsum_multi).  Returns false (nothing
+// done) when the inputs are not aligned.
+bool eval_wsum_aligned_multi(const std::vector<Ct*>& cts, const std::vector<std::vector<double>>& w, Ct** outs) {
+    const int groups = (int)w.size();
+    if (groups < 1 || groups > WSUM_GROUPS) return false;
+    int cmax = 0;
+    for (const auto& g : w) cmax = std::max(cmax, (int)g.size());
+    if (cmax < 2 || cmax > (int)cts.size() || cmax > WSUM_MULTI_MAX_IN) return false;
+    for (const auto& g : w) if (g.size() < 2) return false;     // eval_wsum_aligned declines single terms
+    const Ct* f = cts[0]; Context* c = f->ctx;
+    if (f->deg != 1 || f->lrep) return false;
+    for (int i = 0; i < cmax; i++) {
+        const Ct* g = cts[i];
+        if (g->parts != f->parts || g->nl != f->nl || g->level != f->level || g->deg != 1 || g->sf != f->sf || g->lrep) return false;
+    }
+    const double sf = c->sf_real[f->level];
+    std::vector<u64> sc((size_t)groups * cmax * f->nl, 0);
+    std::vector<const u64*> ins(cmax);
+    for (int i = 0; i < cmax; i++) { ct_wait(cts[i]); ins[i] = cts[i]->d; }
+    std::vector<u64*> od(groups);
+    for (int g = 0; g < groups; g++) {
+        int slots = 0;
+        for (size_t i = 0; i < w[g].size(); i++) {
+            const i128 v = (i128)(w[g][i] * sf + 0.5);                 // same rounding as mult_const_new
+            int_residues(c, v, f->nl, sc.data() + ((size_t)g * cmax + i) * f->nl);
+            slots = std::max(slots, cts[i]->slots);
+            count(c, "mult_const", f->nl);
+            if (i) count(c, "add", f->nl);
+        }
+        outs[g] = ct_new(c, f->parts, f->nl, f->level, 2, f->sf * sf, slots);
+        od[g] = outs[g]->d;
+    }
+    launch_wsum_multi(c, od.data(), groups, ins.data(), sc.data(), cmax, f->parts, f->nl);
+    return true;
+}
+
 // T = init; for i: T = EvalAdd(T, EvalMult(cts[i], pts[i]))   (vecRotsOpt / blindRotationOptN of the reference,
 // src/sort_algo.h:336-345, 567-577).  Every pair is adjusted exactly as EvalMult would (lazy rescale of the ciphertext
 // through its cached twin, lift + rescale of the plaintext), the accumulator exactly as the first EvalAdd would; when

@@ -56,6 +56,7 @@ Ct* eval_linear_wsum_mutable(std::vector<Ct*>& cts, const std::vector<double>& w
 Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coeffs, double a, double b);
 Ct* eval_chebyshev_series(const Ct* x, const std::vector<double>& coeffs, double a, double b);
+bool eval_wsum_aligned_multi(const std::vector<Ct*>& cts, const std::vector<std::vector<double>>& w, Ct** outs);
 Ct* eval_inner_product_plain(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt);
 void eval_inner_product_plain_multi(const Ct* init, const Ct* const* cts, const Ct* const* pts, int cnt, int groups, Ct** outs);
 Ct* eval_poly_linear(const Ct* x, const std::vector<double>& coeffs);

@@ -200,6 +200,79 @@ void launch_wsum(Context* c, u64* out, const u64* const* ins, const u64* hs, int
     }
 }
 
+// G weighted sums over the SAME inputs (the leaves of one Paterson-Stockmeyer evaluation all combine the baby-step basis T_1..T_k-1,
+// cheby.cu wsum_precompute): out_g[row] = sum_i in_i[row] * s_{g,i}[limb].  Every input word is loaded once per G outputs; on limbs
+// of at most 44 bits the products are reduced on the FP64 pipe and the centred residues summed exactly in a double, the 60-bit rows
+// keep Shoup products.  W = device table [G][cnt][nl] of (scalar, Shoup companion).  Same canonical residues as G k_wsum launches.
+template <int G>
+__global__ void __launch_bounds__(256) k_wsum_multi(const __grid_constant__ WsumMultiArgs A, const u64* __restrict__ W, const ModInfo* mi, int n, int nl) {
+    pdl_trigger();
+    X2_PROLOGUE;
+    const int row = blockIdx.y, l = row % nl; const ModInfo m = mi[l];
+    pdl_wait();
+    const size_t o = (size_t)row * n + x;
+    const int cnt = A.cnt;
+    if (m.bits <= PW_FP_BITS) {
+        const double q = (double)m.q, qinv = __drcp_rn(q);
+        double s0[G], s1[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) { s0[g] = 0.0; s1[g] = 0.0; }
+        for (int i = 0; i < cnt; i++) {
+            const u64x2 v = ld2(A.in[i], o);
+            const double a0 = pw_from_u64(v.x), a1 = pw_from_u64(v.y);
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const double w = pw_from_u64(__ldg(W + 2 * ((size_t)(g * cnt + i) * nl + l)));
+                s0[g] = __dadd_rn(s0[g], pw_mulmod(a0, w, q, qinv));
+                s1[g] = __dadd_rn(s1[g], pw_mulmod(a1, w, q, qinv));
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) st2(A.out[g], o, pw_canon(s0[g], q, qinv), pw_canon(s1[g], q, qinv));
+        return;
+    }
+    u64 r0[G], r1[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) { r0[g] = 0; r1[g] = 0; }
+    for (int i = 0; i < cnt; i++) {
+        const u64x2 v = ld2(A.in[i], o);
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const ulonglong2 w = __ldg(reinterpret_cast<const ulonglong2*>(W) + ((size_t)(g * cnt + i) * nl + l));
+            r0[g] = add_mod(r0[g], shoup_mul(v.x, w.x, w.y, m.q), m.q);
+            r1[g] = add_mod(r1[g], shoup_mul(v.y, w.x, w.y, m.q), m.q);
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) st2(A.out[g], o, r0[g], r1[g]);
+}
+// hs: host scalars [groups][cnt][nl] (0 for the inputs a group does not use)
+void launch_wsum_multi(Context* c, u64* const* outs, int groups, const u64* const* ins, const u64* hs, int cnt, int parts, int nl) {
+    KL(c);
+    ProfScope ps(c, KC_POINTWISE, 8.0 * c->n * parts * nl * (cnt + groups));
+    const size_t nw = (size_t)groups * cnt * nl;
+    std::vector<u64> pairs(2 * nw);
+    for (int g = 0; g < groups; g++)
+        for (int i = 0; i < cnt; i++)
+            for (int l = 0; l < nl; l++) {
+                const size_t k = (size_t)(g * cnt + i) * nl + l;
+                pairs[2 * k] = hs[k]; pairs[2 * k + 1] = host_shoup(hs[k], c->moduli[l]);
+            }
+    u64* W = dev_alloc(c, 2 * nw);
+    cudaMemcpyAsync(W, pairs.data(), pairs.size() * sizeof(u64), cudaMemcpyHostToDevice, c->stream);   // pageable source: staged before the call returns
+    WsumMultiArgs A; A.cnt = cnt;
+    for (int i = 0; i < cnt; i++) A.in[i] = ins[i];
+    for (int g = 0; g < WSUM_GROUPS; g++) A.out[g] = g < groups ? outs[g] : nullptr;
+    const dim3 grid = grid_for2(c, parts * nl);
+    switch (groups) {
+        case 1: launch_pdl(c, k_wsum_multi<1>, grid, 256, 0, A, W, c->d_mod, c->n, nl); break;
+        case 2: launch_pdl(c, k_wsum_multi<2>, grid, 256, 0, A, W, c->d_mod, c->n, nl); break;
+        case 3: launch_pdl(c, k_wsum_multi<3>, grid, 256, 0, A, W, c->d_mod, c->n, nl); break;
+        default: launch_pdl(c, k_wsum_multi<4>, grid, 256, 0, A, W, c->d_mod, c->n, nl); break;
+    }
+    dev_free(c, W);
+}
+
 // out[p][l] = init[p][l] + sum_i ct_i[p][l] (.) pt_i[l]   -- the  T = EvalAdd(T, EvalMult(ct_i, pt_i))  chains of the
 // sorters' masked baby-step sums (src/sort_algo.h:336-345, 567-577) in one pass: every product goes into a 128-bit
 // accumulator (<= 16 terms of q^2 < q * 2^64 for q < 2^60), reduced once.  Modular addition and multiplication are
