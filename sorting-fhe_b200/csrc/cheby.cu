@@ -19,6 +19,7 @@ static CtP sub(const CtP& a, const CtP& b) { return wrap(eval_add(a.get(), b.get
 static CtP addc(const CtP& a, double x) { return wrap(eval_add_const(a.get(), x)); }
 static CtP mul(const CtP& a, const CtP& b) { return wrap(eval_mult(a.get(), b.get())); }
 static CtP mulc(const CtP& a, double x) { return wrap(eval_mult_const(a.get(), x)); }
+static CtP dbl_addc(const CtP& a, double x) { return wrap(eval_double_add_const(a.get(), x)); }   // addc(add(a, a), x) in one pass
 
 static int degree(const std::vector<double>& c, size_t len) {
     for (size_t i = len; i > 0; i--) if (c[i - 1] != 0) return (int)i - 1;
@@ -246,7 +247,7 @@ Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coefficient
     for (int i = 2; i <= k; i++) {
         if ((i & (i - 1)) == 0 || i % 2 == 0) {
             CtP sq = mul(T[i / 2 - 1], T[i / 2 - 1]);
-            T[i - 1] = addc(add(sq, sq), -1.0);
+            T[i - 1] = dbl_addc(sq, -1.0);
         } else {
             CtP pr = mul(T[i / 2 - 1], T[i / 2]);
             T[i - 1] = sub(add(pr, pr), y);
@@ -257,7 +258,7 @@ Ct* eval_chebyshev_series_ps(const Ct* x, const std::vector<double>& coefficient
     T2[0] = T[k - 1];
     for (int i = 1; i < m; i++) {
         CtP sq = mul(T2[i - 1], T2[i - 1]);
-        T2[i] = addc(add(sq, sq), -1.0);
+        T2[i] = dbl_addc(sq, -1.0);
     }
     CtP T2km1 = T2[0];
     for (int i = 1; i < m; i++) {
@@ -298,7 +299,7 @@ Ct* eval_chebyshev_series_linear(const Ct* x, const std::vector<double>& coeffic
     for (int i = 2; i <= k; i++) {
         if (i % 2 == 0) {
             CtP sq = mul(T[i / 2 - 1], T[i / 2 - 1]);
-            T[i - 1] = addc(add(sq, sq), -1.0);
+            T[i - 1] = dbl_addc(sq, -1.0);
         } else {
             CtP pr = mul(T[i / 2 - 1], T[i / 2]);
             T[i - 1] = sub(add(pr, pr), y);

@@ -249,7 +249,7 @@ void launch_neg(Context* c, u64* out, const u64* a, int rows, const LimbMods& m)
 void launch_mul(Context* c, u64* out, const u64* a, const u64* b, int rows_out, int rows_b, const LimbMods& m, int lrep_b = 0);
 void launch_mul_scalar(Context* c, u64* out, const u64* in, int rows, const LimbMods& m, const u64* h_scalars /*[m.n]*/, int lrep = 0);
 // out[0] = (negate ? -in[0] : in[0]) + s ; out[p>0] = (negate ? -in[p] : in[p])
-void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* h_scalars, bool negate);
+void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* h_scalars, int negate /* 0 none, 1 negate first, 2 double first */);
 // out[p] = (p < xparts ? x[p] : 0) +- (p < yparts ? y[p] : 0), p < max(xparts, yparts)
 // lrep_x / lrep_y: the 1-part operand may be a compact plaintext
 void launch_addsub_parts(Context* c, u64* out, const u64* x, int xparts, const u64* y, int yparts, int nl, bool sub,

@@ -436,7 +436,17 @@ Ct* eval_add_const(const Ct* a_in, double x) {
     Context* c = a->ctx;
     u64 s[MAX_LIMBS]; add_const_residues(a, x, s);
     Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
-    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, false);
+    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, 0);
+    return r;
+}
+// EvalAdd(EvalAdd(ct, ct), double) in one pass: the T_2i = 2 T_i^2 - 1 steps of the Chebyshev recurrences (cheby.cu)
+Ct* eval_double_add_const(const Ct* a_in, double x) {
+    Opnd fa(a_in); op_full(fa); const Ct* a = fa.v;
+    Context* c = a->ctx;
+    count(c, "add", a->nl);
+    u64 s[MAX_LIMBS]; add_const_residues(a, x, s);
+    Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
+    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, 2);
     return r;
 }
 // EvalSub(double, ct) = -ct + x in one pass
@@ -445,7 +455,7 @@ Ct* eval_const_sub(double x, const Ct* a_in) {
     Context* c = a->ctx;
     u64 s[MAX_LIMBS]; add_const_residues(a, x, s);
     Ct* r = ct_new(c, a->parts, a->nl, a->level, a->deg, a->sf, a->slots);
-    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, true);
+    launch_add_scalar(c, r->d, a->d, a->parts, a->nl, s, 1);
     return r;
 }
 

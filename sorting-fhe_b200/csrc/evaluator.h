@@ -25,6 +25,7 @@ void key_switch(Context* c, const u64* src, int nl, const EvalKey& key, u64* out
 Ct* eval_add(const Ct* a, const Ct* b, int sign);
 Ct* eval_add_const(const Ct* a, double x);
 Ct* eval_const_sub(double x, const Ct* a);
+Ct* eval_double_add_const(const Ct* a, double x);
 Ct* eval_negate(const Ct* a);
 Ct* eval_mult(const Ct* a, const Ct* b);
 Ct* eval_mult_const(const Ct* a, double x);

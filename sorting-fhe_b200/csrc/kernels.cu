@@ -120,15 +120,16 @@ __global__ void k_add_scalar(u64* out, const u64* d, const ModInfo* mi, int n, i
     pdl_wait();   // the modulus entry above comes from a context table: fetched while the predecessor drains
     size_t o = (size_t)row * n + x;
     u64x2 v = ld2(d, o);
-    if (negate) { v.x = neg_mod(v.x, q); v.y = neg_mod(v.y, q); }
+    if (negate == 1) { v.x = neg_mod(v.x, q); v.y = neg_mod(v.y, q); }
+    else if (negate == 2) { v.x = add_mod(v.x, v.x, q); v.y = add_mod(v.y, v.y, q); }   // 2 * ct + const (Chebyshev recurrences)
     if (row < nl) { v.x = add_mod(v.x, s.v[l], q); v.y = add_mod(v.y, s.v[l], q); }
     st2(out, o, v.x, v.y);
 }
-void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* hs, bool negate) {
+void launch_add_scalar(Context* c, u64* out, const u64* in, int parts, int nl, const u64* hs, int negate) {
     KL(c); ProfScope ps(c, KC_POINTWISE, 16.0 * parts * nl * c->n);
     LimbScalars s;
     for (int i = 0; i < nl; i++) { s.v[i] = hs[i]; s.sh[i] = 0; }
-    launch_pdl(c, k_add_scalar, grid_for2(c, parts * nl), 256, 0, out, in, c->d_mod, c->n, nl, s, negate ? 1 : 0);
+    launch_pdl(c, k_add_scalar, grid_for2(c, parts * nl), 256, 0, out, in, c->d_mod, c->n, nl, s, negate);
 }
 
 __global__ void k_addsub_parts(u64* out, const u64* xs, int xparts, const u64* ys, int yparts, const ModInfo* mi, int n, int nl,
