@@ -526,19 +526,33 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
 #pragma unroll
             for (int k = 0; k < 8; k++) v[k] = vin[k];
             if (A.first_pass) {
+                bool switched = false;
                 if (FUSE && !INV && A.f.pro == PRO_SWITCHMOD) {   // rescale: centred switch of the q_last residues to this row's modulus
-                    const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1, qrecip = A.mi[mid].qrecip;
+                    const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
+                    if (ql < 2 * qi && ql < (1ull << FP_BITS)) {
+                        // the centred representative |c| <= q_last / 2 < q is a valid lazy operand as it is: the transform is linear
+                        // modulo q and the final canonicalisation gives the residues that reducing c first would give -- one
+                        // compare and one subtraction on the FP64 pipe instead of a 64-bit Barrett step and two negations per word
+                        const double qld = (double)ql;
 #pragma unroll
-                    for (int k = 0; k < 8; k++) {
-                        const bool neg = v[k] > half;
-                        u64 a = neg ? ql - v[k] : v[k];
-                        a -= __umul64hi(a, qrecip) * qi;
-                        if (a >= qi) a -= qi;
-                        v[k] = neg ? (a ? qi - a : 0) : a;
+                        for (int k = 0; k < 8; k++) { const double c = fp_from_u64(v[k]); r[k] = v[k] > half ? __dadd_rn(c, -qld) : c; }
+                        switched = true;
+                    } else {
+                        const u64 qrecip = A.mi[mid].qrecip;
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            const bool neg = v[k] > half;
+                            u64 a = neg ? ql - v[k] : v[k];
+                            a -= __umul64hi(a, qrecip) * qi;
+                            if (a >= qi) a -= qi;
+                            v[k] = neg ? (a ? qi - a : 0) : a;
+                        }
                     }
                 }
+                if (!switched) {
 #pragma unroll
-                for (int k = 0; k < 8; k++) r[k] = fp_from_u64(v[k]);
+                    for (int k = 0; k < 8; k++) r[k] = fp_from_u64(v[k]);
+                }
             } else {
 #pragma unroll
                 for (int k = 0; k < 8; k++) r[k] = __longlong_as_double((long long)v[k]);
