@@ -186,8 +186,9 @@ __device__ __forceinline__ size_t auto_dest(size_t e, u32 kinv, int logn) {
 // local_index(u, k, p)): the fused epilogue, then the store -- vectorised, scalar, or scattered through an automorphism.
 template <bool FUSE, class GA>
 __device__ __forceinline__ void epilogue_store(const NttArgs& A, const NttRows& R, const int row, const int logn, const bool vec8,
-                                               const int u, const int p, const u64 q, const int mid, u64 (&v)[8], u64* dst, GA gaddr) {
-    if (FUSE && A.f.epi != EPI_NONE) {
+                                               const int u, const int p, const u64 q, const int mid, u64 (&v)[8], u64* dst, GA gaddr,
+                                               const bool apply = true) {
+    if (FUSE && apply && A.f.epi != EPI_NONE) {
         // EPI_RESCALE: out = (in - NTT(switched last limb)) * q_last^-1 (DropLastElementAndScale)
         // EPI_MODDOWN: out = (acc - NTT(converted P part)) * P^-1 [+ addend]    (ApproxModDown of a key switch)
         const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
@@ -381,6 +382,9 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
 // lazy (forward: +q/2 per stage; inverse: doubling, folded back every second round) and are canonicalised once on
 // the final store, so the results are the same residues as the integer path, bit for bit.
 #define FP_BITS 44
+#ifndef NTT_FP_EPILOGUE
+#define NTT_FP_EPILOGUE 1   /* 0: the integer epilogue on FP64 rows too (A/B builds) */
+#endif
 #define FP_MAGIC 6755399441055744.0   // 1.5 * 2^52: adding and subtracting it rounds to the nearest integer
 #define FP_2P52 4503599627370496.0
 __device__ __forceinline__ double fp_from_u64(u64 v) {   // v < 2^52
@@ -581,6 +585,46 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
         } else if (A.final_pass) {
             u64 v[8];
             if (!INV) {
+                if (FUSE && A.f.epi != EPI_NONE && NTT_FP_EPILOGUE) {
+                    // the fused epilogue on the FP64 pipe, straight from the lazy results: out = (in [* s] - r) * pair [+ addend] as exact
+                    // floating-point modular products, canonicalised once -- instead of canonicalising r and then two (three) 64-bit
+                    // Shoup products and conditional subtractions on the integer pipes; same residues
+                    const bool vec8 = !strided && p == 0;
+                    const u64* ein = A.f.epi_in + ((size_t)R.epi[row] << logn);
+                    const double scd = (double)reinterpret_cast<const tw_t*>(A.f.epi_pairs)[mid].x;
+                    u64 xin[8];
+                    if (vec8) load8(ein + gaddr(local_index(u, 0, 0)), xin);
+                    else {
+#pragma unroll
+                        for (int k = 0; k < 8; k++) xin[k] = ein[gaddr(local_index(u, k, p))];
+                    }
+                    double y[8];
+#pragma unroll
+                    for (int k = 0; k < 8; k++) y[k] = fp_from_u64(xin[k]);
+                    if (A.f.epi_pre) {
+                        const double psd = (double)reinterpret_cast<const tw_t*>(A.f.epi_pre)[mid].x;
+#pragma unroll
+                        for (int k = 0; k < 8; k++) y[k] = fp_mulmod(y[k], psd, q, qinv);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; k++) y[k] = fp_mulmod(__dadd_rn(y[k], -r[k]), scd, q, qinv);
+                    const u64* add = A.f.epi == EPI_MODDOWN ? A.f.epi_add[R.addsel[row]] : nullptr;
+                    if (add) {
+                        add += (size_t)R.addrow[row] << logn;
+                        if (vec8) load8(add + gaddr(local_index(u, 0, 0)), xin);
+                        else {
+#pragma unroll
+                            for (int k = 0; k < 8; k++) xin[k] = add[gaddr(local_index(u, k, p))];
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; k++) v[k] = fp_canon(__dadd_rn(y[k], fp_from_u64(xin[k])), q, qinv);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; k++) v[k] = fp_canon_reduced(y[k], q);
+                    }
+                    epilogue_store<FUSE>(A, R, row, logn, vec8, u, p, qi, mid, v, dst, gaddr, false);
+                    continue;
+                }
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
                 epilogue_store<FUSE>(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr);
