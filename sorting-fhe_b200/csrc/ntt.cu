@@ -305,13 +305,18 @@ __device__ __forceinline__ void ntt_tile(const NttArgs& A, const Sched& SR, cons
             if (FUSE && !INV && A.first_pass && A.f.pro == PRO_SWITCHMOD) {
                 // rescale: the source limb holds coefficients mod q_last; centred switch to this row's modulus
                 const u64 ql = A.mi[A.f.pro_mod].q, half = ql >> 1;
+                if (ql <= q) {      // a 40-bit limb dropped under the 60-bit q0: |centred value| < q, nothing to reduce
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    const bool neg = r[k] > half;
-                    u64 a = neg ? ql - r[k] : r[k];
-                    a -= __umul64hi(a, mi.qrecip) * q;
-                    if (a >= q) a -= q;
-                    r[k] = neg ? (a ? q - a : 0) : a;
+                    for (int k = 0; k < 8; k++) r[k] = r[k] > half ? q - (ql - r[k]) : r[k];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        const bool neg = r[k] > half;
+                        u64 a = neg ? ql - r[k] : r[k];
+                        a -= __umul64hi(a, mi.qrecip) * q;
+                        if (a >= q) a -= q;
+                        r[k] = neg ? (a ? q - a : 0) : a;
+                    }
                 }
             }
         } else {
@@ -627,7 +632,7 @@ __device__ __forceinline__ void ntt_tile_fp(const NttArgs& A, const Sched& SR, c
                 }
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = fp_canon(r[k], q, qinv);
-                epilogue_store<FUSE>(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr);
+                epilogue_store<FUSE>(A, R, row, logn, !strided && p == 0, u, p, qi, mid, v, dst, gaddr, !NTT_FP_EPILOGUE);   // no epilogue left here
                 continue;
             } else {
                 const double sc = (double)A.scale[mid].x;
