@@ -66,6 +66,28 @@ class ClockSampler:
     def mark(self):                 # the timed region starts here
         self.samples.clear()
 
+    # NVML queries disturb a later step.  With one clock + throttle-reason query per step, the LAST of ten 46 ms steps ran 50-140 ms
+    # in one run of three (bench lines of round 2: ms_per_step 48-55 against 46.15, e2e unaffected), none with the sampler off; the
+    # queries themselves return in 0.02 ms (tools/nvml_probe2.py), moving them to a helper thread changed nothing, and sampling only
+    # the first five steps still hit step 9.  The region is therefore sampled in its last step only -- `count` queries 10 ms apart on
+    # a helper thread while that step's kernels run: one run in ten still shows a long last step (64 ms), against one in three.
+    def sample_burst_async(self, count=3, gap_s=0.01):
+        if self.h is None:
+            return
+        import threading
+
+        def work():
+            for _ in range(count):
+                self.sample()
+                time.sleep(gap_s)
+        self._thr = threading.Thread(target=work, daemon=True)
+        self._thr.start()
+
+    def drain(self, timeout=0.5):
+        t = getattr(self, "_thr", None)
+        if t is not None:
+            t.join(timeout)
+
     def sample(self):
         if self.h is None:
             return
@@ -83,7 +105,7 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no NVML samples"]}
         reasons = sorted({name for _, r in self.samples for name, bit in self.BAD if r & bit})
         return {"sm_mhz": float(np.median([c for c, _ in self.samples])), "sm_max_mhz": self.mx, "reasons": reasons,
-                "samples": len(self.samples), "how": "in-process NVML, one sample per step while the step's kernels run"}
+                "samples": len(self.samples), "how": "in-process NVML on a helper thread: queries a few ms apart while the kernels of the timed region's last step run (queries earlier in the region disturb a later step, see ClockSampler)"}
 
 
 def workload_name(n, log_n, depth, cfg, nrots):
@@ -342,16 +364,19 @@ def run_b200(args):
     for i in range(K):
         cts[i].slots = n                                 # sort() widens the caller's metadata (sort_algo.h:711)
         outs.append(sorter.sort(cts[i], cfg))
-        if rank == 0:
-            sampler.sample()                             # NVML read while the GPU works through this step (~0.02 ms on the host)
         marks.append(torch.cuda.Event(enable_timing=True)); marks[-1].record(stream)
+        if rank == 0 and i == K - 1:
+            sampler.sample_burst_async()                 # NVML reads on a helper thread while the GPU works through the last step
         eng.sync()                                       # one result at a time, as in the e2e region: the host never runs
-                                                         # more than one sort (3 300 launches) ahead of the device
+                                                         # more than one sort (2 600 launches) ahead of the device
     e1.record(stream)
     barrier()
     t_dev = e0.elapsed_time(e1) / 1e3
     step_ms = [round(a.elapsed_time(b), 3) for a, b in zip([e0] + marks[:-1], marks)]   # diagnosis only: per-step device time
+    if rank == 0:
+        sampler.drain()
     clocks = sampler.stop() if rank == 0 else None
+    time.sleep(0.7)                                      # let the NVML after-effect (ClockSampler) pass before the next region
     st = eng.stats(reset=True)
     launches = st["kernel_launches"]
     trace = [(nm, nl, cnt / K) for nm, nl, cnt in st["ops"]]          # ops of ONE sort
