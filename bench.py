@@ -54,12 +54,20 @@ class ClockSampler:
         self.index, self.h, self.nv, self.samples, self.mx = index, None, None, [], None
 
     def start(self):
+        # NVML is loaded and initialised LATE, by the helper thread of sample_burst_async during the last timed step (BENCH_NVML_EARLY=1
+        # restores initialisation before the warm-up): see the note there
+        self.enabled = True
+        if os.environ.get("BENCH_NVML_EARLY") == "1":
+            self._init()
+
+    def _init(self):
+        if self.h is not None:
+            return
         try:
             import pynvml as nv
             nv.nvmlInit()
             self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(self.index)
             self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
-            self.sample(); self.samples.clear()
         except Exception:
             self.h = None
 
@@ -72,18 +80,19 @@ class ClockSampler:
     # the first five steps still hit step 9.  The region is therefore sampled in its last step only -- `count` queries 10 ms apart on
     # a helper thread while that step's kernels run: one run in ten still shows a long last step (64 ms), against one in three.
     def sample_burst_async(self, count=3, gap_s=0.01):
-        if self.h is None:
+        if not getattr(self, "enabled", False):
             return
         import threading
 
         def work():
+            self._init()                                 # ~30 ms on the helper thread the first time; the step runs 46 ms
             for _ in range(count):
                 self.sample()
                 time.sleep(gap_s)
         self._thr = threading.Thread(target=work, daemon=True)
         self._thr.start()
 
-    def drain(self, timeout=0.5):
+    def drain(self, timeout=2.0):
         t = getattr(self, "_thr", None)
         if t is not None:
             t.join(timeout)
@@ -352,6 +361,12 @@ def run_b200(args):
             break
         prev = dt
     del out
+
+    # Python's cyclic collector stays out of the timed regions (collected now, switched off until the end of the run): a generation-2
+    # pass over the process's objects in the middle of a step would show up as device idle time of that step
+    import gc
+    gc.collect()
+    gc.disable()
 
     # ---- timed region 1: inputs resident in HBM
     eng.stats(reset=True)
