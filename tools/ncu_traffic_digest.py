@@ -25,7 +25,7 @@ def main():
     per = {}
     for row, units in rows(sys.argv[1]):
         name = row["Kernel Name"]
-        m = re.search(r"ntt_kernel<\(?(?:bool\))?(\w+), *\(?(?:int\))?(\d+), *\(?(?:int\))?(\d+)>", name)
+        m = re.search(r"ntt_kernel<\(?(?:bool\))?(\w+), *\(?(?:int\))?(\d+), *\(?(?:int\))?(\d+)(?:, *\(?(?:int\))?\d+)?>", name)   # the 4th argument (row kinds / fused work) is folded
         if not m:
             continue
         key = "ntt_kernel<%s,%s,%s>" % m.groups()
