@@ -429,6 +429,10 @@ void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) 
 // acc[h][e][x] = sum_j dig_j[e][x] * key[j][h][mod(e)][x]; dig_j[e] is the source polynomial row e
 // when e is one of digit j's own limbs, else row of the converted complement (compact layout).
 struct DigitMap { int lo[4], hi[4], base[4]; };   // base: first row of digit j's converted complement in conv
+// NP = number of digits (compile time, 0 = runtime loop): with the loop unrolled every digit's three 16-byte loads are issued before
+// the first multiply-accumulate, so a thread keeps NP x 48 bytes in flight instead of 48 -- the kernel streams the evaluation key
+// (two thirds of its traffic) straight from HBM and was at 65 % of the copy peak inside a sort.
+template <int NP>
 __global__ void __launch_bounds__(256)
 k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __restrict__ conv, const u64* __restrict__ key,
            DigitMap dm, int nparts, int nl, int size_q, int size_p, int M, const ModInfo* __restrict__ mi, int n) {
@@ -442,17 +446,33 @@ k_ks_inner(u64* __restrict__ acc, const u64* __restrict__ src, const u64* __rest
     // switch at l = 32, the inner-product class 5.81 vs 5.64 ms per sort)
     pdl_wait();
     u64 l0 = 0, h0 = 0, l1 = 0, h1 = 0, l2 = 0, h2 = 0, l3 = 0, h3 = 0;
-    for (int j = 0; j < nparts; j++) {
-        ulonglong2 d;
-        if (e >= dm.lo[j] && e < dm.hi[j]) d = *reinterpret_cast<const ulonglong2*>(src + (size_t)e * n + x);
-        else {
-            int r = e < dm.lo[j] ? e : e - (dm.hi[j] - dm.lo[j]);
-            d = *reinterpret_cast<const ulonglong2*>(conv + ((size_t)dm.base[j] + r) * n + x);
+    auto digit_ptr = [&](int j) -> const u64* {
+        if (e >= dm.lo[j] && e < dm.hi[j]) return src + (size_t)e * n + x;
+        const int r = e < dm.lo[j] ? e : e - (dm.hi[j] - dm.lo[j]);
+        return conv + ((size_t)dm.base[j] + r) * n + x;
+    };
+    if (NP > 0) {
+        ulonglong2 d[NP > 0 ? NP : 1], k0[NP > 0 ? NP : 1], k1[NP > 0 ? NP : 1];
+#pragma unroll
+        for (int j = 0; j < NP; j++) {
+            d[j] = *reinterpret_cast<const ulonglong2*>(digit_ptr(j));
+            const u64* kb = key + ((size_t)(j * 2 + 0) * M + mid) * n + x;
+            k0[j] = *reinterpret_cast<const ulonglong2*>(kb);
+            k1[j] = *reinterpret_cast<const ulonglong2*>(kb + (size_t)M * n);
         }
-        const u64* kb = key + ((size_t)(j * 2 + 0) * M + mid) * n + x;
-        const ulonglong2 k0 = *reinterpret_cast<const ulonglong2*>(kb), k1 = *reinterpret_cast<const ulonglong2*>(kb + (size_t)M * n);
-        mac128(l0, h0, d.x, k0.x); mac128(l1, h1, d.x, k1.x);
-        mac128(l2, h2, d.y, k0.y); mac128(l3, h3, d.y, k1.y);
+#pragma unroll
+        for (int j = 0; j < NP; j++) {
+            mac128(l0, h0, d[j].x, k0[j].x); mac128(l1, h1, d[j].x, k1[j].x);
+            mac128(l2, h2, d[j].y, k0[j].y); mac128(l3, h3, d[j].y, k1[j].y);
+        }
+    } else {
+        for (int j = 0; j < nparts; j++) {
+            const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(digit_ptr(j));
+            const u64* kb = key + ((size_t)(j * 2 + 0) * M + mid) * n + x;
+            const ulonglong2 k0 = *reinterpret_cast<const ulonglong2*>(kb), k1 = *reinterpret_cast<const ulonglong2*>(kb + (size_t)M * n);
+            mac128(l0, h0, d.x, k0.x); mac128(l1, h1, d.x, k1.x);
+            mac128(l2, h2, d.y, k0.y); mac128(l3, h3, d.y, k1.y);
+        }
     }
     *reinterpret_cast<ulonglong2*>(acc + (size_t)e * n + x) = make_ulonglong2(mont_reduce(l0, h0, m.q, m.qinv), mont_reduce(l2, h2, m.q, m.qinv));
     *reinterpret_cast<ulonglong2*>(acc + ((size_t)next + e) * n + x) = make_ulonglong2(mont_reduce(l1, h1, m.q, m.qinv), mont_reduce(l3, h3, m.q, m.qinv));
@@ -466,7 +486,15 @@ void launch_ks_inner2(Context* c, u64* acc, const u64* src, const u64* conv, con
         if (j < t.nparts) b += t.modup[j].nout;
     }
     dim3 grid((c->n / 2 + 255) / 256, t.nl + c->size_p);
-    launch_pdl(c, k_ks_inner, grid, 256, 0, acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n);
+#define KS_INNER_LAUNCH(NPV) launch_pdl(c, k_ks_inner<NPV>, grid, 256, 0, acc, src, conv, k.d, dm, t.nparts, t.nl, c->size_q, c->size_p, c->M(), c->d_mod, c->n)
+    switch (t.nparts) {
+        case 1: KS_INNER_LAUNCH(1); break;
+        case 2: KS_INNER_LAUNCH(2); break;
+        case 3: KS_INNER_LAUNCH(3); break;
+        case 4: KS_INNER_LAUNCH(4); break;
+        default: KS_INNER_LAUNCH(0); break;
+    }
+#undef KS_INNER_LAUNCH
 }
 
 // ApproxModDown epilogue for both polynomials h = 0,1 of a key switch:
