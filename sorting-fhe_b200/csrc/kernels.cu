@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(256) k_wsum_multi(const __grid_constant__ Wsum
         double s0[G], s1[G];
 #pragma unroll
         for (int g = 0; g < G; g++) { s0[g] = 0.0; s1[g] = 0.0; }
+#pragma unroll 4
         for (int i = 0; i < cnt; i++) {
             const u64x2 v = ld2(A.in[i], o);
             const double a0 = pw_from_u64(v.x), a1 = pw_from_u64(v.y);
@@ -321,7 +322,8 @@ __global__ void __launch_bounds__(256) k_ip_plain_multi(const __grid_constant__ 
         double s0[G], s1[G];
 #pragma unroll
         for (int g = 0; g < G; g++) { s0[g] = pw_from_u64(v0.x); s1[g] = pw_from_u64(v0.y); }
-        for (int i = 0; i < A.cnt; i++) {
+#pragma unroll 4
+        for (int i = 0; i < A.cnt; i++) {       // unrolled: the loads of four terms are in flight together
             const u64x2 a = ld2(A.ct[i], o);
             const double a0 = pw_from_u64(a.x), a1 = pw_from_u64(a.y);
 #pragma unroll
