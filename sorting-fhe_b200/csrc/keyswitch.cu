@@ -373,7 +373,10 @@ void launch_conv_batch(Context* c, u64* out, const u64* in, const ConvBatch& B) 
     double rows = 0; int max_in = 0, max_out = 0;
     for (int i = 0; i < B.ng; i++) { rows += B.g[i].nin + B.g[i].nout; max_in = std::max(max_in, B.g[i].nin); max_out = std::max(max_out, B.g[i].nout); }
     ProfScope ps(c, KC_BASECONV, 8.0 * c->n * rows);
-    static const int ysplit = getenv("CKKS_B200_CONV_YSPLIT") ? atoi(getenv("CKKS_B200_CONV_YSPLIT")) : 2;
+    // Outputs of a group can be split over `ysplit` CTAs per coefficient block (CKKS_B200_CONV_YSPLIT); every CTA converts the group's
+    // inputs to pieces itself, and one CTA per block measured best at every level: inside DirectSort N=128 ysplit 1 / 2 / 3 = 44.48 /
+    // 45.12 / 45.95 ms per sort, key switch at l = 32 466.1 vs 471.2 us (2 only from 17 / 24 / 30 outputs on: 44.81 / 44.71 / 44.70 ms).
+    static const int ysplit = getenv("CKKS_B200_CONV_YSPLIT") ? std::max(1, atoi(getenv("CKKS_B200_CONV_YSPLIT"))) : 1;
     static const bool generic = getenv("CKKS_B200_GENERIC_CONV") != nullptr;
     static const bool int_conv = getenv("CKKS_B200_INT_CONV") != nullptr;   // A/B switch: the integer-pipe kernel
     static const bool old_fp = getenv("CKKS_B200_OLD_CONV") != nullptr;                 // A/B switch: round 1's k_conv_fp
