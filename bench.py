@@ -445,7 +445,7 @@ def run_b200(args):
         try:
             # in-sort capture: every NTT launch of one steady-state sort under ncu (tools/prof_sort.py + tools/ncu_traffic_digest.py);
             # valid for the DirectSort N=128 ring 2^17 workload only -- other sizes report null
-            with open(os.path.join(ROOT, "profiles", "r05_ntt_traffic_in_sort.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r07_ntt_traffic_in_sort.json")) as f:
                 traffic_ratio = float(json.load(f)["traffic_over_algorithmic"]) if (n, log_n) == (128, 17) else None
         except Exception:
             traffic_ratio = None
@@ -469,7 +469,7 @@ def run_b200(args):
                          "traffic": traffic_ratio * prof_ntt["bytes"] / max(prof_ntt["launches"], 1) if traffic_ratio else None,
                          "traffic_note": ("DRAM bytes per average launch = algorithmic bytes per launch x %.2f, the dram read+write over "
                                           "algorithmic ratio summed over EVERY NTT launch of one steady-state sort of this workload captured "
-                                          "under ncu (profiles/r05_ntt_traffic_in_sort.json)" % traffic_ratio) if traffic_ratio else
+                                          "under ncu (profiles/r07_ntt_traffic_in_sort.json)" % traffic_ratio) if traffic_ratio else
                                          "no in-sort ncu capture for this workload",
                          "algorithmic_bytes_per_launch": prof_ntt["bytes"] / max(prof_ntt["launches"], 1),
                          "peak_source": peak_src, "launches": prof_ntt["launches"],
