@@ -91,6 +91,9 @@ int ckks_decrypt(ckks_ctx_t* ctx, const ckks_ct_t* ct, double* values, int count
 
 /* handle management + metadata (Clone, SetSlots/GetSlots, GetLevel, GetNoiseScaleDeg, GetScalingFactor) */
 int ckks_ct_free(ckks_ct_t* ct);
+/* ct->Clone() (src/sort_algo.h:330,433,563-566).  Copy-on-write: the clone shares the source's limbs -- and the rescaled /
+ * level-adjusted twins and ModUp digits cached on them -- until ckks_ct_set_slots, ckks_ct_mod_reduce or ckks_ct_device_ptr is
+ * applied to either handle; every evaluator entry point is out of place on its operands, so callers see value semantics. */
 int ckks_ct_clone(const ckks_ct_t* ct, ckks_ct_t** out);
 int ckks_ct_set_slots(ckks_ct_t* ct, int slots);
 /* what: 0 slots, 1 level, 2 noiseScaleDeg, 3 #limbs, 4 #polys */
