@@ -8,6 +8,7 @@
 // produce identical doubles and identical ciphertext limbs.
 #include "evaluator.h"
 #include <cmath>
+#include <cstring>
 #include <cstdlib>
 #include <memory>
 #include <stdexcept>
@@ -100,7 +101,9 @@ static CtP wsum(std::vector<CtP>& T, int cnt, const std::vector<double>& coeffs)
     std::vector<Ct*> cts(cnt); std::vector<double> w(cnt);
     for (int i = 0; i < cnt; i++) { cts[i] = T[i].get(); w[i] = coeffs[i + 1]; }
     if (g_wq) {
-        if (g_wq->next >= g_wq->items.size() || g_wq->items[g_wq->next].cnt != cnt || g_wq->items[g_wq->next].w != w)
+        // bitwise comparison: degenerate series (a zero divisor in the Chebyshev long division) carry NaN weights in both walks
+        if (g_wq->next >= g_wq->items.size() || g_wq->items[g_wq->next].cnt != cnt ||
+            std::memcmp(g_wq->items[g_wq->next].w.data(), w.data(), sizeof(double) * (size_t)cnt) != 0)
             throw std::runtime_error("internal: Paterson-Stockmeyer plan and evaluation disagree");
         return g_wq->res[g_wq->next++];
     }

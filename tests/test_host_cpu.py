@@ -112,3 +112,22 @@ def test_production_sampler_block_function_known_answers():
         kb, stream, idx = rng.bytes(32), int(rng.integers(0, 2 ** 63)), int(rng.integers(0, 2 ** 63))
         ks = Cipher(algorithms.ChaCha20(kb, struct.pack("<QQ", idx, stream)), mode=None).encryptor().update(b"\0" * 64)
         assert ks == sf.rng_block(kb, stream, idx)
+
+
+@pytest.mark.parametrize("degree", [5, 13, 27, 59, 119, 247, 495, 848])
+def test_paterson_stockmeyer_plan_matches_evaluation_dry_run(degree):
+    """cheby.cu forms the weighted sums of a Paterson-Stockmeyer evaluation ahead of the recursion, from a plan made on the
+    coefficients alone (ps_plan / wsum_precompute); the recursion then checks every sum it asks for against the plan and fails with
+    "plan and evaluation disagree" otherwise.  Dry-run contexts run the whole host schedule: every degree class the reference
+    reaches (g_4's 27, the sinc tables up to 848 of src/generated_doubled_sinc_coeffs.h) plus dense and sparse coefficient vectors"""
+    rng = np.random.default_rng(degree)
+    eng = sf.Engine(12, 14, 40, dry_run=True)
+    eng.KeyGen(); eng.EvalMultKeyGen()
+    x = eng.encrypt(eng.encode(np.linspace(-0.9, 0.9, 8), slots=8))
+    dense = rng.uniform(-1, 1, degree + 1)
+    sparse = dense.copy(); sparse[::2] = 0.0; sparse[-1] = 0.5          # odd polynomial, like the sign / sinc series
+    lead = np.zeros(degree + 1); lead[-1] = 1.0; lead[1] = 0.25           # almost empty: single-term leaves and short sums
+    for coeffs in (dense, sparse, lead):
+        y = eng.EvalChebyshevSeriesPS(x, coeffs.tolist())
+        assert y.level > x.level
+    eng.close()
