@@ -815,8 +815,7 @@ void launch_ntt_ex(Context* c, u64* dst, const u64* src, int rows, const LimbMod
     if (fuse) A.f = *fuse; else A.f = NttFuse{};
     A.tw = (const tw_t*)(inverse ? c->d_itw : c->d_tw);
     A.twd = inverse ? c->d_itwd : c->d_twd;
-    static const bool no_ot = getenv("CKKS_B200_NTT_NO_OT") != nullptr;   // A/B switch: last round's twiddles from the table
-    A.twb = no_ot ? nullptr : (inverse ? c->d_itwb : c->d_twb);
+    A.twb = inverse ? c->d_itwb : c->d_twb;   // nullptr under CKKS_B200_NO_OT_TWIDDLES=1 (context.cu): last round's twiddles from the table
     A.scale = (const tw_t*)(scale_pairs ? scale_pairs : ninv_pairs_for(c, lrep));
     for (int r0 = 0; r0 < rows; r0 += NTT_MAX_ROWS) {
         const int cnt = rows - r0 < NTT_MAX_ROWS ? rows - r0 : NTT_MAX_ROWS, total = cnt << tpr_log;
