@@ -43,11 +43,10 @@ def parse():
 
 
 class ClockSampler:
-    """SM clock and throttle reasons of one GPU, read through NVML IN THIS PROCESS: one sample per step, taken right after
-    the step's kernels have been enqueued (the GPU is working through them), so every sample falls inside the timed region.
-    NVML is initialised and queried once before the warm-up: the first query costs ~30 ms, later ones ~0.02 ms
-    (tools/nvml_probe.py on a B200: 63.9 ms per sort with and without them).  A separate sampling process -- round 1's
-    design -- stalled this process's kernel launches on the round-2 boxes: 64 -> 78-157 ms per sort."""
+    """SM clock and throttle reasons of one GPU, read through NVML IN THIS PROCESS while the kernels of the timed region's last step
+    run (three queries 10 ms apart on a helper thread that also loads NVML): see sample_burst_async for why not once per step.  A
+    separate sampling process -- round 1's design -- stalled this process's kernel launches on the round-2 boxes: 64 -> 78-157 ms
+    per sort."""
     BAD = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
